@@ -1,0 +1,305 @@
+"""Host-side mirror of the reference interface over the C-ABI (include/cm_gpu.h).
+
+The method names follow the reference's own seam (src/filter.h:46-62, src/match_read.h:45,
+src/chain.h:19): `split_match_hash`, `get_best_chains`, `process_read`.  This module only
+marshals numpy buffers into `libcm_gpu.so`; there is no CPU implementation behind it and
+it raises if the CUDA library is missing or no device is present.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "csrc", "libcm_gpu.so")
+
+CATEGORY = ["CONCRD", "DISCRD", "CHIORF", "CHIBSJ", "CHI2BSJ", "CONGEN", "CHIFUS", "CONGNM", "OEA2", "CANDID",
+            "OEANCH", "ORPHAN", "NOPROC_MANYHIT", "NOPROC_NOMATCH"]
+MAPPED_TYPES = (0, 1, 2, 3, 4, 5, 7)   # carry coordinates (src/filter.cpp:422-423)
+
+
+class CmParams(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "kmer", "max_read_len", "max_ed", "max_sc", "band_width", "seed_lim", "max_tlen", "max_intron_len",
+        "max_chain_len", "scan_level", "mat_sc", "mis_sc", "ind_sc", "xdrop")]
+
+
+class CmCounters(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in (
+        "seeds", "seed_sectors", "seed_hits", "chain_links", "xdrop_cells", "edit_cells", "xdrop_calls",
+        "edit_calls", "pairs", "kernel_launches")]
+
+    def as_dict(self):
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+
+
+_U4P = C.POINTER(C.c_uint32)
+
+
+class CmAnnotFlat(C.Structure):
+    _fields_ = [
+        ("n_iv", C.c_uint32),
+        ("iv_spos", C.c_void_p), ("iv_epos", C.c_void_p), ("iv_max_end", C.c_void_p), ("iv_min_end", C.c_void_p),
+        ("iv_max_next_exon", C.c_void_p), ("iv_seg_off", C.c_void_p),
+        ("n_seg", C.c_uint32),
+        ("seg_start", C.c_void_p), ("seg_end", C.c_void_p), ("seg_next_exon_beg", C.c_void_p),
+        ("seg_gene_id", C.c_void_p), ("seg_tid_off", C.c_void_p),
+        ("n_tid", C.c_uint32), ("tid", C.c_void_p),
+        ("n_trans", C.c_uint32), ("trans_start_ind", C.c_void_p), ("t2s_off", C.c_void_p), ("t2s", C.c_void_p),
+        ("n_genes", C.c_uint32), ("gene_start", C.c_void_p), ("gene_end", C.c_void_p),
+        ("n_chr", C.c_uint32), ("chr_shift", C.c_void_p), ("chr_id", C.c_void_p),
+        ("n_bits", C.c_uint64), ("near_border", C.c_void_p), ("intronic", C.c_void_p)]
+
+
+MREAD_DTYPE = np.dtype([
+    ("spos_r1", "<u4"), ("spos_r2", "<u4"), ("epos_r1", "<u4"), ("epos_r2", "<u4"),
+    ("qspos_r1", "<u4"), ("qspos_r2", "<u4"), ("qepos_r1", "<u4"), ("qepos_r2", "<u4"),
+    ("mlen_r1", "<u4"), ("mlen_r2", "<u4"), ("ed_r1", "<i4"), ("ed_r2", "<i4"), ("type", "<i4"),
+    ("tlen", "<i4"), ("contig_num", "<i4"), ("chr_r1", "<i4"), ("chr_r2", "<i4"), ("junc_num", "<u2"),
+    ("r1_forward", "u1"), ("r2_forward", "u1"), ("gm_compatible", "u1"), ("pad_", "u1", (3,))])
+assert MREAD_DTYPE.itemsize == 76
+
+MREAD_COMPARE_FIELDS = [f for f in MREAD_DTYPE.names if f != "pad_"]
+
+
+def default_params(**kw) -> CmParams:
+    p = CmParams(20, 300, 4, 7, 3, 500, 500, 2000000, 30, 0, 1, -3, -3, 8)
+    for k, v in kw.items():
+        setattr(p, k, v)
+    return p
+
+
+def fresh_mreads(n: int, max_ed: int = 4) -> np.ndarray:
+    """MatchedRead::MatchedRead(void) (src/common.cpp:268-271)."""
+    m = np.zeros(n, MREAD_DTYPE)
+    m["r1_forward"] = 1
+    m["r2_forward"] = 1
+    m["ed_r1"] = max_ed + 1
+    m["ed_r2"] = max_ed + 1
+    m["type"] = 13
+    m["tlen"] = 1000000000
+    m["chr_r1"] = -1
+    m["chr_r2"] = -1
+    return m
+
+
+class CmGpuError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen the CUDA library; fail loudly when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CmGpuError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'`. "
+                         "There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    lib.cm_gpu_last_error.restype = C.c_char_p
+    lib.cm_gpu_last_error.argtypes = [C.c_void_p]
+    _lib = lib
+    return lib
+
+
+def _vp(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _rows(seqs, lens=None):
+    """Accept a 2-D uint8/S1 array (fixed rows) and return (contiguous uint8 2-D, uint16 lens)."""
+    a = np.ascontiguousarray(seqs)
+    if a.dtype != np.uint8:
+        a = a.view(np.uint8)
+    if a.ndim != 2:
+        raise ValueError("reads must be a 2-D byte array [n, stride]")
+    if lens is None:
+        lens = np.full(a.shape[0], a.shape[1], np.uint16)
+    lens = np.ascontiguousarray(lens, np.uint16)
+    if len(lens) != a.shape[0]:
+        raise ValueError("len(lens) != number of rows")
+    return a, lens
+
+
+class Mapper:
+    """One context per GPU (threading contract of SURVEY.md 8(b))."""
+
+    def __init__(self, params: CmParams | None = None, device: int = 0):
+        self.lib = load_library()
+        self.params = params or default_params()
+        self.ctx = C.c_void_p()
+        r = self.lib.cm_gpu_create(device, C.byref(self.params), C.byref(self.ctx))
+        if r != 0:
+            raise CmGpuError(f"cm_gpu_create: {self.lib.cm_gpu_last_error(None).decode()} (status {r})")
+        k = self.params.kmer
+        self.S = 2 * ((self.params.max_read_len + k - 1) // k) - 1
+        self.F = (self.S + 1) // 2
+        self.Cn = self.params.max_chain_len
+        self._keep = []
+
+    def close(self):
+        if self.ctx:
+            self.lib.cm_gpu_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, r, what):
+        if r != 0:
+            raise CmGpuError(f"{what}: {self.lib.cm_gpu_last_error(self.ctx).decode()} (status {r})")
+
+    # ---- index / annotation ------------------------------------------------------------
+    def load_contig_from_reference(self, contig_id, bucket_lists, table_mem, table_mem_entries, cref_gen,
+                                   ref_gen_len):
+        """Raw pointers of the reference's in-memory index (see cm_gpu_load_contig)."""
+        self._chk(self.lib.cm_gpu_load_contig(self.ctx, contig_id, C.c_void_p(bucket_lists), C.c_void_p(table_mem),
+                                              C.c_uint64(table_mem_entries), C.c_void_p(cref_gen),
+                                              C.c_uint32(ref_gen_len)), "cm_gpu_load_contig")
+
+    def build_contig(self, contig_id, seq: np.ndarray):
+        seq = np.ascontiguousarray(seq, np.uint8)
+        self._chk(self.lib.cm_gpu_build_contig(self.ctx, contig_id, _vp(seq), C.c_uint32(len(seq))),
+                  "cm_gpu_build_contig")
+
+    def contig_stats(self, contig_id):
+        n = C.c_uint64()
+        ln = C.c_uint32()
+        self._chk(self.lib.cm_gpu_contig_stats(self.ctx, contig_id, C.byref(n), C.byref(ln)), "cm_gpu_contig_stats")
+        return n.value, ln.value
+
+    def read_bucket(self, contig_id, hv, cap=4096):
+        cks = np.zeros(cap, np.uint16)
+        pos = np.zeros(cap, np.uint32)
+        n = C.c_uint32()
+        self._chk(self.lib.cm_gpu_read_bucket(self.ctx, contig_id, C.c_uint32(hv), C.c_uint32(cap), _vp(cks), _vp(pos),
+                                              C.byref(n)), "cm_gpu_read_bucket")
+        m = min(n.value, cap)
+        return cks[:m], pos[:m], n.value
+
+    def load_annotation(self, contig_id, a: dict):
+        """`a` holds the flat arrays named as in cm_annot_flat (annotation.flatten / RefHarness.annotation)."""
+        f = CmAnnotFlat()
+        keep = []
+
+        def put(name, dtype):
+            arr = np.ascontiguousarray(a[name], dtype)
+            if arr.size == 0:
+                arr = np.zeros(1, dtype)
+            keep.append(arr)
+            setattr(f, name, arr.ctypes.data)
+
+        f.n_iv = int(a["n_iv"]); f.n_seg = int(a["n_seg"]); f.n_tid = int(a["n_tid"])
+        f.n_trans = int(a["n_trans"]); f.n_genes = int(a["n_genes"]); f.n_chr = int(a["n_chr"])
+        f.n_bits = int(a["n_bits"])
+        for nm in ("iv_spos", "iv_epos", "iv_max_end", "iv_min_end", "iv_max_next_exon", "iv_seg_off", "seg_start",
+                   "seg_end", "seg_next_exon_beg", "seg_gene_id", "seg_tid_off", "tid", "t2s_off", "gene_start",
+                   "gene_end", "chr_shift"):
+            put(nm, np.uint32)
+        put("trans_start_ind", np.int32)
+        put("chr_id", np.int32)
+        put("t2s", np.uint8)
+        put("near_border", np.uint64)
+        put("intronic", np.uint64)
+        self._chk(self.lib.cm_gpu_load_annotation(self.ctx, contig_id, C.byref(f)), "cm_gpu_load_annotation")
+
+    # ---- stages ---------------------------------------------------------------------------
+    def split_match_hash(self, contig_id, seqs, lens=None) -> dict:
+        """GenomeSeeder::split_match_hash for every row (src/match_read.cpp:270)."""
+        a, lens = _rows(seqs, lens)
+        n, S = a.shape[0], self.S
+        out = dict(qpos=np.zeros((n, S), np.int32), frag_count=np.zeros((n, S), np.uint32),
+                   has_frags=np.zeros((n, S), np.uint8), first_info=np.zeros((n, S), np.uint32),
+                   last_info=np.zeros((n, S), np.uint32), sum_info=np.zeros((n, S), np.uint64))
+        self._chk(self.lib.cm_gpu_seed_batch(self.ctx, contig_id, C.c_uint32(n), _vp(a), C.c_uint32(a.shape[1]),
+                                             _vp(lens), _vp(out["qpos"]), _vp(out["frag_count"]),
+                                             _vp(out["has_frags"]), _vp(out["first_info"]), _vp(out["last_info"]),
+                                             _vp(out["sum_info"])), "cm_gpu_seed_batch")
+        return out
+
+    def get_best_chains(self, contig_id, seqs, lens=None) -> dict:
+        """FilterRead::get_best_chains for every row (src/filter.cpp:469)."""
+        a, lens = _rows(seqs, lens)
+        n, Cn, F = a.shape[0], self.Cn, self.F
+        out = dict(chain_count=np.zeros(n, np.int32), high_hits=np.zeros(n, np.int32),
+                   score=np.zeros((n, Cn), np.float32), chain_len=np.zeros((n, Cn), np.uint32),
+                   frag_rpos=np.zeros((n, Cn, F), np.uint32), frag_qpos=np.zeros((n, Cn, F), np.int32))
+        self._chk(self.lib.cm_gpu_chain_batch(self.ctx, contig_id, C.c_uint32(n), _vp(a), C.c_uint32(a.shape[1]),
+                                              _vp(lens), _vp(out["chain_count"]), _vp(out["high_hits"]),
+                                              _vp(out["score"]), _vp(out["chain_len"]), _vp(out["frag_rpos"]),
+                                              _vp(out["frag_qpos"])), "cm_gpu_chain_batch")
+        return out
+
+    def align(self, kind, s, ns, t, nt, aux=None) -> dict:
+        s, ns = _rows(s, ns)
+        t, nt = _rows(t, nt)
+        if s.shape != t.shape:
+            raise ValueError("s and t must share shape")
+        n = s.shape[0]
+        aux = np.zeros(n, np.int32) if aux is None else np.ascontiguousarray(aux, np.int32)
+        o = [np.zeros(n, np.int32) for _ in range(4)]
+        self._chk(self.lib.cm_gpu_align_batch(self.ctx, kind, C.c_uint32(n), _vp(s), _vp(ns), _vp(t), _vp(nt),
+                                              C.c_uint32(s.shape[1]), _vp(aux), *[_vp(x) for x in o]),
+                  "cm_gpu_align_batch")
+        return dict(ed=o[0], sclen=o[1], indel=o[2], score=o[3])
+
+    def process_read(self, contig_id, seqs1, seqs2, mreads, lens1=None, lens2=None):
+        """FilterRead::process_read, PE overload, for a batch (src/filter.cpp:124)."""
+        a1, l1 = _rows(seqs1, lens1)
+        a2, l2 = _rows(seqs2, lens2)
+        if a1.shape != a2.shape:
+            raise ValueError("mate arrays must share shape")
+        n = a1.shape[0]
+        mreads = np.ascontiguousarray(mreads)
+        assert mreads.dtype == MREAD_DTYPE and len(mreads) == n
+        out = np.zeros(n, MREAD_DTYPE)
+        state = np.zeros(n, np.int32)
+        self._chk(self.lib.cm_gpu_process_batch_pe(self.ctx, contig_id, C.c_uint32(n), _vp(a1), _vp(a2),
+                                                   C.c_uint32(a1.shape[1]), _vp(l1), _vp(l2), _vp(mreads),
+                                                   _vp(out), _vp(state)), "cm_gpu_process_batch_pe")
+        return out, state
+
+    def process_read_se(self, contig_id, seqs, lens=None):
+        a, l = _rows(seqs, lens)
+        state = np.zeros(a.shape[0], np.int32)
+        self._chk(self.lib.cm_gpu_process_batch_se(self.ctx, contig_id, C.c_uint32(a.shape[0]), _vp(a),
+                                                   C.c_uint32(a.shape[1]), _vp(l), _vp(state)),
+                  "cm_gpu_process_batch_se")
+        return state
+
+    # ---- device-resident batch (kernel-only timing) -------------------------------------
+    def stage(self, seqs1, seqs2, mreads, lens1=None, lens2=None):
+        a1, l1 = _rows(seqs1, lens1)
+        a2, l2 = _rows(seqs2, lens2)
+        mreads = np.ascontiguousarray(mreads)
+        self._staged_n = a1.shape[0]
+        self._chk(self.lib.cm_gpu_stage_batch_pe(self.ctx, C.c_uint32(a1.shape[0]), _vp(a1), _vp(a2),
+                                                 C.c_uint32(a1.shape[1]), _vp(l1), _vp(l2), _vp(mreads)),
+                  "cm_gpu_stage_batch_pe")
+
+    def run_staged(self, contig_id, upto_stage=3):
+        self._chk(self.lib.cm_gpu_run_staged_pe(self.ctx, contig_id, upto_stage), "cm_gpu_run_staged_pe")
+
+    def fetch_staged(self):
+        out = np.zeros(self._staged_n, MREAD_DTYPE)
+        state = np.zeros(self._staged_n, np.int32)
+        self._chk(self.lib.cm_gpu_fetch_staged_pe(self.ctx, _vp(out), _vp(state)), "cm_gpu_fetch_staged_pe")
+        return out, state
+
+    def stage_ms(self):
+        a = (C.c_float * 5)()
+        self.lib.cm_gpu_last_stage_ms(self.ctx, a)
+        return list(a)
+
+    def counters(self, reset=False) -> dict:
+        c = CmCounters()
+        self._chk(self.lib.cm_gpu_get_counters(self.ctx, C.byref(c), int(reset)), "cm_gpu_get_counters")
+        return c.as_dict()

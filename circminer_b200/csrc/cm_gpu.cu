@@ -1,0 +1,741 @@
+// B200 (sm_100a) implementation of the C-ABI in include/cm_gpu.h.
+// Host runtime (context, HBM-resident index/annotation, batch staging) + kernels.
+// No CPU fallback: every entry point needs a CUDA device and fails with CM_ERR_CUDA otherwise.
+#include <cuda_runtime.h>
+#include <cub/cub.cuh>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "cm_types.h"
+#include "cm_seed.h"
+#include "cm_annot.h"
+#include "cm_chain.h"
+#include "cm_align.h"
+#include "cm_extend.h"
+#include "cm_filter.h"
+
+// ------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+struct ContigHost {
+    bool loaded = false;
+    ContigDev d{};
+    bool has_annot = false;
+    AnnotDev a{};
+    std::vector<void *> owned;        // device allocations of this contig
+    std::vector<void *> owned_annot;
+};
+
+struct cm_gpu_ctx {
+    int device = 0;
+    cm_params p{};
+    int max_seg_cnt = 0, n_slots = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[6]{};
+    std::string err;
+    std::vector<ContigHost> contigs;
+    cm_counters *d_counters = nullptr;
+    uint64_t launches = 0;
+    float stage_ms[5] = {0, 0, 0, 0, 0};
+
+    // staged batch (device resident)
+    uint32_t n_pairs = 0;      // pairs (PE) or reads (SE)
+    uint32_t n_strands = 0;    // 4 * pairs (PE) / 2 * reads (SE)
+    uint32_t stride = 0;       // device row stride of strand rows
+    bool staged_pe = false;
+    DevBuf in_seq1, in_seq2, in_len1, in_len2, in_mread;  // raw uploads
+    DevBuf strands, strand_len;                           // [n_strands][stride] fwd/rc rows, lengths
+    DevBuf seed_off, seed_cnt;                            // [n_strands][n_slots]
+    DevBuf cell_off;                                      // [n_strands + 1] dp-cell arena offsets
+    DevBuf rec_cnt, rec_off;                              // [n_strands (+1)] k-best record arena offsets
+    DevBuf dp_score, dp_prev, recs;                       // arenas
+    DevBuf chain_cnt, chain_hh, chain_hdr, chain_frags;   // chains per strand
+    DevBuf out_mread, out_state;
+    DevBuf cub_tmp;
+    DevBuf scratch[8];
+};
+
+static std::string g_create_err;
+
+static int fail(cm_gpu_ctx *ctx, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf; else g_create_err = buf;
+    return code;
+}
+
+#define CUDA_TRY(ctx, call)                                                                         \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess)                                                                      \
+            return fail(ctx, (e_ == cudaErrorMemoryAllocation) ? CM_ERR_ALLOC : CM_ERR_CUDA,        \
+                        "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));         \
+    } while (0)
+
+static int ensure(cm_gpu_ctx *ctx, DevBuf &b, size_t bytes) {
+    if (bytes <= b.cap) return CM_OK;
+    if (b.p) CUDA_TRY(ctx, cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    CUDA_TRY(ctx, cudaMalloc(&b.p, want));
+    b.cap = want;
+    return CM_OK;
+}
+#define ENSURE(ctx, buf, bytes)                      \
+    do {                                             \
+        int r_ = ensure(ctx, buf, bytes);            \
+        if (r_ != CM_OK) return r_;                  \
+    } while (0)
+
+static void release(DevBuf &b) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+}
+
+static inline unsigned grid_for(size_t n, unsigned block) { return (unsigned) ((n + block - 1) / block); }
+
+extern "C" void cm_params_default(cm_params *p) {
+    p->kmer = 20; p->max_read_len = 300; p->max_ed = 4; p->max_sc = 7; p->band_width = 3; p->seed_lim = 500;
+    p->max_tlen = 500; p->max_intron_len = 2000000; p->max_chain_len = 30; p->scan_level = 0;
+    p->mat_sc = 1; p->mis_sc = -3; p->ind_sc = -3; p->xdrop = 8;
+}
+
+extern "C" void cm_mread_init(cm_mread *m, const cm_params *p) {
+    memset(m, 0, sizeof *m);
+    m->r1_forward = 1; m->r2_forward = 1;
+    m->ed_r1 = p->max_ed + 1; m->ed_r2 = p->max_ed + 1;
+    m->type = CM_NOPROC_NOMATCH; m->tlen = CM_INF;
+    m->chr_r1 = -1; m->chr_r2 = -1;
+}
+
+extern "C" const char *cm_gpu_last_error(const cm_gpu_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **out) {
+    if (!params || !out) return fail(nullptr, CM_ERR_ARG, "null argument");
+    *out = nullptr;
+    const cm_params &p = *params;
+    if (p.kmer < CM_WINDOW || p.kmer > CM_WINDOW + 8)
+        return fail(nullptr, CM_ERR_ARG, "kmer must be in [14..22] (commandline_parser.cpp:243)");
+    if (p.band_width < 0 || p.band_width > CM_MAX_BAND) return fail(nullptr, CM_ERR_ARG, "band_width must be in [0..%d]", CM_MAX_BAND);
+    if (p.max_chain_len < 1 || p.max_chain_len > CM_MAX_CHAINS) return fail(nullptr, CM_ERR_ARG, "max_chain_len must be in [1..%d]", CM_MAX_CHAINS);
+    if (p.max_read_len < p.kmer || p.max_read_len > 600) return fail(nullptr, CM_ERR_ARG, "max_read_len must be in [kmer..600]");
+    if ((cm_max_seg_cnt(p) + 1) / 2 > CM_MAX_SEEDS) return fail(nullptr, CM_ERR_ARG, "too many seeds per read");
+    if (p.seed_lim < 1 || p.seed_lim > 65535) return fail(nullptr, CM_ERR_ARG, "seed_lim must be in [1..65535]");
+    if (p.max_ed < 0 || p.max_sc < 0 || p.max_ed > 64 || p.max_sc > 64) return fail(nullptr, CM_ERR_ARG, "max_ed/max_sc out of range");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0)
+        return fail(nullptr, CM_ERR_CUDA, "no CUDA device (%s); this library has no CPU path", cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(nullptr, CM_ERR_ARG, "device %d out of range (%d devices)", device, ndev);
+    cm_gpu_ctx *ctx = new cm_gpu_ctx;
+    ctx->device = device;
+    ctx->p = p;
+    ctx->max_seg_cnt = cm_max_seg_cnt(p);
+    ctx->n_slots = (ctx->max_seg_cnt + 1) / 2;
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete ctx;
+        return fail(nullptr, CM_ERR_CUDA, "cannot initialise device %d", device);
+    }
+    for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    if (cudaMalloc(&ctx->d_counters, sizeof(cm_counters)) != cudaSuccess) {
+        delete ctx;
+        return fail(nullptr, CM_ERR_ALLOC, "cudaMalloc counters");
+    }
+    cudaMemset(ctx->d_counters, 0, sizeof(cm_counters));
+    *out = ctx;
+    return CM_OK;
+}
+
+static void free_contig(ContigHost &c) {
+    for (void *p : c.owned) cudaFree(p);
+    for (void *p : c.owned_annot) cudaFree(p);
+    c = ContigHost();
+}
+
+extern "C" int cm_gpu_destroy(cm_gpu_ctx *ctx) {
+    if (!ctx) return CM_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto &c : ctx->contigs) free_contig(c);
+    DevBuf *bufs[] = {&ctx->in_seq1, &ctx->in_seq2, &ctx->in_len1, &ctx->in_len2, &ctx->in_mread, &ctx->strands,
+                      &ctx->strand_len, &ctx->seed_off, &ctx->seed_cnt, &ctx->cell_off, &ctx->rec_cnt, &ctx->rec_off,
+                      &ctx->dp_score, &ctx->dp_prev, &ctx->recs, &ctx->chain_cnt, &ctx->chain_hh, &ctx->chain_hdr,
+                      &ctx->chain_frags, &ctx->out_mread, &ctx->out_state, &ctx->cub_tmp};
+    for (DevBuf *b : bufs) release(*b);
+    for (auto &b : ctx->scratch) release(b);
+    cudaFree(ctx->d_counters);
+    for (auto &ev : ctx->ev) cudaEventDestroy(ev);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_get_counters(cm_gpu_ctx *ctx, cm_counters *out, int reset) {
+    if (!ctx || !out) return CM_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpy(out, ctx->d_counters, sizeof *out, cudaMemcpyDeviceToHost));
+    out->kernel_launches = ctx->launches;
+    if (reset) {
+        CUDA_TRY(ctx, cudaMemset(ctx->d_counters, 0, sizeof(cm_counters)));
+        ctx->launches = 0;
+    }
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_last_stage_ms(cm_gpu_ctx *ctx, float out[5]) {
+    if (!ctx || !out) return CM_ERR_ARG;
+    for (int i = 0; i < 5; i++) out[i] = ctx->stage_ms[i];
+    return CM_OK;
+}
+
+static ContigHost *get_contig(cm_gpu_ctx *ctx, int contig_id, bool create) {
+    if (contig_id < 0 || contig_id > 4095) return nullptr;
+    if ((size_t) contig_id >= ctx->contigs.size()) {
+        if (!create) return nullptr;
+        ctx->contigs.resize(contig_id + 1);
+    }
+    return &ctx->contigs[contig_id];
+}
+
+template <typename T>
+static int dev_alloc(cm_gpu_ctx *ctx, std::vector<void *> &owned, T **out, size_t count) {
+    void *p = nullptr;
+    CUDA_TRY(ctx, cudaMalloc(&p, (count ? count : 1) * sizeof(T)));
+    owned.push_back(p);
+    *out = (T *) p;
+    return CM_OK;
+}
+
+template <typename T>
+static int dev_upload(cm_gpu_ctx *ctx, std::vector<void *> &owned, const T **out, const T *src, size_t count) {
+    T *p = nullptr;
+    int r = dev_alloc(ctx, owned, &p, count);
+    if (r != CM_OK) return r;
+    if (count) CUDA_TRY(ctx, cudaMemcpy(p, src, count * sizeof(T), cudaMemcpyHostToDevice));
+    *out = p;
+    return CM_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// index: upload of the reference's in-memory layout
+// ------------------------------------------------------------------------------------------
+#pragma pack(push, 1)
+struct GeneralIndexPacked {   // lib/mrsfast/Common.h:105-111
+    uint16_t checksum;
+    uint32_t info;
+};
+#pragma pack(pop)
+
+// 3-bit packed genome (21 bases / word, MSB first; Common.c:174-196) -> ASCII at genome[1..len]
+__global__ void k_unpack_cref(const uint64_t *__restrict__ cref, uint32_t len, uint8_t *__restrict__ genome) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;   // 0-based base index
+    if (i >= len) return;
+    uint64_t w = cref[i / 21];
+    int v = (int) ((w >> (60 - 3 * (i % 21))) & 7);
+    const char lut[8] = {'A', 'C', 'G', 'T', 'N', 'N', 'N', 'N'};   // GenomeSeeder::init, match_read.cpp:15-23
+    genome[i + 1] = lut[v];
+}
+
+extern "C" int cm_gpu_load_contig(cm_gpu_ctx *ctx, int contig_id, const void *const *bucket_lists, const void *table_mem,
+                                  uint64_t table_mem_entries, const uint64_t *cref_gen, uint32_t ref_gen_len) {
+    if (!ctx) return CM_ERR_ARG;
+    if (!bucket_lists || !table_mem || !cref_gen) return fail(ctx, CM_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->device);
+    ContigHost *ch = get_contig(ctx, contig_id, true);
+    if (!ch) return fail(ctx, CM_ERR_ARG, "bad contig id %d", contig_id);
+    free_contig(*ch);
+    const GeneralIndexPacked *mem = (const GeneralIndexPacked *) table_mem;
+    // directory + SoA split on the host (one pass over the buckets, like setHashTablePointers, HashTable.c:1074)
+    std::vector<uint32_t> dir((size_t) CM_NBUCKETS + 1);
+    uint64_t total = 0;
+    for (uint32_t hv = 0; hv < CM_NBUCKETS; hv++) {
+        dir[hv] = (uint32_t) total;
+        const GeneralIndexPacked *l = (const GeneralIndexPacked *) bucket_lists[hv];
+        if (l) {
+            if (l < mem || (uint64_t) (l - mem) + l[0].info + 1 > table_mem_entries)
+                return fail(ctx, CM_ERR_ARG, "bucket %u points outside table_mem", hv);
+            total += l[0].info;
+        }
+    }
+    if (total > 0xFFFFFFFFull) return fail(ctx, CM_ERR_ARG, "more than 2^32 index entries");
+    dir[CM_NBUCKETS] = (uint32_t) total;
+    std::vector<uint16_t> cks(total);
+    std::vector<uint32_t> pos(total);
+    for (uint32_t hv = 0; hv < CM_NBUCKETS; hv++) {
+        const GeneralIndexPacked *l = (const GeneralIndexPacked *) bucket_lists[hv];
+        if (!l) continue;
+        uint32_t n = l[0].info, o = dir[hv];
+        for (uint32_t j = 0; j < n; j++) {
+            cks[o + j] = l[1 + j].checksum;
+            pos[o + j] = l[1 + j].info;
+        }
+    }
+    int r;
+    if ((r = dev_upload(ctx, ch->owned, &ch->d.dir, dir.data(), dir.size())) != CM_OK) return r;
+    if ((r = dev_upload(ctx, ch->owned, &ch->d.cks, cks.data(), cks.size())) != CM_OK) return r;
+    if ((r = dev_upload(ctx, ch->owned, &ch->d.pos, pos.data(), pos.size())) != CM_OK) return r;
+    size_t nwords = (size_t) ref_gen_len / 21 + 1;
+    const uint64_t *d_cref = nullptr;
+    std::vector<void *> tmp;
+    if ((r = dev_upload(ctx, tmp, &d_cref, cref_gen, (ref_gen_len + 20) / 21)) != CM_OK) return r;
+    (void) nwords;
+    uint8_t *genome = nullptr;
+    if ((r = dev_alloc(ctx, ch->owned, &genome, (size_t) ref_gen_len + 64)) != CM_OK) return r;
+    CUDA_TRY(ctx, cudaMemsetAsync(genome, 'N', (size_t) ref_gen_len + 64, ctx->stream));
+    if (ref_gen_len) {
+        k_unpack_cref<<<grid_for(ref_gen_len, 256), 256, 0, ctx->stream>>>(d_cref, ref_gen_len, genome);
+        ctx->launches++;
+    }
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    for (void *p : tmp) cudaFree(p);
+    ch->d.genome = genome;
+    ch->d.n_entries = total;
+    ch->d.ref_len = ref_gen_len;
+    ch->loaded = true;
+    return CM_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// index: device-side build (count -> scan -> scatter/sort), HashTable.c:769-839 semantics
+// ------------------------------------------------------------------------------------------
+// key = hv (28 bits) << 16 | checksum (<= 16 bits); one thread per k-mer start (0-based i, loc = i+1)
+__global__ void k_kmer_keys(const uint8_t *__restrict__ genome /*1-based*/, uint32_t len, int kmer,
+                            uint64_t *__restrict__ keys, uint32_t *__restrict__ locs, uint8_t *__restrict__ valid) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= len) return;
+    uint8_t ok = 0;
+    uint64_t key = 0;
+    if (i + kmer <= len) {
+        ok = 1;
+        for (int j = 0; j < kmer; j++) {
+            int v = cm_nhval(genome[1 + i + j]);
+            if (v < 0) { ok = 0; break; }
+            key = (key << 2) | (uint64_t) v;
+        }
+        if (ok) {
+            int cs = kmer - CM_WINDOW;
+            uint64_t hv = key >> (2 * cs);
+            uint64_t cv = key & ((1ull << (2 * cs)) - 1);
+            key = (hv << 16) | cv;
+        }
+    }
+    keys[i] = key;
+    locs[i] = i + 1;
+    valid[i] = ok;
+}
+
+__global__ void k_bucket_hist(const uint64_t *__restrict__ keys, uint64_t n, uint32_t *__restrict__ dir) {
+    uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    atomicAdd(&dir[(uint32_t) (keys[i] >> 16)], 1u);
+}
+
+__global__ void k_split_keys(const uint64_t *__restrict__ keys, uint64_t n, uint16_t *__restrict__ cks) {
+    uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    cks[i] = (uint16_t) (keys[i] & 0xFFFF);
+}
+
+__global__ void k_ascii_to_genome(const char *__restrict__ seq, uint32_t len, uint8_t *__restrict__ genome) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= len) return;
+    uint8_t c = (uint8_t) seq[i];
+    // nVal (Common.c:229-233): upper-case ACGT kept, everything else is N
+    genome[i + 1] = (c == 'A' || c == 'C' || c == 'G' || c == 'T') ? c : 'N';
+}
+
+extern "C" int cm_gpu_build_contig(cm_gpu_ctx *ctx, int contig_id, const char *contig_seq, uint32_t ref_gen_len) {
+    if (!ctx) return CM_ERR_ARG;
+    if (!contig_seq) return fail(ctx, CM_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->device);
+    ContigHost *ch = get_contig(ctx, contig_id, true);
+    if (!ch) return fail(ctx, CM_ERR_ARG, "bad contig id %d", contig_id);
+    free_contig(*ch);
+    cudaStream_t st = ctx->stream;
+    int r;
+    const uint32_t len = ref_gen_len;
+    uint8_t *genome = nullptr;
+    if ((r = dev_alloc(ctx, ch->owned, &genome, (size_t) len + 64)) != CM_OK) return r;
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *p : tmp) cudaFree(p); };
+    char *d_seq = nullptr;
+    if ((r = dev_alloc(ctx, tmp, &d_seq, (size_t) len)) != CM_OK) { cleanup(); return r; }
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_seq, contig_seq, len, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(genome, 'N', (size_t) len + 64, st));
+    uint64_t *keys = nullptr, *keys_sel = nullptr, *keys_alt = nullptr;
+    uint32_t *locs = nullptr, *locs_sel = nullptr, *locs_alt = nullptr, *dirc = nullptr, *d_nsel = nullptr;
+    uint8_t *valid = nullptr;
+    if ((r = dev_alloc(ctx, tmp, &keys, (size_t) len)) != CM_OK || (r = dev_alloc(ctx, tmp, &locs, (size_t) len)) != CM_OK ||
+        (r = dev_alloc(ctx, tmp, &valid, (size_t) len)) != CM_OK || (r = dev_alloc(ctx, tmp, &keys_sel, (size_t) len)) != CM_OK ||
+        (r = dev_alloc(ctx, tmp, &locs_sel, (size_t) len)) != CM_OK || (r = dev_alloc(ctx, tmp, &d_nsel, 2)) != CM_OK ||
+        (r = dev_alloc(ctx, ch->owned, &dirc, (size_t) CM_NBUCKETS + 1)) != CM_OK) { cleanup(); return r; }
+    if (len) {
+        k_ascii_to_genome<<<grid_for(len, 256), 256, 0, st>>>(d_seq, len, genome);
+        k_kmer_keys<<<grid_for(len, 256), 256, 0, st>>>(genome, len, ctx->p.kmer, keys, locs, valid);
+        ctx->launches += 2;
+    }
+    // compact valid k-mers (ascending position)
+    size_t tb1 = 0, tb2 = 0, tb3 = 0, tb4 = 0;
+    cub::DeviceSelect::Flagged(nullptr, tb1, keys, valid, keys_sel, d_nsel, (int64_t) len, st);
+    cub::DeviceSelect::Flagged(nullptr, tb2, locs, valid, locs_sel, d_nsel, (int64_t) len, st);
+    cub::DoubleBuffer<uint64_t> kb(keys_sel, keys);
+    cub::DoubleBuffer<uint32_t> vb(locs_sel, locs);
+    cub::DeviceRadixSort::SortPairs(nullptr, tb3, kb, vb, (int64_t) len, 0, 44, st);
+    cub::DeviceScan::ExclusiveSum(nullptr, tb4, dirc, dirc, (int64_t) CM_NBUCKETS + 1, st);
+    size_t tb = tb1 > tb2 ? tb1 : tb2;
+    if (tb3 > tb) tb = tb3;
+    if (tb4 > tb) tb = tb4;
+    void *d_tmp = nullptr;
+    if ((r = dev_alloc(ctx, tmp, (uint8_t **) &d_tmp, tb + 16)) != CM_OK) { cleanup(); return r; }
+    uint32_t nsel = 0;
+    if (len) {
+        cub::DeviceSelect::Flagged(d_tmp, tb, keys, valid, keys_sel, d_nsel, (int64_t) len, st);
+        cub::DeviceSelect::Flagged(d_tmp, tb, locs, valid, locs_sel, d_nsel, (int64_t) len, st);
+        CUDA_TRY(ctx, cudaMemcpyAsync(&nsel, d_nsel, sizeof nsel, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    }
+    // stable LSD radix sort over (hv, checksum): positions stay ascending inside equal keys,
+    // i.e. the (checksum, info) total order of Sort.c:110-176 inside each bucket
+    if (nsel) {
+        cub::DeviceRadixSort::SortPairs(d_tmp, tb, kb, vb, (int64_t) nsel, 0, 44, st);
+    }
+    CUDA_TRY(ctx, cudaMemsetAsync(dirc, 0, ((size_t) CM_NBUCKETS + 1) * sizeof(uint32_t), st));
+    uint16_t *cks = nullptr;
+    uint32_t *pos = nullptr;
+    if ((r = dev_alloc(ctx, ch->owned, &cks, (size_t) nsel)) != CM_OK || (r = dev_alloc(ctx, ch->owned, &pos, (size_t) nsel)) != CM_OK) {
+        cleanup();
+        return r;
+    }
+    if (nsel) {
+        k_bucket_hist<<<grid_for(nsel, 256), 256, 0, st>>>(kb.Current(), nsel, dirc);
+        k_split_keys<<<grid_for(nsel, 256), 256, 0, st>>>(kb.Current(), nsel, cks);
+        CUDA_TRY(ctx, cudaMemcpyAsync(pos, vb.Current(), (size_t) nsel * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+        ctx->launches += 2;
+    }
+    cub::DeviceScan::ExclusiveSum(d_tmp, tb, dirc, dirc, (int64_t) CM_NBUCKETS + 1, st);
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, cudaGetLastError());
+    cleanup();
+    ch->d.dir = dirc;
+    ch->d.cks = cks;
+    ch->d.pos = pos;
+    ch->d.genome = genome;
+    ch->d.n_entries = nsel;
+    ch->d.ref_len = len;
+    ch->loaded = true;
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_contig_stats(cm_gpu_ctx *ctx, int contig_id, uint64_t *n_entries, uint32_t *ref_gen_len) {
+    if (!ctx) return CM_ERR_ARG;
+    ContigHost *ch = get_contig(ctx, contig_id, false);
+    if (!ch || !ch->loaded) return fail(ctx, CM_ERR_STATE, "contig %d not loaded", contig_id);
+    if (n_entries) *n_entries = ch->d.n_entries;
+    if (ref_gen_len) *ref_gen_len = ch->d.ref_len;
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_read_bucket(cm_gpu_ctx *ctx, int contig_id, uint32_t hv, uint32_t cap, uint16_t *checksum,
+                                  uint32_t *pos, uint32_t *n) {
+    if (!ctx || !n) return CM_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    ContigHost *ch = get_contig(ctx, contig_id, false);
+    if (!ch || !ch->loaded) return fail(ctx, CM_ERR_STATE, "contig %d not loaded", contig_id);
+    if (hv >= CM_NBUCKETS) return fail(ctx, CM_ERR_ARG, "hv out of range");
+    uint32_t d[2];
+    CUDA_TRY(ctx, cudaMemcpy(d, ch->d.dir + hv, sizeof d, cudaMemcpyDeviceToHost));
+    uint32_t cnt = d[1] - d[0];
+    *n = cnt;
+    uint32_t m = cnt < cap ? cnt : cap;
+    if (m && checksum) CUDA_TRY(ctx, cudaMemcpy(checksum, ch->d.cks + d[0], m * sizeof(uint16_t), cudaMemcpyDeviceToHost));
+    if (m && pos) CUDA_TRY(ctx, cudaMemcpy(pos, ch->d.pos + d[0], m * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    return CM_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// annotation upload
+// ------------------------------------------------------------------------------------------
+extern "C" int cm_gpu_load_annotation(cm_gpu_ctx *ctx, int contig_id, const cm_annot_flat *A) {
+    if (!ctx) return CM_ERR_ARG;
+    if (!A) return fail(ctx, CM_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->device);
+    ContigHost *ch = get_contig(ctx, contig_id, true);
+    if (!ch) return fail(ctx, CM_ERR_ARG, "bad contig id %d", contig_id);
+    for (void *p : ch->owned_annot) cudaFree(p);
+    ch->owned_annot.clear();
+    ch->has_annot = false;
+    if (A->n_iv == 0) return fail(ctx, CM_ERR_ARG, "annotation needs at least the dummy interval (gene_annotation.cpp:368-382)");
+    if (A->n_chr == 0) return fail(ctx, CM_ERR_ARG, "annotation needs the contig's chromosome table");
+    AnnotDev &a = ch->a;
+    a = AnnotDev();
+    int r;
+    auto &own = ch->owned_annot;
+#define UP(field, count)                                                                  \
+    if ((r = dev_upload(ctx, own, &a.field, A->field, (size_t) (count))) != CM_OK) return r;
+    a.n_iv = A->n_iv; a.n_seg = A->n_seg; a.n_trans = A->n_trans; a.n_genes = A->n_genes; a.n_chr = A->n_chr;
+    a.n_bits = A->n_bits;
+    UP(iv_spos, A->n_iv) UP(iv_epos, A->n_iv) UP(iv_max_end, A->n_iv) UP(iv_min_end, A->n_iv)
+    UP(iv_max_next_exon, A->n_iv) UP(iv_seg_off, A->n_iv + 1)
+    UP(seg_start, A->n_seg) UP(seg_end, A->n_seg) UP(seg_next_exon_beg, A->n_seg) UP(seg_gene_id, A->n_seg)
+    UP(seg_tid_off, A->n_seg + 1) UP(tid, A->n_tid)
+    UP(trans_start_ind, A->n_trans) UP(t2s_off, A->n_trans + 1)
+    {
+        uint32_t n_t2s = 0;
+        if (A->n_trans) n_t2s = A->t2s_off[A->n_trans];
+        UP(t2s, n_t2s)
+    }
+    UP(gene_start, A->n_genes) UP(gene_end, A->n_genes) UP(chr_shift, A->n_chr) UP(chr_id, A->n_chr)
+    UP(near_border, (A->n_bits + 63) / 64) UP(intronic, (A->n_bits + 63) / 64)
+#undef UP
+    ch->has_annot = true;
+    return CM_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// batch staging
+// ------------------------------------------------------------------------------------------
+// strand rows: PE pair i -> strands 4i (R1 fwd), 4i+1 (R1 rc), 4i+2 (R2 fwd), 4i+3 (R2 rc)
+//              SE read i -> strands 2i (fwd), 2i+1 (rc)
+__global__ void k_make_strands(const char *__restrict__ s1, const char *__restrict__ s2, const uint16_t *__restrict__ l1,
+                               const uint16_t *__restrict__ l2, uint32_t n, uint32_t in_stride, uint32_t stride,
+                               uint8_t *__restrict__ strands, uint16_t *__restrict__ slen) {
+    // one warp per input read
+    uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    uint32_t n_reads = s2 ? 2 * n : n;
+    if (warp >= n_reads) return;
+    uint32_t i = s2 ? warp >> 1 : warp;
+    bool second = s2 && (warp & 1);
+    const char *src = (second ? s2 : s1) + (size_t) i * in_stride;
+    uint32_t len = second ? l2[i] : l1[i];
+    uint8_t *fw = strands + (size_t) (2 * warp) * stride;
+    uint8_t *rc = fw + stride;
+    for (uint32_t j = lane; j < stride; j += 32) {
+        fw[j] = j < len ? (uint8_t) src[j] : 0;
+        rc[j] = j < len ? cm_comp((uint8_t) src[len - 1 - j]) : 0;
+    }
+    if (lane == 0) {
+        slen[2 * warp] = (uint16_t) len;
+        slen[2 * warp + 1] = (uint16_t) len;
+    }
+}
+
+static int stage_reads(cm_gpu_ctx *ctx, uint32_t n, const char *s1, const char *s2, uint32_t in_stride,
+                       const uint16_t *l1, const uint16_t *l2, const cm_mread *in) {
+    if (n == 0) { ctx->n_pairs = 0; ctx->n_strands = 0; return CM_OK; }
+    if (!s1 || !l1 || (s2 && !l2)) return fail(ctx, CM_ERR_ARG, "null argument");
+    if (in_stride == 0) return fail(ctx, CM_ERR_ARG, "stride is 0");
+    for (uint32_t i = 0; i < n; i++) {
+        if (l1[i] > in_stride || (s2 && l2[i] > in_stride)) return fail(ctx, CM_ERR_ARG, "read %u longer than stride", i);
+        if (l1[i] > ctx->p.max_read_len || (s2 && l2[i] > ctx->p.max_read_len))
+            return fail(ctx, CM_ERR_ARG, "read %u longer than max_read_len", i);
+        if (l1[i] == 0 || (s2 && l2[i] == 0)) return fail(ctx, CM_ERR_ARG, "read %u is empty (fastq_parser.cpp:157 would underflow)", i);
+    }
+    cudaStream_t st = ctx->stream;
+    uint32_t stride = (uint32_t) ((ctx->p.max_read_len + 15) / 16 * 16);
+    uint32_t n_strands = (s2 ? 4u : 2u) * n;
+    ENSURE(ctx, ctx->in_seq1, (size_t) n * in_stride);
+    ENSURE(ctx, ctx->in_len1, (size_t) n * 2);
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->in_seq1.p, s1, (size_t) n * in_stride, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->in_len1.p, l1, (size_t) n * 2, cudaMemcpyHostToDevice, st));
+    if (s2) {
+        ENSURE(ctx, ctx->in_seq2, (size_t) n * in_stride);
+        ENSURE(ctx, ctx->in_len2, (size_t) n * 2);
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->in_seq2.p, s2, (size_t) n * in_stride, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->in_len2.p, l2, (size_t) n * 2, cudaMemcpyHostToDevice, st));
+    }
+    ENSURE(ctx, ctx->in_mread, (size_t) n * sizeof(cm_mread));
+    if (in) CUDA_TRY(ctx, cudaMemcpyAsync(ctx->in_mread.p, in, (size_t) n * sizeof(cm_mread), cudaMemcpyHostToDevice, st));
+    ENSURE(ctx, ctx->strands, (size_t) n_strands * stride);
+    ENSURE(ctx, ctx->strand_len, (size_t) n_strands * 2);
+    ctx->n_pairs = n;
+    ctx->n_strands = n_strands;
+    ctx->stride = stride;
+    ctx->staged_pe = s2 != nullptr;
+    return CM_OK;
+}
+
+static int launch_prep(cm_gpu_ctx *ctx, uint32_t in_stride) {
+    if (!ctx->n_pairs) return CM_OK;
+    uint32_t n_reads = ctx->staged_pe ? 2 * ctx->n_pairs : ctx->n_pairs;
+    k_make_strands<<<grid_for((size_t) n_reads * 32, 256), 256, 0, ctx->stream>>>(
+        (const char *) ctx->in_seq1.p, ctx->staged_pe ? (const char *) ctx->in_seq2.p : nullptr,
+        (const uint16_t *) ctx->in_len1.p, (const uint16_t *) ctx->in_len2.p, ctx->n_pairs, in_stride, ctx->stride,
+        (uint8_t *) ctx->strands.p, (uint16_t *) ctx->strand_len.p);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return CM_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// K1: seed lookup.  One thread per (strand, seed slot).  The dependent gather chain is
+// directory (8 B) -> checksum run (2 B each, binary search); positions are NOT copied:
+// chaining reads them in place through (off, cnt).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_seed(DevView v, const uint8_t *__restrict__ strands, const uint16_t *__restrict__ slen,
+                                              uint32_t n_strands, uint32_t stride, uint32_t *__restrict__ seed_off,
+                                              uint32_t *__restrict__ seed_cnt, cm_counters *__restrict__ ctr) {
+    const int ns = v.n_slots;
+    uint64_t gid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t strand = (uint32_t) (gid / ns), slot = (uint32_t) (gid % ns);
+    uint32_t sectors = 0, hits = 0, looked = 0;
+    if (strand < n_strands) {
+        int len = slen[strand];
+        int q = (int) slot * v.p.kmer;
+        SeedHit h;
+        h.off = 0;
+        h.cnt = 0;
+        if (q + v.p.kmer <= len) {
+            int hv, cv;
+            cm_hash_kmer(strands + (size_t) strand * stride + q, v.p.kmer, hv, cv);
+            h = cm_seed_lookup(v.c, hv, cv, &sectors);
+            looked = 1;
+            uint32_t kept = h.cnt > (uint32_t) v.p.seed_lim ? 0 : h.cnt;
+            hits = kept;
+            sectors += (6 * kept) / 32;
+        }
+        seed_off[gid] = h.off;
+        seed_cnt[gid] = h.cnt;
+    }
+    // warp-aggregated counters (roofline numerators)
+    for (int o = 16; o; o >>= 1) {
+        sectors += __shfl_down_sync(0xffffffffu, sectors, o);
+        hits += __shfl_down_sync(0xffffffffu, hits, o);
+        looked += __shfl_down_sync(0xffffffffu, looked, o);
+    }
+    if ((threadIdx.x & 31) == 0 && looked) {
+        atomicAdd((unsigned long long *) &ctr->seeds, (unsigned long long) looked);
+        atomicAdd((unsigned long long *) &ctr->seed_sectors, (unsigned long long) sectors);
+        atomicAdd((unsigned long long *) &ctr->seed_hits, (unsigned long long) hits);
+    }
+}
+
+static int make_view(cm_gpu_ctx *ctx, int contig_id, bool need_annot, DevView &v) {
+    ContigHost *ch = get_contig(ctx, contig_id, false);
+    if (!ch || !ch->loaded) return fail(ctx, CM_ERR_STATE, "contig %d not loaded (call cm_gpu_load_contig / cm_gpu_build_contig)", contig_id);
+    if (need_annot && !ch->has_annot) return fail(ctx, CM_ERR_STATE, "contig %d has no annotation (call cm_gpu_load_annotation)", contig_id);
+    v.p = ctx->p;
+    v.c = ch->d;
+    v.a = ch->has_annot ? ch->a : AnnotDev();
+    v.contig_id = contig_id;
+    v.max_seg_cnt = ctx->max_seg_cnt;
+    v.n_slots = ctx->n_slots;
+    return CM_OK;
+}
+
+static int launch_seed(cm_gpu_ctx *ctx, const DevView &v) {
+    if (!ctx->n_strands) return CM_OK;
+    size_t total = (size_t) ctx->n_strands * ctx->n_slots;
+    ENSURE(ctx, ctx->seed_off, total * 4);
+    ENSURE(ctx, ctx->seed_cnt, total * 4);
+    k_seed<<<grid_for(total, 256), 256, 0, ctx->stream>>>(v, (const uint8_t *) ctx->strands.p, (const uint16_t *) ctx->strand_len.p,
+                                                         ctx->n_strands, ctx->stride, (uint32_t *) ctx->seed_off.p,
+                                                         (uint32_t *) ctx->seed_cnt.p, ctx->d_counters);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return CM_OK;
+}
+
+// per-slot summary for the stage-level parity entry
+__global__ void k_seed_summary(DevView v, const uint16_t *__restrict__ slen, uint32_t n_strands, const uint32_t *__restrict__ seed_off,
+                               const uint32_t *__restrict__ seed_cnt, int32_t *__restrict__ qpos, uint32_t *__restrict__ frag_count,
+                               uint8_t *__restrict__ has_frags, uint32_t *__restrict__ first_info, uint32_t *__restrict__ last_info,
+                               unsigned long long *__restrict__ sum_info) {
+    const int S = v.max_seg_cnt;
+    uint64_t gid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (uint64_t) n_strands * S) return;
+    uint32_t strand = (uint32_t) (gid / S), s = (uint32_t) (gid % S);
+    int32_t q = 0;
+    uint32_t fc = 0, fi = 0, li = 0;
+    uint8_t hf = 0;
+    unsigned long long sum = 0;
+    if ((s & 1) == 0) {
+        uint32_t slot = s >> 1;
+        int len = slen[strand];
+        if ((int) (slot * v.p.kmer + v.p.kmer) <= len) {
+            q = (int32_t) (slot * v.p.kmer);
+            uint32_t cnt = seed_cnt[(size_t) strand * v.n_slots + slot], off = seed_off[(size_t) strand * v.n_slots + slot];
+            hf = cnt > 0;
+            fc = cnt > (uint32_t) v.p.seed_lim ? 0 : cnt;
+            if (fc) {
+                fi = v.c.pos[off];
+                li = v.c.pos[off + fc - 1];
+                for (uint32_t j = 0; j < fc; j++) sum += v.c.pos[off + j];
+            }
+        }
+    }
+    qpos[gid] = q;
+    frag_count[gid] = fc;
+    has_frags[gid] = hf;
+    first_info[gid] = fi;
+    last_info[gid] = li;
+    sum_info[gid] = sum;
+}
+
+template <typename T>
+static int fetch(cm_gpu_ctx *ctx, T *host, const void *dev, size_t count) {
+    if (!host || !count) return CM_OK;
+    CUDA_TRY(ctx, cudaMemcpyAsync(host, dev, count * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_seed_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride,
+                                 const uint16_t *len, int32_t *qpos, uint32_t *frag_count, uint8_t *has_frags,
+                                 uint32_t *first_info, uint32_t *last_info, uint64_t *sum_info) {
+    if (!ctx) return CM_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    DevView v;
+    int r = make_view(ctx, contig_id, false, v);
+    if (r != CM_OK) return r;
+    if (n == 0) return CM_OK;
+    // each input row is ONE strand here: stage as SE and keep only the forward rows
+    if ((r = stage_reads(ctx, n, seqs, nullptr, stride, len, nullptr, nullptr)) != CM_OK) return r;
+    if ((r = launch_prep(ctx, stride)) != CM_OK) return r;
+    if ((r = launch_seed(ctx, v)) != CM_OK) return r;
+    size_t total = (size_t) ctx->n_strands * ctx->max_seg_cnt;
+    ENSURE(ctx, ctx->scratch[0], total * 4);
+    ENSURE(ctx, ctx->scratch[1], total * 4);
+    ENSURE(ctx, ctx->scratch[2], total);
+    ENSURE(ctx, ctx->scratch[3], total * 4);
+    ENSURE(ctx, ctx->scratch[4], total * 4);
+    ENSURE(ctx, ctx->scratch[5], total * 8);
+    k_seed_summary<<<grid_for(total, 256), 256, 0, ctx->stream>>>(
+        v, (const uint16_t *) ctx->strand_len.p, ctx->n_strands, (const uint32_t *) ctx->seed_off.p, (const uint32_t *) ctx->seed_cnt.p,
+        (int32_t *) ctx->scratch[0].p, (uint32_t *) ctx->scratch[1].p, (uint8_t *) ctx->scratch[2].p, (uint32_t *) ctx->scratch[3].p,
+        (uint32_t *) ctx->scratch[4].p, (unsigned long long *) ctx->scratch[5].p);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    // rows 2i are the forward strands
+    const int S = ctx->max_seg_cnt;
+    auto pull = [&](void *host, const void *dev, size_t esz) -> int {
+        if (!host) return CM_OK;
+        CUDA_TRY(ctx, cudaMemcpy2DAsync(host, (size_t) S * esz, dev, (size_t) 2 * S * esz, (size_t) S * esz, n, cudaMemcpyDeviceToHost,
+                                        ctx->stream));
+        return CM_OK;
+    };
+    if ((r = pull(qpos, ctx->scratch[0].p, 4)) != CM_OK) return r;
+    if ((r = pull(frag_count, ctx->scratch[1].p, 4)) != CM_OK) return r;
+    if ((r = pull(has_frags, ctx->scratch[2].p, 1)) != CM_OK) return r;
+    if ((r = pull(first_info, ctx->scratch[3].p, 4)) != CM_OK) return r;
+    if ((r = pull(last_info, ctx->scratch[4].p, 4)) != CM_OK) return r;
+    if ((r = pull(sum_info, ctx->scratch[5].p, 8)) != CM_OK) return r;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return CM_OK;
+}
+
+#include "cm_pipeline.cuh"

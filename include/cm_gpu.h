@@ -1,0 +1,210 @@
+/*
+ * cm_gpu.h -- C-ABI of the B200 mapping hot path (seed lookup -> chaining ->
+ * extension/alignment -> per-pair classification) of CircMiner.
+ *
+ * The reference has no plugin/FFI layer; this boundary sits exactly on the
+ * member-function seam its thread body calls once per pair
+ * (/root/reference/src/circminer.cpp:354-406 map_reads ->
+ *  FilterRead::process_read, src/filter.cpp:86 and :124).  Each export names
+ * the reference interface it replaces.  Plain pointers and sizes only; every
+ * function returns 0 on success and a negative cm_status on failure (the
+ * reference exit(1)s / asserts instead); cm_gpu_last_error() gives the text.
+ * All host buffers are caller-owned; the context owns all device memory; no
+ * pointer handed back outlives the call.  One context per GPU; calls on one
+ * context must be serialised by the caller, different contexts are concurrent.
+ */
+#ifndef CM_GPU_H
+#define CM_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum cm_status {
+    CM_OK = 0,
+    CM_ERR_ARG = -1,       /* bad argument / precondition violated               */
+    CM_ERR_CUDA = -2,      /* CUDA runtime error (no device, launch failure ...)  */
+    CM_ERR_ALLOC = -3,     /* host or device allocation failed                   */
+    CM_ERR_STATE = -4      /* call order violated (contig / annotation missing)  */
+} cm_status;
+
+/* output categories, order matters (src/common.h:59-72) */
+enum {
+    CM_CONCRD = 0, CM_DISCRD = 1, CM_CHIORF = 2, CM_CHIBSJ = 3, CM_CHI2BSJ = 4, CM_CONGEN = 5, CM_CHIFUS = 6,
+    CM_CONGNM = 7, CM_OEA2 = 8, CM_CANDID = 9, CM_OEANCH = 10, CM_ORPHAN = 11, CM_NOPROC_MANYHIT = 12,
+    CM_NOPROC_NOMATCH = 13
+};
+
+/* The reference's mutable globals (src/common.h:92-114, defaults in
+ * src/commandline_parser.cpp:7-30) and score matrix (src/circminer.cpp:74),
+ * frozen at context creation. */
+typedef struct cm_params {
+    int32_t kmer;            /* 14..22 ; WINDOW_SIZE 14 + checkSumLength            */
+    int32_t max_read_len;    /* maxReadLength (-l), default 300                     */
+    int32_t max_ed;          /* maxEd (-e), 4                                       */
+    int32_t max_sc;          /* maxSc (-c), 7                                       */
+    int32_t band_width;      /* bandWidth (-w), 3                                   */
+    int32_t seed_lim;        /* seedLim (-S), 500                                   */
+    int32_t max_tlen;        /* maxTlen (-T), 500                                   */
+    int32_t max_intron_len;  /* maxIntronLen (-I), 2000000                          */
+    int32_t max_chain_len;   /* maxChainLen (-C), 30                                */
+    int32_t scan_level;      /* scanLevel (-a), 0                                   */
+    int32_t mat_sc, mis_sc, ind_sc, xdrop;   /* score_mat.init(1,-3,-3,8)           */
+} cm_params;
+
+void cm_params_default(cm_params *p);
+
+/* POD mirror of MatchedRead (src/common.h:311-352).  chr_r1/chr_r2 are indices
+ * into the host's chromosome table (row order of <ref>.packed.fa.index.info,
+ * src/genome.cpp:147-167); -1 stands for "-".  genome_spos is derived by the
+ * host when it writes the remain-FASTQ header (src/filter.cpp:425-430). */
+typedef struct cm_mread {
+    uint32_t spos_r1, spos_r2, epos_r1, epos_r2;
+    uint32_t qspos_r1, qspos_r2, qepos_r1, qepos_r2;
+    uint32_t mlen_r1, mlen_r2;
+    int32_t ed_r1, ed_r2;
+    int32_t type;
+    int32_t tlen;
+    int32_t contig_num;
+    int32_t chr_r1, chr_r2;
+    uint16_t junc_num;
+    uint8_t r1_forward, r2_forward, gm_compatible;
+    uint8_t pad_[3];
+} cm_mread;
+
+/* MatchedRead::MatchedRead(void) (src/common.cpp:268-271) */
+void cm_mread_init(cm_mread *m, const cm_params *p);
+
+/* Flattened, read-only copy of what GTFParser holds for ONE packed contig
+ * (src/gene_annotation.h:55-72): FlatIntervalTree<UniqSeg>::disjoint_intervals
+ * as CSR (src/interval_tree.h:16-18, src/interval_info.h:9-18), trans2seg,
+ * trans_start_ind, gid2ginfo, con2chr and the two bitsets
+ * (src/common.h:117-118).  All positions contig-relative, 1-based. */
+typedef struct cm_annot_flat {
+    uint32_t n_iv;                 /* disjoint intervals (including the dummy)   */
+    const uint32_t *iv_spos, *iv_epos, *iv_max_end, *iv_min_end, *iv_max_next_exon;
+    const uint32_t *iv_seg_off;    /* n_iv + 1                                   */
+    uint32_t n_seg;
+    const uint32_t *seg_start, *seg_end, *seg_next_exon_beg, *seg_gene_id;
+    const uint32_t *seg_tid_off;   /* n_seg + 1                                  */
+    uint32_t n_tid;
+    const uint32_t *tid;           /* UniqSeg::trans_id, concatenated            */
+    uint32_t n_trans;
+    const int32_t *trans_start_ind;/* n_trans                                    */
+    const uint32_t *t2s_off;       /* n_trans + 1                                */
+    const uint8_t *t2s;            /* trans2seg states 0/1/2/3                   */
+    uint32_t n_genes;
+    const uint32_t *gene_start, *gene_end;  /* gid2ginfo                         */
+    uint32_t n_chr;                /* con2chr[contig]                            */
+    const uint32_t *chr_shift;
+    const int32_t *chr_id;         /* global chromosome index of each entry      */
+    uint64_t n_bits;               /* bits available in the two masks            */
+    const uint64_t *near_border;   /* bit k of word k/64 = near_border_bs[c][k]  */
+    const uint64_t *intronic;
+} cm_annot_flat;
+
+typedef struct cm_counters {
+    uint64_t seeds;          /* seeds looked up                                    */
+    uint64_t seed_sectors;   /* algorithmic 32-B sectors, SURVEY.md 8(d)-1         */
+    uint64_t seed_hits;      /* kept hit-list entries                              */
+    uint64_t chain_links;    /* (i,j) candidates reaching src/chain.cpp:173        */
+    uint64_t xdrop_cells;    /* src/align.cpp:296-325 cell visits                  */
+    uint64_t edit_cells;     /* banded / one-side / full edit DP cells             */
+    uint64_t xdrop_calls, edit_calls;
+    uint64_t pairs;
+    uint64_t kernel_launches;
+} cm_counters;
+
+typedef struct cm_gpu_ctx cm_gpu_ctx;
+
+/* ---- life cycle ------------------------------------------------------- */
+/* replaces the per-thread scratch set-up in mapping() (src/circminer.cpp:163-191)
+ * and FilterRead::init's TransExtension array (src/filter.cpp:41-44) */
+int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **out);
+int cm_gpu_destroy(cm_gpu_ctx *ctx);
+const char *cm_gpu_last_error(const cm_gpu_ctx *ctx);   /* ctx may be NULL: last create error */
+int cm_gpu_get_counters(cm_gpu_ctx *ctx, cm_counters *out, int reset);
+/* device time (ms, CUDA events on the context's stream) of the stages of the last
+ * batch call: [0] prep, [1] seed, [2] chain, [3] extend+classify, [4] total. */
+int cm_gpu_last_stage_ms(cm_gpu_ctx *ctx, float out[5]);
+
+/* ---- index / genome --------------------------------------------------- */
+/* Upload one packed contig straight from the reference's in-memory index right
+ * after loadHashTable() (src/mrsfast/HashTable.c:971-1057):
+ *   bucket_lists = _ih_hashTable   (IHashTable[4^14], 8-byte pointers or NULL)
+ *   table_mem    = _ih_hashTableMem (6-byte GeneralIndex; list[0].info = count)
+ *   cref_gen     = _ih_crefGen     (3 bits / base, 21 per word, Common.c:174-196)
+ * Replaces getCandidates (HashTable.c:1093) and GenomeSeeder::pac2char
+ * (src/match_read.cpp:288-299) as data sources. contig_id is 0-based (contigNum). */
+int cm_gpu_load_contig(cm_gpu_ctx *ctx, int contig_id, const void *const *bucket_lists, const void *table_mem,
+                       uint64_t table_mem_entries, const uint64_t *cref_gen, uint32_t ref_gen_len);
+/* Same index built on the device from the packed contig's bases ('A','C','G','T',
+ * anything else = N): count -> scan -> scatter -> sort by (checksum, position),
+ * the order src/mrsfast/Sort.c:110-176 produces (HashTable.c:769-839). */
+int cm_gpu_build_contig(cm_gpu_ctx *ctx, int contig_id, const char *contig_seq, uint32_t ref_gen_len);
+int cm_gpu_contig_stats(cm_gpu_ctx *ctx, int contig_id, uint64_t *n_entries, uint32_t *ref_gen_len);
+/* debugging / parity: copy the positions of bucket hv (all checksums) back */
+int cm_gpu_read_bucket(cm_gpu_ctx *ctx, int contig_id, uint32_t hv, uint32_t cap, uint16_t *checksum,
+                       uint32_t *pos, uint32_t *n);
+/* after GTFParser::load_gtf (src/gene_annotation.cpp:191) */
+int cm_gpu_load_annotation(cm_gpu_ctx *ctx, int contig_id, const cm_annot_flat *annot);
+
+/* ---- stage-level batch entries (parity tests) -------------------------- */
+/* Reads are ASCII, n strands, fixed row stride `stride` bytes, length len[i].
+ * The device derives the reverse complement exactly as
+ * FASTQParser::set_reverse_comp does (src/fastq_parser.cpp:141-153). */
+
+/* GenomeSeeder::split_match_hash (src/match_read.cpp:270; get_exact_locs_hash :54).
+ * Outputs are [n][max_seg_cnt] with max_seg_cnt = 2*ceil(max_read_len/kmer)-1:
+ *   qpos, frag_count (0 when > seed_lim), has_frags (frags != NULL),
+ *   first/last/sum of frags[].info over the kept run. */
+int cm_gpu_seed_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride,
+                      const uint16_t *len, int32_t *qpos, uint32_t *frag_count, uint8_t *has_frags,
+                      uint32_t *first_info, uint32_t *last_info, uint64_t *sum_info);
+
+/* get_best_chains = split_match_hash + chain_seeds_sorted_kbest (src/filter.cpp:469,
+ * src/chain.cpp:73).  Outputs: chain_count[n], high_hits[n], and per strand
+ * max_chain_len slots: score, chain_len, frags (rpos, qpos) [n][C][F],
+ * F = (max_seg_cnt+1)/2; fragment len is always kmer. */
+int cm_gpu_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride,
+                       const uint16_t *len, int32_t *chain_count, int32_t *high_hits, float *score,
+                       uint32_t *chain_len, uint32_t *frag_rpos, int32_t *frag_qpos);
+
+/* Alignment kernels, one problem per row (src/align.h:165-176):
+ *   kind 0: DropAlignment::local_alignment_right_sc  (src/align.cpp:669)
+ *   kind 1: DropAlignment::local_alignment_left_sc   (:694)
+ *   kind 2: Alignment::local_alignment_right         (:556)
+ *   kind 3: Alignment::local_alignment_left          (:578)
+ *   kind 4: Alignment::global_one_side_banded_alignment (:219), w in aux[i]
+ * s/t are ASCII rows (stride bytes); out_ed, out_sclen, out_indel, out_score as the
+ * reference returns them (unused ones are 0). */
+int cm_gpu_align_batch(cm_gpu_ctx *ctx, int kind, uint32_t n, const char *s, const uint16_t *n_s, const char *t,
+                       const uint16_t *n_t, uint32_t stride, const int32_t *aux, int32_t *out_ed,
+                       int32_t *out_sclen, int32_t *out_indel, int32_t *out_score);
+
+/* ---- the fused hot path ------------------------------------------------ */
+/* FilterRead::process_read, PE overload (src/filter.cpp:124-241) for n pairs.
+ * seqs1/seqs2: mate rows; in[i] = the pair's carried MatchedRead (what
+ * FASTQParser::fill_map_info reconstructed, src/fastq_parser.cpp:203-269);
+ * out[i] = updated MatchedRead; state[i] = return value.  in may alias out. */
+int cm_gpu_process_batch_pe(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs1, const char *seqs2,
+                            uint32_t stride, const uint16_t *len1, const uint16_t *len2, const cm_mread *in,
+                            cm_mread *out, int32_t *state);
+/* SE overload (src/filter.cpp:86-121): only the return value is observable. */
+int cm_gpu_process_batch_se(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride,
+                            const uint16_t *len, int32_t *state);
+
+/* Device-resident variant used for kernel-only timing: stage the batch once,
+ * then run the pipeline any number of times without host copies. */
+int cm_gpu_stage_batch_pe(cm_gpu_ctx *ctx, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
+                          const uint16_t *len1, const uint16_t *len2, const cm_mread *in);
+int cm_gpu_run_staged_pe(cm_gpu_ctx *ctx, int contig_id, int upto_stage /* 1 seed, 2 chain, 3 all */);
+int cm_gpu_fetch_staged_pe(cm_gpu_ctx *ctx, cm_mread *out, int32_t *state);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CM_GPU_H */

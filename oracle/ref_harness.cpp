@@ -1,0 +1,408 @@
+// TEST INFRASTRUCTURE ONLY -- never linked, imported or executed by the product path.
+//
+// Thin extern "C" harness compiled TOGETHER WITH the unmodified reference objects
+// (see Makefile) into oracle/_ref/libcm_ref.so.  It drives the reference's own
+// globals/singletons (gtf_parser, genome_seeder, filter_read, mrsFAST _ih_*) the way
+// mapping() does (/root/reference/src/circminer.cpp:98-345) and exposes stage-level
+// results as POD arrays so that tests can compare the CUDA path with the reference
+// itself: seed lists, chains, alignments, process_read, plus the in-memory index and
+// annotation a maintainer's shim would hand to cm_gpu_load_contig/_annotation.
+#define private public
+#define protected public
+#include "common.h"
+#include "align.h"
+#include "chain.h"
+#include "extend.h"
+#include "filter.h"
+#include "genome.h"
+#include "gene_annotation.h"
+#include "match_read.h"
+#include "utils.h"
+#include "fastq_parser.h"
+#undef private
+#undef protected
+
+#include <cmath>
+#include <string>
+#include <vector>
+
+#include "../include/cm_gpu.h"
+
+extern "C" {
+#include "mrsfast/Common.h"
+#include "mrsfast/HashTable.h"
+extern IHashTable *_ih_hashTable;
+extern GeneralIndex *_ih_hashTableMem;
+extern unsigned int _ih_hashTableMemSize;
+extern CompressedSeq *_ih_crefGen;
+extern int _ih_refGenLen;
+extern int _ih_maxHashTableSize;
+}
+extern unsigned int CONTIG_SIZE;
+extern unsigned int CONTIG_MAX_SIZE;
+extern int maxCheckSumLen;
+int cm_ref_main(int argc, char **argv);
+
+static std::vector<ContigLen> g_contig_len;
+static std::vector<GIMatchedKmer> g_fl, g_bl;
+static chain_list g_cl[4];
+static int g_max_seg_cnt = 0;
+static bool g_filter_inited = false;
+static std::string g_tmp_prefix;
+static Record *g_rec1 = NULL, *g_rec2 = NULL;
+static char g_comp[128];
+
+static void alloc_chain_list(chain_list &cl) {
+    cl.chains = (chain_t *) malloc(maxChainLen * sizeof(chain_t));
+    for (int i = 0; i < maxChainLen; i++)
+        cl.chains[i].frags = (fragment_t *) malloc(g_max_seg_cnt * sizeof(fragment_t));
+    cl.best_chain_count = 0;
+}
+
+static void revcomp(const char *s, int len, char *rc) {
+    // FASTQParser::set_comp / set_reverse_comp (fastq_parser.cpp:141-164)
+    for (int i = 0; i < len; i++) rc[len - i - 1] = g_comp[(unsigned char) s[i] & 127];
+    rc[len] = '\0';
+}
+
+extern "C" {
+
+// run the unmodified main() (index build, whole pipeline)
+int cmref_main(int argc, char **argv) {
+    optind = 1;
+    return cm_ref_main(argc, argv);
+}
+
+// Globals that parse_command would set (commandline_parser.cpp:7-30,247-262)
+int cmref_set_params(const cm_params *p, int threads) {
+    kmer = p->kmer;
+    maxReadLength = p->max_read_len;
+    maxEd = p->max_ed;
+    maxSc = p->max_sc;
+    bandWidth = p->band_width;
+    seedLim = p->seed_lim;
+    maxTlen = p->max_tlen;
+    maxIntronLen = p->max_intron_len;
+    maxChainLen = p->max_chain_len;
+    scanLevel = p->scan_level;
+    threadCount = threads;
+    THREAD_COUNT = threads;
+    for (int i = 0; i < 255; i++) THREAD_ID[i] = i;
+    checkSumLength = (WINDOW_SIZE > kmer) ? 0 : kmer - WINDOW_SIZE;
+    pairedEnd = true;
+    initCommon();
+    score_mat.init(p->mat_sc, p->mis_sc, p->ind_sc, p->xdrop);
+    edit_mat.init(0, 1, 1, 10000);
+    static bool fq_inited = false;
+    if (!fq_inited) {   // main() does this (circminer.cpp:59-60); keeps the global destructors well-defined
+        fq_parser1.init();
+        fq_parser2.init();
+        fq_inited = true;
+    }
+    memset(g_comp, 0, sizeof(g_comp));
+    g_comp['A'] = 'T'; g_comp['C'] = 'G'; g_comp['G'] = 'C'; g_comp['T'] = 'A'; g_comp['N'] = 'N';
+    g_comp['a'] = 'T'; g_comp['c'] = 'G'; g_comp['g'] = 'C'; g_comp['t'] = 'A'; g_comp['n'] = 'N';
+    return 0;
+}
+
+// GenomePacker::build_index with a caller-chosen CONTIG_SIZE so that small synthetic
+// genomes exercise the multi-contig "rounds" (genome.cpp:96-145). contig_size 0 = default.
+int cmref_build_index(const char *ref_fa, unsigned contig_size, int compact) {
+    CONTIG_SIZE = contig_size ? contig_size : DEF_CONTIG_SIZE;
+    CONTIG_MAX_SIZE = DEF_CONTIG_MAX_SIZE;
+    indexMode = true;
+    genome_packer.init((char *) ref_fa);
+    int r = genome_packer.build_index(compact != 0);
+    indexMode = false;
+    return r ? 0 : -1;
+}
+
+// mapping() prologue (circminer.cpp:125-209): index meta, seeder, scratch, GTF.
+int cmref_open(const char *ref_fa, const char *gtf, const char *tmp_prefix) {
+    genome_packer.init((char *) ref_fa);
+    genome_packer.load_index_info(g_contig_len);
+    char index_file[FILE_NAME_MAX_LEN];
+    strcpy(index_file, genome_packer.get_index_fname().c_str());
+    if (!checkHashTable(index_file)) return -1;
+    if (!initLoadingHashTableMeta(index_file)) return -2;
+    kmer = WINDOW_SIZE + checkSumLength;
+    genome_seeder.init(LOADCONTIGSTRINMEM);
+    g_max_seg_cnt = 2 * (ceil(1.0 * maxReadLength / kmer)) - 1;
+    g_fl.resize(g_max_seg_cnt);
+    g_bl.resize(g_max_seg_cnt);
+    for (int i = 0; i < 4; i++) alloc_chain_list(g_cl[i]);
+    strcpy(gtfFilename, gtf);
+    gtf_parser.init((char *) gtf, g_contig_len);
+    if (!gtf_parser.load_gtf()) return -3;
+    g_tmp_prefix = tmp_prefix;
+    strcpy(outputFilename, tmp_prefix);
+    if (!g_rec1) {
+        g_rec1 = new Record; g_rec1->init();
+        g_rec2 = new Record; g_rec2->init();
+    }
+    return 0;
+}
+
+int cmref_kmer(void) { return kmer; }
+int cmref_max_seg_cnt(void) { return g_max_seg_cnt; }
+int cmref_n_chr(void) { return (int) g_contig_len.size(); }
+const char *cmref_chr_name(int i) { return g_contig_len[i].name.c_str(); }
+int cmref_chr_info(int i, uint32_t *contig_id, uint32_t *start, uint32_t *end) {
+    *contig_id = g_contig_len[i].contig_id; *start = g_contig_len[i].start_pos; *end = g_contig_len[i].end_pos;
+    return 0;
+}
+
+// one "round" (circminer.cpp:229-286): returns 1 if more contigs follow, 0 if last, <0 error
+int cmref_next_contig(void) {
+    double t;
+    int flag = loadHashTable(&t);
+    if (!genome_seeder.pac2char_whole_contig()) return -1;
+    contigName = getRefGenomeName();
+    contigNum = atoi(contigName) - 1;
+    if (g_filter_inited) filter_read.finalize();
+    char fq1[FILE_NAME_MAX_LEN], fq2[FILE_NAME_MAX_LEN];
+    filter_read.init((char *) g_tmp_prefix.c_str(), true, contigNum + 1, !g_filter_inited, !flag, fq1, fq2,
+                     g_contig_len);
+    g_filter_inited = true;
+    return flag ? 1 : 0;
+}
+int cmref_contig_num(void) { return contigNum; }
+
+// what a maintainer's shim passes to cm_gpu_load_contig
+const void *cmref_hash_table(void) { return _ih_hashTable; }
+const void *cmref_hash_mem(void) { return _ih_hashTableMem; }
+uint64_t cmref_hash_mem_size(void) {
+    // _ih_hashTableMemSize is only maintained by the builder; recompute from the directory
+    uint64_t n = 0;
+    for (int hv = 0; hv < _ih_maxHashTableSize; hv++)
+        if (_ih_hashTable[hv].list) {
+            uint64_t end = (uint64_t) (_ih_hashTable[hv].list - _ih_hashTableMem) + _ih_hashTable[hv].list[0].info + 1;
+            if (end > n) n = end;
+        }
+    return n;
+}
+const uint64_t *cmref_cref_gen(void) { return (const uint64_t *) _ih_crefGen; }
+uint32_t cmref_ref_gen_len(void) { return (uint32_t) _ih_refGenLen; }
+int cmref_genome_chars(uint32_t start, int len, char *out) { return genome_seeder.pac2char(start, len, out) ? 0 : -1; }
+
+// ---- annotation dump (current contigNum) -------------------------------------------
+// call with NULL pointers to get sizes first
+int cmref_annot_sizes(uint32_t *n_iv, uint32_t *n_seg, uint32_t *n_tid, uint32_t *n_trans, uint32_t *n_t2s,
+                      uint32_t *n_genes, uint32_t *n_chr) {
+    FlatIntervalTree<UniqSeg> &T = gtf_parser.exons_int_map[contigNum];
+    *n_iv = T.disjoint_intervals.size();
+    uint32_t ns = 0, nt = 0;
+    for (auto &iv : T.disjoint_intervals) {
+        ns += iv.seg_list.size();
+        for (auto &s : iv.seg_list) nt += s.trans_id.size();
+    }
+    *n_seg = ns; *n_tid = nt;
+    uint32_t ntr = (uint32_t) contigNum < gtf_parser.trans2seg.size() ? gtf_parser.trans2seg[contigNum].size() : 0;
+    *n_trans = ntr;
+    uint32_t n2 = 0;
+    for (uint32_t i = 0; i < ntr; i++) n2 += gtf_parser.trans2seg[contigNum][i].size();
+    *n_t2s = n2;
+    *n_genes = (uint32_t) contigNum < gtf_parser.gid2ginfo.size() ? gtf_parser.gid2ginfo[contigNum].size() : 0;
+    *n_chr = gtf_parser.con2chr[contigNum].size();
+    return 0;
+}
+
+int cmref_annot_fill(uint32_t *iv_spos, uint32_t *iv_epos, uint32_t *iv_max_end, uint32_t *iv_min_end,
+                     uint32_t *iv_max_next_exon, uint32_t *iv_seg_off, uint32_t *seg_start, uint32_t *seg_end,
+                     uint32_t *seg_next, uint32_t *seg_gene, uint32_t *seg_tid_off, uint32_t *tid,
+                     int32_t *trans_start_ind, uint32_t *t2s_off, uint8_t *t2s, uint32_t *gene_start,
+                     uint32_t *gene_end, uint32_t *chr_shift, int32_t *chr_id) {
+    FlatIntervalTree<UniqSeg> &T = gtf_parser.exons_int_map[contigNum];
+    uint32_t si = 0, ti = 0;
+    for (size_t i = 0; i < T.disjoint_intervals.size(); i++) {
+        auto &iv = T.disjoint_intervals[i];
+        iv_spos[i] = iv.spos; iv_epos[i] = iv.epos;
+        iv_max_end[i] = iv.max_end; iv_min_end[i] = iv.min_end; iv_max_next_exon[i] = iv.max_next_exon;
+        iv_seg_off[i] = si;
+        for (auto &s : iv.seg_list) {
+            seg_start[si] = s.start; seg_end[si] = s.end; seg_next[si] = s.next_exon_beg; seg_gene[si] = s.gene_id;
+            seg_tid_off[si] = ti;
+            for (auto t : s.trans_id) tid[ti++] = t;
+            si++;
+        }
+    }
+    iv_seg_off[T.disjoint_intervals.size()] = si;
+    seg_tid_off[si] = ti;
+    uint32_t ntr = (uint32_t) contigNum < gtf_parser.trans2seg.size() ? gtf_parser.trans2seg[contigNum].size() : 0;
+    uint32_t o = 0;
+    for (uint32_t i = 0; i < ntr; i++) {
+        trans_start_ind[i] = gtf_parser.trans_start_ind[contigNum][i];
+        t2s_off[i] = o;
+        for (auto v : gtf_parser.trans2seg[contigNum][i]) t2s[o++] = v;
+    }
+    t2s_off[ntr] = o;
+    if ((uint32_t) contigNum < gtf_parser.gid2ginfo.size())
+        for (size_t i = 0; i < gtf_parser.gid2ginfo[contigNum].size(); i++) {
+            gene_start[i] = gtf_parser.gid2ginfo[contigNum][i].start;
+            gene_end[i] = gtf_parser.gid2ginfo[contigNum][i].end;
+        }
+    for (size_t i = 0; i < gtf_parser.con2chr[contigNum].size(); i++) {
+        chr_shift[i] = gtf_parser.con2chr[contigNum][i].shift;
+        chr_id[i] = -1;
+        for (size_t j = 0; j < g_contig_len.size(); j++)
+            if (g_contig_len[j].name == gtf_parser.con2chr[contigNum][i].contig) chr_id[i] = (int32_t) j;
+    }
+    return 0;
+}
+
+// copy the first n_bits of the two std::bitset masks (common.h:117-118) into 64-bit words
+int cmref_annot_masks(uint64_t n_bits, uint64_t *near_border, uint64_t *intronic) {
+    uint64_t nw = (n_bits + 63) / 64;
+    memset(near_border, 0, nw * 8);
+    memset(intronic, 0, nw * 8);
+    if ((size_t) contigNum < near_border_bs.size())
+        for (uint64_t k = 0; k < n_bits; k++)
+            if (near_border_bs[contigNum][k]) near_border[k >> 6] |= 1ull << (k & 63);
+    if ((size_t) contigNum < intronic_bs.size())
+        for (uint64_t k = 0; k < n_bits; k++)
+            if (intronic_bs[contigNum][k]) intronic[k >> 6] |= 1ull << (k & 63);
+    return 0;
+}
+
+// ---- stage dumps ---------------------------------------------------------------------
+// GenomeSeeder::split_match_hash on one strand; arrays of max_seg_cnt
+int cmref_seed(const char *seq, int len, int32_t *qpos, uint32_t *frag_count, uint8_t *has_frags,
+               uint32_t *first_info, uint32_t *last_info, uint64_t *sum_info) {
+    std::vector<char> s(seq, seq + len);
+    s.push_back(0);
+    genome_seeder.split_match_hash(s.data(), len, kmer, g_fl.data());
+    for (int i = 0; i < g_max_seg_cnt; i++) {
+        GIMatchedKmer &m = g_fl[i];
+        qpos[i] = (i % 2 == 0 && i / 2 * kmer + kmer <= len) ? m.qpos : 0;   // odd/unused slots keep stale qpos
+        frag_count[i] = m.frag_count;
+        has_frags[i] = m.frags != NULL;
+        first_info[i] = last_info[i] = 0;
+        sum_info[i] = 0;
+        if (m.frags && m.frag_count) {
+            first_info[i] = m.frags[0].info;
+            last_info[i] = m.frags[m.frag_count - 1].info;
+            for (uint32_t j = 0; j < m.frag_count; j++) sum_info[i] += m.frags[j].info;
+        }
+    }
+    return 0;
+}
+
+// copy the hit list of one slot after cmref_seed (positions), up to cap
+int cmref_seed_slot(int slot, uint32_t cap, uint32_t *info) {
+    GIMatchedKmer &m = g_fl[slot];
+    uint32_t n = m.frag_count < cap ? m.frag_count : cap;
+    for (uint32_t j = 0; j < n; j++) info[j] = m.frags[j].info;
+    return (int) n;
+}
+
+// FilterRead::get_best_chains on one strand (filter.cpp:469-482)
+int cmref_chain(const char *seq, int len, int32_t *chain_count, int32_t *high_hits, float *score,
+                uint32_t *chain_len, uint32_t *frag_rpos, int32_t *frag_qpos) {
+    std::vector<char> s(seq, seq + len);
+    s.push_back(0);
+    int hh = 0;
+    filter_read.get_best_chains(s.data(), len, kmer, g_cl[0], g_fl.data(), hh);
+    int F = (g_max_seg_cnt + 1) / 2;
+    *chain_count = g_cl[0].best_chain_count;
+    *high_hits = hh;
+    for (int c = 0; c < maxChainLen; c++) {
+        score[c] = 0; chain_len[c] = 0;
+        for (int f = 0; f < F; f++) { frag_rpos[c * F + f] = 0; frag_qpos[c * F + f] = 0; }
+    }
+    for (int c = 0; c < g_cl[0].best_chain_count; c++) {
+        score[c] = g_cl[0].chains[c].score;
+        chain_len[c] = g_cl[0].chains[c].chain_len;
+        for (uint32_t f = 0; f < g_cl[0].chains[c].chain_len && (int) f < F; f++) {
+            frag_rpos[c * F + f] = g_cl[0].chains[c].frags[f].rpos;
+            frag_qpos[c * F + f] = g_cl[0].chains[c].frags[f].qpos;
+        }
+    }
+    return 0;
+}
+
+static int chr_index(const std::string &name) {
+    for (size_t j = 0; j < g_contig_len.size(); j++)
+        if (g_contig_len[j].name == name) return (int) j;
+    return -1;
+}
+
+static void mread_to_ref(const cm_mread *m, MatchedRead *r) {
+    r->spos_r1 = m->spos_r1; r->spos_r2 = m->spos_r2; r->epos_r1 = m->epos_r1; r->epos_r2 = m->epos_r2;
+    r->qspos_r1 = m->qspos_r1; r->qspos_r2 = m->qspos_r2; r->qepos_r1 = m->qepos_r1; r->qepos_r2 = m->qepos_r2;
+    r->mlen_r1 = m->mlen_r1; r->mlen_r2 = m->mlen_r2;
+    r->r1_forward = m->r1_forward; r->r2_forward = m->r2_forward;
+    r->ed_r1 = m->ed_r1; r->ed_r2 = m->ed_r2; r->type = m->type; r->tlen = m->tlen;
+    r->junc_num = m->junc_num; r->gm_compatible = m->gm_compatible; r->contig_num = m->contig_num;
+    r->chr_r1 = m->chr_r1 >= 0 ? g_contig_len[m->chr_r1].name : std::string("-");
+    r->chr_r2 = m->chr_r2 >= 0 ? g_contig_len[m->chr_r2].name : std::string("-");
+}
+
+static void ref_to_mread(const MatchedRead *r, cm_mread *m) {
+    memset(m, 0, sizeof(*m));
+    m->spos_r1 = r->spos_r1; m->spos_r2 = r->spos_r2; m->epos_r1 = r->epos_r1; m->epos_r2 = r->epos_r2;
+    m->qspos_r1 = r->qspos_r1; m->qspos_r2 = r->qspos_r2; m->qepos_r1 = r->qepos_r1; m->qepos_r2 = r->qepos_r2;
+    m->mlen_r1 = r->mlen_r1; m->mlen_r2 = r->mlen_r2;
+    m->r1_forward = r->r1_forward; m->r2_forward = r->r2_forward;
+    m->ed_r1 = r->ed_r1; m->ed_r2 = r->ed_r2; m->type = r->type; m->tlen = r->tlen;
+    m->junc_num = r->junc_num; m->gm_compatible = r->gm_compatible; m->contig_num = r->contig_num;
+    m->chr_r1 = chr_index(r->chr_r1);
+    m->chr_r2 = chr_index(r->chr_r2);
+}
+
+// FilterRead::process_read, PE (filter.cpp:124-241), n pairs, rows of `stride` bytes
+int cmref_process_pe(uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride, const uint16_t *len1,
+                     const uint16_t *len2, const cm_mread *in, cm_mread *out, int32_t *state) {
+    for (uint32_t i = 0; i < n; i++) {
+        int l1 = len1[i], l2 = len2[i];
+        memcpy(g_rec1->seq, seqs1 + (size_t) i * stride, l1); g_rec1->seq[l1] = 0;
+        memcpy(g_rec2->seq, seqs2 + (size_t) i * stride, l2); g_rec2->seq[l2] = 0;
+        revcomp(g_rec1->seq, l1, g_rec1->rcseq);
+        revcomp(g_rec2->seq, l2, g_rec2->rcseq);
+        g_rec1->seq_len = l1; g_rec2->seq_len = l2;
+        strcpy(g_rec1->rname, "r"); strcpy(g_rec2->rname, "r");
+        mread_to_ref(&in[i], g_rec1->mr);
+        state[i] = filter_read.process_read(0, g_rec1, g_rec2, kmer, g_fl.data(), g_bl.data(), g_cl[0], g_cl[1],
+                                            g_cl[2], g_cl[3]);
+        ref_to_mread(g_rec1->mr, &out[i]);
+    }
+    return 0;
+}
+
+// SE overload (filter.cpp:86-121)
+int cmref_process_se(uint32_t n, const char *seqs, uint32_t stride, const uint16_t *len, int32_t *state) {
+    for (uint32_t i = 0; i < n; i++) {
+        int l1 = len[i];
+        memcpy(g_rec1->seq, seqs + (size_t) i * stride, l1); g_rec1->seq[l1] = 0;
+        revcomp(g_rec1->seq, l1, g_rec1->rcseq);
+        g_rec1->seq_len = l1;
+        strcpy(g_rec1->rname, "r");
+        state[i] = filter_read.process_read(0, g_rec1, kmer, g_fl.data(), g_bl.data(), g_cl[0], g_cl[1]);
+    }
+    return 0;
+}
+
+// alignment kinds as in cm_gpu_align_batch
+int cmref_align(int kind, uint32_t n, const char *s, const uint16_t *n_s, const char *t, const uint16_t *n_t,
+                uint32_t stride, const int32_t *aux, int32_t *out_ed, int32_t *out_sclen, int32_t *out_indel,
+                int32_t *out_score) {
+    static DropAlignment *al = NULL;
+    if (!al) al = new DropAlignment();
+    al->init();
+    std::vector<char> sb(stride + 8), tb(stride + 8);
+    for (uint32_t i = 0; i < n; i++) {
+        int ns = n_s[i], nt = n_t[i];
+        memcpy(sb.data(), s + (size_t) i * stride, ns); sb[ns] = 0;
+        memcpy(tb.data(), t + (size_t) i * stride, nt); tb[nt] = 0;
+        int sc = 0, indel = 0, ed = 0;
+        if (kind == 0) ed = al->local_alignment_right_sc(sb.data(), ns, tb.data(), nt, sc, indel);
+        else if (kind == 1) ed = al->local_alignment_left_sc(sb.data(), ns, tb.data(), nt, sc, indel);
+        else if (kind == 2) ed = al->local_alignment_right(sb.data(), ns, tb.data(), nt, indel);
+        else if (kind == 3) ed = al->local_alignment_left(sb.data(), ns, tb.data(), nt, indel);
+        else if (kind == 4) ed = al->global_one_side_banded_alignment(sb.data(), ns, tb.data(), nt, aux[i]);
+        out_ed[i] = ed; out_sclen[i] = sc; out_indel[i] = indel;
+        out_score[i] = (kind == 4) ? 0 : al->get_score();
+    }
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,211 @@
+"""TEST INFRASTRUCTURE ONLY.  ctypes wrapper over oracle/_ref/libcm_ref.so (the unmodified
+reference + oracle/ref_harness.cpp).  The reference keeps everything in process-global
+singletons, so one process can open exactly one (reference, GTF) pair; use `python -m
+oracle.refdump` (a subprocess) to produce stage dumps for a dataset.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_SO = os.path.join(HERE, "_ref", "libcm_ref.so")
+REF_BIN = os.path.join(HERE, "_ref", "circminer")
+
+
+class CmParams(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "kmer", "max_read_len", "max_ed", "max_sc", "band_width", "seed_lim", "max_tlen", "max_intron_len",
+        "max_chain_len", "scan_level", "mat_sc", "mis_sc", "ind_sc", "xdrop")]
+
+
+def default_params(**kw) -> CmParams:
+    p = CmParams(20, 300, 4, 7, 3, 500, 500, 2000000, 30, 0, 1, -3, -3, 8)
+    for k, v in kw.items():
+        setattr(p, k, v)
+    return p
+
+
+MREAD_DTYPE = np.dtype([
+    ("spos_r1", "<u4"), ("spos_r2", "<u4"), ("epos_r1", "<u4"), ("epos_r2", "<u4"),
+    ("qspos_r1", "<u4"), ("qspos_r2", "<u4"), ("qepos_r1", "<u4"), ("qepos_r2", "<u4"),
+    ("mlen_r1", "<u4"), ("mlen_r2", "<u4"), ("ed_r1", "<i4"), ("ed_r2", "<i4"), ("type", "<i4"),
+    ("tlen", "<i4"), ("contig_num", "<i4"), ("chr_r1", "<i4"), ("chr_r2", "<i4"), ("junc_num", "<u2"),
+    ("r1_forward", "u1"), ("r2_forward", "u1"), ("gm_compatible", "u1"), ("pad_", "u1", (3,))])
+assert MREAD_DTYPE.itemsize == 76
+
+
+def fresh_mreads(n: int, max_ed: int = 4) -> np.ndarray:
+    """MatchedRead::MatchedRead(void), /root/reference/src/common.cpp:268-271 (unset fields 0)."""
+    m = np.zeros(n, MREAD_DTYPE)
+    m["r1_forward"] = 1
+    m["r2_forward"] = 1
+    m["ed_r1"] = max_ed + 1
+    m["ed_r2"] = max_ed + 1
+    m["type"] = 13
+    m["tlen"] = 1000000000
+    m["chr_r1"] = -1
+    m["chr_r2"] = -1
+    return m
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+class RefHarness:
+    def __init__(self, params: CmParams, threads: int = 1):
+        if not os.path.exists(REF_SO):
+            raise RuntimeError(f"{REF_SO} missing: run `make -C oracle ref` where /root/reference exists")
+        self.lib = C.CDLL(REF_SO)
+        L = self.lib
+        L.cmref_hash_table.restype = C.c_void_p
+        L.cmref_hash_mem.restype = C.c_void_p
+        L.cmref_hash_mem_size.restype = C.c_uint64
+        L.cmref_cref_gen.restype = C.c_void_p
+        L.cmref_ref_gen_len.restype = C.c_uint32
+        L.cmref_chr_name.restype = C.c_char_p
+        self.params = params
+        L.cmref_set_params(C.byref(params), threads)
+
+    def build_index(self, ref_fa: str, contig_size: int = 0, compact: bool = False):
+        r = self.lib.cmref_build_index(ref_fa.encode(), C.c_uint(contig_size), int(compact))
+        if r != 0:
+            raise RuntimeError("reference index build failed")
+
+    def open(self, ref_fa: str, gtf: str, tmp_prefix: str):
+        r = self.lib.cmref_open(ref_fa.encode(), gtf.encode(), tmp_prefix.encode())
+        if r != 0:
+            raise RuntimeError(f"cmref_open failed: {r}")
+        self.kmer = self.lib.cmref_kmer()
+        self.S = self.lib.cmref_max_seg_cnt()
+        self.C_ = self.params.max_chain_len
+        self.F = (self.S + 1) // 2
+        self.chr_names = [self.lib.cmref_chr_name(i).decode() for i in range(self.lib.cmref_n_chr())]
+
+    def chr_info(self):
+        out = []
+        for i in range(len(self.chr_names)):
+            a, b, c = C.c_uint32(), C.c_uint32(), C.c_uint32()
+            self.lib.cmref_chr_info(i, C.byref(a), C.byref(b), C.byref(c))
+            out.append((self.chr_names[i], a.value, b.value, c.value))
+        return out
+
+    def next_contig(self) -> int:
+        r = self.lib.cmref_next_contig()
+        if r < 0:
+            raise RuntimeError("cmref_next_contig failed")
+        self.contig = self.lib.cmref_contig_num()
+        return r
+
+    # raw in-memory index, as a maintainer's shim would pass it
+    def index_pointers(self):
+        L = self.lib
+        return (L.cmref_hash_table(), L.cmref_hash_mem(), L.cmref_hash_mem_size(), L.cmref_cref_gen(),
+                L.cmref_ref_gen_len())
+
+    def genome_chars(self, start: int, length: int) -> bytes:
+        buf = C.create_string_buffer(length + 1)
+        r = self.lib.cmref_genome_chars(C.c_uint32(start), length, buf)
+        if r != 0:
+            raise RuntimeError("pac2char out of range")
+        return buf.raw[:length]
+
+    def annotation(self) -> dict:
+        L = self.lib
+        n = [C.c_uint32() for _ in range(7)]
+        L.cmref_annot_sizes(*[C.byref(x) for x in n])
+        n_iv, n_seg, n_tid, n_trans, n_t2s, n_genes, n_chr = [x.value for x in n]
+        u4 = lambda k: np.zeros(max(k, 1), np.uint32)
+        a = dict(iv_spos=u4(n_iv), iv_epos=u4(n_iv), iv_max_end=u4(n_iv), iv_min_end=u4(n_iv),
+                 iv_max_next_exon=u4(n_iv), iv_seg_off=u4(n_iv + 1), seg_start=u4(n_seg), seg_end=u4(n_seg),
+                 seg_next_exon_beg=u4(n_seg), seg_gene_id=u4(n_seg), seg_tid_off=u4(n_seg + 1), tid=u4(n_tid),
+                 trans_start_ind=np.zeros(max(n_trans, 1), np.int32), t2s_off=u4(n_trans + 1),
+                 t2s=np.zeros(max(n_t2s, 1), np.uint8), gene_start=u4(n_genes), gene_end=u4(n_genes),
+                 chr_shift=u4(n_chr), chr_id=np.zeros(max(n_chr, 1), np.int32))
+        order = ["iv_spos", "iv_epos", "iv_max_end", "iv_min_end", "iv_max_next_exon", "iv_seg_off", "seg_start",
+                 "seg_end", "seg_next_exon_beg", "seg_gene_id", "seg_tid_off", "tid", "trans_start_ind", "t2s_off",
+                 "t2s", "gene_start", "gene_end", "chr_shift", "chr_id"]
+        L.cmref_annot_fill(*[a[k].ctypes.data_as(C.c_void_p) for k in order])
+        n_bits = int(L.cmref_ref_gen_len()) + 64
+        nw = (n_bits + 63) // 64
+        nb = np.zeros(nw, np.uint64)
+        ib = np.zeros(nw, np.uint64)
+        L.cmref_annot_masks(C.c_uint64(n_bits), nb.ctypes.data_as(C.c_void_p), ib.ctypes.data_as(C.c_void_p))
+        a.update(near_border=nb, intronic=ib, n_bits=n_bits, n_iv=n_iv, n_seg=n_seg, n_tid=n_tid, n_trans=n_trans,
+                 n_t2s=n_t2s, n_genes=n_genes, n_chr=n_chr)
+        # trim the max(k,1) padding
+        for k, cnt in (("iv_spos", n_iv), ("iv_epos", n_iv), ("iv_max_end", n_iv), ("iv_min_end", n_iv),
+                       ("iv_max_next_exon", n_iv), ("seg_start", n_seg), ("seg_end", n_seg),
+                       ("seg_next_exon_beg", n_seg), ("seg_gene_id", n_seg), ("tid", n_tid),
+                       ("trans_start_ind", n_trans), ("t2s", n_t2s), ("gene_start", n_genes), ("gene_end", n_genes),
+                       ("chr_shift", n_chr), ("chr_id", n_chr)):
+            a[k] = a[k][:cnt]
+        return a
+
+    def seed(self, seqs: np.ndarray, lens: np.ndarray) -> dict:
+        n, S = len(lens), self.S
+        out = dict(qpos=np.zeros((n, S), np.int32), frag_count=np.zeros((n, S), np.uint32),
+                   has_frags=np.zeros((n, S), np.uint8), first_info=np.zeros((n, S), np.uint32),
+                   last_info=np.zeros((n, S), np.uint32), sum_info=np.zeros((n, S), np.uint64))
+        seqs = np.ascontiguousarray(seqs)
+        for i in range(n):
+            self.lib.cmref_seed(seqs[i].ctypes.data_as(C.c_char_p), int(lens[i]),
+                                *[out[k][i].ctypes.data_as(C.c_void_p) for k in
+                                  ("qpos", "frag_count", "has_frags", "first_info", "last_info", "sum_info")])
+        return out
+
+    def chain(self, seqs: np.ndarray, lens: np.ndarray) -> dict:
+        n, Cn, F = len(lens), self.C_, self.F
+        out = dict(chain_count=np.zeros(n, np.int32), high_hits=np.zeros(n, np.int32),
+                   score=np.zeros((n, Cn), np.float32), chain_len=np.zeros((n, Cn), np.uint32),
+                   frag_rpos=np.zeros((n, Cn, F), np.uint32), frag_qpos=np.zeros((n, Cn, F), np.int32))
+        seqs = np.ascontiguousarray(seqs)
+        for i in range(n):
+            self.lib.cmref_chain(seqs[i].ctypes.data_as(C.c_char_p), int(lens[i]),
+                                 out["chain_count"][i:].ctypes.data_as(C.c_void_p),
+                                 out["high_hits"][i:].ctypes.data_as(C.c_void_p),
+                                 *[out[k][i].ctypes.data_as(C.c_void_p) for k in
+                                   ("score", "chain_len", "frag_rpos", "frag_qpos")])
+        return out
+
+    def process_pe(self, s1, s2, l1, l2, mreads):
+        n = len(l1)
+        s1 = np.ascontiguousarray(s1)
+        s2 = np.ascontiguousarray(s2)
+        assert s1.shape[1] == s2.shape[1]
+        out = np.zeros(n, MREAD_DTYPE)
+        state = np.zeros(n, np.int32)
+        l1 = np.ascontiguousarray(l1, np.uint16)
+        l2 = np.ascontiguousarray(l2, np.uint16)
+        mreads = np.ascontiguousarray(mreads)
+        self.lib.cmref_process_pe(C.c_uint32(n), s1.ctypes.data_as(C.c_char_p), s2.ctypes.data_as(C.c_char_p),
+                                  C.c_uint32(s1.shape[1]), l1.ctypes.data_as(C.c_void_p),
+                                  l2.ctypes.data_as(C.c_void_p), mreads.ctypes.data_as(C.c_void_p),
+                                  out.ctypes.data_as(C.c_void_p), state.ctypes.data_as(C.c_void_p))
+        return out, state
+
+    def process_se(self, s, l):
+        n = len(l)
+        s = np.ascontiguousarray(s)
+        l = np.ascontiguousarray(l, np.uint16)
+        state = np.zeros(n, np.int32)
+        self.lib.cmref_process_se(C.c_uint32(n), s.ctypes.data_as(C.c_char_p), C.c_uint32(s.shape[1]),
+                                  l.ctypes.data_as(C.c_void_p), state.ctypes.data_as(C.c_void_p))
+        return state
+
+    def align(self, kind, s, ns, t, nt, aux=None):
+        n = len(ns)
+        s = np.ascontiguousarray(s)
+        t = np.ascontiguousarray(t)
+        assert s.shape[1] == t.shape[1]
+        ns = np.ascontiguousarray(ns, np.uint16)
+        nt = np.ascontiguousarray(nt, np.uint16)
+        aux = np.zeros(n, np.int32) if aux is None else np.ascontiguousarray(aux, np.int32)
+        o = [np.zeros(n, np.int32) for _ in range(4)]
+        self.lib.cmref_align(kind, C.c_uint32(n), s.ctypes.data_as(C.c_char_p), ns.ctypes.data_as(C.c_void_p),
+                             t.ctypes.data_as(C.c_char_p), nt.ctypes.data_as(C.c_void_p), C.c_uint32(s.shape[1]),
+                             aux.ctypes.data_as(C.c_void_p), *[x.ctypes.data_as(C.c_void_p) for x in o])
+        return dict(ed=o[0], sclen=o[1], indel=o[2], score=o[3])
