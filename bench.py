@@ -1,0 +1,279 @@
+#!/usr/bin/env python
+"""bench.py -- paired-end reads/s of the mapping hot path on B200 (BASELINE.json metric).
+
+A step = one pass of the hot path (seed lookup -> chaining -> extension -> classification, every
+packed contig in order) over one batch of synthetic pairs.  `value` times the batch resident in HBM
+(CUDA events on the library's stream, max over ranks); `e2e` times cm_gpu_process_batch_pe with host
+buffers (H2D + kernels + D2H).  `--impl reference` times the unmodified reference (oracle/_ref) on
+the host cores.  One process per GPU; reads are sharded, the index is replicated, no collective on
+the data path."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C2")
+    ap.add_argument("--pairs", type=int, default=0, help="pairs per GPU per step (0 = the config's)")
+    ap.add_argument("--data", default="/tmp/cm_bench")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--upto", type=int, default=3, help="1 seed, 2 +chain, 3 whole path")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                pass
+        sm, mx, reasons = [], 0, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    from circminer_b200 import workload
+    from circminer_b200.api import Mapper, default_params, fresh_mreads
+
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    t_prep = time.time()
+    w = workload.prepare(a.workload, os.path.join(a.data, f"{a.workload}_r{rank}"), n_pairs=a.pairs or None,
+                         seed_shift=rank)
+    n = len(w["s1"])
+    L = w["s1"].shape[1]
+    m = Mapper(default_params(), device=local)
+    workload.load_into(m, w)
+    n_contigs = len(w["contigs"])
+    t_prep = time.time() - t_prep
+
+    # pinned host buffers for the e2e leg
+    def pinned(arr):
+        t = torch.empty(arr.nbytes, dtype=torch.uint8, pin_memory=True)
+        v = t.numpy().view(arr.dtype).reshape(arr.shape)
+        v[...] = arr
+        return t, v
+    keep = []
+    hb = {}
+    for k, arr in (("s1", w["s1"]), ("s2", w["s2"]), ("mr", fresh_mreads(n))):
+        t, v = pinned(arr)
+        keep.append(t)
+        hb[k] = v
+
+    def step_resident():
+        ms = 0.0
+        for c in range(n_contigs):
+            m.run_staged(c, a.upto)
+            ms += m.stage_ms()[4]
+        return ms
+
+    def step_e2e():
+        mr = hb["mr"]
+        for c in range(n_contigs):
+            if a.upto >= 3:
+                mr, _ = m.process_read(c, hb["s1"], hb["s2"], mr)
+            else:
+                m.stage(hb["s1"], hb["s2"], mr)
+                m.run_staged(c, a.upto)
+        return mr
+
+    m.stage(hb["s1"], hb["s2"], hb["mr"])
+    for _ in range(a.warmup):
+        step_resident()
+    m.counters(reset=True)
+    barrier()
+    clk = ClockSampler(local)
+    clk.start()
+    t0 = time.time()
+    dev_ms = 0.0
+    stage_acc = np.zeros(5)
+    for _ in range(a.steps):
+        dev_ms += step_resident()
+        stage_acc += np.array(m.stage_ms())
+    barrier()
+    wall_ms = (time.time() - t0) * 1e3
+    clocks = clk.stop()
+    ctr = m.counters()
+
+    # e2e through the C-ABI with host buffers
+    step_e2e()
+    barrier()
+    t0 = time.time()
+    for _ in range(a.steps):
+        step_e2e()
+    barrier()
+    e2e_ms = (time.time() - t0) * 1e3
+
+    t = torch.tensor([dev_ms, wall_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, wall_ms, e2e_ms = [float(x) for x in t.tolist()]
+    reads_total = 2.0 * n * world * a.steps
+
+    if rank == 0:
+        peak, how = measured_peak()
+        seed_ms = stage_acc[1] / a.steps
+        seed_bytes = 32.0 * ctr["seed_sectors"] / a.steps
+        ach = seed_bytes / (seed_ms * 1e-3) / 1e9 if seed_ms > 0 else 0.0
+        line = {
+            "metric": "paired-end reads/sec", "value": reads_total / (dev_ms * 1e-3), "unit": "reads/s",
+            "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": dev_ms / a.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": f"{a.workload}: {sum(len(c) for c in w['contigs'])} bp packed reference, "
+                                   f"{len(w['genes'])} genes, {n} pairs 2x{L} per GPU, k=20",
+                       "stages": {1: "seed", 2: "seed+chain", 3: "seed+chain+extend+classify"}[a.upto],
+                       "contigs": n_contigs, "l2": "inputs larger than L2 (index+reads > 1.5 GB per pass)",
+                       "sharding": "reads sharded per rank, index replicated, no collective"},
+            "wall_ms_per_step": wall_ms / a.steps,
+            "stage_ms": {"seed": stage_acc[1] / a.steps, "chain": stage_acc[2] / a.steps,
+                         "extend_classify": stage_acc[3] / a.steps},
+            "e2e": {"value": reads_total / (e2e_ms * 1e-3), "unit": "reads/s",
+                    "h2d_bytes_per_step": int(n_contigs * (hb["s1"].nbytes + hb["s2"].nbytes + hb["mr"].nbytes + 4 * n)),
+                    "d2h_bytes_per_step": int(n_contigs * (hb["mr"].nbytes + 4 * n))},
+            "gpu_launches": int(ctr["kernel_launches"]),
+            "clocks": clocks,
+            "roofline": {"kernel": "k_seed", "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
+                         "frac": ach / peak, "traffic": None, "peak_source": how,
+                         "algorithmic_bytes_per_launch": seed_bytes},
+            "counters": {k: v / a.steps for k, v in ctr.items()},
+            "prep_s": t_prep,
+        }
+        if not a.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_baseline(a, os.path.join(a.data, f"{a.workload}_r0"), n, threads=1)
+        print(json.dumps(line), flush=True)
+    m.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(a, datadir, n_pairs, threads, target_s=12.0):
+    """The unmodified reference (oracle/_ref) on this box's host cores, bounded sample, in a
+    subprocess: checker code never runs inside the product process."""
+    cmd = [sys.executable, "-m", "oracle.cpu_baseline", "--workload", a.workload, "--data", datadir,
+           "--pairs", str(n_pairs), "--threads", str(threads), "--target-s", str(target_s)]
+    try:
+        out = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=1500)
+        for ln in reversed(out.stdout.strip().splitlines()):
+            if ln.startswith("{"):
+                return json.loads(ln)
+        return {"value": None, "error": (out.stderr or out.stdout)[-400:]}
+    except Exception as e:  # noqa: BLE001
+        return {"value": None, "error": repr(e)[:400]}
+
+
+def run_reference(a):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    ncores = os.cpu_count() or 1
+    n = a.pairs or 0
+    res = []
+    datadir = os.path.join(a.data, f"{a.workload}_r0")
+    for _ in range(a.warmup + a.steps):
+        res.append(cpu_baseline(a, datadir, n, threads=ncores, target_s=10.0))
+    res = res[a.warmup:]
+    ok = [r for r in res if r.get("value")]
+    if not ok:
+        print(json.dumps({"impl": "reference", "unavailable": (res[-1].get("error") or "no result")[:200]}))
+        return
+    v = float(np.mean([r["value"] for r in ok]))
+    ms = float(np.mean([r["seconds"] for r in ok])) * 1e3
+    cb = dict(ok[-1])
+    cb["value"] = v
+    print(json.dumps({
+        "impl": "reference", "metric": "paired-end reads/sec", "value": v, "unit": "reads/s", "n_gpus": a.gpus,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+        "config": {"workload": f"{a.workload} (bounded sample per step: {cb.get('sample')})"},
+        "cpu_baseline": cb,
+        "e2e": {"value": v, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
+
+
+if __name__ == "__main__":
+    main()
