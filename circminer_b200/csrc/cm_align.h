@@ -1,2 +1,254 @@
+// Alignment arithmetic of the hot path, restated for one thread with the live band in
+// registers / local memory instead of the reference's 600x600 tables:
+//   ScoreMatrix::init                          src/align.cpp:725-760
+//   Alignment::global_alignment[_reverse]      src/align.cpp:166-212
+//   global_one_side_banded_alignment           src/align.cpp:219-252
+//   global_banded_alignment_drop (X-drop)      src/align.cpp:254-390
+//   global_banded_alignment[_reverse]          src/align.cpp:395-509
+//   local_alignment_right / _left              src/align.cpp:556-600
+//   DropAlignment::local_alignment_*_sc        src/align.cpp:669-723
+//   AlignCandid                                src/align.h:123-153
+// The reference's tables persist between calls, but every cell these functions read is written
+// in the same call (|i-j| = w+1 guard lines, row/column 0), so a rolling band is exact.
 #pragma once
 #include "cm_types.h"
+
+#define CM_BANDSZ (2 * CM_MAX_BAND + 3)
+#define CM_FULLDP_MAX 64   // largest s-length the full-DP fallback accepts (reference needs <= 2w)
+
+// score_ch / diff_ch: equal iff both in "ACGTacgt" and equal ignoring case; N never matches
+CM_HD bool cm_base_eq(uint8_t a, uint8_t b) {
+    uint8_t ua = a & 0xDF, ub = b & 0xDF;
+    if (ua != ub) return false;
+    return ua == 'A' || ua == 'C' || ua == 'G' || ua == 'T';
+}
+
+// logical character x of a sequence of length len, optionally read back to front
+CM_HD uint8_t cm_at(const uint8_t *p, int len, int x, bool rev) { return rev ? p[len - 1 - x] : p[x]; }
+
+struct AlignCand {   // AlignCandid
+    int ed, sclen, indel, score;
+};
+CM_HD AlignCand cm_cand(int e, int s, int i) { AlignCand c; c.ed = e; c.sclen = s; c.indel = i; c.score = -s - 2 * e; return c; }
+CM_HD AlignCand cm_cand4(int e, int s, int i, int scr) { AlignCand c; c.ed = e; c.sclen = s; c.indel = i; c.score = scr; return c; }
+CM_HD bool cm_cand_less(const AlignCand &a, const AlignCand &r) {
+    if (a.score != r.score) return a.score > r.score;
+    if (a.ed != r.ed) return a.ed < r.ed;
+    int x = a.indel < 0 ? -a.indel : a.indel, y = r.indel < 0 ? -r.indel : r.indel;
+    return x < y;
+}
+CM_HD void cm_cand_update(AlignCand &b, const AlignCand &r) { if (cm_cand_less(r, b)) b = r; }
+
+struct AlignStats {      // roofline numerators
+    uint64_t xdrop_cells, edit_cells, xdrop_calls, edit_calls;
+};
+
+// ---- unit-cost edit DP, last column ------------------------------------------------------
+// Fills col[i] = dp[i][m] for the rows the callers read, i in [lo, hi]; entries outside are DPTINF.
+// Banded when the reference bands (n > 2w and m > w), full otherwise.  rev: the *_reverse variant.
+CM_HDN void cm_edit_last_column(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, int w, int lo, int hi,
+                                uint32_t *out /* [hi-lo+1] */, AlignStats *st) {
+    if (st) st->edit_calls++;
+    for (int i = lo; i <= hi; i++) out[i - lo] = CM_DPTINF;
+    if (w < 0 || n <= 2 * w || m <= w) {
+        // global_alignment: full table, rolling column over j
+        if (n > CM_FULLDP_MAX) return;
+        uint32_t col[CM_FULLDP_MAX + 1];
+        for (int i = 0; i <= n; i++) col[i] = (uint32_t) i;
+        for (int j = 1; j <= m; j++) {
+            uint32_t diag = col[0];
+            col[0] = (uint32_t) j;
+            uint8_t tc = cm_at(t, m, j - 1, rev);
+            for (int i = 1; i <= n; i++) {
+                uint32_t up = col[i];   // dp[i][j-1]
+                uint32_t v = diag + (cm_base_eq(cm_at(s, n, i - 1, rev), tc) ? 0u : 1u);
+                uint32_t a = col[i - 1] + 1, b = up + 1;
+                v = v < a ? v : a;
+                v = v < b ? v : b;
+                diag = up;
+                col[i] = v;
+            }
+        }
+        if (st) st->edit_cells += (uint64_t) n * (uint64_t) (m > 0 ? m : 0);
+        for (int i = lo; i <= hi; i++)
+            if (i >= 0 && i <= n) out[i - lo] = col[i];
+        return;
+    }
+    // band: column j holds rows i in [j-w, j+w]; slot d = i - j + w + 1, slots 0 and 2w+2 are the guard lines
+    uint32_t prev[CM_BANDSZ], cur[CM_BANDSZ];
+    const int B = 2 * w + 3;
+    for (int d = 0; d < B; d++) prev[d] = CM_DPTINF;
+    for (int i = 0; i <= w; i++) prev[i + w + 1] = (uint32_t) i;   // column 0: dp[i][0] = i, dp[w+1][0] = INF
+    uint64_t cells = 0;
+    for (int j = 1; j <= m; j++) {
+        for (int d = 0; d < B; d++) cur[d] = CM_DPTINF;
+        if (j <= w) cur[-j + w + 1] = (uint32_t) j;                // row 0: dp[0][j] = j
+        uint8_t tc = cm_at(t, m, j - 1, rev);
+        int i0 = j - w < 1 ? 1 : j - w, i1 = j + w > n ? n : j + w;
+        for (int i = i0; i <= i1; i++) {
+            int d = i - j + w + 1;
+            uint32_t v = prev[d] + (cm_base_eq(cm_at(s, n, i - 1, rev), tc) ? 0u : 1u);   // dp[i-1][j-1]
+            uint32_t a = cur[d - 1] + 1;                                                  // dp[i-1][j]
+            uint32_t b = prev[d + 1] + 1;                                                 // dp[i][j-1]
+            v = v < a ? v : a;
+            v = v < b ? v : b;
+            cur[d] = v;
+        }
+        cells += (uint64_t) (i1 >= i0 ? i1 - i0 + 1 : 0);
+        for (int d = 0; d < B; d++) prev[d] = cur[d];
+    }
+    if (st) st->edit_cells += cells;
+    for (int i = lo; i <= hi; i++) {
+        int d = i - m + w + 1;
+        if (i >= 0 && i <= n && d >= 1 && d <= 2 * w + 1) out[i - lo] = prev[d];
+    }
+}
+
+// Alignment::local_alignment_right (rev = false) / _left (rev = true): s = read piece, t = exon text
+CM_HDN int cm_local_alignment(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &indel,
+                              int &score, AlignStats *st) {
+    const int w = p.band_width;
+    int lo = m - w < 0 ? 0 : m - w, hi = m + w > n ? n : m + w;
+    uint32_t colv[2 * CM_MAX_BAND + 1];
+    if (hi >= lo) cm_edit_last_column(s, n, t, m, rev, w, lo, hi, colv, st);
+    AlignCand best = cm_cand(p.max_ed + 1, p.max_sc + 1, w + 1);
+    for (int i = lo; i <= hi; i++)
+        if (colv[i - lo] <= (uint32_t) p.max_ed) cm_cand_update(best, cm_cand((int) colv[i - lo], 0, m - i));
+    score = -best.ed;
+    indel = best.indel;
+    return best.ed;
+}
+
+// Alignment::global_one_side_banded_alignment: dp[n][m], rows i, columns j in [i, i+w]
+CM_HDN int cm_one_side_banded(const uint8_t *s, int n, const uint8_t *t, int m, int w, AlignStats *st) {
+    if (st) st->edit_calls++;
+    if (w < 0 || n <= w) {
+        uint32_t v = CM_DPTINF;
+        if (n < 0) n = 0;
+        if (n > CM_FULLDP_MAX) return (int) v;
+        uint32_t col[CM_FULLDP_MAX + 1];
+        for (int i = 0; i <= n; i++) col[i] = (uint32_t) i;
+        for (int j = 1; j <= m; j++) {
+            uint32_t diag = col[0];
+            col[0] = (uint32_t) j;
+            for (int i = 1; i <= n; i++) {
+                uint32_t up = col[i];
+                uint32_t x = diag + (cm_base_eq(s[i - 1], t[j - 1]) ? 0u : 1u);
+                uint32_t a = col[i - 1] + 1, b = up + 1;
+                x = x < a ? x : a;
+                x = x < b ? x : b;
+                diag = up;
+                col[i] = x;
+            }
+        }
+        if (st) st->edit_cells += (uint64_t) n * (uint64_t) (m > 0 ? m : 0);
+        return (int) col[n];
+    }
+    if (w > CM_MAX_BAND) return CM_DPTINF;
+    // slot d = j - i + 1 in [1, w+1]; slots 0 and w+2 are dp[i][i-1] and dp[i-1][i+w] (= DPTINF)
+    uint32_t prev[CM_MAX_BAND + 3], cur[CM_MAX_BAND + 3];
+    for (int d = 0; d <= w + 2; d++) prev[d] = CM_DPTINF;
+    for (int j = 0; j <= w; j++) prev[j + 1] = (uint32_t) j;
+    for (int i = 1; i <= n; i++) {
+        cur[0] = CM_DPTINF;
+        cur[w + 2] = CM_DPTINF;
+        uint8_t sc = s[i - 1];
+        for (int d = 1; d <= w + 1; d++) {
+            int j = i + d - 1;
+            uint32_t x = prev[d] + ((j <= m && cm_base_eq(sc, t[j - 1])) ? 0u : 1u);   // dp[i-1][j-1]; columns > m never reach dp[n][m]
+            uint32_t a = prev[d + 1] + 1;                                  // dp[i-1][j]
+            uint32_t b = cur[d - 1] + 1;                                   // dp[i][j-1]
+            x = x < a ? x : a;
+            x = x < b ? x : b;
+            cur[d] = x;
+        }
+        for (int d = 0; d <= w + 2; d++) prev[d] = cur[d];
+    }
+    if (st) st->edit_cells += (uint64_t) n * (uint64_t) (w + 1);
+    int d = m - n + 1;
+    if (d < 1 || d > w + 1) return CM_DPTINF;
+    return (int) prev[d];
+}
+
+// ---- X-drop banded score DP --------------------------------------------------------------
+// Alignment::global_banded_alignment_drop: s = reference text (n), t = read piece (m).  Anti-diagonal
+// k = i + j; slot d = i - j + w + 1 in [1, 2w+1]; slots 0 and 2w+2 are the -DPTINF guard lines
+// dpx[x][x+w+1] / dpx[x+w+1][x].  Returns the last cell (in (k, i) visit order) holding the running
+// maximum, and that maximum (== dpx[on_s][on_t], which is never pruned).
+CM_HDN void cm_xdrop(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &on_s, int &on_t,
+                     int &score, AlignStats *st) {
+    const int w = p.band_width, B = 2 * w + 3;
+    const int ind = p.ind_sc, NEG = -CM_DPTINF;
+    if (st) st->xdrop_calls++;
+    on_s = 0;
+    on_t = 0;
+    score = 0;
+    if (m <= 0 || n <= 0) return;
+    int buf[3][CM_BANDSZ];
+    int *a2 = buf[0], *a1 = buf[1], *a0 = buf[2];
+    for (int d = 0; d < B; d++) { a2[d] = NEG; a1[d] = NEG; }
+    a2[w + 1] = 0;                                  // dpx[0][0]
+    if (w >= 1) { a1[w + 2] = ind; a1[w] = ind; }   // dpx[1][0], dpx[0][1]
+    int pre_optimum = 0, cur_optimum = 0;
+    int lb = 1, ub = 1;
+    int new_ub, pre_ub = 0, best_i = 0, best_j = 0;
+    uint64_t cells = 0;
+    for (int k = 2; k <= m + n; ++k) {
+        for (int d = 0; d < B; d++) a0[d] = NEG;
+        if (k <= w) { a0[k + w + 1] = k * ind; a0[-k + w + 1] = k * ind; }
+        new_ub = -1;
+        for (int i = lb; i <= ub; ++i) {
+            int j = k - i;
+            int d = i - j + w + 1;
+            if (d < 1 || d > 2 * w + 1) continue;   // cannot happen with the reference's lb/ub evolution
+            int sc = cm_base_eq(cm_at(s, n, i - 1, rev), cm_at(t, m, j - 1, rev)) ? p.mat_sc : p.mis_sc;
+            int v = a2[d] + sc;
+            int x = a1[d - 1] + ind;   // dpx[i-1][j]
+            int y = a1[d + 1] + ind;   // dpx[i][j-1]
+            v = v > x ? v : x;
+            v = v > y ? v : y;
+            cells++;
+            if (v > cur_optimum) cur_optimum = v;
+            if (v >= cur_optimum) {
+                cur_optimum = v;
+                best_i = i;
+                best_j = j;
+            }
+            if (v + p.xdrop < pre_optimum) v = NEG;
+            if (v > NEG) new_ub = i;
+            a0[d] = v;
+        }
+        int lb_t = k - lb;
+        if (lb_t == m || (k > w && ((k - w) % 2 == 0))) ++lb;
+        if (ub < n && (k <= w || (k > w && ((k - w) % 2 == 1)))) ++ub;
+        if ((pre_ub == -1 && new_ub == -1) || lb > ub) break;
+        pre_ub = new_ub;
+        if (cur_optimum > pre_optimum) pre_optimum = cur_optimum;
+        int *tmp = a2;
+        a2 = a1;
+        a1 = a0;
+        a0 = tmp;
+    }
+    if (st) st->xdrop_cells += cells;
+    on_s = best_i;
+    on_t = best_j;
+    score = cur_optimum;
+}
+
+// DropAlignment::local_alignment_right_sc (rev = false) / _left_sc (rev = true: both strings reversed)
+CM_HDN int cm_drop_alignment_sc(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &sc_len,
+                                int &indel, int &score, AlignStats *st) {
+    int on_s, on_t;
+    cm_xdrop(s, n, t, m, rev, p, on_s, on_t, score, st);
+    int mx = on_s > on_t ? on_s : on_t;
+    uint32_t ed = (uint32_t) ((p.mat_sc * mx - score) / (p.mat_sc - p.mis_sc));
+    if (ed <= (uint32_t) p.max_ed) {
+        // best.update / best.set always take the candidate: its score is >= 0 == best.score and ed <= max_ed
+        sc_len = m - on_t;
+        indel = on_t - on_s;
+        return (int) ed;
+    }
+    sc_len = (p.max_sc > m ? p.max_sc : m) + 1;
+    indel = p.band_width + 1;
+    return p.max_ed + 1;
+}
