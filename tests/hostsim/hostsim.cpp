@@ -1,0 +1,263 @@
+// TEST INFRASTRUCTURE ONLY -- never loaded by the product path (circminer_b200/).
+//
+// g++ build of the very same CM_HD functions the CUDA kernels run (circminer_b200/csrc/cm_*.h), so
+// that the per-read logic can be compared with the reference (oracle/_ref) in the GPU-less build
+// container.  It is a debugging aid for bit-exactness, not a CPU fallback: the C-ABI library
+// libcm_gpu.so has no host path and fails without a device.
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../../circminer_b200/csrc/cm_pipeline.h"
+
+#pragma pack(push, 1)
+struct GeneralIndexPacked {
+    uint16_t checksum;
+    uint32_t info;
+};
+#pragma pack(pop)
+
+struct HsContig {
+    std::vector<uint32_t> dir, pos;
+    std::vector<uint16_t> cks;
+    std::vector<uint8_t> genome;
+    ContigDev d{};
+    AnnotDev a{};
+    bool has_annot = false;
+};
+
+struct HsCtx {
+    cm_params p;
+    int max_seg_cnt, n_slots;
+    std::vector<HsContig *> contigs;
+};
+
+static uint8_t hs_comp(uint8_t c) { return cm_comp(c); }
+
+extern "C" {
+
+HsCtx *hs_create(const cm_params *p) {
+    HsCtx *c = new HsCtx;
+    c->p = *p;
+    c->max_seg_cnt = cm_max_seg_cnt(*p);
+    c->n_slots = (c->max_seg_cnt + 1) / 2;
+    return c;
+}
+
+void hs_destroy(HsCtx *c) {
+    for (auto *x : c->contigs) delete x;
+    delete c;
+}
+
+// same sources as cm_gpu_load_contig, plus the contig text as ASCII (genome_ascii[0] = base 1)
+int hs_load_contig(HsCtx *c, int contig_id, const void *const *bucket_lists, const void *table_mem, const uint8_t *genome_ascii,
+                   uint32_t ref_len) {
+    if ((size_t) contig_id >= c->contigs.size()) c->contigs.resize(contig_id + 1, nullptr);
+    delete c->contigs[contig_id];
+    HsContig *h = new HsContig;
+    c->contigs[contig_id] = h;
+    h->dir.resize((size_t) CM_NBUCKETS + 1);
+    uint64_t total = 0;
+    for (uint32_t hv = 0; hv < CM_NBUCKETS; hv++) {
+        h->dir[hv] = (uint32_t) total;
+        const GeneralIndexPacked *l = (const GeneralIndexPacked *) bucket_lists[hv];
+        if (l) total += l[0].info;
+    }
+    h->dir[CM_NBUCKETS] = (uint32_t) total;
+    h->cks.resize(total);
+    h->pos.resize(total);
+    for (uint32_t hv = 0; hv < CM_NBUCKETS; hv++) {
+        const GeneralIndexPacked *l = (const GeneralIndexPacked *) bucket_lists[hv];
+        if (!l) continue;
+        for (uint32_t j = 0; j < l[0].info; j++) {
+            h->cks[h->dir[hv] + j] = l[1 + j].checksum;
+            h->pos[h->dir[hv] + j] = l[1 + j].info;
+        }
+    }
+    (void) table_mem;
+    h->genome.assign((size_t) ref_len + 64, 'N');
+    memcpy(h->genome.data() + 1, genome_ascii, ref_len);
+    h->d.dir = h->dir.data();
+    h->d.cks = h->cks.data();
+    h->d.pos = h->pos.data();
+    h->d.genome = h->genome.data();
+    h->d.n_entries = total;
+    h->d.ref_len = ref_len;
+    return 0;
+}
+
+// the arrays of `A` must outlive the context (the Python wrapper keeps them)
+int hs_load_annotation(HsCtx *c, int contig_id, const cm_annot_flat *A) {
+    HsContig *h = c->contigs[contig_id];
+    AnnotDev &a = h->a;
+    a.n_iv = A->n_iv; a.iv_spos = A->iv_spos; a.iv_epos = A->iv_epos; a.iv_max_end = A->iv_max_end;
+    a.iv_min_end = A->iv_min_end; a.iv_max_next_exon = A->iv_max_next_exon; a.iv_seg_off = A->iv_seg_off;
+    a.n_seg = A->n_seg; a.seg_start = A->seg_start; a.seg_end = A->seg_end; a.seg_next_exon_beg = A->seg_next_exon_beg;
+    a.seg_gene_id = A->seg_gene_id; a.seg_tid_off = A->seg_tid_off; a.tid = A->tid;
+    a.n_trans = A->n_trans; a.trans_start_ind = A->trans_start_ind; a.t2s_off = A->t2s_off; a.t2s = A->t2s;
+    a.n_genes = A->n_genes; a.gene_start = A->gene_start; a.gene_end = A->gene_end;
+    a.n_chr = A->n_chr; a.chr_shift = A->chr_shift; a.chr_id = A->chr_id;
+    a.n_bits = A->n_bits; a.near_border = A->near_border; a.intronic = A->intronic;
+    h->has_annot = true;
+    return 0;
+}
+
+static DevView make_view(HsCtx *c, int contig_id) {
+    DevView v;
+    v.p = c->p;
+    v.c = c->contigs[contig_id]->d;
+    v.a = c->contigs[contig_id]->a;
+    v.contig_id = contig_id;
+    v.max_seg_cnt = c->max_seg_cnt;
+    v.n_slots = c->n_slots;
+    return v;
+}
+
+// host mirror of the device batch: strands + seeds + chains
+struct HsBatch {
+    std::vector<uint8_t> strands;
+    std::vector<uint16_t> slen;
+    std::vector<uint32_t> seed_off, seed_cnt, chain_len;
+    std::vector<int32_t> chain_cnt, chain_hh;
+    std::vector<float> chain_score;
+    std::vector<FragDev> chain_frags;
+    BatchDev b{};
+};
+
+static void build_batch(HsCtx *c, const DevView &v, HsBatch &B, uint32_t n_reads, const char *const *srcs, const uint16_t *const *lens,
+                        int n_src, uint32_t in_stride, uint64_t *links) {
+    // read r of source k -> strands 2*(r*n_src+k) (fwd) and +1 (rc)
+    uint32_t stride = (uint32_t) ((c->p.max_read_len + 15) / 16 * 16);
+    uint32_t ns = 2 * n_reads * n_src;
+    B.strands.assign((size_t) ns * stride, 0);
+    B.slen.resize(ns);
+    for (uint32_t r = 0; r < n_reads; r++)
+        for (int k = 0; k < n_src; k++) {
+            uint32_t s0 = 2 * (r * n_src + k);
+            const uint8_t *src = (const uint8_t *) srcs[k] + (size_t) r * in_stride;
+            uint32_t len = lens[k][r];
+            uint8_t *fw = &B.strands[(size_t) s0 * stride], *rc = fw + stride;
+            for (uint32_t j = 0; j < len; j++) {
+                fw[j] = src[j];
+                rc[j] = hs_comp(src[len - 1 - j]);
+            }
+            B.slen[s0] = B.slen[s0 + 1] = (uint16_t) len;
+        }
+    int C = c->p.max_chain_len, F = c->n_slots;
+    B.seed_off.assign((size_t) ns * c->n_slots, 0);
+    B.seed_cnt.assign((size_t) ns * c->n_slots, 0);
+    B.chain_cnt.assign(ns, 0);
+    B.chain_hh.assign(ns, 0);
+    B.chain_score.assign((size_t) ns * C, 0.f);
+    B.chain_len.assign((size_t) ns * C, 0);
+    B.chain_frags.assign((size_t) ns * C * F, FragDev{0, 0});
+    BatchDev &b = B.b;
+    b.strands = B.strands.data(); b.strand_len = B.slen.data(); b.n_strands = ns; b.stride = stride; b.F = F; b.C = C;
+    b.seed_off = B.seed_off.data(); b.seed_cnt = B.seed_cnt.data(); b.chain_cnt = B.chain_cnt.data(); b.chain_hh = B.chain_hh.data();
+    b.chain_score = B.chain_score.data(); b.chain_len = B.chain_len.data(); b.chain_frags = B.chain_frags.data();
+    std::vector<double> dps;
+    std::vector<uint32_t> dpp;
+    std::vector<ChainRec> recs;
+    for (uint32_t s = 0; s < ns; s++) {
+        uint32_t *so = &B.seed_off[(size_t) s * c->n_slots], *sc = &B.seed_cnt[(size_t) s * c->n_slots];
+        cm_strand_seed(v, b.strands + (size_t) s * stride, B.slen[s], so, sc);
+        uint32_t row_pos_off[CM_MAX_SEEDS], row_cnt[CM_MAX_SEEDS], row_off[CM_MAX_SEEDS], cells;
+        int hh;
+        int T = cm_chain_rows(v, so, sc, row_pos_off, row_cnt, row_off, cells, hh);
+        B.chain_hh[s] = hh;
+        if (T <= 0) continue;
+        dps.resize(cells + 1);
+        dpp.resize(cells + 1);
+        uint32_t nrec = cm_chain_dp(v, B.slen[s], T, row_pos_off, row_cnt, row_off, dps.data(), dpp.data(), nullptr, 0, nullptr);
+        recs.resize(nrec + 1);
+        cm_chain_dp(v, B.slen[s], T, row_pos_off, row_cnt, row_off, dps.data(), dpp.data(), recs.data(), nrec, links);
+        ChainOut out;
+        out.count = &B.chain_cnt[s];
+        out.score = &B.chain_score[(size_t) s * C];
+        out.len = &B.chain_len[(size_t) s * C];
+        out.frags = &B.chain_frags[(size_t) s * C * F];
+        out.F = F;
+        cm_chain_backtrack(v, T, row_pos_off, row_cnt, row_off, dps.data(), dpp.data(), recs.data(), nrec, out);
+    }
+}
+
+int hs_chain_batch(HsCtx *c, int contig_id, uint32_t n, const char *seqs, uint32_t stride, const uint16_t *len, int32_t *chain_count,
+                   int32_t *high_hits, float *score, uint32_t *chain_len, uint32_t *frag_rpos, int32_t *frag_qpos) {
+    DevView v = make_view(c, contig_id);
+    HsBatch B;
+    const char *srcs[1] = {seqs};
+    const uint16_t *lens[1] = {len};
+    build_batch(c, v, B, n, srcs, lens, 1, stride, nullptr);
+    int C = c->p.max_chain_len, F = c->n_slots;
+    for (uint32_t i = 0; i < n; i++) {
+        uint32_t s = 2 * i;   // forward strand of row i
+        chain_count[i] = B.chain_cnt[s];
+        high_hits[i] = B.chain_hh[s];
+        for (int k = 0; k < C; k++) {
+            bool live = k < B.chain_cnt[s];
+            score[(size_t) i * C + k] = live ? B.chain_score[(size_t) s * C + k] : 0.f;
+            uint32_t L = live ? B.chain_len[(size_t) s * C + k] : 0;
+            chain_len[(size_t) i * C + k] = L;
+            for (int f = 0; f < F; f++) {
+                bool lf = (uint32_t) f < L;
+                frag_rpos[((size_t) i * C + k) * F + f] = lf ? B.chain_frags[((size_t) s * C + k) * F + f].rpos : 0;
+                frag_qpos[((size_t) i * C + k) * F + f] = lf ? B.chain_frags[((size_t) s * C + k) * F + f].qpos : 0;
+            }
+        }
+    }
+    return 0;
+}
+
+int hs_process_batch_pe(HsCtx *c, int contig_id, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
+                        const uint16_t *len1, const uint16_t *len2, const cm_mread *in, cm_mread *out, int32_t *state,
+                        cm_counters *ctr) {
+    DevView v = make_view(c, contig_id);
+    HsBatch B;
+    const char *srcs[2] = {seqs1, seqs2};
+    const uint16_t *lens[2] = {len1, len2};
+    uint64_t links = 0;
+    build_batch(c, v, B, n, srcs, lens, 2, stride, &links);
+    AlignStats tot{0, 0, 0, 0};
+    for (uint32_t i = 0; i < n; i++) {
+        cm_mread mr = in[i];
+        AlignStats st;
+        state[i] = cm_pair_process(v, B.b, i, mr, st);
+        out[i] = mr;
+        tot.xdrop_cells += st.xdrop_cells; tot.edit_cells += st.edit_cells;
+        tot.xdrop_calls += st.xdrop_calls; tot.edit_calls += st.edit_calls;
+    }
+    if (ctr) {
+        memset(ctr, 0, sizeof *ctr);
+        ctr->chain_links = links; ctr->xdrop_cells = tot.xdrop_cells; ctr->edit_cells = tot.edit_cells;
+        ctr->xdrop_calls = tot.xdrop_calls; ctr->edit_calls = tot.edit_calls; ctr->pairs = n;
+    }
+    return 0;
+}
+
+int hs_process_batch_se(HsCtx *c, int contig_id, uint32_t n, const char *seqs, uint32_t stride, const uint16_t *len, int32_t *state) {
+    DevView v = make_view(c, contig_id);
+    HsBatch B;
+    const char *srcs[1] = {seqs};
+    const uint16_t *lens[1] = {len};
+    build_batch(c, v, B, n, srcs, lens, 1, stride, nullptr);
+    for (uint32_t i = 0; i < n; i++) {
+        AlignStats st;
+        state[i] = cm_read_process_se(v, B.b, i, st);
+    }
+    return 0;
+}
+
+int hs_align_batch(HsCtx *c, int kind, uint32_t n, const char *s, const uint16_t *n_s, const char *t, const uint16_t *n_t,
+                   uint32_t stride, const int32_t *aux, int32_t *out_ed, int32_t *out_sclen, int32_t *out_indel, int32_t *out_score) {
+    for (uint32_t i = 0; i < n; i++) {
+        const uint8_t *si = (const uint8_t *) s + (size_t) i * stride, *ti = (const uint8_t *) t + (size_t) i * stride;
+        int ed = 0, sc = 0, indel = 0, score = 0;
+        if (kind == 0 || kind == 1) ed = cm_drop_alignment_sc(si, n_s[i], ti, n_t[i], kind == 1, c->p, sc, indel, score, nullptr);
+        else if (kind == 2 || kind == 3) ed = cm_local_alignment(si, n_s[i], ti, n_t[i], kind == 3, c->p, indel, score, nullptr);
+        else if (kind == 4) ed = cm_one_side_banded(si, n_s[i], ti, n_t[i], aux[i], nullptr);
+        out_ed[i] = ed; out_sclen[i] = sc; out_indel[i] = indel; out_score[i] = score;
+    }
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,101 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes wrapper over tests/hostsim/libhostsim.so (g++ build of the device
+headers).  Mirrors circminer_b200.api.Mapper so the same comparison code serves CPU debugging and
+the GPU parity tests."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from circminer_b200.api import MREAD_DTYPE, CmAnnotFlat, CmCounters, CmParams, _rows, _vp, default_params
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO = os.path.join(HERE, "hostsim", "libhostsim.so")
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", os.path.join(HERE, "hostsim")])
+
+
+class HostSim:
+    def __init__(self, params: CmParams | None = None):
+        build()
+        self.lib = C.CDLL(SO)
+        self.lib.hs_create.restype = C.c_void_p
+        self.params = params or default_params()
+        self.ctx = C.c_void_p(self.lib.hs_create(C.byref(self.params)))
+        k = self.params.kmer
+        self.S = 2 * ((self.params.max_read_len + k - 1) // k) - 1
+        self.F = (self.S + 1) // 2
+        self.Cn = self.params.max_chain_len
+        self._keep = []
+
+    def load_contig_from_reference(self, contig_id, bucket_lists, table_mem, genome_ascii: np.ndarray):
+        g = np.ascontiguousarray(genome_ascii, np.uint8)
+        self._keep.append(g)
+        self.lib.hs_load_contig(self.ctx, contig_id, C.c_void_p(bucket_lists), C.c_void_p(table_mem), _vp(g),
+                                C.c_uint32(len(g)))
+
+    def load_annotation(self, contig_id, a: dict):
+        f = CmAnnotFlat()
+        for k in ("n_iv", "n_seg", "n_tid", "n_trans", "n_genes", "n_chr", "n_bits"):
+            setattr(f, k, int(a[k]))
+
+        def put(name, dtype):
+            arr = np.ascontiguousarray(a[name], dtype)
+            if arr.size == 0:
+                arr = np.zeros(1, dtype)
+            self._keep.append(arr)
+            setattr(f, name, arr.ctypes.data)
+        for nm in ("iv_spos", "iv_epos", "iv_max_end", "iv_min_end", "iv_max_next_exon", "iv_seg_off", "seg_start",
+                   "seg_end", "seg_next_exon_beg", "seg_gene_id", "seg_tid_off", "tid", "t2s_off", "gene_start",
+                   "gene_end", "chr_shift"):
+            put(nm, np.uint32)
+        put("trans_start_ind", np.int32)
+        put("chr_id", np.int32)
+        put("t2s", np.uint8)
+        put("near_border", np.uint64)
+        put("intronic", np.uint64)
+        self.lib.hs_load_annotation(self.ctx, contig_id, C.byref(f))
+
+    def get_best_chains(self, contig_id, seqs, lens=None):
+        a, lens = _rows(seqs, lens)
+        n, Cn, F = a.shape[0], self.Cn, self.F
+        out = dict(chain_count=np.zeros(n, np.int32), high_hits=np.zeros(n, np.int32),
+                   score=np.zeros((n, Cn), np.float32), chain_len=np.zeros((n, Cn), np.uint32),
+                   frag_rpos=np.zeros((n, Cn, F), np.uint32), frag_qpos=np.zeros((n, Cn, F), np.int32))
+        self.lib.hs_chain_batch(self.ctx, contig_id, C.c_uint32(n), _vp(a), C.c_uint32(a.shape[1]), _vp(lens),
+                                _vp(out["chain_count"]), _vp(out["high_hits"]), _vp(out["score"]),
+                                _vp(out["chain_len"]), _vp(out["frag_rpos"]), _vp(out["frag_qpos"]))
+        return out
+
+    def process_read(self, contig_id, seqs1, seqs2, mreads, lens1=None, lens2=None):
+        a1, l1 = _rows(seqs1, lens1)
+        a2, l2 = _rows(seqs2, lens2)
+        n = a1.shape[0]
+        mreads = np.ascontiguousarray(mreads)
+        out = np.zeros(n, MREAD_DTYPE)
+        state = np.zeros(n, np.int32)
+        self.ctr = CmCounters()
+        self.lib.hs_process_batch_pe(self.ctx, contig_id, C.c_uint32(n), _vp(a1), _vp(a2), C.c_uint32(a1.shape[1]),
+                                     _vp(l1), _vp(l2), _vp(mreads), _vp(out), _vp(state), C.byref(self.ctr))
+        return out, state
+
+    def process_read_se(self, contig_id, seqs, lens=None):
+        a, l = _rows(seqs, lens)
+        state = np.zeros(a.shape[0], np.int32)
+        self.lib.hs_process_batch_se(self.ctx, contig_id, C.c_uint32(a.shape[0]), _vp(a), C.c_uint32(a.shape[1]),
+                                     _vp(l), _vp(state))
+        return state
+
+    def align(self, kind, s, ns, t, nt, aux=None):
+        s, ns = _rows(s, ns)
+        t, nt = _rows(t, nt)
+        n = s.shape[0]
+        aux = np.zeros(n, np.int32) if aux is None else np.ascontiguousarray(aux, np.int32)
+        o = [np.zeros(n, np.int32) for _ in range(4)]
+        self.lib.hs_align_batch(self.ctx, kind, C.c_uint32(n), _vp(s), _vp(ns), _vp(t), _vp(nt),
+                                C.c_uint32(s.shape[1]), _vp(aux), *[_vp(x) for x in o])
+        return dict(ed=o[0], sclen=o[1], indel=o[2], score=o[3])
