@@ -11,13 +11,7 @@
 #include <string>
 #include <vector>
 
-#include "cm_types.h"
-#include "cm_seed.h"
-#include "cm_annot.h"
-#include "cm_chain.h"
-#include "cm_align.h"
-#include "cm_extend.h"
-#include "cm_filter.h"
+#include "cm_pipeline.h"
 
 // ------------------------------------------------------------------------------------------
 // context
@@ -56,10 +50,13 @@ struct cm_gpu_ctx {
     DevBuf in_seq1, in_seq2, in_len1, in_len2, in_mread;  // raw uploads
     DevBuf strands, strand_len;                           // [n_strands][stride] fwd/rc rows, lengths
     DevBuf seed_off, seed_cnt;                            // [n_strands][n_slots]
-    DevBuf cell_off;                                      // [n_strands + 1] dp-cell arena offsets
-    DevBuf rec_cnt, rec_off;                              // [n_strands (+1)] k-best record arena offsets
-    DevBuf dp_score, dp_prev, recs;                       // arenas
-    DevBuf chain_cnt, chain_hh, chain_hdr, chain_frags;   // chains per strand
+    DevBuf cell_cnt, cell_off;                            // dp cells per strand, exclusive prefix (u64)
+    DevBuf dp_score, dp_prev, recs;                       // chaining arenas
+    DevBuf ovf_strand, ovf_nrec, ovf_n, ovf_off, ovf_recs;  // strands whose record list outgrew its slice
+    DevBuf chain_cnt, chain_hh, chain_score, chain_len, chain_frags;   // chains per strand
+    int batch_F = 1;           // fragment slots per chain for the staged batch
+    uint32_t rec_mult = 3;     // record-arena slice = rec_mult * cells + 8 (CM_GPU_REC_MULT overrides; 0 forces the overflow path)
+    uint32_t last_overflow = 0;
     DevBuf out_mread, out_state;
     DevBuf cub_tmp;
     DevBuf scratch[8];
@@ -157,6 +154,7 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
         return fail(nullptr, CM_ERR_ALLOC, "cudaMalloc counters");
     }
     cudaMemset(ctx->d_counters, 0, sizeof(cm_counters));
+    if (const char *e = getenv("CM_GPU_REC_MULT")) ctx->rec_mult = (uint32_t) atoi(e);
     *out = ctx;
     return CM_OK;
 }
@@ -173,8 +171,9 @@ extern "C" int cm_gpu_destroy(cm_gpu_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     for (auto &c : ctx->contigs) free_contig(c);
     DevBuf *bufs[] = {&ctx->in_seq1, &ctx->in_seq2, &ctx->in_len1, &ctx->in_len2, &ctx->in_mread, &ctx->strands,
-                      &ctx->strand_len, &ctx->seed_off, &ctx->seed_cnt, &ctx->cell_off, &ctx->rec_cnt, &ctx->rec_off,
-                      &ctx->dp_score, &ctx->dp_prev, &ctx->recs, &ctx->chain_cnt, &ctx->chain_hh, &ctx->chain_hdr,
+                      &ctx->strand_len, &ctx->seed_off, &ctx->seed_cnt, &ctx->cell_cnt, &ctx->cell_off,
+                      &ctx->dp_score, &ctx->dp_prev, &ctx->recs, &ctx->ovf_strand, &ctx->ovf_nrec, &ctx->ovf_n, &ctx->ovf_off,
+                      &ctx->ovf_recs, &ctx->chain_cnt, &ctx->chain_hh, &ctx->chain_score, &ctx->chain_len,
                       &ctx->chain_frags, &ctx->out_mread, &ctx->out_state, &ctx->cub_tmp};
     for (DevBuf *b : bufs) release(*b);
     for (auto &b : ctx->scratch) release(b);
@@ -540,7 +539,10 @@ static int stage_reads(cm_gpu_ctx *ctx, uint32_t n, const char *s1, const char *
     if (n == 0) { ctx->n_pairs = 0; ctx->n_strands = 0; return CM_OK; }
     if (!s1 || !l1 || (s2 && !l2)) return fail(ctx, CM_ERR_ARG, "null argument");
     if (in_stride == 0) return fail(ctx, CM_ERR_ARG, "stride is 0");
+    uint32_t max_len = 0;
     for (uint32_t i = 0; i < n; i++) {
+        if (l1[i] > max_len) max_len = l1[i];
+        if (s2 && l2[i] > max_len) max_len = l2[i];
         if (l1[i] > in_stride || (s2 && l2[i] > in_stride)) return fail(ctx, CM_ERR_ARG, "read %u longer than stride", i);
         if (l1[i] > ctx->p.max_read_len || (s2 && l2[i] > ctx->p.max_read_len))
             return fail(ctx, CM_ERR_ARG, "read %u longer than max_read_len", i);
@@ -567,6 +569,8 @@ static int stage_reads(cm_gpu_ctx *ctx, uint32_t n, const char *s1, const char *
     ctx->n_strands = n_strands;
     ctx->stride = stride;
     ctx->staged_pe = s2 != nullptr;
+    ctx->batch_F = cm_seed_count((int) max_len, ctx->p.kmer);
+    if (ctx->batch_F < 1) ctx->batch_F = 1;
     return CM_OK;
 }
 
@@ -738,4 +742,5 @@ extern "C" int cm_gpu_seed_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, con
     return CM_OK;
 }
 
-#include "cm_pipeline.cuh"
+#include "cm_kernels.cuh"
+#include "cm_host_pipeline.cuh"

@@ -1,0 +1,263 @@
+// Host side of the batch pipeline: arena sizing, launches, stage timing, C-ABI batch entries.
+#pragma once
+
+static int make_batch(cm_gpu_ctx *ctx, BatchDev &b) {
+    const size_t ns = ctx->n_strands;
+    const int C = ctx->p.max_chain_len, F = ctx->batch_F;
+    ENSURE(ctx, ctx->seed_off, ns * ctx->n_slots * 4);
+    ENSURE(ctx, ctx->seed_cnt, ns * ctx->n_slots * 4);
+    ENSURE(ctx, ctx->chain_cnt, ns * 4);
+    ENSURE(ctx, ctx->chain_hh, ns * 4);
+    ENSURE(ctx, ctx->chain_score, ns * C * 4);
+    ENSURE(ctx, ctx->chain_len, ns * C * 4);
+    ENSURE(ctx, ctx->chain_frags, ns * C * F * sizeof(FragDev));
+    b.strands = (const uint8_t *) ctx->strands.p;
+    b.strand_len = (const uint16_t *) ctx->strand_len.p;
+    b.n_strands = (uint32_t) ns;
+    b.stride = ctx->stride;
+    b.F = F;
+    b.C = C;
+    b.seed_off = (uint32_t *) ctx->seed_off.p;
+    b.seed_cnt = (uint32_t *) ctx->seed_cnt.p;
+    b.chain_cnt = (int32_t *) ctx->chain_cnt.p;
+    b.chain_hh = (int32_t *) ctx->chain_hh.p;
+    b.chain_score = (float *) ctx->chain_score.p;
+    b.chain_len = (uint32_t *) ctx->chain_len.p;
+    b.chain_frags = (FragDev *) ctx->chain_frags.p;
+    return CM_OK;
+}
+
+static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) {
+    if (!ctx->n_strands) return CM_OK;
+    cudaStream_t st = ctx->stream;
+    const uint32_t ns = ctx->n_strands;
+    ENSURE(ctx, ctx->cell_cnt, (size_t) ns * 4);
+    ENSURE(ctx, ctx->cell_off, ((size_t) ns + 1) * 8);
+    k_cell_count<<<grid_for(ns, 256), 256, 0, st>>>(v, b.seed_cnt, ns, (uint32_t *) ctx->cell_cnt.p);
+    ctx->launches++;
+    size_t tb = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tb, (const uint32_t *) ctx->cell_cnt.p, (uint64_t *) ctx->cell_off.p, (int) ns, st);
+    ENSURE(ctx, ctx->cub_tmp, tb + 16);
+    cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tb, (const uint32_t *) ctx->cell_cnt.p, (uint64_t *) ctx->cell_off.p, (int) ns, st);
+    ctx->launches++;
+    // total cells = off[ns-1] + cnt[ns-1]
+    uint64_t last_off = 0;
+    uint32_t last_cnt = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&last_off, (uint64_t *) ctx->cell_off.p + (ns - 1), 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&last_cnt, (uint32_t *) ctx->cell_cnt.p + (ns - 1), 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const uint64_t cells = last_off + last_cnt;
+    ENSURE(ctx, ctx->dp_score, (size_t) (cells + 1) * 8);
+    ENSURE(ctx, ctx->dp_prev, (size_t) (cells + 1) * 4);
+    const uint32_t mult = ctx->rec_mult;
+    ENSURE(ctx, ctx->recs, (size_t) ((uint64_t) mult * cells + 8ull * ns + 1) * sizeof(ChainRec));
+    ENSURE(ctx, ctx->ovf_strand, (size_t) ns * 4);
+    ENSURE(ctx, ctx->ovf_nrec, (size_t) ns * 4);
+    ENSURE(ctx, ctx->ovf_n, 8);
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->ovf_n.p, 0, 8, st));
+    k_chain<<<grid_for(ns, 128), 128, 0, st>>>(v, b, (const uint64_t *) ctx->cell_off.p, (double *) ctx->dp_score.p,
+                                               (uint32_t *) ctx->dp_prev.p, (ChainRec *) ctx->recs.p, mult,
+                                               (uint32_t *) ctx->ovf_strand.p, (uint32_t *) ctx->ovf_nrec.p, (uint32_t *) ctx->ovf_n.p,
+                                               ctx->d_counters);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    uint32_t n_ovf = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&n_ovf, ctx->ovf_n.p, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    ctx->last_overflow = n_ovf;
+    if (n_ovf) {
+        std::vector<uint32_t> nrec(n_ovf);
+        std::vector<uint64_t> off(n_ovf);
+        CUDA_TRY(ctx, cudaMemcpy(nrec.data(), ctx->ovf_nrec.p, (size_t) n_ovf * 4, cudaMemcpyDeviceToHost));
+        uint64_t tot = 0;
+        for (uint32_t k = 0; k < n_ovf; k++) { off[k] = tot; tot += nrec[k]; }
+        ENSURE(ctx, ctx->ovf_off, (size_t) n_ovf * 8);
+        ENSURE(ctx, ctx->ovf_recs, (size_t) (tot + 1) * sizeof(ChainRec));
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->ovf_off.p, off.data(), (size_t) n_ovf * 8, cudaMemcpyHostToDevice, st));
+        k_chain_big<<<grid_for(n_ovf, 128), 128, 0, st>>>(v, b, (const uint64_t *) ctx->cell_off.p, (double *) ctx->dp_score.p,
+                                                         (uint32_t *) ctx->dp_prev.p, (const uint32_t *) ctx->ovf_strand.p,
+                                                         (const uint64_t *) ctx->ovf_off.p, (const uint32_t *) ctx->ovf_nrec.p, n_ovf,
+                                                         (ChainRec *) ctx->ovf_recs.p);
+        ctx->launches++;
+        CUDA_TRY(ctx, cudaGetLastError());
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));   // off[] is host memory
+    }
+    return CM_OK;
+}
+
+static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) {
+    if (!ctx->n_pairs) return CM_OK;
+    const uint32_t n = ctx->n_pairs;
+    ENSURE(ctx, ctx->out_state, (size_t) n * 4);
+    if (ctx->staged_pe) {
+        ENSURE(ctx, ctx->out_mread, (size_t) n * sizeof(cm_mread));
+        k_process_pe<<<grid_for(n, 128), 128, 0, ctx->stream>>>(v, b, (const cm_mread *) ctx->in_mread.p, (cm_mread *) ctx->out_mread.p,
+                                                               (int32_t *) ctx->out_state.p, n, ctx->d_counters);
+    } else {
+        k_process_se<<<grid_for(n, 128), 128, 0, ctx->stream>>>(v, b, (int32_t *) ctx->out_state.p, n, ctx->d_counters);
+    }
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return CM_OK;
+}
+
+// seed -> chain -> extend/classify on the staged batch; stage times from events on the context's stream
+static int run_pipeline(cm_gpu_ctx *ctx, int contig_id, int upto) {
+    DevView v;
+    int r = make_view(ctx, contig_id, upto > 1, v);
+    if (r != CM_OK) return r;
+    for (float &m : ctx->stage_ms) m = 0.f;
+    if (!ctx->n_strands) return CM_OK;
+    BatchDev b;
+    if ((r = make_batch(ctx, b)) != CM_OK) return r;
+    cudaStream_t st = ctx->stream;
+    cudaEventRecord(ctx->ev[0], st);
+    if ((r = launch_seed(ctx, v)) != CM_OK) return r;
+    cudaEventRecord(ctx->ev[1], st);
+    if (upto >= 2 && (r = launch_chain(ctx, v, b)) != CM_OK) return r;
+    cudaEventRecord(ctx->ev[2], st);
+    if (upto >= 3 && (r = launch_process(ctx, v, b)) != CM_OK) return r;
+    cudaEventRecord(ctx->ev[3], st);
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&ctx->stage_ms[1], ctx->ev[0], ctx->ev[1]);
+    cudaEventElapsedTime(&ctx->stage_ms[2], ctx->ev[1], ctx->ev[2]);
+    cudaEventElapsedTime(&ctx->stage_ms[3], ctx->ev[2], ctx->ev[3]);
+    cudaEventElapsedTime(&ctx->stage_ms[4], ctx->ev[0], ctx->ev[3]);
+    return CM_OK;
+}
+
+// ---- C-ABI batch entries ---------------------------------------------------------------
+extern "C" int cm_gpu_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride, const uint16_t *len,
+                                  int32_t *chain_count, int32_t *high_hits, float *score, uint32_t *chain_len, uint32_t *frag_rpos,
+                                  int32_t *frag_qpos) {
+    if (!ctx) return CM_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    DevView v;
+    int r = make_view(ctx, contig_id, true, v);
+    if (r != CM_OK) return r;
+    if (n == 0) return CM_OK;
+    // each input row is one strand: stage as SE reads, export the forward rows
+    if ((r = stage_reads(ctx, n, seqs, nullptr, stride, len, nullptr, nullptr)) != CM_OK) return r;
+    if ((r = launch_prep(ctx, stride)) != CM_OK) return r;
+    if ((r = run_pipeline(ctx, contig_id, 2)) != CM_OK) return r;
+    BatchDev b;
+    if ((r = make_batch(ctx, b)) != CM_OK) return r;
+    const size_t C = ctx->p.max_chain_len, FO = ctx->n_slots, rows = n;
+    ENSURE(ctx, ctx->scratch[0], rows * 4);
+    ENSURE(ctx, ctx->scratch[1], rows * 4);
+    ENSURE(ctx, ctx->scratch[2], rows * C * 4);
+    ENSURE(ctx, ctx->scratch[3], rows * C * 4);
+    ENSURE(ctx, ctx->scratch[4], rows * C * FO * 4);
+    ENSURE(ctx, ctx->scratch[5], rows * C * FO * 4);
+    k_chain_export<<<grid_for(rows * C, 256), 256, 0, ctx->stream>>>(v, b, n, (int32_t *) ctx->scratch[0].p, (int32_t *) ctx->scratch[1].p,
+                                                                    (float *) ctx->scratch[2].p, (uint32_t *) ctx->scratch[3].p,
+                                                                    (uint32_t *) ctx->scratch[4].p, (int32_t *) ctx->scratch[5].p);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    if ((r = fetch(ctx, chain_count, ctx->scratch[0].p, rows)) != CM_OK) return r;
+    if ((r = fetch(ctx, high_hits, ctx->scratch[1].p, rows)) != CM_OK) return r;
+    if ((r = fetch(ctx, score, ctx->scratch[2].p, rows * C)) != CM_OK) return r;
+    if ((r = fetch(ctx, chain_len, ctx->scratch[3].p, rows * C)) != CM_OK) return r;
+    if ((r = fetch(ctx, frag_rpos, ctx->scratch[4].p, rows * C * FO)) != CM_OK) return r;
+    if ((r = fetch(ctx, frag_qpos, ctx->scratch[5].p, rows * C * FO)) != CM_OK) return r;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_align_batch(cm_gpu_ctx *ctx, int kind, uint32_t n, const char *s, const uint16_t *n_s, const char *t,
+                                  const uint16_t *n_t, uint32_t stride, const int32_t *aux, int32_t *out_ed, int32_t *out_sclen,
+                                  int32_t *out_indel, int32_t *out_score) {
+    if (!ctx) return CM_ERR_ARG;
+    if (kind < 0 || kind > 4) return fail(ctx, CM_ERR_ARG, "alignment kind must be 0..4");
+    if (n == 0) return CM_OK;
+    if (!s || !t || !n_s || !n_t || !out_ed || !out_sclen || !out_indel || !out_score || (kind == 4 && !aux))
+        return fail(ctx, CM_ERR_ARG, "null argument");
+    for (uint32_t i = 0; i < n; i++) {
+        if (n_s[i] > stride || n_t[i] > stride) return fail(ctx, CM_ERR_ARG, "problem %u longer than stride", i);
+        if (kind == 4 && aux[i] > CM_MAX_BAND) return fail(ctx, CM_ERR_ARG, "problem %u: band %d > %d", i, aux[i], CM_MAX_BAND);
+        // full-DP fallbacks keep one column of s in local memory
+        bool full = (kind == 2 || kind == 3) ? (n_s[i] <= 2 * ctx->p.band_width || n_t[i] <= ctx->p.band_width)
+                                             : (kind == 4 ? (aux[i] < 0 || n_s[i] <= aux[i]) : false);
+        if (full && n_s[i] > CM_FULLDP_MAX) return fail(ctx, CM_ERR_ARG, "problem %u: unbanded s longer than %d", i, CM_FULLDP_MAX);
+    }
+    cudaSetDevice(ctx->device);
+    cudaStream_t st = ctx->stream;
+    const size_t bytes = (size_t) n * stride;
+    ENSURE(ctx, ctx->scratch[0], bytes + 64);
+    ENSURE(ctx, ctx->scratch[1], bytes + 64);
+    ENSURE(ctx, ctx->scratch[2], (size_t) n * 2);
+    ENSURE(ctx, ctx->scratch[3], (size_t) n * 2);
+    ENSURE(ctx, ctx->scratch[4], (size_t) n * 4);
+    ENSURE(ctx, ctx->scratch[5], (size_t) n * 16);
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->scratch[0].p, s, bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->scratch[1].p, t, bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->scratch[2].p, n_s, (size_t) n * 2, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->scratch[3].p, n_t, (size_t) n * 2, cudaMemcpyHostToDevice, st));
+    if (aux) CUDA_TRY(ctx, cudaMemcpyAsync(ctx->scratch[4].p, aux, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    int32_t *o = (int32_t *) ctx->scratch[5].p;
+    k_align<<<grid_for(n, 128), 128, 0, st>>>(ctx->p, kind, n, (const uint8_t *) ctx->scratch[0].p, (const uint16_t *) ctx->scratch[2].p,
+                                              (const uint8_t *) ctx->scratch[1].p, (const uint16_t *) ctx->scratch[3].p, stride,
+                                              (const int32_t *) ctx->scratch[4].p, o, o + n, o + 2 * (size_t) n, o + 3 * (size_t) n);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    int r;
+    if ((r = fetch(ctx, out_ed, o, n)) != CM_OK) return r;
+    if ((r = fetch(ctx, out_sclen, o + n, n)) != CM_OK) return r;
+    if ((r = fetch(ctx, out_indel, o + 2 * (size_t) n, n)) != CM_OK) return r;
+    if ((r = fetch(ctx, out_score, o + 3 * (size_t) n, n)) != CM_OK) return r;
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_stage_batch_pe(cm_gpu_ctx *ctx, uint32_t n, const char *s1, const char *s2, uint32_t stride, const uint16_t *l1,
+                                     const uint16_t *l2, const cm_mread *in) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n && (!s2 || !in)) return fail(ctx, CM_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->device);
+    int r = stage_reads(ctx, n, s1, s2, stride, l1, l2, in);
+    if (r != CM_OK) return r;
+    if ((r = launch_prep(ctx, stride)) != CM_OK) return r;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_run_staged_pe(cm_gpu_ctx *ctx, int contig_id, int upto_stage) {
+    if (!ctx) return CM_ERR_ARG;
+    if (upto_stage < 1 || upto_stage > 3) return fail(ctx, CM_ERR_ARG, "upto_stage must be 1..3");
+    cudaSetDevice(ctx->device);
+    return run_pipeline(ctx, contig_id, upto_stage);
+}
+
+extern "C" int cm_gpu_fetch_staged_pe(cm_gpu_ctx *ctx, cm_mread *out, int32_t *state) {
+    if (!ctx) return CM_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    if (!ctx->n_pairs) return CM_OK;
+    if (!ctx->out_state.p || (ctx->staged_pe && !ctx->out_mread.p)) return fail(ctx, CM_ERR_STATE, "no results: run stage 3 first");
+    int r;
+    if (ctx->staged_pe && (r = fetch(ctx, out, ctx->out_mread.p, ctx->n_pairs)) != CM_OK) return r;
+    if ((r = fetch(ctx, state, ctx->out_state.p, ctx->n_pairs)) != CM_OK) return r;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_process_batch_pe(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
+                                       const uint16_t *len1, const uint16_t *len2, const cm_mread *in, cm_mread *out, int32_t *state) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n && (!out || !state)) return fail(ctx, CM_ERR_ARG, "null argument");
+    int r = cm_gpu_stage_batch_pe(ctx, n, seqs1, seqs2, stride, len1, len2, in);
+    if (r != CM_OK) return r;
+    if ((r = run_pipeline(ctx, contig_id, 3)) != CM_OK) return r;
+    return cm_gpu_fetch_staged_pe(ctx, out, state);
+}
+
+extern "C" int cm_gpu_process_batch_se(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride, const uint16_t *len,
+                                       int32_t *state) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n && !state) return fail(ctx, CM_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->device);
+    int r = stage_reads(ctx, n, seqs, nullptr, stride, len, nullptr, nullptr);
+    if (r != CM_OK) return r;
+    if ((r = launch_prep(ctx, stride)) != CM_OK) return r;
+    if ((r = run_pipeline(ctx, contig_id, 3)) != CM_OK) return r;
+    return cm_gpu_fetch_staged_pe(ctx, nullptr, state);
+}

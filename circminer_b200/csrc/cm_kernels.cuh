@@ -1,0 +1,164 @@
+// Chaining / classification kernels and the batch pipeline.  Included by cm_gpu.cu after the context.
+#pragma once
+
+// ------------------------------------------------------------------------------------------
+// K2a: dp cells per strand (sum of kept hit-list lengths) -> exclusive scan gives arena offsets
+// ------------------------------------------------------------------------------------------
+__global__ void k_cell_count(DevView v, const uint32_t *__restrict__ seed_cnt, uint32_t n_strands, uint32_t *__restrict__ cells) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_strands) return;
+    uint32_t c = 0;
+    for (int t = 0; t < v.n_slots; t++) {
+        uint32_t raw = seed_cnt[(size_t) s * v.n_slots + t];
+        c += raw > (uint32_t) v.p.seed_lim ? 0 : raw;
+    }
+    cells[s] = c;
+}
+
+CM_HD uint64_t cm_rec_base(uint64_t cell_off, uint32_t strand, uint32_t mult) { return (uint64_t) mult * cell_off + 8ull * strand; }
+CM_HD uint32_t cm_rec_cap(uint32_t cells, uint32_t mult) { return mult * cells + 8u; }
+
+// ------------------------------------------------------------------------------------------
+// K2b: chaining, one thread per strand.  Strands whose improvement list outgrows its slice of the
+// record arena are queued for k_chain_big (exact two-pass sizing) instead of being truncated.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_chain(DevView v, BatchDev b, const uint64_t *__restrict__ cell_off, double *__restrict__ dp_score,
+                                               uint32_t *__restrict__ dp_prev, ChainRec *__restrict__ recs, uint32_t rec_mult,
+                                               uint32_t *__restrict__ ovf_strand, uint32_t *__restrict__ ovf_nrec,
+                                               uint32_t *__restrict__ n_ovf, cm_counters *__restrict__ ctr) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t links = 0;
+    if (s < b.n_strands) {
+        const uint32_t *so = b.seed_off + (size_t) s * v.n_slots, *sc = b.seed_cnt + (size_t) s * v.n_slots;
+        uint32_t row_pos_off[CM_MAX_SEEDS], row_cnt[CM_MAX_SEEDS], row_off[CM_MAX_SEEDS], cells;
+        int hh;
+        int T = cm_chain_rows(v, so, sc, row_pos_off, row_cnt, row_off, cells, hh);
+        b.chain_hh[s] = hh;
+        b.chain_cnt[s] = 0;
+        if (T > 0) {
+            uint64_t base = cell_off[s];
+            uint32_t cap = cm_rec_cap(cells, rec_mult);
+            ChainRec *r = recs + cm_rec_base(base, s, rec_mult);
+            uint32_t nrec = cm_chain_dp(v, b.strand_len[s], T, row_pos_off, row_cnt, row_off, dp_score + base, dp_prev + base, r, cap, &links);
+            if (nrec > cap) {
+                uint32_t k = atomicAdd(n_ovf, 1u);
+                ovf_strand[k] = s;
+                ovf_nrec[k] = nrec;
+            } else {
+                ChainOut out;
+                out.count = b.chain_cnt + s;
+                out.score = b.chain_score + (size_t) s * b.C;
+                out.len = b.chain_len + (size_t) s * b.C;
+                out.frags = b.chain_frags + (size_t) s * b.C * b.F;
+                out.F = b.F;
+                cm_chain_backtrack(v, T, row_pos_off, row_cnt, row_off, dp_score + base, dp_prev + base, r, nrec, out);
+            }
+        }
+    }
+    for (int o = 16; o; o >>= 1) links += __shfl_down_sync(0xffffffffu, links, o);
+    if ((threadIdx.x & 31) == 0 && links) atomicAdd((unsigned long long *) &ctr->chain_links, (unsigned long long) links);
+}
+
+// overflow path: record arena sized exactly from the counts k_chain produced
+__global__ void __launch_bounds__(128) k_chain_big(DevView v, BatchDev b, const uint64_t *__restrict__ cell_off, double *__restrict__ dp_score,
+                                                   uint32_t *__restrict__ dp_prev, const uint32_t *__restrict__ ovf_strand,
+                                                   const uint64_t *__restrict__ ovf_off, const uint32_t *__restrict__ ovf_nrec, uint32_t n_ovf,
+                                                   ChainRec *__restrict__ recs) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_ovf) return;
+    uint32_t s = ovf_strand[k];
+    const uint32_t *so = b.seed_off + (size_t) s * v.n_slots, *sc = b.seed_cnt + (size_t) s * v.n_slots;
+    uint32_t row_pos_off[CM_MAX_SEEDS], row_cnt[CM_MAX_SEEDS], row_off[CM_MAX_SEEDS], cells;
+    int hh;
+    int T = cm_chain_rows(v, so, sc, row_pos_off, row_cnt, row_off, cells, hh);
+    uint64_t base = cell_off[s];
+    ChainRec *r = recs + ovf_off[k];
+    uint32_t nrec = cm_chain_dp(v, b.strand_len[s], T, row_pos_off, row_cnt, row_off, dp_score + base, dp_prev + base, r, ovf_nrec[k], nullptr);
+    ChainOut out;
+    out.count = b.chain_cnt + s;
+    out.score = b.chain_score + (size_t) s * b.C;
+    out.len = b.chain_len + (size_t) s * b.C;
+    out.frags = b.chain_frags + (size_t) s * b.C * b.F;
+    out.F = b.F;
+    cm_chain_backtrack(v, T, row_pos_off, row_cnt, row_off, dp_score + base, dp_prev + base, r, nrec, out);
+}
+
+// ------------------------------------------------------------------------------------------
+// K3: extension + classification, one thread per pair (PE) / read (SE)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void warp_add_stats(const AlignStats &st, uint32_t pairs, cm_counters *ctr) {
+    unsigned long long a = st.xdrop_cells, b = st.edit_cells, c = st.xdrop_calls, d = st.edit_calls, e = pairs;
+    for (int o = 16; o; o >>= 1) {
+        a += __shfl_down_sync(0xffffffffu, a, o);
+        b += __shfl_down_sync(0xffffffffu, b, o);
+        c += __shfl_down_sync(0xffffffffu, c, o);
+        d += __shfl_down_sync(0xffffffffu, d, o);
+        e += __shfl_down_sync(0xffffffffu, e, o);
+    }
+    if ((threadIdx.x & 31) == 0 && e) {
+        atomicAdd((unsigned long long *) &ctr->xdrop_cells, a);
+        atomicAdd((unsigned long long *) &ctr->edit_cells, b);
+        atomicAdd((unsigned long long *) &ctr->xdrop_calls, c);
+        atomicAdd((unsigned long long *) &ctr->edit_calls, d);
+        atomicAdd((unsigned long long *) &ctr->pairs, e);
+    }
+}
+
+__global__ void __launch_bounds__(128) k_process_pe(DevView v, BatchDev b, const cm_mread *__restrict__ in, cm_mread *__restrict__ out,
+                                                    int32_t *__restrict__ state, uint32_t n_pairs, cm_counters *__restrict__ ctr) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    AlignStats st = {0, 0, 0, 0};
+    if (i < n_pairs) {
+        cm_mread mr = in[i];
+        state[i] = cm_pair_process(v, b, i, mr, st);
+        out[i] = mr;
+    }
+    warp_add_stats(st, i < n_pairs ? 1u : 0u, ctr);
+}
+
+__global__ void __launch_bounds__(128) k_process_se(DevView v, BatchDev b, int32_t *__restrict__ state, uint32_t n_reads,
+                                                    cm_counters *__restrict__ ctr) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    AlignStats st = {0, 0, 0, 0};
+    if (i < n_reads) state[i] = cm_read_process_se(v, b, i, st);
+    warp_add_stats(st, i < n_reads ? 1u : 0u, ctr);
+}
+
+// stage-level parity entry: chains of the forward strand of each row, in the API layout [n][C][n_slots]
+__global__ void k_chain_export(DevView v, BatchDev b, uint32_t n_rows, int32_t *__restrict__ chain_count, int32_t *__restrict__ high_hits,
+                               float *__restrict__ score, uint32_t *__restrict__ chain_len, uint32_t *__restrict__ frag_rpos,
+                               int32_t *__restrict__ frag_qpos) {
+    uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= n_rows * (uint32_t) b.C) return;
+    uint32_t row = gid / b.C, k = gid % b.C, s = 2 * row;
+    const int FO = v.n_slots;
+    if (k == 0) {
+        chain_count[row] = b.chain_cnt[s];
+        high_hits[row] = b.chain_hh[s];
+    }
+    bool live = (int) k < b.chain_cnt[s];
+    score[gid] = live ? b.chain_score[(size_t) s * b.C + k] : 0.f;
+    uint32_t L = live ? b.chain_len[(size_t) s * b.C + k] : 0;
+    chain_len[gid] = L;
+    for (int f = 0; f < FO; f++) {
+        bool lf = (uint32_t) f < L && f < b.F;
+        const FragDev *fr = b.chain_frags + ((size_t) s * b.C + k) * b.F + f;
+        frag_rpos[(size_t) gid * FO + f] = lf ? fr->rpos : 0;
+        frag_qpos[(size_t) gid * FO + f] = lf ? fr->qpos : 0;
+    }
+}
+
+// alignment kinds of cm_gpu_align_batch, one thread per problem
+__global__ void k_align(cm_params p, int kind, uint32_t n, const uint8_t *__restrict__ s, const uint16_t *__restrict__ n_s,
+                        const uint8_t *__restrict__ t, const uint16_t *__restrict__ n_t, uint32_t stride, const int32_t *__restrict__ aux,
+                        int32_t *__restrict__ out_ed, int32_t *__restrict__ out_sclen, int32_t *__restrict__ out_indel,
+                        int32_t *__restrict__ out_score) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint8_t *si = s + (size_t) i * stride, *ti = t + (size_t) i * stride;
+    int ed = 0, sc = 0, indel = 0, score = 0;
+    if (kind == 0 || kind == 1) ed = cm_drop_alignment_sc(si, n_s[i], ti, n_t[i], kind == 1, p, sc, indel, score, nullptr);
+    else if (kind == 2 || kind == 3) ed = cm_local_alignment(si, n_s[i], ti, n_t[i], kind == 3, p, indel, score, nullptr);
+    else ed = cm_one_side_banded(si, n_s[i], ti, n_t[i], aux[i], nullptr);
+    out_ed[i] = ed; out_sclen[i] = sc; out_indel[i] = indel; out_score[i] = score;
+}

@@ -1,0 +1,144 @@
+"""TEST INFRASTRUCTURE ONLY.  Runs the UNMODIFIED reference (oracle/_ref/libcm_ref.so) over a synthetic
+workload, contig by contig as mapping() does, and dumps stage-level results to an .npz:
+seed lists, chains, process_read (PE, carried MatchedRead) and optionally SE states and alignment
+kernels on random problems.  One process per dump (the reference lives in process-global singletons).
+
+    python -m oracle.refdump --workload T0 --contig-size 250000 --out tests/golden/T0_k20.npz
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+import tempfile
+import zlib
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+
+
+def align_problems(seed: int, n: int, stride: int = 200):
+    """Random (s, t) problems for the five alignment kinds: t derived from s by a few edits, plus junk tails."""
+    rng = np.random.default_rng(seed)
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    out = {}
+    for kind in range(5):
+        s = np.zeros((n, stride), np.uint8)
+        t = np.zeros((n, stride), np.uint8)
+        ns = np.zeros(n, np.uint16)
+        nt = np.zeros(n, np.uint16)
+        aux = np.zeros(n, np.int32)
+        for i in range(n):
+            L = int(rng.integers(1, 120))
+            base = acgt[rng.integers(0, 4, size=L + 40)]
+            q = list(base[:L])
+            for _ in range(int(rng.integers(0, 5))):
+                p = int(rng.integers(0, max(1, len(q))))
+                r = rng.random()
+                if r < 0.5 and q:
+                    q[p] = int(acgt[rng.integers(0, 4)])
+                elif r < 0.75 and len(q) > 1:
+                    del q[p]
+                else:
+                    q.insert(p, int(acgt[rng.integers(0, 4)]))
+            if rng.random() < 0.3:          # diverging tail -> soft clip / x-drop
+                k = int(rng.integers(1, 12))
+                q = q[:max(1, len(q) - k)] + [int(x) for x in acgt[rng.integers(0, 4, size=k)]]
+            if rng.random() < 0.05:
+                q[int(rng.integers(0, len(q)))] = ord("N")
+            q = np.array(q[:stride - 8], np.uint8)
+            if kind in (0, 1):       # s = reference text (len + band), t = read piece
+                a, b = base[:min(L + 3, stride - 8)], q
+                if kind == 1:
+                    a, b = a[::-1], b[::-1]
+            elif kind in (2, 3):     # s = read piece (<= m + band), t = exon text
+                m = min(L, stride - 8)
+                b = base[:m]
+                a = np.concatenate([q, acgt[rng.integers(0, 4, size=8)]])[:m + 3]
+                if kind == 3:
+                    a, b = a[::-1], b[::-1]
+            else:                    # one-side banded: m = n + w
+                w = int(rng.integers(0, 4))
+                a = q
+                tail = acgt[rng.integers(0, 4, size=w + len(q))]
+                b = np.concatenate([base, tail])[:len(q) + w]
+                aux[i] = w
+            s[i, :len(a)] = a
+            t[i, :len(b)] = b
+            ns[i] = len(a)
+            nt[i] = len(b)
+        out[kind] = (s, ns, t, nt, aux)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="T0")
+    ap.add_argument("--contig-size", type=int, default=250_000)
+    ap.add_argument("--pairs", type=int, default=0)
+    ap.add_argument("--kmer", type=int, default=20)
+    ap.add_argument("--scan-level", type=int, default=0)
+    ap.add_argument("--max-ed", type=int, default=4)
+    ap.add_argument("--band", type=int, default=3)
+    ap.add_argument("--se", action="store_true")
+    ap.add_argument("--align", type=int, default=0, help="random alignment problems per kind")
+    ap.add_argument("--no-stage-dumps", action="store_true", help="only process_read results (large workloads)")
+    ap.add_argument("--out", required=True)
+    a = ap.parse_args()
+
+    from circminer_b200 import workload
+    from oracle.refharness import REF_BIN, RefHarness, default_params, fresh_mreads
+    import subprocess
+
+    tmp = tempfile.mkdtemp(prefix="cm_refdump_")
+    w = workload.prepare(a.workload, tmp, contig_size=a.contig_size, n_pairs=a.pairs or None)
+    p = default_params(kmer=a.kmer, scan_level=a.scan_level, max_ed=a.max_ed, band_width=a.band)
+    h = RefHarness(p)
+    if a.kmer != 20:
+        # the harness builds with checkSumLength from set_params (commandline_parser.cpp:247)
+        pass
+    h.build_index(w["fa"], contig_size=a.contig_size)
+    h.open(w["fa"], w["gtf"], os.path.join(tmp, "ref"))
+    s1, s2 = w["s1"], w["s2"]
+    n, L = s1.shape
+    lens = np.full(n, L, np.uint16)
+    out = dict(n_pairs=n, read_len=L, kmer=h.kmer, reads_crc=zlib.crc32(s1.tobytes() + s2.tobytes()),
+               chr_names=np.array(h.chr_names))
+    mr = fresh_mreads(n, a.max_ed)
+    more, rounds = 1, 0
+    while more:
+        more = h.next_contig()
+        c = h.contig
+        rounds += 1
+        if not a.no_stage_dumps:
+            for nm, s in (("r1", s1), ("r2", s2)):
+                sd = h.seed(s, lens)
+                for k, v in sd.items():
+                    out[f"c{c}_seed_{nm}_{k}"] = v
+                cd = h.chain(s, lens)
+                for k, v in cd.items():
+                    out[f"c{c}_chain_{nm}_{k}"] = v
+        if a.se:
+            out[f"c{c}_se_state"] = h.process_se(s1, lens)
+        mr, st = h.process_pe(s1, s2, lens, lens, mr)
+        out[f"c{c}_pe_mread"] = mr.copy()
+        out[f"c{c}_pe_state"] = st
+    out["n_contigs"] = rounds
+    if a.align:
+        probs = align_problems(77, a.align)
+        for kind, (s, ns, t, nt, aux) in probs.items():
+            r = h.align(kind, s, ns, t, nt, aux)
+            for k, v in r.items():
+                out[f"align{kind}_{k}"] = v
+    os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)
+    np.savez_compressed(a.out, **out)
+    print("wrote", a.out, "contigs", rounds, "pairs", n)
+    sys.stdout.flush()
+    os._exit(0)
+
+
+if __name__ == "__main__":
+    main()
