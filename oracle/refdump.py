@@ -114,6 +114,8 @@ def main():
         c = h.contig
         rounds += 1
         if not a.no_stage_dumps:
+            for k, v in h.annotation().items():     # the reference's own tables for this contig
+                out[f"c{c}_annot_{k}"] = v
             for nm, s in (("r1", s1), ("r2", s2)):
                 sd = h.seed(s, lens)
                 for k, v in sd.items():

@@ -86,6 +86,23 @@ int hs_load_contig(HsCtx *c, int contig_id, const void *const *bucket_lists, con
     return 0;
 }
 
+// index given directly as the SoA arrays (built by the caller from the contig text)
+int hs_set_index(HsCtx *c, int contig_id, const uint32_t *dir, const uint16_t *cks, const uint32_t *pos, uint64_t n_entries,
+                 const uint8_t *genome_ascii, uint32_t ref_len) {
+    if ((size_t) contig_id >= c->contigs.size()) c->contigs.resize(contig_id + 1, nullptr);
+    delete c->contigs[contig_id];
+    HsContig *h = new HsContig;
+    c->contigs[contig_id] = h;
+    h->dir.assign(dir, dir + (size_t) CM_NBUCKETS + 1);
+    h->cks.assign(cks, cks + n_entries);
+    h->pos.assign(pos, pos + n_entries);
+    h->genome.assign((size_t) ref_len + 64, 'N');
+    memcpy(h->genome.data() + 1, genome_ascii, ref_len);
+    h->d.dir = h->dir.data(); h->d.cks = h->cks.data(); h->d.pos = h->pos.data(); h->d.genome = h->genome.data();
+    h->d.n_entries = n_entries; h->d.ref_len = ref_len;
+    return 0;
+}
+
 // the arrays of `A` must outlive the context (the Python wrapper keeps them)
 int hs_load_annotation(HsCtx *c, int contig_id, const cm_annot_flat *A) {
     HsContig *h = c->contigs[contig_id];

@@ -38,6 +38,38 @@ class HostSim:
         self.lib.hs_load_contig(self.ctx, contig_id, C.c_void_p(bucket_lists), C.c_void_p(table_mem), _vp(g),
                                 C.c_uint32(len(g)))
 
+    def build_contig(self, contig_id, seq: np.ndarray):
+        """Index of one packed contig from its text, (bucket, checksum, position) order
+        (src/mrsfast/HashTable.c:769-839, Sort.c:110-176) -- numpy restatement for the CPU tests."""
+        g = np.ascontiguousarray(seq, np.uint8)
+        k = self.params.kmer
+        code = np.full(256, 4, np.int64)
+        for i, ch in enumerate(b"ACGT"):
+            code[ch] = i
+        v = code[g]
+        n = len(g) - k + 1
+        if n <= 0:
+            key = np.zeros(0, np.int64); pos = np.zeros(0, np.uint32)
+        else:
+            bad = np.concatenate([[0], np.cumsum(v == 4)])
+            ok = (bad[k:k + n] - bad[:n]) == 0
+            key = np.zeros(n, np.int64)
+            for j in range(k):
+                key = key * 4 + (v[j:j + n] & 3)
+            pos = np.nonzero(ok)[0]
+            key = key[pos]
+            order = np.argsort(key, kind="stable")
+            key = key[order]
+            pos = (pos[order] + 1).astype(np.uint32)
+        cs = 2 * (k - 14)
+        hv = key >> cs
+        cks = (key & ((1 << cs) - 1)).astype(np.uint16)
+        dirv = np.zeros(4 ** 14 + 1, np.uint32)
+        dirv[1:] = np.cumsum(np.bincount(hv, minlength=4 ** 14)).astype(np.uint32)
+        self._keep += [g]
+        self.lib.hs_set_index(self.ctx, contig_id, _vp(dirv), _vp(cks), _vp(np.ascontiguousarray(pos)), C.c_uint64(len(pos)),
+                              _vp(g), C.c_uint32(len(g)))
+
     def load_annotation(self, contig_id, a: dict):
         f = CmAnnotFlat()
         for k in ("n_iv", "n_seg", "n_tid", "n_trans", "n_genes", "n_chr", "n_bits"):

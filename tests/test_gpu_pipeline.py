@@ -1,0 +1,104 @@
+"""GPU parity through the C-ABI (libcm_gpu.so): chaining, alignment kernels, process_read PE/SE against
+the committed golden fixtures (T0) and against the reference itself run live on the box (T1)."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import has_ref
+from parity import GOLDEN, check_reads, compare_align, compare_contig, live_dump
+
+pytestmark = pytest.mark.gpu
+T0_CONTIG = 250_000
+
+
+@pytest.fixture(scope="module")
+def w_t0(tmp_path_factory):
+    from circminer_b200 import workload
+    return workload.prepare("T0", str(tmp_path_factory.mktemp("t0w")), contig_size=T0_CONTIG)
+
+
+def _mapper(w, **params):
+    from circminer_b200 import workload
+    from circminer_b200.api import Mapper, default_params
+    m = Mapper(default_params(**params))
+    workload.load_into(m, w)
+    return m
+
+
+def test_t0_golden_k20(w_t0):
+    from circminer_b200.api import fresh_mreads
+    gold = np.load(os.path.join(GOLDEN, "T0_k20.npz"))
+    check_reads(w_t0, gold)
+    m = _mapper(w_t0)
+    mr = fresh_mreads(len(w_t0["s1"]))
+    for c in range(int(gold["n_contigs"])):
+        mr = compare_contig(m, c, w_t0, gold, mr, se=True)
+    compare_align(m, gold, 400)
+    cnt = m.counters()
+    assert cnt["kernel_launches"] > 0 and cnt["xdrop_cells"] > 0 and cnt["chain_links"] > 0
+    m.close()
+
+
+def test_t0_golden_k22_scan2(w_t0):
+    from circminer_b200.api import fresh_mreads
+    gold = np.load(os.path.join(GOLDEN, "T0_k22_scan2.npz"))
+    m = _mapper(w_t0, kmer=22, scan_level=2)
+    mr = fresh_mreads(len(w_t0["s1"]))
+    for c in range(int(gold["n_contigs"])):
+        mr = compare_contig(m, c, w_t0, gold, mr)
+    m.close()
+
+
+def test_chain_overflow_path_is_exact(w_t0, monkeypatch):
+    """Force every multi-hit strand through k_chain_big (record arena slice of 8) and compare again."""
+    from circminer_b200.api import fresh_mreads
+    monkeypatch.setenv("CM_GPU_REC_MULT", "0")
+    gold = np.load(os.path.join(GOLDEN, "T0_k20.npz"))
+    m = _mapper(w_t0)
+    mr = fresh_mreads(len(w_t0["s1"]))
+    for c in range(int(gold["n_contigs"])):
+        mr = compare_contig(m, c, w_t0, gold, mr, stages=("chain", "pe"))
+    m.close()
+
+
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_t1_live_reference(tmp_path):
+    """20 000 pairs 2x150 over two packed contigs, the reference run on this box as the checker."""
+    from circminer_b200 import workload
+    from circminer_b200.api import fresh_mreads
+    dump = live_dump(str(tmp_path / "t1.npz"), workload="T1", contig_size=3_500_000, no_stage_dumps=True)
+    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000)
+    check_reads(w, dump)
+    m = _mapper(w)
+    mr = fresh_mreads(len(w["s1"]))
+    for c in range(int(dump["n_contigs"])):
+        mr = compare_contig(m, c, w, dump, mr, stages=("pe",))
+    types = np.bincount(mr["type"], minlength=14)
+    assert types[0] > 10000 and types[3] > 100      # concordant and back-splice classes both populated
+    m.close()
+
+
+def test_ragged_and_degenerate_reads(w_t0):
+    """Ragged lengths, reads shorter than k, N / lower-case bases: states must equal the all-contig golden
+    run restricted to untouched rows, and nothing may fault."""
+    from circminer_b200.api import fresh_mreads
+    m = _mapper(w_t0)
+    s1, s2 = w_t0["s1"][:64].copy(), w_t0["s2"][:64].copy()
+    l1 = np.full(64, s1.shape[1], np.uint16)
+    l2 = l1.copy()
+    l1[0] = 19
+    l2[1] = 1
+    l1[2] = 57
+    s1[3, :] = ord("N")
+    s2[4, 10:30] = np.frombuffer(bytes(s2[4, 10:30]).lower(), np.uint8)
+    out, st = m.process_read(0, s1, s2, fresh_mreads(64), l1, l2)
+    gold = np.load(os.path.join(GOLDEN, "T0_k20.npz"))
+    keep = np.ones(64, bool)
+    keep[:5] = False
+    assert (st[keep] == gold["c0_pe_state"][:64][keep]).all()
+    assert st[3] in (10, 13)          # one mate all-N: OEANCH or NOPROC_NOMATCH
+    # empty batch
+    out, st = m.process_read(0, s1[:0], s2[:0], fresh_mreads(0))
+    assert len(st) == 0
+    m.close()
