@@ -49,7 +49,8 @@ struct cm_gpu_ctx {
     bool staged_pe = false;
     DevBuf in_seq1, in_seq2, in_len1, in_len2, in_mread;  // raw uploads
     DevBuf strands, strand_len;                           // [n_strands][stride] fwd/rc rows, lengths
-    DevBuf seed_off, seed_cnt;                            // [n_strands][n_slots]
+    DevBuf seed_key;                                      // [n_strands][batch_F] (hv, cv) of every seed slot
+    DevBuf seed_off, seed_cnt;                            // [n_strands][batch_F]
     DevBuf cell_cnt, cell_off;                            // dp cells per strand, exclusive prefix (u64)
     DevBuf dp_score, dp_prev, recs;                       // chaining arenas
     DevBuf ovf_strand, ovf_nrec, ovf_n, ovf_off, ovf_recs;  // strands whose record list outgrew its slice
@@ -59,6 +60,7 @@ struct cm_gpu_ctx {
     uint32_t last_overflow = 0;
     DevBuf out_mread, out_state;
     DevBuf cub_tmp;
+    DevBuf key32[2], key64[2], perm[2];                   // work-signature sort of strands / pairs
     DevBuf scratch[8];
 };
 
@@ -171,12 +173,13 @@ extern "C" int cm_gpu_destroy(cm_gpu_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     for (auto &c : ctx->contigs) free_contig(c);
     DevBuf *bufs[] = {&ctx->in_seq1, &ctx->in_seq2, &ctx->in_len1, &ctx->in_len2, &ctx->in_mread, &ctx->strands,
-                      &ctx->strand_len, &ctx->seed_off, &ctx->seed_cnt, &ctx->cell_cnt, &ctx->cell_off,
+                      &ctx->strand_len, &ctx->seed_key, &ctx->seed_off, &ctx->seed_cnt, &ctx->cell_cnt, &ctx->cell_off,
                       &ctx->dp_score, &ctx->dp_prev, &ctx->recs, &ctx->ovf_strand, &ctx->ovf_nrec, &ctx->ovf_n, &ctx->ovf_off,
                       &ctx->ovf_recs, &ctx->chain_cnt, &ctx->chain_hh, &ctx->chain_score, &ctx->chain_len,
                       &ctx->chain_frags, &ctx->out_mread, &ctx->out_state, &ctx->cub_tmp};
     for (DevBuf *b : bufs) release(*b);
     for (auto &b : ctx->scratch) release(b);
+    for (int q = 0; q < 2; q++) { release(ctx->key32[q]); release(ctx->key64[q]); release(ctx->perm[q]); }
     cudaFree(ctx->d_counters);
     for (auto &ev : ctx->ev) cudaEventDestroy(ev);
     cudaStreamDestroy(ctx->stream);
@@ -511,26 +514,47 @@ extern "C" int cm_gpu_load_annotation(cm_gpu_ctx *ctx, int contig_id, const cm_a
 // ------------------------------------------------------------------------------------------
 // strand rows: PE pair i -> strands 4i (R1 fwd), 4i+1 (R1 rc), 4i+2 (R2 fwd), 4i+3 (R2 rc)
 //              SE read i -> strands 2i (fwd), 2i+1 (rc)
+// One warp per input read.  Besides the two ASCII rows it emits the (hv, cv) pair of every seed slot
+// (hashVal / checkSumVal, lib/mrsfast/Common.c:199-225) so that the gather kernel never touches read
+// bytes: hv = -1 / cv = -1 on a non-ACGT base, hv = -2 when the slot holds no seed (q + k > len).
 __global__ void k_make_strands(const char *__restrict__ s1, const char *__restrict__ s2, const uint16_t *__restrict__ l1,
                                const uint16_t *__restrict__ l2, uint32_t n, uint32_t in_stride, uint32_t stride,
-                               uint8_t *__restrict__ strands, uint16_t *__restrict__ slen) {
-    // one warp per input read
+                               uint8_t *__restrict__ strands, uint16_t *__restrict__ slen, int kmer, int F,
+                               int2 *__restrict__ seed_key) {
     uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     uint32_t n_reads = s2 ? 2 * n : n;
     if (warp >= n_reads) return;
     uint32_t i = s2 ? warp >> 1 : warp;
     bool second = s2 && (warp & 1);
-    const char *src = (second ? s2 : s1) + (size_t) i * in_stride;
+    const uint8_t *src = (const uint8_t *) (second ? s2 : s1) + (size_t) i * in_stride;
     uint32_t len = second ? l2[i] : l1[i];
     uint8_t *fw = strands + (size_t) (2 * warp) * stride;
     uint8_t *rc = fw + stride;
     for (uint32_t j = lane; j < stride; j += 32) {
-        fw[j] = j < len ? (uint8_t) src[j] : 0;
-        rc[j] = j < len ? cm_comp((uint8_t) src[len - 1 - j]) : 0;
+        fw[j] = j < len ? src[j] : 0;
+        rc[j] = j < len ? cm_comp(src[len - 1 - j]) : 0;
     }
     if (lane == 0) {
         slen[2 * warp] = (uint16_t) len;
         slen[2 * warp + 1] = (uint16_t) len;
+    }
+    for (int idx = (int) lane; idx < 2 * F; idx += 32) {
+        int str = idx / F, t = idx - str * F;
+        int q = t * kmer;
+        int hv = -2, cv = 0;
+        if (q + kmer <= (int) len) {
+            hv = 0;
+            bool bad_h = false, bad_c = false;
+            for (int x = 0; x < kmer; x++) {
+                uint8_t c = str ? cm_comp(src[len - 1 - (q + x)]) : src[q + x];
+                int v = cm_nhval(c);
+                if (x < CM_WINDOW) { if (v < 0) bad_h = true; hv = (hv << 2) | (v & 3); }
+                else { if (v < 0) bad_c = true; cv = (cv << 2) | (v & 3); }
+            }
+            if (bad_h) hv = -1;
+            if (bad_c) cv = -1;
+        }
+        seed_key[((size_t) 2 * warp + str) * F + t] = make_int2(hv, cv);
     }
 }
 
@@ -577,37 +601,33 @@ static int stage_reads(cm_gpu_ctx *ctx, uint32_t n, const char *s1, const char *
 static int launch_prep(cm_gpu_ctx *ctx, uint32_t in_stride) {
     if (!ctx->n_pairs) return CM_OK;
     uint32_t n_reads = ctx->staged_pe ? 2 * ctx->n_pairs : ctx->n_pairs;
+    ENSURE(ctx, ctx->seed_key, (size_t) ctx->n_strands * ctx->batch_F * sizeof(int2));
     k_make_strands<<<grid_for((size_t) n_reads * 32, 256), 256, 0, ctx->stream>>>(
         (const char *) ctx->in_seq1.p, ctx->staged_pe ? (const char *) ctx->in_seq2.p : nullptr,
         (const uint16_t *) ctx->in_len1.p, (const uint16_t *) ctx->in_len2.p, ctx->n_pairs, in_stride, ctx->stride,
-        (uint8_t *) ctx->strands.p, (uint16_t *) ctx->strand_len.p);
+        (uint8_t *) ctx->strands.p, (uint16_t *) ctx->strand_len.p, ctx->p.kmer, ctx->batch_F, (int2 *) ctx->seed_key.p);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     return CM_OK;
 }
 
 // ------------------------------------------------------------------------------------------
-// K1: seed lookup.  One thread per (strand, seed slot).  The dependent gather chain is
-// directory (8 B) -> checksum run (2 B each, binary search); positions are NOT copied:
-// chaining reads them in place through (off, cnt).
+// K1: seed lookup.  One thread per (strand, seed slot): 8 coalesced bytes of key in, then the dependent
+// random gathers directory (dir[hv], dir[hv+1]) -> checksum run (binary search).  Positions are NOT
+// copied: chaining reads them in place through (off, cnt).
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_seed(DevView v, const uint8_t *__restrict__ strands, const uint16_t *__restrict__ slen,
-                                              uint32_t n_strands, uint32_t stride, uint32_t *__restrict__ seed_off,
-                                              uint32_t *__restrict__ seed_cnt, cm_counters *__restrict__ ctr) {
-    const int ns = v.n_slots;
+__global__ void __launch_bounds__(256) k_seed(DevView v, const int2 *__restrict__ seed_key, uint64_t total,
+                                              uint32_t *__restrict__ seed_off, uint32_t *__restrict__ seed_cnt,
+                                              cm_counters *__restrict__ ctr) {
     uint64_t gid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t strand = (uint32_t) (gid / ns), slot = (uint32_t) (gid % ns);
     uint32_t sectors = 0, hits = 0, looked = 0;
-    if (strand < n_strands) {
-        int len = slen[strand];
-        int q = (int) slot * v.p.kmer;
+    if (gid < total) {
+        int2 key = seed_key[gid];
         SeedHit h;
         h.off = 0;
         h.cnt = 0;
-        if (q + v.p.kmer <= len) {
-            int hv, cv;
-            cm_hash_kmer(strands + (size_t) strand * stride + q, v.p.kmer, hv, cv);
-            h = cm_seed_lookup(v.c, hv, cv, &sectors);
+        if (key.x != -2) {
+            h = cm_seed_lookup(v.c, key.x, key.y, &sectors);
             looked = 1;
             uint32_t kept = h.cnt > (uint32_t) v.p.seed_lim ? 0 : h.cnt;
             hits = kept;
@@ -638,18 +658,17 @@ static int make_view(cm_gpu_ctx *ctx, int contig_id, bool need_annot, DevView &v
     v.a = ch->has_annot ? ch->a : AnnotDev();
     v.contig_id = contig_id;
     v.max_seg_cnt = ctx->max_seg_cnt;
-    v.n_slots = ctx->n_slots;
+    v.n_slots = ctx->batch_F;   // seed / chain arrays of the staged batch use the batch's own slot count
     return CM_OK;
 }
 
 static int launch_seed(cm_gpu_ctx *ctx, const DevView &v) {
     if (!ctx->n_strands) return CM_OK;
-    size_t total = (size_t) ctx->n_strands * ctx->n_slots;
+    size_t total = (size_t) ctx->n_strands * ctx->batch_F;
     ENSURE(ctx, ctx->seed_off, total * 4);
     ENSURE(ctx, ctx->seed_cnt, total * 4);
-    k_seed<<<grid_for(total, 256), 256, 0, ctx->stream>>>(v, (const uint8_t *) ctx->strands.p, (const uint16_t *) ctx->strand_len.p,
-                                                         ctx->n_strands, ctx->stride, (uint32_t *) ctx->seed_off.p,
-                                                         (uint32_t *) ctx->seed_cnt.p, ctx->d_counters);
+    k_seed<<<grid_for(total, 256), 256, 0, ctx->stream>>>(v, (const int2 *) ctx->seed_key.p, (uint64_t) total,
+                                                         (uint32_t *) ctx->seed_off.p, (uint32_t *) ctx->seed_cnt.p, ctx->d_counters);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     return CM_OK;
@@ -671,7 +690,7 @@ __global__ void k_seed_summary(DevView v, const uint16_t *__restrict__ slen, uin
     if ((s & 1) == 0) {
         uint32_t slot = s >> 1;
         int len = slen[strand];
-        if ((int) (slot * v.p.kmer + v.p.kmer) <= len) {
+        if ((int) slot < v.n_slots && (int) (slot * v.p.kmer + v.p.kmer) <= len) {
             q = (int32_t) (slot * v.p.kmer);
             uint32_t cnt = seed_cnt[(size_t) strand * v.n_slots + slot], off = seed_off[(size_t) strand * v.n_slots + slot];
             hf = cnt > 0;
@@ -709,6 +728,7 @@ extern "C" int cm_gpu_seed_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, con
     if (n == 0) return CM_OK;
     // each input row is ONE strand here: stage as SE and keep only the forward rows
     if ((r = stage_reads(ctx, n, seqs, nullptr, stride, len, nullptr, nullptr)) != CM_OK) return r;
+    if ((r = make_view(ctx, contig_id, false, v)) != CM_OK) return r;
     if ((r = launch_prep(ctx, stride)) != CM_OK) return r;
     if ((r = launch_seed(ctx, v)) != CM_OK) return r;
     size_t total = (size_t) ctx->n_strands * ctx->max_seg_cnt;

@@ -4,8 +4,8 @@
 static int make_batch(cm_gpu_ctx *ctx, BatchDev &b) {
     const size_t ns = ctx->n_strands;
     const int C = ctx->p.max_chain_len, F = ctx->batch_F;
-    ENSURE(ctx, ctx->seed_off, ns * ctx->n_slots * 4);
-    ENSURE(ctx, ctx->seed_cnt, ns * ctx->n_slots * 4);
+    ENSURE(ctx, ctx->seed_off, ns * F * 4);
+    ENSURE(ctx, ctx->seed_cnt, ns * F * 4);
     ENSURE(ctx, ctx->chain_cnt, ns * 4);
     ENSURE(ctx, ctx->chain_hh, ns * 4);
     ENSURE(ctx, ctx->chain_score, ns * C * 4);
@@ -55,10 +55,25 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) {
     ENSURE(ctx, ctx->ovf_nrec, (size_t) ns * 4);
     ENSURE(ctx, ctx->ovf_n, 8);
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->ovf_n.p, 0, 8, st));
+    // strands in work-signature order
+    ENSURE(ctx, ctx->key32[0], (size_t) ns * 4);
+    ENSURE(ctx, ctx->key32[1], (size_t) ns * 4);
+    ENSURE(ctx, ctx->perm[0], (size_t) ns * 4);
+    ENSURE(ctx, ctx->perm[1], (size_t) ns * 4);
+    k_strand_key<<<grid_for(ns, 256), 256, 0, st>>>(v, b.seed_cnt, ns, (uint32_t *) ctx->key32[0].p, (uint32_t *) ctx->perm[0].p);
+    {
+        size_t tb2 = 0;
+        cub::DeviceRadixSort::SortPairs(nullptr, tb2, (const uint32_t *) ctx->key32[0].p, (uint32_t *) ctx->key32[1].p,
+                                        (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) ns, 0, 32, st);
+        ENSURE(ctx, ctx->cub_tmp, tb2 + 16);
+        cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tb2, (const uint32_t *) ctx->key32[0].p, (uint32_t *) ctx->key32[1].p,
+                                        (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) ns, 0, 32, st);
+    }
+    ctx->launches += 2;
     k_chain<<<grid_for(ns, 128), 128, 0, st>>>(v, b, (const uint64_t *) ctx->cell_off.p, (double *) ctx->dp_score.p,
                                                (uint32_t *) ctx->dp_prev.p, (ChainRec *) ctx->recs.p, mult,
                                                (uint32_t *) ctx->ovf_strand.p, (uint32_t *) ctx->ovf_nrec.p, (uint32_t *) ctx->ovf_n.p,
-                                               ctx->d_counters);
+                                               (const uint32_t *) ctx->perm[1].p, ctx->d_counters);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     uint32_t n_ovf = 0;
@@ -91,8 +106,21 @@ static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) 
     ENSURE(ctx, ctx->out_state, (size_t) n * 4);
     if (ctx->staged_pe) {
         ENSURE(ctx, ctx->out_mread, (size_t) n * sizeof(cm_mread));
-        k_process_pe<<<grid_for(n, 128), 128, 0, ctx->stream>>>(v, b, (const cm_mread *) ctx->in_mread.p, (cm_mread *) ctx->out_mread.p,
-                                                               (int32_t *) ctx->out_state.p, n, ctx->d_counters);
+        ENSURE(ctx, ctx->key64[0], (size_t) n * 8);
+        ENSURE(ctx, ctx->key64[1], (size_t) n * 8);
+        ENSURE(ctx, ctx->perm[0], (size_t) n * 4);
+        ENSURE(ctx, ctx->perm[1], (size_t) n * 4);
+        cudaStream_t st = ctx->stream;
+        k_pair_key<<<grid_for(n, 256), 256, 0, st>>>(v, b, n, (unsigned long long *) ctx->key64[0].p, (uint32_t *) ctx->perm[0].p);
+        size_t tb = 0;
+        cub::DeviceRadixSort::SortPairs(nullptr, tb, (const unsigned long long *) ctx->key64[0].p, (unsigned long long *) ctx->key64[1].p,
+                                        (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, 43, st);
+        ENSURE(ctx, ctx->cub_tmp, tb + 16);
+        cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tb, (const unsigned long long *) ctx->key64[0].p, (unsigned long long *) ctx->key64[1].p,
+                                        (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, 43, st);
+        ctx->launches += 2;
+        k_process_pe<<<grid_for(n, 128), 128, 0, st>>>(v, b, (const cm_mread *) ctx->in_mread.p, (cm_mread *) ctx->out_mread.p,
+                                                      (int32_t *) ctx->out_state.p, n, (const uint32_t *) ctx->perm[1].p, ctx->d_counters);
     } else {
         k_process_se<<<grid_for(n, 128), 128, 0, ctx->stream>>>(v, b, (int32_t *) ctx->out_state.p, n, ctx->d_counters);
     }
@@ -138,6 +166,7 @@ extern "C" int cm_gpu_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, co
     if (n == 0) return CM_OK;
     // each input row is one strand: stage as SE reads, export the forward rows
     if ((r = stage_reads(ctx, n, seqs, nullptr, stride, len, nullptr, nullptr)) != CM_OK) return r;
+    if ((r = make_view(ctx, contig_id, true, v)) != CM_OK) return r;
     if ((r = launch_prep(ctx, stride)) != CM_OK) return r;
     if ((r = run_pipeline(ctx, contig_id, 2)) != CM_OK) return r;
     BatchDev b;
@@ -149,7 +178,7 @@ extern "C" int cm_gpu_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, co
     ENSURE(ctx, ctx->scratch[3], rows * C * 4);
     ENSURE(ctx, ctx->scratch[4], rows * C * FO * 4);
     ENSURE(ctx, ctx->scratch[5], rows * C * FO * 4);
-    k_chain_export<<<grid_for(rows * C, 256), 256, 0, ctx->stream>>>(v, b, n, (int32_t *) ctx->scratch[0].p, (int32_t *) ctx->scratch[1].p,
+    k_chain_export<<<grid_for(rows * C, 256), 256, 0, ctx->stream>>>(v, b, n, (int) FO, (int32_t *) ctx->scratch[0].p, (int32_t *) ctx->scratch[1].p,
                                                                     (float *) ctx->scratch[2].p, (uint32_t *) ctx->scratch[3].p,
                                                                     (uint32_t *) ctx->scratch[4].p, (int32_t *) ctx->scratch[5].p);
     ctx->launches++;

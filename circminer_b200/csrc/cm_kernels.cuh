@@ -25,10 +25,12 @@ CM_HD uint32_t cm_rec_cap(uint32_t cells, uint32_t mult) { return mult * cells +
 __global__ void __launch_bounds__(128) k_chain(DevView v, BatchDev b, const uint64_t *__restrict__ cell_off, double *__restrict__ dp_score,
                                                uint32_t *__restrict__ dp_prev, ChainRec *__restrict__ recs, uint32_t rec_mult,
                                                uint32_t *__restrict__ ovf_strand, uint32_t *__restrict__ ovf_nrec,
-                                               uint32_t *__restrict__ n_ovf, cm_counters *__restrict__ ctr) {
-    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+                                               uint32_t *__restrict__ n_ovf, const uint32_t *__restrict__ order,
+                                               cm_counters *__restrict__ ctr) {
+    uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     uint64_t links = 0;
-    if (s < b.n_strands) {
+    if (slot < b.n_strands) {
+        const uint32_t s = order[slot];   // strands with the same row shape sit in the same warp
         const uint32_t *so = b.seed_off + (size_t) s * v.n_slots, *sc = b.seed_cnt + (size_t) s * v.n_slots;
         uint32_t row_pos_off[CM_MAX_SEEDS], row_cnt[CM_MAX_SEEDS], row_off[CM_MAX_SEEDS], cells;
         int hh;
@@ -105,15 +107,18 @@ __device__ __forceinline__ void warp_add_stats(const AlignStats &st, uint32_t pa
 }
 
 __global__ void __launch_bounds__(128) k_process_pe(DevView v, BatchDev b, const cm_mread *__restrict__ in, cm_mread *__restrict__ out,
-                                                    int32_t *__restrict__ state, uint32_t n_pairs, cm_counters *__restrict__ ctr) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+                                                    int32_t *__restrict__ state, uint32_t n_pairs, const uint32_t *__restrict__ order,
+                                                    cm_counters *__restrict__ ctr) {
+    uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     AlignStats st = {0, 0, 0, 0};
-    if (i < n_pairs) {
+    const bool live = slot < n_pairs;
+    if (live) {
+        const uint32_t i = order[slot];   // pairs with the same control-flow signature sit in the same warp
         cm_mread mr = in[i];
         state[i] = cm_pair_process(v, b, i, mr, st);
         out[i] = mr;
     }
-    warp_add_stats(st, i < n_pairs ? 1u : 0u, ctr);
+    warp_add_stats(st, live ? 1u : 0u, ctr);
 }
 
 __global__ void __launch_bounds__(128) k_process_se(DevView v, BatchDev b, int32_t *__restrict__ state, uint32_t n_reads,
@@ -125,13 +130,12 @@ __global__ void __launch_bounds__(128) k_process_se(DevView v, BatchDev b, int32
 }
 
 // stage-level parity entry: chains of the forward strand of each row, in the API layout [n][C][n_slots]
-__global__ void k_chain_export(DevView v, BatchDev b, uint32_t n_rows, int32_t *__restrict__ chain_count, int32_t *__restrict__ high_hits,
+__global__ void k_chain_export(DevView v, BatchDev b, uint32_t n_rows, int FO, int32_t *__restrict__ chain_count, int32_t *__restrict__ high_hits,
                                float *__restrict__ score, uint32_t *__restrict__ chain_len, uint32_t *__restrict__ frag_rpos,
                                int32_t *__restrict__ frag_qpos) {
     uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
     if (gid >= n_rows * (uint32_t) b.C) return;
     uint32_t row = gid / b.C, k = gid % b.C, s = 2 * row;
-    const int FO = v.n_slots;
     if (k == 0) {
         chain_count[row] = b.chain_cnt[s];
         high_hits[row] = b.chain_hh[s];
@@ -161,4 +165,58 @@ __global__ void k_align(cm_params p, int kind, uint32_t n, const uint8_t *__rest
     else if (kind == 2 || kind == 3) ed = cm_local_alignment(si, n_s[i], ti, n_t[i], kind == 3, p, indel, score, nullptr);
     else ed = cm_one_side_banded(si, n_s[i], ti, n_t[i], aux[i], nullptr);
     out_ed[i] = ed; out_sclen[i] = sc; out_indel[i] = indel; out_score[i] = score;
+}
+
+// ------------------------------------------------------------------------------------------
+// Work signatures.  Thread-per-unit kernels diverge on data-dependent control flow; sorting the units
+// by a cheap signature first puts units that take the same path into the same warp.  Results do not
+// depend on the order (every unit writes its own slots).
+// ------------------------------------------------------------------------------------------
+// strand: heavy first (inverted cell count), then the mask of non-empty rows
+__global__ void k_strand_key(DevView v, const uint32_t *__restrict__ seed_cnt, uint32_t n_strands, uint32_t *__restrict__ key,
+                             uint32_t *__restrict__ idx) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_strands) return;
+    uint32_t cells = 0, mask = 0;
+    for (int t = 0; t < v.n_slots; t++) {
+        uint32_t raw = seed_cnt[(size_t) s * v.n_slots + t];
+        uint32_t kept = raw > (uint32_t) v.p.seed_lim ? 0 : raw;
+        cells += kept;
+        if (kept) mask |= 1u << t;
+    }
+    uint32_t cq = cells > 255 ? 255 : cells;
+    key[s] = ((255u - cq) << 24) | (mask & 0xFFFFFFu);
+    idx[s] = s;
+}
+
+// pair: chain counts of the four strands, attempt order, and the shape of the leading chains
+__global__ void k_pair_key(DevView v, BatchDev b, uint32_t n_pairs, unsigned long long *__restrict__ key, uint32_t *__restrict__ idx) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pairs) return;
+    unsigned long long k = 0;
+    int cnt[4];
+    float sc[4];
+    for (int q = 0; q < 4; q++) {
+        cnt[q] = b.chain_cnt[4 * i + q];
+        sc[q] = cnt[q] > 0 ? b.chain_score[(size_t) (4 * i + q) * b.C] : 0.f;
+        int c = cnt[q] > 7 ? 7 : cnt[q];
+        k = (k << 3) | (unsigned) c;
+    }
+    bool first = __fadd_rn(sc[0], sc[3]) >= __fadd_rn(sc[2], sc[1]);
+    k = (k << 1) | (first ? 1u : 0u);
+    // the two strands of the first attempt: (R1 fwd, R2 rc) or (R2 fwd, R1 rc)
+    int sa = first ? 0 : 2, sb = first ? 3 : 1;
+    for (int q = 0; q < 2; q++) {
+        uint32_t s = 4 * i + (q ? sb : sa);
+        unsigned sig = 0;
+        if (b.chain_cnt[s] > 0) {
+            uint32_t L = b.chain_len[(size_t) s * b.C];
+            const FragDev *fr = b.chain_frags + (size_t) s * b.C * b.F;
+            unsigned q0 = (unsigned) (fr[0].qpos / v.p.kmer) & 31u, q1 = (unsigned) (fr[L - 1].qpos / v.p.kmer) & 31u;
+            sig = (q0 << 10) | (q1 << 5) | (L & 31u);
+        }
+        k = (k << 15) | sig;
+    }
+    key[i] = k;
+    idx[i] = i;
 }

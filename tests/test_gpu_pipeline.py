@@ -74,6 +74,7 @@ def test_t1_live_reference(tmp_path):
     mr = fresh_mreads(len(w["s1"]))
     for c in range(int(dump["n_contigs"])):
         mr = compare_contig(m, c, w, dump, mr, stages=("pe",))
+    assert m.counters()["pairs"] == len(w["s1"]) * int(dump["n_contigs"])
     types = np.bincount(mr["type"], minlength=14)
     assert types[0] > 10000 and types[3] > 100      # concordant and back-splice classes both populated
     m.close()
