@@ -235,9 +235,23 @@ CM_HDN void cm_xdrop(const uint8_t *s, int n, const uint8_t *t, int m, bool rev,
     score = cur_optimum;
 }
 
+// A result computed ahead of time by the dense alignment kernel for exactly this problem (same text
+// pointers, lengths and direction): a pure memo, consulted before running the DP inline.
+struct DropHint {
+    const uint8_t *s, *t;
+    int n, m, rev, valid;
+    int ed, sclen, indel, score;
+};
+
 // DropAlignment::local_alignment_right_sc (rev = false) / _left_sc (rev = true: both strings reversed)
 CM_HDN int cm_drop_alignment_sc(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &sc_len,
-                                int &indel, int &score, AlignStats *st) {
+                                int &indel, int &score, AlignStats *st, const DropHint *h = nullptr) {
+    if (h && h->valid && h->s == s && h->t == t && h->n == n && h->m == m && h->rev == (int) rev) {
+        sc_len = h->sclen;
+        indel = h->indel;
+        score = h->score;
+        return h->ed;
+    }
     int on_s, on_t;
     cm_xdrop(s, n, t, m, rev, p, on_s, on_t, score, st);
     int mx = on_s > on_t ? on_s : on_t;

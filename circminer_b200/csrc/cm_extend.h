@@ -74,10 +74,22 @@ CM_HD void mate_init(MateD &m, const cm_params &p) {   // MatchedMate::MatchedMa
     m.exons_spos = m.exons_epos = -1;
 }
 
+// Per-chain results of the dense pre-alignment kernel (k_chain_spec): the middle edit distance of
+// calc_middle_ed(ch, maxEd) and the genome-text X-drop alignment of the two read ends.
+struct EndRes {
+    int32_t ed, sclen, indel, score;
+};
+struct ChainAux {
+    int32_t mid_ed;
+    uint8_t has_mid, has_l, has_r, pad_;
+    EndRes l, r;
+};
+
 // chain view used by the extension: fragment len is always kmer
 struct ChainView {
     const FragDev *frags;
     uint32_t chain_len;
+    const ChainAux *aux;   // nullable
 };
 
 // common_tid of a MatePair: tids of interval iv_a that also occur in interval iv_b (iv_a < 0: empty)
@@ -105,15 +117,50 @@ CM_HD void memo_insert(AlignMemo &m, uint32_t rs, uint32_t rl, uint32_t qs, uint
     e.rspos = rs; e.rlen = rl; e.qspos = qs; e.qlen = ql; e.res = r;
 }
 
-struct ExtCtx {
-    const DevView *v;
-    AlignStats st;
-};
-
 // GenomeSeeder::pac2char: text of [start, start+len-1] (1-based) or NULL when out of range
 CM_HD const uint8_t *cm_pac2char(const DevView &v, uint32_t start, int len) {
     if ((int) start < 0 || (int) start + len - 1 > (int) v.c.ref_len) return nullptr;
     return v.c.genome + start;
+}
+
+struct ExtCtx {
+    const DevView *v;
+    AlignStats st;
+    DropHint hint;   // valid only while the end of a chain with ChainAux is being extended
+};
+
+// The genome-text alignment problem of one chain end as extend_left / extend_right pose it in their
+// "intron retention" step (src/extend.cpp:336, :411) -- and, when the exon reaches far enough, in the
+// transcript walk too.  false when there is nothing to extend or the text is out of range.
+CM_HD bool cm_end_problem(const DevView &v, const ChainView &ch, const uint8_t *seq, int seq_len, bool right, const uint8_t *&s,
+                          int &n, const uint8_t *&t, int &m) {
+    const int k = v.p.kmer, w = v.p.band_width;
+    if (ch.chain_len == 0) return false;
+    if (right) {
+        const FragDev &fl = ch.frags[ch.chain_len - 1];
+        m = seq_len - (fl.qpos + k);
+        if (m <= 0) return false;
+        n = m + w;
+        t = seq + seq_len - m;
+        s = cm_pac2char(v, fl.rpos + (uint32_t) k, n);
+    } else {
+        m = ch.frags[0].qpos;
+        if (m <= 0) return false;
+        n = m + w;
+        t = seq;
+        s = cm_pac2char(v, ch.frags[0].rpos - (uint32_t) n, n);
+    }
+    return s != nullptr;
+}
+
+CM_HD void cm_set_hint(ExtCtx &x, const ChainView &ch, const uint8_t *seq, int seq_len, bool right) {
+    x.hint.valid = 0;
+    if (!ch.aux || !(right ? ch.aux->has_r : ch.aux->has_l)) return;
+    if (!cm_end_problem(*x.v, ch, seq, seq_len, right, x.hint.s, x.hint.n, x.hint.t, x.hint.m)) return;
+    const EndRes &r = right ? ch.aux->r : ch.aux->l;
+    x.hint.rev = right ? 0 : 1;
+    x.hint.ed = r.ed; x.hint.sclen = r.sclen; x.hint.indel = r.indel; x.hint.score = r.score;
+    x.hint.valid = 1;
 }
 
 // get_location_overlap_ind: find_ind + "seg_list.size() == 0 -> NULL" (src/gene_annotation.cpp:555-568)
@@ -176,6 +223,7 @@ CM_HDN int cm_calc_middle_ed(ExtCtx &x, const ChainView &ch, int edth, const uin
     const cm_params &p = x.v->p;
     int mid_err = 0;
     if (ch.chain_len == 0) return 0;
+    if (ch.aux && ch.aux->has_mid && edth == p.max_ed) return ch.aux->mid_ed;
     for (uint32_t i = 0; i + 1 < ch.chain_len; i++) {
         if (ch.frags[i + 1].qpos > ch.frags[i].qpos + p.kmer) {
             int diff = (int) (ch.frags[i + 1].rpos - ch.frags[i].rpos) - (ch.frags[i + 1].qpos - ch.frags[i].qpos);
@@ -224,7 +272,7 @@ CM_HDN void cm_extend_right_end(ExtCtx &x, uint32_t pos, uint32_t ref_len, const
     const uint8_t *ref = cm_pac2char(*x.v, pos + 1, (int) ref_len);
     if (!ref) return;
     int sclen, indel, score;
-    int edit_dist = cm_drop_alignment_sc(ref, (int) ref_len, qseq, qseq_len, false, p, sclen, indel, score, &x.st);
+    int edit_dist = cm_drop_alignment_sc(ref, (int) ref_len, qseq, qseq_len, false, p, sclen, indel, score, &x.st, &x.hint);
     uint32_t new_rmpos = pos + (uint32_t) qseq_len - (uint32_t) indel;
     ar_set(exon_res, new_rmpos, edit_dist, sclen, indel, qseq_len, score);
     int actual_mapped_bp = qseq_len - sclen;
@@ -364,7 +412,7 @@ CM_HDN bool cm_extend_right(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &
     const uint8_t *ref;
     if (!consecutive && (ref = cm_pac2char(*x.v, orig_pos + 1, ref_len)) != nullptr) {
         int score;
-        min_ed = cm_drop_alignment_sc(ref, ref_len, seq, seq_len, false, p, sclen_best, indel, score, &x.st);
+        min_ed = cm_drop_alignment_sc(ref, ref_len, seq, seq_len, false, p, sclen_best, indel, score, &x.st, &x.hint);
         if (min_ed <= ed_th && sclen_best <= p.max_sc) {
             ar_set(curr, orig_pos + (uint32_t) seq_len - (uint32_t) indel, min_ed, sclen_best, indel, seq_len, score);
             if (ar_update_by_score(best, curr, true)) {
@@ -413,7 +461,7 @@ CM_HDN void cm_extend_left_end(ExtCtx &x, uint32_t pos, uint32_t ref_len, const 
     const uint8_t *ref = cm_pac2char(*x.v, pos - ref_len, (int) ref_len);
     if (!ref) return;
     int sclen, indel, score;
-    int edit_dist = cm_drop_alignment_sc(ref, (int) ref_len, qseq, qseq_len, true, p, sclen, indel, score, &x.st);
+    int edit_dist = cm_drop_alignment_sc(ref, (int) ref_len, qseq, qseq_len, true, p, sclen, indel, score, &x.st, &x.hint);
     uint32_t new_lmpos = pos - (uint32_t) qseq_len + (uint32_t) indel;
     ar_set(exon_res, new_lmpos, edit_dist, sclen, indel, qseq_len, score);
     int actual_mapped_bp = qseq_len - sclen;
@@ -538,7 +586,7 @@ CM_HDN bool cm_extend_left(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &p
     const uint8_t *ref;
     if (!consecutive && (ref = cm_pac2char(*x.v, orig_pos - (uint32_t) ref_len, ref_len)) != nullptr) {
         int score;
-        min_ed = cm_drop_alignment_sc(ref, ref_len, seq, seq_len, true, p, sclen_best, indel, score, &x.st);
+        min_ed = cm_drop_alignment_sc(ref, ref_len, seq, seq_len, true, p, sclen_best, indel, score, &x.st, &x.hint);
         if (min_ed <= ed_th && sclen_best <= p.max_sc) {
             ar_set(curr, orig_pos - (uint32_t) seq_len + (uint32_t) indel, min_ed, sclen_best, indel, seq_len, score);
             if (ar_update_by_score(best, curr, false)) {
@@ -569,7 +617,11 @@ CM_HDN bool cm_extend_chain_right(ExtCtx &x, TidSet ts, const ChainView &ch, con
     int remain_end = seq_len - (fl.qpos + p.kmer);
     bool right_ok = (remain_end <= 0);
     AlignResD best = ar_init(ub);
-    if (remain_end > 0) right_ok = cm_extend_right(x, ts, seq + seq_len - remain_end, rm_pos, remain_end, p.max_ed - err, ub, best);
+    if (remain_end > 0) {
+        cm_set_hint(x, ch, seq, seq_len, true);
+        right_ok = cm_extend_right(x, ts, seq + seq_len - remain_end, rm_pos, remain_end, p.max_ed - err, ub, best);
+        x.hint.valid = 0;
+    }
     int sclen_right = best.sclen;
     int err_right = best.ed;
     remain_end -= best.qcovlen;
@@ -590,7 +642,11 @@ CM_HDN bool cm_extend_chain_left(ExtCtx &x, TidSet ts, const ChainView &ch, cons
     int remain_beg = ch.frags[0].qpos - qspos;
     bool left_ok = (remain_beg <= 0);
     AlignResD best = ar_init(lb);
-    if (remain_beg > 0) left_ok = cm_extend_left(x, ts, seq, lm_pos, remain_beg, p.max_ed - err, lb, best);
+    if (remain_beg > 0) {
+        if (qspos == 0) cm_set_hint(x, ch, seq, 0, false);
+        left_ok = cm_extend_left(x, ts, seq, lm_pos, remain_beg, p.max_ed - err, lb, best);
+        x.hint.valid = 0;
+    }
     int sclen_left = best.sclen;
     int err_left = best.ed;
     remain_beg -= best.qcovlen;
@@ -661,7 +717,11 @@ CM_HDN int cm_extend_chain_both_sides(ExtCtx &x, const ChainView &ch, const uint
     int remain_beg = ch.frags[0].qpos;
     bool left_ok = (remain_beg <= 0);
     AlignResD best_left = ar_init(CM_MINLB);
-    if (remain_beg > 0) left_ok = cm_extend_left(x, empty, seq, lm_pos, remain_beg, p.max_ed - mr.middle_ed, CM_MINLB, best_left);
+    if (remain_beg > 0) {
+        cm_set_hint(x, ch, seq, seq_len, false);
+        left_ok = cm_extend_left(x, empty, seq, lm_pos, remain_beg, p.max_ed - mr.middle_ed, CM_MINLB, best_left);
+        x.hint.valid = 0;
+    }
     int err_left = best_left.ed;
     int sclen_left = best_left.sclen;
     remain_beg -= best_left.qcovlen;
@@ -670,9 +730,12 @@ CM_HDN int cm_extend_chain_both_sides(ExtCtx &x, const ChainView &ch, const uint
     int remain_end = seq_len - (fl.qpos + p.kmer);
     bool right_ok = (remain_end <= 0);
     AlignResD best = ar_init(CM_MAXUB);
-    if (remain_end > 0)
+    if (remain_end > 0) {
+        cm_set_hint(x, ch, seq, seq_len, true);
         right_ok = cm_extend_right(x, empty, seq + seq_len - remain_end, rm_pos, remain_end, p.max_ed - mr.middle_ed - err_left,
                                    CM_MAXUB, best);
+        x.hint.valid = 0;
+    }
     int err_right = best.ed;
     int sclen_right = best.sclen;
     remain_end -= best.qcovlen;
@@ -695,4 +758,30 @@ CM_HDN int cm_extend_chain_both_sides(ExtCtx &x, const ChainView &ch, const uint
         mr.type = CM_ORPHAN;
     }
     return mr.type;
+}
+
+
+// ---- dense pre-alignment -------------------------------------------------------------------
+// kind 0: calc_middle_ed(ch, maxEd); kind 1 / 2: the genome-text X-drop of the left / right read end.
+// Each kind writes its own fields of ChainAux, so the three may run in different threads.
+CM_HDN void cm_chain_spec(ExtCtx &x, const ChainView &ch, const uint8_t *seq, int seq_len, int kind, ChainAux &aux) {
+    const cm_params &p = x.v->p;
+    if (kind == 0) {
+        ChainView c = ch;
+        c.aux = nullptr;
+        aux.mid_ed = cm_calc_middle_ed(x, c, p.max_ed, seq, seq_len);
+        aux.has_mid = 1;
+        return;
+    }
+    const bool right = kind == 2;
+    const uint8_t *s, *t;
+    int n, m;
+    EndRes r;
+    r.ed = r.sclen = r.indel = r.score = 0;
+    uint8_t has = 0;
+    if (cm_end_problem(*x.v, ch, seq, seq_len, right, s, n, t, m)) {
+        r.ed = cm_drop_alignment_sc(s, n, t, m, !right, p, r.sclen, r.indel, r.score, &x.st, nullptr);
+        has = 1;
+    }
+    if (right) { aux.r = r; aux.has_r = has; } else { aux.l = r; aux.has_l = has; }
 }

@@ -15,11 +15,13 @@ struct ChainListView {
     const uint32_t *len;       // [C]
     const FragDev *frags;      // [C][F]
     int F;
+    const ChainAux *aux;       // [count] or nullptr
 };
 CM_HD ChainView cl_chain(const ChainListView &l, int i) {
     ChainView c;
     c.frags = l.frags + (size_t) i * l.F;
     c.chain_len = l.len[i];
+    c.aux = l.aux ? l.aux + i : nullptr;
     return c;
 }
 

@@ -60,6 +60,9 @@ struct cm_gpu_ctx {
     uint32_t last_overflow = 0;
     DevBuf out_mread, out_state;
     DevBuf cub_tmp;
+    DevBuf chain_base, chain_ids, chain_aux;              // compact chain list + pre-alignment results
+    uint32_t last_chains = 0;
+    bool no_spec = false;      // CM_GPU_NO_SPEC=1: every DP inline in the per-pair kernel (debug / A-B)
     DevBuf key32[2], key64[2], perm[2];                   // work-signature sort of strands / pairs
     DevBuf scratch[8];
 };
@@ -157,6 +160,7 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
     }
     cudaMemset(ctx->d_counters, 0, sizeof(cm_counters));
     if (const char *e = getenv("CM_GPU_REC_MULT")) ctx->rec_mult = (uint32_t) atoi(e);
+    if (const char *e = getenv("CM_GPU_NO_SPEC")) ctx->no_spec = atoi(e) != 0;
     *out = ctx;
     return CM_OK;
 }
@@ -179,6 +183,7 @@ extern "C" int cm_gpu_destroy(cm_gpu_ctx *ctx) {
                       &ctx->chain_frags, &ctx->out_mread, &ctx->out_state, &ctx->cub_tmp};
     for (DevBuf *b : bufs) release(*b);
     for (auto &b : ctx->scratch) release(b);
+    release(ctx->chain_base); release(ctx->chain_ids); release(ctx->chain_aux);
     for (int q = 0; q < 2; q++) { release(ctx->key32[q]); release(ctx->key64[q]); release(ctx->perm[q]); }
     cudaFree(ctx->d_counters);
     for (auto &ev : ctx->ev) cudaEventDestroy(ev);

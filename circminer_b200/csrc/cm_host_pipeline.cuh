@@ -24,10 +24,12 @@ static int make_batch(cm_gpu_ctx *ctx, BatchDev &b) {
     b.chain_score = (float *) ctx->chain_score.p;
     b.chain_len = (uint32_t *) ctx->chain_len.p;
     b.chain_frags = (FragDev *) ctx->chain_frags.p;
+    b.chain_base = nullptr;
+    b.aux = nullptr;
     return CM_OK;
 }
 
-static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) {
+static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
     if (!ctx->n_strands) return CM_OK;
     cudaStream_t st = ctx->stream;
     const uint32_t ns = ctx->n_strands;
@@ -96,6 +98,32 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) {
         ctx->launches++;
         CUDA_TRY(ctx, cudaGetLastError());
         CUDA_TRY(ctx, cudaStreamSynchronize(st));   // off[] is host memory
+    }
+    // dense pre-alignment of every chain (memo for the per-pair kernel)
+    ENSURE(ctx, ctx->chain_base, ((size_t) ns + 1) * 4);
+    {
+        size_t tb3 = 0;
+        cub::DeviceScan::ExclusiveSum(nullptr, tb3, (const int32_t *) ctx->chain_cnt.p, (uint32_t *) ctx->chain_base.p, (int) ns, st);
+        ENSURE(ctx, ctx->cub_tmp, tb3 + 16);
+        cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tb3, (const int32_t *) ctx->chain_cnt.p, (uint32_t *) ctx->chain_base.p, (int) ns, st);
+        ctx->launches++;
+    }
+    uint32_t last_base = 0;
+    int32_t last_n = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&last_base, (uint32_t *) ctx->chain_base.p + (ns - 1), 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&last_n, (int32_t *) ctx->chain_cnt.p + (ns - 1), 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const uint32_t n_chains = last_base + (uint32_t) last_n;
+    ctx->last_chains = n_chains;
+    b.chain_base = (const uint32_t *) ctx->chain_base.p;
+    if (n_chains && !ctx->no_spec) {
+        ENSURE(ctx, ctx->chain_ids, (size_t) n_chains * 4);
+        ENSURE(ctx, ctx->chain_aux, (size_t) n_chains * sizeof(ChainAux));
+        b.aux = (ChainAux *) ctx->chain_aux.p;
+        k_chain_list<<<grid_for(ns, 256), 256, 0, st>>>(b, (uint32_t *) ctx->chain_ids.p);
+        k_chain_spec<<<grid_for(3ull * n_chains, 128), 128, 0, st>>>(v, b, (const uint32_t *) ctx->chain_ids.p, n_chains, ctx->d_counters);
+        ctx->launches += 2;
+        CUDA_TRY(ctx, cudaGetLastError());
     }
     return CM_OK;
 }

@@ -88,27 +88,38 @@ __global__ void __launch_bounds__(128) k_chain_big(DevView v, BatchDev b, const 
 // ------------------------------------------------------------------------------------------
 // K3: extension + classification, one thread per pair (PE) / read (SE)
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void warp_add_stats(const AlignStats &st, uint32_t pairs, cm_counters *ctr) {
-    unsigned long long a = st.xdrop_cells, b = st.edit_cells, c = st.xdrop_calls, d = st.edit_calls, e = pairs;
-    for (int o = 16; o; o >>= 1) {
-        a += __shfl_down_sync(0xffffffffu, a, o);
-        b += __shfl_down_sync(0xffffffffu, b, o);
-        c += __shfl_down_sync(0xffffffffu, c, o);
-        d += __shfl_down_sync(0xffffffffu, d, o);
-        e += __shfl_down_sync(0xffffffffu, e, o);
-    }
-    if ((threadIdx.x & 31) == 0 && e) {
-        atomicAdd((unsigned long long *) &ctr->xdrop_cells, a);
-        atomicAdd((unsigned long long *) &ctr->edit_cells, b);
-        atomicAdd((unsigned long long *) &ctr->xdrop_calls, c);
-        atomicAdd((unsigned long long *) &ctr->edit_calls, d);
-        atomicAdd((unsigned long long *) &ctr->pairs, e);
+// Block-level accumulation of the work counters.  Shared-memory atomics instead of warp shuffles: the
+// threads of a warp leave the per-pair code at unrelated points, and a full-mask shuffle after that much
+// divergence lost contributions on sm_100a.
+struct BlockStats {
+    unsigned long long v[5];
+};
+__device__ __forceinline__ void block_stats_init(BlockStats &sh) {
+    if (threadIdx.x < 5) sh.v[threadIdx.x] = 0;
+    __syncthreads();
+}
+__device__ __forceinline__ void block_stats_add(BlockStats &sh, const AlignStats &st, uint32_t units, cm_counters *ctr) {
+    if (st.xdrop_cells) atomicAdd(&sh.v[0], (unsigned long long) st.xdrop_cells);
+    if (st.edit_cells) atomicAdd(&sh.v[1], (unsigned long long) st.edit_cells);
+    if (st.xdrop_calls) atomicAdd(&sh.v[2], (unsigned long long) st.xdrop_calls);
+    if (st.edit_calls) atomicAdd(&sh.v[3], (unsigned long long) st.edit_calls);
+    if (units) atomicAdd(&sh.v[4], (unsigned long long) units);
+    __syncthreads();
+    if (threadIdx.x < 5 && sh.v[threadIdx.x]) {
+        unsigned long long *dst = threadIdx.x == 0 ? (unsigned long long *) &ctr->xdrop_cells
+                                  : threadIdx.x == 1 ? (unsigned long long *) &ctr->edit_cells
+                                  : threadIdx.x == 2 ? (unsigned long long *) &ctr->xdrop_calls
+                                  : threadIdx.x == 3 ? (unsigned long long *) &ctr->edit_calls
+                                                     : (unsigned long long *) &ctr->pairs;
+        atomicAdd(dst, sh.v[threadIdx.x]);
     }
 }
 
 __global__ void __launch_bounds__(128) k_process_pe(DevView v, BatchDev b, const cm_mread *__restrict__ in, cm_mread *__restrict__ out,
                                                     int32_t *__restrict__ state, uint32_t n_pairs, const uint32_t *__restrict__ order,
                                                     cm_counters *__restrict__ ctr) {
+    __shared__ BlockStats sh;
+    block_stats_init(sh);
     uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     AlignStats st = {0, 0, 0, 0};
     const bool live = slot < n_pairs;
@@ -118,15 +129,17 @@ __global__ void __launch_bounds__(128) k_process_pe(DevView v, BatchDev b, const
         state[i] = cm_pair_process(v, b, i, mr, st);
         out[i] = mr;
     }
-    warp_add_stats(st, live ? 1u : 0u, ctr);
+    block_stats_add(sh, st, live ? 1u : 0u, ctr);
 }
 
 __global__ void __launch_bounds__(128) k_process_se(DevView v, BatchDev b, int32_t *__restrict__ state, uint32_t n_reads,
                                                     cm_counters *__restrict__ ctr) {
+    __shared__ BlockStats sh;
+    block_stats_init(sh);
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     AlignStats st = {0, 0, 0, 0};
     if (i < n_reads) state[i] = cm_read_process_se(v, b, i, st);
-    warp_add_stats(st, i < n_reads ? 1u : 0u, ctr);
+    block_stats_add(sh, st, i < n_reads ? 1u : 0u, ctr);
 }
 
 // stage-level parity entry: chains of the forward strand of each row, in the API layout [n][C][n_slots]
@@ -219,4 +232,40 @@ __global__ void k_pair_key(DevView v, BatchDev b, uint32_t n_pairs, unsigned lon
     }
     key[i] = k;
     idx[i] = i;
+}
+
+// ------------------------------------------------------------------------------------------
+// K2c: dense pre-alignment.  The per-pair code is control-flow heavy and its threads diverge; the DP
+// work it would do is mostly determined by the chains alone (gap edit distances, genome-text X-drop of
+// the two read ends), so it is done here first, one thread per (chain, kind) with all lanes of a warp
+// on the same kind, and handed to k_process_* as a memo (ChainAux / DropHint).
+// ------------------------------------------------------------------------------------------
+__global__ void k_chain_list(BatchDev b, uint32_t *__restrict__ list) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= b.n_strands) return;
+    uint32_t base = b.chain_base[s];
+    int n = b.chain_cnt[s];
+    for (int c = 0; c < n; c++) list[base + c] = (s << 5) | (uint32_t) c;
+}
+
+__global__ void __launch_bounds__(128) k_chain_spec(DevView v, BatchDev b, const uint32_t *__restrict__ list, uint32_t n_chains,
+                                                    cm_counters *__restrict__ ctr) {
+    __shared__ BlockStats sh;
+    block_stats_init(sh);
+    uint64_t gid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    ExtCtx x;
+    x.v = &v;
+    x.st.xdrop_cells = x.st.edit_cells = x.st.xdrop_calls = x.st.edit_calls = 0;
+    x.hint.valid = 0;
+    if (gid < 3ull * n_chains) {
+        int kind = (int) (gid / n_chains);
+        uint32_t id = (uint32_t) (gid - (uint64_t) kind * n_chains);
+        uint32_t e = list[id], s = e >> 5, c = e & 31u;
+        ChainView ch;
+        ch.frags = b.chain_frags + ((size_t) s * b.C + c) * b.F;
+        ch.chain_len = b.chain_len[(size_t) s * b.C + c];
+        ch.aux = nullptr;
+        cm_chain_spec(x, ch, b.strands + (size_t) s * b.stride, b.strand_len[s], kind, b.aux[id]);
+    }
+    block_stats_add(sh, x.st, 0u, ctr);
 }

@@ -25,6 +25,8 @@ struct BatchDev {
     float *chain_score;          // [n_strands][C]
     uint32_t *chain_len;         // [n_strands][C]
     FragDev *chain_frags;        // [n_strands][C][F]
+    const uint32_t *chain_base;  // [n_strands + 1] exclusive prefix of chain_cnt (nullptr: no pre-alignment)
+    ChainAux *aux;               // [total chains]
 };
 
 // GenomeSeeder::split_match_hash for one strand (src/match_read.cpp:270-286): fills n_slots (off, cnt)
@@ -51,6 +53,7 @@ CM_HD ChainListView cm_chain_list(const BatchDev &b, uint32_t strand) {
     l.len = b.chain_len + (size_t) strand * b.C;
     l.frags = b.chain_frags + (size_t) strand * b.C * b.F;
     l.F = b.F;
+    l.aux = (b.aux && b.chain_base) ? b.aux + b.chain_base[strand] : nullptr;
     return l;
 }
 
@@ -67,6 +70,7 @@ CM_HD int cm_pair_process(const DevView &v, const BatchDev &b, uint32_t pair, cm
     FilterCtx f;
     f.x.v = &v;
     f.x.st.xdrop_cells = f.x.st.edit_cells = f.x.st.xdrop_calls = f.x.st.edit_calls = 0;
+    f.x.hint.valid = 0;
     f.contig_id = v.contig_id;
     PairView pv;
     for (int k = 0; k < 4; k++) {
@@ -83,6 +87,7 @@ CM_HD int cm_read_process_se(const DevView &v, const BatchDev &b, uint32_t read,
     FilterCtx f;
     f.x.v = &v;
     f.x.st.xdrop_cells = f.x.st.edit_cells = f.x.st.xdrop_calls = f.x.st.edit_calls = 0;
+    f.x.hint.valid = 0;
     f.contig_id = v.contig_id;
     StrandView fw = cm_strand_view(b, 2 * read), bw = cm_strand_view(b, 2 * read + 1);
     int r = cm_process_read_se(f, fw, bw);

@@ -138,6 +138,8 @@ struct HsBatch {
     std::vector<int32_t> chain_cnt, chain_hh;
     std::vector<float> chain_score;
     std::vector<FragDev> chain_frags;
+    std::vector<uint32_t> chain_base;
+    std::vector<ChainAux> aux;
     BatchDev b{};
 };
 
@@ -195,6 +197,28 @@ static void build_batch(HsCtx *c, const DevView &v, HsBatch &B, uint32_t n_reads
         out.frags = &B.chain_frags[(size_t) s * C * F];
         out.F = F;
         cm_chain_backtrack(v, T, row_pos_off, row_cnt, row_off, dps.data(), dpp.data(), recs.data(), nrec, out);
+    }
+    // dense pre-alignment of every chain (k_chain_spec on the device); HS_NO_SPEC=1 keeps every DP inline
+    b.chain_base = nullptr;
+    b.aux = nullptr;
+    if (!getenv("HS_NO_SPEC")) {
+        B.chain_base.assign(ns + 1, 0);
+        for (uint32_t s = 0; s < ns; s++) B.chain_base[s + 1] = B.chain_base[s] + (uint32_t) B.chain_cnt[s];
+        B.aux.assign(B.chain_base[ns] + 1, ChainAux{});
+        ExtCtx x;
+        x.v = &v;
+        x.st = AlignStats{0, 0, 0, 0};
+        x.hint.valid = 0;
+        for (uint32_t s = 0; s < ns; s++) {
+            ChainListView l = cm_chain_list(b, s);
+            for (int k = 0; k < l.count; k++) {
+                ChainView ch = cl_chain(l, k);
+                for (int kind = 0; kind < 3; kind++)
+                    cm_chain_spec(x, ch, b.strands + (size_t) s * stride, B.slen[s], kind, B.aux[B.chain_base[s] + k]);
+            }
+        }
+        b.chain_base = B.chain_base.data();
+        b.aux = B.aux.data();
     }
 }
 

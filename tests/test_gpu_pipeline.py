@@ -62,6 +62,18 @@ def test_chain_overflow_path_is_exact(w_t0, monkeypatch):
     m.close()
 
 
+def test_inline_dp_path_is_exact(w_t0, monkeypatch):
+    """CM_GPU_NO_SPEC=1: no pre-alignment memo, every DP runs inline in the per-pair kernel."""
+    from circminer_b200.api import fresh_mreads
+    monkeypatch.setenv("CM_GPU_NO_SPEC", "1")
+    gold = np.load(os.path.join(GOLDEN, "T0_k20.npz"))
+    m = _mapper(w_t0)
+    mr = fresh_mreads(len(w_t0["s1"]))
+    for c in range(int(gold["n_contigs"])):
+        mr = compare_contig(m, c, w_t0, gold, mr, stages=("pe",), se=True)
+    m.close()
+
+
 @pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
 def test_t1_live_reference(tmp_path):
     """20 000 pairs 2x150 over two packed contigs, the reference run on this box as the checker."""
