@@ -14,6 +14,15 @@
 #include "cm_types.h"
 
 #define CM_BANDSZ (2 * CM_MAX_BAND + 3)
+// debug switches (CM_GPU_DBG on the device build): bit 0 generic X-drop, bit 1 ignore hints, bit 2 no counters
+#if defined(__CUDACC__)
+__device__ int g_cm_dbg_flags = 0;
+#endif
+#if defined(__CUDA_ARCH__)
+#define CM_DBG_FLAGS g_cm_dbg_flags
+#else
+#define CM_DBG_FLAGS 0
+#endif
 #define CM_FULLDP_MAX 64   // largest s-length the full-DP fallback accepts (reference needs <= 2w)
 
 // score_ch / diff_ch: equal iff both in "ACGTacgt" and equal ignoring case; N never matches
@@ -175,8 +184,8 @@ CM_HDN int cm_one_side_banded(const uint8_t *s, int n, const uint8_t *t, int m, 
 // k = i + j; slot d = i - j + w + 1 in [1, 2w+1]; slots 0 and 2w+2 are the -DPTINF guard lines
 // dpx[x][x+w+1] / dpx[x+w+1][x].  Returns the last cell (in (k, i) visit order) holding the running
 // maximum, and that maximum (== dpx[on_s][on_t], which is never pruned).
-CM_HDN void cm_xdrop(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &on_s, int &on_t,
-                     int &score, AlignStats *st) {
+CM_HDN void cm_xdrop_generic(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &on_s, int &on_t,
+                             int &score, AlignStats *st) {
     const int w = p.band_width, B = 2 * w + 3;
     const int ind = p.ind_sc, NEG = -CM_DPTINF;
     if (st) st->xdrop_calls++;
@@ -235,6 +244,87 @@ CM_HDN void cm_xdrop(const uint8_t *s, int n, const uint8_t *t, int m, bool rev,
     score = cur_optimum;
 }
 
+// Register-resident form for a compile-time band W.  Cell (i, j) lives in slot e = i - j + W + 1 of ONE
+// array: slots whose parity matches anti-diagonal k hold diagonal k, the others diagonal k-1, so the
+// update X[e] = max(X[e] + sc, X[e-1] + ind, X[e+1] + ind) is in place (X[e] still holds diagonal k-2)
+// and every index is a compile-time constant after unrolling.  Same visit order, same lb/ub evolution,
+// same pruning as cm_xdrop_generic, hence the same (on_s, on_t, score).
+template <int W, int PAR>
+CM_HD void cm_xdrop_step(int (&X)[2 * W + 3], int k, int lb, int ub, const uint8_t *s, int n, const uint8_t *t, int m, bool rev,
+                         int mat, int mis, int ind, int xd, int pre, int &cur, int &best_i, int &best_j, int &new_ub, uint32_t &cells) {
+    const int NEG = -CM_DPTINF;
+#pragma unroll
+    for (int e = 1; e <= 2 * W + 1; e++) {
+        if ((e & 1) != PAR) continue;
+        const int d = e - W - 1;
+        const int i = (k + d) >> 1, j = k - i;
+        int v;
+        if (i >= lb && i <= ub) {
+            int sc = cm_base_eq(cm_at(s, n, i - 1, rev), cm_at(t, m, j - 1, rev)) ? mat : mis;
+            v = X[e] + sc;
+            int a = X[e - 1] + ind, b = X[e + 1] + ind;
+            v = v > a ? v : a;
+            v = v > b ? v : b;
+            cells++;
+            if (v >= cur) { cur = v; best_i = i; best_j = j; }
+            if (v + xd < pre) v = NEG;
+            if (v > NEG) new_ub = i;
+        } else {
+            v = (k <= W && (d == k || d == -k)) ? k * ind : NEG;
+        }
+        X[e] = v;
+    }
+}
+
+template <int W>
+CM_HD void cm_xdrop_reg(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &on_s, int &on_t,
+                        int &score, AlignStats *st) {
+    const int ind = p.ind_sc, NEG = -CM_DPTINF, mat = p.mat_sc, mis = p.mis_sc, xd = p.xdrop;
+    if (st) st->xdrop_calls++;
+    on_s = 0;
+    on_t = 0;
+    score = 0;
+    if (m <= 0 || n <= 0) return;
+    int X[2 * W + 3];
+#pragma unroll
+    for (int e = 0; e < 2 * W + 3; e++) X[e] = NEG;
+    X[W + 1] = 0;                                  // dpx[0][0]  (anti-diagonal 0)
+    if (W >= 1) { X[W + 2] = ind; X[W] = ind; }    // dpx[1][0], dpx[0][1]  (anti-diagonal 1)
+    int pre = 0, cur = 0, lb = 1, ub = 1, pre_ub = 0, best_i = 0, best_j = 0;
+    uint32_t cells = 0;
+    constexpr int P_EVEN = (W + 1) & 1;            // slot parity of even anti-diagonals
+    for (int k = 2; k <= m + n; ++k) {
+        int new_ub = -1;
+        if (k & 1) cm_xdrop_step<W, P_EVEN ^ 1>(X, k, lb, ub, s, n, t, m, rev, mat, mis, ind, xd, pre, cur, best_i, best_j, new_ub, cells);
+        else cm_xdrop_step<W, P_EVEN>(X, k, lb, ub, s, n, t, m, rev, mat, mis, ind, xd, pre, cur, best_i, best_j, new_ub, cells);
+        int lb_t = k - lb;
+        if (lb_t == m || (k > W && ((k - W) % 2 == 0))) ++lb;
+        if (ub < n && (k <= W || (k > W && ((k - W) % 2 == 1)))) ++ub;
+        if ((pre_ub == -1 && new_ub == -1) || lb > ub) break;
+        pre_ub = new_ub;
+        if (cur > pre) pre = cur;
+    }
+    if (st) st->xdrop_cells += cells;
+    on_s = best_i;
+    on_t = best_j;
+    score = cur;
+}
+
+CM_HDN void cm_xdrop(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &on_s, int &on_t, int &score,
+                     AlignStats *st) {
+#ifdef CM_XDROP_CHECK
+    if (p.band_width == 3) {
+        int a, b, c;
+        cm_xdrop_generic(s, n, t, m, rev, p, a, b, c, nullptr);
+        cm_xdrop_reg<3>(s, n, t, m, rev, p, on_s, on_t, score, st);
+        if (a != on_s || b != on_t || c != score) __builtin_trap();
+        return;
+    }
+#endif
+    if (p.band_width == 3 && !(CM_DBG_FLAGS & 1)) cm_xdrop_reg<3>(s, n, t, m, rev, p, on_s, on_t, score, st);
+    else cm_xdrop_generic(s, n, t, m, rev, p, on_s, on_t, score, st);
+}
+
 // A result computed ahead of time by the dense alignment kernel for exactly this problem (same text
 // pointers, lengths and direction): a pure memo, consulted before running the DP inline.
 struct DropHint {
@@ -246,7 +336,7 @@ struct DropHint {
 // DropAlignment::local_alignment_right_sc (rev = false) / _left_sc (rev = true: both strings reversed)
 CM_HDN int cm_drop_alignment_sc(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &sc_len,
                                 int &indel, int &score, AlignStats *st, const DropHint *h = nullptr) {
-    if (h && h->valid && h->s == s && h->t == t && h->n == n && h->m == m && h->rev == (int) rev) {
+    if (h && !(CM_DBG_FLAGS & 2) && h->valid && h->s == s && h->t == t && h->n == n && h->m == m && h->rev == (int) rev) {
         sc_len = h->sclen;
         indel = h->indel;
         score = h->score;

@@ -62,6 +62,7 @@ struct cm_gpu_ctx {
     DevBuf cub_tmp;
     DevBuf chain_base, chain_ids, chain_aux;              // compact chain list + pre-alignment results
     uint32_t last_chains = 0;
+    bool sync_each = false;    // CM_GPU_SYNC_EACH=1: synchronise after every launch and name the kernel that failed
     bool no_spec = false;      // CM_GPU_NO_SPEC=1: every DP inline in the per-pair kernel (debug / A-B)
     DevBuf key32[2], key64[2], perm[2];                   // work-signature sort of strands / pairs
     DevBuf scratch[8];
@@ -109,7 +110,22 @@ static void release(DevBuf &b) {
     b.cap = 0;
 }
 
+static int dbg_sync(cm_gpu_ctx *ctx, const char *what);
+#define DBG_SYNC(ctx, what)                                  \
+    do {                                                     \
+        int r_ = dbg_sync(ctx, what);                        \
+        if (r_ != CM_OK) return r_;                          \
+    } while (0)
+
 static inline unsigned grid_for(size_t n, unsigned block) { return (unsigned) ((n + block - 1) / block); }
+
+static int dbg_sync(cm_gpu_ctx *ctx, const char *what) {
+    if (!ctx->sync_each) return CM_OK;
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(ctx, CM_ERR_CUDA, "after %s: %s", what, cudaGetErrorString(e));
+    return CM_OK;
+}
 
 extern "C" void cm_params_default(cm_params *p) {
     p->kmer = 20; p->max_read_len = 300; p->max_ed = 4; p->max_sc = 7; p->band_width = 3; p->seed_lim = 500;
@@ -158,9 +174,15 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
         delete ctx;
         return fail(nullptr, CM_ERR_ALLOC, "cudaMalloc counters");
     }
-    cudaMemset(ctx->d_counters, 0, sizeof(cm_counters));
+    cudaMemsetAsync(ctx->d_counters, 0, sizeof(cm_counters), ctx->stream);
+    cudaStreamSynchronize(ctx->stream);
     if (const char *e = getenv("CM_GPU_REC_MULT")) ctx->rec_mult = (uint32_t) atoi(e);
     if (const char *e = getenv("CM_GPU_NO_SPEC")) ctx->no_spec = atoi(e) != 0;
+    if (const char *e = getenv("CM_GPU_SYNC_EACH")) ctx->sync_each = atoi(e) != 0;
+    if (const char *e = getenv("CM_GPU_DBG")) {
+        int f = atoi(e);
+        cudaMemcpyToSymbol(g_cm_dbg_flags, &f, sizeof f);
+    }
     *out = ctx;
     return CM_OK;
 }
@@ -199,7 +221,9 @@ extern "C" int cm_gpu_get_counters(cm_gpu_ctx *ctx, cm_counters *out, int reset)
     CUDA_TRY(ctx, cudaMemcpy(out, ctx->d_counters, sizeof *out, cudaMemcpyDeviceToHost));
     out->kernel_launches = ctx->launches;
     if (reset) {
-        CUDA_TRY(ctx, cudaMemset(ctx->d_counters, 0, sizeof(cm_counters)));
+        // on the context's own (non-blocking) stream: a legacy-stream memset is not ordered against later launches
+        CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(cm_counters), ctx->stream));
+        CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
         ctx->launches = 0;
     }
     return CM_OK;
@@ -613,6 +637,7 @@ static int launch_prep(cm_gpu_ctx *ctx, uint32_t in_stride) {
         (uint8_t *) ctx->strands.p, (uint16_t *) ctx->strand_len.p, ctx->p.kmer, ctx->batch_F, (int2 *) ctx->seed_key.p);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
+    DBG_SYNC(ctx, "k_make_strands");
     return CM_OK;
 }
 
@@ -676,6 +701,7 @@ static int launch_seed(cm_gpu_ctx *ctx, const DevView &v) {
                                                          (uint32_t *) ctx->seed_off.p, (uint32_t *) ctx->seed_cnt.p, ctx->d_counters);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
+    DBG_SYNC(ctx, "k_seed");
     return CM_OK;
 }
 

@@ -37,6 +37,7 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
     ENSURE(ctx, ctx->cell_off, ((size_t) ns + 1) * 8);
     k_cell_count<<<grid_for(ns, 256), 256, 0, st>>>(v, b.seed_cnt, ns, (uint32_t *) ctx->cell_cnt.p);
     ctx->launches++;
+    DBG_SYNC(ctx, "k_cell_count");
     size_t tb = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, tb, (const uint32_t *) ctx->cell_cnt.p, (uint64_t *) ctx->cell_off.p, (int) ns, st);
     ENSURE(ctx, ctx->cub_tmp, tb + 16);
@@ -72,12 +73,14 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
                                         (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) ns, 0, 32, st);
     }
     ctx->launches += 2;
+    DBG_SYNC(ctx, "k_strand_key + sort");
     k_chain<<<grid_for(ns, 128), 128, 0, st>>>(v, b, (const uint64_t *) ctx->cell_off.p, (double *) ctx->dp_score.p,
                                                (uint32_t *) ctx->dp_prev.p, (ChainRec *) ctx->recs.p, mult,
                                                (uint32_t *) ctx->ovf_strand.p, (uint32_t *) ctx->ovf_nrec.p, (uint32_t *) ctx->ovf_n.p,
                                                (const uint32_t *) ctx->perm[1].p, ctx->d_counters);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
+    DBG_SYNC(ctx, "k_chain");
     uint32_t n_ovf = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&n_ovf, ctx->ovf_n.p, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
@@ -121,9 +124,11 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
         ENSURE(ctx, ctx->chain_aux, (size_t) n_chains * sizeof(ChainAux));
         b.aux = (ChainAux *) ctx->chain_aux.p;
         k_chain_list<<<grid_for(ns, 256), 256, 0, st>>>(b, (uint32_t *) ctx->chain_ids.p);
+        DBG_SYNC(ctx, "k_chain_list");
         k_chain_spec<<<grid_for(3ull * n_chains, 128), 128, 0, st>>>(v, b, (const uint32_t *) ctx->chain_ids.p, n_chains, ctx->d_counters);
         ctx->launches += 2;
         CUDA_TRY(ctx, cudaGetLastError());
+        DBG_SYNC(ctx, "k_chain_spec");
     }
     return CM_OK;
 }
@@ -147,6 +152,7 @@ static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) 
         cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tb, (const unsigned long long *) ctx->key64[0].p, (unsigned long long *) ctx->key64[1].p,
                                         (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, 43, st);
         ctx->launches += 2;
+        DBG_SYNC(ctx, "k_pair_key + sort");
         k_process_pe<<<grid_for(n, 128), 128, 0, st>>>(v, b, (const cm_mread *) ctx->in_mread.p, (cm_mread *) ctx->out_mread.p,
                                                       (int32_t *) ctx->out_state.p, n, (const uint32_t *) ctx->perm[1].p, ctx->d_counters);
     } else {
@@ -154,6 +160,7 @@ static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) 
     }
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
+    DBG_SYNC(ctx, "k_process");
     return CM_OK;
 }
 

@@ -99,6 +99,7 @@ __device__ __forceinline__ void block_stats_init(BlockStats &sh) {
     __syncthreads();
 }
 __device__ __forceinline__ void block_stats_add(BlockStats &sh, const AlignStats &st, uint32_t units, cm_counters *ctr) {
+    if (CM_DBG_FLAGS & 4) return;
     if (st.xdrop_cells) atomicAdd(&sh.v[0], (unsigned long long) st.xdrop_cells);
     if (st.edit_cells) atomicAdd(&sh.v[1], (unsigned long long) st.edit_cells);
     if (st.xdrop_calls) atomicAdd(&sh.v[2], (unsigned long long) st.xdrop_calls);
