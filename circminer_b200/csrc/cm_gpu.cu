@@ -13,6 +13,8 @@
 
 #include "cm_pipeline.h"
 
+#define CM_CTR_SLOTS 256   // copies of cm_counters on the device (power of two), summed on read
+
 // ------------------------------------------------------------------------------------------
 // context
 // ------------------------------------------------------------------------------------------
@@ -170,11 +172,16 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
         return fail(nullptr, CM_ERR_CUDA, "cannot initialise device %d", device);
     }
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
-    if (cudaMalloc(&ctx->d_counters, sizeof(cm_counters)) != cudaSuccess) {
+    {   // the index gathers are 32-byte random reads: ask L2 not to promote misses to 64/128-byte DRAM fetches
+        size_t g = 32;
+        if (const char *e = getenv("CM_GPU_L2_FETCH")) g = (size_t) atoi(e);
+        if (g) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, g);
+    }
+    if (cudaMalloc(&ctx->d_counters, CM_CTR_SLOTS * sizeof(cm_counters)) != cudaSuccess) {
         delete ctx;
         return fail(nullptr, CM_ERR_ALLOC, "cudaMalloc counters");
     }
-    cudaMemsetAsync(ctx->d_counters, 0, sizeof(cm_counters), ctx->stream);
+    cudaMemsetAsync(ctx->d_counters, 0, CM_CTR_SLOTS * sizeof(cm_counters), ctx->stream);
     cudaStreamSynchronize(ctx->stream);
     if (const char *e = getenv("CM_GPU_REC_MULT")) ctx->rec_mult = (uint32_t) atoi(e);
     if (const char *e = getenv("CM_GPU_NO_SPEC")) ctx->no_spec = atoi(e) != 0;
@@ -218,11 +225,17 @@ extern "C" int cm_gpu_get_counters(cm_gpu_ctx *ctx, cm_counters *out, int reset)
     if (!ctx || !out) return CM_ERR_ARG;
     cudaSetDevice(ctx->device);
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    CUDA_TRY(ctx, cudaMemcpy(out, ctx->d_counters, sizeof *out, cudaMemcpyDeviceToHost));
+    static_assert(sizeof(cm_counters) % 8 == 0, "cm_counters is an array of u64");
+    std::vector<uint64_t> slots(CM_CTR_SLOTS * sizeof(cm_counters) / 8);
+    CUDA_TRY(ctx, cudaMemcpy(slots.data(), ctx->d_counters, slots.size() * 8, cudaMemcpyDeviceToHost));
+    uint64_t *o = (uint64_t *) out;
+    const size_t nf = sizeof(cm_counters) / 8;
+    for (size_t f = 0; f < nf; f++) o[f] = 0;
+    for (size_t k = 0; k < slots.size(); k++) o[k % nf] += slots[k];
     out->kernel_launches = ctx->launches;
     if (reset) {
         // on the context's own (non-blocking) stream: a legacy-stream memset is not ordered against later launches
-        CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(cm_counters), ctx->stream));
+        CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_counters, 0, CM_CTR_SLOTS * sizeof(cm_counters), ctx->stream));
         CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
         ctx->launches = 0;
     }
@@ -666,16 +679,24 @@ __global__ void __launch_bounds__(256) k_seed(DevView v, const int2 *__restrict_
         seed_off[gid] = h.off;
         seed_cnt[gid] = h.cnt;
     }
-    // warp-aggregated counters (roofline numerators)
+    // block-aggregated counters (roofline numerators): one thread per block adds into one
+    // of CM_CTR_SLOTS copies; per-warp same-address atomics were what bounded this kernel before.
+    __shared__ uint32_t sh[3][8];
     for (int o = 16; o; o >>= 1) {
         sectors += __shfl_down_sync(0xffffffffu, sectors, o);
         hits += __shfl_down_sync(0xffffffffu, hits, o);
         looked += __shfl_down_sync(0xffffffffu, looked, o);
     }
-    if ((threadIdx.x & 31) == 0 && looked) {
-        atomicAdd((unsigned long long *) &ctr->seeds, (unsigned long long) looked);
-        atomicAdd((unsigned long long *) &ctr->seed_sectors, (unsigned long long) sectors);
-        atomicAdd((unsigned long long *) &ctr->seed_hits, (unsigned long long) hits);
+    const uint32_t w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) { sh[0][w] = looked; sh[1][w] = sectors; sh[2][w] = hits; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        unsigned long long t = 0;
+        for (uint32_t k = 0; k < (blockDim.x >> 5); k++) t += sh[threadIdx.x][k];
+        cm_counters *c = ctr + (blockIdx.x & (CM_CTR_SLOTS - 1));
+        unsigned long long *dst = threadIdx.x == 0 ? (unsigned long long *) &c->seeds
+                                  : threadIdx.x == 1 ? (unsigned long long *) &c->seed_sectors : (unsigned long long *) &c->seed_hits;
+        if (t) atomicAdd(dst, t);
     }
 }
 

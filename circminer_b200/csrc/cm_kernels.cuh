@@ -57,8 +57,10 @@ __global__ void __launch_bounds__(128) k_chain(DevView v, BatchDev b, const uint
             }
         }
     }
-    for (int o = 16; o; o >>= 1) links += __shfl_down_sync(0xffffffffu, links, o);
-    if ((threadIdx.x & 31) == 0 && links) atomicAdd((unsigned long long *) &ctr->chain_links, (unsigned long long) links);
+    if (links) {
+        cm_counters *c = ctr + ((blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) & (CM_CTR_SLOTS - 1));
+        atomicAdd((unsigned long long *) &c->chain_links, (unsigned long long) links);
+    }
 }
 
 // overflow path: record arena sized exactly from the counts k_chain produced
@@ -88,39 +90,23 @@ __global__ void __launch_bounds__(128) k_chain_big(DevView v, BatchDev b, const 
 // ------------------------------------------------------------------------------------------
 // K3: extension + classification, one thread per pair (PE) / read (SE)
 // ------------------------------------------------------------------------------------------
-// Block-level accumulation of the work counters.  Shared-memory atomics instead of warp shuffles: the
-// threads of a warp leave the per-pair code at unrelated points, and a full-mask shuffle after that much
-// divergence lost contributions on sm_100a.
-struct BlockStats {
-    unsigned long long v[5];
-};
-__device__ __forceinline__ void block_stats_init(BlockStats &sh) {
-    if (threadIdx.x < 5) sh.v[threadIdx.x] = 0;
-    __syncthreads();
-}
-__device__ __forceinline__ void block_stats_add(BlockStats &sh, const AlignStats &st, uint32_t units, cm_counters *ctr) {
+// Work counters.  No block barrier here: the threads of a warp leave the per-pair code at unrelated points and
+// an aligned bar.sync reached by a diverged warp is undefined (it lost contributions on sm_100a).  Each thread
+// adds its non-zero counts into one of CM_CTR_SLOTS copies of cm_counters (summed by cm_gpu_get_counters),
+// chosen by warp, so same-address atomics stay rare.
+__device__ __forceinline__ void stats_flush(const AlignStats &st, uint32_t units, cm_counters *ctr) {
     if (CM_DBG_FLAGS & 4) return;
-    if (st.xdrop_cells) atomicAdd(&sh.v[0], (unsigned long long) st.xdrop_cells);
-    if (st.edit_cells) atomicAdd(&sh.v[1], (unsigned long long) st.edit_cells);
-    if (st.xdrop_calls) atomicAdd(&sh.v[2], (unsigned long long) st.xdrop_calls);
-    if (st.edit_calls) atomicAdd(&sh.v[3], (unsigned long long) st.edit_calls);
-    if (units) atomicAdd(&sh.v[4], (unsigned long long) units);
-    __syncthreads();
-    if (threadIdx.x < 5 && sh.v[threadIdx.x]) {
-        unsigned long long *dst = threadIdx.x == 0 ? (unsigned long long *) &ctr->xdrop_cells
-                                  : threadIdx.x == 1 ? (unsigned long long *) &ctr->edit_cells
-                                  : threadIdx.x == 2 ? (unsigned long long *) &ctr->xdrop_calls
-                                  : threadIdx.x == 3 ? (unsigned long long *) &ctr->edit_calls
-                                                     : (unsigned long long *) &ctr->pairs;
-        atomicAdd(dst, sh.v[threadIdx.x]);
-    }
+    cm_counters *c = ctr + ((blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) & (CM_CTR_SLOTS - 1));
+    if (st.xdrop_cells) atomicAdd((unsigned long long *) &c->xdrop_cells, (unsigned long long) st.xdrop_cells);
+    if (st.edit_cells) atomicAdd((unsigned long long *) &c->edit_cells, (unsigned long long) st.edit_cells);
+    if (st.xdrop_calls) atomicAdd((unsigned long long *) &c->xdrop_calls, (unsigned long long) st.xdrop_calls);
+    if (st.edit_calls) atomicAdd((unsigned long long *) &c->edit_calls, (unsigned long long) st.edit_calls);
+    if (units) atomicAdd((unsigned int *) &c->pairs, units);   // low word of the slot; 2^32 units per slot between resets
 }
 
 __global__ void __launch_bounds__(128) k_process_pe(DevView v, BatchDev b, const cm_mread *__restrict__ in, cm_mread *__restrict__ out,
                                                     int32_t *__restrict__ state, uint32_t n_pairs, const uint32_t *__restrict__ order,
                                                     cm_counters *__restrict__ ctr) {
-    __shared__ BlockStats sh;
-    block_stats_init(sh);
     uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     AlignStats st = {0, 0, 0, 0};
     const bool live = slot < n_pairs;
@@ -130,17 +116,15 @@ __global__ void __launch_bounds__(128) k_process_pe(DevView v, BatchDev b, const
         state[i] = cm_pair_process(v, b, i, mr, st);
         out[i] = mr;
     }
-    block_stats_add(sh, st, live ? 1u : 0u, ctr);
+    stats_flush(st, live ? 1u : 0u, ctr);
 }
 
 __global__ void __launch_bounds__(128) k_process_se(DevView v, BatchDev b, int32_t *__restrict__ state, uint32_t n_reads,
                                                     cm_counters *__restrict__ ctr) {
-    __shared__ BlockStats sh;
-    block_stats_init(sh);
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     AlignStats st = {0, 0, 0, 0};
     if (i < n_reads) state[i] = cm_read_process_se(v, b, i, st);
-    block_stats_add(sh, st, i < n_reads ? 1u : 0u, ctr);
+    stats_flush(st, i < n_reads ? 1u : 0u, ctr);
 }
 
 // stage-level parity entry: chains of the forward strand of each row, in the API layout [n][C][n_slots]
@@ -251,8 +235,6 @@ __global__ void k_chain_list(BatchDev b, uint32_t *__restrict__ list) {
 
 __global__ void __launch_bounds__(128) k_chain_spec(DevView v, BatchDev b, const uint32_t *__restrict__ list, uint32_t n_chains,
                                                     cm_counters *__restrict__ ctr) {
-    __shared__ BlockStats sh;
-    block_stats_init(sh);
     uint64_t gid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
     ExtCtx x;
     x.v = &v;
@@ -268,5 +250,5 @@ __global__ void __launch_bounds__(128) k_chain_spec(DevView v, BatchDev b, const
         ch.aux = nullptr;
         cm_chain_spec(x, ch, b.strands + (size_t) s * b.stride, b.strand_len[s], kind, b.aux[id]);
     }
-    block_stats_add(sh, x.st, 0u, ctr);
+    stats_flush(x.st, 0u, ctr);
 }

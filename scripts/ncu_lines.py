@@ -36,6 +36,7 @@ for ln in dis.splitlines():
 short = re.sub(r"\(.*", "", b["name"])
 cands = [f for f in lines_by_fn if short in f]
 assert cands, (short, list(lines_by_fn)[:5])
+cands.sort(key=lambda f: abs(len(lines_by_fn[f]) - len(b["rows"])))
 li = lines_by_fn[cands[0]]
 n = min(len(li), len(b["rows"]))
 print(f"# {b['name'][:60]}  sass rows {len(b['rows'])}  disasm instrs {len(li)}")
