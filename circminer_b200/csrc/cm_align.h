@@ -249,18 +249,32 @@ CM_HDN void cm_xdrop_generic(const uint8_t *s, int n, const uint8_t *t, int m, b
 // update X[e] = max(X[e] + sc, X[e-1] + ind, X[e+1] + ind) is in place (X[e] still holds diagonal k-2)
 // and every index is a compile-time constant after unrolling.  Same visit order, same lb/ub evolution,
 // same pruning as cm_xdrop_generic, hence the same (on_s, on_t, score).
-template <int W, int PAR>
-CM_HD void cm_xdrop_step(int (&X)[2 * W + 3], int k, int lb, int ub, const uint8_t *s, int n, const uint8_t *t, int m, bool rev,
-                         int mat, int mis, int ind, int xd, int pre, int &cur, int &best_i, int &best_j, int &new_ub, uint32_t &cells) {
+//
+// The two strings are not read cell by cell: anti-diagonals k = 2q and 2q + 1 only touch characters
+// q + LO .. q + HI of s and of t (LO = -(W/2 + 1), HI = (W + 1)/2 - 1), so a window of W + 1 character
+// codes per string sits in registers and slides by one character per q (one byte load per string per
+// two anti-diagonals, issued ahead of its use).  Codes: 'A','C','G','T' (case folded) or a value that
+// never compares equal (N never matches N, align.cpp:745-759).
+CM_HD int cm_code(uint8_t c, int bad) {
+    uint8_t u = c & 0xDF;
+    return (u == 'A' || u == 'C' || u == 'G' || u == 'T') ? (int) u : bad;
+}
+CM_HD int cm_code_at(const uint8_t *p0, int step, int len, int c, int bad) { return (c >= 0 && c < len) ? cm_code(p0[c * step], bad) : bad; }
+
+template <int W, int KP>
+CM_HD void cm_xdrop_step(int (&X)[2 * W + 3], const int (&SW)[W + 1], const int (&TW)[W + 1], int k, int q, int lb, int ub, int mat, int mis,
+                         int ind, int xd, int pre, int &cur, int &best_i, int &best_j, int &new_ub, uint32_t &cells) {
     const int NEG = -CM_DPTINF;
+    constexpr int LO = -(W / 2 + 1);
 #pragma unroll
     for (int e = 1; e <= 2 * W + 1; e++) {
-        if ((e & 1) != PAR) continue;
         const int d = e - W - 1;
-        const int i = (k + d) >> 1, j = k - i;
+        if (((d + KP) & 1) != 0) continue;          // slot belongs to the other parity
+        const int h = (KP + d) / 2;                 // exact: KP + d is even
+        const int i = q + h, j = k - i;
         int v;
         if (i >= lb && i <= ub) {
-            int sc = cm_base_eq(cm_at(s, n, i - 1, rev), cm_at(t, m, j - 1, rev)) ? mat : mis;
+            int sc = SW[h - 1 - LO] == TW[(KP - d) / 2 - 1 - LO] ? mat : mis;
             v = X[e] + sc;
             int a = X[e - 1] + ind, b = X[e + 1] + ind;
             v = v > a ? v : a;
@@ -290,19 +304,40 @@ CM_HD void cm_xdrop_reg(const uint8_t *s, int n, const uint8_t *t, int m, bool r
     for (int e = 0; e < 2 * W + 3; e++) X[e] = NEG;
     X[W + 1] = 0;                                  // dpx[0][0]  (anti-diagonal 0)
     if (W >= 1) { X[W + 2] = ind; X[W] = ind; }    // dpx[1][0], dpx[0][1]  (anti-diagonal 1)
+    constexpr int LO = -(W / 2 + 1), HI = (W + 1) / 2 - 1;
+    const uint8_t *s0 = rev ? s + n - 1 : s, *t0 = rev ? t + m - 1 : t;
+    const int step = rev ? -1 : 1;
+    int SW[W + 1], TW[W + 1];
+#pragma unroll
+    for (int x = 0; x <= W; x++) {                 // window of q = 1
+        SW[x] = cm_code_at(s0, step, n, 1 + LO + x, 1);
+        TW[x] = cm_code_at(t0, step, m, 1 + LO + x, 2);
+    }
     int pre = 0, cur = 0, lb = 1, ub = 1, pre_ub = 0, best_i = 0, best_j = 0;
     uint32_t cells = 0;
-    constexpr int P_EVEN = (W + 1) & 1;            // slot parity of even anti-diagonals
-    for (int k = 2; k <= m + n; ++k) {
-        int new_ub = -1;
-        if (k & 1) cm_xdrop_step<W, P_EVEN ^ 1>(X, k, lb, ub, s, n, t, m, rev, mat, mis, ind, xd, pre, cur, best_i, best_j, new_ub, cells);
-        else cm_xdrop_step<W, P_EVEN>(X, k, lb, ub, s, n, t, m, rev, mat, mis, ind, xd, pre, cur, best_i, best_j, new_ub, cells);
-        int lb_t = k - lb;
-        if (lb_t == m || (k > W && ((k - W) % 2 == 0))) ++lb;
-        if (ub < n && (k <= W || (k > W && ((k - W) % 2 == 1)))) ++ub;
-        if ((pre_ub == -1 && new_ub == -1) || lb > ub) break;
-        pre_ub = new_ub;
-        if (cur > pre) pre = cur;
+    const int K = m + n;
+    for (int q = 1; 2 * q <= K; ++q) {
+        const int ns = cm_code_at(s0, step, n, q + 1 + HI, 1), nt = cm_code_at(t0, step, m, q + 1 + HI, 2);   // for q + 1
+        bool stop = false;
+#pragma unroll
+        for (int kp = 0; kp < 2; kp++) {
+            const int k = 2 * q + kp;
+            if (k > K) { stop = true; break; }
+            int new_ub = -1;
+            if (kp) cm_xdrop_step<W, 1>(X, SW, TW, k, q, lb, ub, mat, mis, ind, xd, pre, cur, best_i, best_j, new_ub, cells);
+            else cm_xdrop_step<W, 0>(X, SW, TW, k, q, lb, ub, mat, mis, ind, xd, pre, cur, best_i, best_j, new_ub, cells);
+            int lb_t = k - lb;
+            if (lb_t == m || (k > W && ((k - W) % 2 == 0))) ++lb;
+            if (ub < n && (k <= W || (k > W && ((k - W) % 2 == 1)))) ++ub;
+            if ((pre_ub == -1 && new_ub == -1) || lb > ub) { stop = true; break; }
+            pre_ub = new_ub;
+            if (cur > pre) pre = cur;
+        }
+        if (stop) break;
+#pragma unroll
+        for (int x = 0; x < W; x++) { SW[x] = SW[x + 1]; TW[x] = TW[x + 1]; }
+        SW[W] = ns;
+        TW[W] = nt;
     }
     if (st) st->xdrop_cells += cells;
     on_s = best_i;

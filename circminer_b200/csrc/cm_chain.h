@@ -80,7 +80,18 @@ CM_HDN uint32_t cm_chain_dp(const DevView &v, int seq_len, int T, const uint32_t
                 if (cu == 0 || lb_ind[u] >= cu) continue;
                 const uint32_t *pu = pos + row_pos_off[u];
                 if (seg_start + (uint32_t) v.p.max_intron_len < pu[lb_ind[u]]) continue;
-                while (lb_ind[u] < cu && pu[lb_ind[u]] <= seg_start) lb_ind[u]++;
+                // first index >= lb_ind[u] with pu[idx] > seg_start (rows are ascending): gallop + bisect
+                // instead of the reference's linear cursor walk (chain.cpp:153-156), same result
+                if (pu[lb_ind[u]] <= seg_start) {
+                    uint32_t lo = lb_ind[u], step = 1;
+                    while (lo + step < cu && pu[lo + step] <= seg_start) { lo += step; step <<= 1; }
+                    uint32_t hi = lo + step < cu ? lo + step : cu;   // pu[lo] <= seg_start < pu[hi] (or hi == cu)
+                    while (hi - lo > 1) {
+                        uint32_t mid = (lo + hi) >> 1;
+                        if (pu[mid] <= seg_start) lo = mid; else hi = mid;
+                    }
+                    lb_ind[u] = hi;
+                }
                 if (lb_ind[u] >= cu) continue;
                 if (max_lpos_lim == CM_MAXUB)
                     max_lpos_lim = cm_upper_bound(v.a, v.p, seg_start, (uint32_t) kmer, read_remain, max_exon_end, ol_iv);
@@ -137,6 +148,8 @@ CM_HDN void cm_chain_backtrack(const DevView &v, int T, const uint32_t *row_pos_
         if (recs[r].score > best_score) best_score = recs[r].score;
     double thresh = 0;
     bool first = true;
+    uint64_t bloom[16];
+    for (int q = 0; q < 16; q++) bloom[q] = 0;
     while (best_count < max_best) {
         // next distinct score below thresh
         bool found = false;
@@ -159,8 +172,10 @@ CM_HDN void cm_chain_backtrack(const DevView &v, int T, const uint32_t *row_pos_
             uint32_t loc = recs[r].loc;
             uint32_t spos = pos[row_pos_off[loc >> 16] + (loc & 0xFFFF)];
             if (s < best_score) {
-                // `repeats`: rpos of every non-first fragment of the chains emitted so far
+                // `repeats`: rpos of every non-first fragment of the chains emitted so far.  A small Bloom
+                // filter answers most queries; the exact scan runs only on a filter hit.
                 bool rep = false;
+                if ((bloom[(spos >> 6) & 15u] >> (spos & 63u)) & 1ull)
                 for (uint32_t c = 0; c < best_count && !rep; c++)
                     for (uint32_t f = 1; f < out.len[c]; f++)
                         if (out.frags[c * out.F + f].rpos == spos) {
@@ -176,6 +191,7 @@ CM_HDN void cm_chain_backtrack(const DevView &v, int T, const uint32_t *row_pos_
                 uint32_t row = cur >> 16, ind = cur & 0xFFFF;
                 out.frags[j * out.F + n].rpos = pos[row_pos_off[row] + ind];
                 out.frags[j * out.F + n].qpos = (int32_t) row * kmer;
+                if (n) { uint32_t rp = pos[row_pos_off[row] + ind]; bloom[(rp >> 6) & 15u] |= 1ull << (rp & 63u); }
                 n++;
                 cur = dp_prev[row_off[row] + ind];
             }

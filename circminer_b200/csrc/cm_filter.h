@@ -15,13 +15,14 @@ struct ChainListView {
     const uint32_t *len;       // [C]
     const FragDev *frags;      // [C][F]
     int F;
-    const ChainAux *aux;       // [count] or nullptr
+    const ChainAux *aux;       // [n_aux] or nullptr: pre-alignment results of the first n_aux chains
+    int n_aux;
 };
 CM_HD ChainView cl_chain(const ChainListView &l, int i) {
     ChainView c;
     c.frags = l.frags + (size_t) i * l.F;
     c.chain_len = l.len[i];
-    c.aux = l.aux ? l.aux + i : nullptr;
+    c.aux = (l.aux && i < l.n_aux) ? l.aux + i : nullptr;
     return c;
 }
 

@@ -65,7 +65,9 @@ struct cm_gpu_ctx {
     DevBuf chain_base, chain_ids, chain_aux;              // compact chain list + pre-alignment results
     uint32_t last_chains = 0;
     bool sync_each = false;    // CM_GPU_SYNC_EACH=1: synchronise after every launch and name the kernel that failed
+    int spec_k = CM_MAX_CHAINS;            // CM_GPU_SPEC_K: leading chains per strand handed to the dense pre-alignment kernel
     bool no_spec = false;      // CM_GPU_NO_SPEC=1: every DP inline in the per-pair kernel (debug / A-B)
+    DevBuf spec_key[2], spec_item[2];                     // pre-alignment work items, before / after the cost sort
     DevBuf key32[2], key64[2], perm[2];                   // work-signature sort of strands / pairs
     DevBuf scratch[8];
 };
@@ -184,6 +186,7 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
     cudaMemsetAsync(ctx->d_counters, 0, CM_CTR_SLOTS * sizeof(cm_counters), ctx->stream);
     cudaStreamSynchronize(ctx->stream);
     if (const char *e = getenv("CM_GPU_REC_MULT")) ctx->rec_mult = (uint32_t) atoi(e);
+    if (const char *e = getenv("CM_GPU_SPEC_K")) ctx->spec_k = atoi(e) < 1 ? 1 : atoi(e);
     if (const char *e = getenv("CM_GPU_NO_SPEC")) ctx->no_spec = atoi(e) != 0;
     if (const char *e = getenv("CM_GPU_SYNC_EACH")) ctx->sync_each = atoi(e) != 0;
     if (const char *e = getenv("CM_GPU_DBG")) {
@@ -213,6 +216,7 @@ extern "C" int cm_gpu_destroy(cm_gpu_ctx *ctx) {
     for (DevBuf *b : bufs) release(*b);
     for (auto &b : ctx->scratch) release(b);
     release(ctx->chain_base); release(ctx->chain_ids); release(ctx->chain_aux);
+    for (int q = 0; q < 2; q++) { release(ctx->spec_key[q]); release(ctx->spec_item[q]); }
     for (int q = 0; q < 2; q++) { release(ctx->key32[q]); release(ctx->key64[q]); release(ctx->perm[q]); }
     cudaFree(ctx->d_counters);
     for (auto &ev : ctx->ev) cudaEventDestroy(ev);

@@ -26,6 +26,7 @@ static int make_batch(cm_gpu_ctx *ctx, BatchDev &b) {
     b.chain_frags = (FragDev *) ctx->chain_frags.p;
     b.chain_base = nullptr;
     b.aux = nullptr;
+    b.spec_k = 0;
     return CM_OK;
 }
 
@@ -104,17 +105,20 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
     }
     // dense pre-alignment of every chain (memo for the per-pair kernel)
     ENSURE(ctx, ctx->chain_base, ((size_t) ns + 1) * 4);
+    ENSURE(ctx, ctx->key32[0], (size_t) ns * 4);
+    b.spec_k = ctx->spec_k;
+    uint32_t *spec_cnt = (uint32_t *) ctx->key32[0].p;   // the strand sort is done with its keys
+    k_spec_count<<<grid_for(ns, 256), 256, 0, st>>>(b, spec_cnt);
     {
         size_t tb3 = 0;
-        cub::DeviceScan::ExclusiveSum(nullptr, tb3, (const int32_t *) ctx->chain_cnt.p, (uint32_t *) ctx->chain_base.p, (int) ns, st);
+        cub::DeviceScan::ExclusiveSum(nullptr, tb3, (const uint32_t *) spec_cnt, (uint32_t *) ctx->chain_base.p, (int) ns, st);
         ENSURE(ctx, ctx->cub_tmp, tb3 + 16);
-        cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tb3, (const int32_t *) ctx->chain_cnt.p, (uint32_t *) ctx->chain_base.p, (int) ns, st);
-        ctx->launches++;
+        cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tb3, (const uint32_t *) spec_cnt, (uint32_t *) ctx->chain_base.p, (int) ns, st);
+        ctx->launches += 2;
     }
-    uint32_t last_base = 0;
-    int32_t last_n = 0;
+    uint32_t last_base = 0, last_n = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&last_base, (uint32_t *) ctx->chain_base.p + (ns - 1), 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaMemcpyAsync(&last_n, (int32_t *) ctx->chain_cnt.p + (ns - 1), 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&last_n, spec_cnt + (ns - 1), 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     const uint32_t n_chains = last_base + (uint32_t) last_n;
     ctx->last_chains = n_chains;
@@ -123,10 +127,26 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
         ENSURE(ctx, ctx->chain_ids, (size_t) n_chains * 4);
         ENSURE(ctx, ctx->chain_aux, (size_t) n_chains * sizeof(ChainAux));
         b.aux = (ChainAux *) ctx->chain_aux.p;
-        k_chain_list<<<grid_for(ns, 256), 256, 0, st>>>(b, (uint32_t *) ctx->chain_ids.p);
+        CUDA_TRY(ctx, cudaMemsetAsync(ctx->chain_aux.p, 0, (size_t) n_chains * sizeof(ChainAux), st));
+        const size_t n_items = 3ull * n_chains;
+        ENSURE(ctx, ctx->spec_key[0], n_items);
+        ENSURE(ctx, ctx->spec_key[1], n_items);
+        ENSURE(ctx, ctx->spec_item[0], n_items * 4);
+        ENSURE(ctx, ctx->spec_item[1], n_items * 4);
+        k_chain_ids<<<grid_for(ns, 256), 256, 0, st>>>(b, (uint32_t *) ctx->chain_ids.p);
+        k_chain_list<<<grid_for(ns, 256), 256, 0, st>>>(v, b, n_chains, (uint8_t *) ctx->spec_key[0].p, (uint32_t *) ctx->spec_item[0].p);
         DBG_SYNC(ctx, "k_chain_list");
-        k_chain_spec<<<grid_for(3ull * n_chains, 128), 128, 0, st>>>(v, b, (const uint32_t *) ctx->chain_ids.p, n_chains, ctx->d_counters);
-        ctx->launches += 2;
+        {
+            size_t tb4 = 0;
+            cub::DeviceRadixSort::SortPairsDescending(nullptr, tb4, (const uint8_t *) ctx->spec_key[0].p, (uint8_t *) ctx->spec_key[1].p,
+                                                      (const uint32_t *) ctx->spec_item[0].p, (uint32_t *) ctx->spec_item[1].p, (int) n_items, 0, 8, st);
+            ENSURE(ctx, ctx->cub_tmp, tb4 + 16);
+            cub::DeviceRadixSort::SortPairsDescending(ctx->cub_tmp.p, tb4, (const uint8_t *) ctx->spec_key[0].p, (uint8_t *) ctx->spec_key[1].p,
+                                                      (const uint32_t *) ctx->spec_item[0].p, (uint32_t *) ctx->spec_item[1].p, (int) n_items, 0, 8, st);
+        }
+        k_chain_spec<<<grid_for(n_items, 128), 128, 0, st>>>(v, b, (const uint32_t *) ctx->chain_ids.p, (const uint8_t *) ctx->spec_key[1].p,
+                                                            (const uint32_t *) ctx->spec_item[1].p, n_chains, ctx->d_counters);
+        ctx->launches += 4;
         CUDA_TRY(ctx, cudaGetLastError());
         DBG_SYNC(ctx, "k_chain_spec");
     }
@@ -146,10 +166,10 @@ static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) 
         cudaStream_t st = ctx->stream;
         k_pair_key<<<grid_for(n, 256), 256, 0, st>>>(v, b, n, (unsigned long long *) ctx->key64[0].p, (uint32_t *) ctx->perm[0].p);
         size_t tb = 0;
-        cub::DeviceRadixSort::SortPairs(nullptr, tb, (const unsigned long long *) ctx->key64[0].p, (unsigned long long *) ctx->key64[1].p,
+        cub::DeviceRadixSort::SortPairsDescending(nullptr, tb, (const unsigned long long *) ctx->key64[0].p, (unsigned long long *) ctx->key64[1].p,
                                         (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, 43, st);
         ENSURE(ctx, ctx->cub_tmp, tb + 16);
-        cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tb, (const unsigned long long *) ctx->key64[0].p, (unsigned long long *) ctx->key64[1].p,
+        cub::DeviceRadixSort::SortPairsDescending(ctx->cub_tmp.p, tb, (const unsigned long long *) ctx->key64[0].p, (unsigned long long *) ctx->key64[1].p,
                                         (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, 43, st);
         ctx->launches += 2;
         DBG_SYNC(ctx, "k_pair_key + sort");

@@ -225,30 +225,68 @@ __global__ void k_pair_key(DevView v, BatchDev b, uint32_t n_pairs, unsigned lon
 // the two read ends), so it is done here first, one thread per (chain, kind) with all lanes of a warp
 // on the same kind, and handed to k_process_* as a memo (ChainAux / DropHint).
 // ------------------------------------------------------------------------------------------
-__global__ void k_chain_list(BatchDev b, uint32_t *__restrict__ list) {
+__global__ void k_spec_count(BatchDev b, uint32_t *__restrict__ cnt) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= b.n_strands) return;
+    int n = b.chain_cnt[s];
+    cnt[s] = (uint32_t) (n < b.spec_k ? n : b.spec_k);
+}
+
+// Work items of the pre-alignment: (chain, kind) with a cost key = read bases the DP has to cover.  Items are
+// sorted by descending cost, so the lanes of a warp run DPs of the same kind and about the same length and the
+// zero-cost items (nothing to align: ChainAux stays zeroed, has_* = 0) fall to the end, where whole warps exit.
+__global__ void k_chain_list(DevView v, BatchDev b, uint32_t n_chains, uint8_t *__restrict__ key, uint32_t *__restrict__ item) {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= b.n_strands) return;
     uint32_t base = b.chain_base[s];
     int n = b.chain_cnt[s];
+    if (n > b.spec_k) n = b.spec_k;
+    const int k = v.p.kmer, len = b.strand_len[s];
+    for (int c = 0; c < n; c++) {
+        const FragDev *fr = b.chain_frags + ((size_t) s * b.C + c) * b.F;
+        const uint32_t L = b.chain_len[(size_t) s * b.C + c];
+        int gap = 0;
+        for (uint32_t i = 0; i + 1 < L; i++) {
+            int g = fr[i + 1].qpos - fr[i].qpos - k;
+            if (g > 0) gap += g;
+        }
+        int ml = L ? fr[0].qpos : 0, mr = L ? len - (fr[L - 1].qpos + k) : 0;
+        const uint32_t id = base + (uint32_t) c;
+        const int cost[3] = {gap, ml, mr};
+        for (int kind = 0; kind < 3; kind++) {
+            int q = cost[kind] < 0 ? 0 : (cost[kind] > 255 ? 255 : cost[kind]);
+            key[(size_t) kind * n_chains + id] = (uint8_t) q;
+            item[(size_t) kind * n_chains + id] = ((uint32_t) kind << 30) | id;
+        }
+    }
+}
+
+// chain id -> (strand << 5 | chain)
+__global__ void k_chain_ids(BatchDev b, uint32_t *__restrict__ list) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= b.n_strands) return;
+    uint32_t base = b.chain_base[s];
+    int n = b.chain_cnt[s];
+    if (n > b.spec_k) n = b.spec_k;
     for (int c = 0; c < n; c++) list[base + c] = (s << 5) | (uint32_t) c;
 }
 
-__global__ void __launch_bounds__(128) k_chain_spec(DevView v, BatchDev b, const uint32_t *__restrict__ list, uint32_t n_chains,
-                                                    cm_counters *__restrict__ ctr) {
+__global__ void __launch_bounds__(128) k_chain_spec(DevView v, BatchDev b, const uint32_t *__restrict__ list, const uint8_t *__restrict__ key,
+                                                    const uint32_t *__restrict__ item, uint32_t n_chains, cm_counters *__restrict__ ctr) {
     uint64_t gid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
     ExtCtx x;
     x.v = &v;
     x.st.xdrop_cells = x.st.edit_cells = x.st.xdrop_calls = x.st.edit_calls = 0;
     x.hint.valid = 0;
-    if (gid < 3ull * n_chains) {
-        int kind = (int) (gid / n_chains);
-        uint32_t id = (uint32_t) (gid - (uint64_t) kind * n_chains);
-        uint32_t e = list[id], s = e >> 5, c = e & 31u;
-        ChainView ch;
-        ch.frags = b.chain_frags + ((size_t) s * b.C + c) * b.F;
-        ch.chain_len = b.chain_len[(size_t) s * b.C + c];
-        ch.aux = nullptr;
-        cm_chain_spec(x, ch, b.strands + (size_t) s * b.stride, b.strand_len[s], kind, b.aux[id]);
-    }
+    if (gid >= 3ull * n_chains || key[gid] == 0) return;
+    const uint32_t it = item[gid];
+    const int kind = (int) (it >> 30);
+    const uint32_t id = it & 0x3FFFFFFFu;
+    uint32_t e = list[id], s = e >> 5, c = e & 31u;
+    ChainView ch;
+    ch.frags = b.chain_frags + ((size_t) s * b.C + c) * b.F;
+    ch.chain_len = b.chain_len[(size_t) s * b.C + c];
+    ch.aux = nullptr;
+    cm_chain_spec(x, ch, b.strands + (size_t) s * b.stride, b.strand_len[s], kind, b.aux[id]);
     stats_flush(x.st, 0u, ctr);
 }

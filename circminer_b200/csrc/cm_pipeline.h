@@ -25,8 +25,9 @@ struct BatchDev {
     float *chain_score;          // [n_strands][C]
     uint32_t *chain_len;         // [n_strands][C]
     FragDev *chain_frags;        // [n_strands][C][F]
-    const uint32_t *chain_base;  // [n_strands + 1] exclusive prefix of chain_cnt (nullptr: no pre-alignment)
-    ChainAux *aux;               // [total chains]
+    const uint32_t *chain_base;  // [n_strands + 1] exclusive prefix of min(chain_cnt, spec_k) (nullptr: no pre-alignment)
+    ChainAux *aux;               // [pre-aligned chains]
+    int spec_k;                  // leading chains of each strand that k_chain_spec pre-aligns
 };
 
 // GenomeSeeder::split_match_hash for one strand (src/match_read.cpp:270-286): fills n_slots (off, cnt)
@@ -54,6 +55,7 @@ CM_HD ChainListView cm_chain_list(const BatchDev &b, uint32_t strand) {
     l.frags = b.chain_frags + (size_t) strand * b.C * b.F;
     l.F = b.F;
     l.aux = (b.aux && b.chain_base) ? b.aux + b.chain_base[strand] : nullptr;
+    l.n_aux = l.count < b.spec_k ? l.count : b.spec_k;
     return l;
 }
 
