@@ -100,7 +100,7 @@ def load_library():
     if not os.path.exists(LIB_PATH):
         raise CmGpuError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'`. "
                          "There is no CPU fallback.")
-    lib = C.CDLL(LIB_PATH)
+    lib = C.CDLL(os.environ.get("CM_GPU_LIB", LIB_PATH))   # CM_GPU_LIB: an alternative build of the same library (A/B runs)
     lib.cm_gpu_last_error.restype = C.c_char_p
     lib.cm_gpu_last_error.argtypes = [C.c_void_p]
     _lib = lib

@@ -65,6 +65,8 @@ struct cm_gpu_ctx {
     DevBuf chain_base, chain_ids, chain_aux;              // compact chain list + pre-alignment results
     uint32_t last_chains = 0;
     bool sync_each = false;    // CM_GPU_SYNC_EACH=1: synchronise after every launch and name the kernel that failed
+    uint32_t heavy_th = 64;    // CM_GPU_HEAVY_TH: strands with more dp cells than this are chained by one warp each (< 255)
+    uint32_t last_heavy = 0;
     int spec_k = CM_MAX_CHAINS;            // CM_GPU_SPEC_K: leading chains per strand handed to the dense pre-alignment kernel
     bool no_spec = false;      // CM_GPU_NO_SPEC=1: every DP inline in the per-pair kernel (debug / A-B)
     DevBuf spec_key[2], spec_item[2];                     // pre-alignment work items, before / after the cost sort
@@ -186,6 +188,7 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
     cudaMemsetAsync(ctx->d_counters, 0, CM_CTR_SLOTS * sizeof(cm_counters), ctx->stream);
     cudaStreamSynchronize(ctx->stream);
     if (const char *e = getenv("CM_GPU_REC_MULT")) ctx->rec_mult = (uint32_t) atoi(e);
+    if (const char *e = getenv("CM_GPU_HEAVY_TH")) { int t = atoi(e); ctx->heavy_th = (uint32_t) (t < 0 ? 0 : (t > 254 ? 254 : t)); }
     if (const char *e = getenv("CM_GPU_SPEC_K")) ctx->spec_k = atoi(e) < 1 ? 1 : atoi(e);
     if (const char *e = getenv("CM_GPU_NO_SPEC")) ctx->no_spec = atoi(e) != 0;
     if (const char *e = getenv("CM_GPU_SYNC_EACH")) ctx->sync_each = atoi(e) != 0;

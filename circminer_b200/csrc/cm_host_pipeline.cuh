@@ -44,27 +44,15 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
     ENSURE(ctx, ctx->cub_tmp, tb + 16);
     cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tb, (const uint32_t *) ctx->cell_cnt.p, (uint64_t *) ctx->cell_off.p, (int) ns, st);
     ctx->launches++;
-    // total cells = off[ns-1] + cnt[ns-1]
-    uint64_t last_off = 0;
-    uint32_t last_cnt = 0;
-    CUDA_TRY(ctx, cudaMemcpyAsync(&last_off, (uint64_t *) ctx->cell_off.p + (ns - 1), 8, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaMemcpyAsync(&last_cnt, (uint32_t *) ctx->cell_cnt.p + (ns - 1), 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
-    const uint64_t cells = last_off + last_cnt;
-    ENSURE(ctx, ctx->dp_score, (size_t) (cells + 1) * 8);
-    ENSURE(ctx, ctx->dp_prev, (size_t) (cells + 1) * 4);
-    const uint32_t mult = ctx->rec_mult;
-    ENSURE(ctx, ctx->recs, (size_t) ((uint64_t) mult * cells + 8ull * ns + 1) * sizeof(ChainRec));
-    ENSURE(ctx, ctx->ovf_strand, (size_t) ns * 4);
-    ENSURE(ctx, ctx->ovf_nrec, (size_t) ns * 4);
-    ENSURE(ctx, ctx->ovf_n, 8);
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->ovf_n.p, 0, 8, st));
-    // strands in work-signature order
+    // strands in work-signature order (heavy first) + the number of heavy ones
     ENSURE(ctx, ctx->key32[0], (size_t) ns * 4);
     ENSURE(ctx, ctx->key32[1], (size_t) ns * 4);
     ENSURE(ctx, ctx->perm[0], (size_t) ns * 4);
     ENSURE(ctx, ctx->perm[1], (size_t) ns * 4);
-    k_strand_key<<<grid_for(ns, 256), 256, 0, st>>>(v, b.seed_cnt, ns, (uint32_t *) ctx->key32[0].p, (uint32_t *) ctx->perm[0].p);
+    ENSURE(ctx, ctx->ovf_n, 8);
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->ovf_n.p, 0, 8, st));   // [0] overflow queue length, [1] heavy strands
+    k_strand_key<<<grid_for(ns, 256), 256, 0, st>>>(v, b.seed_cnt, ns, (uint32_t *) ctx->key32[0].p, (uint32_t *) ctx->perm[0].p,
+                                                    ctx->heavy_th, (uint32_t *) ctx->ovf_n.p + 1);
     {
         size_t tb2 = 0;
         cub::DeviceRadixSort::SortPairs(nullptr, tb2, (const uint32_t *) ctx->key32[0].p, (uint32_t *) ctx->key32[1].p,
@@ -74,11 +62,35 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
                                         (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) ns, 0, 32, st);
     }
     ctx->launches += 2;
+    // total cells = off[ns-1] + cnt[ns-1]
+    uint64_t last_off = 0;
+    uint32_t last_cnt = 0, n_heavy = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&last_off, (uint64_t *) ctx->cell_off.p + (ns - 1), 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&last_cnt, (uint32_t *) ctx->cell_cnt.p + (ns - 1), 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&n_heavy, (uint32_t *) ctx->ovf_n.p + 1, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
     DBG_SYNC(ctx, "k_strand_key + sort");
-    k_chain<<<grid_for(ns, 128), 128, 0, st>>>(v, b, (const uint64_t *) ctx->cell_off.p, (double *) ctx->dp_score.p,
-                                               (uint32_t *) ctx->dp_prev.p, (ChainRec *) ctx->recs.p, mult,
-                                               (uint32_t *) ctx->ovf_strand.p, (uint32_t *) ctx->ovf_nrec.p, (uint32_t *) ctx->ovf_n.p,
-                                               (const uint32_t *) ctx->perm[1].p, ctx->d_counters);
+    ctx->last_heavy = n_heavy;
+    const uint64_t cells = last_off + last_cnt;
+    ENSURE(ctx, ctx->dp_score, (size_t) (cells + 1) * 8);
+    ENSURE(ctx, ctx->dp_prev, (size_t) (cells + 1) * 4);
+    const uint32_t mult = ctx->rec_mult;
+    ENSURE(ctx, ctx->recs, (size_t) ((uint64_t) mult * cells + 8ull * ns + 1) * sizeof(ChainRec));
+    ENSURE(ctx, ctx->ovf_strand, (size_t) ns * 4);
+    ENSURE(ctx, ctx->ovf_nrec, (size_t) ns * 4);
+    if (n_heavy) {
+        k_chain_warp<<<grid_for((size_t) n_heavy * 32, 128), 128, 0, st>>>(v, b, (const uint64_t *) ctx->cell_off.p, (double *) ctx->dp_score.p,
+                                                                          (uint32_t *) ctx->dp_prev.p, (ChainRec *) ctx->recs.p, mult,
+                                                                          (uint32_t *) ctx->ovf_strand.p, (uint32_t *) ctx->ovf_nrec.p,
+                                                                          (uint32_t *) ctx->ovf_n.p, (const uint32_t *) ctx->perm[1].p, n_heavy,
+                                                                          ctx->d_counters);
+        ctx->launches++;
+    }
+    if (ns > n_heavy)
+        k_chain<<<grid_for(ns - n_heavy, 128), 128, 0, st>>>(v, b, (const uint64_t *) ctx->cell_off.p, (double *) ctx->dp_score.p,
+                                                             (uint32_t *) ctx->dp_prev.p, (ChainRec *) ctx->recs.p, mult,
+                                                             (uint32_t *) ctx->ovf_strand.p, (uint32_t *) ctx->ovf_nrec.p, (uint32_t *) ctx->ovf_n.p,
+                                                             (const uint32_t *) ctx->perm[1].p + n_heavy, ns - n_heavy, ctx->d_counters);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     DBG_SYNC(ctx, "k_chain");
@@ -173,7 +185,7 @@ static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) 
                                         (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, 43, st);
         ctx->launches += 2;
         DBG_SYNC(ctx, "k_pair_key + sort");
-        k_process_pe<<<grid_for(n, 128), 128, 0, st>>>(v, b, (const cm_mread *) ctx->in_mread.p, (cm_mread *) ctx->out_mread.p,
+        k_process_pe<<<grid_for(n, CM_PE_BLOCK), CM_PE_BLOCK, 0, st>>>(v, b, (const cm_mread *) ctx->in_mread.p, (cm_mread *) ctx->out_mread.p,
                                                       (int32_t *) ctx->out_state.p, n, (const uint32_t *) ctx->perm[1].p, ctx->d_counters);
     } else {
         k_process_se<<<grid_for(n, 128), 128, 0, ctx->stream>>>(v, b, (int32_t *) ctx->out_state.p, n, ctx->d_counters);

@@ -22,14 +22,23 @@ CM_HD uint32_t cm_rec_cap(uint32_t cells, uint32_t mult) { return mult * cells +
 // K2b: chaining, one thread per strand.  Strands whose improvement list outgrows its slice of the
 // record arena are queued for k_chain_big (exact two-pass sizing) instead of being truncated.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_chain(DevView v, BatchDev b, const uint64_t *__restrict__ cell_off, double *__restrict__ dp_score,
+#ifndef CM_CHAIN_MINB
+#define CM_CHAIN_MINB 1
+#endif
+#ifndef CM_PE_MINB
+#define CM_PE_MINB 1
+#endif
+#ifndef CM_PE_BLOCK
+#define CM_PE_BLOCK 128   // threads per block of the per-pair kernel
+#endif
+__global__ void __launch_bounds__(128, CM_CHAIN_MINB) k_chain(DevView v, BatchDev b, const uint64_t *__restrict__ cell_off, double *__restrict__ dp_score,
                                                uint32_t *__restrict__ dp_prev, ChainRec *__restrict__ recs, uint32_t rec_mult,
                                                uint32_t *__restrict__ ovf_strand, uint32_t *__restrict__ ovf_nrec,
-                                               uint32_t *__restrict__ n_ovf, const uint32_t *__restrict__ order,
+                                               uint32_t *__restrict__ n_ovf, const uint32_t *__restrict__ order, uint32_t n_units,
                                                cm_counters *__restrict__ ctr) {
     uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     uint64_t links = 0;
-    if (slot < b.n_strands) {
+    if (slot < n_units) {
         const uint32_t s = order[slot];   // strands with the same row shape sit in the same warp
         const uint32_t *so = b.seed_off + (size_t) s * v.n_slots, *sc = b.seed_cnt + (size_t) s * v.n_slots;
         uint32_t row_pos_off[CM_MAX_SEEDS], row_cnt[CM_MAX_SEEDS], row_off[CM_MAX_SEEDS], cells;
@@ -37,6 +46,7 @@ __global__ void __launch_bounds__(128) k_chain(DevView v, BatchDev b, const uint
         int T = cm_chain_rows(v, so, sc, row_pos_off, row_cnt, row_off, cells, hh);
         b.chain_hh[s] = hh;
         b.chain_cnt[s] = 0;
+        if ((CM_DBG_FLAGS & 16) && cells > 64) T = 0;   // timing probe: light strands only (results invalid)
         if (T > 0) {
             uint64_t base = cell_off[s];
             uint32_t cap = cm_rec_cap(cells, rec_mult);
@@ -87,6 +97,8 @@ __global__ void __launch_bounds__(128) k_chain_big(DevView v, BatchDev b, const 
     cm_chain_backtrack(v, T, row_pos_off, row_cnt, row_off, dp_score + base, dp_prev + base, r, nrec, out);
 }
 
+#include "cm_chain_warp.cuh"
+
 // ------------------------------------------------------------------------------------------
 // K3: extension + classification, one thread per pair (PE) / read (SE)
 // ------------------------------------------------------------------------------------------
@@ -104,7 +116,7 @@ __device__ __forceinline__ void stats_flush(const AlignStats &st, uint32_t units
     if (units) atomicAdd((unsigned int *) &c->pairs, units);   // low word of the slot; 2^32 units per slot between resets
 }
 
-__global__ void __launch_bounds__(128) k_process_pe(DevView v, BatchDev b, const cm_mread *__restrict__ in, cm_mread *__restrict__ out,
+__global__ void __launch_bounds__(CM_PE_BLOCK, CM_PE_MINB) k_process_pe(DevView v, BatchDev b, const cm_mread *__restrict__ in, cm_mread *__restrict__ out,
                                                     int32_t *__restrict__ state, uint32_t n_pairs, const uint32_t *__restrict__ order,
                                                     cm_counters *__restrict__ ctr) {
     uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
@@ -113,6 +125,8 @@ __global__ void __launch_bounds__(128) k_process_pe(DevView v, BatchDev b, const
     if (live) {
         const uint32_t i = order[slot];   // pairs with the same control-flow signature sit in the same warp
         cm_mread mr = in[i];
+        if ((CM_DBG_FLAGS & 32) && (b.chain_cnt[4 * i] + b.chain_cnt[4 * i + 1] + b.chain_cnt[4 * i + 2] + b.chain_cnt[4 * i + 3] > 4)) state[i] = 0;   // timing probe
+        else
         state[i] = cm_pair_process(v, b, i, mr, st);
         out[i] = mr;
     }
@@ -172,7 +186,7 @@ __global__ void k_align(cm_params p, int kind, uint32_t n, const uint8_t *__rest
 // ------------------------------------------------------------------------------------------
 // strand: heavy first (inverted cell count), then the mask of non-empty rows
 __global__ void k_strand_key(DevView v, const uint32_t *__restrict__ seed_cnt, uint32_t n_strands, uint32_t *__restrict__ key,
-                             uint32_t *__restrict__ idx) {
+                             uint32_t *__restrict__ idx, uint32_t heavy_th, uint32_t *__restrict__ n_heavy) {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_strands) return;
     uint32_t cells = 0, mask = 0;
@@ -185,6 +199,9 @@ __global__ void k_strand_key(DevView v, const uint32_t *__restrict__ seed_cnt, u
     uint32_t cq = cells > 255 ? 255 : cells;
     key[s] = ((255u - cq) << 24) | (mask & 0xFFFFFFu);
     idx[s] = s;
+    // strands with more than heavy_th (< 255) cells sort to the front and go to the warp-per-strand kernel
+    unsigned hm = __ballot_sync(__activemask(), cells > heavy_th);
+    if (hm && (threadIdx.x & 31u) == (unsigned) (__ffs(hm) - 1)) atomicAdd(n_heavy, (uint32_t) __popc(hm));
 }
 
 // pair: chain counts of the four strands, attempt order, and the shape of the leading chains

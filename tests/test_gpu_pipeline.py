@@ -62,6 +62,33 @@ def test_chain_overflow_path_is_exact(w_t0, monkeypatch):
     m.close()
 
 
+@pytest.mark.parametrize("heavy_th", ["0", "3", "254"])
+def test_warp_chaining_is_exact(w_t0, monkeypatch, heavy_th):
+    """CM_GPU_HEAVY_TH: 0 sends every strand with a hit through the warp-per-strand kernel (k_chain_warp), 254
+    nearly none; chains and the per-pair results must not depend on which kernel chained a strand."""
+    from circminer_b200.api import fresh_mreads
+    monkeypatch.setenv("CM_GPU_HEAVY_TH", heavy_th)
+    gold = np.load(os.path.join(GOLDEN, "T0_k20.npz"))
+    m = _mapper(w_t0)
+    mr = fresh_mreads(len(w_t0["s1"]))
+    for c in range(int(gold["n_contigs"])):
+        mr = compare_contig(m, c, w_t0, gold, mr, stages=("chain", "pe"))
+    m.close()
+
+
+def test_warp_chaining_overflow_path(w_t0, monkeypatch):
+    """k_chain_warp with a record slice of 8: overflowing strands are re-run by k_chain_big."""
+    from circminer_b200.api import fresh_mreads
+    monkeypatch.setenv("CM_GPU_HEAVY_TH", "0")
+    monkeypatch.setenv("CM_GPU_REC_MULT", "0")
+    gold = np.load(os.path.join(GOLDEN, "T0_k20.npz"))
+    m = _mapper(w_t0)
+    mr = fresh_mreads(len(w_t0["s1"]))
+    for c in range(int(gold["n_contigs"])):
+        mr = compare_contig(m, c, w_t0, gold, mr, stages=("chain", "pe"))
+    m.close()
+
+
 def test_inline_dp_path_is_exact(w_t0, monkeypatch):
     """CM_GPU_NO_SPEC=1: no pre-alignment memo, every DP runs inline in the per-pair kernel."""
     from circminer_b200.api import fresh_mreads
