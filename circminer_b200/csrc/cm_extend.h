@@ -85,11 +85,30 @@ struct ChainAux {
     EndRes l, r;
 };
 
+// DP results of the transcript walk of one chain end (extend_right / extend_left over every transcript of
+// the end's exon interval), recorded by the dense pre-alignment kernel.  An entry is the value of one DP as
+// a pure function of its inputs (texts, lengths, direction, kind); the per-pair kernel uses it in place of
+// running that DP and otherwise proceeds exactly as if it had computed it.
+struct SpecEntry {
+    uint32_t s_off;          // reference text: offset into ContigDev::genome
+    uint16_t t_off, n, m;    // read text: offset into the strand row; lengths of the two texts
+    uint8_t kind;            // 0 X-drop, 1 X-drop reversed, 2 banded edit, 3 banded edit reversed
+    int8_t ed;
+    int16_t sclen, indel;
+    int32_t score;
+};
+#define CM_SPEC_CAP 4
+struct EndSpec {
+    uint32_t n;
+    SpecEntry e[CM_SPEC_CAP];
+};
+
 // chain view used by the extension: fragment len is always kmer
 struct ChainView {
     const FragDev *frags;
     uint32_t chain_len;
     const ChainAux *aux;   // nullable
+    const EndSpec *spec;   // nullable: [0] left end, [1] right end; valid where aux->has_l / has_r
 };
 
 // common_tid of a MatePair: tids of interval iv_a that also occur in interval iv_b (iv_a < 0: empty)
@@ -126,8 +145,19 @@ CM_HD const uint8_t *cm_pac2char(const DevView &v, uint32_t start, int len) {
 struct ExtCtx {
     const DevView *v;
     AlignStats st;
-    DropHint hint;   // valid only while the end of a chain with ChainAux is being extended
+    DropHint hint;          // valid only while the end of a chain with ChainAux is being extended
+    const EndSpec *seed;    // pre-computed DPs of that end's transcript walk (nullable)
+    EndSpec *capture;       // pre-alignment kernel only: where the walk's DPs are recorded (nullable)
+    const uint8_t *tbase;   // strand row the t_off of seed / capture entries refer to
 };
+CM_HD void ext_ctx_init(ExtCtx &x, const DevView *v) {
+    x.v = v;
+    x.st.xdrop_cells = x.st.edit_cells = x.st.xdrop_calls = x.st.edit_calls = 0;
+    x.hint.valid = 0;
+    x.seed = nullptr;
+    x.capture = nullptr;
+    x.tbase = nullptr;
+}
 
 // The genome-text alignment problem of one chain end as extend_left / extend_right pose it in their
 // "intron retention" step (src/extend.cpp:336, :411) -- and, when the exon reaches far enough, in the
@@ -245,6 +275,51 @@ CM_HDN int cm_calc_middle_ed(ExtCtx &x, const ChainView &ch, int edth, const uin
     return mid_err;
 }
 
+// The two DPs of the transcript walk, behind the seed / capture lists.
+CM_HD const SpecEntry *cm_spec_find(const ExtCtx &x, const uint8_t *s, int n, const uint8_t *t, int m, int kind) {
+    if (!x.seed) return nullptr;
+    const uint32_t so = (uint32_t) (s - x.v->c.genome);
+    const uint16_t to = (uint16_t) (t - x.tbase);
+    const uint32_t cnt = x.seed->n < CM_SPEC_CAP ? x.seed->n : CM_SPEC_CAP;
+    for (uint32_t k = 0; k < cnt; k++) {
+        const SpecEntry &e = x.seed->e[k];
+        if (e.s_off == so && e.t_off == to && e.n == (uint16_t) n && e.m == (uint16_t) m && e.kind == (uint8_t) kind) return &e;
+    }
+    return nullptr;
+}
+CM_HD void cm_spec_put(ExtCtx &x, const uint8_t *s, int n, const uint8_t *t, int m, int kind, int ed, int sclen, int indel, int score) {
+    if (!x.capture || x.capture->n >= CM_SPEC_CAP) return;
+    SpecEntry &e = x.capture->e[x.capture->n++];
+    e.s_off = (uint32_t) (s - x.v->c.genome);
+    e.t_off = (uint16_t) (t - x.tbase);
+    e.n = (uint16_t) n; e.m = (uint16_t) m; e.kind = (uint8_t) kind;
+    e.ed = (int8_t) ed; e.sclen = (int16_t) sclen; e.indel = (int16_t) indel; e.score = score;
+}
+// DropAlignment::local_alignment_{right,left}_sc of reference text s against read text t
+CM_HD int cm_x_drop(ExtCtx &x, const uint8_t *s, int n, const uint8_t *t, int m, bool rev, int &sclen, int &indel, int &score) {
+    const DropHint &h = x.hint;
+    const bool hinted = h.valid && h.s == s && h.t == t && h.n == n && h.m == m && h.rev == (int) rev;
+    if (!hinted) {
+        if (const SpecEntry *e = cm_spec_find(x, s, n, t, m, rev ? 1 : 0)) {
+            sclen = e->sclen; indel = e->indel; score = e->score;
+            return e->ed;
+        }
+    }
+    int ed = cm_drop_alignment_sc(s, n, t, m, rev, x.v->p, sclen, indel, score, &x.st, &x.hint);
+    if (!hinted) cm_spec_put(x, s, n, t, m, rev ? 1 : 0, ed, sclen, indel, score);
+    return ed;
+}
+// Alignment::local_alignment_{right,left} of read text t (first argument of the reference call) against exon text s
+CM_HD int cm_x_local(ExtCtx &x, const uint8_t *t, int m, const uint8_t *s, int n, bool rev, int &indel, int &score) {
+    if (const SpecEntry *e = cm_spec_find(x, s, n, t, m, rev ? 3 : 2)) {
+        indel = e->indel; score = e->score;
+        return e->ed;
+    }
+    int ed = cm_local_alignment(t, m, s, n, rev, x.v->p, indel, score, &x.st);
+    cm_spec_put(x, s, n, t, m, rev ? 3 : 2, ed, 0, indel, score);
+    return ed;
+}
+
 // ---- right side --------------------------------------------------------------------------
 // extend_right_middle (src/extend.cpp:435-461)
 CM_HDN bool cm_extend_right_middle(ExtCtx &x, uint32_t pos, uint32_t exon_len, const uint8_t *qseq, uint32_t qseq_len,
@@ -254,7 +329,7 @@ CM_HDN bool cm_extend_right_middle(ExtCtx &x, uint32_t pos, uint32_t exon_len, c
     if (!ref) return false;
     int indel, score;
     uint32_t seq_remain = exon_len + (uint32_t) p.band_width < qseq_len ? exon_len + (uint32_t) p.band_width : qseq_len;
-    int edit_dist = cm_local_alignment(qseq, (int) seq_remain, ref, (int) exon_len, false, p, indel, score, &x.st);
+    int edit_dist = cm_x_local(x, qseq, (int) seq_remain, ref, (int) exon_len, false, indel, score);
     uint32_t new_rmpos = pos + exon_len;
     ar_set(exon_res, new_rmpos, edit_dist, 0, -indel, (int) exon_len - indel, score);
     if (curr.ed + edit_dist <= ed_th) {
@@ -272,7 +347,7 @@ CM_HDN void cm_extend_right_end(ExtCtx &x, uint32_t pos, uint32_t ref_len, const
     const uint8_t *ref = cm_pac2char(*x.v, pos + 1, (int) ref_len);
     if (!ref) return;
     int sclen, indel, score;
-    int edit_dist = cm_drop_alignment_sc(ref, (int) ref_len, qseq, qseq_len, false, p, sclen, indel, score, &x.st, &x.hint);
+    int edit_dist = cm_x_drop(x, ref, (int) ref_len, qseq, qseq_len, false, sclen, indel, score);
     uint32_t new_rmpos = pos + (uint32_t) qseq_len - (uint32_t) indel;
     ar_set(exon_res, new_rmpos, edit_dist, sclen, indel, qseq_len, score);
     int actual_mapped_bp = qseq_len - sclen;
@@ -443,7 +518,7 @@ CM_HDN bool cm_extend_left_middle(ExtCtx &x, uint32_t pos, uint32_t exon_len, co
     if (!ref) return false;
     int indel, score;
     uint32_t seq_remain = exon_len + (uint32_t) p.band_width < qseq_len ? exon_len + (uint32_t) p.band_width : qseq_len;
-    int edit_dist = cm_local_alignment(qseq, (int) seq_remain, ref, (int) exon_len, true, p, indel, score, &x.st);
+    int edit_dist = cm_x_local(x, qseq, (int) seq_remain, ref, (int) exon_len, true, indel, score);
     uint32_t new_lmpos = pos - exon_len;
     ar_set(exon_res, new_lmpos, edit_dist, 0, -indel, (int) exon_len - indel, score);
     if (curr.ed + edit_dist <= ed_th) {
@@ -461,7 +536,7 @@ CM_HDN void cm_extend_left_end(ExtCtx &x, uint32_t pos, uint32_t ref_len, const 
     const uint8_t *ref = cm_pac2char(*x.v, pos - ref_len, (int) ref_len);
     if (!ref) return;
     int sclen, indel, score;
-    int edit_dist = cm_drop_alignment_sc(ref, (int) ref_len, qseq, qseq_len, true, p, sclen, indel, score, &x.st, &x.hint);
+    int edit_dist = cm_x_drop(x, ref, (int) ref_len, qseq, qseq_len, true, sclen, indel, score);
     uint32_t new_lmpos = pos - (uint32_t) qseq_len + (uint32_t) indel;
     ar_set(exon_res, new_lmpos, edit_dist, sclen, indel, qseq_len, score);
     int actual_mapped_bp = qseq_len - sclen;
@@ -619,8 +694,10 @@ CM_HDN bool cm_extend_chain_right(ExtCtx &x, TidSet ts, const ChainView &ch, con
     AlignResD best = ar_init(ub);
     if (remain_end > 0) {
         cm_set_hint(x, ch, seq, seq_len, true);
+        if (x.hint.valid && ch.spec) { x.seed = ch.spec + 1; x.tbase = seq; }
         right_ok = cm_extend_right(x, ts, seq + seq_len - remain_end, rm_pos, remain_end, p.max_ed - err, ub, best);
         x.hint.valid = 0;
+        x.seed = nullptr;
     }
     int sclen_right = best.sclen;
     int err_right = best.ed;
@@ -644,8 +721,10 @@ CM_HDN bool cm_extend_chain_left(ExtCtx &x, TidSet ts, const ChainView &ch, cons
     AlignResD best = ar_init(lb);
     if (remain_beg > 0) {
         if (qspos == 0) cm_set_hint(x, ch, seq, 0, false);
+        if (x.hint.valid && ch.spec) { x.seed = ch.spec; x.tbase = seq; }
         left_ok = cm_extend_left(x, ts, seq, lm_pos, remain_beg, p.max_ed - err, lb, best);
         x.hint.valid = 0;
+        x.seed = nullptr;
     }
     int sclen_left = best.sclen;
     int err_left = best.ed;
@@ -764,14 +843,17 @@ CM_HDN int cm_extend_chain_both_sides(ExtCtx &x, const ChainView &ch, const uint
 // ---- dense pre-alignment -------------------------------------------------------------------
 // kind 0: calc_middle_ed(ch, maxEd); kind 1 / 2: the genome-text X-drop of the left / right read end.
 // Each kind writes its own fields of ChainAux, so the three may run in different threads.
-CM_HDN void cm_chain_spec(ExtCtx &x, const ChainView &ch, const uint8_t *seq, int seq_len, int kind, ChainAux &aux) {
+// For an end with something to align, kinds 1 / 2 return true when the end's transcript walk may pose further DPs
+// (cm_chain_walk records those); spec[0] / spec[1] is emptied either way.
+CM_HDN bool cm_chain_spec(ExtCtx &x, const ChainView &ch, const uint8_t *seq, int seq_len, int kind, ChainAux &aux, EndSpec *spec) {
     const cm_params &p = x.v->p;
     if (kind == 0) {
         ChainView c = ch;
         c.aux = nullptr;
+        c.spec = nullptr;
         aux.mid_ed = cm_calc_middle_ed(x, c, p.max_ed, seq, seq_len);
         aux.has_mid = 1;
-        return;
+        return false;
     }
     const bool right = kind == 2;
     const uint8_t *s, *t;
@@ -779,9 +861,49 @@ CM_HDN void cm_chain_spec(ExtCtx &x, const ChainView &ch, const uint8_t *seq, in
     EndRes r;
     r.ed = r.sclen = r.indel = r.score = 0;
     uint8_t has = 0;
+    bool walk = false;
     if (cm_end_problem(*x.v, ch, seq, seq_len, right, s, n, t, m)) {
         r.ed = cm_drop_alignment_sc(s, n, t, m, !right, p, r.sclen, r.indel, r.score, &x.st, nullptr);
         has = 1;
+        if (spec) {
+            spec[right ? 1 : 0].n = 0;
+            uint32_t pos = right ? ch.frags[ch.chain_len - 1].rpos + (uint32_t) p.kmer - 1 : ch.frags[0].rpos;
+            int ind;
+            const int iv = cm_location_overlap_ind(x.v->a, pos, ind);
+            // When the exon piece under the end holds m + w more bases, every transcript's walk stops at once and poses the
+            // genome-text problem solved above (extend_*_trans: "exon_len >= qseq_len" break, remain_ref_len == ref_len).
+            walk = iv >= 0 && (right ? (int) (x.v->a.iv_epos[iv] - pos) : (int) (pos - x.v->a.iv_spos[iv])) < m + p.band_width;
+        }
     }
     if (right) { aux.r = r; aux.has_r = has; } else { aux.l = r; aux.has_l = has; }
+    return walk;
+}
+
+// The transcript walk of one chain end: extend_left / extend_right over every transcript of the end's exon interval
+// with the most permissive thresholds, recording the DPs met on the way in spec[0] (left) / spec[1] (right).
+CM_HDN void cm_chain_walk(ExtCtx &x, const ChainView &ch, const uint8_t *seq, int seq_len, bool right, const ChainAux &aux, EndSpec *spec) {
+    const cm_params &p = x.v->p;
+    const uint8_t *s, *t;
+    int n, m;
+    if (!spec || !(right ? aux.has_r : aux.has_l) || !cm_end_problem(*x.v, ch, seq, seq_len, right, s, n, t, m)) return;
+    EndSpec &out = spec[right ? 1 : 0];
+    uint32_t pos = right ? ch.frags[ch.chain_len - 1].rpos + (uint32_t) p.kmer - 1 : ch.frags[0].rpos;
+    int ind;
+    const int iv = cm_location_overlap_ind(x.v->a, pos, ind);
+    if (iv < 0) return;
+    const EndRes &r = right ? aux.r : aux.l;
+    x.hint.s = s; x.hint.t = t; x.hint.n = n; x.hint.m = m; x.hint.rev = right ? 0 : 1;
+    x.hint.ed = r.ed; x.hint.sclen = r.sclen; x.hint.indel = r.indel; x.hint.score = r.score;
+    x.hint.valid = 1;
+    x.seed = nullptr;
+    x.capture = &out;
+    x.tbase = seq;
+    TidSet ts;
+    ts.iv_a = iv;
+    ts.iv_b = iv;
+    AlignResD best;
+    if (right) cm_extend_right(x, ts, seq + seq_len - m, pos, m, p.max_ed, CM_MAXUB, best);
+    else cm_extend_left(x, ts, seq, pos, m, p.max_ed, CM_MINLB, best);
+    x.capture = nullptr;
+    x.hint.valid = 0;
 }

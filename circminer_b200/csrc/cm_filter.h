@@ -16,6 +16,7 @@ struct ChainListView {
     const FragDev *frags;      // [C][F]
     int F;
     const ChainAux *aux;       // [n_aux] or nullptr: pre-alignment results of the first n_aux chains
+    const EndSpec *spec;       // [n_aux][2] or nullptr: transcript-walk DPs of the two ends
     int n_aux;
 };
 CM_HD ChainView cl_chain(const ChainListView &l, int i) {
@@ -23,6 +24,7 @@ CM_HD ChainView cl_chain(const ChainListView &l, int i) {
     c.frags = l.frags + (size_t) i * l.F;
     c.chain_len = l.len[i];
     c.aux = (l.aux && i < l.n_aux) ? l.aux + i : nullptr;
+    c.spec = (c.aux && l.spec) ? l.spec + 2 * (size_t) i : nullptr;
     return c;
 }
 

@@ -40,6 +40,8 @@ struct cm_gpu_ctx {
     cudaEvent_t ev[6]{};
     std::string err;
     std::vector<ContigHost> contigs;
+    cudaStream_t stream2 = nullptr;   // side stream: kernels that run beside the main one (heavy strands)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cm_counters *d_counters = nullptr;
     uint64_t launches = 0;
     float stage_ms[5] = {0, 0, 0, 0, 0};
@@ -62,12 +64,14 @@ struct cm_gpu_ctx {
     uint32_t last_overflow = 0;
     DevBuf out_mread, out_state;
     DevBuf cub_tmp;
+    DevBuf chain_spec;                                    // transcript-walk DPs of every pre-aligned chain end
     DevBuf chain_base, chain_ids, chain_aux;              // compact chain list + pre-alignment results
     uint32_t last_chains = 0;
     bool sync_each = false;    // CM_GPU_SYNC_EACH=1: synchronise after every launch and name the kernel that failed
     uint32_t heavy_th = 64;    // CM_GPU_HEAVY_TH: strands with more dp cells than this are chained by one warp each (< 255)
     uint32_t last_heavy = 0;
     int spec_k = CM_MAX_CHAINS;            // CM_GPU_SPEC_K: leading chains per strand handed to the dense pre-alignment kernel
+    bool no_walk_spec = false; // CM_GPU_NO_WALK_SPEC=1: pre-align the genome-text ends only (A-B)
     bool no_spec = false;      // CM_GPU_NO_SPEC=1: every DP inline in the per-pair kernel (debug / A-B)
     DevBuf spec_key[2], spec_item[2];                     // pre-alignment work items, before / after the cost sort
     DevBuf key32[2], key64[2], perm[2];                   // work-signature sort of strands / pairs
@@ -176,6 +180,9 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
         return fail(nullptr, CM_ERR_CUDA, "cannot initialise device %d", device);
     }
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming);
     {   // the index gathers are 32-byte random reads: ask L2 not to promote misses to 64/128-byte DRAM fetches
         size_t g = 32;
         if (const char *e = getenv("CM_GPU_L2_FETCH")) g = (size_t) atoi(e);
@@ -190,6 +197,7 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
     if (const char *e = getenv("CM_GPU_REC_MULT")) ctx->rec_mult = (uint32_t) atoi(e);
     if (const char *e = getenv("CM_GPU_HEAVY_TH")) { int t = atoi(e); ctx->heavy_th = (uint32_t) (t < 0 ? 0 : (t > 254 ? 254 : t)); }
     if (const char *e = getenv("CM_GPU_SPEC_K")) ctx->spec_k = atoi(e) < 1 ? 1 : atoi(e);
+    if (const char *e = getenv("CM_GPU_NO_WALK_SPEC")) ctx->no_walk_spec = atoi(e) != 0;
     if (const char *e = getenv("CM_GPU_NO_SPEC")) ctx->no_spec = atoi(e) != 0;
     if (const char *e = getenv("CM_GPU_SYNC_EACH")) ctx->sync_each = atoi(e) != 0;
     if (const char *e = getenv("CM_GPU_DBG")) {
@@ -218,11 +226,14 @@ extern "C" int cm_gpu_destroy(cm_gpu_ctx *ctx) {
                       &ctx->chain_frags, &ctx->out_mread, &ctx->out_state, &ctx->cub_tmp};
     for (DevBuf *b : bufs) release(*b);
     for (auto &b : ctx->scratch) release(b);
-    release(ctx->chain_base); release(ctx->chain_ids); release(ctx->chain_aux);
+    release(ctx->chain_spec); release(ctx->chain_base); release(ctx->chain_ids); release(ctx->chain_aux);
     for (int q = 0; q < 2; q++) { release(ctx->spec_key[q]); release(ctx->spec_item[q]); }
     for (int q = 0; q < 2; q++) { release(ctx->key32[q]); release(ctx->key64[q]); release(ctx->perm[q]); }
     cudaFree(ctx->d_counters);
     for (auto &ev : ctx->ev) cudaEventDestroy(ev);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return CM_OK;

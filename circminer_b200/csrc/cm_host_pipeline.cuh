@@ -26,6 +26,7 @@ static int make_batch(cm_gpu_ctx *ctx, BatchDev &b) {
     b.chain_frags = (FragDev *) ctx->chain_frags.p;
     b.chain_base = nullptr;
     b.aux = nullptr;
+    b.spec = nullptr;
     b.spec_k = 0;
     return CM_OK;
 }
@@ -79,11 +80,15 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
     ENSURE(ctx, ctx->ovf_strand, (size_t) ns * 4);
     ENSURE(ctx, ctx->ovf_nrec, (size_t) ns * 4);
     if (n_heavy) {
-        k_chain_warp<<<grid_for((size_t) n_heavy * 32, 128), 128, 0, st>>>(v, b, (const uint64_t *) ctx->cell_off.p, (double *) ctx->dp_score.p,
+        // heavy and light strands are independent: the warp kernel runs beside k_chain on a second stream
+        cudaEventRecord(ctx->ev_fork, st);
+        cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0);
+        k_chain_warp<<<grid_for((size_t) n_heavy * 32, 128), 128, 0, ctx->stream2>>>(v, b, (const uint64_t *) ctx->cell_off.p, (double *) ctx->dp_score.p,
                                                                           (uint32_t *) ctx->dp_prev.p, (ChainRec *) ctx->recs.p, mult,
                                                                           (uint32_t *) ctx->ovf_strand.p, (uint32_t *) ctx->ovf_nrec.p,
                                                                           (uint32_t *) ctx->ovf_n.p, (const uint32_t *) ctx->perm[1].p, n_heavy,
                                                                           ctx->d_counters);
+        cudaEventRecord(ctx->ev_join, ctx->stream2);
         ctx->launches++;
     }
     if (ns > n_heavy)
@@ -92,6 +97,7 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
                                                              (uint32_t *) ctx->ovf_strand.p, (uint32_t *) ctx->ovf_nrec.p, (uint32_t *) ctx->ovf_n.p,
                                                              (const uint32_t *) ctx->perm[1].p + n_heavy, ns - n_heavy, ctx->d_counters);
     ctx->launches++;
+    if (n_heavy) cudaStreamWaitEvent(st, ctx->ev_join, 0);
     CUDA_TRY(ctx, cudaGetLastError());
     DBG_SYNC(ctx, "k_chain");
     uint32_t n_ovf = 0;
@@ -139,6 +145,10 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
         ENSURE(ctx, ctx->chain_ids, (size_t) n_chains * 4);
         ENSURE(ctx, ctx->chain_aux, (size_t) n_chains * sizeof(ChainAux));
         b.aux = (ChainAux *) ctx->chain_aux.p;
+        if (!ctx->no_walk_spec) {
+            ENSURE(ctx, ctx->chain_spec, (size_t) n_chains * 2 * sizeof(EndSpec));
+            b.spec = (EndSpec *) ctx->chain_spec.p;
+        }
         CUDA_TRY(ctx, cudaMemsetAsync(ctx->chain_aux.p, 0, (size_t) n_chains * sizeof(ChainAux), st));
         const size_t n_items = 3ull * n_chains;
         ENSURE(ctx, ctx->spec_key[0], n_items);
@@ -156,8 +166,15 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
             cub::DeviceRadixSort::SortPairsDescending(ctx->cub_tmp.p, tb4, (const uint8_t *) ctx->spec_key[0].p, (uint8_t *) ctx->spec_key[1].p,
                                                       (const uint32_t *) ctx->spec_item[0].p, (uint32_t *) ctx->spec_item[1].p, (int) n_items, 0, 8, st);
         }
+        // spec_item[0] is free again after the sort: it becomes the walk queue (at most 2 ends per chain)
+        uint32_t *walk_q = (uint32_t *) ctx->spec_item[0].p, *n_walk = (uint32_t *) ctx->ovf_n.p + 1;
+        CUDA_TRY(ctx, cudaMemsetAsync(n_walk, 0, 4, st));
         k_chain_spec<<<grid_for(n_items, 128), 128, 0, st>>>(v, b, (const uint32_t *) ctx->chain_ids.p, (const uint8_t *) ctx->spec_key[1].p,
-                                                            (const uint32_t *) ctx->spec_item[1].p, n_chains, ctx->d_counters);
+                                                            (const uint32_t *) ctx->spec_item[1].p, n_chains, walk_q, n_walk, ctx->d_counters);
+        if (b.spec) {
+            k_chain_walk<<<grid_for(2ull * n_chains, 128), 128, 0, st>>>(v, b, (const uint32_t *) ctx->chain_ids.p, walk_q, n_walk, ctx->d_counters);
+            ctx->launches++;
+        }
         ctx->launches += 4;
         CUDA_TRY(ctx, cudaGetLastError());
         DBG_SYNC(ctx, "k_chain_spec");

@@ -289,12 +289,11 @@ __global__ void k_chain_ids(BatchDev b, uint32_t *__restrict__ list) {
 }
 
 __global__ void __launch_bounds__(128) k_chain_spec(DevView v, BatchDev b, const uint32_t *__restrict__ list, const uint8_t *__restrict__ key,
-                                                    const uint32_t *__restrict__ item, uint32_t n_chains, cm_counters *__restrict__ ctr) {
+                                                    const uint32_t *__restrict__ item, uint32_t n_chains, uint32_t *__restrict__ walk_q,
+                                                    uint32_t *__restrict__ n_walk, cm_counters *__restrict__ ctr) {
     uint64_t gid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
     ExtCtx x;
-    x.v = &v;
-    x.st.xdrop_cells = x.st.edit_cells = x.st.xdrop_calls = x.st.edit_calls = 0;
-    x.hint.valid = 0;
+    ext_ctx_init(x, &v);
     if (gid >= 3ull * n_chains || key[gid] == 0) return;
     const uint32_t it = item[gid];
     const int kind = (int) (it >> 30);
@@ -304,6 +303,36 @@ __global__ void __launch_bounds__(128) k_chain_spec(DevView v, BatchDev b, const
     ch.frags = b.chain_frags + ((size_t) s * b.C + c) * b.F;
     ch.chain_len = b.chain_len[(size_t) s * b.C + c];
     ch.aux = nullptr;
-    cm_chain_spec(x, ch, b.strands + (size_t) s * b.stride, b.strand_len[s], kind, b.aux[id]);
+    ch.spec = nullptr;
+    const bool walk = cm_chain_spec(x, ch, b.strands + (size_t) s * b.stride, b.strand_len[s], kind, b.aux[id],
+                                    b.spec ? b.spec + 2 * (size_t) id : nullptr);
+    if (walk) {   // queue the end for k_chain_walk; the lanes that are here together share one atomic
+        const unsigned act = __activemask(), lane = threadIdx.x & 31u;
+        const int leader = __ffs(act) - 1;
+        uint32_t base = 0;
+        if ((int) lane == leader) base = atomicAdd(n_walk, (uint32_t) __popc(act));
+        base = __shfl_sync(act, base, leader);
+        walk_q[base + __popc(act & ((1u << lane) - 1u))] = it;
+    }
+    stats_flush(x.st, 0u, ctr);
+}
+
+// transcript walks of the queued chain ends (roughly in the cost order k_chain_spec met them)
+__global__ void __launch_bounds__(128) k_chain_walk(DevView v, BatchDev b, const uint32_t *__restrict__ list, const uint32_t *__restrict__ walk_q,
+                                                    const uint32_t *__restrict__ n_walk, cm_counters *__restrict__ ctr) {
+    uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= *n_walk) return;
+    ExtCtx x;
+    ext_ctx_init(x, &v);
+    const uint32_t it = walk_q[gid];
+    const int kind = (int) (it >> 30);
+    const uint32_t id = it & 0x3FFFFFFFu;
+    uint32_t e = list[id], s = e >> 5, c = e & 31u;
+    ChainView ch;
+    ch.frags = b.chain_frags + ((size_t) s * b.C + c) * b.F;
+    ch.chain_len = b.chain_len[(size_t) s * b.C + c];
+    ch.aux = nullptr;
+    ch.spec = nullptr;
+    cm_chain_walk(x, ch, b.strands + (size_t) s * b.stride, b.strand_len[s], kind == 2, b.aux[id], b.spec + 2 * (size_t) id);
     stats_flush(x.st, 0u, ctr);
 }

@@ -27,6 +27,7 @@ struct BatchDev {
     FragDev *chain_frags;        // [n_strands][C][F]
     const uint32_t *chain_base;  // [n_strands + 1] exclusive prefix of min(chain_cnt, spec_k) (nullptr: no pre-alignment)
     ChainAux *aux;               // [pre-aligned chains]
+    EndSpec *spec;               // [pre-aligned chains][2] transcript-walk DPs (nullptr: none)
     int spec_k;                  // leading chains of each strand that k_chain_spec pre-aligns
 };
 
@@ -55,6 +56,7 @@ CM_HD ChainListView cm_chain_list(const BatchDev &b, uint32_t strand) {
     l.frags = b.chain_frags + (size_t) strand * b.C * b.F;
     l.F = b.F;
     l.aux = (b.aux && b.chain_base) ? b.aux + b.chain_base[strand] : nullptr;
+    l.spec = (l.aux && b.spec) ? b.spec + 2 * (size_t) b.chain_base[strand] : nullptr;
     l.n_aux = l.count < b.spec_k ? l.count : b.spec_k;
     return l;
 }
@@ -70,9 +72,7 @@ CM_HD StrandView cm_strand_view(const BatchDev &b, uint32_t strand) {
 // FilterRead::process_read (PE) for pair i of the batch
 CM_HD int cm_pair_process(const DevView &v, const BatchDev &b, uint32_t pair, cm_mread &mr, AlignStats &st) {
     FilterCtx f;
-    f.x.v = &v;
-    f.x.st.xdrop_cells = f.x.st.edit_cells = f.x.st.xdrop_calls = f.x.st.edit_calls = 0;
-    f.x.hint.valid = 0;
+    ext_ctx_init(f.x, &v);
     f.contig_id = v.contig_id;
     PairView pv;
     for (int k = 0; k < 4; k++) {
@@ -87,9 +87,7 @@ CM_HD int cm_pair_process(const DevView &v, const BatchDev &b, uint32_t pair, cm
 // SE overload for read i
 CM_HD int cm_read_process_se(const DevView &v, const BatchDev &b, uint32_t read, AlignStats &st) {
     FilterCtx f;
-    f.x.v = &v;
-    f.x.st.xdrop_cells = f.x.st.edit_cells = f.x.st.xdrop_calls = f.x.st.edit_calls = 0;
-    f.x.hint.valid = 0;
+    ext_ctx_init(f.x, &v);
     f.contig_id = v.contig_id;
     StrandView fw = cm_strand_view(b, 2 * read), bw = cm_strand_view(b, 2 * read + 1);
     int r = cm_process_read_se(f, fw, bw);

@@ -140,6 +140,7 @@ struct HsBatch {
     std::vector<FragDev> chain_frags;
     std::vector<uint32_t> chain_base;
     std::vector<ChainAux> aux;
+    std::vector<EndSpec> spec;
     BatchDev b{};
 };
 
@@ -201,25 +202,30 @@ static void build_batch(HsCtx *c, const DevView &v, HsBatch &B, uint32_t n_reads
     // dense pre-alignment of every chain (k_chain_spec on the device); HS_NO_SPEC=1 keeps every DP inline
     b.chain_base = nullptr;
     b.aux = nullptr;
+    b.spec = nullptr;
     b.spec_k = getenv("HS_SPEC_K") ? atoi(getenv("HS_SPEC_K")) : CM_MAX_CHAINS;
     if (!getenv("HS_NO_SPEC")) {
         B.chain_base.assign(ns + 1, 0);
         for (uint32_t s = 0; s < ns; s++) B.chain_base[s + 1] = B.chain_base[s] + (uint32_t) (B.chain_cnt[s] < b.spec_k ? B.chain_cnt[s] : b.spec_k);
         B.aux.assign(B.chain_base[ns] + 1, ChainAux{});
+        B.spec.assign(2 * (size_t) B.chain_base[ns] + 2, EndSpec{});
+        const bool walk = !getenv("HS_NO_WALK_SPEC");
         ExtCtx x;
-        x.v = &v;
-        x.st = AlignStats{0, 0, 0, 0};
-        x.hint.valid = 0;
+        ext_ctx_init(x, &v);
         for (uint32_t s = 0; s < ns; s++) {
             ChainListView l = cm_chain_list(b, s);
             for (int k = 0; k < l.count && k < b.spec_k; k++) {
                 ChainView ch = cl_chain(l, k);
+                EndSpec *sp = walk ? &B.spec[2 * (size_t) (B.chain_base[s] + k)] : nullptr;
+                ChainAux &ax = B.aux[B.chain_base[s] + k];
                 for (int kind = 0; kind < 3; kind++)
-                    cm_chain_spec(x, ch, b.strands + (size_t) s * stride, B.slen[s], kind, B.aux[B.chain_base[s] + k]);
+                    if (cm_chain_spec(x, ch, b.strands + (size_t) s * stride, B.slen[s], kind, ax, sp))
+                        cm_chain_walk(x, ch, b.strands + (size_t) s * stride, B.slen[s], kind == 2, ax, sp);
             }
         }
         b.chain_base = B.chain_base.data();
         b.aux = B.aux.data();
+        b.spec = walk ? B.spec.data() : nullptr;
     }
 }
 
