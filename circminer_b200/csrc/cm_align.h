@@ -14,15 +14,6 @@
 #include "cm_types.h"
 
 #define CM_BANDSZ (2 * CM_MAX_BAND + 3)
-// debug switches (CM_GPU_DBG on the device build): bit 0 generic X-drop, bit 1 ignore hints, bit 2 no counters
-#if defined(__CUDACC__)
-__device__ int g_cm_dbg_flags = 0;
-#endif
-#if defined(__CUDA_ARCH__)
-#define CM_DBG_FLAGS g_cm_dbg_flags
-#else
-#define CM_DBG_FLAGS 0
-#endif
 #define CM_FULLDP_MAX 64   // largest s-length the full-DP fallback accepts (reference needs <= 2w)
 
 // score_ch / diff_ch: equal iff both in "ACGTacgt" and equal ignoring case; N never matches

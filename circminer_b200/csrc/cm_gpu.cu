@@ -275,6 +275,9 @@ static ContigHost *get_contig(cm_gpu_ctx *ctx, int contig_id, bool create) {
     return &ctx->contigs[contig_id];
 }
 
+struct ContigHost;
+static int build_dirx(cm_gpu_ctx *ctx, ContigHost *ch);
+
 template <typename T>
 static int dev_alloc(cm_gpu_ctx *ctx, std::vector<void *> &owned, T **out, size_t count) {
     void *p = nullptr;
@@ -369,6 +372,7 @@ extern "C" int cm_gpu_load_contig(cm_gpu_ctx *ctx, int contig_id, const void *co
     ch->d.genome = genome;
     ch->d.n_entries = total;
     ch->d.ref_len = ref_gen_len;
+    if ((r = build_dirx(ctx, ch)) != CM_OK) return r;
     ch->loaded = true;
     return CM_OK;
 }
@@ -500,6 +504,7 @@ extern "C" int cm_gpu_build_contig(cm_gpu_ctx *ctx, int contig_id, const char *c
     ch->d.genome = genome;
     ch->d.n_entries = nsel;
     ch->d.ref_len = len;
+    if ((r = build_dirx(ctx, ch)) != CM_OK) return r;
     ch->loaded = true;
     return CM_OK;
 }
@@ -566,6 +571,30 @@ extern "C" int cm_gpu_load_annotation(cm_gpu_ctx *ctx, int contig_id, const cm_a
     UP(near_border, (A->n_bits + 63) / 64) UP(intronic, (A->n_bits + 63) / 64)
 #undef UP
     ch->has_annot = true;
+    return CM_OK;
+}
+
+// fused directory: one thread per bucket
+__global__ void k_build_dirx(const uint32_t *__restrict__ dir, const uint16_t *__restrict__ cks, DirX *__restrict__ dirx) {
+    uint32_t hv = blockIdx.x * blockDim.x + threadIdx.x;
+    if (hv >= CM_NBUCKETS) return;
+    uint32_t lo = dir[hv], hi = dir[hv + 1];
+    DirX e;
+    e.off = lo;
+    e.cnt = hi - lo;
+    for (uint32_t k = 0; k < CM_DIRX_INLINE; k++) e.c[k] = lo + k < hi ? cks[lo + k] : (uint16_t) 0xFFFFu;
+    dirx[hv] = e;
+}
+static int build_dirx(cm_gpu_ctx *ctx, ContigHost *ch) {
+    if (getenv("CM_GPU_NO_DIRX")) { ch->d.dirx = nullptr; return CM_OK; }
+    DirX *dx = nullptr;
+    int r = dev_alloc(ctx, ch->owned, &dx, (size_t) CM_NBUCKETS);
+    if (r != CM_OK) return r;
+    k_build_dirx<<<grid_for(CM_NBUCKETS, 256), 256, 0, ctx->stream>>>(ch->d.dir, ch->d.cks, dx);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ch->d.dirx = dx;
     return CM_OK;
 }
 
@@ -688,7 +717,7 @@ __global__ void __launch_bounds__(256) k_seed(DevView v, const int2 *__restrict_
         h.off = 0;
         h.cnt = 0;
         if (key.x != -2) {
-            h = cm_seed_lookup(v.c, key.x, key.y, &sectors);
+            h = v.c.dirx ? cm_seed_lookup_x(v.c, key.x, key.y, &sectors) : cm_seed_lookup(v.c, key.x, key.y, &sectors);
             looked = 1;
             uint32_t kept = h.cnt > (uint32_t) v.p.seed_lim ? 0 : h.cnt;
             hits = kept;
