@@ -182,10 +182,8 @@ def run_b200(a):
     barrier()
     e2e_ms = (time.time() - t0) * 1e3
 
-    t = torch.tensor([dev_ms, wall_ms, e2e_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, wall_ms, e2e_ms = [float(x) for x in t.tolist()]
+    from circminer_b200 import sharding
+    dev_ms, wall_ms, e2e_ms = sharding.max_over_ranks([dev_ms, wall_ms, e2e_ms], world, dist=dist, device="cuda")
     reads_total = 2.0 * n * world * a.steps
 
     if rank == 0:
