@@ -1,0 +1,249 @@
+// The reference-side binding of libcm_gpu.so: a batched replacement of map_reads (src/circminer.cpp:354-406).
+// Compiled against the reference's own headers and linked with its unmodified objects (oracle/Makefile target
+// `gpu`): the reference keeps reading FASTQ, keeping the per-round MatchedRead state in the read headers and
+// writing mapping.pam / *_remain_R?.fastq; only FilterRead::process_read is replaced, N pairs at a time, by
+// cm_gpu_process_batch_pe.  This file is what INTEGRATION.md describes, in working form.
+#define private public
+#define protected public
+#include "common.h"
+#include "filter.h"
+#include "fastq_parser.h"
+#include "gene_annotation.h"
+#include "match_read.h"
+#undef private
+#undef protected
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../include/cm_gpu.h"
+
+extern "C" {
+#include "mrsfast/Common.h"
+#include "mrsfast/HashTable.h"
+extern IHashTable *_ih_hashTable;
+extern GeneralIndex *_ih_hashTableMem;
+extern CompressedSeq *_ih_crefGen;
+extern int _ih_refGenLen;
+extern int _ih_maxHashTableSize;
+}
+extern pthread_mutex_t buffer_lock;
+
+namespace {
+
+cm_gpu_ctx *g_ctx = nullptr;
+std::vector<std::string> g_chr;   // chromosome names <-> cm_mread::chr_r1 / chr_r2 indices
+int g_loaded_contig = -1;
+
+[[noreturn]] void die(const char *what) {
+    fprintf(stderr, "circminer_gpu: %s: %s\n", what, cm_gpu_last_error(g_ctx));
+    exit(1);
+}
+
+int chr_index(const std::string &name) {
+    if (name == "-") return -1;
+    for (size_t j = 0; j < g_chr.size(); j++)
+        if (g_chr[j] == name) return (int) j;
+    g_chr.push_back(name);
+    return (int) g_chr.size() - 1;
+}
+
+void to_pod(const MatchedRead *r, cm_mread *m) {
+    memset(m, 0, sizeof *m);
+    m->spos_r1 = r->spos_r1; m->spos_r2 = r->spos_r2; m->epos_r1 = r->epos_r1; m->epos_r2 = r->epos_r2;
+    m->qspos_r1 = r->qspos_r1; m->qspos_r2 = r->qspos_r2; m->qepos_r1 = r->qepos_r1; m->qepos_r2 = r->qepos_r2;
+    m->mlen_r1 = r->mlen_r1; m->mlen_r2 = r->mlen_r2;
+    m->r1_forward = r->r1_forward; m->r2_forward = r->r2_forward;
+    m->ed_r1 = r->ed_r1; m->ed_r2 = r->ed_r2; m->type = r->type; m->tlen = r->tlen;
+    m->junc_num = r->junc_num; m->gm_compatible = r->gm_compatible; m->contig_num = r->contig_num;
+    m->chr_r1 = chr_index(r->chr_r1);
+    m->chr_r2 = chr_index(r->chr_r2);
+}
+
+void from_pod(const cm_mread *m, MatchedRead *r) {
+    r->spos_r1 = m->spos_r1; r->spos_r2 = m->spos_r2; r->epos_r1 = m->epos_r1; r->epos_r2 = m->epos_r2;
+    r->qspos_r1 = m->qspos_r1; r->qspos_r2 = m->qspos_r2; r->qepos_r1 = m->qepos_r1; r->qepos_r2 = m->qepos_r2;
+    r->mlen_r1 = m->mlen_r1; r->mlen_r2 = m->mlen_r2;
+    r->r1_forward = m->r1_forward; r->r2_forward = m->r2_forward;
+    r->ed_r1 = m->ed_r1; r->ed_r2 = m->ed_r2; r->type = m->type; r->tlen = m->tlen;
+    r->junc_num = m->junc_num; r->gm_compatible = m->gm_compatible; r->contig_num = m->contig_num;
+    r->chr_r1 = m->chr_r1 >= 0 ? g_chr[m->chr_r1] : std::string("-");
+    r->chr_r2 = m->chr_r2 >= 0 ? g_chr[m->chr_r2] : std::string("-");
+}
+
+// GTFParser tables of the current contig as the flat arrays of cm_annot_flat
+void upload_annotation(int c) {
+    FlatIntervalTree<UniqSeg> &T = gtf_parser.exons_int_map[c];
+    const size_t n_iv = T.disjoint_intervals.size();
+    std::vector<uint32_t> iv_spos(n_iv), iv_epos(n_iv), iv_max_end(n_iv), iv_min_end(n_iv), iv_next(n_iv), iv_seg_off(n_iv + 1);
+    std::vector<uint32_t> seg_start, seg_end, seg_next, seg_gene, seg_tid_off, tid;
+    for (size_t i = 0; i < n_iv; i++) {
+        auto &iv = T.disjoint_intervals[i];
+        iv_spos[i] = iv.spos; iv_epos[i] = iv.epos; iv_max_end[i] = iv.max_end; iv_min_end[i] = iv.min_end;
+        iv_next[i] = iv.max_next_exon;
+        iv_seg_off[i] = (uint32_t) seg_start.size();
+        for (auto &s : iv.seg_list) {
+            seg_start.push_back(s.start); seg_end.push_back(s.end); seg_next.push_back(s.next_exon_beg);
+            seg_gene.push_back(s.gene_id);
+            seg_tid_off.push_back((uint32_t) tid.size());
+            for (auto t : s.trans_id) tid.push_back(t);
+        }
+    }
+    iv_seg_off[n_iv] = (uint32_t) seg_start.size();
+    seg_tid_off.push_back((uint32_t) tid.size());
+    const size_t ntr = (size_t) c < gtf_parser.trans2seg.size() ? gtf_parser.trans2seg[c].size() : 0;
+    std::vector<int32_t> trans_start(ntr);
+    std::vector<uint32_t> t2s_off(ntr + 1);
+    std::vector<uint8_t> t2s;
+    for (size_t i = 0; i < ntr; i++) {
+        trans_start[i] = gtf_parser.trans_start_ind[c][i];
+        t2s_off[i] = (uint32_t) t2s.size();
+        for (auto v : gtf_parser.trans2seg[c][i]) t2s.push_back((uint8_t) v);
+    }
+    t2s_off[ntr] = (uint32_t) t2s.size();
+    std::vector<uint32_t> gene_start, gene_end;
+    if ((size_t) c < gtf_parser.gid2ginfo.size())
+        for (auto &g : gtf_parser.gid2ginfo[c]) { gene_start.push_back(g.start); gene_end.push_back(g.end); }
+    std::vector<uint32_t> chr_shift;
+    std::vector<int32_t> chr_id;
+    for (auto &cc : gtf_parser.con2chr[c]) { chr_shift.push_back(cc.shift); chr_id.push_back(chr_index(cc.contig)); }
+    const uint64_t n_bits = (uint64_t) _ih_refGenLen + 2;
+    std::vector<uint64_t> nb((n_bits + 63) / 64, 0), in((n_bits + 63) / 64, 0);
+    if ((size_t) c < near_border_bs.size())
+        for (uint64_t k = 0; k < n_bits; k++)
+            if (near_border_bs[c][k]) nb[k >> 6] |= 1ull << (k & 63);
+    if ((size_t) c < intronic_bs.size())
+        for (uint64_t k = 0; k < n_bits; k++)
+            if (intronic_bs[c][k]) in[k >> 6] |= 1ull << (k & 63);
+    auto pad = [](auto &v) { if (v.empty()) v.resize(1); };
+    pad(seg_start); pad(seg_end); pad(seg_next); pad(seg_gene); pad(tid); pad(trans_start); pad(t2s); pad(gene_start); pad(gene_end);
+    pad(chr_shift); pad(chr_id);
+    cm_annot_flat A;
+    memset(&A, 0, sizeof A);
+    A.n_iv = (uint32_t) n_iv;
+    A.iv_spos = iv_spos.data(); A.iv_epos = iv_epos.data(); A.iv_max_end = iv_max_end.data(); A.iv_min_end = iv_min_end.data();
+    A.iv_max_next_exon = iv_next.data(); A.iv_seg_off = iv_seg_off.data();
+    A.n_seg = iv_seg_off[n_iv];
+    A.seg_start = seg_start.data(); A.seg_end = seg_end.data(); A.seg_next_exon_beg = seg_next.data(); A.seg_gene_id = seg_gene.data();
+    A.seg_tid_off = seg_tid_off.data();
+    A.n_tid = seg_tid_off.back();
+    A.tid = tid.data();
+    A.n_trans = (uint32_t) ntr;
+    A.trans_start_ind = trans_start.data(); A.t2s_off = t2s_off.data(); A.t2s = t2s.data();
+    A.n_genes = (size_t) c < gtf_parser.gid2ginfo.size() ? (uint32_t) gtf_parser.gid2ginfo[c].size() : 0;
+    A.gene_start = gene_start.data(); A.gene_end = gene_end.data();
+    A.n_chr = (uint32_t) gtf_parser.con2chr[c].size();
+    A.chr_shift = chr_shift.data(); A.chr_id = chr_id.data();
+    A.n_bits = n_bits;
+    A.near_border = nb.data(); A.intronic = in.data();
+    if (cm_gpu_load_annotation(g_ctx, c, &A) != CM_OK) die("cm_gpu_load_annotation");
+}
+
+void ensure_round(int c) {
+    if (!g_ctx) {
+        cm_params p;
+        cm_params_default(&p);
+        p.kmer = kmer; p.max_read_len = maxReadLength; p.max_ed = maxEd; p.max_sc = maxSc; p.band_width = bandWidth;
+        p.seed_lim = seedLim; p.max_tlen = maxTlen; p.max_intron_len = maxIntronLen; p.max_chain_len = maxChainLen;
+        p.scan_level = scanLevel;
+        const char *dev = getenv("CM_GPU_DEVICE");
+        if (cm_gpu_create(dev ? atoi(dev) : 0, &p, &g_ctx) != CM_OK) die("cm_gpu_create");
+    }
+    if (g_loaded_contig == c) return;
+    // entries in use = end of the furthest bucket (_ih_hashTableMemSize is only maintained by the index builder)
+    uint64_t n = 0;
+    for (int hv = 0; hv < _ih_maxHashTableSize; hv++)
+        if (_ih_hashTable[hv].list) {
+            uint64_t end = (uint64_t) (_ih_hashTable[hv].list - _ih_hashTableMem) + _ih_hashTable[hv].list[0].info + 1;
+            if (end > n) n = end;
+        }
+    if (cm_gpu_load_contig(g_ctx, c, (const void *const *) _ih_hashTable, _ih_hashTableMem, n, (const uint64_t *) _ih_crefGen,
+                           (uint32_t) _ih_refGenLen) != CM_OK)
+        die("cm_gpu_load_contig");
+    upload_annotation(c);
+    g_loaded_contig = c;
+}
+
+// a Record that outlives FASTQParser's per-thread buffer
+struct Held {
+    Record rec;
+    std::vector<char> buf;
+    void take(const Record *src) {
+        const size_t ln = strlen(src->rname) + 1, ls = src->seq_len + 1, lc = strlen(src->comment) + 1, lq = strlen(src->qual) + 1;
+        buf.resize(ln + 2 * ls + lc + 2 * lq);
+        char *p = buf.data();
+        rec.rname = p; memcpy(p, src->rname, ln); p += ln;
+        rec.seq = p; memcpy(p, src->seq, ls); p += ls;
+        rec.rcseq = p; memcpy(p, src->rcseq, ls); p += ls;
+        rec.comment = p; memcpy(p, src->comment, lc); p += lc;
+        rec.qual = p; memcpy(p, src->qual, lq); p += lq;
+        rec.rqual = p; memcpy(p, src->rqual, lq);
+        rec.seq_len = src->seq_len;
+        *rec.mr = *src->mr;
+    }
+};
+
+void *gpu_map_reads(void *args) {
+    FilterArgs *fa = (FilterArgs *) args;
+    ensure_round(contigNum);
+    const int is_last = filter_read.get_last_round();
+    const char *bs = getenv("CM_GPU_BATCH");
+    const size_t B = bs ? (size_t) atol(bs) : 262144;
+    const uint32_t stride = (uint32_t) maxReadLength;
+    std::vector<Held> h1(B), h2(B);
+    std::vector<char> s1(B * stride), s2(B * stride);
+    std::vector<uint16_t> l1(B), l2(B);
+    std::vector<cm_mread> in(B), out(B);
+    std::vector<int32_t> state(B);
+    bool more = true;
+    while (more) {
+        size_t n = 0;
+        for (; n < B; n++) {   // the reference's serial section, unchanged (src/circminer.cpp:373-379)
+            Record *r1 = fq_parser1.get_next_read(fa->id);
+            Record *r2 = r1 ? fq_parser2.get_next_read(fa->id) : nullptr;
+            if (!r1) { more = false; break; }
+            h1[n].take(r1);
+            h2[n].take(r2);
+            memcpy(&s1[n * stride], r1->seq, r1->seq_len);
+            memcpy(&s2[n * stride], r2->seq, r2->seq_len);
+            l1[n] = (uint16_t) r1->seq_len;
+            l2[n] = (uint16_t) r2->seq_len;
+            to_pod(r1->mr, &in[n]);
+        }
+        if (!n) break;
+        if (cm_gpu_process_batch_pe(g_ctx, contigNum, (uint32_t) n, s1.data(), s2.data(), stride, l1.data(), l2.data(), in.data(),
+                                    out.data(), state.data()) != CM_OK)
+            die("cm_gpu_process_batch_pe");
+        for (size_t i = 0; i < n; i++) {   // the reference's policy, in input order (src/circminer.cpp:386-397)
+            Record *r1 = &h1[i].rec, *r2 = &h2[i].rec;
+            from_pod(&out[i], r1->mr);
+            const int st = state[i];
+            bool skip = (scanLevel == 0 and st == CONCRD) or
+                        (scanLevel == 1 and st == CONCRD and r1->mr->gm_compatible and (r1->mr->ed_r1 + r1->mr->ed_r2 == 0) and
+                         (r1->mr->mlen_r1 + r1->mr->mlen_r2 == r1->seq_len + r2->seq_len));
+            if (skip or is_last) {
+                if (reportMapping == SAMFORMAT) filter_read.print_sam(r1, r2);
+                else if (reportMapping == PAMFORMAT) filter_read.print_pam(r1, r2);
+            }
+            if ((!is_last and !skip) or (is_last and (r1->mr->type == CHIBSJ or r1->mr->type == CHI2BSJ)))
+                filter_read.write_read_category(r1, r2, *(r1->mr));
+        }
+    }
+    return NULL;
+}
+
+void *idle(void *) { return NULL; }
+
+}   // namespace
+
+int cm_shim_pthread_create(pthread_t *t, const pthread_attr_t *a, void *(*)(void *), void *arg) {
+    FilterArgs *fa = (FilterArgs *) arg;
+    if (!pairedEnd) {
+        fprintf(stderr, "circminer_gpu: single-end mode writes no output in the reference (SURVEY.md 0.5b); use the C-ABI directly\n");
+        exit(1);
+    }
+    return (::pthread_create)(t, a, fa->id == 0 ? gpu_map_reads : idle, arg);
+}

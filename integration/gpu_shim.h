@@ -1,0 +1,10 @@
+/* Force-included (g++ -include) into the reference's src/circminer.cpp when building the drop-in binary
+ * oracle/_ref/circminer_gpu.  The only change to the reference driver is where its mapping threads start:
+ * mapping() calls pthread_create(..., map_reads, filter_args[th]) (src/circminer.cpp:290-293); here that call
+ * is routed to cm_shim_pthread_create, which runs the batched GPU map_reads (integration/gpu_map_reads.cpp)
+ * on thread 0 and nothing on the others.  Everything else -- index loading, FASTQ parsing, PAM / remain-FASTQ
+ * writers, the round loop and stage 2 -- is the reference's own code, unmodified. */
+#pragma once
+#include <pthread.h>
+int cm_shim_pthread_create(pthread_t *t, const pthread_attr_t *a, void *(*fn)(void *), void *arg);
+#define pthread_create cm_shim_pthread_create

@@ -1,0 +1,58 @@
+"""Whole-binary parity of the drop-in: the reference's own driver with its mapping threads routed to
+libcm_gpu.so (oracle/_ref/circminer_gpu = unmodified reference objects + integration/gpu_map_reads.cpp)
+against the unmodified reference binary, same inputs, two packed contigs (two rounds with the MatchedRead
+state carried through the remain FASTQ headers) and stage 2 (circRNA calling) run by the reference code on
+both sides.  Every output file must be byte-identical: mapping.pam, the per-round remain FASTQs,
+candidates.pam and circ_report."""
+import filecmp
+import glob
+import os
+import subprocess
+import sys
+
+import pytest
+
+from conftest import has_ref
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref", "circminer")
+GPU = os.path.join(ROOT, "oracle", "_ref", "circminer_gpu")
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(binary, w, out, env=None, extra=()):
+    cmd = [binary, "-r", w["fa"], "-g", w["gtf"], "-1", w["fq1"], "-2", w["fq2"], "-k", "20", "-t", "1", "-P", "-z", "-o", out, *extra]
+    e = dict(os.environ, LC_ALL="C")
+    e.update(env or {})
+    p = subprocess.run(cmd, capture_output=True, text=True, env=e, timeout=1500)
+    assert p.returncode == 0, (p.stdout + p.stderr)[-2000:]
+    return p
+
+
+@pytest.mark.skipif(not (has_ref() and os.path.exists(GPU)), reason="oracle/_ref/circminer_gpu not built")
+@pytest.mark.parametrize("scan", ["0", "2"])
+def test_dropin_binary_outputs_are_byte_identical(tmp_path, scan):
+    from circminer_b200 import workload
+    d = str(tmp_path / "t1")
+    w = workload.prepare("T1", d, contig_size=3_500_000, write_reads=True)
+    # the reference's index with two packed contigs (its CLI always packs at 1.1 Gbp)
+    subprocess.run([sys.executable, "-c",
+                    "import sys; sys.path.insert(0, %r)\n"
+                    "from oracle.refharness import RefHarness, default_params\n"
+                    "RefHarness(default_params()).build_index(%r, contig_size=3500000)" % (ROOT, w["fa"])],
+                   check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=900)
+    info = open(w["fa"] + ".packed.fa.index.info").read().split("\n")
+    assert len({ln.split()[0] for ln in info if ln.strip()}) >= 2, "expected at least two packed contigs"
+    ref_out, gpu_out = str(tmp_path / "ref"), str(tmp_path / "gpu")
+    _run(REF, w, ref_out, extra=("-a", scan))
+    _run(GPU, w, gpu_out, env={"CM_GPU_BATCH": "4096"}, extra=("-a", scan))
+    ref_files = sorted(os.path.basename(f)[3:] for f in glob.glob(ref_out + "*") if os.path.isfile(f))
+    gpu_files = sorted(os.path.basename(f)[3:] for f in glob.glob(gpu_out + "*") if os.path.isfile(f))
+    assert ref_files == gpu_files and any(f.endswith("circ_report") for f in ref_files), (ref_files, gpu_files)
+    assert any("remain_R1" in f for f in ref_files)
+    for suffix in ref_files:
+        a, b = ref_out + suffix, gpu_out + suffix
+        assert filecmp.cmp(a, b, shallow=False), f"{suffix} differs ({os.path.getsize(a)} vs {os.path.getsize(b)} bytes)"
+    assert os.path.getsize(ref_out + ".mapping.pam") > 100000
+    assert os.path.getsize(ref_out + ".circ_report") > 0
