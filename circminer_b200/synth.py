@@ -51,6 +51,9 @@ CONFIGS = {
     # mid-size parity shape (seconds on the CPU oracle)
     "T1": SynthConfig("T1", [3_000_000, 2_000_000], 120, 20_000, 150, 250, 450, 21, 22, n_repeats=1500,
                       n_long_repeats=20, n_gaps=2),
+    # C5's shape in small: 2x250 reads for the k=14 compact index (17 seeds per strand, long hit lists)
+    "T2": SynthConfig("T2", [1_500_000, 1_000_000], 60, 4_000, 250, 400, 700, 31, 32, n_repeats=800,
+                      n_long_repeats=10, n_gaps=1),
 }
 
 

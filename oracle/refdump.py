@@ -84,6 +84,7 @@ def main():
     ap.add_argument("--max-ed", type=int, default=4)
     ap.add_argument("--band", type=int, default=3)
     ap.add_argument("--se", action="store_true")
+    ap.add_argument("--compact", action="store_true", help="build the reference index with -m (counts only)")
     ap.add_argument("--align", type=int, default=0, help="random alignment problems per kind")
     ap.add_argument("--no-stage-dumps", action="store_true", help="only process_read results (large workloads)")
     ap.add_argument("--out", required=True)
@@ -100,7 +101,7 @@ def main():
     if a.kmer != 20:
         # the harness builds with checkSumLength from set_params (commandline_parser.cpp:247)
         pass
-    h.build_index(w["fa"], contig_size=a.contig_size)
+    h.build_index(w["fa"], contig_size=a.contig_size, compact=a.compact)
     h.open(w["fa"], w["gtf"], os.path.join(tmp, "ref"))
     s1, s2 = w["s1"], w["s2"]
     n, L = s1.shape

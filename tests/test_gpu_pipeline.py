@@ -119,6 +119,43 @@ def test_t1_live_reference(tmp_path):
     m.close()
 
 
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_t2_k14_compact_2x250_live_reference(tmp_path):
+    """C5's shape in small: 2x250 reads, k = 14 (checksum length 0: every bucket entry matches), the reference's
+    compact (-m) index, 17 seeds per strand; seeds, chains and process_read over two packed contigs."""
+    from circminer_b200 import workload
+    from circminer_b200.api import fresh_mreads
+    dump = live_dump(str(tmp_path / "t2.npz"), workload="T2", contig_size=1_800_000, kmer=14, compact=True)
+    assert int(dump["kmer"]) == 14 and int(dump["n_contigs"]) == 2
+    w = workload.prepare("T2", str(tmp_path / "t2"), contig_size=1_800_000)
+    check_reads(w, dump)
+    m = _mapper(w, kmer=14)
+    mr = fresh_mreads(len(w["s1"]))
+    for c in range(2):
+        mr = compare_contig(m, c, w, dump, mr)
+    m.close()
+
+
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_t1_single_end_k22_scan2_live_reference(tmp_path):
+    """C4's shape in small: single-end, k = 22 (the int16_t checksum truncation of match_read.cpp:77 is part of the
+    contract), scan-lev 2, max-ed 4, band 3.  The reference's SE mode writes no files, so the pinned result is the
+    return value of FilterRead::process_read (SE overload) per read per contig."""
+    from circminer_b200 import workload
+    dump = live_dump(str(tmp_path / "t1se.npz"), workload="T1", contig_size=3_500_000, kmer=22, scan_level=2, se=True,
+                     pairs=6000, no_stage_dumps=True)
+    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000, n_pairs=6000)
+    check_reads(w, dump)
+    m = _mapper(w, kmer=22, scan_level=2)
+    for c in range(int(dump["n_contigs"])):
+        st = m.process_read_se(c, w["s1"])
+        want = dump[f"c{c}_se_state"]
+        bad = np.nonzero(st != want)[0]
+        assert len(bad) == 0, f"contig {c}: {len(bad)} SE states differ, first {bad[:5]}"
+    assert len(np.unique(dump["c0_se_state"])) >= 3
+    m.close()
+
+
 def test_ragged_and_degenerate_reads(w_t0):
     """Ragged lengths, reads shorter than k, N / lower-case bases: states must equal the all-contig golden
     run restricted to untouched rows, and nothing may fault."""
