@@ -129,11 +129,16 @@ def _rows(seqs, lens=None):
 class Mapper:
     """One context per GPU (threading contract of SURVEY.md 8(b))."""
 
-    def __init__(self, params: CmParams | None = None, device: int = 0):
+    def __init__(self, params: CmParams | None = None, device: int = 0, parent: "Mapper | None" = None):
+        """parent: share that Mapper's resident contigs and annotation (cm_gpu_create_shared); own stream and buffers."""
         self.lib = load_library()
-        self.params = params or default_params()
+        self.params = parent.params if parent is not None else (params or default_params())
         self.ctx = C.c_void_p()
-        r = self.lib.cm_gpu_create(device, C.byref(self.params), C.byref(self.ctx))
+        self.parent = parent
+        if parent is not None:
+            r = self.lib.cm_gpu_create_shared(parent.ctx, C.byref(self.ctx))
+        else:
+            r = self.lib.cm_gpu_create(device, C.byref(self.params), C.byref(self.ctx))
         if r != 0:
             raise CmGpuError(f"cm_gpu_create: {self.lib.cm_gpu_last_error(None).decode()} (status {r})")
         k = self.params.kmer
@@ -251,8 +256,9 @@ class Mapper:
                   "cm_gpu_align_batch")
         return dict(ed=o[0], sclen=o[1], indel=o[2], score=o[3])
 
-    def process_read(self, contig_id, seqs1, seqs2, mreads, lens1=None, lens2=None):
-        """FilterRead::process_read, PE overload, for a batch (src/filter.cpp:124)."""
+    def process_read(self, contig_id, seqs1, seqs2, mreads, lens1=None, lens2=None, out=None, state=None):
+        """FilterRead::process_read, PE overload, for a batch (src/filter.cpp:124).  out / state: caller-owned result
+        buffers (pinned memory makes the device->host copy several times faster)."""
         a1, l1 = _rows(seqs1, lens1)
         a2, l2 = _rows(seqs2, lens2)
         if a1.shape != a2.shape:
@@ -260,8 +266,11 @@ class Mapper:
         n = a1.shape[0]
         mreads = np.ascontiguousarray(mreads)
         assert mreads.dtype == MREAD_DTYPE and len(mreads) == n
-        out = np.zeros(n, MREAD_DTYPE)
-        state = np.zeros(n, np.int32)
+        if out is None:
+            out = np.zeros(n, MREAD_DTYPE)
+        if state is None:
+            state = np.zeros(n, np.int32)
+        assert out.dtype == MREAD_DTYPE and len(out) == n and state.dtype == np.int32 and len(state) == n
         self._chk(self.lib.cm_gpu_process_batch_pe(self.ctx, contig_id, C.c_uint32(n), _vp(a1), _vp(a2),
                                                    C.c_uint32(a1.shape[1]), _vp(l1), _vp(l2), _vp(mreads),
                                                    _vp(out), _vp(state)), "cm_gpu_process_batch_pe")

@@ -40,6 +40,7 @@ struct cm_gpu_ctx {
     cudaEvent_t ev[6]{};
     std::string err;
     std::vector<ContigHost> contigs;
+    cm_gpu_ctx *parent = nullptr;     // cm_gpu_create_shared: index and annotation live in (and are owned by) the parent
     cudaStream_t stream2 = nullptr;   // side stream: kernels that run beside the main one (heavy strands)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cm_counters *d_counters = nullptr;
@@ -208,6 +209,18 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
     return CM_OK;
 }
 
+// A second context on the same device that shares the parent's resident contigs (index, genome, annotation; read-only
+// on this path) and owns its own stream and batch buffers: two host threads alternating batches over the two contexts
+// overlap one batch's host<->device copies with the other's kernels.
+extern "C" int cm_gpu_create_shared(cm_gpu_ctx *parent, cm_gpu_ctx **out) {
+    if (!parent || !out) return CM_ERR_ARG;
+    if (parent->parent) return fail(parent, CM_ERR_ARG, "the parent of a shared context must be a root context");
+    int r = cm_gpu_create(parent->device, &parent->p, out);
+    if (r != CM_OK) return r;
+    (*out)->parent = parent;
+    return CM_OK;
+}
+
 static void free_contig(ContigHost &c) {
     for (void *p : c.owned) cudaFree(p);
     for (void *p : c.owned_annot) cudaFree(p);
@@ -268,6 +281,7 @@ extern "C" int cm_gpu_last_stage_ms(cm_gpu_ctx *ctx, float out[5]) {
 
 static ContigHost *get_contig(cm_gpu_ctx *ctx, int contig_id, bool create) {
     if (contig_id < 0 || contig_id > 4095) return nullptr;
+    if (ctx->parent) return create ? nullptr : get_contig(ctx->parent, contig_id, false);   // shared contexts only read
     if ((size_t) contig_id >= ctx->contigs.size()) {
         if (!create) return nullptr;
         ctx->contigs.resize(contig_id + 1);
@@ -323,7 +337,7 @@ extern "C" int cm_gpu_load_contig(cm_gpu_ctx *ctx, int contig_id, const void *co
     if (!bucket_lists || !table_mem || !cref_gen) return fail(ctx, CM_ERR_ARG, "null argument");
     cudaSetDevice(ctx->device);
     ContigHost *ch = get_contig(ctx, contig_id, true);
-    if (!ch) return fail(ctx, CM_ERR_ARG, "bad contig id %d", contig_id);
+    if (!ch) return fail(ctx, CM_ERR_ARG, ctx->parent ? "contig %d: a shared context cannot load (load into its parent)" : "bad contig id %d", contig_id);
     free_contig(*ch);
     const GeneralIndexPacked *mem = (const GeneralIndexPacked *) table_mem;
     // directory + SoA split on the host (one pass over the buckets, like setHashTablePointers, HashTable.c:1074)
@@ -431,7 +445,7 @@ extern "C" int cm_gpu_build_contig(cm_gpu_ctx *ctx, int contig_id, const char *c
     if (!contig_seq) return fail(ctx, CM_ERR_ARG, "null argument");
     cudaSetDevice(ctx->device);
     ContigHost *ch = get_contig(ctx, contig_id, true);
-    if (!ch) return fail(ctx, CM_ERR_ARG, "bad contig id %d", contig_id);
+    if (!ch) return fail(ctx, CM_ERR_ARG, ctx->parent ? "contig %d: a shared context cannot load (load into its parent)" : "bad contig id %d", contig_id);
     free_contig(*ch);
     cudaStream_t st = ctx->stream;
     int r;
@@ -543,7 +557,7 @@ extern "C" int cm_gpu_load_annotation(cm_gpu_ctx *ctx, int contig_id, const cm_a
     if (!A) return fail(ctx, CM_ERR_ARG, "null argument");
     cudaSetDevice(ctx->device);
     ContigHost *ch = get_contig(ctx, contig_id, true);
-    if (!ch) return fail(ctx, CM_ERR_ARG, "bad contig id %d", contig_id);
+    if (!ch) return fail(ctx, CM_ERR_ARG, ctx->parent ? "contig %d: a shared context cannot load (load into its parent)" : "bad contig id %d", contig_id);
     for (void *p : ch->owned_annot) cudaFree(p);
     ch->owned_annot.clear();
     ch->has_annot = false;
@@ -662,7 +676,7 @@ static int stage_reads(cm_gpu_ctx *ctx, uint32_t n, const char *s1, const char *
         if (l1[i] == 0 || (s2 && l2[i] == 0)) return fail(ctx, CM_ERR_ARG, "read %u is empty (fastq_parser.cpp:157 would underflow)", i);
     }
     cudaStream_t st = ctx->stream;
-    uint32_t stride = (uint32_t) ((ctx->p.max_read_len + 15) / 16 * 16);
+    uint32_t stride = (max_len + 15) / 16 * 16;   // strand rows as long as this batch's longest read, not max_read_len
     uint32_t n_strands = (s2 ? 4u : 2u) * n;
     ENSURE(ctx, ctx->in_seq1, (size_t) n * in_stride);
     ENSURE(ctx, ctx->in_len1, (size_t) n * 2);

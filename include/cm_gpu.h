@@ -124,6 +124,12 @@ typedef struct cm_gpu_ctx cm_gpu_ctx;
 /* replaces the per-thread scratch set-up in mapping() (src/circminer.cpp:163-191)
  * and FilterRead::init's TransExtension array (src/filter.cpp:41-44) */
 int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **out);
+/* A context on the same device that shares `parent`'s resident contigs and annotation
+ * (read-only on this path) but owns its stream and batch buffers, so that two host threads
+ * alternating batches overlap one batch's copies with the other's kernels -- the role the
+ * reference's threadCount map_reads threads over shared globals play (src/circminer.cpp:290).
+ * Loading entry points are refused on it; destroy it before its parent. */
+int cm_gpu_create_shared(cm_gpu_ctx *parent, cm_gpu_ctx **out);
 int cm_gpu_destroy(cm_gpu_ctx *ctx);
 const char *cm_gpu_last_error(const cm_gpu_ctx *ctx);   /* ctx may be NULL: last create error */
 int cm_gpu_get_counters(cm_gpu_ctx *ctx, cm_counters *out, int reset);

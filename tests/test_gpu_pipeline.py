@@ -156,6 +156,33 @@ def test_t1_single_end_k22_scan2_live_reference(tmp_path):
     m.close()
 
 
+def test_shared_context_gives_the_same_results(w_t0):
+    """cm_gpu_create_shared: a second context over the parent's resident contigs, used from a second host thread."""
+    import threading
+    from circminer_b200.api import CmGpuError, Mapper, fresh_mreads
+    gold = np.load(os.path.join(GOLDEN, "T0_k20.npz"))
+    m = _mapper(w_t0)
+    m2 = Mapper(parent=m)
+    with pytest.raises(CmGpuError):
+        m2.build_contig(0, w_t0["contigs"][0])
+    res = {}
+
+    def work(name, mp):
+        mr = fresh_mreads(len(w_t0["s1"]))
+        for c in range(int(gold["n_contigs"])):
+            mr = compare_contig(mp, c, w_t0, gold, mr, stages=("pe",))
+        res[name] = mr
+
+    th = [threading.Thread(target=work, args=(k, mp)) for k, mp in (("a", m), ("b", m2))]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert "a" in res and "b" in res and (res["a"] == res["b"]).all()
+    m2.close()
+    m.close()
+
+
 def test_ragged_and_degenerate_reads(w_t0):
     """Ragged lengths, reads shorter than k, N / lower-case bases: states must equal the all-contig golden
     run restricted to untouched rows, and nothing may fault."""
