@@ -13,6 +13,18 @@ CM_HD bool cm_bit(const uint64_t *w, uint64_t n_bits, uint64_t k) {
 
 // FlatIntervalTree::search: returns i such that target in [spos[i-1], spos[i])
 CM_HD int cm_iv_search(const AnnotDev &a, uint32_t target) {
+    if (a.iv_lut && a.n_iv > 1) {
+        // the loop below returns max(1, #{spos <= target}); count inside the bucket of `target` only
+        uint32_t b = target >> a.iv_lut_shift;
+        if (b >= a.iv_lut_n) b = a.iv_lut_n - 1;
+        uint32_t lo = a.iv_lut[b], hi = a.iv_lut[b + 1];   // spos[k] <= target for k < lo; spos[k] > target for k >= hi
+        if (b == a.iv_lut_n - 1) hi = a.n_iv;
+        while (lo < hi) {
+            uint32_t mid = (lo + hi) >> 1;
+            if (a.iv_spos[mid] <= target) lo = mid + 1; else hi = mid;
+        }
+        return lo < 1 ? 1 : (int) lo;
+    }
     int beg = 0, end = (int) a.n_iv;
     while (end - beg > 1) {
         int mid = (beg + end) / 2;

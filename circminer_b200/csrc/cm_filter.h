@@ -340,101 +340,90 @@ struct StrandView {
     int seq_len;
 };
 
-// FilterRead::process_mates (src/filter.cpp:244-395) with pair_chains (:484-551) folded in: the
-// MatePair vector is replaced by a 2-bit code per (i, j) visited in the same order.
-CM_HDN int cm_process_mates(FilterCtx &f, const StrandView &fw, const StrandView &bw, cm_mread &mr, bool r1_forward) {
+// One MatePair of process_mates' main loop (src/filter.cpp:272-356): extend both chains, classify, update mr.
+// Returns true when process_mates returns CONCRD at once (scan-lev 0).
+struct MatesAcc {
+    int min_ret1, min_ret2;
+    bool r1_genic, r2_genic;
+};
+CM_HDN bool cm_mates_candidate(FilterCtx &f, const StrandView &fw, const StrandView &bw, int i, int j, int pair_type, int f_iv_i,
+                               int b_iv_j, cm_mread &mr, bool r1_forward, MatesAcc &acc) {
     const AnnotDev &a = f.x.v->a;
     const cm_params &p = f.x.v->p;
-    const int nf = fw.chains.count, nb = bw.chains.count;
-    const int saved_type = mr.type;
-    int f_iv[CM_MAX_CHAINS], b_iv[CM_MAX_CHAINS];
-    for (int i = 0; i < nf; i++) f_iv[i] = cm_location_overlap_ne(a, cl_chain(fw.chains, i).frags[0].rpos);
-    for (int j = 0; j < nb; j++) b_iv[j] = cm_location_overlap_ne(a, cl_chain(bw.chains, j).frags[0].rpos);
-    uint8_t code[(CM_MAX_CHAINS * CM_MAX_CHAINS + 3) / 4];
-    for (unsigned q = 0; q < sizeof code; q++) code[q] = 0;
-    uint32_t f_paired = 0, b_paired = 0;
-    for (int i = 0; i < nf; i++) {
-        ChainView ci = cl_chain(fw.chains, i);
-        uint32_t fs = ci.frags[0].rpos, fe = ci.frags[ci.chain_len - 1].rpos + (uint32_t) p.kmer;
-        for (int j = 0; j < nb; j++) {
-            ChainView cj = cl_chain(bw.chains, j);
-            uint32_t rs = cj.frags[0].rpos, re = cj.frags[cj.chain_len - 1].rpos + (uint32_t) p.kmer;
-            int tlen = (fs < rs) ? (int) (re - fs) : (int) (fe - rs);
-            bool same_tr = false, same_gen = false;
-            if (f_iv[i] >= 0 && b_iv[j] >= 0) same_tr = cm_same_transcript(a, f_iv[i], b_iv[j]);
-            if (!same_tr && f_iv[i] >= 0 &&
-                ((p.scan_level == 0 && saved_type > CM_CONGEN) || (p.scan_level > 0 && saved_type >= CM_CONGEN)))
-                same_gen = cm_same_gene_range(a, f_iv[i], rs, re);
-            if (!same_gen && b_iv[j] >= 0 && (saved_type >= CM_CONGEN)) same_gen = cm_same_gene_range(a, b_iv[j], fs, fe);
-            if (same_tr || same_gen || ((tlen <= CM_MAXDISCRDTLEN) && (saved_type >= CM_CONGNM))) {
-                int c = same_tr ? 1 : (same_gen ? 2 : 3);   // MatePair::type + 1
-                int q = i * CM_MAX_CHAINS + j;
-                code[q >> 2] |= (uint8_t) (c << ((q & 3) * 2));
-                f_paired |= 1u << i;
-                b_paired |= 1u << j;
+    ChainView cf = cl_chain(fw.chains, i), cb = cl_chain(bw.chains, j);
+    TidSet ts;
+    ts.iv_a = pair_type == 0 ? f_iv_i : -1;
+    ts.iv_b = pair_type == 0 ? b_iv_j : -1;
+    MateD r1_mm, r2_mm;
+    mate_init(r1_mm, p);
+    mate_init(r2_mm, p);
+    r1_mm.dir = 1;
+    r2_mm.dir = -1;
+    bool success;
+    bool is_forward_left = cm_is_left_chain(cf, cb, fw.seq_len, p.kmer);
+    if (is_forward_left) {
+        success = cm_extend_both_mates(f.x, cf, cb, ts, fw.seq, bw.seq, 1, 1, fw.seq_len, bw.seq_len, r1_mm, r2_mm);
+        if (success) {
+            ConShiftD cs = cm_con_shift(a, r1_mm.spos);
+            cm_overlap_to_epos(a, r1_mm);
+            cm_overlap_to_spos(a, r1_mm);
+            cm_overlap_to_epos(a, r2_mm);
+            cm_overlap_to_spos(a, r2_mm);
+            if (r1_mm.type == CM_CONCRD && r2_mm.type == CM_CONCRD) {
+                if (cm_concordant_explanation(f, r1_mm, r2_mm, mr, cs, r1_forward, pair_type) && p.scan_level == 0) return true;
+            } else if ((r1_mm.type == CM_CANDID && r2_mm.type == CM_CONCRD) || (r1_mm.type == CM_CONCRD && r2_mm.type == CM_CANDID)) {
+                cm_check_bsj(f, r1_mm, r2_mm, mr, cs, r1_forward);
+            } else if (r1_mm.type == CM_CANDID && r2_mm.type == CM_CANDID) {
+                cm_check_2bsj(f, r1_mm, r2_mm, mr, cs, r1_forward);
+            }
+        }
+    } else {
+        success = cm_extend_both_mates(f.x, cb, cf, ts, bw.seq, fw.seq, 1, 1, bw.seq_len, fw.seq_len, r2_mm, r1_mm);
+        if (success) {
+            ConShiftD cs = cm_con_shift(a, r2_mm.spos);
+            cm_overlap_to_epos(a, r1_mm);
+            cm_overlap_to_spos(a, r1_mm);
+            cm_overlap_to_epos(a, r2_mm);
+            cm_overlap_to_spos(a, r2_mm);
+            if (r1_mm.type == CM_CONCRD && r2_mm.type == CM_CONCRD) {
+                cm_check_chimeric(f, r2_mm, r1_mm, mr, cs, !r1_forward);
+            } else if ((r1_mm.type == CM_CANDID && r2_mm.type == CM_CONCRD) || (r1_mm.type == CM_CONCRD && r2_mm.type == CM_CANDID)) {
+                cm_check_bsj(f, r2_mm, r1_mm, mr, cs, !r1_forward);
+            } else if (r1_mm.type == CM_CANDID && r2_mm.type == CM_CANDID) {
+                cm_check_2bsj(f, r2_mm, r1_mm, mr, cs, !r1_forward);
             }
         }
     }
-    int min_ret1 = CM_ORPHAN, min_ret2 = CM_ORPHAN;
-    bool r1_genic = false, r2_genic = false;
-    for (int i = 0; i < nf; i++)
-        for (int j = 0; j < nb; j++) {
-            int q = i * CM_MAX_CHAINS + j;
-            int c = (code[q >> 2] >> ((q & 3) * 2)) & 3;
-            if (!c) continue;
-            int pair_type = c - 1;
-            ChainView cf = cl_chain(fw.chains, i), cb = cl_chain(bw.chains, j);
-            TidSet ts;
-            ts.iv_a = pair_type == 0 ? f_iv[i] : -1;
-            ts.iv_b = pair_type == 0 ? b_iv[j] : -1;
-            MateD r1_mm, r2_mm;
-            mate_init(r1_mm, p);
-            mate_init(r2_mm, p);
-            r1_mm.dir = 1;
-            r2_mm.dir = -1;
-            bool success;
-            bool is_forward_left = cm_is_left_chain(cf, cb, fw.seq_len, p.kmer);
-            if (is_forward_left) {
-                success = cm_extend_both_mates(f.x, cf, cb, ts, fw.seq, bw.seq, 1, 1, fw.seq_len, bw.seq_len, r1_mm, r2_mm);
-                if (success) {
-                    ConShiftD cs = cm_con_shift(a, r1_mm.spos);
-                    cm_overlap_to_epos(a, r1_mm);
-                    cm_overlap_to_spos(a, r1_mm);
-                    cm_overlap_to_epos(a, r2_mm);
-                    cm_overlap_to_spos(a, r2_mm);
-                    if (r1_mm.type == CM_CONCRD && r2_mm.type == CM_CONCRD) {
-                        if (cm_concordant_explanation(f, r1_mm, r2_mm, mr, cs, r1_forward, pair_type) && p.scan_level == 0)
-                            return CM_CONCRD;
-                    } else if ((r1_mm.type == CM_CANDID && r2_mm.type == CM_CONCRD) ||
-                               (r1_mm.type == CM_CONCRD && r2_mm.type == CM_CANDID)) {
-                        cm_check_bsj(f, r1_mm, r2_mm, mr, cs, r1_forward);
-                    } else if (r1_mm.type == CM_CANDID && r2_mm.type == CM_CANDID) {
-                        cm_check_2bsj(f, r1_mm, r2_mm, mr, cs, r1_forward);
-                    }
-                }
-            } else {
-                success = cm_extend_both_mates(f.x, cb, cf, ts, bw.seq, fw.seq, 1, 1, bw.seq_len, fw.seq_len, r2_mm, r1_mm);
-                if (success) {
-                    ConShiftD cs = cm_con_shift(a, r2_mm.spos);
-                    cm_overlap_to_epos(a, r1_mm);
-                    cm_overlap_to_spos(a, r1_mm);
-                    cm_overlap_to_epos(a, r2_mm);
-                    cm_overlap_to_spos(a, r2_mm);
-                    if (r1_mm.type == CM_CONCRD && r2_mm.type == CM_CONCRD) {
-                        cm_check_chimeric(f, r2_mm, r1_mm, mr, cs, !r1_forward);
-                    } else if ((r1_mm.type == CM_CANDID && r2_mm.type == CM_CONCRD) ||
-                               (r1_mm.type == CM_CONCRD && r2_mm.type == CM_CANDID)) {
-                        cm_check_bsj(f, r2_mm, r1_mm, mr, cs, !r1_forward);
-                    } else if (r1_mm.type == CM_CANDID && r2_mm.type == CM_CANDID) {
-                        cm_check_2bsj(f, r2_mm, r1_mm, mr, cs, !r1_forward);
-                    }
-                }
-            }
-            min_ret1 = r1_mm.type < min_ret1 ? r1_mm.type : min_ret1;
-            min_ret2 = r2_mm.type < min_ret2 ? r2_mm.type : min_ret2;
-            r1_genic = (r1_mm.exons_spos >= 0) || (r1_mm.exons_epos >= 0);
-            r2_genic = (r2_mm.exons_spos >= 0) || (r2_mm.exons_epos >= 0);
-        }
+    acc.min_ret1 = r1_mm.type < acc.min_ret1 ? r1_mm.type : acc.min_ret1;
+    acc.min_ret2 = r2_mm.type < acc.min_ret2 ? r2_mm.type : acc.min_ret2;
+    acc.r1_genic = (r1_mm.exons_spos >= 0) || (r1_mm.exons_epos >= 0);
+    acc.r2_genic = (r2_mm.exons_spos >= 0) || (r2_mm.exons_epos >= 0);
+    return false;
+}
+
+// pair_chains (src/filter.cpp:484-551) for one (i, j): 0 = not paired, else MatePair::type + 1
+CM_HD int cm_pair_code(const AnnotDev &a, const cm_params &p, const ChainView &ci, const ChainView &cj, int f_iv_i, int b_iv_j,
+                       int saved_type) {
+    uint32_t fs = ci.frags[0].rpos, fe = ci.frags[ci.chain_len - 1].rpos + (uint32_t) p.kmer;
+    uint32_t rs = cj.frags[0].rpos, re = cj.frags[cj.chain_len - 1].rpos + (uint32_t) p.kmer;
+    int tlen = (fs < rs) ? (int) (re - fs) : (int) (fe - rs);
+    bool same_tr = false, same_gen = false;
+    if (f_iv_i >= 0 && b_iv_j >= 0) same_tr = cm_same_transcript(a, f_iv_i, b_iv_j);
+    if (!same_tr && f_iv_i >= 0 && ((p.scan_level == 0 && saved_type > CM_CONGEN) || (p.scan_level > 0 && saved_type >= CM_CONGEN)))
+        same_gen = cm_same_gene_range(a, f_iv_i, rs, re);
+    if (!same_gen && b_iv_j >= 0 && (saved_type >= CM_CONGEN)) same_gen = cm_same_gene_range(a, b_iv_j, fs, fe);
+    if (same_tr || same_gen || ((tlen <= CM_MAXDISCRDTLEN) && (saved_type >= CM_CONGNM))) return same_tr ? 1 : (same_gen ? 2 : 3);
+    return 0;
+}
+
+// The rest of process_mates after the MatePair loop (src/filter.cpp:358-394): unpaired chains, fallback type.
+CM_HDN int cm_mates_leftovers(FilterCtx &f, const StrandView &fw, const StrandView &bw, cm_mread &mr, uint32_t f_paired,
+                              uint32_t b_paired, MatesAcc acc) {
+    const AnnotDev &a = f.x.v->a;
+    const cm_params &p = f.x.v->p;
+    const int nf = fw.chains.count, nb = bw.chains.count;
+    int min_ret1 = acc.min_ret1, min_ret2 = acc.min_ret2;
+    bool r1_genic = acc.r1_genic, r2_genic = acc.r2_genic;
     if (mr.type == CM_CONCRD || mr.type == CM_DISCRD || mr.type == CM_CHIORF || mr.type == CM_CHIBSJ || mr.type == CM_CHI2BSJ)
         return mr.type;
     MateD mm1;
@@ -468,6 +457,45 @@ CM_HDN int cm_process_mates(FilterCtx &f, const StrandView &fw, const StrandView
                                    : ((min_ret1 == CM_CONCRD) && (min_ret2 == CM_CONCRD)) ? CM_OEA2 : CM_CANDID;
     mr_update_type(mr, new_type);
     return mr.type;
+}
+
+
+// FilterRead::process_mates (src/filter.cpp:244-395) with pair_chains (:484-551) folded in: the
+// MatePair vector is replaced by a 2-bit code per (i, j) visited in the same order.
+CM_HDN int cm_process_mates(FilterCtx &f, const StrandView &fw, const StrandView &bw, cm_mread &mr, bool r1_forward) {
+    const AnnotDev &a = f.x.v->a;
+    const cm_params &p = f.x.v->p;
+    const int nf = fw.chains.count, nb = bw.chains.count;
+    const int saved_type = mr.type;
+    int f_iv[CM_MAX_CHAINS], b_iv[CM_MAX_CHAINS];
+    for (int i = 0; i < nf; i++) f_iv[i] = cm_location_overlap_ne(a, cl_chain(fw.chains, i).frags[0].rpos);
+    for (int j = 0; j < nb; j++) b_iv[j] = cm_location_overlap_ne(a, cl_chain(bw.chains, j).frags[0].rpos);
+    uint8_t code[(CM_MAX_CHAINS * CM_MAX_CHAINS + 3) / 4];
+    for (unsigned q = 0; q < sizeof code; q++) code[q] = 0;
+    uint32_t f_paired = 0, b_paired = 0;
+    for (int i = 0; i < nf; i++) {
+        ChainView ci = cl_chain(fw.chains, i);
+        for (int j = 0; j < nb; j++) {
+            int c = cm_pair_code(a, p, ci, cl_chain(bw.chains, j), f_iv[i], b_iv[j], saved_type);
+            if (c) {
+                int q = i * CM_MAX_CHAINS + j;
+                code[q >> 2] |= (uint8_t) (c << ((q & 3) * 2));
+                f_paired |= 1u << i;
+                b_paired |= 1u << j;
+            }
+        }
+    }
+    MatesAcc acc;
+    acc.min_ret1 = acc.min_ret2 = CM_ORPHAN;
+    acc.r1_genic = acc.r2_genic = false;
+    for (int i = 0; i < nf; i++)
+        for (int j = 0; j < nb; j++) {
+            int q = i * CM_MAX_CHAINS + j;
+            int c = (code[q >> 2] >> ((q & 3) * 2)) & 3;
+            if (!c) continue;
+            if (cm_mates_candidate(f, fw, bw, i, j, c - 1, f_iv[i], b_iv[j], mr, r1_forward, acc)) return CM_CONCRD;
+        }
+    return cm_mates_leftovers(f, fw, bw, mr, f_paired, b_paired, acc);
 }
 
 // one pair: the four strands' chain lists + high_hits (get_best_chains results), R1 fwd, R1 rc, R2 fwd, R2 rc

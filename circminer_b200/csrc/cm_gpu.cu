@@ -71,6 +71,12 @@ struct cm_gpu_ctx {
     bool sync_each = false;    // CM_GPU_SYNC_EACH=1: synchronise after every launch and name the kernel that failed
     uint32_t heavy_th = 64;    // CM_GPU_HEAVY_TH: strands with more dp cells than this are chained by one warp each (< 255)
     uint32_t last_heavy = 0;
+    // CM_GPU_HEAVY_PAIR_TH: pairs with more candidate chain pairs than this get one warp each.  Unset: 16 for batches of
+    // up to heavy_pair_batch pairs, where such a pair is the critical path of the launch (6.3 -> 1.3 ms at 125 k pairs
+    // of C2); off for larger batches, which are throughput-bound and where the warp kernel costs more than it saves.
+    uint32_t heavy_pair_th = 16, heavy_pair_batch = 300000;
+    bool heavy_pair_forced = false;
+    uint32_t last_heavy_pairs = 0;
     int spec_k = CM_MAX_CHAINS;            // CM_GPU_SPEC_K: leading chains per strand handed to the dense pre-alignment kernel
     bool no_walk_spec = false; // CM_GPU_NO_WALK_SPEC=1: pre-align the genome-text ends only (A-B)
     bool no_spec = false;      // CM_GPU_NO_SPEC=1: every DP inline in the per-pair kernel (debug / A-B)
@@ -197,6 +203,7 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
     cudaStreamSynchronize(ctx->stream);
     if (const char *e = getenv("CM_GPU_REC_MULT")) ctx->rec_mult = (uint32_t) atoi(e);
     if (const char *e = getenv("CM_GPU_HEAVY_TH")) { int t = atoi(e); ctx->heavy_th = (uint32_t) (t < 0 ? 0 : (t > 254 ? 254 : t)); }
+    if (const char *e = getenv("CM_GPU_HEAVY_PAIR_TH")) { ctx->heavy_pair_th = (uint32_t) atol(e); ctx->heavy_pair_forced = true; }
     if (const char *e = getenv("CM_GPU_SPEC_K")) ctx->spec_k = atoi(e) < 1 ? 1 : atoi(e);
     if (const char *e = getenv("CM_GPU_NO_WALK_SPEC")) ctx->no_walk_spec = atoi(e) != 0;
     if (const char *e = getenv("CM_GPU_NO_SPEC")) ctx->no_spec = atoi(e) != 0;
@@ -584,6 +591,21 @@ extern "C" int cm_gpu_load_annotation(cm_gpu_ctx *ctx, int contig_id, const cm_a
     UP(gene_start, A->n_genes) UP(gene_end, A->n_genes) UP(chr_shift, A->n_chr) UP(chr_id, A->n_chr)
     UP(near_border, (A->n_bits + 63) / 64) UP(intronic, (A->n_bits + 63) / 64)
 #undef UP
+    if (!getenv("CM_GPU_NO_IVLUT")) {   // radix index over the interval starts (cm_iv_search)
+        const uint32_t shift = 10;
+        const uint32_t top = A->iv_spos[A->n_iv - 1];
+        const uint32_t nb = (top >> shift) + 2;
+        std::vector<uint32_t> lut((size_t) nb + 1);
+        uint32_t k = 0;
+        for (uint32_t b = 0; b <= nb; b++) {
+            const uint64_t lim = (uint64_t) b << shift;
+            while (k < A->n_iv && (uint64_t) A->iv_spos[k] < lim) k++;
+            lut[b] = k;
+        }
+        if ((r = dev_upload(ctx, own, &a.iv_lut, lut.data(), lut.size())) != CM_OK) return r;
+        a.iv_lut_n = nb;
+        a.iv_lut_shift = shift;
+    }
     ch->has_annot = true;
     return CM_OK;
 }

@@ -193,17 +193,36 @@ static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) 
         ENSURE(ctx, ctx->perm[0], (size_t) n * 4);
         ENSURE(ctx, ctx->perm[1], (size_t) n * 4);
         cudaStream_t st = ctx->stream;
-        k_pair_key<<<grid_for(n, 256), 256, 0, st>>>(v, b, n, (unsigned long long *) ctx->key64[0].p, (uint32_t *) ctx->perm[0].p);
+        ENSURE(ctx, ctx->ovf_n, 8);
+        uint32_t *d_heavy = (uint32_t *) ctx->ovf_n.p + 1;
+        CUDA_TRY(ctx, cudaMemsetAsync(d_heavy, 0, 4, st));
+        k_pair_key<<<grid_for(n, 256), 256, 0, st>>>(v, b, n, (unsigned long long *) ctx->key64[0].p, (uint32_t *) ctx->perm[0].p,
+                                                     (ctx->heavy_pair_forced || n <= ctx->heavy_pair_batch) ? ctx->heavy_pair_th : 0xFFFFFFFFu, d_heavy);
         size_t tb = 0;
         cub::DeviceRadixSort::SortPairsDescending(nullptr, tb, (const unsigned long long *) ctx->key64[0].p, (unsigned long long *) ctx->key64[1].p,
-                                        (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, 43, st);
+                                        (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, 44, st);
         ENSURE(ctx, ctx->cub_tmp, tb + 16);
         cub::DeviceRadixSort::SortPairsDescending(ctx->cub_tmp.p, tb, (const unsigned long long *) ctx->key64[0].p, (unsigned long long *) ctx->key64[1].p,
-                                        (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, 43, st);
+                                        (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, 44, st);
         ctx->launches += 2;
+        uint32_t n_heavy = 0;
+        CUDA_TRY(ctx, cudaMemcpyAsync(&n_heavy, d_heavy, 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
         DBG_SYNC(ctx, "k_pair_key + sort");
-        k_process_pe<<<grid_for(n, CM_PE_BLOCK), CM_PE_BLOCK, 0, st>>>(v, b, (const cm_mread *) ctx->in_mread.p, (cm_mread *) ctx->out_mread.p,
-                                                      (int32_t *) ctx->out_state.p, n, (const uint32_t *) ctx->perm[1].p, ctx->d_counters);
+        ctx->last_heavy_pairs = n_heavy;
+        if (n_heavy) {   // heavy pairs beside the light ones, on the side stream
+            cudaEventRecord(ctx->ev_fork, st);
+            cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0);
+            k_process_pe_warp<<<grid_for((size_t) n_heavy * 32, 128), 128, 0, ctx->stream2>>>(
+                v, b, (const cm_mread *) ctx->in_mread.p, (cm_mread *) ctx->out_mread.p, (int32_t *) ctx->out_state.p, n_heavy,
+                (const uint32_t *) ctx->perm[1].p, ctx->d_counters);
+            cudaEventRecord(ctx->ev_join, ctx->stream2);
+            ctx->launches++;
+        }
+        if (n > n_heavy)
+            k_process_pe<<<grid_for(n - n_heavy, CM_PE_BLOCK), CM_PE_BLOCK, 0, st>>>(v, b, (const cm_mread *) ctx->in_mread.p, (cm_mread *) ctx->out_mread.p,
+                                                      (int32_t *) ctx->out_state.p, n - n_heavy, (const uint32_t *) ctx->perm[1].p + n_heavy, ctx->d_counters);
+        if (n_heavy) cudaStreamWaitEvent(st, ctx->ev_join, 0);
     } else {
         k_process_se<<<grid_for(n, 128), 128, 0, ctx->stream>>>(v, b, (int32_t *) ctx->out_state.p, n, ctx->d_counters);
     }

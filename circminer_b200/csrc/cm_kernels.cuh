@@ -26,7 +26,7 @@ CM_HD uint32_t cm_rec_cap(uint32_t cells, uint32_t mult) { return mult * cells +
 #define CM_CHAIN_MINB 1
 #endif
 #ifndef CM_PE_MINB
-#define CM_PE_MINB 1
+#define CM_PE_MINB 3
 #endif
 #ifndef CM_PE_BLOCK
 #define CM_PE_BLOCK 128   // threads per block of the per-pair kernel
@@ -141,6 +141,8 @@ __global__ void __launch_bounds__(128) k_process_se(DevView v, BatchDev b, int32
     stats_flush(st, i < n_reads ? 1u : 0u, ctr);
 }
 
+#include "cm_pair_warp.cuh"
+
 // stage-level parity entry: chains of the forward strand of each row, in the API layout [n][C][n_slots]
 __global__ void k_chain_export(DevView v, BatchDev b, uint32_t n_rows, int FO, int32_t *__restrict__ chain_count, int32_t *__restrict__ high_hits,
                                float *__restrict__ score, uint32_t *__restrict__ chain_len, uint32_t *__restrict__ frag_rpos,
@@ -205,7 +207,8 @@ __global__ void k_strand_key(DevView v, const uint32_t *__restrict__ seed_cnt, u
 }
 
 // pair: chain counts of the four strands, attempt order, and the shape of the leading chains
-__global__ void k_pair_key(DevView v, BatchDev b, uint32_t n_pairs, unsigned long long *__restrict__ key, uint32_t *__restrict__ idx) {
+__global__ void k_pair_key(DevView v, BatchDev b, uint32_t n_pairs, unsigned long long *__restrict__ key, uint32_t *__restrict__ idx,
+                           uint32_t heavy_th, uint32_t *__restrict__ n_heavy) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_pairs) return;
     unsigned long long k = 0;
@@ -232,8 +235,13 @@ __global__ void k_pair_key(DevView v, BatchDev b, uint32_t n_pairs, unsigned lon
         }
         k = (k << 15) | sig;
     }
+    // pairs with more than heavy_th candidate chain pairs (both attempts) sort to the front: one warp each
+    const bool heavy = (uint32_t) (cnt[0] * cnt[3] + cnt[2] * cnt[1]) > heavy_th;
+    if (heavy) k |= 1ull << 43;
     key[i] = k;
     idx[i] = i;
+    unsigned hm = __ballot_sync(__activemask(), heavy);
+    if (hm && (threadIdx.x & 31u) == (unsigned) (__ffs(hm) - 1)) atomicAdd(n_heavy, (uint32_t) __popc(hm));
 }
 
 // ------------------------------------------------------------------------------------------

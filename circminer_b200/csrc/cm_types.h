@@ -61,6 +61,10 @@ struct ContigDev {
 struct AnnotDev {
     uint32_t n_iv;
     const uint32_t *iv_spos, *iv_epos, *iv_max_end, *iv_min_end, *iv_max_next_exon, *iv_seg_off;
+    // optional radix index over iv_spos (device builds): iv_lut[b] = number of intervals with spos < (b << iv_lut_shift),
+    // b in [0, iv_lut_n]; narrows FlatIntervalTree::search from ~17 dependent probes to the few intervals of one bucket
+    const uint32_t *iv_lut;
+    uint32_t iv_lut_n, iv_lut_shift;
     uint32_t n_seg;
     const uint32_t *seg_start, *seg_end, *seg_next_exon_beg, *seg_gene_id, *seg_tid_off;
     const uint32_t *tid;

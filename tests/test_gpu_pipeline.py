@@ -76,6 +76,21 @@ def test_warp_chaining_is_exact(w_t0, monkeypatch, heavy_th):
     m.close()
 
 
+@pytest.mark.parametrize("th", ["0", "2"])
+def test_warp_pair_kernel_is_exact(w_t0, monkeypatch, th):
+    """CM_GPU_HEAVY_PAIR_TH=0 sends every pair with a candidate chain pair through the warp-per-pair kernel
+    (speculative evaluation of a row's MatePairs, in-order commit); results must equal the goldens, scan-lev 0 and 2."""
+    from circminer_b200.api import fresh_mreads
+    monkeypatch.setenv("CM_GPU_HEAVY_PAIR_TH", th)
+    for name, kw in (("T0_k20.npz", {}), ("T0_k22_scan2.npz", dict(kmer=22, scan_level=2))):
+        gold = np.load(os.path.join(GOLDEN, name))
+        m = _mapper(w_t0, **kw)
+        mr = fresh_mreads(len(w_t0["s1"]))
+        for c in range(int(gold["n_contigs"])):
+            mr = compare_contig(m, c, w_t0, gold, mr, stages=("pe",))
+        m.close()
+
+
 def test_warp_chaining_overflow_path(w_t0, monkeypatch):
     """k_chain_warp with a record slice of 8: overflowing strands are re-run by k_chain_big."""
     from circminer_b200.api import fresh_mreads
