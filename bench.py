@@ -26,7 +26,7 @@ import numpy as np  # noqa: E402
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="C2")
@@ -56,7 +56,12 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def mark(self):
+        """Start of the timed region: only samples taken after this count (the sampler itself starts earlier,
+        nvidia-smi takes a while to come up)."""
+        self.t_mark = time.time()
 
     def stop(self):
         if self.proc:
@@ -66,7 +71,9 @@ class ClockSampler:
             except Exception:
                 pass
         sm, mx, reasons = [], 0, set()
-        for r in self.rows:
+        t_mark = getattr(self, "t_mark", 0.0)
+        rows = [r for t, r in self.rows if t >= t_mark] or [r for _, r in self.rows[-3:]]
+        for r in rows:
             try:
                 sm.append(float(r[0]))
                 mx = max(mx, float(r[1]))
@@ -108,6 +115,7 @@ def run_b200(a):
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ["NCCL_DEBUG"] = os.environ.get("CM_NCCL_DEBUG", "WARN")   # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -176,12 +184,13 @@ def run_b200(a):
             t.join()
 
     m.stage(hb["s1"], hb["s2"], hb["mr"])
+    clk = ClockSampler(local)
+    clk.start()
     for _ in range(a.warmup):
         step_resident()
     m.counters(reset=True)
     barrier()
-    clk = ClockSampler(local)
-    clk.start()
+    clk.mark()
     t0 = time.time()
     dev_ms = 0.0
     stage_acc = np.zeros(5)
@@ -210,6 +219,13 @@ def run_b200(a):
         seed_ms = stage_acc[1] / a.steps
         seed_bytes = 32.0 * ctr["seed_sectors"] / a.steps
         ach = seed_bytes / (seed_ms * 1e-3) / 1e9 if seed_ms > 0 else 0.0
+        traffic = None   # dram read + write bytes of k_seed per launch, from the committed ncu capture of this workload
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_kernel_traffic.json")))
+            if tr["workload"] == a.workload and tr["pairs_per_launch"] == n and a.upto >= 1:
+                traffic = tr["kernels"]["k_seed"]["dram_bytes_read"] + tr["kernels"]["k_seed"]["dram_bytes_write"]
+        except Exception:
+            pass
         line = {
             "metric": "paired-end reads/sec", "value": reads_total / (dev_ms * 1e-3), "unit": "reads/s",
             "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": dev_ms / a.steps,
@@ -230,7 +246,7 @@ def run_b200(a):
             "gpu_launches": int(ctr["kernel_launches"]),
             "clocks": clocks,
             "roofline": {"kernel": "k_seed", "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "traffic": None, "peak_source": how,
+                         "frac": ach / peak, "traffic": traffic, "peak_source": how,
                          "algorithmic_bytes_per_launch": seed_bytes},
             "counters": {k: v / a.steps for k, v in ctr.items()},
             "prep_s": t_prep,

@@ -239,7 +239,7 @@ __device__ void cw_chain_backtrack(const DevView &v, int T, const uint32_t *row_
 }
 
 // K2b': heavy strands (the first n_heavy entries of the work-signature order), one warp each
-__global__ void __launch_bounds__(128) k_chain_warp(DevView v, BatchDev b, const uint64_t *__restrict__ cell_off, double *__restrict__ dp_score,
+__global__ void __launch_bounds__(128) k_chain_warp(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, const uint64_t *__restrict__ cell_off, double *__restrict__ dp_score,
                                                     uint32_t *__restrict__ dp_prev, ChainRec *__restrict__ recs, uint32_t rec_mult,
                                                     uint32_t *__restrict__ ovf_strand, uint32_t *__restrict__ ovf_nrec,
                                                     uint32_t *__restrict__ n_ovf, const uint32_t *__restrict__ order, uint32_t n_heavy,

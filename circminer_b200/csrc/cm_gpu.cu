@@ -742,7 +742,7 @@ static int launch_prep(cm_gpu_ctx *ctx, uint32_t in_stride) {
 // random gathers directory (dir[hv], dir[hv+1]) -> checksum run (binary search).  Positions are NOT
 // copied: chaining reads them in place through (off, cnt).
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_seed(DevView v, const int2 *__restrict__ seed_key, uint64_t total,
+__global__ void __launch_bounds__(256) k_seed(const __grid_constant__ DevView v, const int2 *__restrict__ seed_key, uint64_t total,
                                               uint32_t *__restrict__ seed_off, uint32_t *__restrict__ seed_cnt,
                                               cm_counters *__restrict__ ctr) {
     uint64_t gid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -810,7 +810,7 @@ static int launch_seed(cm_gpu_ctx *ctx, const DevView &v) {
 }
 
 // per-slot summary for the stage-level parity entry
-__global__ void k_seed_summary(DevView v, const uint16_t *__restrict__ slen, uint32_t n_strands, const uint32_t *__restrict__ seed_off,
+__global__ void k_seed_summary(const __grid_constant__ DevView v, const uint16_t *__restrict__ slen, uint32_t n_strands, const uint32_t *__restrict__ seed_off,
                                const uint32_t *__restrict__ seed_cnt, int32_t *__restrict__ qpos, uint32_t *__restrict__ frag_count,
                                uint8_t *__restrict__ has_frags, uint32_t *__restrict__ first_info, uint32_t *__restrict__ last_info,
                                unsigned long long *__restrict__ sum_info) {

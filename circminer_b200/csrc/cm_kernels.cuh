@@ -4,7 +4,7 @@
 // ------------------------------------------------------------------------------------------
 // K2a: dp cells per strand (sum of kept hit-list lengths) -> exclusive scan gives arena offsets
 // ------------------------------------------------------------------------------------------
-__global__ void k_cell_count(DevView v, const uint32_t *__restrict__ seed_cnt, uint32_t n_strands, uint32_t *__restrict__ cells) {
+__global__ void k_cell_count(const __grid_constant__ DevView v, const uint32_t *__restrict__ seed_cnt, uint32_t n_strands, uint32_t *__restrict__ cells) {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_strands) return;
     uint32_t c = 0;
@@ -31,7 +31,7 @@ CM_HD uint32_t cm_rec_cap(uint32_t cells, uint32_t mult) { return mult * cells +
 #ifndef CM_PE_BLOCK
 #define CM_PE_BLOCK 128   // threads per block of the per-pair kernel
 #endif
-__global__ void __launch_bounds__(128, CM_CHAIN_MINB) k_chain(DevView v, BatchDev b, const uint64_t *__restrict__ cell_off, double *__restrict__ dp_score,
+__global__ void __launch_bounds__(128, CM_CHAIN_MINB) k_chain(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, const uint64_t *__restrict__ cell_off, double *__restrict__ dp_score,
                                                uint32_t *__restrict__ dp_prev, ChainRec *__restrict__ recs, uint32_t rec_mult,
                                                uint32_t *__restrict__ ovf_strand, uint32_t *__restrict__ ovf_nrec,
                                                uint32_t *__restrict__ n_ovf, const uint32_t *__restrict__ order, uint32_t n_units,
@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(128, CM_CHAIN_MINB) k_chain(DevView v, BatchDe
 }
 
 // overflow path: record arena sized exactly from the counts k_chain produced
-__global__ void __launch_bounds__(128) k_chain_big(DevView v, BatchDev b, const uint64_t *__restrict__ cell_off, double *__restrict__ dp_score,
+__global__ void __launch_bounds__(128) k_chain_big(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, const uint64_t *__restrict__ cell_off, double *__restrict__ dp_score,
                                                    uint32_t *__restrict__ dp_prev, const uint32_t *__restrict__ ovf_strand,
                                                    const uint64_t *__restrict__ ovf_off, const uint32_t *__restrict__ ovf_nrec, uint32_t n_ovf,
                                                    ChainRec *__restrict__ recs) {
@@ -116,7 +116,7 @@ __device__ __forceinline__ void stats_flush(const AlignStats &st, uint32_t units
     if (units) atomicAdd((unsigned int *) &c->pairs, units);   // low word of the slot; 2^32 units per slot between resets
 }
 
-__global__ void __launch_bounds__(CM_PE_BLOCK, CM_PE_MINB) k_process_pe(DevView v, BatchDev b, const cm_mread *__restrict__ in, cm_mread *__restrict__ out,
+__global__ void __launch_bounds__(CM_PE_BLOCK, CM_PE_MINB) k_process_pe(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, const cm_mread *__restrict__ in, cm_mread *__restrict__ out,
                                                     int32_t *__restrict__ state, uint32_t n_pairs, const uint32_t *__restrict__ order,
                                                     cm_counters *__restrict__ ctr) {
     uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(CM_PE_BLOCK, CM_PE_MINB) k_process_pe(DevView 
     stats_flush(st, live ? 1u : 0u, ctr);
 }
 
-__global__ void __launch_bounds__(128) k_process_se(DevView v, BatchDev b, int32_t *__restrict__ state, uint32_t n_reads,
+__global__ void __launch_bounds__(128) k_process_se(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, int32_t *__restrict__ state, uint32_t n_reads,
                                                     cm_counters *__restrict__ ctr) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     AlignStats st = {0, 0, 0, 0};
@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(128) k_process_se(DevView v, BatchDev b, int32
 #include "cm_pair_warp.cuh"
 
 // stage-level parity entry: chains of the forward strand of each row, in the API layout [n][C][n_slots]
-__global__ void k_chain_export(DevView v, BatchDev b, uint32_t n_rows, int FO, int32_t *__restrict__ chain_count, int32_t *__restrict__ high_hits,
+__global__ void k_chain_export(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, uint32_t n_rows, int FO, int32_t *__restrict__ chain_count, int32_t *__restrict__ high_hits,
                                float *__restrict__ score, uint32_t *__restrict__ chain_len, uint32_t *__restrict__ frag_rpos,
                                int32_t *__restrict__ frag_qpos) {
     uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -187,7 +187,7 @@ __global__ void k_align(cm_params p, int kind, uint32_t n, const uint8_t *__rest
 // depend on the order (every unit writes its own slots).
 // ------------------------------------------------------------------------------------------
 // strand: heavy first (inverted cell count), then the mask of non-empty rows
-__global__ void k_strand_key(DevView v, const uint32_t *__restrict__ seed_cnt, uint32_t n_strands, uint32_t *__restrict__ key,
+__global__ void k_strand_key(const __grid_constant__ DevView v, const uint32_t *__restrict__ seed_cnt, uint32_t n_strands, uint32_t *__restrict__ key,
                              uint32_t *__restrict__ idx, uint32_t heavy_th, uint32_t *__restrict__ n_heavy) {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_strands) return;
@@ -207,7 +207,7 @@ __global__ void k_strand_key(DevView v, const uint32_t *__restrict__ seed_cnt, u
 }
 
 // pair: chain counts of the four strands, attempt order, and the shape of the leading chains
-__global__ void k_pair_key(DevView v, BatchDev b, uint32_t n_pairs, unsigned long long *__restrict__ key, uint32_t *__restrict__ idx,
+__global__ void k_pair_key(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, uint32_t n_pairs, unsigned long long *__restrict__ key, uint32_t *__restrict__ idx,
                            uint32_t heavy_th, uint32_t *__restrict__ n_heavy) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_pairs) return;
@@ -250,7 +250,7 @@ __global__ void k_pair_key(DevView v, BatchDev b, uint32_t n_pairs, unsigned lon
 // the two read ends), so it is done here first, one thread per (chain, kind) with all lanes of a warp
 // on the same kind, and handed to k_process_* as a memo (ChainAux / DropHint).
 // ------------------------------------------------------------------------------------------
-__global__ void k_spec_count(BatchDev b, uint32_t *__restrict__ cnt) {
+__global__ void k_spec_count(const __grid_constant__ BatchDev b, uint32_t *__restrict__ cnt) {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= b.n_strands) return;
     int n = b.chain_cnt[s];
@@ -260,7 +260,7 @@ __global__ void k_spec_count(BatchDev b, uint32_t *__restrict__ cnt) {
 // Work items of the pre-alignment: (chain, kind) with a cost key = read bases the DP has to cover.  Items are
 // sorted by descending cost, so the lanes of a warp run DPs of the same kind and about the same length and the
 // zero-cost items (nothing to align: ChainAux stays zeroed, has_* = 0) fall to the end, where whole warps exit.
-__global__ void k_chain_list(DevView v, BatchDev b, uint32_t n_chains, uint8_t *__restrict__ key, uint32_t *__restrict__ item) {
+__global__ void k_chain_list(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, uint32_t n_chains, uint8_t *__restrict__ key, uint32_t *__restrict__ item) {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= b.n_strands) return;
     uint32_t base = b.chain_base[s];
@@ -287,7 +287,7 @@ __global__ void k_chain_list(DevView v, BatchDev b, uint32_t n_chains, uint8_t *
 }
 
 // chain id -> (strand << 5 | chain)
-__global__ void k_chain_ids(BatchDev b, uint32_t *__restrict__ list) {
+__global__ void k_chain_ids(const __grid_constant__ BatchDev b, uint32_t *__restrict__ list) {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= b.n_strands) return;
     uint32_t base = b.chain_base[s];
@@ -296,7 +296,7 @@ __global__ void k_chain_ids(BatchDev b, uint32_t *__restrict__ list) {
     for (int c = 0; c < n; c++) list[base + c] = (s << 5) | (uint32_t) c;
 }
 
-__global__ void __launch_bounds__(128) k_chain_spec(DevView v, BatchDev b, const uint32_t *__restrict__ list, const uint8_t *__restrict__ key,
+__global__ void __launch_bounds__(128) k_chain_spec(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, const uint32_t *__restrict__ list, const uint8_t *__restrict__ key,
                                                     const uint32_t *__restrict__ item, uint32_t n_chains, uint32_t *__restrict__ walk_q,
                                                     uint32_t *__restrict__ n_walk, cm_counters *__restrict__ ctr) {
     uint64_t gid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -326,7 +326,7 @@ __global__ void __launch_bounds__(128) k_chain_spec(DevView v, BatchDev b, const
 }
 
 // transcript walks of the queued chain ends (roughly in the cost order k_chain_spec met them)
-__global__ void __launch_bounds__(128) k_chain_walk(DevView v, BatchDev b, const uint32_t *__restrict__ list, const uint32_t *__restrict__ walk_q,
+__global__ void __launch_bounds__(128) k_chain_walk(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, const uint32_t *__restrict__ list, const uint32_t *__restrict__ walk_q,
                                                     const uint32_t *__restrict__ n_walk, cm_counters *__restrict__ ctr) {
     uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
     if (gid >= *n_walk) return;

@@ -136,7 +136,7 @@ __device__ int cw_process_read_pe(FilterCtx &f, const PairView &pv, cm_mread &mr
 }
 
 // K3': heavy pairs (the first n_heavy entries of the pair order), one warp each
-__global__ void __launch_bounds__(128) k_process_pe_warp(DevView v, BatchDev b, const cm_mread *__restrict__ in, cm_mread *__restrict__ out,
+__global__ void __launch_bounds__(128) k_process_pe_warp(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, const cm_mread *__restrict__ in, cm_mread *__restrict__ out,
                                                          int32_t *__restrict__ state, uint32_t n_heavy, const uint32_t *__restrict__ order,
                                                          cm_counters *__restrict__ ctr) {
     const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
