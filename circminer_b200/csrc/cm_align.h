@@ -252,33 +252,67 @@ CM_HD int cm_code(uint8_t c, int bad) {
 }
 CM_HD int cm_code_at(const uint8_t *p0, int step, int len, int c, int bad) { return (c >= 0 && c < len) ? cm_code(p0[c * step], bad) : bad; }
 
-template <int W, int KP>
-CM_HD void cm_xdrop_step(int (&X)[2 * W + 3], const int (&SW)[W + 1], const int (&TW)[W + 1], int k, int q, int lb, int ub, int mat, int mis,
-                         int ind, int xd, int pre, int &cur, int &best_i, int &best_j, int &new_ub, uint32_t &cells) {
+// State of one X-drop run (registers after inlining).
+template <int W>
+struct XdropState {
+    int X[2 * W + 3];
+    int SW[W + 1], TW[W + 1];
+    int pre, cur, lb, ub, pre_ub, best_i, best_k;
+    uint32_t cells;
+};
+
+// One anti-diagonal k = 2q + KP.  EARLY: k may be <= W (boundary cells dpx[k][0], dpx[0][k] still enter the band).
+// Row indices are handled relative to q (h = i - q is a compile-time constant per slot); the cell count of a diagonal
+// is ub - lb + 1 (every i in [lb, ub] has a slot in the band); the best cell is kept as (i, k).
+template <int W, int KP, bool EARLY>
+CM_HD void cm_xdrop_step(XdropState<W> &S, int k, int q, int mat, int mis, int ind, int xd, int &new_ub) {
     const int NEG = -CM_DPTINF;
     constexpr int LO = -(W / 2 + 1);
+    const int lq = S.lb - q, uq = S.ub - q, lim = S.pre - xd;
+    int nub_h = -1000;
+    S.cells += (uint32_t) (S.ub - S.lb + 1);
 #pragma unroll
     for (int e = 1; e <= 2 * W + 1; e++) {
         const int d = e - W - 1;
         if (((d + KP) & 1) != 0) continue;          // slot belongs to the other parity
         const int h = (KP + d) / 2;                 // exact: KP + d is even
-        const int i = q + h, j = k - i;
         int v;
-        if (i >= lb && i <= ub) {
-            int sc = SW[h - 1 - LO] == TW[(KP - d) / 2 - 1 - LO] ? mat : mis;
-            v = X[e] + sc;
-            int a = X[e - 1] + ind, b = X[e + 1] + ind;
+        if (h >= lq && h <= uq) {
+            int sc = S.SW[h - 1 - LO] == S.TW[(KP - d) / 2 - 1 - LO] ? mat : mis;
+            v = S.X[e] + sc;
+            int a = S.X[e - 1] + ind, b = S.X[e + 1] + ind;
             v = v > a ? v : a;
             v = v > b ? v : b;
-            cells++;
-            if (v >= cur) { cur = v; best_i = i; best_j = j; }
-            if (v + xd < pre) v = NEG;
-            if (v > NEG) new_ub = i;
+            if (v >= S.cur) { S.cur = v; S.best_i = q + h; S.best_k = k; }
+            if (v < lim) v = NEG;                   // v + xdrop < pre_optimum
+            if (v > NEG) nub_h = h;                 // h ascends with e: the last live cell wins
         } else {
-            v = (k <= W && (d == k || d == -k)) ? k * ind : NEG;
+            v = (EARLY && k <= W && (d == k || d == -k)) ? k * ind : NEG;
         }
-        X[e] = v;
+        S.X[e] = v;
     }
+    new_ub = nub_h > -1000 ? q + nub_h : -1;
+}
+
+// anti-diagonals 2q and 2q + 1; true = the run is over
+template <int W, bool EARLY>
+CM_HD bool cm_xdrop_pair(XdropState<W> &S, int q, int K, int n, int m, int mat, int mis, int ind, int xd) {
+#pragma unroll
+    for (int kp = 0; kp < 2; kp++) {
+        const int k = 2 * q + kp;
+        if (k > K) return true;
+        int new_ub;
+        if (kp) cm_xdrop_step<W, 1, EARLY>(S, k, q, mat, mis, ind, xd, new_ub);
+        else cm_xdrop_step<W, 0, EARLY>(S, k, q, mat, mis, ind, xd, new_ub);
+        const bool even_kw = ((kp ^ W) & 1) == 0;   // (k - W) % 2 == 0
+        const bool past = !EARLY || k > W;
+        if (k - S.lb == m || (past && even_kw)) ++S.lb;
+        if (S.ub < n && (!past || !even_kw)) ++S.ub;
+        if ((S.pre_ub == -1 && new_ub == -1) || S.lb > S.ub) return true;
+        S.pre_ub = new_ub;
+        if (S.cur > S.pre) S.pre = S.cur;
+    }
+    return false;
 }
 
 template <int W>
@@ -290,50 +324,38 @@ CM_HD void cm_xdrop_reg(const uint8_t *s, int n, const uint8_t *t, int m, bool r
     on_t = 0;
     score = 0;
     if (m <= 0 || n <= 0) return;
-    int X[2 * W + 3];
+    XdropState<W> S;
 #pragma unroll
-    for (int e = 0; e < 2 * W + 3; e++) X[e] = NEG;
-    X[W + 1] = 0;                                  // dpx[0][0]  (anti-diagonal 0)
-    if (W >= 1) { X[W + 2] = ind; X[W] = ind; }    // dpx[1][0], dpx[0][1]  (anti-diagonal 1)
+    for (int e = 0; e < 2 * W + 3; e++) S.X[e] = NEG;
+    S.X[W + 1] = 0;                                    // dpx[0][0]  (anti-diagonal 0)
+    if (W >= 1) { S.X[W + 2] = ind; S.X[W] = ind; }    // dpx[1][0], dpx[0][1]  (anti-diagonal 1)
     constexpr int LO = -(W / 2 + 1), HI = (W + 1) / 2 - 1;
     const uint8_t *s0 = rev ? s + n - 1 : s, *t0 = rev ? t + m - 1 : t;
     const int step = rev ? -1 : 1;
-    int SW[W + 1], TW[W + 1];
 #pragma unroll
-    for (int x = 0; x <= W; x++) {                 // window of q = 1
-        SW[x] = cm_code_at(s0, step, n, 1 + LO + x, 1);
-        TW[x] = cm_code_at(t0, step, m, 1 + LO + x, 2);
+    for (int x = 0; x <= W; x++) {                     // window of q = 1
+        S.SW[x] = cm_code_at(s0, step, n, 1 + LO + x, 1);
+        S.TW[x] = cm_code_at(t0, step, m, 1 + LO + x, 2);
     }
-    int pre = 0, cur = 0, lb = 1, ub = 1, pre_ub = 0, best_i = 0, best_j = 0;
-    uint32_t cells = 0;
+    S.pre = 0; S.cur = 0; S.lb = 1; S.ub = 1; S.pre_ub = 0; S.best_i = 0; S.best_k = 0; S.cells = 0;
     const int K = m + n;
     for (int q = 1; 2 * q <= K; ++q) {
-        const int ns = cm_code_at(s0, step, n, q + 1 + HI, 1), nt = cm_code_at(t0, step, m, q + 1 + HI, 2);   // for q + 1
-        bool stop = false;
-#pragma unroll
-        for (int kp = 0; kp < 2; kp++) {
-            const int k = 2 * q + kp;
-            if (k > K) { stop = true; break; }
-            int new_ub = -1;
-            if (kp) cm_xdrop_step<W, 1>(X, SW, TW, k, q, lb, ub, mat, mis, ind, xd, pre, cur, best_i, best_j, new_ub, cells);
-            else cm_xdrop_step<W, 0>(X, SW, TW, k, q, lb, ub, mat, mis, ind, xd, pre, cur, best_i, best_j, new_ub, cells);
-            int lb_t = k - lb;
-            if (lb_t == m || (k > W && ((k - W) % 2 == 0))) ++lb;
-            if (ub < n && (k <= W || (k > W && ((k - W) % 2 == 1)))) ++ub;
-            if ((pre_ub == -1 && new_ub == -1) || lb > ub) { stop = true; break; }
-            pre_ub = new_ub;
-            if (cur > pre) pre = cur;
-        }
+        // raw bytes of the characters that enter the windows at q + 1: loaded here, first used after the two anti-diagonals
+        const int cn = q + 1 + HI;
+        const bool in_s = cn < n, in_t = cn < m;
+        const uint8_t rs = in_s ? s0[cn * step] : (uint8_t) 0, rt = in_t ? t0[cn * step] : (uint8_t) 0;
+        const bool stop = (2 * q <= W) ? cm_xdrop_pair<W, true>(S, q, K, n, m, mat, mis, ind, xd)
+                                       : cm_xdrop_pair<W, false>(S, q, K, n, m, mat, mis, ind, xd);
         if (stop) break;
 #pragma unroll
-        for (int x = 0; x < W; x++) { SW[x] = SW[x + 1]; TW[x] = TW[x + 1]; }
-        SW[W] = ns;
-        TW[W] = nt;
+        for (int x = 0; x < W; x++) { S.SW[x] = S.SW[x + 1]; S.TW[x] = S.TW[x + 1]; }
+        S.SW[W] = in_s ? cm_code(rs, 1) : 1;
+        S.TW[W] = in_t ? cm_code(rt, 2) : 2;
     }
-    if (st) st->xdrop_cells += cells;
-    on_s = best_i;
-    on_t = best_j;
-    score = cur;
+    if (st) st->xdrop_cells += S.cells;
+    on_s = S.best_i;
+    on_t = S.best_k - S.best_i;
+    score = S.cur;
 }
 
 CM_HDN void cm_xdrop(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &on_s, int &on_t, int &score,
