@@ -171,6 +171,28 @@ def test_t1_single_end_k22_scan2_live_reference(tmp_path):
     m.close()
 
 
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_c2_sample_live_reference(tmp_path):
+    """The bench workload itself (C2: 100 Mb, 15 000 + 500 repeat families, N gaps), first 100 000 pairs, against the
+    reference run on this box: the repeat-rich strands go through k_chain_warp, the many-candidate pairs through
+    k_process_pe_warp (batch <= 300 k), everything else through the thread-per-unit kernels."""
+    from circminer_b200 import workload
+    from circminer_b200.api import fresh_mreads
+    n = 100_000
+    dump = live_dump(str(tmp_path / "c2.npz"), workload="C2", contig_size=1_100_000_000, pairs=n, no_stage_dumps=True)
+    w = workload.prepare("C2", str(tmp_path / "c2"), n_pairs=n)
+    check_reads(w, dump)
+    m = _mapper(w)
+    mr = fresh_mreads(n)
+    for c in range(int(dump["n_contigs"])):
+        mr = compare_contig(m, c, w, dump, mr, stages=("pe",))
+    cnt = m.counters()
+    assert cnt["pairs"] == n * int(dump["n_contigs"])
+    types = np.bincount(mr["type"], minlength=14)
+    assert types[0] > 0.5 * n and types[3] > 1000
+    m.close()
+
+
 def test_shared_context_gives_the_same_results(w_t0):
     """cm_gpu_create_shared: a second context over the parent's resident contigs, used from a second host thread."""
     import threading
