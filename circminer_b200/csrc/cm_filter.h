@@ -470,31 +470,32 @@ CM_HDN int cm_process_mates(FilterCtx &f, const StrandView &fw, const StrandView
     int f_iv[CM_MAX_CHAINS], b_iv[CM_MAX_CHAINS];
     for (int i = 0; i < nf; i++) f_iv[i] = cm_location_overlap_ne(a, cl_chain(fw.chains, i).frags[0].rpos);
     for (int j = 0; j < nb; j++) b_iv[j] = cm_location_overlap_ne(a, cl_chain(bw.chains, j).frags[0].rpos);
-    uint8_t code[(CM_MAX_CHAINS * CM_MAX_CHAINS + 3) / 4];
-    for (unsigned q = 0; q < sizeof code; q++) code[q] = 0;
+    uint64_t rowc[CM_MAX_CHAINS];   // row i of the code matrix, 2 bits per j
     uint32_t f_paired = 0, b_paired = 0;
     for (int i = 0; i < nf; i++) {
         ChainView ci = cl_chain(fw.chains, i);
+        uint64_t r = 0;
         for (int j = 0; j < nb; j++) {
             int c = cm_pair_code(a, p, ci, cl_chain(bw.chains, j), f_iv[i], b_iv[j], saved_type);
             if (c) {
-                int q = i * CM_MAX_CHAINS + j;
-                code[q >> 2] |= (uint8_t) (c << ((q & 3) * 2));
-                f_paired |= 1u << i;
+                r |= (uint64_t) c << (2 * j);
                 b_paired |= 1u << j;
             }
         }
+        rowc[i] = r;
+        if (r) f_paired |= 1u << i;
     }
     MatesAcc acc;
     acc.min_ret1 = acc.min_ret2 = CM_ORPHAN;
     acc.r1_genic = acc.r2_genic = false;
-    for (int i = 0; i < nf; i++)
-        for (int j = 0; j < nb; j++) {
-            int q = i * CM_MAX_CHAINS + j;
-            int c = (code[q >> 2] >> ((q & 3) * 2)) & 3;
+    for (int i = 0; i < nf; i++) {
+        uint64_t r = rowc[i];
+        for (int j = 0; r; j++, r >>= 2) {
+            const int c = (int) (r & 3u);
             if (!c) continue;
             if (cm_mates_candidate(f, fw, bw, i, j, c - 1, f_iv[i], b_iv[j], mr, r1_forward, acc)) return CM_CONCRD;
         }
+    }
     return cm_mates_leftovers(f, fw, bw, mr, f_paired, b_paired, acc);
 }
 

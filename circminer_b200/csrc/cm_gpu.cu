@@ -75,6 +75,7 @@ struct cm_gpu_ctx {
     // up to heavy_pair_batch pairs, where such a pair is the critical path of the launch (6.3 -> 1.3 ms at 125 k pairs
     // of C2); off for larger batches, which are throughput-bound and where the warp kernel costs more than it saves.
     uint32_t heavy_pair_th = 16, heavy_pair_batch = 300000;
+    int pair_sig = 2;
     bool heavy_pair_forced = false;
     uint32_t last_heavy_pairs = 0;
     int spec_k = CM_MAX_CHAINS;            // CM_GPU_SPEC_K: leading chains per strand handed to the dense pre-alignment kernel
@@ -203,6 +204,7 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
     cudaStreamSynchronize(ctx->stream);
     if (const char *e = getenv("CM_GPU_REC_MULT")) ctx->rec_mult = (uint32_t) atoi(e);
     if (const char *e = getenv("CM_GPU_HEAVY_TH")) { int t = atoi(e); ctx->heavy_th = (uint32_t) (t < 0 ? 0 : (t > 254 ? 254 : t)); }
+    if (const char *e = getenv("CM_GPU_PAIR_SIG")) ctx->pair_sig = atoi(e);
     if (const char *e = getenv("CM_GPU_HEAVY_PAIR_TH")) { ctx->heavy_pair_th = (uint32_t) atol(e); ctx->heavy_pair_forced = true; }
     if (const char *e = getenv("CM_GPU_SPEC_K")) ctx->spec_k = atoi(e) < 1 ? 1 : atoi(e);
     if (const char *e = getenv("CM_GPU_NO_WALK_SPEC")) ctx->no_walk_spec = atoi(e) != 0;

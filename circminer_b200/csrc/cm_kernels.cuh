@@ -208,7 +208,7 @@ __global__ void k_strand_key(const __grid_constant__ DevView v, const uint32_t *
 
 // pair: chain counts of the four strands, attempt order, and the shape of the leading chains
 __global__ void k_pair_key(const __grid_constant__ DevView v, const __grid_constant__ BatchDev b, uint32_t n_pairs, unsigned long long *__restrict__ key, uint32_t *__restrict__ idx,
-                           uint32_t heavy_th, uint32_t *__restrict__ n_heavy) {
+                           uint32_t heavy_th, uint32_t *__restrict__ n_heavy, int sig_mode) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_pairs) return;
     unsigned long long k = 0;
@@ -235,9 +235,24 @@ __global__ void k_pair_key(const __grid_constant__ DevView v, const __grid_const
         }
         k = (k << 15) | sig;
     }
+    // how far the transcript walk of the leading chains' ends went (EndSpec::n): ends that leave their exon take
+    // the long way through extend_left / extend_right
+    if (sig_mode) {
+        unsigned w = 0;
+        for (int q = 0; q < 2; q++) {
+            uint32_t s = 4 * i + (q ? sb : sa);
+            for (int e = 0; e < 2; e++) {
+                unsigned nn = 0;
+                if (b.chain_cnt[s] > 0 && b.spec && b.chain_base && b.spec_k > 0) nn = b.spec[2 * (size_t) b.chain_base[s] + e].n;
+                if (sig_mode == 1) nn = nn ? 1u : 0u;
+                w = (w << 2) | (nn > 3u ? 3u : nn);
+            }
+        }
+        k = (k << 8) | w;
+    }
     // pairs with more than heavy_th candidate chain pairs (both attempts) sort to the front: one warp each
     const bool heavy = (uint32_t) (cnt[0] * cnt[3] + cnt[2] * cnt[1]) > heavy_th;
-    if (heavy) k |= 1ull << 43;
+    if (heavy) k |= 1ull << (sig_mode ? 51 : 43);
     key[i] = k;
     idx[i] = i;
     unsigned hm = __ballot_sync(__activemask(), heavy);
