@@ -644,42 +644,64 @@ static int build_dirx(cm_gpu_ctx *ctx, ContigHost *ch) {
 // One warp per input read.  Besides the two ASCII rows it emits the (hv, cv) pair of every seed slot
 // (hashVal / checkSumVal, lib/mrsfast/Common.c:199-225) so that the gather kernel never touches read
 // bytes: hv = -1 / cv = -1 on a non-ACGT base, hv = -2 when the slot holds no seed (q + k > len).
-__global__ void k_make_strands(const char *__restrict__ s1, const char *__restrict__ s2, const uint16_t *__restrict__ l1,
+#define CM_PREP_BLOCK 256
+__global__ void __launch_bounds__(CM_PREP_BLOCK) k_make_strands(const char *__restrict__ s1, const char *__restrict__ s2, const uint16_t *__restrict__ l1,
                                const uint16_t *__restrict__ l2, uint32_t n, uint32_t in_stride, uint32_t stride,
                                uint8_t *__restrict__ strands, uint16_t *__restrict__ slen, int kmer, int F,
                                int2 *__restrict__ seed_key) {
+    // byte -> complement and byte -> 2-bit code (0x80: not ACGT) tables, one entry per thread of the block
+    __shared__ uint8_t lut_comp[256], lut_nh[256];
+    extern __shared__ __align__(16) uint8_t warp_buf[];   // per warp: raw read, forward codes, reverse-complement codes
+    {
+        int v = cm_nhval((uint8_t) threadIdx.x);
+        lut_comp[threadIdx.x] = cm_comp((uint8_t) threadIdx.x);
+        lut_nh[threadIdx.x] = v < 0 ? 0x80 : (uint8_t) v;
+    }
+    __syncthreads();
     uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     uint32_t n_reads = s2 ? 2 * n : n;
     if (warp >= n_reads) return;
     uint32_t i = s2 ? warp >> 1 : warp;
     bool second = s2 && (warp & 1);
     const uint8_t *src = (const uint8_t *) (second ? s2 : s1) + (size_t) i * in_stride;
-    uint32_t len = second ? l2[i] : l1[i];
-    uint8_t *fw = strands + (size_t) (2 * warp) * stride;
-    uint8_t *rc = fw + stride;
-    for (uint32_t j = lane; j < stride; j += 32) {
-        fw[j] = j < len ? src[j] : 0;
-        rc[j] = j < len ? cm_comp(src[len - 1 - j]) : 0;
+    const uint32_t len = second ? l2[i] : l1[i];
+    uint8_t *raw = warp_buf + (size_t) (threadIdx.x >> 5) * 3 * stride, *cf = raw + stride, *cr = cf + stride;
+    for (uint32_t j = lane; j < len; j += 32) raw[j] = src[j];
+    __syncwarp();
+    uint32_t *fw = (uint32_t *) (strands + (size_t) (2 * warp) * stride), *rc = fw + stride / 4;
+    for (uint32_t w = lane; w < stride / 4; w += 32) {
+        uint32_t wf = 0, wr = 0, kf = 0, kr = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < 4; k++) {
+            const uint32_t j = 4 * w + k;
+            const uint8_t c = j < len ? raw[j] : 0, r = j < len ? lut_comp[raw[len - 1 - j]] : 0;
+            wf |= (uint32_t) c << (8 * k);
+            wr |= (uint32_t) r << (8 * k);
+            kf |= (uint32_t) lut_nh[c] << (8 * k);
+            kr |= (uint32_t) lut_nh[r] << (8 * k);
+        }
+        fw[w] = wf;
+        rc[w] = wr;
+        ((uint32_t *) cf)[w] = kf;
+        ((uint32_t *) cr)[w] = kr;
     }
     if (lane == 0) {
         slen[2 * warp] = (uint16_t) len;
         slen[2 * warp + 1] = (uint16_t) len;
     }
+    __syncwarp();
     for (int idx = (int) lane; idx < 2 * F; idx += 32) {
         int str = idx / F, t = idx - str * F;
         int q = t * kmer;
         int hv = -2, cv = 0;
         if (q + kmer <= (int) len) {
+            const uint8_t *code = (str ? cr : cf) + q;
+            uint32_t bad_h = 0, bad_c = 0;
             hv = 0;
-            bool bad_h = false, bad_c = false;
-            for (int x = 0; x < kmer; x++) {
-                uint8_t c = str ? cm_comp(src[len - 1 - (q + x)]) : src[q + x];
-                int v = cm_nhval(c);
-                if (x < CM_WINDOW) { if (v < 0) bad_h = true; hv = (hv << 2) | (v & 3); }
-                else { if (v < 0) bad_c = true; cv = (cv << 2) | (v & 3); }
-            }
-            if (bad_h) hv = -1;
-            if (bad_c) cv = -1;
+            for (int x = 0; x < CM_WINDOW; x++) { uint32_t v = code[x]; bad_h |= v; hv = (hv << 2) | (int) (v & 3u); }
+            for (int x = CM_WINDOW; x < kmer; x++) { uint32_t v = code[x]; bad_c |= v; cv = (cv << 2) | (int) (v & 3u); }
+            if (bad_h & 0x80u) hv = -1;
+            if (bad_c & 0x80u) cv = -1;
         }
         seed_key[((size_t) 2 * warp + str) * F + t] = make_int2(hv, cv);
     }
@@ -729,7 +751,7 @@ static int launch_prep(cm_gpu_ctx *ctx, uint32_t in_stride) {
     if (!ctx->n_pairs) return CM_OK;
     uint32_t n_reads = ctx->staged_pe ? 2 * ctx->n_pairs : ctx->n_pairs;
     ENSURE(ctx, ctx->seed_key, (size_t) ctx->n_strands * ctx->batch_F * sizeof(int2));
-    k_make_strands<<<grid_for((size_t) n_reads * 32, 256), 256, 0, ctx->stream>>>(
+    k_make_strands<<<grid_for((size_t) n_reads * 32, CM_PREP_BLOCK), CM_PREP_BLOCK, (size_t) (CM_PREP_BLOCK / 32) * 3 * ctx->stride, ctx->stream>>>(
         (const char *) ctx->in_seq1.p, ctx->staged_pe ? (const char *) ctx->in_seq2.p : nullptr,
         (const uint16_t *) ctx->in_len1.p, (const uint16_t *) ctx->in_len2.p, ctx->n_pairs, in_stride, ctx->stride,
         (uint8_t *) ctx->strands.p, (uint16_t *) ctx->strand_len.p, ctx->p.kmer, ctx->batch_F, (int2 *) ctx->seed_key.p);
