@@ -161,6 +161,8 @@ extern "C" void cm_mread_init(cm_mread *m, const cm_params *p) {
 
 extern "C" const char *cm_gpu_last_error(const cm_gpu_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
 
+__global__ void k_init_prep_lut();   // tables of the read staging kernel, below
+
 extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **out) {
     if (!params || !out) return fail(nullptr, CM_ERR_ARG, "null argument");
     *out = nullptr;
@@ -189,6 +191,7 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
     }
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
     cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking);
+    k_init_prep_lut<<<1, 256, 0, ctx->stream>>>();
     cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming);
     {   // the index gathers are 32-byte random reads: ask L2 not to promote misses to 64/128-byte DRAM fetches
@@ -645,18 +648,21 @@ static int build_dirx(cm_gpu_ctx *ctx, ContigHost *ch) {
 // (hashVal / checkSumVal, lib/mrsfast/Common.c:199-225) so that the gather kernel never touches read
 // bytes: hv = -1 / cv = -1 on a non-ACGT base, hv = -2 when the slot holds no seed (q + k > len).
 #define CM_PREP_BLOCK 256
+// byte -> complement ([0..255]) and byte -> 2-bit code, 0x80 when not ACGT ([256..511]); written once per context
+__device__ uint8_t g_prep_lut[512];
+__global__ void k_init_prep_lut() {
+    int v = cm_nhval((uint8_t) threadIdx.x);
+    g_prep_lut[threadIdx.x] = cm_comp((uint8_t) threadIdx.x);
+    g_prep_lut[256 + threadIdx.x] = v < 0 ? 0x80 : (uint8_t) v;
+}
 __global__ void __launch_bounds__(CM_PREP_BLOCK) k_make_strands(const char *__restrict__ s1, const char *__restrict__ s2, const uint16_t *__restrict__ l1,
                                const uint16_t *__restrict__ l2, uint32_t n, uint32_t in_stride, uint32_t stride,
                                uint8_t *__restrict__ strands, uint16_t *__restrict__ slen, int kmer, int F,
                                int2 *__restrict__ seed_key) {
-    // byte -> complement and byte -> 2-bit code (0x80: not ACGT) tables, one entry per thread of the block
     __shared__ uint8_t lut_comp[256], lut_nh[256];
-    extern __shared__ __align__(16) uint8_t warp_buf[];   // per warp: raw read, forward codes, reverse-complement codes
-    {
-        int v = cm_nhval((uint8_t) threadIdx.x);
-        lut_comp[threadIdx.x] = cm_comp((uint8_t) threadIdx.x);
-        lut_nh[threadIdx.x] = v < 0 ? 0x80 : (uint8_t) v;
-    }
+    extern __shared__ __align__(16) uint8_t warp_buf[];   // per warp: raw read (+ 4 bytes of alignment slack), forward codes, reverse-complement codes
+    lut_comp[threadIdx.x] = g_prep_lut[threadIdx.x];
+    lut_nh[threadIdx.x] = g_prep_lut[256 + threadIdx.x];
     __syncthreads();
     uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     uint32_t n_reads = s2 ? 2 * n : n;
@@ -665,8 +671,14 @@ __global__ void __launch_bounds__(CM_PREP_BLOCK) k_make_strands(const char *__re
     bool second = s2 && (warp & 1);
     const uint8_t *src = (const uint8_t *) (second ? s2 : s1) + (size_t) i * in_stride;
     const uint32_t len = second ? l2[i] : l1[i];
-    uint8_t *raw = warp_buf + (size_t) (threadIdx.x >> 5) * 3 * stride, *cf = raw + stride, *cr = cf + stride;
-    for (uint32_t j = lane; j < len; j += 32) raw[j] = src[j];
+    uint8_t *wb = warp_buf + (size_t) (threadIdx.x >> 5) * (3 * stride + 16);
+    // the read as aligned words (rows of the upload are in_stride bytes apart: any alignment); the upload buffers carry
+    // 16 bytes of slack behind the last row
+    const uint32_t mis = (uint32_t) ((uintptr_t) src & 3u);
+    const uint32_t *src_w = (const uint32_t *) (src - mis);
+    for (uint32_t w = lane; 4 * w < mis + len; w += 32) ((uint32_t *) wb)[w] = src_w[w];
+    const uint8_t *raw = wb + mis;
+    uint8_t *cf = wb + stride + 16, *cr = cf + stride;
     __syncwarp();
     uint32_t *fw = (uint32_t *) (strands + (size_t) (2 * warp) * stride), *rc = fw + stride / 4;
     for (uint32_t w = lane; w < stride / 4; w += 32) {
@@ -724,12 +736,12 @@ static int stage_reads(cm_gpu_ctx *ctx, uint32_t n, const char *s1, const char *
     cudaStream_t st = ctx->stream;
     uint32_t stride = (max_len + 15) / 16 * 16;   // strand rows as long as this batch's longest read, not max_read_len
     uint32_t n_strands = (s2 ? 4u : 2u) * n;
-    ENSURE(ctx, ctx->in_seq1, (size_t) n * in_stride);
+    ENSURE(ctx, ctx->in_seq1, (size_t) n * in_stride + 16);
     ENSURE(ctx, ctx->in_len1, (size_t) n * 2);
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->in_seq1.p, s1, (size_t) n * in_stride, cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->in_len1.p, l1, (size_t) n * 2, cudaMemcpyHostToDevice, st));
     if (s2) {
-        ENSURE(ctx, ctx->in_seq2, (size_t) n * in_stride);
+        ENSURE(ctx, ctx->in_seq2, (size_t) n * in_stride + 16);
         ENSURE(ctx, ctx->in_len2, (size_t) n * 2);
         CUDA_TRY(ctx, cudaMemcpyAsync(ctx->in_seq2.p, s2, (size_t) n * in_stride, cudaMemcpyHostToDevice, st));
         CUDA_TRY(ctx, cudaMemcpyAsync(ctx->in_len2.p, l2, (size_t) n * 2, cudaMemcpyHostToDevice, st));
@@ -751,7 +763,7 @@ static int launch_prep(cm_gpu_ctx *ctx, uint32_t in_stride) {
     if (!ctx->n_pairs) return CM_OK;
     uint32_t n_reads = ctx->staged_pe ? 2 * ctx->n_pairs : ctx->n_pairs;
     ENSURE(ctx, ctx->seed_key, (size_t) ctx->n_strands * ctx->batch_F * sizeof(int2));
-    k_make_strands<<<grid_for((size_t) n_reads * 32, CM_PREP_BLOCK), CM_PREP_BLOCK, (size_t) (CM_PREP_BLOCK / 32) * 3 * ctx->stride, ctx->stream>>>(
+    k_make_strands<<<grid_for((size_t) n_reads * 32, CM_PREP_BLOCK), CM_PREP_BLOCK, (size_t) (CM_PREP_BLOCK / 32) * (3 * ctx->stride + 16), ctx->stream>>>(
         (const char *) ctx->in_seq1.p, ctx->staged_pe ? (const char *) ctx->in_seq2.p : nullptr,
         (const uint16_t *) ctx->in_len1.p, (const uint16_t *) ctx->in_len2.p, ctx->n_pairs, in_stride, ctx->stride,
         (uint8_t *) ctx->strands.p, (uint16_t *) ctx->strand_len.p, ctx->p.kmer, ctx->batch_F, (int2 *) ctx->seed_key.p);

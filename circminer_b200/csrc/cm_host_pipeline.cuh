@@ -196,8 +196,9 @@ static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) 
         ENSURE(ctx, ctx->ovf_n, 8);
         uint32_t *d_heavy = (uint32_t *) ctx->ovf_n.p + 1;
         CUDA_TRY(ctx, cudaMemsetAsync(d_heavy, 0, 4, st));
+        const bool split_heavy = ctx->heavy_pair_forced || n <= ctx->heavy_pair_batch;
         k_pair_key<<<grid_for(n, 256), 256, 0, st>>>(v, b, n, (unsigned long long *) ctx->key64[0].p, (uint32_t *) ctx->perm[0].p,
-                                                     (ctx->heavy_pair_forced || n <= ctx->heavy_pair_batch) ? ctx->heavy_pair_th : 0xFFFFFFFFu, d_heavy, ctx->pair_sig);
+                                                     split_heavy ? ctx->heavy_pair_th : 0xFFFFFFFFu, d_heavy, ctx->pair_sig);
         size_t tb = 0;
         cub::DeviceRadixSort::SortPairsDescending(nullptr, tb, (const unsigned long long *) ctx->key64[0].p, (unsigned long long *) ctx->key64[1].p,
                                         (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, ctx->pair_sig ? 52 : 44, st);
@@ -206,8 +207,10 @@ static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) 
                                         (const uint32_t *) ctx->perm[0].p, (uint32_t *) ctx->perm[1].p, (int) n, 0, ctx->pair_sig ? 52 : 44, st);
         ctx->launches += 2;
         uint32_t n_heavy = 0;
-        CUDA_TRY(ctx, cudaMemcpyAsync(&n_heavy, d_heavy, 4, cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        if (split_heavy) {   // the only host round trip of this stage; none when every pair takes the thread kernel
+            CUDA_TRY(ctx, cudaMemcpyAsync(&n_heavy, d_heavy, 4, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        }
         DBG_SYNC(ctx, "k_pair_key + sort");
         ctx->last_heavy_pairs = n_heavy;
         if (n_heavy) {   // heavy pairs beside the light ones, on the side stream
