@@ -43,9 +43,80 @@ struct AlignStats {      // roofline numerators
     uint64_t xdrop_cells, edit_cells, xdrop_calls, edit_calls;
 };
 
+// ---- banded edit DP with the band in registers ---------------------------------------------
+// Same recurrence, same arithmetic and the same DPTINF guard values as the banded branch of
+// cm_edit_last_column below, for a compile-time band W: one array of 2W+3 slots updated in place
+// (slot d of column j reads its own old value = dp[i-1][j-1], the old slot d+1 = dp[i][j-1] and the new
+// slot d-1 = dp[i-1][j]), and the 2W+1 characters of s under the band in a sliding window of codes
+// (0..3 = ACGT ignoring case, 4 = anything else in s, 5 = anything else in t: never equal).
+CM_HD uint32_t cm_base_code(uint8_t c, uint32_t other) {
+    const uint8_t u = c & 0xDF;
+    return u == 'A' ? 0u : u == 'C' ? 1u : u == 'G' ? 2u : u == 'T' ? 3u : other;
+}
+template <int W, bool CHECK>
+CM_HD void cm_edit_col_reg(uint32_t (&a)[2 * W + 3], const uint32_t (&win)[2 * W + 1], uint32_t tc, int j, int n) {
+    // rows of this column: i = j - W - 1 + d for slot d in [1, 2W+1]
+#pragma unroll
+    for (int d = 1; d <= 2 * W + 1; d++) {
+        uint32_t v = a[d] + (win[d - 1] == tc ? 0u : 1u);
+        const uint32_t x = a[d - 1] + 1, y = a[d + 1] + 1;
+        v = v < x ? v : x;
+        v = v < y ? v : y;
+        if (CHECK) {
+            const int i = j - W - 1 + d;
+            if (i < 1 || i > n) v = CM_DPTINF;
+            if (i == 0) v = (uint32_t) j;   // row 0: dp[0][j] = j (only while j <= W)
+        }
+        a[d] = v;
+    }
+}
+template <int W>
+CM_HD void cm_edit_banded_reg(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, int lo, int hi, uint32_t *out, AlignStats *st) {
+    uint32_t a[2 * W + 3], win[2 * W + 1];
+#pragma unroll
+    for (int d = 0; d < 2 * W + 3; d++) a[d] = CM_DPTINF;
+#pragma unroll
+    for (int i = 0; i <= W; i++) a[i + W + 1] = (uint32_t) i;
+    // window of column 1: slot d holds s[i-1] with i = d - W, so characters -W .. W of s
+#pragma unroll
+    for (int d = 1; d <= 2 * W + 1; d++) {
+        const int x = d - W - 1;
+        win[d - 1] = (x >= 0 && x < n) ? cm_base_code(cm_at(s, n, x, rev), 4u) : 4u;
+    }
+    const int sstep = rev ? -1 : 1, tstep = rev ? -1 : 1;
+    const uint8_t *sp = rev ? s + (n - 1 - (W + 1)) : s + (W + 1);   // character W+1 of s: enters the window at column 2
+    const uint8_t *tp = rev ? t + (m - 1) : t;
+    uint64_t cells = 0;
+    for (int j = 1; j <= m; j++) {
+        const uint32_t tc = cm_base_code(*tp, 5u);
+        tp += tstep;
+        if (j > W && j + W <= n) cm_edit_col_reg<W, false>(a, win, tc, j, n);
+        else cm_edit_col_reg<W, true>(a, win, tc, j, n);
+        const int i0 = j - W < 1 ? 1 : j - W, i1 = j + W > n ? n : j + W;
+        cells += (uint64_t) (i1 >= i0 ? i1 - i0 + 1 : 0);
+        // slide: column j+1 sees characters j-W .. j+W
+#pragma unroll
+        for (int d = 0; d < 2 * W; d++) win[d] = win[d + 1];
+        win[2 * W] = (j + W < n) ? cm_base_code(*sp, 4u) : 4u;
+        sp += sstep;
+    }
+    if (st) st->edit_cells += cells;
+    for (int i = lo; i <= hi; i++) {
+        const int d = i - m + W + 1;
+        if (i >= 0 && i <= n && d >= 1 && d <= 2 * W + 1) {
+            uint32_t v = 0;
+#pragma unroll
+            for (int q = 1; q <= 2 * W + 1; q++) v = q == d ? a[q] : v;
+            out[i - lo] = v;
+        }
+    }
+}
+
 // ---- unit-cost edit DP, last column ------------------------------------------------------
 // Fills col[i] = dp[i][m] for the rows the callers read, i in [lo, hi]; entries outside are DPTINF.
 // Banded when the reference bands (n > 2w and m > w), full otherwise.  rev: the *_reverse variant.
+CM_HDN void cm_edit_last_column_generic_banded(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, int w, int lo, int hi,
+                                               uint32_t *out, AlignStats *st);
 CM_HDN void cm_edit_last_column(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, int w, int lo, int hi,
                                 uint32_t *out /* [hi-lo+1] */, AlignStats *st) {
     if (st) st->edit_calls++;
@@ -74,6 +145,30 @@ CM_HDN void cm_edit_last_column(const uint8_t *s, int n, const uint8_t *t, int m
             if (i >= 0 && i <= n) out[i - lo] = col[i];
         return;
     }
+#if !defined(CM_EDIT_GENERIC_ONLY)
+    if (w == 3) {
+#ifdef CM_EDIT_CHECK
+        uint32_t chk[2 * CM_MAX_BAND + 1];
+        for (int i = lo; i <= hi; i++) chk[i - lo] = CM_DPTINF;
+        AlignStats st2 = {0, 0, 0, 0};
+        cm_edit_banded_reg<3>(s, n, t, m, rev, lo, hi, chk, &st2);
+        uint32_t ref_out[2 * CM_MAX_BAND + 1];
+        AlignStats st3 = {0, 0, 0, 0};
+        cm_edit_last_column_generic_banded(s, n, t, m, rev, w, lo, hi, ref_out, &st3);
+        for (int i = lo; i <= hi; i++)
+            if (chk[i - lo] != ref_out[i - lo] || st2.edit_cells != st3.edit_cells) __builtin_trap();
+#endif
+        cm_edit_banded_reg<3>(s, n, t, m, rev, lo, hi, out, st);
+        return;
+    }
+#endif
+    cm_edit_last_column_generic_banded(s, n, t, m, rev, w, lo, hi, out, st);
+}
+
+// the banded branch for any band width (arrays indexed at run time)
+CM_HDN void cm_edit_last_column_generic_banded(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, int w, int lo, int hi,
+                                               uint32_t *out, AlignStats *st) {
+    for (int i = lo; i <= hi; i++) out[i - lo] = CM_DPTINF;
     // band: column j holds rows i in [j-w, j+w]; slot d = i - j + w + 1, slots 0 and 2w+2 are the guard lines
     uint32_t prev[CM_BANDSZ], cur[CM_BANDSZ];
     const int B = 2 * w + 3;
