@@ -214,7 +214,43 @@ CM_HDN int cm_local_alignment(const uint8_t *s, int n, const uint8_t *t, int m, 
     return best.ed;
 }
 
+// One-side band (columns j in [i, i+W] of row i) in registers: slot d = j - i + 1, updated in place (its own old
+// value = dp[i-1][j-1], old slot d+1 = dp[i-1][j], new slot d-1 = dp[i][j-1]); the W+1 characters of t under the band
+// slide by one per row.  Same arithmetic and guards as the run-time-indexed loop in cm_one_side_banded.
+template <int W>
+CM_HD int cm_one_side_banded_reg(const uint8_t *s, int n, const uint8_t *t, int m) {
+    uint32_t a[W + 3], tw[W + 1];
+    a[0] = CM_DPTINF;
+    a[W + 2] = CM_DPTINF;
+#pragma unroll
+    for (int j = 0; j <= W; j++) {
+        a[j + 1] = (uint32_t) j;
+        tw[j] = j < m ? cm_base_code(t[j], 5u) : 5u;
+    }
+    for (int i = 1; i <= n; i++) {
+        const uint32_t sc = cm_base_code(s[i - 1], 4u);
+#pragma unroll
+        for (int d = 1; d <= W + 1; d++) {
+            uint32_t x = a[d] + (sc == tw[d - 1] ? 0u : 1u);
+            const uint32_t y = a[d + 1] + 1, z = a[d - 1] + 1;
+            x = x < y ? x : y;
+            x = x < z ? x : z;
+            a[d] = x;
+        }
+#pragma unroll
+        for (int k = 0; k < W; k++) tw[k] = tw[k + 1];
+        tw[W] = i + W < m ? cm_base_code(t[i + W], 5u) : 5u;
+    }
+    const int d = m - n + 1;
+    if (d < 1 || d > W + 1) return CM_DPTINF;
+    uint32_t v = 0;
+#pragma unroll
+    for (int q = 1; q <= W + 1; q++) v = q == d ? a[q] : v;
+    return (int) v;
+}
+
 // Alignment::global_one_side_banded_alignment: dp[n][m], rows i, columns j in [i, i+w]
+CM_HDN int cm_one_side_banded_generic(const uint8_t *s, int n, const uint8_t *t, int m, int w);
 CM_HDN int cm_one_side_banded(const uint8_t *s, int n, const uint8_t *t, int m, int w, AlignStats *st) {
     if (st) st->edit_calls++;
     if (w < 0 || n <= w) {
@@ -240,6 +276,23 @@ CM_HDN int cm_one_side_banded(const uint8_t *s, int n, const uint8_t *t, int m, 
         return (int) col[n];
     }
     if (w > CM_MAX_BAND) return CM_DPTINF;
+#if !defined(CM_EDIT_GENERIC_ONLY)
+    if (w <= 3) {
+        const int r = w == 0 ? cm_one_side_banded_reg<0>(s, n, t, m) : w == 1 ? cm_one_side_banded_reg<1>(s, n, t, m)
+                    : w == 2 ? cm_one_side_banded_reg<2>(s, n, t, m) : cm_one_side_banded_reg<3>(s, n, t, m);
+#ifdef CM_EDIT_CHECK
+        if (r != cm_one_side_banded_generic(s, n, t, m, w)) __builtin_trap();
+#endif
+        if (st) st->edit_cells += (uint64_t) n * (uint64_t) (w + 1);
+        return r;
+    }
+#endif
+    if (st) st->edit_cells += (uint64_t) n * (uint64_t) (w + 1);
+    return cm_one_side_banded_generic(s, n, t, m, w);
+}
+
+// the banded branch for any band width (arrays indexed at run time)
+CM_HDN int cm_one_side_banded_generic(const uint8_t *s, int n, const uint8_t *t, int m, int w) {
     // slot d = j - i + 1 in [1, w+1]; slots 0 and w+2 are dp[i][i-1] and dp[i-1][i+w] (= DPTINF)
     uint32_t prev[CM_MAX_BAND + 3], cur[CM_MAX_BAND + 3];
     for (int d = 0; d <= w + 2; d++) prev[d] = CM_DPTINF;
@@ -259,7 +312,6 @@ CM_HDN int cm_one_side_banded(const uint8_t *s, int n, const uint8_t *t, int m, 
         }
         for (int d = 0; d <= w + 2; d++) prev[d] = cur[d];
     }
-    if (st) st->edit_cells += (uint64_t) n * (uint64_t) (w + 1);
     int d = m - n + 1;
     if (d < 1 || d > w + 1) return CM_DPTINF;
     return (int) prev[d];
