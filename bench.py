@@ -146,11 +146,15 @@ def run_b200(a):
         keep.append(t)
         hb[k] = v
 
+    align_acc = np.zeros(2)
+
     def step_resident():
         ms = 0.0
         for c in range(n_contigs):
             m.run_staged(c, a.upto)
             ms += m.stage_ms()[4]
+            if a.upto >= 2:
+                align_acc[:] += m.align_ms()
         return ms
 
     # e2e: two contexts sharing the resident index (cm_gpu_create_shared), one host thread each, alternating
@@ -189,6 +193,7 @@ def run_b200(a):
     for _ in range(a.warmup):
         step_resident()
     m.counters(reset=True)
+    align_acc[:] = 0
     barrier()
     clk.mark()
     t0 = time.time()
@@ -249,6 +254,7 @@ def run_b200(a):
                          "frac": ach / peak, "traffic": traffic, "peak_source": how,
                          "algorithmic_bytes_per_launch": seed_bytes},
             "counters": {k: v / a.steps for k, v in ctr.items()},
+            "alignment": alignment_line(ctr, align_acc, stage_acc, a.steps),
             "prep_s": t_prep,
         }
         if not a.no_cpu_baseline and world == 1:
@@ -258,6 +264,23 @@ def run_b200(a):
     m.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def alignment_line(ctr, align_acc, stage_acc, steps):
+    """GCUPS of the banded DPs (X-drop + banded edit distance, src/align.cpp:166-723).  Cells are counted on the
+    device by every DP call (cm_counters); nearly all of them run in k_chain_spec / k_chain_walk, whose time is taken
+    with CUDA events on the launching stream.  INT32 roofline: one cell costs ~10 integer instructions (three adds,
+    compare/select chain, the character compare, band bookkeeping) -> peak cells/s = SMs x 128 lanes x clock / 10."""
+    cells = (ctr["xdrop_cells"] + ctr["edit_cells"]) / steps
+    ms = float(align_acc.sum()) / steps
+    if ms <= 0:
+        return None
+    gcups = cells / (ms * 1e-3) / 1e9
+    int32_peak_gcups = 148 * 128 * 1.965 / 10.0
+    return {"gcups": gcups, "cells_per_step": cells, "dp_calls_per_step": (ctr["xdrop_calls"] + ctr["edit_calls"]) / steps,
+            "k_chain_spec_ms": float(align_acc[0]) / steps, "k_chain_walk_ms": float(align_acc[1]) / steps,
+            "int32_peak_gcups": int32_peak_gcups, "frac_int32": gcups / int32_peak_gcups,
+            "note": "band 3 (7 cells per row), thread per DP, band in registers; peak assumes 10 INT32 instr per cell"}
 
 
 def cpu_baseline(a, datadir, n_pairs, threads, target_s=12.0):

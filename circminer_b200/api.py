@@ -308,6 +308,12 @@ class Mapper:
         self.lib.cm_gpu_last_stage_ms(self.ctx, a)
         return list(a)
 
+    def align_ms(self):
+        """[k_chain_spec, k_chain_walk] device ms of the last chain stage."""
+        a = (C.c_float * 2)()
+        self._chk(self.lib.cm_gpu_last_align_ms(self.ctx, a), "cm_gpu_last_align_ms")
+        return list(a)
+
     def counters(self, reset=False) -> dict:
         c = CmCounters()
         self._chk(self.lib.cm_gpu_get_counters(self.ctx, C.byref(c), int(reset)), "cm_gpu_get_counters")

@@ -37,7 +37,7 @@ struct cm_gpu_ctx {
     cm_params p{};
     int max_seg_cnt = 0, n_slots = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[6]{};
+    cudaEvent_t ev[7]{};   // [0..3] stage boundaries, [4..6] around k_chain_spec / k_chain_walk
     std::string err;
     std::vector<ContigHost> contigs;
     cm_gpu_ctx *parent = nullptr;     // cm_gpu_create_shared: index and annotation live in (and are owned by) the parent
@@ -46,6 +46,7 @@ struct cm_gpu_ctx {
     cm_counters *d_counters = nullptr;
     uint64_t launches = 0;
     float stage_ms[5] = {0, 0, 0, 0, 0};
+    bool align_timed = false;   // ev[4..6] were recorded by the last chain stage
 
     // staged batch (device resident)
     uint32_t n_pairs = 0;      // pairs (PE) or reads (SE)
@@ -288,6 +289,16 @@ extern "C" int cm_gpu_get_counters(cm_gpu_ctx *ctx, cm_counters *out, int reset)
 extern "C" int cm_gpu_last_stage_ms(cm_gpu_ctx *ctx, float out[5]) {
     if (!ctx || !out) return CM_ERR_ARG;
     for (int i = 0; i < 5; i++) out[i] = ctx->stage_ms[i];
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_last_align_ms(cm_gpu_ctx *ctx, float out[2]) {
+    if (!ctx || !out) return CM_ERR_ARG;
+    out[0] = out[1] = 0.f;
+    if (!ctx->align_timed) return CM_OK;
+    if (cudaEventSynchronize(ctx->ev[6]) != cudaSuccess) return CM_ERR_CUDA;
+    cudaEventElapsedTime(&out[0], ctx->ev[4], ctx->ev[5]);
+    cudaEventElapsedTime(&out[1], ctx->ev[5], ctx->ev[6]);
     return CM_OK;
 }
 

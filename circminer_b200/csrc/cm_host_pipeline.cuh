@@ -134,6 +134,7 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
         cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tb3, (const uint32_t *) spec_cnt, (uint32_t *) ctx->chain_base.p, (int) ns, st);
         ctx->launches += 2;
     }
+    ctx->align_timed = false;
     uint32_t last_base = 0, last_n = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&last_base, (uint32_t *) ctx->chain_base.p + (ns - 1), 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(&last_n, spec_cnt + (ns - 1), 4, cudaMemcpyDeviceToHost, st));
@@ -169,12 +170,16 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
         // spec_item[0] is free again after the sort: it becomes the walk queue (at most 2 ends per chain)
         uint32_t *walk_q = (uint32_t *) ctx->spec_item[0].p, *n_walk = (uint32_t *) ctx->ovf_n.p + 1;
         CUDA_TRY(ctx, cudaMemsetAsync(n_walk, 0, 4, st));
+        cudaEventRecord(ctx->ev[4], st);
         k_chain_spec<<<grid_for(n_items, 128), 128, 0, st>>>(v, b, (const uint32_t *) ctx->chain_ids.p, (const uint8_t *) ctx->spec_key[1].p,
                                                             (const uint32_t *) ctx->spec_item[1].p, n_chains, walk_q, n_walk, ctx->d_counters);
+        cudaEventRecord(ctx->ev[5], st);
         if (b.spec) {
             k_chain_walk<<<grid_for(2ull * n_chains, 128), 128, 0, st>>>(v, b, (const uint32_t *) ctx->chain_ids.p, walk_q, n_walk, ctx->d_counters);
             ctx->launches++;
         }
+        cudaEventRecord(ctx->ev[6], st);
+        ctx->align_timed = true;
         ctx->launches += 4;
         CUDA_TRY(ctx, cudaGetLastError());
         DBG_SYNC(ctx, "k_chain_spec");

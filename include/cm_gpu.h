@@ -136,6 +136,11 @@ int cm_gpu_get_counters(cm_gpu_ctx *ctx, cm_counters *out, int reset);
 /* device time (ms, CUDA events on the context's stream) of the stages of the last
  * batch call: [0] prep, [1] seed, [2] chain, [3] extend+classify, [4] total. */
 int cm_gpu_last_stage_ms(cm_gpu_ctx *ctx, float out[5]);
+/* device time (ms) of the dense alignment kernels of the last chain stage: [0] k_chain_spec (middle edit
+ * distance + X-drop of both read ends on the genome text, src/align.cpp:166-723), [1] k_chain_walk
+ * (the same DPs along transcripts, src/extend.cpp:37-920); with cm_counters.xdrop_cells + edit_cells
+ * this gives the GCUPS of the alignment stage. */
+int cm_gpu_last_align_ms(cm_gpu_ctx *ctx, float out[2]);
 
 /* ---- index / genome --------------------------------------------------- */
 /* Upload one packed contig straight from the reference's in-memory index right
