@@ -292,6 +292,16 @@ extern "C" int cm_gpu_last_stage_ms(cm_gpu_ctx *ctx, float out[5]) {
     return CM_OK;
 }
 
+extern "C" int cm_gpu_host_alloc(size_t bytes, void **out) {
+    if (!out) return CM_ERR_ARG;
+    *out = nullptr;
+    return cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable) == cudaSuccess ? CM_OK : CM_ERR_ALLOC;
+}
+
+extern "C" int cm_gpu_host_free(void *p) {
+    return !p || cudaFreeHost(p) == cudaSuccess ? CM_OK : CM_ERR_CUDA;
+}
+
 extern "C" int cm_gpu_last_align_ms(cm_gpu_ctx *ctx, float out[2]) {
     if (!ctx || !out) return CM_ERR_ARG;
     out[0] = out[1] = 0.f;

@@ -132,6 +132,11 @@ int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **out);
 int cm_gpu_create_shared(cm_gpu_ctx *parent, cm_gpu_ctx **out);
 int cm_gpu_destroy(cm_gpu_ctx *ctx);
 const char *cm_gpu_last_error(const cm_gpu_ctx *ctx);   /* ctx may be NULL: last create error */
+/* page-locked host memory for the batch buffers of the callers below (the reference allocates its per-thread
+ * scratch with malloc, src/circminer.cpp:163-191; pinned buffers let the H2D / D2H copies of a batch run at
+ * full PCIe speed and overlap kernels).  Any host pointer is accepted by the batch calls; these are optional. */
+int cm_gpu_host_alloc(size_t bytes, void **out);
+int cm_gpu_host_free(void *p);
 int cm_gpu_get_counters(cm_gpu_ctx *ctx, cm_counters *out, int reset);
 /* device time (ms, CUDA events on the context's stream) of the stages of the last
  * batch call: [0] prep, [1] seed, [2] chain, [3] extend+classify, [4] total. */

@@ -13,9 +13,12 @@
 #undef private
 #undef protected
 
+#include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -35,6 +38,8 @@ extern pthread_mutex_t buffer_lock;
 namespace {
 
 cm_gpu_ctx *g_ctx = nullptr;
+cm_params g_params;
+FilterArgs *g_fa = nullptr;   // mapping thread 0's arguments (the reference's per-thread scratch)
 std::vector<std::string> g_chr;   // chromosome names <-> cm_mread::chr_r1 / chr_r2 indices
 int g_loaded_contig = -1;
 
@@ -43,11 +48,24 @@ int g_loaded_contig = -1;
     exit(1);
 }
 
+// Called by the parsing threads of host_feed.h: g_chr never reallocates (reserved once), readers scan the
+// published prefix, a new name is appended under the mutex.
+std::atomic<size_t> g_nchr(0);
+std::mutex g_chr_mu;
+constexpr size_t CHR_CAP = 1 << 16;
+
 int chr_index(const std::string &name) {
     if (name == "-") return -1;
-    for (size_t j = 0; j < g_chr.size(); j++)
+    const size_t n0 = g_nchr.load(std::memory_order_acquire);
+    for (size_t j = 0; j < n0; j++)
         if (g_chr[j] == name) return (int) j;
+    std::lock_guard<std::mutex> lk(g_chr_mu);
+    if (g_chr.capacity() < CHR_CAP) g_chr.reserve(CHR_CAP);
+    for (size_t j = n0; j < g_chr.size(); j++)
+        if (g_chr[j] == name) return (int) j;
+    if (g_chr.size() >= CHR_CAP) { fprintf(stderr, "circminer_gpu: more than %zu chromosome names\n", CHR_CAP); exit(1); }
     g_chr.push_back(name);
+    g_nchr.store(g_chr.size(), std::memory_order_release);
     return (int) g_chr.size() - 1;
 }
 
@@ -73,6 +91,10 @@ void from_pod(const cm_mread *m, MatchedRead *r) {
     r->chr_r1 = m->chr_r1 >= 0 ? g_chr[m->chr_r1] : std::string("-");
     r->chr_r2 = m->chr_r2 >= 0 ? g_chr[m->chr_r2] : std::string("-");
 }
+
+}   // namespace
+#include "host_feed.h"
+namespace {
 
 // GTFParser tables of the current contig as the flat arrays of cm_annot_flat
 void upload_annotation(int c) {
@@ -112,12 +134,22 @@ void upload_annotation(int c) {
     for (auto &cc : gtf_parser.con2chr[c]) { chr_shift.push_back(cc.shift); chr_id.push_back(chr_index(cc.contig)); }
     const uint64_t n_bits = (uint64_t) _ih_refGenLen + 2;
     std::vector<uint64_t> nb((n_bits + 63) / 64, 0), in((n_bits + 63) / 64, 0);
-    if ((size_t) c < near_border_bs.size())
-        for (uint64_t k = 0; k < n_bits; k++)
-            if (near_border_bs[c][k]) nb[k >> 6] |= 1ull << (k & 63);
-    if ((size_t) c < intronic_bs.size())
-        for (uint64_t k = 0; k < n_bits; k++)
-            if (intronic_bs[c][k]) in[k >> 6] |= 1ull << (k & 63);
+    {   // std::bitset has no word access: the bits are read one by one, whole words per thread
+        const int T = std::max(1, threadCount);
+        const size_t nw = nb.size();
+        const bool has_nb = (size_t) c < near_border_bs.size(), has_in = (size_t) c < intronic_bs.size();
+        feed::parallel_for(T, [&](int t) {
+            for (size_t w = nw * t / T; w < nw * (t + 1) / T; w++) {
+                uint64_t a = 0, b = 0;
+                const uint64_t k0 = (uint64_t) w << 6, k1 = std::min<uint64_t>(k0 + 64, n_bits);
+                for (uint64_t k = k0; k < k1; k++) {
+                    if (has_nb && near_border_bs[c][k]) a |= 1ull << (k & 63);
+                    if (has_in && intronic_bs[c][k]) b |= 1ull << (k & 63);
+                }
+                nb[w] = a; in[w] = b;
+            }
+        });
+    }
     auto pad = [](auto &v) { if (v.empty()) v.resize(1); };
     pad(seg_start); pad(seg_end); pad(seg_next); pad(seg_gene); pad(tid); pad(trans_start); pad(t2s); pad(gene_start); pad(gene_end);
     pad(chr_shift); pad(chr_id);
@@ -144,7 +176,8 @@ void upload_annotation(int c) {
 
 void ensure_round(int c) {
     if (!g_ctx) {
-        cm_params p;
+        g_chr.reserve(CHR_CAP);
+        cm_params &p = g_params;
         cm_params_default(&p);
         p.kmer = kmer; p.max_read_len = maxReadLength; p.max_ed = maxEd; p.max_sc = maxSc; p.band_width = bandWidth;
         p.seed_lim = seedLim; p.max_tlen = maxTlen; p.max_intron_len = maxIntronLen; p.max_chain_len = maxChainLen;
@@ -186,12 +219,85 @@ struct Held {
     }
 };
 
+template <class T> T *pinned(size_t n) {
+    void *p = nullptr;
+    if (cm_gpu_host_alloc(n * sizeof(T), &p) != CM_OK) die("cm_gpu_host_alloc");
+    return (T *) p;
+}
+
+// Batched rounds with the parallel host feed of host_feed.h (PAM output or none).
+void gpu_map_reads_parallel(size_t B) {
+    const int is_last = filter_read.get_last_round();
+    const int T = std::max(1, threadCount);
+    const uint32_t stride = (uint32_t) maxReadLength;
+    const size_t cap = std::min<size_t>(std::max<size_t>(B * 512, 1u << 20), 1u << 30);
+    feed::RawFile raw[2][2];
+    for (int s = 0; s < 2; s++) {
+        raw[s][0].init(fq_parser1.gzinput, cap);
+        raw[s][1].init(fq_parser2.gzinput, cap);
+    }
+    char *s1 = pinned<char>(B * stride), *s2 = pinned<char>(B * stride);
+    uint16_t *l1 = pinned<uint16_t>(B), *l2 = pinned<uint16_t>(B);
+    cm_mread *in = pinned<cm_mread>(B), *out = pinned<cm_mread>(B);
+    int32_t *state = pinned<int32_t>(B);
+    std::vector<feed::RecMeta> m1(B), m2(B);
+    std::vector<feed::TextOut> text(T);
+    cm_mread fresh;
+    cm_mread_init(&fresh, &g_params);
+    int cur = 0;
+    feed::parallel_for(2, [&](int k) { raw[cur][k].fill(); });
+    feed::LineIndex ix1, ix2;
+    while (true) {
+        feed::count_lines(raw[cur][0], T, ix1);
+        feed::count_lines(raw[cur][1], T, ix2);
+        const size_t n = (size_t) std::min<uint64_t>(B, std::min(ix1.lines, ix2.lines) / 4);
+        if (!n) break;
+        size_t e[2] = {raw[cur][0].len, raw[cur][1].len};
+        feed::parse_records(raw[cur][0], ix1, T, n, stride, m1.data(), s1, l1, in, fresh, e[0]);
+        feed::parse_records(raw[cur][1], ix2, T, n, stride, m2.data(), s2, l2, nullptr, fresh, e[1]);
+        // the next block of both files is read while this batch is mapped and written
+        std::thread pre[2];
+        for (int k = 0; k < 2; k++)
+            pre[k] = std::thread([&, k] {
+                feed::RawFile &a = raw[cur][k], &b = raw[cur ^ 1][k];
+                b.len = a.len - e[k];
+                memcpy(b.buf.data(), a.buf.data() + e[k], b.len);
+                b.eof = a.eof;
+                b.fill();
+            });
+        if (cm_gpu_process_batch_pe(g_ctx, contigNum, (uint32_t) n, s1, s2, stride, l1, l2, in, out, state) != CM_OK)
+            die("cm_gpu_process_batch_pe");
+        const char *b1 = raw[cur][0].buf.data(), *b2 = raw[cur][1].buf.data();
+        feed::parallel_for(T, [&](int t) {
+            feed::TextOut &o = text[t];
+            o.pam.clear(); o.r1.clear(); o.r2.clear();
+            feed::format_range(n * t / T, n * (t + 1) / T, b1, b2, m1.data(), m2.data(), out, state, is_last, o);
+        });
+        for (int t = 0; t < T; t++) {   // input order == the reference's -t 1 order
+            if (!text[t].pam.empty()) fwrite(text[t].pam.data(), 1, text[t].pam.size(), filter_read.sam_output.outsam);
+            if (!text[t].r1.empty()) fwrite(text[t].r1.data(), 1, text[t].r1.size(), filter_read.temp_fq_r1);
+            if (!text[t].r2.empty()) fwrite(text[t].r2.data(), 1, text[t].r2.size(), filter_read.temp_fq_r2);
+        }
+        for (auto &p : pre) p.join();
+        cur ^= 1;
+    }
+    cm_gpu_host_free(s1); cm_gpu_host_free(s2); cm_gpu_host_free(l1); cm_gpu_host_free(l2);
+    cm_gpu_host_free(in); cm_gpu_host_free(out); cm_gpu_host_free(state);
+}
+
 void *gpu_map_reads(void *args) {
     FilterArgs *fa = (FilterArgs *) args;
+    g_fa = fa;
     ensure_round(contigNum);
     const int is_last = filter_read.get_last_round();
     const char *bs = getenv("CM_GPU_BATCH");
     const size_t B = bs ? (size_t) atol(bs) : 262144;
+    if (reportMapping != SAMFORMAT && !getenv("CM_GPU_SERIAL_HOST")) {
+        gpu_map_reads_parallel(B);
+        return NULL;
+    }
+    // SAM output (needs the reference's Record-based writer) or CM_GPU_SERIAL_HOST=1: the reference's own parser and
+    // writers, one pair at a time, around the batched call
     const uint32_t stride = (uint32_t) maxReadLength;
     std::vector<Held> h1(B), h2(B);
     std::vector<char> s1(B * stride), s2(B * stride);

@@ -1,0 +1,57 @@
+"""Host side of the drop-in (integration/host_feed.h: block reads, parallel FASTQ parse, header tokens -> cm_mread,
+PAM / remain-FASTQ text in input order) checked on the CPU: oracle/_ref/circminer_feedtest is the drop-in's shim with a
+stand-in for the C-ABI that answers each batch with the reference's own process_read (tests/hostfeed/feed_mock.cpp), so
+every byte that differs from the reference binary is a host-feed bug.  Two packed contigs = two rounds, the second one
+parsing the 23-token headers the first one wrote.  The GPU counterpart is tests/test_gpu_dropin.py."""
+import filecmp
+import glob
+import os
+import subprocess
+import sys
+
+import pytest
+
+from conftest import has_ref
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref", "circminer")
+FEED = os.path.join(ROOT, "oracle", "_ref", "circminer_feedtest")
+
+
+def _run(binary, w, out, threads, env=None, extra=()):
+    cmd = [binary, "-r", w["fa"], "-g", w["gtf"], "-1", w["fq1"], "-2", w["fq2"], "-k", "20", "-t", str(threads), "-P", "-z",
+           "-o", out, *extra]
+    e = dict(os.environ, LC_ALL="C")
+    e.update(env or {})
+    p = subprocess.run(cmd, capture_output=True, text=True, env=e, timeout=1500)
+    assert p.returncode == 0, (p.stdout + p.stderr)[-2000:]
+
+
+@pytest.fixture(scope="module")
+def dataset(tmp_path_factory):
+    from circminer_b200 import workload
+    d = str(tmp_path_factory.mktemp("feed") / "t1")
+    w = workload.prepare("T1", d, contig_size=3_500_000, n_pairs=6000, write_reads=True)
+    subprocess.run([sys.executable, "-c",
+                    "import sys; sys.path.insert(0, %r)\n"
+                    "from oracle.refharness import RefHarness, default_params\n"
+                    "RefHarness(default_params()).build_index(%r, contig_size=3500000)" % (ROOT, w["fa"])],
+                   check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=900)
+    return w
+
+
+@pytest.mark.skipif(not (has_ref() and os.path.exists(FEED)), reason="oracle/_ref/circminer_feedtest not built")
+@pytest.mark.parametrize("scan,threads,batch", [("0", 4, 1000), ("2", 3, 257), ("0", 1, 262144)])
+def test_host_feed_outputs_are_byte_identical(dataset, tmp_path, scan, threads, batch):
+    w = dataset
+    ref_out, feed_out = str(tmp_path / "ref"), str(tmp_path / "feed")
+    _run(REF, w, ref_out, 1, extra=("-a", scan))
+    _run(FEED, w, feed_out, threads, env={"CM_GPU_BATCH": str(batch)}, extra=("-a", scan))
+    ref_files = sorted(os.path.basename(f)[3:] for f in glob.glob(ref_out + "*") if os.path.isfile(f))
+    feed_files = sorted(os.path.basename(f)[4:] for f in glob.glob(feed_out + "*") if os.path.isfile(f))
+    assert ref_files == feed_files and any(f.endswith("circ_report") for f in ref_files), (ref_files, feed_files)
+    assert any("remain_R1" in f for f in ref_files)
+    for suffix in ref_files:
+        a, b = ref_out + suffix, feed_out + suffix
+        assert filecmp.cmp(a, b, shallow=False), f"{suffix} differs ({os.path.getsize(a)} vs {os.path.getsize(b)} bytes)"
+    assert os.path.getsize(ref_out + ".mapping.pam") > 10000
