@@ -10,6 +10,8 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <thread>
+#include <atomic>
 
 #include "cm_pipeline.h"
 
@@ -292,6 +294,11 @@ extern "C" int cm_gpu_last_stage_ms(cm_gpu_ctx *ctx, float out[5]) {
     return CM_OK;
 }
 
+extern "C" int cm_gpu_warmup(int device) {
+    if (cudaSetDevice(device) != cudaSuccess) return CM_ERR_CUDA;
+    return cudaFree(nullptr) == cudaSuccess ? CM_OK : CM_ERR_CUDA;
+}
+
 extern "C" int cm_gpu_host_alloc(size_t bytes, void **out) {
     if (!out) return CM_ERR_ARG;
     *out = nullptr;
@@ -364,6 +371,22 @@ __global__ void k_unpack_cref(const uint64_t *__restrict__ cref, uint32_t len, u
     genome[i + 1] = lut[v];
 }
 
+// host-side helpers of the loader: uninitialised buffers (no 1 GiB zero fill) and a fork-join over host threads
+template <class T> struct HostBuf {
+    T *p = nullptr;
+    size_t n = 0;
+    explicit HostBuf(size_t n_) : p((T *) malloc((n_ ? n_ : 1) * sizeof(T))), n(n_) {}
+    ~HostBuf() { free(p); }
+    HostBuf(const HostBuf &) = delete;
+    HostBuf &operator=(const HostBuf &) = delete;
+};
+template <class F> static void host_parallel_for(int T, F &&fn) {
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; t++) th.emplace_back([&fn, t] { fn(t); });
+    fn(0);
+    for (auto &x : th) x.join();
+}
+
 extern "C" int cm_gpu_load_contig(cm_gpu_ctx *ctx, int contig_id, const void *const *bucket_lists, const void *table_mem,
                                   uint64_t table_mem_entries, const uint64_t *cref_gen, uint32_t ref_gen_len) {
     if (!ctx) return CM_ERR_ARG;
@@ -373,35 +396,52 @@ extern "C" int cm_gpu_load_contig(cm_gpu_ctx *ctx, int contig_id, const void *co
     if (!ch) return fail(ctx, CM_ERR_ARG, ctx->parent ? "contig %d: a shared context cannot load (load into its parent)" : "bad contig id %d", contig_id);
     free_contig(*ch);
     const GeneralIndexPacked *mem = (const GeneralIndexPacked *) table_mem;
-    // directory + SoA split on the host (one pass over the buckets, like setHashTablePointers, HashTable.c:1074)
-    std::vector<uint32_t> dir((size_t) CM_NBUCKETS + 1);
-    uint64_t total = 0;
-    for (uint32_t hv = 0; hv < CM_NBUCKETS; hv++) {
-        dir[hv] = (uint32_t) total;
-        const GeneralIndexPacked *l = (const GeneralIndexPacked *) bucket_lists[hv];
-        if (l) {
-            if (l < mem || (uint64_t) (l - mem) + l[0].info + 1 > table_mem_entries)
-                return fail(ctx, CM_ERR_ARG, "bucket %u points outside table_mem", hv);
-            total += l[0].info;
+    // directory + SoA split on the host (setHashTablePointers order, HashTable.c:1074), by all host threads: the
+    // 2 GiB pointer table is cut into slices, every slice counts its entries, a prefix over the slices gives each
+    // one its first entry, then the slices fill their part of the directory and of the two arrays.
+    const int T = (int) std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 64u);
+    HostBuf<uint32_t> dir((size_t) CM_NBUCKETS + 1);
+    if (!dir.p) return fail(ctx, CM_ERR_ALLOC, "host memory for the directory");
+    std::vector<uint64_t> slice_total(T + 1, 0);
+    std::atomic<uint32_t> bad_bucket(0xFFFFFFFFu);
+    host_parallel_for(T, [&](int t) {
+        const uint32_t h0 = (uint32_t) ((uint64_t) CM_NBUCKETS * t / T), h1 = (uint32_t) ((uint64_t) CM_NBUCKETS * (t + 1) / T);
+        uint64_t sum = 0;
+        for (uint32_t hv = h0; hv < h1; hv++) {
+            const GeneralIndexPacked *l = (const GeneralIndexPacked *) bucket_lists[hv];
+            if (!l) continue;
+            if (l < mem || (uint64_t) (l - mem) + l[0].info + 1 > table_mem_entries) { bad_bucket.store(hv); return; }
+            sum += l[0].info;
         }
-    }
+        slice_total[t + 1] = sum;
+    });
+    if (bad_bucket.load() != 0xFFFFFFFFu) return fail(ctx, CM_ERR_ARG, "bucket %u points outside table_mem", bad_bucket.load());
+    for (int t = 0; t < T; t++) slice_total[t + 1] += slice_total[t];
+    const uint64_t total = slice_total[T];
     if (total > 0xFFFFFFFFull) return fail(ctx, CM_ERR_ARG, "more than 2^32 index entries");
-    dir[CM_NBUCKETS] = (uint32_t) total;
-    std::vector<uint16_t> cks(total);
-    std::vector<uint32_t> pos(total);
-    for (uint32_t hv = 0; hv < CM_NBUCKETS; hv++) {
-        const GeneralIndexPacked *l = (const GeneralIndexPacked *) bucket_lists[hv];
-        if (!l) continue;
-        uint32_t n = l[0].info, o = dir[hv];
-        for (uint32_t j = 0; j < n; j++) {
-            cks[o + j] = l[1 + j].checksum;
-            pos[o + j] = l[1 + j].info;
+    dir.p[CM_NBUCKETS] = (uint32_t) total;
+    HostBuf<uint16_t> cks(total);
+    HostBuf<uint32_t> pos(total);
+    if (total && (!cks.p || !pos.p)) return fail(ctx, CM_ERR_ALLOC, "host memory for the index entries");
+    host_parallel_for(T, [&](int t) {
+        const uint32_t h0 = (uint32_t) ((uint64_t) CM_NBUCKETS * t / T), h1 = (uint32_t) ((uint64_t) CM_NBUCKETS * (t + 1) / T);
+        uint32_t o = (uint32_t) slice_total[t];
+        for (uint32_t hv = h0; hv < h1; hv++) {
+            dir.p[hv] = o;
+            const GeneralIndexPacked *l = (const GeneralIndexPacked *) bucket_lists[hv];
+            if (!l) continue;
+            const uint32_t n = l[0].info;
+            for (uint32_t j = 0; j < n; j++) {
+                cks.p[o + j] = l[1 + j].checksum;
+                pos.p[o + j] = l[1 + j].info;
+            }
+            o += n;
         }
-    }
+    });
     int r;
-    if ((r = dev_upload(ctx, ch->owned, &ch->d.dir, dir.data(), dir.size())) != CM_OK) return r;
-    if ((r = dev_upload(ctx, ch->owned, &ch->d.cks, cks.data(), cks.size())) != CM_OK) return r;
-    if ((r = dev_upload(ctx, ch->owned, &ch->d.pos, pos.data(), pos.size())) != CM_OK) return r;
+    if ((r = dev_upload(ctx, ch->owned, &ch->d.dir, dir.p, dir.n)) != CM_OK) return r;
+    if ((r = dev_upload(ctx, ch->owned, &ch->d.cks, cks.p, cks.n)) != CM_OK) return r;
+    if ((r = dev_upload(ctx, ch->owned, &ch->d.pos, pos.p, pos.n)) != CM_OK) return r;
     size_t nwords = (size_t) ref_gen_len / 21 + 1;
     const uint64_t *d_cref = nullptr;
     std::vector<void *> tmp;

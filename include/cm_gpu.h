@@ -129,6 +129,10 @@ int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **out);
  * alternating batches overlap one batch's copies with the other's kernels -- the role the
  * reference's threadCount map_reads threads over shared globals play (src/circminer.cpp:290).
  * Loading entry points are refused on it; destroy it before its parent. */
+/* Creates the CUDA context of `device` (a second or two on a large part) and nothing else.  Optional: a host
+ * program calls it from a side thread at start-up so that the cost overlaps its own index / GTF loading
+ * (src/circminer.cpp:125-260) instead of landing in the first cm_gpu_create. */
+int cm_gpu_warmup(int device);
 int cm_gpu_create_shared(cm_gpu_ctx *parent, cm_gpu_ctx **out);
 int cm_gpu_destroy(cm_gpu_ctx *ctx);
 const char *cm_gpu_last_error(const cm_gpu_ctx *ctx);   /* ctx may be NULL: last create error */

@@ -18,8 +18,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../include/cm_gpu.h"
@@ -39,6 +41,12 @@ namespace {
 
 cm_gpu_ctx *g_ctx = nullptr;
 cm_params g_params;
+const bool g_verbose = getenv("CM_GPU_VERBOSE") != nullptr;   // phase times on stderr
+double now_s() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec + 1e-9 * ts.tv_nsec;
+}
 FilterArgs *g_fa = nullptr;   // mapping thread 0's arguments (the reference's per-thread scratch)
 std::vector<std::string> g_chr;   // chromosome names <-> cm_mread::chr_r1 / chr_r2 indices
 int g_loaded_contig = -1;
@@ -174,7 +182,22 @@ void upload_annotation(int c) {
     if (cm_gpu_load_annotation(g_ctx, c, &A) != CM_OK) die("cm_gpu_load_annotation");
 }
 
+int gpu_device() {
+    const char *dev = getenv("CM_GPU_DEVICE");
+    return dev ? atoi(dev) : 0;
+}
+
+// CUDA context creation overlaps the reference's own start-up (GTF, index meta, first loadHashTable)
+struct Warmup {
+    std::thread th;
+    Warmup() : th([] { cm_gpu_warmup(gpu_device()); }) {}
+    void wait() { if (th.joinable()) th.join(); }
+    ~Warmup() { wait(); }
+} g_warmup;
+
 void ensure_round(int c) {
+    const double t_in = now_s();
+    g_warmup.wait();
     if (!g_ctx) {
         g_chr.reserve(CHR_CAP);
         cm_params &p = g_params;
@@ -182,22 +205,36 @@ void ensure_round(int c) {
         p.kmer = kmer; p.max_read_len = maxReadLength; p.max_ed = maxEd; p.max_sc = maxSc; p.band_width = bandWidth;
         p.seed_lim = seedLim; p.max_tlen = maxTlen; p.max_intron_len = maxIntronLen; p.max_chain_len = maxChainLen;
         p.scan_level = scanLevel;
-        const char *dev = getenv("CM_GPU_DEVICE");
-        if (cm_gpu_create(dev ? atoi(dev) : 0, &p, &g_ctx) != CM_OK) die("cm_gpu_create");
+        if (cm_gpu_create(gpu_device(), &p, &g_ctx) != CM_OK) die("cm_gpu_create");
     }
     if (g_loaded_contig == c) return;
+    const double t_ctx = now_s();
     // entries in use = end of the furthest bucket (_ih_hashTableMemSize is only maintained by the index builder)
     uint64_t n = 0;
-    for (int hv = 0; hv < _ih_maxHashTableSize; hv++)
-        if (_ih_hashTable[hv].list) {
-            uint64_t end = (uint64_t) (_ih_hashTable[hv].list - _ih_hashTableMem) + _ih_hashTable[hv].list[0].info + 1;
-            if (end > n) n = end;
-        }
+    {
+        const int T = std::max(1, threadCount);
+        std::vector<uint64_t> part(T, 0);
+        feed::parallel_for(T, [&](int t) {
+            uint64_t m = 0;
+            for (int64_t hv = (int64_t) _ih_maxHashTableSize * t / T; hv < (int64_t) _ih_maxHashTableSize * (t + 1) / T; hv++)
+                if (_ih_hashTable[hv].list) {
+                    uint64_t end = (uint64_t) (_ih_hashTable[hv].list - _ih_hashTableMem) + _ih_hashTable[hv].list[0].info + 1;
+                    if (end > m) m = end;
+                }
+            part[t] = m;
+        });
+        for (uint64_t m : part) n = std::max(n, m);
+    }
+    const double t_scan = now_s();
     if (cm_gpu_load_contig(g_ctx, c, (const void *const *) _ih_hashTable, _ih_hashTableMem, n, (const uint64_t *) _ih_crefGen,
                            (uint32_t) _ih_refGenLen) != CM_OK)
         die("cm_gpu_load_contig");
+    const double t_idx = now_s();
     upload_annotation(c);
     g_loaded_contig = c;
+    if (g_verbose)
+        fprintf(stderr, "circminer_gpu: contig %d: context %.3f s, table scan %.3f s, index upload %.3f s, annotation %.3f s\n", c,
+                t_ctx - t_in, t_scan - t_ctx, t_idx - t_scan, now_s() - t_idx);
 }
 
 // a Record that outlives FASTQParser's per-thread buffer
@@ -231,23 +268,45 @@ void gpu_map_reads_parallel(size_t B) {
     const int T = std::max(1, threadCount);
     const uint32_t stride = (uint32_t) maxReadLength;
     const size_t cap = std::min<size_t>(std::max<size_t>(B * 512, 1u << 20), 1u << 30);
-    feed::RawFile raw[2][2];
+    // block buffers, pinned batch arrays and text buffers live across rounds (one allocation per run)
+    static feed::RawFile raw[2][2];
+    static size_t B_alloc = 0;
+    static char *s1, *s2;
+    static uint16_t *l1, *l2;
+    static cm_mread *in, *out;
+    static int32_t *state;
+    static std::vector<feed::RecMeta> m1, m2;
+    static std::vector<feed::TextOut> text;
+    const double t_setup = now_s();
     for (int s = 0; s < 2; s++) {
         raw[s][0].init(fq_parser1.gzinput, cap);
         raw[s][1].init(fq_parser2.gzinput, cap);
     }
-    char *s1 = pinned<char>(B * stride), *s2 = pinned<char>(B * stride);
-    uint16_t *l1 = pinned<uint16_t>(B), *l2 = pinned<uint16_t>(B);
-    cm_mread *in = pinned<cm_mread>(B), *out = pinned<cm_mread>(B);
-    int32_t *state = pinned<int32_t>(B);
-    std::vector<feed::RecMeta> m1(B), m2(B);
-    std::vector<feed::TextOut> text(T);
+    if (B_alloc < B) {
+        if (B_alloc) {
+            cm_gpu_host_free(s1); cm_gpu_host_free(s2); cm_gpu_host_free(l1); cm_gpu_host_free(l2);
+            cm_gpu_host_free(in); cm_gpu_host_free(out); cm_gpu_host_free(state);
+        }
+        s1 = pinned<char>(B * stride); s2 = pinned<char>(B * stride);
+        l1 = pinned<uint16_t>(B); l2 = pinned<uint16_t>(B);
+        in = pinned<cm_mread>(B); out = pinned<cm_mread>(B);
+        state = pinned<int32_t>(B);
+        m1.resize(B); m2.resize(B);
+        B_alloc = B;
+    }
+    text.resize(T);
     cm_mread fresh;
     cm_mread_init(&fresh, &g_params);
     int cur = 0;
+    const double t_begin = now_s();
+    if (g_verbose) fprintf(stderr, "circminer_gpu: host buffers %.3f s\n", t_begin - t_setup);
     feed::parallel_for(2, [&](int k) { raw[cur][k].fill(); });
     feed::LineIndex ix1, ix2;
+    double ph[6] = {0, 0, 0, 0, 0, 0};   // first read, parse, map, format, write, wait for the next block
+    ph[0] = now_s() - t_begin;
+    size_t n_batches = 0, n_total = 0;
     while (true) {
+        double t0 = now_s();
         feed::count_lines(raw[cur][0], T, ix1);
         feed::count_lines(raw[cur][1], T, ix2);
         const size_t n = (size_t) std::min<uint64_t>(B, std::min(ix1.lines, ix2.lines) / 4);
@@ -265,24 +324,36 @@ void gpu_map_reads_parallel(size_t B) {
                 b.eof = a.eof;
                 b.fill();
             });
+        double t1 = now_s();
+        ph[1] += t1 - t0;
         if (cm_gpu_process_batch_pe(g_ctx, contigNum, (uint32_t) n, s1, s2, stride, l1, l2, in, out, state) != CM_OK)
             die("cm_gpu_process_batch_pe");
+        t0 = now_s();
+        ph[2] += t0 - t1;
         const char *b1 = raw[cur][0].buf.data(), *b2 = raw[cur][1].buf.data();
         feed::parallel_for(T, [&](int t) {
             feed::TextOut &o = text[t];
             o.pam.clear(); o.r1.clear(); o.r2.clear();
             feed::format_range(n * t / T, n * (t + 1) / T, b1, b2, m1.data(), m2.data(), out, state, is_last, o);
         });
+        t1 = now_s();
+        ph[3] += t1 - t0;
         for (int t = 0; t < T; t++) {   // input order == the reference's -t 1 order
             if (!text[t].pam.empty()) fwrite(text[t].pam.data(), 1, text[t].pam.size(), filter_read.sam_output.outsam);
             if (!text[t].r1.empty()) fwrite(text[t].r1.data(), 1, text[t].r1.size(), filter_read.temp_fq_r1);
             if (!text[t].r2.empty()) fwrite(text[t].r2.data(), 1, text[t].r2.size(), filter_read.temp_fq_r2);
         }
+        t0 = now_s();
+        ph[4] += t0 - t1;
         for (auto &p : pre) p.join();
+        ph[5] += now_s() - t0;
         cur ^= 1;
+        n_batches++;
+        n_total += n;
     }
-    cm_gpu_host_free(s1); cm_gpu_host_free(s2); cm_gpu_host_free(l1); cm_gpu_host_free(l2);
-    cm_gpu_host_free(in); cm_gpu_host_free(out); cm_gpu_host_free(state);
+    if (g_verbose)
+        fprintf(stderr, "circminer_gpu: round: %zu pairs in %zu batches, %d host threads: first read %.3f s, parse %.3f s, map %.3f s, "
+                "format %.3f s, write %.3f s, wait for next block %.3f s\n", n_total, n_batches, T, ph[0], ph[1], ph[2], ph[3], ph[4], ph[5]);
 }
 
 void *gpu_map_reads(void *args) {

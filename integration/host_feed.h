@@ -28,10 +28,19 @@ template <class F> void parallel_for(int T, F &&fn) {
 
 struct RawFile {
     gzFile gz = nullptr;
-    std::vector<char> buf;
+    struct Bytes {   // uninitialised storage: a std::vector would zero-fill (and page in) the whole block first
+        char *p = nullptr;
+        size_t n = 0;
+        char *data() { return p; }
+        const char *data() const { return p; }
+        size_t size() const { return n; }
+        char &operator[](size_t i) { return p[i]; }
+        void reserve_bytes(size_t m) { if (m > n) { free(p); p = (char *) malloc(m); n = p ? m : 0; if (!p) { fprintf(stderr, "circminer_gpu: out of host memory\n"); exit(1); } } }
+        ~Bytes() { free(p); }
+    } buf;
     size_t len = 0;
     bool eof = false;
-    void init(gzFile g, size_t cap) { gz = g; buf.resize(cap + 1); len = 0; eof = false; }
+    void init(gzFile g, size_t cap) { gz = g; buf.reserve_bytes(cap + 1); len = 0; eof = false; }
     void fill() {
         const size_t cap = buf.size() - 1;
         while (!eof && len < cap) {

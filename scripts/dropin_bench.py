@@ -33,7 +33,8 @@ def run(binary, d, fq1, fq2, out, threads, env=None, extra=()):
     if p.returncode != 0:
         raise SystemExit(f"{binary} failed:\n{txt[-2000:]}")
     rounds = [float(x) for x in re.findall(r"Completed round \S+ \(CPU time: [\d.]+s; Real time: ([\d.]+)s\)", txt)]
-    return {"wall_s": wall, "round_s": rounds, "mapping_s": sum(rounds), "log_tail": txt[-600:]}
+    phases = [ln for ln in txt.splitlines() if ln.startswith("circminer_gpu:")]
+    return {"wall_s": wall, "round_s": rounds, "mapping_s": sum(rounds), "phases": phases}
 
 
 def digest(path, sort_lines=False):
@@ -82,7 +83,7 @@ def main():
     res = {"workload": a.workload, "pairs": n, "read_len": int(d["r1"].shape[1]), "host_cores": ncores}
     res["reference"] = run(REF_BIN, d, fq1, fq2, ref_out, ncores)
     res["reference"]["threads"] = ncores
-    res["dropin"] = run(gpu_bin, d, fq1, fq2, gpu_out, ncores, env={"CM_GPU_BATCH": str(a.batch)})
+    res["dropin"] = run(gpu_bin, d, fq1, fq2, gpu_out, ncores, env={"CM_GPU_BATCH": str(a.batch), "CM_GPU_VERBOSE": "1"})
     res["dropin"]["batch"] = a.batch
     same = {}
     for suffix, sort_lines in ((".mapping.pam", True), (".candidates.pam", False), (".circ_report", False)):

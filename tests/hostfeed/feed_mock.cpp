@@ -34,6 +34,7 @@ void cm_mread_init(cm_mread *m, const cm_params *p) {
     m->type = NOPROC_NOMATCH; m->tlen = (int32_t) INF;
     m->chr_r1 = -1; m->chr_r2 = -1;
 }
+int cm_gpu_warmup(int) { return CM_OK; }
 int cm_gpu_create(int, const cm_params *, cm_gpu_ctx **out) { *out = (cm_gpu_ctx *) &g_params; return CM_OK; }
 const char *cm_gpu_last_error(const cm_gpu_ctx *) { return "mock"; }
 int cm_gpu_load_contig(cm_gpu_ctx *, int, const void *const *, const void *, uint64_t, const uint64_t *, uint32_t) { return CM_OK; }
