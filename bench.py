@@ -115,7 +115,12 @@ def run_b200(a):
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ["NCCL_DEBUG"] = os.environ.get("CM_NCCL_DEBUG", "WARN")   # keep stdout to the one JSON line
+        # keep stdout to the one JSON line: NCCL prints its version banner on stdout from NCCL_DEBUG=VERSION upwards
+        if "CM_NCCL_DEBUG" in os.environ:
+            os.environ["NCCL_DEBUG"] = os.environ["CM_NCCL_DEBUG"]
+        else:
+            os.environ.pop("NCCL_DEBUG", None)
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -255,6 +260,7 @@ def run_b200(a):
                          "algorithmic_bytes_per_launch": seed_bytes},
             "counters": {k: v / a.steps for k, v in ctr.items()},
             "alignment": alignment_line(ctr, align_acc, stage_acc, a.steps),
+            "chaining": chaining_line(ctr, align_acc, stage_acc, a.steps),
             "prep_s": t_prep,
         }
         if not a.no_cpu_baseline and world == 1:
@@ -281,6 +287,17 @@ def alignment_line(ctr, align_acc, stage_acc, steps):
             "k_chain_spec_ms": float(align_acc[0]) / steps, "k_chain_walk_ms": float(align_acc[1]) / steps,
             "int32_peak_gcups": int32_peak_gcups, "frac_int32": gcups / int32_peak_gcups,
             "note": "band 3 (7 cells per row), thread per DP, band in registers; peak assumes 10 INT32 instr per cell"}
+
+
+def chaining_line(ctr, align_acc, stage_acc, steps):
+    """Links = candidate evaluations reaching src/chain.cpp:173, counted on the device; time = the chain stage minus the
+    dense alignment kernels that run in the same stage (sorts and k_chain / k_chain_warp / k_chain_big remain)."""
+    ms = (float(stage_acc[2]) - float(align_acc.sum())) / steps
+    if ms <= 0:
+        return None
+    links = ctr["chain_links"] / steps
+    return {"mlinks_per_s": links / (ms * 1e-3) / 1e6, "links_per_step": links, "ms": ms, "seed_hits_per_step": ctr["seed_hits"] / steps,
+            "note": "FP64 scores (IEEE, no contraction), thread per strand + warp per repeat-rich strand; latency bound, no HBM claim"}
 
 
 def cpu_baseline(a, datadir, n_pairs, threads, target_s=12.0):
