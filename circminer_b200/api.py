@@ -175,6 +175,11 @@ class Mapper:
         self._chk(self.lib.cm_gpu_build_contig(self.ctx, contig_id, _vp(seq), C.c_uint32(len(seq))),
                   "cm_gpu_build_contig")
 
+    def build_contig_packed(self, contig_id, cref_gen, ref_gen_len):
+        """Device build from the reference's 3-bit packed contig (raw pointer to _ih_crefGen)."""
+        self._chk(self.lib.cm_gpu_build_contig_packed(self.ctx, contig_id, C.c_void_p(cref_gen), C.c_uint32(ref_gen_len)),
+                  "cm_gpu_build_contig_packed")
+
     def contig_stats(self, contig_id):
         n = C.c_uint64()
         ln = C.c_uint32()

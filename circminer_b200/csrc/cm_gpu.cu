@@ -513,24 +513,13 @@ __global__ void k_ascii_to_genome(const char *__restrict__ seq, uint32_t len, ui
     genome[i + 1] = (c == 'A' || c == 'C' || c == 'G' || c == 'T') ? c : 'N';
 }
 
-extern "C" int cm_gpu_build_contig(cm_gpu_ctx *ctx, int contig_id, const char *contig_seq, uint32_t ref_gen_len) {
-    if (!ctx) return CM_ERR_ARG;
-    if (!contig_seq) return fail(ctx, CM_ERR_ARG, "null argument");
-    cudaSetDevice(ctx->device);
-    ContigHost *ch = get_contig(ctx, contig_id, true);
-    if (!ch) return fail(ctx, CM_ERR_ARG, ctx->parent ? "contig %d: a shared context cannot load (load into its parent)" : "bad contig id %d", contig_id);
-    free_contig(*ch);
+// Device-side index build from the contig text already at genome[1..len] (count -> select -> stable radix sort on
+// (hv, checksum) -> histogram / scan -> fused directory); what HashTable.c:769-839 + Sort.c:110-176 produce.
+static int finish_build(cm_gpu_ctx *ctx, ContigHost *ch, uint8_t *genome, uint32_t len) {
     cudaStream_t st = ctx->stream;
     int r;
-    const uint32_t len = ref_gen_len;
-    uint8_t *genome = nullptr;
-    if ((r = dev_alloc(ctx, ch->owned, &genome, (size_t) len + 64)) != CM_OK) return r;
     std::vector<void *> tmp;
     auto cleanup = [&]() { for (void *p : tmp) cudaFree(p); };
-    char *d_seq = nullptr;
-    if ((r = dev_alloc(ctx, tmp, &d_seq, (size_t) len)) != CM_OK) { cleanup(); return r; }
-    CUDA_TRY(ctx, cudaMemcpyAsync(d_seq, contig_seq, len, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(ctx, cudaMemsetAsync(genome, 'N', (size_t) len + 64, st));
     uint64_t *keys = nullptr, *keys_sel = nullptr, *keys_alt = nullptr;
     uint32_t *locs = nullptr, *locs_sel = nullptr, *locs_alt = nullptr, *dirc = nullptr, *d_nsel = nullptr;
     uint8_t *valid = nullptr;
@@ -539,9 +528,8 @@ extern "C" int cm_gpu_build_contig(cm_gpu_ctx *ctx, int contig_id, const char *c
         (r = dev_alloc(ctx, tmp, &locs_sel, (size_t) len)) != CM_OK || (r = dev_alloc(ctx, tmp, &d_nsel, 2)) != CM_OK ||
         (r = dev_alloc(ctx, ch->owned, &dirc, (size_t) CM_NBUCKETS + 1)) != CM_OK) { cleanup(); return r; }
     if (len) {
-        k_ascii_to_genome<<<grid_for(len, 256), 256, 0, st>>>(d_seq, len, genome);
         k_kmer_keys<<<grid_for(len, 256), 256, 0, st>>>(genome, len, ctx->p.kmer, keys, locs, valid);
-        ctx->launches += 2;
+        ctx->launches++;
     }
     // compact valid k-mers (ascending position)
     size_t tb1 = 0, tb2 = 0, tb3 = 0, tb4 = 0;
@@ -594,6 +582,63 @@ extern "C" int cm_gpu_build_contig(cm_gpu_ctx *ctx, int contig_id, const char *c
     if ((r = build_dirx(ctx, ch)) != CM_OK) return r;
     ch->loaded = true;
     return CM_OK;
+}
+
+extern "C" int cm_gpu_build_contig(cm_gpu_ctx *ctx, int contig_id, const char *contig_seq, uint32_t ref_gen_len) {
+    if (!ctx) return CM_ERR_ARG;
+    if (!contig_seq) return fail(ctx, CM_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->device);
+    ContigHost *ch = get_contig(ctx, contig_id, true);
+    if (!ch) return fail(ctx, CM_ERR_ARG, ctx->parent ? "contig %d: a shared context cannot load (load into its parent)" : "bad contig id %d", contig_id);
+    free_contig(*ch);
+    cudaStream_t st = ctx->stream;
+    int r;
+    const uint32_t len = ref_gen_len;
+    uint8_t *genome = nullptr;
+    if ((r = dev_alloc(ctx, ch->owned, &genome, (size_t) len + 64)) != CM_OK) return r;
+    std::vector<void *> tmp;
+    char *d_seq = nullptr;
+    if ((r = dev_alloc(ctx, tmp, &d_seq, (size_t) len)) != CM_OK) return r;
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_seq, contig_seq, len, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(genome, 'N', (size_t) len + 64, st));
+    if (len) {
+        k_ascii_to_genome<<<grid_for(len, 256), 256, 0, st>>>(d_seq, len, genome);
+        ctx->launches++;
+    }
+    r = finish_build(ctx, ch, genome, len);
+    cudaStreamSynchronize(st);
+    for (void *p : tmp) cudaFree(p);
+    return r;
+}
+
+// Same build from the reference's 3-bit packed contig (_ih_crefGen, 21 bases per word, Common.c:174-196): 0.4 bytes per
+// base over PCIe instead of the 2 GiB pointer table + 6-byte entries that cm_gpu_load_contig converts and uploads.
+extern "C" int cm_gpu_build_contig_packed(cm_gpu_ctx *ctx, int contig_id, const uint64_t *cref_gen, uint32_t ref_gen_len) {
+    if (!ctx) return CM_ERR_ARG;
+    if (!cref_gen) return fail(ctx, CM_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->device);
+    ContigHost *ch = get_contig(ctx, contig_id, true);
+    if (!ch) return fail(ctx, CM_ERR_ARG, ctx->parent ? "contig %d: a shared context cannot load (load into its parent)" : "bad contig id %d", contig_id);
+    free_contig(*ch);
+    cudaStream_t st = ctx->stream;
+    int r;
+    const uint32_t len = ref_gen_len;
+    uint8_t *genome = nullptr;
+    if ((r = dev_alloc(ctx, ch->owned, &genome, (size_t) len + 64)) != CM_OK) return r;
+    std::vector<void *> tmp;
+    uint64_t *d_cref = nullptr;
+    const size_t nwords = ((size_t) len + 20) / 21;
+    if ((r = dev_alloc(ctx, tmp, &d_cref, nwords + 1)) != CM_OK) return r;
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_cref, cref_gen, nwords * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(genome, 'N', (size_t) len + 64, st));
+    if (len) {
+        k_unpack_cref<<<grid_for(len, 256), 256, 0, st>>>(d_cref, len, genome);
+        ctx->launches++;
+    }
+    r = finish_build(ctx, ch, genome, len);
+    cudaStreamSynchronize(st);
+    for (void *p : tmp) cudaFree(p);
+    return r;
 }
 
 extern "C" int cm_gpu_contig_stats(cm_gpu_ctx *ctx, int contig_id, uint64_t *n_entries, uint32_t *ref_gen_len) {

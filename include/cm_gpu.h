@@ -165,6 +165,10 @@ int cm_gpu_load_contig(cm_gpu_ctx *ctx, int contig_id, const void *const *bucket
  * anything else = N): count -> scan -> scatter -> sort by (checksum, position),
  * the order src/mrsfast/Sort.c:110-176 produces (HashTable.c:769-839). */
 int cm_gpu_build_contig(cm_gpu_ctx *ctx, int contig_id, const char *contig_seq, uint32_t ref_gen_len);
+/* The same device-side build from the reference's 3-bit packed contig (_ih_crefGen / _ih_refGenLen,
+ * lib/mrsfast/RefGenome.c; 21 bases per 64-bit word, Common.c:174-196): what a host that has just run
+ * loadHashTable() holds, without converting and uploading its bucket table. */
+int cm_gpu_build_contig_packed(cm_gpu_ctx *ctx, int contig_id, const uint64_t *cref_gen, uint32_t ref_gen_len);
 int cm_gpu_contig_stats(cm_gpu_ctx *ctx, int contig_id, uint64_t *n_entries, uint32_t *ref_gen_len);
 /* debugging / parity: copy the positions of bucket hv (all checksums) back */
 int cm_gpu_read_bucket(cm_gpu_ctx *ctx, int contig_id, uint32_t hv, uint32_t cap, uint16_t *checksum,

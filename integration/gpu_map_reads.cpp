@@ -209,9 +209,14 @@ void ensure_round(int c) {
     }
     if (g_loaded_contig == c) return;
     const double t_ctx = now_s();
-    // entries in use = end of the furthest bucket (_ih_hashTableMemSize is only maintained by the index builder)
-    uint64_t n = 0;
-    {
+    // Index of this contig on the device.  Default: built there from the 3-bit packed contig the reference has just
+    // loaded (38 MB over PCIe per 100 Mbp).  CM_GPU_INDEX=upload converts and uploads the reference's own bucket table
+    // instead (the two are compared entry by entry in tests/test_gpu_seed.py).
+    double t_scan = now_s();
+    const char *how = getenv("CM_GPU_INDEX");
+    if (how && !strcmp(how, "upload")) {
+        // entries in use = end of the furthest bucket (_ih_hashTableMemSize is only maintained by the index builder)
+        uint64_t n = 0;
         const int T = std::max(1, threadCount);
         std::vector<uint64_t> part(T, 0);
         feed::parallel_for(T, [&](int t) {
@@ -224,16 +229,17 @@ void ensure_round(int c) {
             part[t] = m;
         });
         for (uint64_t m : part) n = std::max(n, m);
-    }
-    const double t_scan = now_s();
-    if (cm_gpu_load_contig(g_ctx, c, (const void *const *) _ih_hashTable, _ih_hashTableMem, n, (const uint64_t *) _ih_crefGen,
-                           (uint32_t) _ih_refGenLen) != CM_OK)
-        die("cm_gpu_load_contig");
+        t_scan = now_s();
+        if (cm_gpu_load_contig(g_ctx, c, (const void *const *) _ih_hashTable, _ih_hashTableMem, n, (const uint64_t *) _ih_crefGen,
+                               (uint32_t) _ih_refGenLen) != CM_OK)
+            die("cm_gpu_load_contig");
+    } else if (cm_gpu_build_contig_packed(g_ctx, c, (const uint64_t *) _ih_crefGen, (uint32_t) _ih_refGenLen) != CM_OK)
+        die("cm_gpu_build_contig_packed");
     const double t_idx = now_s();
     upload_annotation(c);
     g_loaded_contig = c;
     if (g_verbose)
-        fprintf(stderr, "circminer_gpu: contig %d: context %.3f s, table scan %.3f s, index upload %.3f s, annotation %.3f s\n", c,
+        fprintf(stderr, "circminer_gpu: contig %d: context %.3f s, table scan %.3f s, index on device %.3f s, annotation %.3f s\n", c,
                 t_ctx - t_in, t_scan - t_ctx, t_idx - t_scan, now_s() - t_idx);
 }
 

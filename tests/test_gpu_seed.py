@@ -20,6 +20,7 @@ def test_index_and_seed_parity(t0, t0_packed, ref_t0):
     h = ref_t0
     m_ref = Mapper(default_params())     # index uploaded from the reference's memory
     m_own = Mapper(default_params())     # index built on the device
+    m_pck = Mapper(default_params())     # index built on the device from the reference's 3-bit packed contig
     s1, s2 = ascii_reads(t0)
     reads = np.concatenate([s1, revcomp_ascii(s1), s2, revcomp_ascii(s2)])
     # edge cases: N inside a seed, lower-case base, short read, read shorter than k
@@ -37,7 +38,8 @@ def test_index_and_seed_parity(t0, t0_packed, ref_t0):
         tab, mem, memsz, cref, rlen = h.index_pointers()
         m_ref.load_contig_from_reference(c, tab, mem, memsz, cref, rlen)
         m_own.build_contig(c, t0_packed["contigs"][c])
-        assert m_ref.contig_stats(c) == m_own.contig_stats(c)
+        m_pck.build_contig_packed(c, cref, rlen)
+        assert m_ref.contig_stats(c) == m_own.contig_stats(c) == m_pck.contig_stats(c)
         assert rlen == len(t0_packed["contigs"][c])
         # bucket-level equality on random + occupied buckets
         sd = h.seed(reads[:64], lens[:64])
@@ -54,11 +56,12 @@ def test_index_and_seed_parity(t0, t0_packed, ref_t0):
                 hvs.append(v)
         for hv in hvs:
             a = m_ref.read_bucket(c, int(hv))
-            b = m_own.read_bucket(c, int(hv))
-            assert a[2] == b[2]
-            assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
+            for mm in (m_own, m_pck):
+                b = mm.read_bucket(c, int(hv))
+                assert a[2] == b[2]
+                assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
         want = h.seed(reads, lens)
-        for m in (m_ref, m_own):
+        for m in (m_ref, m_own, m_pck):
             got = m.split_match_hash(c, reads, lens)
             for k in ("frag_count", "has_frags", "first_info", "last_info", "sum_info"):
                 assert (got[k] == want[k]).all(), k
@@ -69,6 +72,7 @@ def test_index_and_seed_parity(t0, t0_packed, ref_t0):
     assert cnt["seeds"] > 0 and cnt["seed_sectors"] >= cnt["seeds"] * 0
     m_ref.close()
     m_own.close()
+    m_pck.close()
 
 
 def test_create_rejects_bad_params():
