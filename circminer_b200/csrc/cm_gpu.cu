@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <vector>
 #include <thread>
@@ -520,6 +521,9 @@ static int finish_build(cm_gpu_ctx *ctx, ContigHost *ch, uint8_t *genome, uint32
     int r;
     std::vector<void *> tmp;
     auto cleanup = [&]() { for (void *p : tmp) cudaFree(p); };
+    const bool verbose = getenv("CM_GPU_VERBOSE") != nullptr;
+    auto now = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec + 1e-9 * ts.tv_nsec; };
+    const double t0 = now();
     uint64_t *keys = nullptr, *keys_sel = nullptr, *keys_alt = nullptr;
     uint32_t *locs = nullptr, *locs_sel = nullptr, *locs_alt = nullptr, *dirc = nullptr, *d_nsel = nullptr;
     uint8_t *valid = nullptr;
@@ -544,6 +548,7 @@ static int finish_build(cm_gpu_ctx *ctx, ContigHost *ch, uint8_t *genome, uint32
     if (tb4 > tb) tb = tb4;
     void *d_tmp = nullptr;
     if ((r = dev_alloc(ctx, tmp, (uint8_t **) &d_tmp, tb + 16)) != CM_OK) { cleanup(); return r; }
+    const double t1 = now();
     uint32_t nsel = 0;
     if (len) {
         cub::DeviceSelect::Flagged(d_tmp, tb, keys, valid, keys_sel, d_nsel, (int64_t) len, st);
@@ -572,7 +577,9 @@ static int finish_build(cm_gpu_ctx *ctx, ContigHost *ch, uint8_t *genome, uint32
     cub::DeviceScan::ExclusiveSum(d_tmp, tb, dirc, dirc, (int64_t) CM_NBUCKETS + 1, st);
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     CUDA_TRY(ctx, cudaGetLastError());
+    const double t2 = now();
     cleanup();
+    const double t3 = now();
     ch->d.dir = dirc;
     ch->d.cks = cks;
     ch->d.pos = pos;
@@ -580,6 +587,9 @@ static int finish_build(cm_gpu_ctx *ctx, ContigHost *ch, uint8_t *genome, uint32
     ch->d.n_entries = nsel;
     ch->d.ref_len = len;
     if ((r = build_dirx(ctx, ch)) != CM_OK) return r;
+    if (verbose)
+        fprintf(stderr, "cm_gpu: index build of %u bp: allocations %.3f s, keys / select / sort / directory %.3f s, frees %.3f s, "
+                "fused directory %.3f s\n", len, t1 - t0, t2 - t1, t3 - t2, now() - t3);
     ch->loaded = true;
     return CM_OK;
 }

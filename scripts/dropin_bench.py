@@ -33,7 +33,7 @@ def run(binary, d, fq1, fq2, out, threads, env=None, extra=()):
     if p.returncode != 0:
         raise SystemExit(f"{binary} failed:\n{txt[-2000:]}")
     rounds = [float(x) for x in re.findall(r"Completed round \S+ \(CPU time: [\d.]+s; Real time: ([\d.]+)s\)", txt)]
-    phases = [ln for ln in txt.splitlines() if ln.startswith("circminer_gpu:")]
+    phases = [ln for ln in txt.splitlines() if ln.startswith(("circminer_gpu:", "cm_gpu:"))]
     return {"wall_s": wall, "round_s": rounds, "mapping_s": sum(rounds), "phases": phases}
 
 
