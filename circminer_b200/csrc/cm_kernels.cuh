@@ -22,6 +22,12 @@ CM_HD uint32_t cm_rec_cap(uint32_t cells, uint32_t mult) { return mult * cells +
 // K2b: chaining, one thread per strand.  Strands whose improvement list outgrows its slice of the
 // record arena are queued for k_chain_big (exact two-pass sizing) instead of being truncated.
 // ------------------------------------------------------------------------------------------
+#ifndef CM_CHAIN_LOCAL
+#define CM_CHAIN_LOCAL 1
+#endif
+#ifndef CM_CHAIN_LOCAL_CELLS
+#define CM_CHAIN_LOCAL_CELLS 64
+#endif
 #ifndef CM_CHAIN_MINB
 #define CM_CHAIN_MINB 1
 #endif
@@ -51,7 +57,21 @@ __global__ void __launch_bounds__(128, CM_CHAIN_MINB) k_chain(const __grid_const
             uint64_t base = cell_off[s];
             uint32_t cap = cm_rec_cap(cells, rec_mult);
             ChainRec *r = recs + cm_rec_base(base, s, rec_mult);
-            uint32_t nrec = cm_chain_dp(v, b.strand_len[s], T, row_pos_off, row_cnt, row_off, dp_score + base, dp_prev + base, r, cap, &links);
+#if CM_CHAIN_LOCAL
+            // dp cells of a light strand (<= CM_CHAIN_LOCAL_CELLS; the heavy ones go to k_chain_warp) live in local memory:
+            // the hardware interleaves local words across the lanes of a warp, so the per-thread rows that were scattered
+            // 128-byte lines in the global arena become coalesced, L1-resident accesses.  The arena is still what
+            // k_chain_big and the warp kernel use.
+            double ls[CM_CHAIN_LOCAL_CELLS];
+            uint32_t lp[CM_CHAIN_LOCAL_CELLS];
+            const bool loc = cells <= CM_CHAIN_LOCAL_CELLS;
+            double *ds = loc ? ls : dp_score + base;
+            uint32_t *dpv = loc ? lp : dp_prev + base;
+#else
+            double *ds = dp_score + base;
+            uint32_t *dpv = dp_prev + base;
+#endif
+            uint32_t nrec = cm_chain_dp(v, b.strand_len[s], T, row_pos_off, row_cnt, row_off, ds, dpv, r, cap, &links);
             if (nrec > cap) {
                 uint32_t k = atomicAdd(n_ovf, 1u);
                 ovf_strand[k] = s;
@@ -63,7 +83,7 @@ __global__ void __launch_bounds__(128, CM_CHAIN_MINB) k_chain(const __grid_const
                 out.len = b.chain_len + (size_t) s * b.C;
                 out.frags = b.chain_frags + (size_t) s * b.C * b.F;
                 out.F = b.F;
-                cm_chain_backtrack(v, T, row_pos_off, row_cnt, row_off, dp_score + base, dp_prev + base, r, nrec, out);
+                cm_chain_backtrack(v, T, row_pos_off, row_cnt, row_off, ds, dpv, r, nrec, out);
             }
         }
     }
