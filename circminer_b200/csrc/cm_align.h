@@ -50,8 +50,10 @@ struct AlignStats {      // roofline numerators
 // slot d-1 = dp[i-1][j]), and the 2W+1 characters of s under the band in a sliding window of codes
 // (0..3 = ACGT ignoring case, 4 = anything else in s, 5 = anything else in t: never equal).
 CM_HD uint32_t cm_base_code(uint8_t c, uint32_t other) {
-    const uint8_t u = c & 0xDF;
-    return u == 'A' ? 0u : u == 'C' ? 1u : u == 'G' ? 2u : u == 'T' ? 3u : other;
+    // 'A' 0x41, 'C' 0x43, 'G' 0x47, 'T' 0x54: bits 1..2 tell them apart (A 0, C 1, T 2, G 3; only equality is ever tested);
+    // membership is one bit test in the mask of the letters A, C, G, T
+    const uint32_t u = c & 0xDFu, idx = u - 'A';
+    return (idx < 26u && ((0x80045u >> idx) & 1u)) ? ((u >> 1) & 3u) : other;
 }
 template <int W, bool CHECK>
 CM_HD void cm_edit_col_reg(uint32_t (&a)[2 * W + 3], const uint32_t (&win)[2 * W + 1], uint32_t tc, int j, int n) {
@@ -394,8 +396,8 @@ CM_HDN void cm_xdrop_generic(const uint8_t *s, int n, const uint8_t *t, int m, b
 // two anti-diagonals, issued ahead of its use).  Codes: 'A','C','G','T' (case folded) or a value that
 // never compares equal (N never matches N, align.cpp:745-759).
 CM_HD int cm_code(uint8_t c, int bad) {
-    uint8_t u = c & 0xDF;
-    return (u == 'A' || u == 'C' || u == 'G' || u == 'T') ? (int) u : bad;
+    const uint32_t u = c & 0xDFu, idx = u - 'A';
+    return (idx < 26u && ((0x80045u >> idx) & 1u)) ? (int) u : bad;
 }
 CM_HD int cm_code_at(const uint8_t *p0, int step, int len, int c, int bad) { return (c >= 0 && c < len) ? cm_code(p0[c * step], bad) : bad; }
 
