@@ -28,6 +28,9 @@ CM_HD uint32_t cm_rec_cap(uint32_t cells, uint32_t mult) { return mult * cells +
 #ifndef CM_CHAIN_LOCAL_CELLS
 #define CM_CHAIN_LOCAL_CELLS 64
 #endif
+#ifndef CM_CHAIN_LOCAL_RECS
+#define CM_CHAIN_LOCAL_RECS 32
+#endif
 #ifndef CM_CHAIN_MINB
 #define CM_CHAIN_MINB 1
 #endif
@@ -57,6 +60,11 @@ __global__ void __launch_bounds__(128, CM_CHAIN_MINB) k_chain(const __grid_const
             uint64_t base = cell_off[s];
             uint32_t cap = cm_rec_cap(cells, rec_mult);
             ChainRec *r = recs + cm_rec_base(base, s, rec_mult);
+#if CM_CHAIN_LOCAL_RECS
+            // same for the improvement records of a strand whose slice is small (unique hits: 7 cells -> 29 records)
+            ChainRec lr[CM_CHAIN_LOCAL_RECS];
+            if (cap <= CM_CHAIN_LOCAL_RECS) r = lr;
+#endif
 #if CM_CHAIN_LOCAL
             // dp cells of a light strand (<= CM_CHAIN_LOCAL_CELLS; the heavy ones go to k_chain_warp) live in local memory:
             // the hardware interleaves local words across the lanes of a warp, so the per-thread rows that were scattered
