@@ -61,9 +61,8 @@ CM_HD void cm_edit_col_reg(uint32_t (&a)[2 * W + 3], const uint32_t (&win)[2 * W
 #pragma unroll
     for (int d = 1; d <= 2 * W + 1; d++) {
         uint32_t v = a[d] + (win[d - 1] == tc ? 0u : 1u);
-        const uint32_t x = a[d - 1] + 1, y = a[d + 1] + 1;
-        v = v < x ? v : x;
-        v = v < y ? v : y;
+        const uint32_t xy = (a[d - 1] < a[d + 1] ? a[d - 1] : a[d + 1]) + 1;   // min(x + 1, y + 1); values <= DPTINF + m
+        v = v < xy ? v : xy;
         if (CHECK) {
             const int i = j - W - 1 + d;
             if (i < 1 || i > n) v = CM_DPTINF;
@@ -417,8 +416,11 @@ template <int W, int KP, bool EARLY>
 CM_HD void cm_xdrop_step(XdropState<W> &S, int k, int q, int mat, int mis, int ind, int xd, int &new_ub) {
     const int NEG = -CM_DPTINF;
     constexpr int LO = -(W / 2 + 1);
-    const int lq = S.lb - q, uq = S.ub - q, lim = S.pre - xd;
+    const int lq = S.lb - q, uq = S.ub - q, lim = S.pre - xd;   // lim >= -xd > NEG: a cell that survives the X-drop is live
     int nub_h = -1000;
+    // best cell of this diagonal (last one among equals, as the running "v >= cur" of the reference picks), merged into
+    // the running optimum once per diagonal: the same (cur, i, k) as updating per cell
+    int dmax = -2 * CM_DPTINF, dh = 0;
     S.cells += (uint32_t) (S.ub - S.lb + 1);
 #pragma unroll
     for (int e = 1; e <= 2 * W + 1; e++) {
@@ -429,17 +431,19 @@ CM_HD void cm_xdrop_step(XdropState<W> &S, int k, int q, int mat, int mis, int i
         if (h >= lq && h <= uq) {
             int sc = S.SW[h - 1 - LO] == S.TW[(KP - d) / 2 - 1 - LO] ? mat : mis;
             v = S.X[e] + sc;
-            int a = S.X[e - 1] + ind, b = S.X[e + 1] + ind;
-            v = v > a ? v : a;
-            v = v > b ? v : b;
-            if (v >= S.cur) { S.cur = v; S.best_i = q + h; S.best_k = k; }
-            if (v < lim) v = NEG;                   // v + xdrop < pre_optimum
-            if (v > NEG) nub_h = h;                 // h ascends with e: the last live cell wins
+            int ab = S.X[e - 1] > S.X[e + 1] ? S.X[e - 1] : S.X[e + 1];
+            ab += ind;                              // max(a + ind, b + ind); |values| <= DPTINF + a few hundred, no overflow
+            v = v > ab ? v : ab;
+            if (v >= dmax) { dmax = v; dh = h; }
+            const bool live = v >= lim;             // otherwise v + xdrop < pre_optimum
+            v = live ? v : NEG;
+            if (live) nub_h = h;                    // h ascends with e: the last live cell wins
         } else {
             v = (EARLY && k <= W && (d == k || d == -k)) ? k * ind : NEG;
         }
         S.X[e] = v;
     }
+    if (dmax >= S.cur) { S.cur = dmax; S.best_i = q + dh; S.best_k = k; }
     new_ub = nub_h > -1000 ? q + nub_h : -1;
 }
 
