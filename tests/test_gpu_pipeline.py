@@ -243,3 +243,40 @@ def test_ragged_and_degenerate_reads(w_t0):
     out, st = m.process_read(0, s1[:0], s2[:0], fresh_mreads(0))
     assert len(st) == 0
     m.close()
+
+
+def test_host_buffers_warmup_and_alignment_timers(w_t0):
+    """cm_gpu_host_alloc / cm_gpu_host_free (pinned batch buffers of the drop-in's host feed), cm_gpu_warmup and
+    cm_gpu_last_align_ms: results from pinned caller buffers equal the goldens; the alignment kernels report a time."""
+    import ctypes as C
+    from circminer_b200.api import fresh_mreads, load_library, MREAD_DTYPE
+    lib = load_library()
+    assert lib.cm_gpu_warmup(0) == 0
+    gold = np.load(os.path.join(GOLDEN, "T0_k20.npz"))
+    m = _mapper(w_t0)
+    n = len(w_t0["s1"])
+    bufs = []
+
+    def pinned_like(arr):
+        p = C.c_void_p()
+        assert lib.cm_gpu_host_alloc(C.c_size_t(arr.nbytes), C.byref(p)) == 0 and p.value
+        bufs.append(p)
+        v = np.frombuffer((C.c_char * arr.nbytes).from_address(p.value), dtype=arr.dtype).reshape(arr.shape)
+        v[...] = arr
+        return v
+
+    s1, s2 = pinned_like(w_t0["s1"]), pinned_like(w_t0["s2"])
+    mr = pinned_like(fresh_mreads(n))
+    out = pinned_like(np.zeros(n, MREAD_DTYPE))
+    state = pinned_like(np.zeros(n, np.int32))
+    want = fresh_mreads(n)
+    for c in range(int(gold["n_contigs"])):
+        want = compare_contig(m, c, w_t0, gold, want, stages=("pe",))
+        got, st = m.process_read(c, s1, s2, mr, out=out, state=state)
+        mr[...] = got
+        a = m.align_ms()
+        assert len(a) == 2 and a[0] >= 0 and a[1] >= 0
+    assert (mr == want).all()
+    m.close()
+    for p in bufs:
+        assert lib.cm_gpu_host_free(p) == 0
