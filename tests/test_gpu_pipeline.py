@@ -197,7 +197,8 @@ def test_shared_context_gives_the_same_results(w_t0):
     """cm_gpu_create_shared: a second context over the parent's resident contigs, used from a second host thread."""
     import threading
     from circminer_b200.api import CmGpuError, Mapper, fresh_mreads
-    gold = np.load(os.path.join(GOLDEN, "T0_k20.npz"))
+    with np.load(os.path.join(GOLDEN, "T0_k20.npz")) as z:
+        gold = {k: z[k] for k in z.files}   # materialised: a lazily read NpzFile (zipfile) is not safe from two threads
     m = _mapper(w_t0)
     m2 = Mapper(parent=m)
     with pytest.raises(CmGpuError):
