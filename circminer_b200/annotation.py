@@ -9,6 +9,8 @@ against the reference's own tables in tests/test_annotation.py.
 """
 from __future__ import annotations
 
+import re
+
 import numpy as np
 
 DEF_CONTIG_SIZE = 1_100_000_000   # src/common.h:81
@@ -40,19 +42,15 @@ def pack_genome(chroms, contig_size: int = DEF_CONTIG_SIZE):
     return contigs, info
 
 
+_TOK = {}
+
+
 def _tokenize(s: str, delims: str):
     """GTFParser::tokenize (gene_annotation.cpp:84-104): split on any delimiter, skip empties."""
-    out, cur = [], []
-    for ch in s:
-        if ch in delims:
-            if cur:
-                out.append("".join(cur))
-                cur = []
-        else:
-            cur.append(ch)
-    if cur:
-        out.append("".join(cur))
-    return out
+    rx = _TOK.get(delims)
+    if rx is None:
+        rx = _TOK[delims] = re.compile("[^" + re.escape(delims) + "]+")
+    return rx.findall(s)
 
 
 def parse_gtf(path: str):

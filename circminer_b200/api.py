@@ -180,6 +180,16 @@ class Mapper:
         self._chk(self.lib.cm_gpu_build_contig_packed(self.ctx, contig_id, C.c_void_p(cref_gen), C.c_uint32(ref_gen_len)),
                   "cm_gpu_build_contig_packed")
 
+    def write_index(self, path, n_contigs, compact=False, contig_max_size=1_300_000_000):
+        """The reference's <ref>.packed.fa.index from the resident contigs (cm_gpu_write_index)."""
+        self._chk(self.lib.cm_gpu_write_index(self.ctx, os.fsencode(path), n_contigs, int(compact), C.c_uint32(contig_max_size)),
+                  "cm_gpu_write_index")
+
+    def load_index_file(self, path, first_id=0):
+        n = C.c_int()
+        self._chk(self.lib.cm_gpu_load_index_file(self.ctx, os.fsencode(path), first_id, C.byref(n)), "cm_gpu_load_index_file")
+        return n.value
+
     def contig_stats(self, contig_id):
         n = C.c_uint64()
         ln = C.c_uint32()
@@ -280,6 +290,46 @@ class Mapper:
                                                    C.c_uint32(a1.shape[1]), _vp(l1), _vp(l2), _vp(mreads),
                                                    _vp(out), _vp(state)), "cm_gpu_process_batch_pe")
         return out, state
+
+    def map_rounds(self, seqs1, seqs2, mreads, first=0, n_contigs=1, lens1=None, lens2=None, snapshots=False,
+                   out=None, state=None):
+        """The reference's round loop for a batch over resident contigs first .. first + n_contigs - 1
+        (src/circminer.cpp:229-308; cm_gpu_map_rounds_pe).  Returns a dict: out / state / final_round per pair and,
+        with snapshots, round_out / round_state [n_contigs, n] (state -1 = the pair was already final)."""
+        a1, l1 = _rows(seqs1, lens1)
+        a2, l2 = _rows(seqs2, lens2)
+        if a1.shape != a2.shape:
+            raise ValueError("mate arrays must share shape")
+        n = a1.shape[0]
+        mreads = np.ascontiguousarray(mreads)
+        assert mreads.dtype == MREAD_DTYPE and len(mreads) == n
+        res = dict(out=np.zeros(n, MREAD_DTYPE) if out is None else out,
+                   state=np.zeros(n, np.int32) if state is None else state, final_round=np.zeros(n, np.int32))
+        if snapshots:
+            res["round_out"] = np.zeros((n_contigs, n), MREAD_DTYPE)
+            res["round_state"] = np.zeros((n_contigs, n), np.int32)
+        self._chk(self.lib.cm_gpu_map_rounds_pe(self.ctx, first, n_contigs, C.c_uint32(n), _vp(a1), _vp(a2),
+                                                C.c_uint32(a1.shape[1]), _vp(l1), _vp(l2), _vp(mreads), _vp(res["out"]),
+                                                _vp(res["state"]), _vp(res["final_round"]), _vp(res.get("round_out")),
+                                                _vp(res.get("round_state"))), "cm_gpu_map_rounds_pe")
+        return res
+
+    def run_staged_rounds(self, first=0, n_contigs=1):
+        self._chk(self.lib.cm_gpu_run_staged_rounds_pe(self.ctx, first, n_contigs), "cm_gpu_run_staged_rounds_pe")
+
+    def fetch_rounds(self):
+        out = np.zeros(self._staged_n, MREAD_DTYPE)
+        state = np.zeros(self._staged_n, np.int32)
+        fr = np.zeros(self._staged_n, np.int32)
+        self._chk(self.lib.cm_gpu_fetch_rounds_pe(self.ctx, _vp(out), _vp(state), _vp(fr)), "cm_gpu_fetch_rounds_pe")
+        return out, state, fr
+
+    def rounds_ms(self, cap=8):
+        """(ms[8], pairs_per_round): see cm_gpu_last_rounds_ms."""
+        a = (C.c_float * 8)()
+        pr = (C.c_uint32 * cap)()
+        k = self.lib.cm_gpu_last_rounds_ms(self.ctx, a, pr, cap)
+        return list(a), list(pr)[:max(0, k)]
 
     def process_read_se(self, contig_id, seqs, lens=None):
         a, l = _rows(seqs, lens)

@@ -17,6 +17,7 @@
 #include "cm_pipeline.h"
 
 #define CM_CTR_SLOTS 256   // copies of cm_counters on the device (power of two), summed on read
+#define CM_MAX_ROUNDS 64   // packed contigs one cm_gpu_map_rounds_pe call may visit
 
 // ------------------------------------------------------------------------------------------
 // context
@@ -88,6 +89,15 @@ struct cm_gpu_ctx {
     DevBuf spec_key[2], spec_item[2];                     // pre-alignment work items, before / after the cost sort
     DevBuf key32[2], key64[2], perm[2];                   // work-signature sort of strands / pairs
     DevBuf scratch[8];
+    // rounds on the device (cm_gpu_map_rounds_pe): two compacted batches used in turn, per-pair final results
+    DevBuf rb_strands[2], rb_slen[2], rb_key[2], rb_in[2], rb_ids[2];
+    DevBuf fin_mread, fin_state, fin_round, surv_flag, surv_idx, surv_n, snap_mread, snap_state;
+    cudaEvent_t ev_r[2]{};
+    float rounds_ms[6] = {0, 0, 0, 0, 0, 0};   // stage sums over the rounds, [5] the whole run
+    float rounds_align_ms[2] = {0, 0};
+    uint32_t round_pairs[CM_MAX_ROUNDS] = {0};
+    int rounds_run = 0;
+    uint32_t rounds_n = 0;                     // pairs of the batch the final arrays describe
 };
 
 static std::string g_create_err;
@@ -194,6 +204,7 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
         return fail(nullptr, CM_ERR_CUDA, "cannot initialise device %d", device);
     }
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    for (auto &ev : ctx->ev_r) cudaEventCreate(&ev);
     cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking);
     k_init_prep_lut<<<1, 256, 0, ctx->stream>>>();
     cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming);
@@ -258,8 +269,12 @@ extern "C" int cm_gpu_destroy(cm_gpu_ctx *ctx) {
     release(ctx->chain_spec); release(ctx->chain_base); release(ctx->chain_ids); release(ctx->chain_aux);
     for (int q = 0; q < 2; q++) { release(ctx->spec_key[q]); release(ctx->spec_item[q]); }
     for (int q = 0; q < 2; q++) { release(ctx->key32[q]); release(ctx->key64[q]); release(ctx->perm[q]); }
+    for (int q = 0; q < 2; q++) { release(ctx->rb_strands[q]); release(ctx->rb_slen[q]); release(ctx->rb_key[q]); release(ctx->rb_in[q]); release(ctx->rb_ids[q]); }
+    DevBuf *rbufs[] = {&ctx->fin_mread, &ctx->fin_state, &ctx->fin_round, &ctx->surv_flag, &ctx->surv_idx, &ctx->surv_n, &ctx->snap_mread, &ctx->snap_state};
+    for (DevBuf *b : rbufs) release(*b);
     cudaFree(ctx->d_counters);
     for (auto &ev : ctx->ev) cudaEventDestroy(ev);
+    for (auto &ev : ctx->ev_r) cudaEventDestroy(ev);
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
@@ -1051,3 +1066,4 @@ extern "C" int cm_gpu_seed_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, con
 
 #include "cm_kernels.cuh"
 #include "cm_host_pipeline.cuh"
+#include "cm_index_io.cuh"

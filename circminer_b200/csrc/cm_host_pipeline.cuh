@@ -401,3 +401,161 @@ extern "C" int cm_gpu_process_batch_se(cm_gpu_ctx *ctx, int contig_id, uint32_t 
     if ((r = run_pipeline(ctx, contig_id, 3)) != CM_OK) return r;
     return cm_gpu_fetch_staged_pe(ctx, nullptr, state);
 }
+
+// ---- rounds on the device ----------------------------------------------------------------
+// The staged batch visits contigs first .. first + n_contigs - 1 in order; after each contig the pairs the
+// reference would print are committed and the rest is gathered into the next contig's batch (k_round_commit /
+// k_round_compact).  The caller's staged batch stays intact (the compacted batches live in their own buffers).
+struct StagedBatchGuard {
+    cm_gpu_ctx *ctx;
+    DevBuf strands, slen, key, in;
+    uint32_t n_pairs, n_strands;
+    explicit StagedBatchGuard(cm_gpu_ctx *c)
+        : ctx(c), strands(c->strands), slen(c->strand_len), key(c->seed_key), in(c->in_mread), n_pairs(c->n_pairs), n_strands(c->n_strands) {}
+    ~StagedBatchGuard() {
+        ctx->strands = strands; ctx->strand_len = slen; ctx->seed_key = key; ctx->in_mread = in;
+        ctx->n_pairs = n_pairs; ctx->n_strands = n_strands;
+    }
+};
+
+static int run_rounds(cm_gpu_ctx *ctx, int first, int n_contigs, bool want_snap) {
+    if (n_contigs < 1 || n_contigs > CM_MAX_ROUNDS || first < 0) return fail(ctx, CM_ERR_ARG, "rounds: contigs [%d, %d) out of range", first, first + n_contigs);
+    for (float &m : ctx->rounds_ms) m = 0.f;
+    ctx->rounds_align_ms[0] = ctx->rounds_align_ms[1] = 0.f;
+    for (auto &x : ctx->round_pairs) x = 0;
+    ctx->rounds_run = 0;
+    ctx->rounds_n = ctx->n_pairs;
+    if (!ctx->n_pairs) return CM_OK;
+    if (!ctx->staged_pe) return fail(ctx, CM_ERR_STATE, "rounds need a staged paired-end batch");
+    for (int r = 0; r < n_contigs; r++) {   // fail before any work when a contig is missing
+        DevView v;
+        int rc = make_view(ctx, first + r, true, v);
+        if (rc != CM_OK) return rc;
+    }
+    const uint32_t n = ctx->n_pairs;
+    cudaStream_t st = ctx->stream;
+    ENSURE(ctx, ctx->fin_mread, (size_t) n * sizeof(cm_mread));
+    ENSURE(ctx, ctx->fin_state, (size_t) n * 4);
+    ENSURE(ctx, ctx->fin_round, (size_t) n * 4);
+    ENSURE(ctx, ctx->surv_flag, (size_t) n);
+    ENSURE(ctx, ctx->surv_idx, (size_t) n * 4);
+    ENSURE(ctx, ctx->surv_n, 8);
+    if (want_snap) {
+        ENSURE(ctx, ctx->snap_mread, (size_t) n_contigs * n * sizeof(cm_mread));
+        ENSURE(ctx, ctx->snap_state, (size_t) n_contigs * n * 4);
+        CUDA_TRY(ctx, cudaMemsetAsync(ctx->snap_mread.p, 0, (size_t) n_contigs * n * sizeof(cm_mread), st));
+        CUDA_TRY(ctx, cudaMemsetAsync(ctx->snap_state.p, 0xFF, (size_t) n_contigs * n * 4, st));   // -1: the pair did not visit the contig
+    }
+    StagedBatchGuard guard(ctx);
+    const uint32_t *ids = nullptr;
+    int cur = -1;   // -1: the caller's staged batch, 0 / 1: compacted set in use
+    cudaEventRecord(ctx->ev_r[0], st);
+    for (int r = 0; r < n_contigs; r++) {
+        const int c = first + r;
+        const bool last = r == n_contigs - 1;
+        int rc = run_pipeline(ctx, c, 3);
+        if (rc != CM_OK) return rc;
+        for (int k = 1; k < 5; k++) ctx->rounds_ms[k] += ctx->stage_ms[k];
+        {
+            float am[2];
+            if (cm_gpu_last_align_ms(ctx, am) == CM_OK) { ctx->rounds_align_ms[0] += am[0]; ctx->rounds_align_ms[1] += am[1]; }
+        }
+        const uint32_t n_cur = ctx->n_pairs;
+        ctx->round_pairs[r] = n_cur;
+        ctx->rounds_run = r + 1;
+        k_round_commit<<<grid_for(n_cur, 256), 256, 0, st>>>(
+            ctx->p, n_cur, ids, (const cm_mread *) ctx->out_mread.p, (const int32_t *) ctx->out_state.p, (const uint16_t *) ctx->strand_len.p,
+            last ? 1 : 0, c, (cm_mread *) ctx->fin_mread.p, (int32_t *) ctx->fin_state.p, (int32_t *) ctx->fin_round.p,
+            (uint8_t *) ctx->surv_flag.p, want_snap ? (cm_mread *) ctx->snap_mread.p + (size_t) r * n : nullptr,
+            want_snap ? (int32_t *) ctx->snap_state.p + (size_t) r * n : nullptr);
+        ctx->launches++;
+        CUDA_TRY(ctx, cudaGetLastError());
+        if (last) break;
+        cub::CountingInputIterator<uint32_t> it(0);
+        size_t tb = 0;
+        cub::DeviceSelect::Flagged(nullptr, tb, it, (const uint8_t *) ctx->surv_flag.p, (uint32_t *) ctx->surv_idx.p, (uint32_t *) ctx->surv_n.p, (int) n_cur, st);
+        ENSURE(ctx, ctx->cub_tmp, tb + 16);
+        cub::DeviceSelect::Flagged(ctx->cub_tmp.p, tb, it, (const uint8_t *) ctx->surv_flag.p, (uint32_t *) ctx->surv_idx.p, (uint32_t *) ctx->surv_n.p, (int) n_cur, st);
+        ctx->launches++;
+        uint32_t n_surv = 0;
+        CUDA_TRY(ctx, cudaMemcpyAsync(&n_surv, ctx->surv_n.p, 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        if (!n_surv) break;
+        const int nx = cur == 0 ? 1 : 0;
+        const int F = ctx->batch_F;
+        ENSURE(ctx, ctx->rb_strands[nx], (size_t) n_surv * 4 * ctx->stride);
+        ENSURE(ctx, ctx->rb_slen[nx], (size_t) n_surv * 4 * 2);
+        ENSURE(ctx, ctx->rb_key[nx], (size_t) n_surv * 4 * F * sizeof(int2));
+        ENSURE(ctx, ctx->rb_in[nx], (size_t) n_surv * sizeof(cm_mread));
+        ENSURE(ctx, ctx->rb_ids[nx], (size_t) n_surv * 4);
+        k_round_compact<<<grid_for((size_t) n_surv * 32, 256), 256, 0, st>>>(
+            ctx->p, n_surv, (const uint32_t *) ctx->surv_idx.p, ids, ctx->stride, F, (const uint8_t *) ctx->strands.p,
+            (const uint16_t *) ctx->strand_len.p, (const int2 *) ctx->seed_key.p, (const cm_mread *) ctx->out_mread.p,
+            (uint8_t *) ctx->rb_strands[nx].p, (uint16_t *) ctx->rb_slen[nx].p, (int2 *) ctx->rb_key[nx].p, (cm_mread *) ctx->rb_in[nx].p,
+            (uint32_t *) ctx->rb_ids[nx].p);
+        ctx->launches++;
+        CUDA_TRY(ctx, cudaGetLastError());
+        DBG_SYNC(ctx, "k_round_compact");
+        ctx->strands = ctx->rb_strands[nx];
+        ctx->strand_len = ctx->rb_slen[nx];
+        ctx->seed_key = ctx->rb_key[nx];
+        ctx->in_mread = ctx->rb_in[nx];
+        ids = (const uint32_t *) ctx->rb_ids[nx].p;
+        ctx->n_pairs = n_surv;
+        ctx->n_strands = 4 * n_surv;
+        cur = nx;
+    }
+    cudaEventRecord(ctx->ev_r[1], st);
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&ctx->rounds_ms[5], ctx->ev_r[0], ctx->ev_r[1]);
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_run_staged_rounds_pe(cm_gpu_ctx *ctx, int first_contig, int n_contigs) {
+    if (!ctx) return CM_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    return run_rounds(ctx, first_contig, n_contigs, false);
+}
+
+extern "C" int cm_gpu_fetch_rounds_pe(cm_gpu_ctx *ctx, cm_mread *out, int32_t *state, int32_t *final_round) {
+    if (!ctx) return CM_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    const uint32_t n = ctx->rounds_n;
+    if (!n) return CM_OK;
+    if (!ctx->rounds_run) return fail(ctx, CM_ERR_STATE, "no results: run the rounds first");
+    int r;
+    if ((r = fetch(ctx, out, ctx->fin_mread.p, n)) != CM_OK) return r;
+    if ((r = fetch(ctx, state, ctx->fin_state.p, n)) != CM_OK) return r;
+    if ((r = fetch(ctx, final_round, ctx->fin_round.p, n)) != CM_OK) return r;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_last_rounds_ms(cm_gpu_ctx *ctx, float out[8], uint32_t *pairs_per_round, int cap) {
+    if (!ctx || !out) return CM_ERR_ARG;
+    for (int i = 0; i < 6; i++) out[i] = ctx->rounds_ms[i];
+    out[6] = ctx->rounds_align_ms[0];
+    out[7] = ctx->rounds_align_ms[1];
+    if (pairs_per_round)
+        for (int r = 0; r < cap; r++) pairs_per_round[r] = r < ctx->rounds_run ? ctx->round_pairs[r] : 0;
+    return ctx->rounds_run;
+}
+
+extern "C" int cm_gpu_map_rounds_pe(cm_gpu_ctx *ctx, int first_contig, int n_contigs, uint32_t n, const char *seqs1, const char *seqs2,
+                                    uint32_t stride, const uint16_t *len1, const uint16_t *len2, const cm_mread *in, cm_mread *out,
+                                    int32_t *state, int32_t *final_round, cm_mread *round_out, int32_t *round_state) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n && (!out || !state)) return fail(ctx, CM_ERR_ARG, "null argument");
+    int r = cm_gpu_stage_batch_pe(ctx, n, seqs1, seqs2, stride, len1, len2, in);
+    if (r != CM_OK) return r;
+    const bool snap = round_out || round_state;
+    if ((r = run_rounds(ctx, first_contig, n_contigs, snap)) != CM_OK) return r;
+    if (!n) return CM_OK;
+    if ((r = fetch(ctx, out, ctx->fin_mread.p, n)) != CM_OK) return r;
+    if ((r = fetch(ctx, state, ctx->fin_state.p, n)) != CM_OK) return r;
+    if ((r = fetch(ctx, final_round, ctx->fin_round.p, n)) != CM_OK) return r;
+    if ((r = fetch(ctx, round_out, ctx->snap_mread.p, (size_t) n_contigs * n)) != CM_OK) return r;
+    if ((r = fetch(ctx, round_state, ctx->snap_state.p, (size_t) n_contigs * n)) != CM_OK) return r;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return CM_OK;
+}

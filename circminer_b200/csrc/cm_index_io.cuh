@@ -1,0 +1,274 @@
+// The reference's on-disk index (src/mrsfast/HashTable.c:106-254 writer, :617-655 / :971-1057 loader), written from
+// and read into the device-resident index.  Included by cm_gpu.cu.
+//
+//   file   := u8 magic (3 full | 2 compact), u8 WINDOW_SIZE, u8 checkSumLength, u32 maxMemSize, u32 IOBufferSize,
+//             u32 CONTIG_MAX_SIZE, i32 nContigs, { i32 nameLen, name, i32 length } * nContigs, contig *
+//   contig := u8 moreFollow (2 | 0), i16 nameLen, name, i32 offset, u32 refGenLen, u64 crefGen[ceil(len / 21)],
+//             u32 nNonEmptyBuckets, { i32 nbytes, varbyte(hv delta) varbyte(count) ... } *,
+//             [full only] u32 memSize, GeneralIndex[memSize]
+// `count` of a bucket is the number of 14-base windows without N that hash to it (HashTable.c:316-334) -- not the number
+// of k-mers: the table reserves count + 1 six-byte slots per bucket (header: info = number of entries actually stored,
+// then the entries sorted by (checksum, position), then unused slots), HashTable.c:1065-1091, :824-839.
+#pragma once
+
+#define CM_IO_BUFFER (1u << 24)   // _ih_IOBufferSize (HashTable.c:60)
+
+// windows of CM_WINDOW valid bases per bucket; one thread per window start (0-based i, text is 1-based)
+__global__ void k_window_count(const uint8_t *__restrict__ genome, uint32_t len, uint32_t *__restrict__ cnt) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i + CM_WINDOW > len) return;
+    uint32_t hv = 0;
+    for (int j = 0; j < CM_WINDOW; j++) {
+        int v = cm_nhval(genome[1 + i + j]);
+        if (v < 0) return;
+        hv = (hv << 2) | (uint32_t) v;
+    }
+    atomicAdd(&cnt[hv], 1u);
+}
+
+__global__ void k_slot_count(const uint32_t *__restrict__ cnt, uint64_t *__restrict__ slots) {
+    uint32_t hv = blockIdx.x * blockDim.x + threadIdx.x;
+    if (hv >= CM_NBUCKETS) return;
+    slots[hv] = cnt[hv] ? (uint64_t) cnt[hv] + 1 : 0;
+}
+
+// the table as the reference lays it out, 3 u16 per 6-byte GeneralIndex {u16 checksum; u32 info}; pre-zeroed
+__global__ void k_fill_ref_table(const uint32_t *__restrict__ cnt, const uint64_t *__restrict__ slot_off, const uint32_t *__restrict__ dir,
+                                 const uint16_t *__restrict__ cks, const uint32_t *__restrict__ pos, uint64_t slot_lo, uint64_t slot_hi,
+                                 uint16_t *__restrict__ out /* slots [slot_lo, slot_hi) */) {
+    uint32_t hv = blockIdx.x * blockDim.x + threadIdx.x;
+    if (hv >= CM_NBUCKETS || !cnt[hv]) return;
+    const uint64_t o = slot_off[hv];
+    const uint32_t e0 = dir[hv], n = dir[hv + 1] - e0;
+    if (o + n + 1 <= slot_lo || o >= slot_hi) return;
+    for (uint32_t j = 0; j <= n; j++) {
+        const uint64_t s = o + j;
+        if (s < slot_lo || s >= slot_hi) continue;
+        const uint16_t c = j ? cks[e0 + j - 1] : (uint16_t) 0;
+        const uint32_t info = j ? pos[e0 + j - 1] : n;
+        uint16_t *w = out + 3 * (s - slot_lo);
+        w[0] = c;
+        w[1] = (uint16_t) (info & 0xFFFFu);
+        w[2] = (uint16_t) (info >> 16);
+    }
+}
+
+// compressSequence (lib/mrsfast/Common.c:174-196): 21 bases per word, first base in the top bits
+__global__ void k_pack_cref(const uint8_t *__restrict__ genome, uint32_t len, uint64_t *__restrict__ cref, uint32_t n_words) {
+    uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= n_words) return;
+    uint64_t v = 0;
+    for (uint32_t j = 0; j < 21; j++) {
+        const uint32_t i = 21 * w + j;
+        uint64_t c = 0;
+        if (i < len) {
+            const int h = cm_nhval(genome[1 + i]);
+            c = h < 0 ? 4u : (uint64_t) h;
+        }
+        v = (v << 3) | c;
+    }
+    cref[w] = v;
+}
+
+static inline size_t io_varbyte(unsigned char *buf, uint32_t value) {   // encodeVariableByte, HashTable.c:74-84
+    size_t t = 0;
+    do {
+        buf[t++] = (unsigned char) (value & 127u);
+        value /= 128u;
+    } while (value != 0);
+    buf[t - 1] |= 128u;
+    return t;
+}
+
+struct IoFile {
+    FILE *f = nullptr;
+    ~IoFile() { if (f) fclose(f); }
+};
+
+extern "C" int cm_gpu_write_index(cm_gpu_ctx *ctx, const char *path, int n_contigs, int compact, uint32_t contig_max_size) {
+    if (!ctx) return CM_ERR_ARG;
+    if (!path || n_contigs < 1) return fail(ctx, CM_ERR_ARG, "bad argument");
+    cudaSetDevice(ctx->device);
+    cudaStream_t st = ctx->stream;
+    std::vector<ContigHost *> chs;
+    for (int c = 0; c < n_contigs; c++) {
+        ContigHost *ch = get_contig(ctx, c, false);
+        if (!ch || !ch->loaded) return fail(ctx, CM_ERR_STATE, "contig %d not loaded", c);
+        chs.push_back(ch);
+    }
+    IoFile io;
+    io.f = fopen(path, "wb");
+    if (!io.f) return fail(ctx, CM_ERR_ARG, "cannot open %s for writing", path);
+    FILE *f = io.f;
+    auto put = [&](const void *p, size_t n) { return fwrite(p, 1, n, f) == n; };
+    const unsigned char magic = compact ? 2 : 3, win = CM_WINDOW, csl = (unsigned char) (ctx->p.kmer - CM_WINDOW);
+    uint32_t max_mem = 0;
+    const uint32_t iobuf = CM_IO_BUFFER;
+    bool ok = put(&magic, 1) && put(&win, 1) && put(&csl, 1) && put(&max_mem, 4) && put(&iobuf, 4) && put(&contig_max_size, 4);
+    const int32_t nc = n_contigs;
+    ok = ok && put(&nc, 4);
+    for (int c = 0; c < n_contigs && ok; c++) {
+        char name[32];
+        const int32_t nl = snprintf(name, sizeof name, "%d", c + 1), gl = (int32_t) chs[c]->d.ref_len;
+        ok = put(&nl, 4) && put(name, (size_t) nl) && put(&gl, 4);
+    }
+    if (!ok) return fail(ctx, CM_ERR_ARG, "write to %s failed", path);
+
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *p : tmp) cudaFree(p); tmp.clear(); };
+    uint32_t *d_cnt = nullptr;
+    uint64_t *d_slots = nullptr, *d_off = nullptr;
+    int r;
+    if ((r = dev_alloc(ctx, tmp, &d_cnt, (size_t) CM_NBUCKETS)) != CM_OK || (r = dev_alloc(ctx, tmp, &d_slots, (size_t) CM_NBUCKETS + 1)) != CM_OK ||
+        (r = dev_alloc(ctx, tmp, &d_off, (size_t) CM_NBUCKETS + 1)) != CM_OK) { cleanup(); return r; }
+    HostBuf<uint32_t> h_cnt((size_t) CM_NBUCKETS);
+    std::vector<unsigned char> vb(CM_IO_BUFFER);
+    const size_t CH_SLOTS = (size_t) 1 << 26;   // table chunk: 64 Mi slots = 384 MiB
+    uint16_t *d_chunk = nullptr;
+    void *h_chunk = nullptr;
+    if (!compact) {
+        if ((r = dev_alloc(ctx, tmp, &d_chunk, 3 * CH_SLOTS)) != CM_OK) { cleanup(); return r; }
+        if (cudaHostAlloc(&h_chunk, 6 * CH_SLOTS, cudaHostAllocDefault) != cudaSuccess) { cleanup(); return fail(ctx, CM_ERR_ALLOC, "pinned chunk buffer"); }
+    }
+    auto bail = [&](int code, const char *what) {
+        cleanup();
+        if (h_chunk) cudaFreeHost(h_chunk);
+        return fail(ctx, code, "%s", what);
+    };
+    for (int c = 0; c < n_contigs; c++) {
+        const ContigDev &d = chs[c]->d;
+        const uint32_t len = d.ref_len;
+        const unsigned char more = c + 1 < n_contigs ? 2 : 0;   // loadRefGenome's return value (RefGenome.c:112-116)
+        char name[32];
+        const int16_t nl = (int16_t) snprintf(name, sizeof name, "%d", c + 1);
+        const int32_t off0 = 0;
+        ok = put(&more, 1) && put(&nl, 2) && put(name, (size_t) nl) && put(&off0, 4) && put(&len, 4);
+        // packed text
+        const uint32_t n_words = len / 21 + (len % 21 ? 1 : 0);
+        uint64_t *d_cref = nullptr;
+        std::vector<void *> t2;
+        if ((r = dev_alloc(ctx, t2, &d_cref, (size_t) n_words)) != CM_OK) { cleanup(); if (h_chunk) cudaFreeHost(h_chunk); return r; }
+        if (n_words) k_pack_cref<<<grid_for(n_words, 256), 256, 0, st>>>(d.genome, len, d_cref, n_words);
+        HostBuf<uint64_t> h_cref(n_words);
+        cudaMemcpyAsync(h_cref.p, d_cref, (size_t) n_words * 8, cudaMemcpyDeviceToHost, st);
+        // window counts and slot offsets
+        cudaMemsetAsync(d_cnt, 0, (size_t) CM_NBUCKETS * 4, st);
+        if (len >= CM_WINDOW) k_window_count<<<grid_for(len, 256), 256, 0, st>>>(d.genome, len, d_cnt);
+        k_slot_count<<<grid_for(CM_NBUCKETS, 256), 256, 0, st>>>(d_cnt, d_slots);
+        size_t tb = 0;
+        cub::DeviceScan::ExclusiveSum(nullptr, tb, d_slots, d_off, (int) CM_NBUCKETS, st);
+        if (ensure(ctx, ctx->cub_tmp, tb + 16) != CM_OK) { for (void *p : t2) cudaFree(p); return bail(CM_ERR_ALLOC, "scan scratch"); }
+        cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tb, d_slots, d_off, (int) CM_NBUCKETS, st);
+        ctx->launches += 4;
+        cudaMemcpyAsync(h_cnt.p, d_cnt, (size_t) CM_NBUCKETS * 4, cudaMemcpyDeviceToHost, st);
+        uint64_t last_off = 0, last_slots = 0;
+        cudaMemcpyAsync(&last_off, d_off + (CM_NBUCKETS - 1), 8, cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(&last_slots, d_slots + (CM_NBUCKETS - 1), 8, cudaMemcpyDeviceToHost, st);
+        if (cudaStreamSynchronize(st) != cudaSuccess) { for (void *p : t2) cudaFree(p); return bail(CM_ERR_CUDA, "index write: device pass failed"); }
+        for (void *p : t2) cudaFree(p);
+        const uint64_t mem64 = last_off + last_slots;
+        if (mem64 > 0xFFFFFFFFull) return bail(CM_ERR_ARG, "table larger than 2^32 slots");
+        const uint32_t mem_size = (uint32_t) mem64;
+        if (mem_size > max_mem) max_mem = mem_size;
+        ok = ok && put(h_cref.p, (size_t) n_words * 8);
+        // bucket counts, variable-byte coded in blocks of at most IOBufferSize bytes (HashTable.c:231-250)
+        uint32_t n_nonempty = 0;
+        for (uint32_t hv = 0; hv < CM_NBUCKETS; hv++) n_nonempty += h_cnt.p[hv] != 0;
+        ok = ok && put(&n_nonempty, 4);
+        size_t k = 0;
+        uint32_t prev = 0;
+        for (uint32_t hv = 0; hv < CM_NBUCKETS && ok; hv++) {
+            if (!h_cnt.p[hv]) continue;
+            k += io_varbyte(vb.data() + k, hv - prev);
+            prev = hv;
+            k += io_varbyte(vb.data() + k, h_cnt.p[hv]);
+            if (k > CM_IO_BUFFER - 10) {
+                const int32_t kk = (int32_t) k;
+                ok = put(&kk, 4) && put(vb.data(), k);
+                k = 0;
+            }
+        }
+        if (k && ok) {
+            const int32_t kk = (int32_t) k;
+            ok = put(&kk, 4) && put(vb.data(), k);
+        }
+        if (!compact) {
+            ok = ok && put(&mem_size, 4);
+            for (uint64_t lo = 0; lo < mem64 && ok; lo += CH_SLOTS) {
+                const uint64_t hi = lo + CH_SLOTS < mem64 ? lo + CH_SLOTS : mem64;
+                cudaMemsetAsync(d_chunk, 0, (size_t) (hi - lo) * 6, st);
+                k_fill_ref_table<<<grid_for(CM_NBUCKETS, 256), 256, 0, st>>>(d_cnt, d_off, d.dir, d.cks, d.pos, lo, hi, d_chunk);
+                ctx->launches++;
+                cudaMemcpyAsync(h_chunk, d_chunk, (size_t) (hi - lo) * 6, cudaMemcpyDeviceToHost, st);
+                if (cudaStreamSynchronize(st) != cudaSuccess) return bail(CM_ERR_CUDA, "index write: table pass failed");
+                ok = put(h_chunk, (size_t) (hi - lo) * 6);
+            }
+        }
+        if (!ok) return bail(CM_ERR_ARG, "write failed (disk full?)");
+    }
+    cleanup();
+    if (h_chunk) cudaFreeHost(h_chunk);
+    // finalizeSavingIHashTable: the largest table of the file goes into the header
+    if (fseek(f, 3, SEEK_SET) != 0 || !put(&max_mem, 4)) return fail(ctx, CM_ERR_ARG, "write to %s failed", path);
+    if (fclose(f) != 0) { io.f = nullptr; return fail(ctx, CM_ERR_ARG, "close of %s failed", path); }
+    io.f = nullptr;
+    return CM_OK;
+}
+
+// Reads only what the device build needs from an index file: the header and every contig's packed text; the bucket
+// counts and (full indexes) the six-byte table are skipped with fseek.  Contigs are loaded as ids first_id, first_id + 1 ...
+extern "C" int cm_gpu_load_index_file(cm_gpu_ctx *ctx, const char *path, int first_id, int *n_loaded) {
+    if (!ctx) return CM_ERR_ARG;
+    if (!path) return fail(ctx, CM_ERR_ARG, "null argument");
+    if (n_loaded) *n_loaded = 0;
+    IoFile io;
+    io.f = fopen(path, "rb");
+    if (!io.f) return fail(ctx, CM_ERR_ARG, "cannot open %s", path);
+    FILE *f = io.f;
+    auto get = [&](void *p, size_t n) { return fread(p, 1, n, f) == n; };
+    unsigned char magic = 0, win = 0, csl = 0;
+    uint32_t max_mem = 0, iobuf = 0, cms = 0;
+    int32_t nchr = 0;
+    if (!get(&magic, 1) || !get(&win, 1) || !get(&csl, 1) || !get(&max_mem, 4) || !get(&iobuf, 4) || !get(&cms, 4) || !get(&nchr, 4))
+        return fail(ctx, CM_ERR_ARG, "%s: short header", path);
+    if (magic != 2 && magic != 3) return fail(ctx, CM_ERR_ARG, "%s: unsupported index version %d", path, (int) magic);
+    if (win != CM_WINDOW) return fail(ctx, CM_ERR_ARG, "%s: window size %d, expected %d", path, (int) win, CM_WINDOW);
+    if ((int) win + (int) csl != ctx->p.kmer) return fail(ctx, CM_ERR_ARG, "%s: index k = %d, context k = %d", path, (int) win + (int) csl, ctx->p.kmer);
+    for (int32_t i = 0; i < nchr; i++) {
+        int32_t nl = 0, gl = 0;
+        if (!get(&nl, 4) || nl < 0 || nl > 4096 || fseek(f, nl, SEEK_CUR) != 0 || !get(&gl, 4)) return fail(ctx, CM_ERR_ARG, "%s: bad meta block", path);
+    }
+    int id = first_id;
+    std::vector<unsigned char> vb;
+    while (true) {
+        unsigned char more = 0;
+        int16_t nl = 0;
+        int32_t off = 0;
+        uint32_t len = 0, n_nonempty = 0;
+        if (!get(&more, 1)) break;
+        if (!get(&nl, 2) || nl < 0 || fseek(f, nl, SEEK_CUR) != 0 || !get(&off, 4) || !get(&len, 4)) return fail(ctx, CM_ERR_ARG, "%s: bad contig header", path);
+        if (off != 0) return fail(ctx, CM_ERR_ARG, "%s: contig split into overlapping pieces (larger than CONTIG_SIZE): not supported", path);
+        const size_t n_words = (size_t) len / 21 + (len % 21 ? 1 : 0);
+        HostBuf<uint64_t> cref(n_words);
+        if (!cref.p || !get(cref.p, n_words * 8) || !get(&n_nonempty, 4)) return fail(ctx, CM_ERR_ARG, "%s: short contig", path);
+        for (uint32_t seen = 0; seen < n_nonempty;) {   // varbyte blocks: two terminated numbers per bucket
+            int32_t nb = 0;
+            if (!get(&nb, 4) || nb <= 0) return fail(ctx, CM_ERR_ARG, "%s: bad count block", path);
+            vb.resize((size_t) nb);
+            if (!get(vb.data(), (size_t) nb)) return fail(ctx, CM_ERR_ARG, "%s: short count block", path);
+            uint32_t ends = 0;
+            for (int32_t k = 0; k < nb; k++) ends += vb[k] >> 7;
+            seen += ends / 2;
+        }
+        if (magic == 3) {
+            uint32_t mem = 0;
+            if (!get(&mem, 4) || fseeko(f, (off_t) mem * 6, SEEK_CUR) != 0) return fail(ctx, CM_ERR_ARG, "%s: short table", path);
+        }
+        int r = cm_gpu_build_contig_packed(ctx, id, cref.p, len);
+        if (r != CM_OK) return r;
+        id++;
+        if (n_loaded) *n_loaded = id - first_id;
+        if (!more) break;
+    }
+    return CM_OK;
+}

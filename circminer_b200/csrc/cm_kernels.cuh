@@ -387,3 +387,58 @@ __global__ void __launch_bounds__(128) k_chain_walk(const __grid_constant__ DevV
     cm_chain_walk(x, ch, b.strands + (size_t) s * b.stride, b.strand_len[s], kind == 2, b.aux[id], b.spec + 2 * (size_t) id);
     stats_flush(x.st, 0u, ctr);
 }
+
+// ------------------------------------------------------------------------------------------
+// Rounds on the device.  The reference maps one packed contig per "round" (src/circminer.cpp:229-308): a pair that
+// is final in round c is printed, every other pair is written to the remain FASTQs with its MatchedRead in the
+// header (src/filter.cpp:413-455) and parsed back in round c + 1 (src/fastq_parser.cpp:203-269).  With every
+// contig resident the same state machine runs here without files: k_round_commit applies the skip rule
+// (src/circminer.cpp:386-390) to the results of one contig, k_round_compact gathers the survivors' rows, seed keys
+// and carried MatchedRead (after the header's lossy round trip) into the batch of the next contig.
+// ------------------------------------------------------------------------------------------
+// one thread per pair of the current batch; ids == nullptr: the batch is the caller's (pair k is input pair k)
+__global__ void k_round_commit(const __grid_constant__ cm_params p, uint32_t n_cur, const uint32_t *__restrict__ ids,
+                               const cm_mread *__restrict__ out, const int32_t *__restrict__ state,
+                               const uint16_t *__restrict__ strand_len, int is_last, int contig_id,
+                               cm_mread *__restrict__ final_mread, int32_t *__restrict__ final_state,
+                               int32_t *__restrict__ final_round, uint8_t *__restrict__ survive,
+                               cm_mread *__restrict__ snap_mread, int32_t *__restrict__ snap_state) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_cur) return;
+    const uint32_t id = ids ? ids[k] : k;
+    const cm_mread m = out[k];
+    const int st = state[k];
+    const bool skip = cm_skip_rule(p, st, m, (int) strand_len[4 * (size_t) k] + (int) strand_len[4 * (size_t) k + 2]);
+    if (snap_mread) snap_mread[id] = m;
+    if (snap_state) snap_state[id] = st;
+    const bool fin = skip || is_last;
+    if (fin) {
+        final_mread[id] = m;
+        final_state[id] = st;
+        if (final_round) final_round[id] = contig_id;
+    }
+    survive[k] = fin ? 0 : 1;
+}
+
+// one warp per surviving pair: rows of the four strands, their lengths and seed keys, the carried MatchedRead
+__global__ void __launch_bounds__(256) k_round_compact(const __grid_constant__ cm_params p, uint32_t n_surv, const uint32_t *__restrict__ surv,
+                                const uint32_t *__restrict__ ids, uint32_t stride, int F,
+                                const uint8_t *__restrict__ strands, const uint16_t *__restrict__ slen, const int2 *__restrict__ key,
+                                const cm_mread *__restrict__ out,
+                                uint8_t *__restrict__ strands_n, uint16_t *__restrict__ slen_n, int2 *__restrict__ key_n,
+                                cm_mread *__restrict__ in_n, uint32_t *__restrict__ ids_n) {
+    const uint32_t j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (j >= n_surv) return;
+    const uint32_t k = surv[j];
+    const uint4 *src = (const uint4 *) (strands + (size_t) 4 * k * stride);
+    uint4 *dst = (uint4 *) (strands_n + (size_t) 4 * j * stride);
+    for (uint32_t w = lane; w < stride / 4; w += 32) dst[w] = src[w];   // 4 rows of stride bytes = stride / 4 uint4
+    const int2 *ks = key + (size_t) 4 * k * F;
+    int2 *kd = key_n + (size_t) 4 * j * F;
+    for (int w = (int) lane; w < 4 * F; w += 32) kd[w] = ks[w];
+    if (lane < 4) slen_n[4 * (size_t) j + lane] = slen[4 * (size_t) k + lane];
+    if (lane == 0) {
+        in_n[j] = cm_header_round_trip(out[k], p);
+        ids_n[j] = ids ? ids[k] : k;
+    }
+}

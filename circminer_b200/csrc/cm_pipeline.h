@@ -8,6 +8,7 @@
 #include "cm_align.h"
 #include "cm_extend.h"
 #include "cm_filter.h"
+#include "cm_rounds.h"
 
 // Device-resident batch layout (all arrays indexed by strand; PE pair i owns strands 4i..4i+3 =
 // R1 fwd, R1 rc, R2 fwd, R2 rc; SE read i owns 2i, 2i+1).

@@ -166,12 +166,12 @@ def write_fasta(path, chroms):
             f.write(b"\n")
 
 
-def write_gtf(path, genes):
+def write_gtf(path, genes, names=None):
     with open(path, "w") as f:
         f.write("#!synthetic annotation\n")
         tcount = 0
         for gi, g in enumerate(genes):
-            ch = chrom_name(g["chr"])
+            ch = names[g["chr"]] if names else chrom_name(g["chr"])
             gid = f"SG{gi:06d}"
             attr_g = f'gene_id "{gid}"; gene_name "N{gi}";'
             f.write(f"{ch}\tsynth\tgene\t{g['start']}\t{g['end']}\t.\t{g['strand']}\t.\t{attr_g}\n")
@@ -219,9 +219,10 @@ def _build_pools(cfg, chroms, genes, rng):
             circ, np.array(circ_off, np.int64), np.array(circ_len, np.int64))
 
 
-def make_reads(cfg: SynthConfig, chroms, genes):
+def make_reads(cfg: SynthConfig, chroms, genes, genome=None, avoid_n=False):
     """Returns (r1, r2) uint8 code arrays of shape (n_pairs, read_len) and a kind array
-    (0 linear, 1 circ, 2 genomic)."""
+    (0 linear, 1 circ, 2 genomic).  genome: the chromosomes back to back when the caller already holds them as
+    one array; avoid_n: redraw genomic fragments that start or end in an N block (GRCh38-scale references)."""
     rng = np.random.default_rng(cfg.seed_reads)
     n, L = cfg.n_pairs, cfg.read_len
     lin, lin_off, lin_len, circ, circ_off, circ_len = _build_pools(cfg, chroms, genes, rng)
@@ -235,7 +236,8 @@ def make_reads(cfg: SynthConfig, chroms, genes):
     r1 = np.empty((n, L), np.uint8)
     r2 = np.empty((n, L), np.uint8)
     ar = np.arange(L)
-    genome = np.concatenate(chroms)
+    if genome is None:
+        genome = np.concatenate(chroms)
     goff = np.concatenate([[0], np.cumsum([len(c) for c in chroms])])
 
     CH = 200_000
@@ -268,6 +270,12 @@ def make_reads(cfg: SynthConfig, chroms, genes):
             clen = np.array([len(x) for x in chroms])[c]
             st = (rng.random(len(sel)) * (clen - F[sel] - 2000)).astype(np.int64) + 1000
             base = goff[c] + st
+            if avoid_n:
+                for _ in range(8):
+                    bad = np.nonzero((genome[base] == 4) | (genome[base + F[sel] - 1] == 4))[0]
+                    if not len(bad):
+                        break
+                    base[bad] = goff[c[bad]] + 1000 + (rng.random(len(bad)) * (clen[bad] - F[sel][bad] - 2000)).astype(np.int64)
             left[sel] = genome[base[:, None] + ar]
             right[sel] = genome[(base + F[sel] - L)[:, None] + ar]
         flip = rng.random(m) < 0.5

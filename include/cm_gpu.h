@@ -169,6 +169,18 @@ int cm_gpu_build_contig(cm_gpu_ctx *ctx, int contig_id, const char *contig_seq, 
  * lib/mrsfast/RefGenome.c; 21 bases per 64-bit word, Common.c:174-196): what a host that has just run
  * loadHashTable() holds, without converting and uploading its bucket table. */
 int cm_gpu_build_contig_packed(cm_gpu_ctx *ctx, int contig_id, const uint64_t *cref_gen, uint32_t ref_gen_len);
+/* The reference's on-disk index, <ref>.packed.fa.index, without the reference's builder and loader:
+ *   cm_gpu_write_index      writes the file `circminer --index` would write (generateHashTableOnDisk / generateHashTable,
+ *                           src/mrsfast/HashTable.c:257-481; format :106-254) from resident contigs 0 .. n_contigs - 1
+ *                           (names "1", "2", ... as GenomePacker::pack_genome numbers them, src/genome.cpp:96-145);
+ *                           compact != 0: counts only (magic 2, `-m`).  Every packed contig must fit one piece
+ *                           (non-N bases <= CONTIG_SIZE), as GenomePacker guarantees for chromosomes <= 1.1 Gbp.
+ *   cm_gpu_load_index_file  reads the header and every contig's packed text from such a file (the bucket counts and
+ *                           the six-byte table are skipped, not read) and builds the device index of each, ids
+ *                           first_id, first_id + 1, ...: what loadHashTable (HashTable.c:971-1057) + cm_gpu_build_contig_packed
+ *                           do, at 0.4 bytes of file I/O per base instead of ~8. */
+int cm_gpu_write_index(cm_gpu_ctx *ctx, const char *path, int n_contigs, int compact, uint32_t contig_max_size);
+int cm_gpu_load_index_file(cm_gpu_ctx *ctx, const char *path, int first_id, int *n_loaded);
 int cm_gpu_contig_stats(cm_gpu_ctx *ctx, int contig_id, uint64_t *n_entries, uint32_t *ref_gen_len);
 /* debugging / parity: copy the positions of bucket hv (all checksums) back */
 int cm_gpu_read_bucket(cm_gpu_ctx *ctx, int contig_id, uint32_t hv, uint32_t cap, uint16_t *checksum,
@@ -227,6 +239,29 @@ int cm_gpu_stage_batch_pe(cm_gpu_ctx *ctx, uint32_t n, const char *seqs1, const 
                           const uint16_t *len1, const uint16_t *len2, const cm_mread *in);
 int cm_gpu_run_staged_pe(cm_gpu_ctx *ctx, int contig_id, int upto_stage /* 1 seed, 2 chain, 3 all */);
 int cm_gpu_fetch_staged_pe(cm_gpu_ctx *ctx, cm_mread *out, int32_t *state);
+
+/* ---- rounds --------------------------------------------------------------- */
+/* The reference's round loop for one batch with every packed contig resident (mapping(), src/circminer.cpp:229-308):
+ * contigs first_contig .. first_contig + n_contigs - 1 in order.  After each contig the skip rule of map_reads
+ * (src/circminer.cpp:386-390: scan-lev 0 -> a CONCRD pair is final; scan-lev 1 -> CONCRD, gm-compatible, no edits,
+ * fully matched; scan-lev 2 -> never) picks the pairs the reference prints in that round; every other pair goes on to
+ * the next contig with the MatchedRead the reference would read back from the remain-FASTQ header
+ * (FilterRead::write_read_category src/filter.cpp:413-455 -> FASTQParser::fill_map_info src/fastq_parser.cpp:203-269:
+ * unmapped types keep only `type`).  Survivors are compacted on the device; nothing returns to the host between contigs.
+ *   out[i], state[i]   MatchedRead / process_read return of pair i in the round it was printed (skip, or last contig)
+ *   final_round[i]     that contig (nullable)
+ *   round_out, round_state   optional [n_contigs][n] snapshots after every contig, state -1 where the pair was already
+ *                      final (what the per-round remain files of a `-z` run hold); for parity tests. */
+int cm_gpu_map_rounds_pe(cm_gpu_ctx *ctx, int first_contig, int n_contigs, uint32_t n, const char *seqs1, const char *seqs2,
+                         uint32_t stride, const uint16_t *len1, const uint16_t *len2, const cm_mread *in, cm_mread *out,
+                         int32_t *state, int32_t *final_round, cm_mread *round_out, int32_t *round_state);
+/* the same on the batch staged by cm_gpu_stage_batch_pe (kernel-only timing; the staged batch is left intact) */
+int cm_gpu_run_staged_rounds_pe(cm_gpu_ctx *ctx, int first_contig, int n_contigs);
+int cm_gpu_fetch_rounds_pe(cm_gpu_ctx *ctx, cm_mread *out, int32_t *state, int32_t *final_round);
+/* device ms of the last rounds call: [0] unused, [1] seed, [2] chain, [3] extend+classify, [4] sum of the contigs' stage
+ * totals, [5] the whole call on the stream (commit / compaction included), [6] k_chain_spec, [7] k_chain_walk;
+ * pairs_per_round[r] = pairs that visited the r-th contig (cap entries).  Returns the number of contigs visited. */
+int cm_gpu_last_rounds_ms(cm_gpu_ctx *ctx, float out[8], uint32_t *pairs_per_round, int cap);
 
 #ifdef __cplusplus
 }

@@ -282,6 +282,49 @@ int hs_process_batch_pe(HsCtx *c, int contig_id, uint32_t n, const char *seqs1, 
     return 0;
 }
 
+// cm_gpu_map_rounds_pe on the host: the same skip rule / header round trip (cm_rounds.h), survivors as an index list
+int hs_map_rounds_pe(HsCtx *c, int first, int n_contigs, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
+                     const uint16_t *len1, const uint16_t *len2, const cm_mread *in, cm_mread *out, int32_t *state,
+                     int32_t *final_round, cm_mread *round_out, int32_t *round_state) {
+    std::vector<uint32_t> ids(n);
+    for (uint32_t i = 0; i < n; i++) ids[i] = i;
+    std::vector<cm_mread> cur(in, in + n);
+    if (round_state) for (size_t k = 0; k < (size_t) n_contigs * n; k++) round_state[k] = -1;
+    for (int r = 0; r < n_contigs && !ids.empty(); r++) {
+        const uint32_t m = (uint32_t) ids.size();
+        std::vector<char> s1((size_t) m * stride), s2((size_t) m * stride);
+        std::vector<uint16_t> l1(m), l2(m);
+        std::vector<cm_mread> o(m);
+        std::vector<int32_t> st(m);
+        for (uint32_t k = 0; k < m; k++) {
+            memcpy(&s1[(size_t) k * stride], seqs1 + (size_t) ids[k] * stride, stride);
+            memcpy(&s2[(size_t) k * stride], seqs2 + (size_t) ids[k] * stride, stride);
+            l1[k] = len1[ids[k]];
+            l2[k] = len2[ids[k]];
+        }
+        hs_process_batch_pe(c, first + r, m, s1.data(), s2.data(), stride, l1.data(), l2.data(), cur.data(), o.data(), st.data(), nullptr);
+        const bool last = r == n_contigs - 1;
+        std::vector<uint32_t> nids;
+        std::vector<cm_mread> ncur;
+        for (uint32_t k = 0; k < m; k++) {
+            const uint32_t id = ids[k];
+            if (round_out) round_out[(size_t) r * n + id] = o[k];
+            if (round_state) round_state[(size_t) r * n + id] = st[k];
+            if (cm_skip_rule(c->p, st[k], o[k], (int) l1[k] + (int) l2[k]) || last) {
+                out[id] = o[k];
+                state[id] = st[k];
+                if (final_round) final_round[id] = first + r;
+            } else {
+                nids.push_back(id);
+                ncur.push_back(cm_header_round_trip(o[k], c->p));
+            }
+        }
+        ids.swap(nids);
+        cur.swap(ncur);
+    }
+    return 0;
+}
+
 int hs_process_batch_se(HsCtx *c, int contig_id, uint32_t n, const char *seqs, uint32_t stride, const uint16_t *len, int32_t *state) {
     DevView v = make_view(c, contig_id);
     HsBatch B;

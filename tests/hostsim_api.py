@@ -115,6 +115,19 @@ class HostSim:
                                      _vp(l1), _vp(l2), _vp(mreads), _vp(out), _vp(state), C.byref(self.ctr))
         return out, state
 
+    def map_rounds(self, seqs1, seqs2, mreads, first=0, n_contigs=1, lens1=None, lens2=None, snapshots=False):
+        a1, l1 = _rows(seqs1, lens1)
+        a2, l2 = _rows(seqs2, lens2)
+        n = a1.shape[0]
+        res = dict(out=np.zeros(n, MREAD_DTYPE), state=np.zeros(n, np.int32), final_round=np.zeros(n, np.int32))
+        if snapshots:
+            res["round_out"] = np.zeros((n_contigs, n), MREAD_DTYPE)
+            res["round_state"] = np.zeros((n_contigs, n), np.int32)
+        self.lib.hs_map_rounds_pe(self.ctx, first, n_contigs, C.c_uint32(n), _vp(a1), _vp(a2), C.c_uint32(a1.shape[1]), _vp(l1),
+                                  _vp(l2), _vp(np.ascontiguousarray(mreads)), _vp(res["out"]), _vp(res["state"]),
+                                  _vp(res["final_round"]), _vp(res.get("round_out")), _vp(res.get("round_state")))
+        return res
+
     def process_read_se(self, contig_id, seqs, lens=None):
         a, l = _rows(seqs, lens)
         state = np.zeros(a.shape[0], np.int32)
