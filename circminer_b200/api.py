@@ -369,6 +369,11 @@ class Mapper:
         self._chk(self.lib.cm_gpu_last_align_ms(self.ctx, a), "cm_gpu_last_align_ms")
         return list(a)
 
+    def int32_peak(self) -> float:
+        v = C.c_double()
+        self._chk(self.lib.cm_gpu_int32_peak(self.ctx, C.byref(v)), "cm_gpu_int32_peak")
+        return v.value
+
     def counters(self, reset=False) -> dict:
         c = CmCounters()
         self._chk(self.lib.cm_gpu_get_counters(self.ctx, C.byref(c), int(reset)), "cm_gpu_get_counters")

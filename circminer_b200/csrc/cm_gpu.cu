@@ -76,10 +76,11 @@ struct cm_gpu_ctx {
     bool sync_each = false;    // CM_GPU_SYNC_EACH=1: synchronise after every launch and name the kernel that failed
     uint32_t heavy_th = 64;    // CM_GPU_HEAVY_TH: strands with more dp cells than this are chained by one warp each (< 255)
     uint32_t last_heavy = 0;
-    // CM_GPU_HEAVY_PAIR_TH: pairs with more candidate chain pairs than this get one warp each.  Unset: 16 for batches of
-    // up to heavy_pair_batch pairs, where such a pair is the critical path of the launch (6.3 -> 1.3 ms at 125 k pairs
-    // of C2); off for larger batches, which are throughput-bound and where the warp kernel costs more than it saves.
-    uint32_t heavy_pair_th = 16, heavy_pair_batch = 300000;
+    // CM_GPU_HEAVY_PAIR_TH: pairs whose weight (candidate chain pairs of both attempts + chains of the four strands, i.e.
+    // the MatePairs process_mates may extend plus the unpaired chains it extends afterwards) exceeds this get one warp
+    // each: candidates and leftover chains run one per lane.  On a GRCh38-scale batch a tenth of the pairs carry 30 chains
+    // per strand and, one thread each, were 2/3 of the step (extend stage 236 -> 81 ms per million pairs).
+    uint32_t heavy_pair_th = 40;
     int pair_sig = 2;
     bool heavy_pair_forced = false;
     uint32_t last_heavy_pairs = 0;
@@ -91,7 +92,10 @@ struct cm_gpu_ctx {
     DevBuf scratch[8];
     // rounds on the device (cm_gpu_map_rounds_pe): two compacted batches used in turn, per-pair final results
     DevBuf rb_strands[2], rb_slen[2], rb_key[2], rb_in[2], rb_ids[2];
-    DevBuf fin_mread, fin_state, fin_round, surv_flag, surv_idx, surv_n, snap_mread, snap_state;
+    DevBuf fin_mread, fin_state, fin_round, surv_flag, surv_idx, surv_n, snap_mread, snap_state, round_out, round_state;
+    cm_mread *out_view = nullptr;              // where launch_process writes when a round runs in chunks (else out_mread / out_state)
+    int32_t *state_view = nullptr;
+    uint32_t chunk_pairs = 1u << 20;           // CM_GPU_CHUNK: pairs per pipeline pass inside cm_gpu_map_rounds_pe
     cudaEvent_t ev_r[2]{};
     float rounds_ms[6] = {0, 0, 0, 0, 0, 0};   // stage sums over the rounds, [5] the whole run
     float rounds_align_ms[2] = {0, 0};
@@ -228,6 +232,7 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
     if (const char *e = getenv("CM_GPU_NO_WALK_SPEC")) ctx->no_walk_spec = atoi(e) != 0;
     if (const char *e = getenv("CM_GPU_NO_SPEC")) ctx->no_spec = atoi(e) != 0;
     if (const char *e = getenv("CM_GPU_SYNC_EACH")) ctx->sync_each = atoi(e) != 0;
+    if (const char *e = getenv("CM_GPU_CHUNK")) { long c = atol(e); ctx->chunk_pairs = (uint32_t) (c < 1024 ? 1024 : c); }
     if (const char *e = getenv("CM_GPU_DBG")) {
         int f = atoi(e);
         cudaMemcpyToSymbol(g_cm_dbg_flags, &f, sizeof f);
@@ -270,7 +275,8 @@ extern "C" int cm_gpu_destroy(cm_gpu_ctx *ctx) {
     for (int q = 0; q < 2; q++) { release(ctx->spec_key[q]); release(ctx->spec_item[q]); }
     for (int q = 0; q < 2; q++) { release(ctx->key32[q]); release(ctx->key64[q]); release(ctx->perm[q]); }
     for (int q = 0; q < 2; q++) { release(ctx->rb_strands[q]); release(ctx->rb_slen[q]); release(ctx->rb_key[q]); release(ctx->rb_in[q]); release(ctx->rb_ids[q]); }
-    DevBuf *rbufs[] = {&ctx->fin_mread, &ctx->fin_state, &ctx->fin_round, &ctx->surv_flag, &ctx->surv_idx, &ctx->surv_n, &ctx->snap_mread, &ctx->snap_state};
+    DevBuf *rbufs[] = {&ctx->fin_mread, &ctx->fin_state, &ctx->fin_round, &ctx->surv_flag, &ctx->surv_idx, &ctx->surv_n, &ctx->snap_mread, &ctx->snap_state,
+                       &ctx->round_out, &ctx->round_state};
     for (DevBuf *b : rbufs) release(*b);
     cudaFree(ctx->d_counters);
     for (auto &ev : ctx->ev) cudaEventDestroy(ev);

@@ -190,9 +190,17 @@ static int launch_chain(cm_gpu_ctx *ctx, const DevView &v, BatchDev &b) {
 static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) {
     if (!ctx->n_pairs) return CM_OK;
     const uint32_t n = ctx->n_pairs;
-    ENSURE(ctx, ctx->out_state, (size_t) n * 4);
+    int32_t *out_state = ctx->state_view;
+    cm_mread *out_mread = ctx->out_view;
+    if (!out_state) {
+        ENSURE(ctx, ctx->out_state, (size_t) n * 4);
+        out_state = (int32_t *) ctx->out_state.p;
+    }
     if (ctx->staged_pe) {
-        ENSURE(ctx, ctx->out_mread, (size_t) n * sizeof(cm_mread));
+        if (!out_mread) {
+            ENSURE(ctx, ctx->out_mread, (size_t) n * sizeof(cm_mread));
+            out_mread = (cm_mread *) ctx->out_mread.p;
+        }
         ENSURE(ctx, ctx->key64[0], (size_t) n * 8);
         ENSURE(ctx, ctx->key64[1], (size_t) n * 8);
         ENSURE(ctx, ctx->perm[0], (size_t) n * 4);
@@ -201,7 +209,7 @@ static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) 
         ENSURE(ctx, ctx->ovf_n, 8);
         uint32_t *d_heavy = (uint32_t *) ctx->ovf_n.p + 1;
         CUDA_TRY(ctx, cudaMemsetAsync(d_heavy, 0, 4, st));
-        const bool split_heavy = ctx->heavy_pair_forced || n <= ctx->heavy_pair_batch;
+        const bool split_heavy = ctx->heavy_pair_th != 0xFFFFFFFFu;
         k_pair_key<<<grid_for(n, 256), 256, 0, st>>>(v, b, n, (unsigned long long *) ctx->key64[0].p, (uint32_t *) ctx->perm[0].p,
                                                      split_heavy ? ctx->heavy_pair_th : 0xFFFFFFFFu, d_heavy, ctx->pair_sig);
         size_t tb = 0;
@@ -222,17 +230,17 @@ static int launch_process(cm_gpu_ctx *ctx, const DevView &v, const BatchDev &b) 
             cudaEventRecord(ctx->ev_fork, st);
             cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0);
             k_process_pe_warp<<<grid_for((size_t) n_heavy * 32, 128), 128, 0, ctx->stream2>>>(
-                v, b, (const cm_mread *) ctx->in_mread.p, (cm_mread *) ctx->out_mread.p, (int32_t *) ctx->out_state.p, n_heavy,
+                v, b, (const cm_mread *) ctx->in_mread.p, out_mread, out_state, n_heavy,
                 (const uint32_t *) ctx->perm[1].p, ctx->d_counters);
             cudaEventRecord(ctx->ev_join, ctx->stream2);
             ctx->launches++;
         }
         if (n > n_heavy)
-            k_process_pe<<<grid_for(n - n_heavy, CM_PE_BLOCK), CM_PE_BLOCK, 0, st>>>(v, b, (const cm_mread *) ctx->in_mread.p, (cm_mread *) ctx->out_mread.p,
-                                                      (int32_t *) ctx->out_state.p, n - n_heavy, (const uint32_t *) ctx->perm[1].p + n_heavy, ctx->d_counters);
+            k_process_pe<<<grid_for(n - n_heavy, CM_PE_BLOCK), CM_PE_BLOCK, 0, st>>>(v, b, (const cm_mread *) ctx->in_mread.p, out_mread,
+                                                      out_state, n - n_heavy, (const uint32_t *) ctx->perm[1].p + n_heavy, ctx->d_counters);
         if (n_heavy) cudaStreamWaitEvent(st, ctx->ev_join, 0);
     } else {
-        k_process_se<<<grid_for(n, 128), 128, 0, ctx->stream>>>(v, b, (int32_t *) ctx->out_state.p, n, ctx->d_counters);
+        k_process_se<<<grid_for(n, 128), 128, 0, ctx->stream>>>(v, b, out_state, n, ctx->d_counters);
     }
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
@@ -449,22 +457,46 @@ static int run_rounds(cm_gpu_ctx *ctx, int first, int n_contigs, bool want_snap)
     StagedBatchGuard guard(ctx);
     const uint32_t *ids = nullptr;
     int cur = -1;   // -1: the caller's staged batch, 0 / 1: compacted set in use
+    const uint32_t chunk = ctx->chunk_pairs;
+    ENSURE(ctx, ctx->round_out, (size_t) n * sizeof(cm_mread));
+    ENSURE(ctx, ctx->round_state, (size_t) n * 4);
     cudaEventRecord(ctx->ev_r[0], st);
     for (int r = 0; r < n_contigs; r++) {
         const int c = first + r;
         const bool last = r == n_contigs - 1;
-        int rc = run_pipeline(ctx, c, 3);
-        if (rc != CM_OK) return rc;
-        for (int k = 1; k < 5; k++) ctx->rounds_ms[k] += ctx->stage_ms[k];
-        {
-            float am[2];
-            if (cm_gpu_last_align_ms(ctx, am) == CM_OK) { ctx->rounds_align_ms[0] += am[0]; ctx->rounds_align_ms[1] += am[1]; }
-        }
         const uint32_t n_cur = ctx->n_pairs;
+        // the round's batch in chunks of at most chunk_pairs pairs: the arenas of the chaining and pre-alignment stages
+        // are sized by the chunk, not by the batch (a repeat-rich GRCh38 batch needs ~30 GB per million pairs)
+        {
+            const DevBuf r_strands = ctx->strands, r_slen = ctx->strand_len, r_key = ctx->seed_key, r_in = ctx->in_mread;
+            int rc = CM_OK;
+            for (uint32_t start = 0; start < n_cur && rc == CM_OK; start += chunk) {
+                const uint32_t mcur = n_cur - start < chunk ? n_cur - start : chunk;
+                ctx->strands.p = (uint8_t *) r_strands.p + (size_t) 4 * start * ctx->stride;
+                ctx->strand_len.p = (uint16_t *) r_slen.p + (size_t) 4 * start;
+                ctx->seed_key.p = (int2 *) r_key.p + (size_t) 4 * start * ctx->batch_F;
+                ctx->in_mread.p = (cm_mread *) r_in.p + start;
+                ctx->out_view = (cm_mread *) ctx->round_out.p + start;
+                ctx->state_view = (int32_t *) ctx->round_state.p + start;
+                ctx->n_pairs = mcur;
+                ctx->n_strands = 4 * mcur;
+                rc = run_pipeline(ctx, c, 3);
+                if (rc == CM_OK) {
+                    for (int k = 1; k < 5; k++) ctx->rounds_ms[k] += ctx->stage_ms[k];
+                    float am[2];
+                    if (cm_gpu_last_align_ms(ctx, am) == CM_OK) { ctx->rounds_align_ms[0] += am[0]; ctx->rounds_align_ms[1] += am[1]; }
+                }
+            }
+            ctx->strands = r_strands; ctx->strand_len = r_slen; ctx->seed_key = r_key; ctx->in_mread = r_in;
+            ctx->out_view = nullptr; ctx->state_view = nullptr;
+            ctx->n_pairs = n_cur;
+            ctx->n_strands = 4 * n_cur;
+            if (rc != CM_OK) return rc;
+        }
         ctx->round_pairs[r] = n_cur;
         ctx->rounds_run = r + 1;
         k_round_commit<<<grid_for(n_cur, 256), 256, 0, st>>>(
-            ctx->p, n_cur, ids, (const cm_mread *) ctx->out_mread.p, (const int32_t *) ctx->out_state.p, (const uint16_t *) ctx->strand_len.p,
+            ctx->p, n_cur, ids, (const cm_mread *) ctx->round_out.p, (const int32_t *) ctx->round_state.p, (const uint16_t *) ctx->strand_len.p,
             last ? 1 : 0, c, (cm_mread *) ctx->fin_mread.p, (int32_t *) ctx->fin_state.p, (int32_t *) ctx->fin_round.p,
             (uint8_t *) ctx->surv_flag.p, want_snap ? (cm_mread *) ctx->snap_mread.p + (size_t) r * n : nullptr,
             want_snap ? (int32_t *) ctx->snap_state.p + (size_t) r * n : nullptr);
@@ -490,7 +522,7 @@ static int run_rounds(cm_gpu_ctx *ctx, int first, int n_contigs, bool want_snap)
         ENSURE(ctx, ctx->rb_ids[nx], (size_t) n_surv * 4);
         k_round_compact<<<grid_for((size_t) n_surv * 32, 256), 256, 0, st>>>(
             ctx->p, n_surv, (const uint32_t *) ctx->surv_idx.p, ids, ctx->stride, F, (const uint8_t *) ctx->strands.p,
-            (const uint16_t *) ctx->strand_len.p, (const int2 *) ctx->seed_key.p, (const cm_mread *) ctx->out_mread.p,
+            (const uint16_t *) ctx->strand_len.p, (const int2 *) ctx->seed_key.p, (const cm_mread *) ctx->round_out.p,
             (uint8_t *) ctx->rb_strands[nx].p, (uint16_t *) ctx->rb_slen[nx].p, (int2 *) ctx->rb_key[nx].p, (cm_mread *) ctx->rb_in[nx].p,
             (uint32_t *) ctx->rb_ids[nx].p);
         ctx->launches++;

@@ -272,3 +272,48 @@ extern "C" int cm_gpu_load_index_file(cm_gpu_ctx *ctx, const char *path, int fir
     }
     return CM_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// INT32 roofline calibration: add + max chains, 8 independent accumulators per thread, so the
+// integer pipes are the only limit.  Returns lane-operations per second (one IADD or IMNMX of one lane = 1).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_int32_peak(int *__restrict__ out, int iters, int a, int b) {
+    int x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            x0 = max(x0 + a, b); x1 = max(x1 + a, b); x2 = max(x2 + a, b); x3 = max(x3 + a, b);
+            x4 = max(x4 + a, b); x5 = max(x5 + a, b); x6 = max(x6 + a, b); x7 = max(x7 + a, b);
+            b ^= u;
+        }
+    }
+    const int s = x0 ^ x1 ^ x2 ^ x3 ^ x4 ^ x5 ^ x6 ^ x7;
+    if (s == 0x7fffffff) out[0] = s;   // keeps the chains alive
+}
+
+extern "C" int cm_gpu_int32_peak(cm_gpu_ctx *ctx, double *lane_ops_per_s) {
+    if (!ctx || !lane_ops_per_s) return CM_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    ENSURE(ctx, ctx->scratch[7], 64);
+    const int iters = 4096, blocks = sms * 8;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; rep++) {
+        cudaEventRecord(e0, ctx->stream);
+        k_int32_peak<<<blocks, 256, 0, ctx->stream>>>((int *) ctx->scratch[7].p, iters, 1, -1000000);
+        cudaEventRecord(e1, ctx->stream);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return fail(ctx, CM_ERR_CUDA, "int32 probe failed"); }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (rep && ms < best) best = ms;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    ctx->launches += 4;
+    *lane_ops_per_s = (double) blocks * 256.0 * iters * 8.0 * 8.0 * 2.0 / (best * 1e-3);
+    return CM_OK;
+}

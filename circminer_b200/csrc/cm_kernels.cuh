@@ -278,8 +278,9 @@ __global__ void k_pair_key(const __grid_constant__ DevView v, const __grid_const
         }
         k = (k << 8) | w;
     }
-    // pairs with more than heavy_th candidate chain pairs (both attempts) sort to the front: one warp each
-    const bool heavy = (uint32_t) (cnt[0] * cnt[3] + cnt[2] * cnt[1]) > heavy_th;
+    // pairs heavier than heavy_th (candidate chain pairs of both attempts + chains to extend as leftovers) sort to the
+    // front: one warp each
+    const bool heavy = (uint32_t) (cnt[0] * cnt[3] + cnt[2] * cnt[1] + cnt[0] + cnt[1] + cnt[2] + cnt[3]) > heavy_th;
     if (heavy) k |= 1ull << (sig_mode ? 51 : 43);
     key[i] = k;
     idx[i] = i;

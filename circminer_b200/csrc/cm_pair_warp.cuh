@@ -28,6 +28,54 @@ __device__ __forceinline__ bool cw_same_mread(const cm_mread &a, const cm_mread 
     return same;
 }
 
+// The unpaired chains of one side (src/filter.cpp:356-386), one lane per chain.  The reference extends them one after the
+// other into ONE MatchedMate: the value extend_chain_both_sides returns does not depend on what the previous chain left
+// in it (every field it reads it has written first), min_ret is a minimum over the chains, and the exon look-ups behind
+// r*_genic happen only for the first unpaired chain (overlap_to_spos / _epos return at once when looked_up_* is set,
+// src/utils.cpp:667-683) -- so the lanes are independent and the fold is exact.
+__device__ __forceinline__ void cw_leftover_side(FilterCtx &f, const StrandView &sv, uint32_t paired, int dir, int &min_ret, bool &genic) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = (int) (threadIdx.x & 31u);
+    const int n = sv.chains.count;
+    const uint32_t todo = ~paired & (n >= 32 ? FULL : ((1u << n) - 1u));
+    if (min_ret == CM_CONCRD || !todo) return;
+    const AnnotDev &a = f.x.v->a;
+    MateD mm;
+    mate_init(mm, f.x.v->p);
+    int ex = 0x7fffffff;
+    if ((todo >> lane) & 1u) ex = cm_extend_chain_both_sides(f.x, cl_chain(sv.chains, lane), sv.seq, sv.seq_len, mm, dir);
+    const int m = __reduce_min_sync(FULL, ex);
+    min_ret = m < min_ret ? m : min_ret;
+    const int first = __ffs(todo) - 1;
+    int g = 0;
+    if (lane == first) {
+        cm_overlap_to_spos(a, mm);
+        cm_overlap_to_epos(a, mm);
+        g = (mm.exons_spos >= 0) || (mm.exons_epos >= 0);
+    }
+    genic = __shfl_sync(FULL, g, first) != 0;
+}
+
+// The rest of process_mates after the MatePair loop (cm_mates_leftovers), by one warp
+__device__ int cw_mates_leftovers(FilterCtx &f, const StrandView &fw, const StrandView &bw, cm_mread &mr, uint32_t f_paired,
+                                  uint32_t b_paired, MatesAcc acc) {
+    if (mr.type == CM_CONCRD || mr.type == CM_DISCRD || mr.type == CM_CHIORF || mr.type == CM_CHIBSJ || mr.type == CM_CHI2BSJ)
+        return mr.type;
+    int min_ret1 = acc.min_ret1, min_ret2 = acc.min_ret2;
+    bool r1_genic = acc.r1_genic, r2_genic = acc.r2_genic;
+    cw_leftover_side(f, fw, f_paired, 1, min_ret1, r1_genic);
+    cw_leftover_side(f, bw, b_paired, -1, min_ret2, r2_genic);
+    int new_type = (((min_ret1 == CM_ORPHAN) && (min_ret2 == CM_CONCRD)) || ((min_ret1 == CM_CONCRD) && (min_ret2 == CM_ORPHAN)))
+                       ? CM_OEANCH
+                       : ((min_ret1 == CM_ORPHAN) || (min_ret2 == CM_ORPHAN))
+                             ? CM_ORPHAN
+                             : ((min_ret1 == CM_CONCRD) && (min_ret2 == CM_CONCRD) && (r1_genic && r2_genic))
+                                   ? CM_CHIFUS
+                                   : ((min_ret1 == CM_CONCRD) && (min_ret2 == CM_CONCRD)) ? CM_OEA2 : CM_CANDID;
+    mr_update_type(mr, new_type);
+    return mr.type;
+}
+
 // process_mates by one warp; every lane enters and leaves with the same mr and return value
 __device__ int cw_process_mates(FilterCtx &f, const StrandView &fw, const StrandView &bw, cm_mread &mr, bool r1_forward) {
     const unsigned FULL = 0xffffffffu;
@@ -102,11 +150,7 @@ __device__ int cw_process_mates(FilterCtx &f, const StrandView &fw, const Strand
             start += upto + 1;
         }
     }
-    // unpaired chains and the fallback type: every lane runs the same code on the same state (counted once)
-    const AlignStats keep = f.x.st;
-    const int ret = cm_mates_leftovers(f, fw, bw, mr, f_paired, b_paired, acc);
-    if (lane != 0) f.x.st = keep;
-    return ret;
+    return cw_mates_leftovers(f, fw, bw, mr, f_paired, b_paired, acc);
 }
 
 // FilterRead::process_read, PE (src/filter.cpp:124-241), by one warp
@@ -156,6 +200,6 @@ __global__ void __launch_bounds__(128) k_process_pe_warp(const __grid_constant__
         state[i] = r;
         out[i] = mr;
     }
-    // lanes repeat the uniform parts (leftovers); the DP counters keep lane 0's view of those plus every lane's candidates
+    // every lane did its own candidates and leftover chains
     stats_flush(f.x.st, lane == 0 ? 1u : 0u, ctr);
 }

@@ -150,6 +150,9 @@ int cm_gpu_last_stage_ms(cm_gpu_ctx *ctx, float out[5]);
  * (the same DPs along transcripts, src/extend.cpp:37-920); with cm_counters.xdrop_cells + edit_cells
  * this gives the GCUPS of the alignment stage. */
 int cm_gpu_last_align_ms(cm_gpu_ctx *ctx, float out[2]);
+/* INT32 roofline denominator measured on this device: lane-operations per second of an add + max chain kernel
+ * ("calibrate with an IADD3/IMNMX micro-benchmark on the box and use the lower of the two"). */
+int cm_gpu_int32_peak(cm_gpu_ctx *ctx, double *lane_ops_per_s);
 
 /* ---- index / genome --------------------------------------------------- */
 /* Upload one packed contig straight from the reference's in-memory index right

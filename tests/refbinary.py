@@ -93,3 +93,105 @@ def assert_rows_equal(got, want, rows, what, with_contig=False):
     for f in COORD_FIELDS + (["contig_num"] if with_contig else []):
         bad = mp[got[f][mp] != want[f][mp]]
         assert len(bad) == 0, f"{what}: field {f}: {len(bad)} differ, first {bad[:5]}: {got[f][bad[:5]]} vs {want[f][bad[:5]]}"
+
+
+def parse_index(path):
+    """The reference's on-disk index (src/mrsfast/HashTable.c:106-254) -> (header dict, [contig dict]).  The six-byte table of a
+    full index is returned canonical: the bytes the reference never initialises and never reads (the checksum field of every
+    bucket's header slot and the slots behind a bucket's last entry; its table is malloc'ed, HashTable.c:346) are zeroed."""
+    import struct
+    b = np.fromfile(path, np.uint8)
+    raw = b.tobytes() if len(b) < (1 << 28) else None
+    mv = memoryview(b)
+
+    def unpack(fmt, o):
+        return struct.unpack_from(fmt, mv, o)
+    magic, win, csl = int(b[0]), int(b[1]), int(b[2])
+    maxmem, iobuf, cms = unpack("<III", 3)
+    o = 15
+    nchr, = unpack("<i", o)
+    o += 4
+    chrs = []
+    for _ in range(nchr):
+        nl, = unpack("<i", o)
+        o += 4
+        name = bytes(mv[o:o + nl]).decode()
+        o += nl
+        gl, = unpack("<i", o)
+        o += 4
+        chrs.append((name, gl))
+    hdr = dict(magic=magic, window=win, checksum_len=csl, max_mem=maxmem, io_buffer=iobuf, contig_max_size=cms, chrs=chrs)
+    contigs = []
+    while o < len(b):
+        more = int(b[o])
+        o += 1
+        nl, = unpack("<h", o)
+        o += 2
+        name = bytes(mv[o:o + nl]).decode()
+        o += nl
+        off, ln = unpack("<iI", o)
+        o += 8
+        nw = ln // 21 + (1 if ln % 21 else 0)
+        cref = b[o:o + 8 * nw].view(np.uint64).copy()
+        o += 8 * nw
+        nne, = unpack("<I", o)
+        o += 4
+        blocks = []
+        seen = 0
+        while seen < nne:
+            nb, = unpack("<i", o)
+            o += 4
+            blk = b[o:o + nb]
+            o += nb
+            blocks.append(blk.copy())
+            seen += int((blk >> 7).sum()) // 2
+        c = dict(more=more, name=name, offset=off, len=ln, cref=cref, n_nonempty=nne, blocks=blocks)
+        if magic == 3:
+            mem, = unpack("<I", o)
+            o += 4
+            tab = b[o:o + 6 * mem].reshape(mem, 6)
+            o += 6 * mem
+            cks = tab[:, 0].astype(np.uint16) | (tab[:, 1].astype(np.uint16) << 8)
+            info = np.ascontiguousarray(tab[:, 2:]).view(np.uint32)[:, 0].copy()
+            # decode the counts -> slot offsets of every non-empty bucket
+            allb = np.concatenate(blocks)
+            ends = np.nonzero(allb >> 7)[0]
+            starts = np.concatenate([[0], ends[:-1] + 1])
+            vals = np.zeros(len(ends), np.uint64)
+            for k in range(5):   # a 32-bit value takes at most 5 bytes
+                idx = starts + k
+                ok = idx <= ends
+                vals[ok] |= (allb[idx[ok]].astype(np.uint64) & 127) << np.uint64(7 * k)
+            cnt = vals[1::2].astype(np.int64)
+            slot0 = np.concatenate([[0], np.cumsum(cnt + 1)[:-1]])
+            assert int((cnt + 1).sum()) == mem
+            n_used = info[slot0].astype(np.int64)
+            assert (n_used <= cnt).all()
+            keep = np.zeros(mem + 1, np.int64)
+            np.add.at(keep, slot0 + 1, 1)
+            np.add.at(keep, slot0 + 1 + n_used, -1)
+            used = np.cumsum(keep[:mem]) > 0      # entry slots
+            head = np.zeros(mem, bool)
+            head[slot0] = True
+            cks = np.where(used, cks, 0).astype(np.uint16)
+            info = np.where(used | head, info, 0).astype(np.uint32)
+            c.update(mem=mem, cks=cks, info=info, bucket_windows=cnt)
+        contigs.append(c)
+    return hdr, contigs
+
+
+def assert_same_index(mine, ref):
+    h1, c1 = parse_index(mine)
+    h2, c2 = parse_index(ref)
+    assert h1 == h2, (h1, h2)
+    assert len(c1) == len(c2)
+    for a, b in zip(c1, c2):
+        for k in ("more", "name", "offset", "len", "n_nonempty"):
+            assert a[k] == b[k], (k, a[k], b[k])
+        assert (a["cref"] == b["cref"]).all(), "packed text differs"
+        assert len(a["blocks"]) == len(b["blocks"]) and all((x.shape == y.shape) and (x == y).all() for x, y in zip(a["blocks"], b["blocks"])), \
+            "bucket-count blocks differ"
+        if "mem" in b:
+            assert a["mem"] == b["mem"]
+            assert (a["info"] == b["info"]).all(), "table positions / bucket sizes differ"
+            assert (a["cks"] == b["cks"]).all(), "table checksums differ"

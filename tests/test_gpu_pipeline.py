@@ -76,10 +76,11 @@ def test_warp_chaining_is_exact(w_t0, monkeypatch, heavy_th):
     m.close()
 
 
-@pytest.mark.parametrize("th", ["0", "2"])
+@pytest.mark.parametrize("th", ["0", "2", "4294967295"])
 def test_warp_pair_kernel_is_exact(w_t0, monkeypatch, th):
-    """CM_GPU_HEAVY_PAIR_TH=0 sends every pair with a candidate chain pair through the warp-per-pair kernel
-    (speculative evaluation of a row's MatePairs, in-order commit); results must equal the goldens, scan-lev 0 and 2."""
+    """CM_GPU_HEAVY_PAIR_TH=0 sends every pair with chains through the warp-per-pair kernel (speculative evaluation of a
+    row's MatePairs with in-order commit, unpaired chains one per lane), 4294967295 sends every pair -- the heavy ones
+    too -- through the thread-per-pair kernel; results must equal the goldens, scan-lev 0 and 2."""
     from circminer_b200.api import fresh_mreads
     monkeypatch.setenv("CM_GPU_HEAVY_PAIR_TH", th)
     for name, kw in (("T0_k20.npz", {}), ("T0_k22_scan2.npz", dict(kmer=22, scan_level=2))):

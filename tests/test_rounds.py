@@ -90,11 +90,13 @@ def test_rounds_hostsim_vs_reference_binary(t1_rounds, scan):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("scan", [0, 1, 2])
-def test_rounds_gpu_vs_reference_binary(t1_rounds, scan):
+@pytest.mark.parametrize("scan,chunk", [(0, None), (1, None), (2, None), (0, "2048")])
+def test_rounds_gpu_vs_reference_binary(t1_rounds, scan, chunk, monkeypatch):
     from circminer_b200 import workload
     from circminer_b200.api import Mapper, default_params, fresh_mreads
     w, outs = t1_rounds
+    if chunk:   # several pipeline passes per round (the arenas are sized by the chunk)
+        monkeypatch.setenv("CM_GPU_CHUNK", chunk)
     m = Mapper(default_params(scan_level=scan))
     workload.load_into(m, w)
     n = len(w["s1"])
