@@ -522,7 +522,7 @@ CM_HDN void cm_xdrop(const uint8_t *s, int n, const uint8_t *t, int m, bool rev,
         return;
     }
 #endif
-    if (p.band_width == 3 && !(CM_DBG_FLAGS & 1)) cm_xdrop_reg<3>(s, n, t, m, rev, p, on_s, on_t, score, st);
+    if (p.band_width == 3) cm_xdrop_reg<3>(s, n, t, m, rev, p, on_s, on_t, score, st);
     else cm_xdrop_generic(s, n, t, m, rev, p, on_s, on_t, score, st);
 }
 
@@ -537,7 +537,7 @@ struct DropHint {
 // DropAlignment::local_alignment_right_sc (rev = false) / _left_sc (rev = true: both strings reversed)
 CM_HDN int cm_drop_alignment_sc(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &sc_len,
                                 int &indel, int &score, AlignStats *st, const DropHint *h = nullptr) {
-    if (h && !(CM_DBG_FLAGS & 2) && h->valid && h->s == s && h->t == t && h->n == n && h->m == m && h->rev == (int) rev) {
+    if (h && h->valid && h->s == s && h->t == t && h->n == n && h->m == m && h->rev == (int) rev) {
         sc_len = h->sclen;
         indel = h->indel;
         score = h->score;

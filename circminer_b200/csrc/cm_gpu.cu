@@ -34,6 +34,7 @@ struct ContigHost {
     AnnotDev a{};
     std::vector<void *> owned;        // device allocations of this contig
     std::vector<void *> owned_annot;
+    uint32_t n_big = 0;               // buckets with a coarse checksum table
 };
 
 struct cm_gpu_ctx {
@@ -45,6 +46,7 @@ struct cm_gpu_ctx {
     std::string err;
     std::vector<ContigHost> contigs;
     cm_gpu_ctx *parent = nullptr;     // cm_gpu_create_shared: index and annotation live in (and are owned by) the parent
+    std::atomic<int> n_children{0};   // shared contexts alive on this root: resident contigs cannot be replaced meanwhile
     cudaStream_t stream2 = nullptr;   // side stream: kernels that run beside the main one (heavy strands)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cm_counters *d_counters = nullptr;
@@ -104,7 +106,7 @@ struct cm_gpu_ctx {
     uint32_t rounds_n = 0;                     // pairs of the batch the final arrays describe
 };
 
-static std::string g_create_err;
+static thread_local std::string g_create_err;   // last cm_gpu_create failure of the calling thread
 
 static int fail(cm_gpu_ctx *ctx, int code, const char *fmt, ...) {
     char buf[512];
@@ -181,7 +183,23 @@ extern "C" const char *cm_gpu_last_error(const cm_gpu_ctx *ctx) { return ctx ? c
 
 __global__ void k_init_prep_lut();   // tables of the read staging kernel, below
 
-extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **out) {
+static void destroy_ctx_resources(cm_gpu_ctx *ctx) {
+    if (ctx->d_counters) cudaFree(ctx->d_counters);
+    for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    for (auto &ev : ctx->ev_r) if (ev) cudaEventDestroy(ev);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    ctx->d_counters = nullptr;
+    ctx->stream = ctx->stream2 = nullptr;
+}
+
+static int create_ctx(int device, const cm_params *params, cm_gpu_ctx **out, cm_gpu_ctx *shared_of);
+
+extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **out) { return create_ctx(device, params, out, nullptr); }
+
+static int create_ctx(int device, const cm_params *params, cm_gpu_ctx **out, cm_gpu_ctx *shared_of) {
     if (!params || !out) return fail(nullptr, CM_ERR_ARG, "null argument");
     *out = nullptr;
     const cm_params &p = *params;
@@ -203,27 +221,29 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
     ctx->p = p;
     ctx->max_seg_cnt = cm_max_seg_cnt(p);
     ctx->n_slots = (ctx->max_seg_cnt + 1) / 2;
-    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    if (cudaSetDevice(device) != cudaSuccess) {
         delete ctx;
         return fail(nullptr, CM_ERR_CUDA, "cannot initialise device %d", device);
     }
-    for (auto &ev : ctx->ev) cudaEventCreate(&ev);
-    for (auto &ev : ctx->ev_r) cudaEventCreate(&ev);
-    cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking);
-    k_init_prep_lut<<<1, 256, 0, ctx->stream>>>();
-    cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming);
-    {   // the index gathers are 32-byte random reads: ask L2 not to promote misses to 64/128-byte DRAM fetches
-        size_t g = 32;
-        if (const char *e = getenv("CM_GPU_L2_FETCH")) g = (size_t) atoi(e);
-        if (g) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, g);
+    bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking) == cudaSuccess;
+    for (auto &ev : ctx->ev) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
+    for (auto &ev : ctx->ev_r) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaMalloc(&ctx->d_counters, CM_CTR_SLOTS * sizeof(cm_counters)) == cudaSuccess;
+    if (ok && !shared_of) {   // staging tables: written once per root context (a shared context reads its parent's)
+        k_init_prep_lut<<<1, 256, 0, ctx->stream>>>();
+        ok = cudaGetLastError() == cudaSuccess;
     }
-    if (cudaMalloc(&ctx->d_counters, CM_CTR_SLOTS * sizeof(cm_counters)) != cudaSuccess) {
+    ok = ok && cudaMemsetAsync(ctx->d_counters, 0, CM_CTR_SLOTS * sizeof(cm_counters), ctx->stream) == cudaSuccess;
+    ok = ok && cudaStreamSynchronize(ctx->stream) == cudaSuccess;
+    if (!ok) {
+        const cudaError_t ce = cudaGetLastError();
+        destroy_ctx_resources(ctx);
         delete ctx;
-        return fail(nullptr, CM_ERR_ALLOC, "cudaMalloc counters");
+        return fail(nullptr, CM_ERR_CUDA, "cannot create the context's streams / events / counters on device %d (%s)", device, cudaGetErrorString(ce));
     }
-    cudaMemsetAsync(ctx->d_counters, 0, CM_CTR_SLOTS * sizeof(cm_counters), ctx->stream);
-    cudaStreamSynchronize(ctx->stream);
     if (const char *e = getenv("CM_GPU_REC_MULT")) ctx->rec_mult = (uint32_t) atoi(e);
     if (const char *e = getenv("CM_GPU_HEAVY_TH")) { int t = atoi(e); ctx->heavy_th = (uint32_t) (t < 0 ? 0 : (t > 254 ? 254 : t)); }
     if (const char *e = getenv("CM_GPU_PAIR_SIG")) ctx->pair_sig = atoi(e);
@@ -233,10 +253,6 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
     if (const char *e = getenv("CM_GPU_NO_SPEC")) ctx->no_spec = atoi(e) != 0;
     if (const char *e = getenv("CM_GPU_SYNC_EACH")) ctx->sync_each = atoi(e) != 0;
     if (const char *e = getenv("CM_GPU_CHUNK")) { long c = atol(e); ctx->chunk_pairs = (uint32_t) (c < 1024 ? 1024 : c); }
-    if (const char *e = getenv("CM_GPU_DBG")) {
-        int f = atoi(e);
-        cudaMemcpyToSymbol(g_cm_dbg_flags, &f, sizeof f);
-    }
     *out = ctx;
     return CM_OK;
 }
@@ -247,9 +263,10 @@ extern "C" int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **o
 extern "C" int cm_gpu_create_shared(cm_gpu_ctx *parent, cm_gpu_ctx **out) {
     if (!parent || !out) return CM_ERR_ARG;
     if (parent->parent) return fail(parent, CM_ERR_ARG, "the parent of a shared context must be a root context");
-    int r = cm_gpu_create(parent->device, &parent->p, out);
+    int r = create_ctx(parent->device, &parent->p, out, parent);
     if (r != CM_OK) return r;
     (*out)->parent = parent;
+    parent->n_children++;
     return CM_OK;
 }
 
@@ -257,6 +274,21 @@ static void free_contig(ContigHost &c) {
     for (void *p : c.owned) cudaFree(p);
     for (void *p : c.owned_annot) cudaFree(p);
     c = ContigHost();
+}
+// the index loaders replace the index only: an annotation uploaded before (or kept across a reload) stays
+static void free_index(ContigHost &c) {
+    for (void *p : c.owned) cudaFree(p);
+    c.owned.clear();
+    c.d = ContigDev();
+    c.loaded = false;
+    c.n_big = 0;
+}
+// a contig that shared contexts may be reading cannot be replaced under them
+static int check_reload(cm_gpu_ctx *ctx, ContigHost *ch, int contig_id) {
+    if ((ch->loaded || ch->has_annot) && ctx->n_children.load() > 0)
+        return fail(ctx, CM_ERR_STATE, "contig %d is resident and %d shared context(s) may be using it: destroy them before reloading", contig_id,
+                    ctx->n_children.load());
+    return CM_OK;
 }
 
 extern "C" int cm_gpu_destroy(cm_gpu_ctx *ctx) {
@@ -278,13 +310,8 @@ extern "C" int cm_gpu_destroy(cm_gpu_ctx *ctx) {
     DevBuf *rbufs[] = {&ctx->fin_mread, &ctx->fin_state, &ctx->fin_round, &ctx->surv_flag, &ctx->surv_idx, &ctx->surv_n, &ctx->snap_mread, &ctx->snap_state,
                        &ctx->round_out, &ctx->round_state};
     for (DevBuf *b : rbufs) release(*b);
-    cudaFree(ctx->d_counters);
-    for (auto &ev : ctx->ev) cudaEventDestroy(ev);
-    for (auto &ev : ctx->ev_r) cudaEventDestroy(ev);
-    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
-    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
-    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
-    cudaStreamDestroy(ctx->stream);
+    if (ctx->parent) ctx->parent->n_children--;
+    destroy_ctx_resources(ctx);
     delete ctx;
     return CM_OK;
 }
@@ -416,7 +443,8 @@ extern "C" int cm_gpu_load_contig(cm_gpu_ctx *ctx, int contig_id, const void *co
     cudaSetDevice(ctx->device);
     ContigHost *ch = get_contig(ctx, contig_id, true);
     if (!ch) return fail(ctx, CM_ERR_ARG, ctx->parent ? "contig %d: a shared context cannot load (load into its parent)" : "bad contig id %d", contig_id);
-    free_contig(*ch);
+    { int rr = check_reload(ctx, ch, contig_id); if (rr != CM_OK) return rr; }
+    free_index(*ch);
     const GeneralIndexPacked *mem = (const GeneralIndexPacked *) table_mem;
     // directory + SoA split on the host (setHashTablePointers order, HashTable.c:1074), by all host threads: the
     // 2 GiB pointer table is cut into slices, every slice counts its entries, a prefix over the slices gives each
@@ -621,7 +649,8 @@ extern "C" int cm_gpu_build_contig(cm_gpu_ctx *ctx, int contig_id, const char *c
     cudaSetDevice(ctx->device);
     ContigHost *ch = get_contig(ctx, contig_id, true);
     if (!ch) return fail(ctx, CM_ERR_ARG, ctx->parent ? "contig %d: a shared context cannot load (load into its parent)" : "bad contig id %d", contig_id);
-    free_contig(*ch);
+    { int rr = check_reload(ctx, ch, contig_id); if (rr != CM_OK) return rr; }
+    free_index(*ch);
     cudaStream_t st = ctx->stream;
     int r;
     const uint32_t len = ref_gen_len;
@@ -650,7 +679,8 @@ extern "C" int cm_gpu_build_contig_packed(cm_gpu_ctx *ctx, int contig_id, const 
     cudaSetDevice(ctx->device);
     ContigHost *ch = get_contig(ctx, contig_id, true);
     if (!ch) return fail(ctx, CM_ERR_ARG, ctx->parent ? "contig %d: a shared context cannot load (load into its parent)" : "bad contig id %d", contig_id);
-    free_contig(*ch);
+    { int rr = check_reload(ctx, ch, contig_id); if (rr != CM_OK) return rr; }
+    free_index(*ch);
     cudaStream_t st = ctx->stream;
     int r;
     const uint32_t len = ref_gen_len;
@@ -707,6 +737,7 @@ extern "C" int cm_gpu_load_annotation(cm_gpu_ctx *ctx, int contig_id, const cm_a
     cudaSetDevice(ctx->device);
     ContigHost *ch = get_contig(ctx, contig_id, true);
     if (!ch) return fail(ctx, CM_ERR_ARG, ctx->parent ? "contig %d: a shared context cannot load (load into its parent)" : "bad contig id %d", contig_id);
+    { int rr = check_reload(ctx, ch, contig_id); if (rr != CM_OK && ch->has_annot) return rr; }
     for (void *p : ch->owned_annot) cudaFree(p);
     ch->owned_annot.clear();
     ch->has_annot = false;
@@ -752,8 +783,9 @@ extern "C" int cm_gpu_load_annotation(cm_gpu_ctx *ctx, int contig_id, const cm_a
     return CM_OK;
 }
 
-// fused directory: one thread per bucket
-__global__ void k_build_dirx(const uint32_t *__restrict__ dir, const uint16_t *__restrict__ cks, DirX *__restrict__ dirx) {
+// fused directory: one thread per bucket; large buckets take a row of the coarse table (numbered by an atomic counter)
+__global__ void k_build_dirx(const uint32_t *__restrict__ dir, const uint16_t *__restrict__ cks, DirX *__restrict__ dirx, uint32_t big_th,
+                             uint32_t *__restrict__ n_big, uint32_t *__restrict__ big_hv, uint32_t big_cap) {
     uint32_t hv = blockIdx.x * blockDim.x + threadIdx.x;
     if (hv >= CM_NBUCKETS) return;
     uint32_t lo = dir[hv], hi = dir[hv + 1];
@@ -761,18 +793,92 @@ __global__ void k_build_dirx(const uint32_t *__restrict__ dir, const uint16_t *_
     e.off = lo;
     e.cnt = hi - lo;
     for (uint32_t k = 0; k < CM_DIRX_INLINE; k++) e.c[k] = lo + k < hi ? cks[lo + k] : (uint16_t) 0xFFFFu;
-    dirx[hv] = e;
+    if (big_hv && e.cnt >= big_th) {
+        const uint32_t id = atomicAdd(n_big, 1u);
+        if (id < big_cap) big_hv[id] = hv;
+        e.c[0] = (uint16_t) (id & 0xFFFFu);
+        e.c[1] = (uint16_t) (id >> 16);
+    }
+    uint4 *dst = reinterpret_cast<uint4 *>(dirx + hv);
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(&e);
+    dst[0] = make_uint4(src[0], src[1], src[2], src[3]);
+    dst[1] = make_uint4(src[4], src[5], src[6], src[7]);
+}
+// number of buckets of >= big_th entries
+__global__ void k_count_big(const uint32_t *__restrict__ dir, uint32_t big_th, uint32_t *__restrict__ n_big) {
+    uint32_t hv = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool big = hv < CM_NBUCKETS && dir[hv + 1] - dir[hv] >= big_th;
+    const unsigned m = __ballot_sync(0xffffffffu, big);
+    if (m && (threadIdx.x & 31u) == 0) atomicAdd(n_big, (uint32_t) __popc(m));
+}
+// coarse table of one large bucket per warp: row[t] = first entry with (cks >> shift) >= t, row[2^bits] = cnt
+__global__ void k_build_big_tab(const uint32_t *__restrict__ dir, const uint16_t *__restrict__ cks, const uint32_t *__restrict__ big_hv,
+                                uint32_t n_big, int bits, int shift, uint32_t *__restrict__ tab) {
+    const uint32_t wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (wid >= n_big) return;
+    const uint32_t hv = big_hv[wid], lo = dir[hv], cnt = dir[hv + 1] - lo;
+    const uint32_t nt = 1u << bits;
+    uint32_t *row = tab + (size_t) wid * (nt + 1);
+    for (uint32_t t = lane; t <= nt; t += 32) {
+        uint32_t a = 0, b = cnt;
+        if (t == nt) a = cnt;
+        else
+            while (a < b) {
+                const uint32_t mid = (a + b) >> 1;
+                if ((uint32_t) (cks[lo + mid] >> shift) < t) a = mid + 1; else b = mid;
+            }
+        row[t] = a;
+    }
 }
 static int build_dirx(cm_gpu_ctx *ctx, ContigHost *ch) {
-    if (getenv("CM_GPU_NO_DIRX")) { ch->d.dirx = nullptr; return CM_OK; }
+    ch->d.dirx = nullptr;
+    ch->d.big_tab = nullptr;
+    ch->d.big_th = 0xFFFFFFFFu;
+    ch->d.big_bits = 0;
+    ch->d.big_shift = 0;
+    if (getenv("CM_GPU_NO_DIRX")) return CM_OK;
+    cudaStream_t st = ctx->stream;
     DirX *dx = nullptr;
     int r = dev_alloc(ctx, ch->owned, &dx, (size_t) CM_NBUCKETS);
     if (r != CM_OK) return r;
-    k_build_dirx<<<grid_for(CM_NBUCKETS, 256), 256, 0, ctx->stream>>>(ch->d.dir, ch->d.cks, dx);
+    const int cs_bits = 2 * (ctx->p.kmer - CM_WINDOW);
+    uint32_t big_th = CM_BIG_TH_DEFAULT;
+    if (const char *e = getenv("CM_GPU_BIG_TH")) { long v = atol(e); big_th = v <= CM_DIRX_INLINE ? CM_DIRX_INLINE + 1 : (uint32_t) v; }
+    uint32_t n_big = 0, *d_nbig = nullptr, *big_hv = nullptr, *tab = nullptr;
+    std::vector<void *> tmp;
+    if (cs_bits > 0) {   // with no checksum (k = 14) every entry of a bucket matches: nothing to search
+        if ((r = dev_alloc(ctx, tmp, &d_nbig, 2)) != CM_OK) return r;
+        CUDA_TRY(ctx, cudaMemsetAsync(d_nbig, 0, 8, st));
+        k_count_big<<<grid_for(CM_NBUCKETS, 256), 256, 0, st>>>(ch->d.dir, big_th, d_nbig);
+        CUDA_TRY(ctx, cudaMemcpyAsync(&n_big, d_nbig, 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        ctx->launches++;
+    }
+    const int bits = cs_bits < 10 ? cs_bits : 10;
+    if (n_big) {
+        if ((r = dev_alloc(ctx, tmp, &big_hv, (size_t) n_big)) != CM_OK || (r = dev_alloc(ctx, ch->owned, &tab, (size_t) n_big * ((1u << bits) + 1))) != CM_OK) {
+            for (void *p : tmp) cudaFree(p);
+            return r;
+        }
+        CUDA_TRY(ctx, cudaMemsetAsync(d_nbig, 0, 4, st));
+    }
+    k_build_dirx<<<grid_for(CM_NBUCKETS, 256), 256, 0, st>>>(ch->d.dir, ch->d.cks, dx, big_th, d_nbig, n_big ? big_hv : nullptr, n_big);
     ctx->launches++;
+    if (n_big) {
+        k_build_big_tab<<<grid_for((size_t) n_big * 32, 256), 256, 0, st>>>(ch->d.dir, ch->d.cks, big_hv, n_big, bits, cs_bits - bits, tab);
+        ctx->launches++;
+    }
     CUDA_TRY(ctx, cudaGetLastError());
-    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    for (void *p : tmp) cudaFree(p);
     ch->d.dirx = dx;
+    if (n_big) {
+        ch->d.big_tab = tab;
+        ch->d.big_th = big_th;
+        ch->d.big_bits = bits;
+        ch->d.big_shift = cs_bits - bits;
+    }
+    ch->n_big = n_big;
     return CM_OK;
 }
 

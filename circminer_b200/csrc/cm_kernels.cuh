@@ -55,7 +55,6 @@ __global__ void __launch_bounds__(128, CM_CHAIN_MINB) k_chain(const __grid_const
         int T = cm_chain_rows(v, so, sc, row_pos_off, row_cnt, row_off, cells, hh);
         b.chain_hh[s] = hh;
         b.chain_cnt[s] = 0;
-        if ((CM_DBG_FLAGS & 16) && cells > 64) T = 0;   // timing probe: light strands only (results invalid)
         if (T > 0) {
             uint64_t base = cell_off[s];
             uint32_t cap = cm_rec_cap(cells, rec_mult);
@@ -135,7 +134,6 @@ __global__ void __launch_bounds__(128) k_chain_big(const __grid_constant__ DevVi
 // adds its non-zero counts into one of CM_CTR_SLOTS copies of cm_counters (summed by cm_gpu_get_counters),
 // chosen by warp, so same-address atomics stay rare.
 __device__ __forceinline__ void stats_flush(const AlignStats &st, uint32_t units, cm_counters *ctr) {
-    if (CM_DBG_FLAGS & 4) return;
     cm_counters *c = ctr + ((blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) & (CM_CTR_SLOTS - 1));
     if (st.xdrop_cells) atomicAdd((unsigned long long *) &c->xdrop_cells, (unsigned long long) st.xdrop_cells);
     if (st.edit_cells) atomicAdd((unsigned long long *) &c->edit_cells, (unsigned long long) st.edit_cells);
@@ -153,8 +151,6 @@ __global__ void __launch_bounds__(CM_PE_BLOCK, CM_PE_MINB) k_process_pe(const __
     if (live) {
         const uint32_t i = order[slot];   // pairs with the same control-flow signature sit in the same warp
         cm_mread mr = in[i];
-        if ((CM_DBG_FLAGS & 32) && (b.chain_cnt[4 * i] + b.chain_cnt[4 * i + 1] + b.chain_cnt[4 * i + 2] + b.chain_cnt[4 * i + 3] > 4)) state[i] = 0;   // timing probe
-        else
         state[i] = cm_pair_process(v, b, i, mr, st);
         out[i] = mr;
     }
@@ -271,7 +267,11 @@ __global__ void k_pair_key(const __grid_constant__ DevView v, const __grid_const
             uint32_t s = 4 * i + (q ? sb : sa);
             for (int e = 0; e < 2; e++) {
                 unsigned nn = 0;
-                if (b.chain_cnt[s] > 0 && b.spec && b.chain_base && b.spec_k > 0) nn = b.spec[2 * (size_t) b.chain_base[s] + e].n;
+                // EndSpec::n is written only for ends that had something to align (ChainAux::has_l / has_r)
+                if (b.chain_cnt[s] > 0 && b.spec && b.aux && b.chain_base && b.spec_k > 0) {
+                    const ChainAux &ax = b.aux[b.chain_base[s]];
+                    if (e ? ax.has_r : ax.has_l) nn = b.spec[2 * (size_t) b.chain_base[s] + e].n;
+                }
                 if (sig_mode == 1) nn = nn ? 1u : 0u;
                 w = (w << 2) | (nn > 3u ? 3u : nn);
             }

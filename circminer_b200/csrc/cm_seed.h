@@ -83,58 +83,81 @@ CM_HD SeedHit cm_seed_lookup(const ContigDev &c, int hv, int cv, uint32_t *secto
 }
 
 // The same look-up through the fused directory (ContigDev::dirx).  Equal range of `target` in the sorted bucket:
-// positions < 4 are answered from the inline checksums, the rest by bisection of cks[off + 4, off + cnt).
+// positions < 12 are answered from the inline checksums, the rest by bisection of cks[off + 12, off + cnt); a large
+// bucket goes through its coarse checksum table first.
 CM_HD SeedHit cm_seed_lookup_x(const ContigDev &c, int hv, int cv, uint32_t *sectors) {
     SeedHit h;
     h.off = 0;
     h.cnt = 0;
     if (sectors) *sectors = 0;
     if (hv < 0 || cv < 0) return h;
+    uint32_t w[8];
 #if defined(__CUDA_ARCH__)
-    const uint4 *dp = reinterpret_cast<const uint4 *>(c.dirx) + hv;
-    uint4 raw;
-    switch ((CM_DBG_FLAGS >> 8) & 7) {   // load-path A/B (CM_GPU_DBG = 256 * variant); measured equal in DRAM bytes, 0 is 4 % faster
-        default: asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(raw.x), "=r"(raw.y), "=r"(raw.z), "=r"(raw.w) : "l"(dp)); break;
-        case 1: raw = *dp; break;
-        case 2: raw = __ldcg(dp); break;
-        case 3: raw = __ldg(dp); break;
-    }
-    const uint32_t off = raw.x, cnt = raw.y;
-    const uint16_t c0 = (uint16_t) (raw.z & 0xFFFFu), c1 = (uint16_t) (raw.z >> 16), c2 = (uint16_t) (raw.w & 0xFFFFu), c3 = (uint16_t) (raw.w >> 16);
+    const uint4 *dp = reinterpret_cast<const uint4 *>(c.dirx) + 2 * (size_t) hv;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(dp));
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "l"(dp + 1));
 #else
-    const DirX e = c.dirx[hv];
-    const uint32_t off = e.off, cnt = e.cnt;
-    const uint16_t c0 = e.c[0], c1 = e.c[1], c2 = e.c[2], c3 = e.c[3];
+    {
+        const DirX &e = c.dirx[hv];
+        w[0] = e.off; w[1] = e.cnt;
+        for (int k = 0; k < 6; k++) w[2 + k] = (uint32_t) e.c[2 * k] | ((uint32_t) e.c[2 * k + 1] << 16);
+    }
 #endif
+    const uint32_t off = w[0], cnt = w[1];
     if (sectors) *sectors = 1;                 // directory sector
     if (cnt == 0) return h;                    // getCandidates == NULL
     if (sectors) *sectors = 2;                 // bucket head
     if (cv >= 32768) return h;                 // `int16_t target = cv` (match_read.cpp:77)
-    const uint16_t target = (uint16_t) cv;
-    const uint32_t ni = cnt < CM_DIRX_INLINE ? cnt : CM_DIRX_INLINE;
-    // inline part: entries 0..ni-1 (unused slots are never counted)
-    const uint32_t lt = (uint32_t) (c0 < target) + (uint32_t) (ni > 1 && c1 < target) + (uint32_t) (ni > 2 && c2 < target) +
-                        (uint32_t) (ni > 3 && c3 < target);
-    const uint32_t le = (uint32_t) (c0 <= target) + (uint32_t) (ni > 1 && c1 <= target) + (uint32_t) (ni > 2 && c2 <= target) +
-                        (uint32_t) (ni > 3 && c3 <= target);
-    uint32_t LB = lt, UB = le;                 // lower / upper bound as indices into the bucket
-    if (cnt > CM_DIRX_INLINE && le == CM_DIRX_INLINE) {
-        // the range may continue (or start) past the inline entries
-        const uint32_t lo0 = off + CM_DIRX_INLINE, hi0 = off + cnt;
-        uint32_t a = lo0, b = hi0;
-        if (lt == CM_DIRX_INLINE) {            // all four inline entries are smaller: lower bound is in memory too
-            while (a < b) {
-                uint32_t mid = (a + b) >> 1;
-                if (c.cks[mid] < target) a = mid + 1; else b = mid;
-            }
-            LB = a - off;
-            b = hi0;
+    const uint32_t target = (uint32_t) cv;
+    uint32_t LB, UB;                           // lower / upper bound as indices into the bucket
+    if (cnt >= c.big_th && c.big_tab) {
+        // large bucket: w[2] = its row of the coarse table; the equal range lies inside one table cell
+        const uint32_t *row = c.big_tab + (size_t) w[2] * ((1u << c.big_bits) + 1u);
+        const uint32_t t = target >> c.big_shift;
+        uint32_t a = off + row[t], b = off + row[t + 1];
+        const uint32_t hi0 = b;
+        while (a < b) {
+            uint32_t mid = (a + b) >> 1;
+            if (c.cks[mid] < target) a = mid + 1; else b = mid;
         }
+        LB = a - off;
+        b = hi0;
         while (a < b) {
             uint32_t mid = (a + b) >> 1;
             if (c.cks[mid] <= target) a = mid + 1; else b = mid;
         }
         UB = a - off;
+    } else {
+        const uint32_t ni = cnt < CM_DIRX_INLINE ? cnt : CM_DIRX_INLINE;
+        uint32_t lt = 0, le = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (uint32_t k = 0; k < CM_DIRX_INLINE; k++) {   // unused slots are never counted
+            const uint32_t ck = (w[2 + (k >> 1)] >> (16 * (k & 1))) & 0xFFFFu;
+            lt += (uint32_t) (k < ni && ck < target);
+            le += (uint32_t) (k < ni && ck <= target);
+        }
+        LB = lt;
+        UB = le;
+        if (cnt > CM_DIRX_INLINE && le == CM_DIRX_INLINE) {
+            // the range may continue (or start) past the inline entries
+            const uint32_t lo0 = off + CM_DIRX_INLINE, hi0 = off + cnt;
+            uint32_t a = lo0, b = hi0;
+            if (lt == CM_DIRX_INLINE) {        // every inline entry is smaller: the lower bound is in memory too
+                while (a < b) {
+                    uint32_t mid = (a + b) >> 1;
+                    if (c.cks[mid] < target) a = mid + 1; else b = mid;
+                }
+                LB = a - off;
+                b = hi0;
+            }
+            while (a < b) {
+                uint32_t mid = (a + b) >> 1;
+                if (c.cks[mid] <= target) a = mid + 1; else b = mid;
+            }
+            UB = a - off;
+        }
     }
     if (UB <= LB) return h;
     h.off = off + LB;

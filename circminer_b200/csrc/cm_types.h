@@ -15,17 +15,6 @@
 #define CM_HDN
 #endif
 
-// debug switches (CM_GPU_DBG on the device build): bit 0 generic X-drop, bit 1 ignore hints, bit 2 no counters,
-// bits 4-5 timing probes, bits 8-10 load path of the fused directory
-#if defined(__CUDACC__)
-__device__ int g_cm_dbg_flags = 0;
-#endif
-#if defined(__CUDA_ARCH__)
-#define CM_DBG_FLAGS g_cm_dbg_flags
-#else
-#define CM_DBG_FLAGS 0
-#endif
-
 #define CM_WINDOW 14                       // WINDOW_SIZE, src/common.cpp:7
 #define CM_NBUCKETS (1u << (2 * CM_WINDOW))  // 4^14 directory entries
 #define CM_INF 1000000000                  // INF 1e9, src/common.h:34
@@ -37,19 +26,27 @@ __device__ int g_cm_dbg_flags = 0;
 #define CM_MAX_SEEDS 22                    // seeds per strand we support: ceil(300/14)
 #define CM_MAX_BAND 15                     // largest band_width the register DP supports
 
-// Fused directory entry: bucket offset and size plus the bucket's first four checksums in ONE 16-byte read, so
-// a look-up in a bucket of <= 4 entries (or whose key sorts before the 4th) never touches the checksum array:
-// one random DRAM access per seed instead of two dependent ones.
+// Fused directory entry, one 32-byte sector: bucket offset and size plus the bucket's first twelve checksums, so a
+// look-up in a bucket of <= 12 entries (or whose key sorts before the 12th) never touches the checksum array -- one
+// random DRAM access per seed instead of the reference's two dependent ones (directory -> bucket).  At GRCh38 occupancy
+// (4 entries per bucket on average, Poisson) that is 99.9 % of the non-repeat buckets.
+// A bucket of >= ContigDev::big_th entries (repeat families: up to 10^5 entries) keeps, instead of inline checksums, the
+// number of its row in ContigDev::big_tab: the first entry of every value of the checksum's top big_bits bits, which
+// narrows the bisection from 17 dependent DRAM probes to a run of cnt / 2^big_bits entries.
 struct DirX {
     uint32_t off, cnt;
-    uint16_t c[4];
+    uint16_t c[12];
 };
-#define CM_DIRX_INLINE 4
+#define CM_DIRX_INLINE 12
+#define CM_BIG_TH_DEFAULT 96
 
 // One packed contig resident in HBM.
 struct ContigDev {
     const uint32_t *dir;     // [4^14 + 1] exclusive prefix of bucket sizes
-    const DirX *dirx;        // [4^14] fused directory entry (device builds only; nullptr in tests/hostsim)
+    const DirX *dirx;        // [4^14] fused directory entry (nullptr: look-ups go through dir + cks)
+    const uint32_t *big_tab; // [n_big][2^big_bits + 1] coarse checksum index of the large buckets (bucket-relative)
+    uint32_t big_th;         // buckets with cnt >= big_th are "large"
+    int big_bits, big_shift; // table index of a checksum = cks >> big_shift
     const uint16_t *cks;     // [n_entries] checksum of each hit, sorted by (bucket, checksum, pos)
     const uint32_t *pos;     // [n_entries] 1-based contig position of the k-mer
     const uint8_t *genome;   // [ref_len + 2] ASCII, genome[p] = base at 1-based p; genome[0] unused

@@ -103,6 +103,79 @@ int hs_set_index(HsCtx *c, int contig_id, const uint32_t *dir, const uint16_t *c
     return 0;
 }
 
+// Host build of the fused directory + coarse tables of the large buckets (what build_dirx does on the device), then
+// cm_seed_lookup_x against the plain cm_seed_lookup on every stored (bucket, checksum) of a sample of entries, their
+// neighbours checksum +- 1, and random keys.  Returns the number of look-ups that differ (0 = the two are the same map).
+long hs_seed_x_check(HsCtx *c, int contig_id, uint32_t big_th, uint32_t n_probe, uint64_t seed) {
+    HsContig *h = c->contigs[contig_id];
+    const int cs_bits = 2 * (c->p.kmer - CM_WINDOW);
+    const int bits = cs_bits < 10 ? cs_bits : 10;
+    DirX *dx = (DirX *) calloc((size_t) CM_NBUCKETS, sizeof(DirX));   // untouched pages stay unmapped: only non-empty buckets are written
+    std::vector<uint32_t> tab;
+    uint32_t n_big = 0;
+    for (uint32_t hv = 0; hv < CM_NBUCKETS; hv++) {
+        const uint32_t lo = h->dir[hv], hi = h->dir[hv + 1];
+        if (hi == lo) continue;
+        DirX e;
+        e.off = lo;
+        e.cnt = hi - lo;
+        for (uint32_t k = 0; k < CM_DIRX_INLINE; k++) e.c[k] = lo + k < hi ? h->cks[lo + k] : (uint16_t) 0xFFFFu;
+        if (cs_bits > 0 && e.cnt >= big_th) {
+            const uint32_t id = n_big++, nt = 1u << bits;
+            e.c[0] = (uint16_t) (id & 0xFFFFu);
+            e.c[1] = (uint16_t) (id >> 16);
+            for (uint32_t t = 0; t <= nt; t++) {
+                uint32_t a = 0;
+                if (t == nt) a = e.cnt;
+                else while (a < e.cnt && (uint32_t) (h->cks[lo + a] >> (cs_bits - bits)) < t) a++;
+                tab.push_back(a);
+            }
+        }
+        dx[hv] = e;
+    }
+    ContigDev d = h->d;
+    d.dirx = dx;
+    d.big_tab = n_big ? tab.data() : nullptr;
+    d.big_th = n_big ? big_th : 0xFFFFFFFFu;
+    d.big_bits = bits;
+    d.big_shift = cs_bits - bits;
+    ContigDev plain = h->d;
+    plain.dirx = nullptr;
+    long bad = 0;
+    uint64_t x = seed * 0x9E3779B97F4A7C15ull + 1;
+    auto rnd = [&]() { x ^= x << 13; x ^= x >> 7; x ^= x << 17; return x; };
+    auto probe = [&](int hv, int cv) {
+        uint32_t s1, s2;
+        SeedHit a = cm_seed_lookup(plain, hv, cv, &s1), b = cm_seed_lookup_x(d, hv, cv, &s2);
+        if (a.cnt != b.cnt || (a.cnt && a.off != b.off) || s1 != s2) bad++;
+    };
+    const int cmax = cs_bits ? (1 << cs_bits) : 1;
+    // every large bucket in full, then samples
+    for (uint32_t hv = 0; hv < CM_NBUCKETS; hv++)
+        if (dx[hv].cnt >= big_th)
+            for (uint32_t j = 0; j < dx[hv].cnt; j++) {
+                const int cv = h->cks[dx[hv].off + j];
+                probe((int) hv, cv);
+                if (cv + 1 < cmax) probe((int) hv, cv + 1);
+                if (cv > 0) probe((int) hv, cv - 1);
+            }
+    for (uint32_t k = 0; k < n_probe && h->d.n_entries; k++) {
+        const uint64_t e = rnd() % h->d.n_entries;
+        // bucket of entry e
+        uint32_t a = 0, b = CM_NBUCKETS;
+        while (a < b) { uint32_t mid = (a + b) >> 1; if (h->dir[mid + 1] <= e) a = mid + 1; else b = mid; }
+        const int cv = h->cks[e];
+        probe((int) a, cv);
+        if (cv + 1 < cmax) probe((int) a, cv + 1);
+        if (cv > 0) probe((int) a, cv - 1);
+        probe((int) (rnd() % CM_NBUCKETS), (int) (rnd() % cmax));
+    }
+    probe(-1, 0);
+    probe(0, -1);
+    free(dx);
+    return bad + (n_big == 0 && big_th < 50 ? 1000000 : 0);   // a small threshold must produce large buckets on the test data
+}
+
 // the arrays of `A` must outlive the context (the Python wrapper keeps them)
 int hs_load_annotation(HsCtx *c, int contig_id, const cm_annot_flat *A) {
     HsContig *h = c->contigs[contig_id];

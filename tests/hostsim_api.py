@@ -70,6 +70,10 @@ class HostSim:
         self.lib.hs_set_index(self.ctx, contig_id, _vp(dirv), _vp(cks), _vp(np.ascontiguousarray(pos)), C.c_uint64(len(pos)),
                               _vp(g), C.c_uint32(len(g)))
 
+    def seed_x_check(self, contig_id, big_th=96, n_probe=200000, seed=1):
+        self.lib.hs_seed_x_check.restype = C.c_long
+        return self.lib.hs_seed_x_check(self.ctx, contig_id, C.c_uint32(big_th), C.c_uint32(n_probe), C.c_uint64(seed))
+
     def load_annotation(self, contig_id, a: dict):
         f = CmAnnotFlat()
         for k in ("n_iv", "n_seg", "n_tid", "n_trans", "n_genes", "n_chr", "n_bits"):

@@ -114,3 +114,16 @@ def test_product_package_never_imports_oracle():
         for f in fs:
             if f.endswith((".py", ".cu", ".cuh", ".h")) and f != "smoke.py":
                 assert not pat.search(open(os.path.join(dp, f)).read()), (dp, f)
+
+
+@pytest.mark.parametrize("kmer,big_th", [(20, 5), (22, 5), (14, 5)])
+def test_fused_directory_lookup_equals_plain_lookup(t0_packed, kmer, big_th):
+    """cm_seed_lookup_x (32-byte directory entry with 12 inline checksums + coarse checksum tables for large buckets) is the
+    same map as the plain directory -> bucket bisection of GenomeSeeder::get_exact_locs_hash (src/match_read.cpp:54-110)."""
+    from hostsim_api import HostSim
+    from circminer_b200.api import default_params
+    hs = HostSim(default_params(kmer=kmer))
+    for c, seq in enumerate(t0_packed["contigs"][:1]):
+        hs.build_contig(c, seq)
+        bad = hs.seed_x_check(c, big_th=big_th, n_probe=100000, seed=c + 1)
+        assert bad == 0 or (kmer == 14 and bad == 1000000), f"contig {c}: {bad} look-ups differ"
