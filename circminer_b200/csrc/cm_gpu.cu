@@ -801,8 +801,7 @@ __global__ void k_build_dirx(const uint32_t *__restrict__ dir, const uint16_t *_
     }
     uint4 *dst = reinterpret_cast<uint4 *>(dirx + hv);
     const uint32_t *src = reinterpret_cast<const uint32_t *>(&e);
-    dst[0] = make_uint4(src[0], src[1], src[2], src[3]);
-    dst[1] = make_uint4(src[4], src[5], src[6], src[7]);
+    for (unsigned q = 0; q < sizeof(DirX) / 16; q++) dst[q] = make_uint4(src[4 * q], src[4 * q + 1], src[4 * q + 2], src[4 * q + 3]);
 }
 // number of buckets of >= big_th entries
 __global__ void k_count_big(const uint32_t *__restrict__ dir, uint32_t big_th, uint32_t *__restrict__ n_big) {
@@ -1024,6 +1023,9 @@ static int launch_prep(cm_gpu_ctx *ctx, uint32_t in_stride) {
 __global__ void __launch_bounds__(256) k_seed(const __grid_constant__ DevView v, const int2 *__restrict__ seed_key, uint64_t total,
                                               uint32_t *__restrict__ seed_off, uint32_t *__restrict__ seed_cnt,
                                               cm_counters *__restrict__ ctr) {
+    __shared__ uint32_t sh[4];   // looked, sectors, hits, warps done
+    if (threadIdx.x < 4) sh[threadIdx.x] = 0;
+    __syncthreads();             // at the start every warp arrives at once
     uint64_t gid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t sectors = 0, hits = 0, looked = 0;
     if (gid < total) {
@@ -1041,24 +1043,28 @@ __global__ void __launch_bounds__(256) k_seed(const __grid_constant__ DevView v,
         seed_off[gid] = h.off;
         seed_cnt[gid] = h.cnt;
     }
-    // block-aggregated counters (roofline numerators): one thread per block adds into one
-    // of CM_CTR_SLOTS copies; per-warp same-address atomics were what bounded this kernel before.
-    __shared__ uint32_t sh[3][8];
+    // Work counters (roofline numerators), block-aggregated without a barrier behind the look-ups: every
+    // warp adds its sums to shared memory and the last warp to arrive adds the block's totals to one of CM_CTR_SLOTS
+    // copies.  A __syncthreads here made every warp of a block wait for the one with the longest chain of dependent probes
+    // (a third of the kernel's stall cycles in the ncu capture); per-warp global atomics on three addresses bounded it before.
     for (int o = 16; o; o >>= 1) {
         sectors += __shfl_down_sync(0xffffffffu, sectors, o);
         hits += __shfl_down_sync(0xffffffffu, hits, o);
         looked += __shfl_down_sync(0xffffffffu, looked, o);
     }
-    const uint32_t w = threadIdx.x >> 5;
-    if ((threadIdx.x & 31) == 0) { sh[0][w] = looked; sh[1][w] = sectors; sh[2][w] = hits; }
-    __syncthreads();
-    if (threadIdx.x < 3) {
-        unsigned long long t = 0;
-        for (uint32_t k = 0; k < (blockDim.x >> 5); k++) t += sh[threadIdx.x][k];
-        cm_counters *c = ctr + (blockIdx.x & (CM_CTR_SLOTS - 1));
-        unsigned long long *dst = threadIdx.x == 0 ? (unsigned long long *) &c->seeds
-                                  : threadIdx.x == 1 ? (unsigned long long *) &c->seed_sectors : (unsigned long long *) &c->seed_hits;
-        if (t) atomicAdd(dst, t);
+    if ((threadIdx.x & 31) == 0) {
+        if (looked) atomicAdd(&sh[0], looked);
+        if (sectors) atomicAdd(&sh[1], sectors);
+        if (hits) atomicAdd(&sh[2], hits);
+        __threadfence_block();
+        if (atomicAdd(&sh[3], 1u) == (blockDim.x >> 5) - 1) {
+            __threadfence_block();
+            cm_counters *c = ctr + (blockIdx.x & (CM_CTR_SLOTS - 1));
+            const uint32_t a = atomicAdd(&sh[0], 0u), b = atomicAdd(&sh[1], 0u), d = atomicAdd(&sh[2], 0u);
+            if (a) atomicAdd((unsigned long long *) &c->seeds, (unsigned long long) a);
+            if (b) atomicAdd((unsigned long long *) &c->seed_sectors, (unsigned long long) b);
+            if (d) atomicAdd((unsigned long long *) &c->seed_hits, (unsigned long long) d);
+        }
     }
 }
 

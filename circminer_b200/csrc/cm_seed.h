@@ -83,7 +83,7 @@ CM_HD SeedHit cm_seed_lookup(const ContigDev &c, int hv, int cv, uint32_t *secto
 }
 
 // The same look-up through the fused directory (ContigDev::dirx).  Equal range of `target` in the sorted bucket:
-// positions < 12 are answered from the inline checksums, the rest by bisection of cks[off + 12, off + cnt); a large
+// positions < CM_DIRX_INLINE are answered from the inline checksums, the rest by bisection of the bucket's tail; a large
 // bucket goes through its coarse checksum table first.
 CM_HD SeedHit cm_seed_lookup_x(const ContigDev &c, int hv, int cv, uint32_t *sectors) {
     SeedHit h;
@@ -91,16 +91,18 @@ CM_HD SeedHit cm_seed_lookup_x(const ContigDev &c, int hv, int cv, uint32_t *sec
     h.cnt = 0;
     if (sectors) *sectors = 0;
     if (hv < 0 || cv < 0) return h;
-    uint32_t w[8];
+    constexpr unsigned NW = sizeof(DirX) / 4;
+    uint32_t w[NW];
 #if defined(__CUDA_ARCH__)
-    const uint4 *dp = reinterpret_cast<const uint4 *>(c.dirx) + 2 * (size_t) hv;
+    const uint4 *dp = reinterpret_cast<const uint4 *>(c.dirx + hv);
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(dp));
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "l"(dp + 1));
+    if (NW == 8)
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[4 % NW]), "=r"(w[5 % NW]), "=r"(w[6 % NW]), "=r"(w[7 % NW]) : "l"(dp + 1));
 #else
     {
         const DirX &e = c.dirx[hv];
         w[0] = e.off; w[1] = e.cnt;
-        for (int k = 0; k < 6; k++) w[2 + k] = (uint32_t) e.c[2 * k] | ((uint32_t) e.c[2 * k + 1] << 16);
+        for (int k = 0; k < CM_DIRX_INLINE / 2; k++) w[2 + k] = (uint32_t) e.c[2 * k] | ((uint32_t) e.c[2 * k + 1] << 16);
     }
 #endif
     const uint32_t off = w[0], cnt = w[1];

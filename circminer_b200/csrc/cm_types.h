@@ -26,18 +26,21 @@
 #define CM_MAX_SEEDS 22                    // seeds per strand we support: ceil(300/14)
 #define CM_MAX_BAND 15                     // largest band_width the register DP supports
 
-// Fused directory entry, one 32-byte sector: bucket offset and size plus the bucket's first twelve checksums, so a
-// look-up in a bucket of <= 12 entries (or whose key sorts before the 12th) never touches the checksum array -- one
-// random DRAM access per seed instead of the reference's two dependent ones (directory -> bucket).  At GRCh38 occupancy
-// (4 entries per bucket on average, Poisson) that is 99.9 % of the non-repeat buckets.
+// Fused directory entry: bucket offset and size plus the bucket's first CM_DIRX_INLINE checksums in one 16-byte (or
+// 32-byte) read, so a look-up in a small bucket (or whose key sorts before the last inline checksum) never touches the
+// checksum array -- one random DRAM access per seed instead of the reference's two dependent ones (directory -> bucket).
 // A bucket of >= ContigDev::big_th entries (repeat families: up to 10^5 entries) keeps, instead of inline checksums, the
 // number of its row in ContigDev::big_tab: the first entry of every value of the checksum's top big_bits bits, which
 // narrows the bisection from 17 dependent DRAM probes to a run of cnt / 2^big_bits entries.
+#ifndef CM_DIRX_INLINE
+#define CM_DIRX_INLINE 4    // 4: 16-byte entry, 12: 32-byte entry.  Measured on C3 (28 M seeds, contig 1): 1.70 ms against 2.11 ms --
+                            // the smaller table wins although 13 % of the GRCh38 buckets overflow four inline checksums
+#endif
 struct DirX {
     uint32_t off, cnt;
-    uint16_t c[12];
+    uint16_t c[CM_DIRX_INLINE];
 };
-#define CM_DIRX_INLINE 12
+static_assert(sizeof(DirX) == 16 || sizeof(DirX) == 32, "the directory entry is one or two 16-byte loads");
 #define CM_BIG_TH_DEFAULT 96
 
 // One packed contig resident in HBM.
