@@ -271,6 +271,20 @@ class Mapper:
                   "cm_gpu_align_batch")
         return dict(ed=o[0], sclen=o[1], indel=o[2], score=o[3])
 
+    def align_noalloc(self, kind, s, ns, t, nt, aux=None) -> dict:
+        """cm_gpu_align_batch_noalloc: same results as align(), staged in the library's fixed 4 MiB device array."""
+        s, ns = _rows(s, ns)
+        t, nt = _rows(t, nt)
+        if s.shape != t.shape:
+            raise ValueError("s and t must share shape")
+        n = s.shape[0]
+        aux = np.zeros(n, np.int32) if aux is None else np.ascontiguousarray(aux, np.int32)
+        o = [np.zeros(n, np.int32) for _ in range(4)]
+        self._chk(self.lib.cm_gpu_align_batch_noalloc(self.ctx, kind, C.c_uint32(n), _vp(s), _vp(ns), _vp(t), _vp(nt),
+                                                      C.c_uint32(s.shape[1]), _vp(aux), *[_vp(x) for x in o]),
+                  "cm_gpu_align_batch_noalloc")
+        return dict(ed=o[0], sclen=o[1], indel=o[2], score=o[3])
+
     def process_read(self, contig_id, seqs1, seqs2, mreads, lens1=None, lens2=None, out=None, state=None):
         """FilterRead::process_read, PE overload, for a batch (src/filter.cpp:124).  out / state: caller-owned result
         buffers (pinned memory makes the device->host copy several times faster)."""

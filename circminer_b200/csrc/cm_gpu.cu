@@ -13,6 +13,7 @@
 #include <vector>
 #include <thread>
 #include <atomic>
+#include <mutex>
 
 #include "cm_pipeline.h"
 
@@ -1185,3 +1186,4 @@ extern "C" int cm_gpu_seed_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, con
 #include "cm_kernels.cuh"
 #include "cm_host_pipeline.cuh"
 #include "cm_index_io.cuh"
+#include "cm_noalloc.cuh"

@@ -224,6 +224,17 @@ int cm_gpu_align_batch(cm_gpu_ctx *ctx, int kind, uint32_t n, const char *s, con
                        const uint16_t *n_t, uint32_t stride, const int32_t *aux, int32_t *out_ed,
                        int32_t *out_sclen, int32_t *out_indel, int32_t *out_score);
 
+/* cm_gpu_align_batch for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments
+ * and results as cm_gpu_align_batch; inputs and results are staged in one fixed device array of
+ * cm_gpu_noalloc_scratch_bytes() = 4 MiB that every GPU loading the library holds until exit.  The call makes no
+ * cudaMalloc / cudaFree; a batch that needs more than the array (about 2 * n * stride + 24 * n bytes) is refused with
+ * CM_ERR_ARG.  All calls on a device share the array: calls that overlap on the GPU race, the caller serialises them. */
+int cm_gpu_align_batch_noalloc(cm_gpu_ctx *ctx, int kind, uint32_t n, const char *s, const uint16_t *n_s, const char *t,
+                               const uint16_t *n_t, uint32_t stride, const int32_t *aux, int32_t *out_ed,
+                               int32_t *out_sclen, int32_t *out_indel, int32_t *out_score);
+size_t cm_gpu_noalloc_scratch_bytes(void);
+
 /* ---- the fused hot path ------------------------------------------------ */
 /* FilterRead::process_read, PE overload (src/filter.cpp:124-241) for n pairs.
  * seqs1/seqs2: mate rows; in[i] = the pair's carried MatchedRead (what
