@@ -152,10 +152,14 @@ def run_b200(a):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU path")
     torch.cuda.set_device(local)
+    # stdout carries the one JSON line and nothing else: NCCL prints its version banner (and, under NCCL_DEBUG=INFO, its log)
+    # on file descriptor 1 whatever NCCL_DEBUG_FILE says, so fd 1 points at stderr until the line is printed.  NCCL_DEBUG
+    # is left as the caller set it.
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL's banner / INFO lines go to stderr, stdout stays the one JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -327,7 +331,10 @@ def run_b200(a):
             line["alignment"] = {"error": repr(e)[:300]}
         if not a.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(a, w, n, threads=1)
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
     m2.close()
     m.close()
     if world > 1:
