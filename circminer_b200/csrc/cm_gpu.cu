@@ -344,9 +344,18 @@ extern "C" int cm_gpu_last_stage_ms(cm_gpu_ctx *ctx, float out[5]) {
     return CM_OK;
 }
 
+extern "C" int cm_gpu_device_count(void) {
+    int n = 0;
+    return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0;
+}
+
+static void preload_kernels();   // end of this file: the kernels are defined below
+
 extern "C" int cm_gpu_warmup(int device) {
     if (cudaSetDevice(device) != cudaSuccess) return CM_ERR_CUDA;
-    return cudaFree(nullptr) == cudaSuccess ? CM_OK : CM_ERR_CUDA;
+    if (cudaFree(nullptr) != cudaSuccess) return CM_ERR_CUDA;
+    preload_kernels();   // CUDA loads a kernel's code at its first launch: take that out of the first batch too
+    return CM_OK;
 }
 
 extern "C" int cm_gpu_host_alloc(size_t bytes, void **out) {
@@ -1187,3 +1196,17 @@ extern "C" int cm_gpu_seed_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, con
 #include "cm_host_pipeline.cuh"
 #include "cm_index_io.cuh"
 #include "cm_noalloc.cuh"
+
+// the hot-path kernels, loaded on the current device (cudaFuncGetAttributes forces the lazy load)
+static void preload_kernels() {
+    cudaFuncAttributes fa;
+    const void *ks[] = {(const void *) k_make_strands, (const void *) k_seed, (const void *) k_cell_count, (const void *) k_strand_key,
+                        (const void *) k_chain, (const void *) k_chain_warp, (const void *) k_chain_big, (const void *) k_spec_count,
+                        (const void *) k_chain_ids, (const void *) k_chain_list, (const void *) k_chain_spec, (const void *) k_chain_walk,
+                        (const void *) k_pair_key, (const void *) k_process_pe, (const void *) k_process_pe_warp, (const void *) k_process_se,
+                        (const void *) k_round_commit, (const void *) k_round_compact, (const void *) k_unpack_cref, (const void *) k_kmer_keys,
+                        (const void *) k_bucket_hist, (const void *) k_split_keys, (const void *) k_build_dirx, (const void *) k_count_big,
+                        (const void *) k_build_big_tab, (const void *) k_init_prep_lut};
+    for (const void *k : ks) cudaFuncGetAttributes(&fa, k);
+    cudaGetLastError();
+}

@@ -133,6 +133,9 @@ int cm_gpu_create(int device, const cm_params *params, cm_gpu_ctx **out);
  * program calls it from a side thread at start-up so that the cost overlaps its own index / GTF loading
  * (src/circminer.cpp:125-260) instead of landing in the first cm_gpu_create. */
 int cm_gpu_warmup(int device);
+/* number of CUDA devices visible to the process (0 when there is none): how many contexts a multi-GPU host creates, the
+ * role of `-t threadCount` for the reference's mapping threads (src/circminer.cpp:290-297) */
+int cm_gpu_device_count(void);
 int cm_gpu_create_shared(cm_gpu_ctx *parent, cm_gpu_ctx **out);
 int cm_gpu_destroy(cm_gpu_ctx *ctx);
 const char *cm_gpu_last_error(const cm_gpu_ctx *ctx);   /* ctx may be NULL: last create error */

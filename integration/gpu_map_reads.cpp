@@ -19,6 +19,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <ctime>
+#include <condition_variable>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -39,7 +41,9 @@ extern pthread_mutex_t buffer_lock;
 
 namespace {
 
-cm_gpu_ctx *g_ctx = nullptr;
+cm_gpu_ctx *g_ctx = nullptr;            // first root context (serial / SAM path, error text)
+std::vector<cm_gpu_ctx *> g_roots;      // one per device in use: owns that GPU's resident contigs and annotation
+std::vector<cm_gpu_ctx *> g_workers;    // contexts batches are dealt to: every root plus its shared contexts
 cm_params g_params;
 const bool g_verbose = getenv("CM_GPU_VERBOSE") != nullptr;   // phase times on stderr
 double now_s() {
@@ -179,39 +183,58 @@ void upload_annotation(int c) {
     A.chr_shift = chr_shift.data(); A.chr_id = chr_id.data();
     A.n_bits = n_bits;
     A.near_border = nb.data(); A.intronic = in.data();
-    if (cm_gpu_load_annotation(g_ctx, c, &A) != CM_OK) die("cm_gpu_load_annotation");
+    for (cm_gpu_ctx *root : g_roots)
+        if (cm_gpu_load_annotation(root, c, &A) != CM_OK) { g_ctx = root; die("cm_gpu_load_annotation"); }
 }
 
-int gpu_device() {
-    const char *dev = getenv("CM_GPU_DEVICE");
-    return dev ? atoi(dev) : 0;
+// Devices the mapping round uses: CM_GPU_DEVICES = "all" or a comma list ("0,1,2,3"; a device may be named twice, which gives
+// it two independent root contexts); else CM_GPU_DEVICE (one device); else every visible GPU.  The reference's counterpart
+// is `-t threadCount` mapping threads over one shared index (src/circminer.cpp:290-297): here every GPU holds the index
+// and batches of pairs are dealt to them round-robin.
+std::vector<int> gpu_devices() {
+    std::vector<int> d;
+    const char *list = getenv("CM_GPU_DEVICES"), *one = getenv("CM_GPU_DEVICE");
+    if (list && strcmp(list, "all")) {
+        for (const char *p = list; *p;) {
+            d.push_back(atoi(p));
+            while (*p && *p != ',') p++;
+            if (*p == ',') p++;
+        }
+    } else if (!list && one) {
+        d.push_back(atoi(one));
+    } else {
+        const int n = cm_gpu_device_count();
+        for (int i = 0; i < n; i++) d.push_back(i);
+    }
+    if (d.empty()) d.push_back(0);
+    return d;
 }
+int gpu_device() { return gpu_devices()[0]; }
 
-// CUDA context creation overlaps the reference's own start-up (GTF, index meta, first loadHashTable)
-struct Warmup {
-    std::thread th;
-    Warmup() : th([] { cm_gpu_warmup(gpu_device()); }) {}
-    void wait() { if (th.joinable()) th.join(); }
-    ~Warmup() { wait(); }
-} g_warmup;
+void warmup_wait();
 
 void ensure_round(int c) {
     const double t_in = now_s();
-    g_warmup.wait();
-    if (!g_ctx) {
+    warmup_wait();
+    if (g_roots.empty()) {
         g_chr.reserve(CHR_CAP);
         cm_params &p = g_params;
         cm_params_default(&p);
         p.kmer = kmer; p.max_read_len = maxReadLength; p.max_ed = maxEd; p.max_sc = maxSc; p.band_width = bandWidth;
         p.seed_lim = seedLim; p.max_tlen = maxTlen; p.max_intron_len = maxIntronLen; p.max_chain_len = maxChainLen;
         p.scan_level = scanLevel;
-        if (cm_gpu_create(gpu_device(), &p, &g_ctx) != CM_OK) die("cm_gpu_create");
+        for (int dev : gpu_devices()) {
+            cm_gpu_ctx *root = nullptr;
+            if (cm_gpu_create(dev, &p, &root) != CM_OK) die("cm_gpu_create");
+            g_roots.push_back(root);
+        }
+        g_ctx = g_roots[0];
     }
     if (g_loaded_contig == c) return;
     const double t_ctx = now_s();
-    // Index of this contig on the device.  Default: built there from the 3-bit packed contig the reference has just
-    // loaded (38 MB over PCIe per 100 Mbp).  CM_GPU_INDEX=upload converts and uploads the reference's own bucket table
-    // instead (the two are compared entry by entry in tests/test_gpu_seed.py).
+    // Index of this contig on every device.  Default: built there from the 3-bit packed contig the reference has just
+    // loaded (38 MB over PCIe per 100 Mbp), all devices at once.  CM_GPU_INDEX=upload converts and uploads the reference's own
+    // bucket table instead (the two are compared entry by entry in tests/test_gpu_seed.py).
     double t_scan = now_s();
     const char *how = getenv("CM_GPU_INDEX");
     if (how && !strcmp(how, "upload")) {
@@ -230,17 +253,34 @@ void ensure_round(int c) {
         });
         for (uint64_t m : part) n = std::max(n, m);
         t_scan = now_s();
-        if (cm_gpu_load_contig(g_ctx, c, (const void *const *) _ih_hashTable, _ih_hashTableMem, n, (const uint64_t *) _ih_crefGen,
-                               (uint32_t) _ih_refGenLen) != CM_OK)
-            die("cm_gpu_load_contig");
-    } else if (cm_gpu_build_contig_packed(g_ctx, c, (const uint64_t *) _ih_crefGen, (uint32_t) _ih_refGenLen) != CM_OK)
-        die("cm_gpu_build_contig_packed");
+        for (cm_gpu_ctx *root : g_roots)
+            if (cm_gpu_load_contig(root, c, (const void *const *) _ih_hashTable, _ih_hashTableMem, n, (const uint64_t *) _ih_crefGen,
+                                   (uint32_t) _ih_refGenLen) != CM_OK) { g_ctx = root; die("cm_gpu_load_contig"); }
+    } else {
+        std::atomic<int> bad(-1);
+        feed::parallel_for((int) g_roots.size(), [&](int k) {
+            if (cm_gpu_build_contig_packed(g_roots[k], c, (const uint64_t *) _ih_crefGen, (uint32_t) _ih_refGenLen) != CM_OK) bad = k;
+        });
+        if (bad.load() >= 0) { g_ctx = g_roots[bad.load()]; die("cm_gpu_build_contig_packed"); }
+    }
     const double t_idx = now_s();
     upload_annotation(c);
     g_loaded_contig = c;
+    if (g_workers.empty()) {
+        // CM_GPU_CTX_PER_DEVICE (default 2): contexts per device; the extra ones share their root's index and let one batch's
+        // copies run beside another batch's kernels
+        const char *e = getenv("CM_GPU_CTX_PER_DEVICE");
+        const int per = std::max(1, e ? atoi(e) : 2);
+        for (int k = 0; k < per; k++)
+            for (cm_gpu_ctx *root : g_roots) {
+                cm_gpu_ctx *w = root;
+                if (k && cm_gpu_create_shared(root, &w) != CM_OK) { g_ctx = root; die("cm_gpu_create_shared"); }
+                g_workers.push_back(w);
+            }
+    }
     if (g_verbose)
-        fprintf(stderr, "circminer_gpu: contig %d: context %.3f s, table scan %.3f s, index on device %.3f s, annotation %.3f s\n", c,
-                t_ctx - t_in, t_scan - t_ctx, t_idx - t_scan, now_s() - t_idx);
+        fprintf(stderr, "circminer_gpu: contig %d on %zu device(s), %zu contexts: context %.3f s, table scan %.3f s, index on device %.3f s, annotation %.3f s\n",
+                c, g_roots.size(), g_workers.size(), t_ctx - t_in, t_scan - t_ctx, t_idx - t_scan, now_s() - t_idx);
 }
 
 // a Record that outlives FASTQParser's per-thread buffer
@@ -268,98 +308,248 @@ template <class T> T *pinned(size_t n) {
     return (T *) p;
 }
 
-// Batched rounds with the parallel host feed of host_feed.h (PAM output or none).
+// One batch in flight: its block of both FASTQ files, the pinned batch arrays, and where it stands.
+struct Slot {
+    feed::RawFile raw[2];
+    size_t B = 0;
+    uint32_t stride_ = 0;
+    char *s1 = nullptr, *s2 = nullptr;
+    uint16_t *l1 = nullptr, *l2 = nullptr;
+    cm_mread *in = nullptr, *out = nullptr;
+    int32_t *state = nullptr;
+    std::vector<feed::RecMeta> m1, m2;
+    size_t n = 0;
+    enum { EMPTY, READY, DONE } st = EMPTY;
+    bool quit = false;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::thread prep;   // allocates this slot's buffers beside the first block read (page-locking 0.6 GB takes 0.15 s)
+    void reserve_async(size_t b, uint32_t stride, size_t cap) {
+        if (prep.joinable()) prep.join();
+        if (B >= b && stride_ >= stride && raw[0].buf.size() >= cap + 1) return;
+        prep = std::thread([this, b, stride, cap] { reserve(b, stride, cap); });
+    }
+    void ready() { if (prep.joinable()) prep.join(); }
+    ~Slot() { ready(); }
+    void reserve(size_t b, uint32_t stride, size_t cap) {
+        raw[0].buf.reserve_bytes(cap + 1);
+        raw[1].buf.reserve_bytes(cap + 1);
+        if (B >= b && stride_ >= stride) return;
+        if (B) {
+            cm_gpu_host_free(s1); cm_gpu_host_free(s2); cm_gpu_host_free(l1); cm_gpu_host_free(l2);
+            cm_gpu_host_free(in); cm_gpu_host_free(out); cm_gpu_host_free(state);
+        }
+        s1 = pinned<char>(b * stride); s2 = pinned<char>(b * stride);
+        l1 = pinned<uint16_t>(b); l2 = pinned<uint16_t>(b);
+        in = pinned<cm_mread>(b); out = pinned<cm_mread>(b);
+        state = pinned<int32_t>(b);
+        m1.resize(b); m2.resize(b);
+        B = b;
+        stride_ = stride;
+    }
+};
+
+std::vector<std::unique_ptr<Slot>> g_slots;
+
+// CUDA context creation (and kernel loading) on every device in use, and the page-locking of the batch buffers, overlap
+// the reference's own start-up (GTF, index meta, first loadHashTable): threads started from a static initialiser.  The
+// buffers are sized for the default maximum read length; a run with a larger -l re-allocates them in its first round.
+size_t batch_pairs() {
+    const char *bs = getenv("CM_GPU_BATCH");
+    return bs ? (size_t) atol(bs) : 524288;
+}
+size_t block_bytes(size_t B) { return std::min<size_t>(std::max<size_t>(B * 512, 1u << 20), 1u << 30); }
+struct Warmup {
+    std::vector<std::thread> th;
+    Warmup() {
+        if (getenv("CM_GPU_NO_WARMUP")) return;
+        const std::vector<int> devs = gpu_devices();
+        for (int dev : devs) th.emplace_back([dev] { cm_gpu_warmup(dev); });
+        const char *e = getenv("CM_GPU_CTX_PER_DEVICE");
+        const size_t K = devs.size() * (size_t) std::max(1, e ? atoi(e) : 2), B = batch_pairs();
+        while (g_slots.size() < K) g_slots.emplace_back(new Slot);
+        for (auto &sl : g_slots) sl->reserve_async(B, 300, block_bytes(B));
+    }
+    void wait() { for (auto &t : th) if (t.joinable()) t.join(); }
+    ~Warmup() { wait(); }
+} g_warmup;
+void warmup_wait() { g_warmup.wait(); }
+
+// Batched rounds with the parallel host feed of host_feed.h (PAM output or none).  Batches are dealt round-robin to the
+// worker contexts (every GPU in use, CM_GPU_CTX_PER_DEVICE contexts each): batch b goes to slot / context b mod K, the
+// host reads and parses batch b + 1 while earlier batches are on the GPUs, and results are formatted and written in batch
+// order -- the reference's `-t 1` order -- so the files do not depend on how many GPUs took part.
 void gpu_map_reads_parallel(size_t B) {
     const int is_last = filter_read.get_last_round();
     const int T = std::max(1, threadCount);
     const uint32_t stride = (uint32_t) maxReadLength;
-    const size_t cap = std::min<size_t>(std::max<size_t>(B * 512, 1u << 20), 1u << 30);
-    // block buffers, pinned batch arrays and text buffers live across rounds (one allocation per run)
-    static feed::RawFile raw[2][2];
-    static size_t B_alloc = 0;
-    static char *s1, *s2;
-    static uint16_t *l1, *l2;
-    static cm_mread *in, *out;
-    static int32_t *state;
-    static std::vector<feed::RecMeta> m1, m2;
+    const size_t cap = block_bytes(B);
+    const size_t K = g_workers.size();
+    // slots (block buffers, pinned batch arrays) and text buffers live across rounds
+    auto &slots = g_slots;
     static std::vector<feed::TextOut> text;
-    const double t_setup = now_s();
-    for (int s = 0; s < 2; s++) {
-        raw[s][0].init(fq_parser1.gzinput, cap);
-        raw[s][1].init(fq_parser2.gzinput, cap);
-    }
-    if (B_alloc < B) {
-        if (B_alloc) {
-            cm_gpu_host_free(s1); cm_gpu_host_free(s2); cm_gpu_host_free(l1); cm_gpu_host_free(l2);
-            cm_gpu_host_free(in); cm_gpu_host_free(out); cm_gpu_host_free(state);
-        }
-        s1 = pinned<char>(B * stride); s2 = pinned<char>(B * stride);
-        l1 = pinned<uint16_t>(B); l2 = pinned<uint16_t>(B);
-        in = pinned<cm_mread>(B); out = pinned<cm_mread>(B);
-        state = pinned<int32_t>(B);
-        m1.resize(B); m2.resize(B);
-        B_alloc = B;
-    }
+    while (slots.size() < K) slots.emplace_back(new Slot);
+    for (size_t k = 0; k < K; k++) slots[k]->reserve_async(B, stride, cap);
     text.resize(T);
     cm_mread fresh;
     cm_mread_init(&fresh, &g_params);
-    int cur = 0;
-    const double t_begin = now_s();
-    if (g_verbose) fprintf(stderr, "circminer_gpu: host buffers %.3f s\n", t_begin - t_setup);
-    feed::parallel_for(2, [&](int k) { raw[cur][k].fill(); });
-    feed::LineIndex ix1, ix2;
-    double ph[6] = {0, 0, 0, 0, 0, 0};   // first read, parse, map, format, write, wait for the next block
-    ph[0] = now_s() - t_begin;
-    size_t n_batches = 0, n_total = 0;
-    while (true) {
+    const int contig = contigNum;
+    double ph[6] = {0, 0, 0, 0, 0, 0};   // read, parse, wait for GPUs, format, write, host buffers
+    std::vector<double> gpu_busy(K, 0.0);
+    std::vector<std::vector<float>> call_ms(K);
+    std::atomic<int> failed(-1);
+
+    std::vector<std::thread> workers;
+    for (size_t k = 0; k < K; k++) {
+        slots[k]->st = Slot::EMPTY;
+        slots[k]->quit = false;
+        workers.emplace_back([&, k] {
+            Slot &sl = *slots[k];
+            for (;;) {
+                std::unique_lock<std::mutex> lk(sl.mu);
+                sl.cv.wait(lk, [&] { return sl.st == Slot::READY || sl.quit; });
+                if (sl.st != Slot::READY) return;
+                lk.unlock();
+                const double t0 = now_s();
+                if (cm_gpu_process_batch_pe(g_workers[k], contig, (uint32_t) sl.n, sl.s1, sl.s2, stride, sl.l1, sl.l2, sl.in, sl.out, sl.state) != CM_OK)
+                    failed = (int) k;
+                gpu_busy[k] += now_s() - t0;
+                call_ms[k].push_back((float) ((now_s() - t0) * 1e3));
+                lk.lock();
+                sl.st = Slot::DONE;
+                sl.cv.notify_all();
+            }
+        });
+    }
+    auto stop_workers = [&] {
+        for (size_t k = 0; k < K; k++) {
+            { std::lock_guard<std::mutex> lk(slots[k]->mu); slots[k]->quit = true; }
+            slots[k]->cv.notify_all();
+        }
+        for (auto &w : workers) w.join();
+    };
+    // batch `b` (in slot b mod K): wait for its GPU call, format, write, free the slot
+    auto retire = [&](size_t b) {
+        Slot &sl = *slots[b % K];
         double t0 = now_s();
-        feed::count_lines(raw[cur][0], T, ix1);
-        feed::count_lines(raw[cur][1], T, ix2);
-        const size_t n = (size_t) std::min<uint64_t>(B, std::min(ix1.lines, ix2.lines) / 4);
-        if (!n) break;
-        size_t e[2] = {raw[cur][0].len, raw[cur][1].len};
-        feed::parse_records(raw[cur][0], ix1, T, n, stride, m1.data(), s1, l1, in, fresh, e[0]);
-        feed::parse_records(raw[cur][1], ix2, T, n, stride, m2.data(), s2, l2, nullptr, fresh, e[1]);
-        // the next block of both files is read while this batch is mapped and written
-        std::thread pre[2];
-        for (int k = 0; k < 2; k++)
-            pre[k] = std::thread([&, k] {
-                feed::RawFile &a = raw[cur][k], &b = raw[cur ^ 1][k];
-                b.len = a.len - e[k];
-                memcpy(b.buf.data(), a.buf.data() + e[k], b.len);
-                b.eof = a.eof;
-                b.fill();
-            });
+        {
+            std::unique_lock<std::mutex> lk(sl.mu);
+            sl.cv.wait(lk, [&] { return sl.st == Slot::DONE; });
+        }
+        if (failed.load() >= 0) { g_ctx = g_workers[failed.load()]; die("cm_gpu_process_batch_pe"); }
         double t1 = now_s();
-        ph[1] += t1 - t0;
-        if (cm_gpu_process_batch_pe(g_ctx, contigNum, (uint32_t) n, s1, s2, stride, l1, l2, in, out, state) != CM_OK)
-            die("cm_gpu_process_batch_pe");
-        t0 = now_s();
-        ph[2] += t0 - t1;
-        const char *b1 = raw[cur][0].buf.data(), *b2 = raw[cur][1].buf.data();
+        ph[2] += t1 - t0;
+        const char *b1 = sl.raw[0].buf.data(), *b2 = sl.raw[1].buf.data();
+        const size_t n = sl.n;
         feed::parallel_for(T, [&](int t) {
             feed::TextOut &o = text[t];
             o.pam.clear(); o.r1.clear(); o.r2.clear();
-            feed::format_range(n * t / T, n * (t + 1) / T, b1, b2, m1.data(), m2.data(), out, state, is_last, o);
+            feed::format_range(n * t / T, n * (t + 1) / T, b1, b2, sl.m1.data(), sl.m2.data(), sl.out, sl.state, is_last, o);
         });
-        t1 = now_s();
-        ph[3] += t1 - t0;
+        t0 = now_s();
+        ph[3] += t0 - t1;
         for (int t = 0; t < T; t++) {   // input order == the reference's -t 1 order
             if (!text[t].pam.empty()) fwrite(text[t].pam.data(), 1, text[t].pam.size(), filter_read.sam_output.outsam);
             if (!text[t].r1.empty()) fwrite(text[t].r1.data(), 1, text[t].r1.size(), filter_read.temp_fq_r1);
             if (!text[t].r2.empty()) fwrite(text[t].r2.data(), 1, text[t].r2.size(), filter_read.temp_fq_r2);
         }
+        ph[4] += now_s() - t0;
+        {
+            std::lock_guard<std::mutex> lk(sl.mu);
+            sl.st = Slot::EMPTY;
+        }
+        sl.cv.notify_all();
+    };
+    // batches are retired in order by a thread of their own, so that formatting and writing batch b run beside the reading
+    // and parsing of batch b + K
+    std::mutex flow_mu;
+    std::condition_variable flow_cv;
+    size_t dispatched = 0;
+    bool input_done = false;
+    std::thread retirer([&] {
+        for (size_t b = 0;; b++) {
+            {
+                std::unique_lock<std::mutex> lk(flow_mu);
+                flow_cv.wait(lk, [&] { return dispatched > b || input_done; });
+                if (dispatched <= b) return;
+            }
+            retire(b);
+        }
+    });
+
+    const double t_begin = now_s();
+    feed::LineIndex ix1, ix2;
+    size_t n_batches = 0, n_total = 0;
+    size_t carry_len[2] = {0, 0};
+    const char *carry_src[2] = {nullptr, nullptr};
+    bool eof[2] = {false, false};
+    for (size_t b = 0;; b++) {
+        Slot &sl = *slots[b % K];
+        double t0 = now_s();
+        sl.ready();
+        {   // the slot batch b needs is free again once batch b - K has been written
+            std::unique_lock<std::mutex> lk(sl.mu);
+            sl.cv.wait(lk, [&] { return sl.st == Slot::EMPTY; });
+        }
+        double t1 = now_s();
+        ph[5] += t1 - t0;
+        gzFile gz[2] = {fq_parser1.gzinput, fq_parser2.gzinput};
+        feed::parallel_for(2, [&](int k) {
+            feed::RawFile &r = sl.raw[k];
+            r.gz = gz[k];
+            if (carry_len[k]) memmove(r.buf.data(), carry_src[k], carry_len[k]);   // the unread tail of the previous block
+            r.len = carry_len[k];
+            r.eof = eof[k];
+            r.fill();
+            eof[k] = r.eof;
+        });
         t0 = now_s();
-        ph[4] += t0 - t1;
-        for (auto &p : pre) p.join();
-        ph[5] += now_s() - t0;
-        cur ^= 1;
+        ph[0] += t0 - t1;
+        feed::count_lines(sl.raw[0], T, ix1);
+        feed::count_lines(sl.raw[1], T, ix2);
+        const size_t n = (size_t) std::min<uint64_t>(B, std::min(ix1.lines, ix2.lines) / 4);
+        if (!n) break;
+        size_t e[2] = {sl.raw[0].len, sl.raw[1].len};
+        feed::parse_records(sl.raw[0], ix1, T, n, stride, sl.m1.data(), sl.s1, sl.l1, sl.in, fresh, e[0]);
+        feed::parse_records(sl.raw[1], ix2, T, n, stride, sl.m2.data(), sl.s2, sl.l2, nullptr, fresh, e[1]);
+        for (int k = 0; k < 2; k++) {
+            carry_src[k] = sl.raw[k].buf.data() + e[k];
+            carry_len[k] = sl.raw[k].len - e[k];
+        }
+        sl.n = n;
+        ph[1] += now_s() - t0;
+        {
+            std::lock_guard<std::mutex> lk(sl.mu);
+            sl.st = Slot::READY;
+        }
+        sl.cv.notify_all();
         n_batches++;
         n_total += n;
+        {
+            std::lock_guard<std::mutex> lk(flow_mu);
+            dispatched = n_batches;
+        }
+        flow_cv.notify_all();
     }
-    if (g_verbose)
-        fprintf(stderr, "circminer_gpu: round: %zu pairs in %zu batches, %d host threads: first read %.3f s, parse %.3f s, map %.3f s, "
-                "format %.3f s, write %.3f s, wait for next block %.3f s\n", n_total, n_batches, T, ph[0], ph[1], ph[2], ph[3], ph[4], ph[5]);
+    {
+        std::lock_guard<std::mutex> lk(flow_mu);
+        input_done = true;
+    }
+    flow_cv.notify_all();
+    retirer.join();
+    stop_workers();
+    if (g_verbose) {
+        double busy = 0;
+        for (double x : gpu_busy) busy += x;
+        fprintf(stderr, "circminer_gpu: round: %zu pairs in %zu batches over %zu contexts on %zu device(s), %d host threads, %.3f s: feeding thread: wait for a free slot %.3f s, "
+                "read %.3f s, parse %.3f s | retiring thread: wait for GPUs %.3f s, format %.3f s, write %.3f s | GPU calls %.3f s in total\n", n_total, n_batches, K,
+                g_roots.size(), T, now_s() - t_begin, ph[5], ph[0], ph[1], ph[2], ph[3], ph[4], busy);
+        for (size_t k = 0; k < K; k++) {
+            fprintf(stderr, "circminer_gpu:   context %zu: GPU call ms", k);
+            for (size_t j = 0; j < call_ms[k].size() && j < 12; j++) fprintf(stderr, " %.1f", call_ms[k][j]);
+            fprintf(stderr, "\n");
+        }
+    }
 }
 
 void *gpu_map_reads(void *args) {
@@ -367,8 +557,7 @@ void *gpu_map_reads(void *args) {
     g_fa = fa;
     ensure_round(contigNum);
     const int is_last = filter_read.get_last_round();
-    const char *bs = getenv("CM_GPU_BATCH");
-    const size_t B = bs ? (size_t) atol(bs) : 262144;
+    const size_t B = batch_pairs();
     if (reportMapping != SAMFORMAT && !getenv("CM_GPU_SERIAL_HOST")) {
         gpu_map_reads_parallel(B);
         return NULL;

@@ -1,6 +1,7 @@
 """Whole-binary comparison at bench scale: the unmodified reference (`oracle/_ref/circminer -t <all cores>`)
 against the drop-in (`oracle/_ref/circminer_gpu`, the same objects with the mapping threads routed to
-libcm_gpu.so) on the first --pairs pairs of a bench workload (default C2, 1 M pairs 2x150).
+libcm_gpu.so) on the first --pairs pairs of a bench workload (default C2, 1 M pairs 2x150; C3 = GRCh38 scale, three
+rounds), the drop-in once per --devices setting (CM_GPU_DEVICES: which GPUs the batches are dealt to).
 
 Reports, per binary, the mapping time (sum of the reference's own "Completed round" real-time log lines,
 src/circminer.cpp:302: FASTQ parse, mapping and PAM / remain writes; index and GTF load excluded), the whole
@@ -58,19 +59,18 @@ def main():
     ap.add_argument("--pairs", type=int, default=0)
     ap.add_argument("--data", default="/tmp/cm_bench")
     ap.add_argument("--out", default="")
-    ap.add_argument("--batch", type=int, default=262144)
+    ap.add_argument("--batch", type=int, default=524288)
+    ap.add_argument("--devices", nargs="+", default=["0"], help="CM_GPU_DEVICES settings to time the drop-in under, e.g. 0 0,1 all")
+    ap.add_argument("--skip-reference", action="store_true")
     a = ap.parse_args()
-    from dataclasses import replace
-    from circminer_b200 import synth
+    from circminer_b200 import synth, workload
     from oracle.cpu_baseline import ensure_ref_index
     from oracle.refharness import REF_BIN
     gpu_bin = os.path.join(ROOT, "oracle", "_ref", "circminer_gpu")
-    cfg = synth.CONFIGS[a.workload]
-    if a.pairs:
-        cfg = replace(cfg, n_pairs=a.pairs)
+    cfg = workload.config(a.workload)
     datadir = os.path.join(a.data, f"{a.workload}_r0")
-    d = synth.generate(cfg, datadir, write_reads=False)
-    ensure_ref_index(d["fa"])
+    d = workload.prepare(a.workload, datadir, n_pairs=a.pairs or cfg.n_pairs)
+    ensure_ref_index(d, a.workload, workload.params_for(a.workload).kmer)
     n = len(d["r1"])
     fq1 = os.path.join(datadir, f"dropin_{n}_1.fastq")
     fq2 = os.path.join(datadir, f"dropin_{n}_2.fastq")
@@ -83,17 +83,19 @@ def main():
     res = {"workload": a.workload, "pairs": n, "read_len": int(d["r1"].shape[1]), "host_cores": ncores}
     res["reference"] = run(REF_BIN, d, fq1, fq2, ref_out, ncores)
     res["reference"]["threads"] = ncores
-    res["dropin"] = run(gpu_bin, d, fq1, fq2, gpu_out, ncores, env={"CM_GPU_BATCH": str(a.batch), "CM_GPU_VERBOSE": "1"})
-    res["dropin"]["batch"] = a.batch
+    res["reference"]["reads_per_s_mapping"] = 2.0 * n / res["reference"]["mapping_s"]
     same = {}
-    for suffix, sort_lines in ((".mapping.pam", True), (".candidates.pam", False), (".circ_report", False)):
-        ra, rb = digest(ref_out + suffix, sort_lines), digest(gpu_out + suffix, sort_lines)
-        same[suffix] = {"identical": ra is not None and ra == rb, "bytes": os.path.getsize(ref_out + suffix) if ra else None,
-                        "compared": "sorted lines" if sort_lines else "bytes"}
+    res["dropin"] = []
+    for dev in a.devices:
+        r = run(gpu_bin, d, fq1, fq2, gpu_out, ncores, env={"CM_GPU_BATCH": str(a.batch), "CM_GPU_VERBOSE": "1", "CM_GPU_DEVICES": dev})
+        r.update(batch=a.batch, devices=dev, reads_per_s_mapping=2.0 * n / r["mapping_s"] if r["mapping_s"] else None,
+                 speedup_mapping=res["reference"]["mapping_s"] / r["mapping_s"] if r["mapping_s"] else None)
+        for suffix, sort_lines in ((".mapping.pam", True), (".candidates.pam", False), (".circ_report", False)):
+            ra, rb = digest(ref_out + suffix, sort_lines), digest(gpu_out + suffix, sort_lines)
+            same[f"{dev}:{suffix}"] = {"identical": ra is not None and ra == rb, "bytes": os.path.getsize(ref_out + suffix) if ra else None,
+                                       "compared": "sorted lines" if sort_lines else "bytes"}
+        res["dropin"].append(r)
     res["outputs"] = same
-    for k in ("reference", "dropin"):
-        res[k]["reads_per_s_mapping"] = 2.0 * n / res[k]["mapping_s"] if res[k]["mapping_s"] else None
-    res["speedup_mapping"] = res["reference"]["mapping_s"] / res["dropin"]["mapping_s"] if res["dropin"]["mapping_s"] else None
     line = json.dumps(res)
     print(line)
     if a.out:

@@ -1,6 +1,6 @@
 // TEST INFRASTRUCTURE ONLY -- never part of the product.
 // The drop-in shim (integration/gpu_map_reads.cpp + host_feed.h) compiled into one translation unit with a stand-in
-// for the nine C-ABI calls it makes, so that the HOST side of the drop-in -- block reads, parallel FASTQ parse, header
+// for the C-ABI calls it makes, so that the HOST side of the drop-in -- block reads, parallel FASTQ parse, header
 // tokens -> cm_mread, PAM / remain-FASTQ text, write order -- can be checked byte for byte against the reference on a
 // box without a GPU.  The stand-in answers cm_gpu_process_batch_pe with the reference's own FilterRead::process_read
 // (src/filter.cpp:124), one pair at a time, on the scratch of mapping thread 0; nothing here touches libcm_gpu.so.
@@ -35,7 +35,9 @@ void cm_mread_init(cm_mread *m, const cm_params *p) {
     m->chr_r1 = -1; m->chr_r2 = -1;
 }
 int cm_gpu_warmup(int) { return CM_OK; }
+int cm_gpu_device_count(void) { return 1; }
 int cm_gpu_create(int, const cm_params *, cm_gpu_ctx **out) { *out = (cm_gpu_ctx *) &g_params; return CM_OK; }
+int cm_gpu_create_shared(cm_gpu_ctx *parent, cm_gpu_ctx **out) { *out = parent; return CM_OK; }
 const char *cm_gpu_last_error(const cm_gpu_ctx *) { return "mock"; }
 int cm_gpu_load_contig(cm_gpu_ctx *, int, const void *const *, const void *, uint64_t, const uint64_t *, uint32_t) { return CM_OK; }
 int cm_gpu_build_contig_packed(cm_gpu_ctx *, int, const uint64_t *, uint32_t) { return CM_OK; }
@@ -45,6 +47,8 @@ int cm_gpu_host_free(void *p) { free(p); return CM_OK; }
 
 int cm_gpu_process_batch_pe(cm_gpu_ctx *, int, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
                             const uint16_t *len1, const uint16_t *len2, const cm_mread *in, cm_mread *out, int32_t *state) {
+    static std::mutex mu;   // the shim runs one host thread per context; the reference's scratch here is thread 0's
+    std::lock_guard<std::mutex> lk(mu);
     static Record *r1 = nullptr, *r2 = nullptr;
     if (!r1) { r1 = new Record; r1->init(); r2 = new Record; r2->init(); }
     FilterArgs *fa = mock_scratch();

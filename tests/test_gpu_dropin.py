@@ -31,8 +31,13 @@ def _run(binary, w, out, env=None, extra=()):
 
 
 @pytest.mark.skipif(not (has_ref() and os.path.exists(GPU)), reason="oracle/_ref/circminer_gpu not built")
-@pytest.mark.parametrize("scan", ["0", "2"])
-def test_dropin_binary_outputs_are_byte_identical(tmp_path, scan):
+@pytest.mark.parametrize("scan,devices", [("0", "0"), ("2", "0"), ("0", "multi")])
+def test_dropin_binary_outputs_are_byte_identical(tmp_path, scan, devices):
+    """devices "multi": every visible GPU, or -- on a one-GPU box -- device 0 twice (two root contexts with their own copy
+    of the index): batches dealt round-robin over four contexts, files still the reference's."""
+    if devices == "multi":
+        import torch
+        devices = "all" if torch.cuda.device_count() > 1 else "0,0"
     from circminer_b200 import workload
     d = str(tmp_path / "t1")
     w = workload.prepare("T1", d, contig_size=3_500_000, write_reads=True)
@@ -46,7 +51,7 @@ def test_dropin_binary_outputs_are_byte_identical(tmp_path, scan):
     assert len({ln.split()[0] for ln in info if ln.strip()}) >= 2, "expected at least two packed contigs"
     ref_out, gpu_out = str(tmp_path / "ref"), str(tmp_path / "gpu")
     _run(REF, w, ref_out, extra=("-a", scan))
-    _run(GPU, w, gpu_out, env={"CM_GPU_BATCH": "4096"}, extra=("-a", scan))
+    _run(GPU, w, gpu_out, env={"CM_GPU_BATCH": "4096" if devices == "0" else "1500", "CM_GPU_DEVICES": devices}, extra=("-a", scan))
     ref_files = sorted(os.path.basename(f)[3:] for f in glob.glob(ref_out + "*") if os.path.isfile(f))
     gpu_files = sorted(os.path.basename(f)[3:] for f in glob.glob(gpu_out + "*") if os.path.isfile(f))
     assert ref_files == gpu_files and any(f.endswith("circ_report") for f in ref_files), (ref_files, gpu_files)

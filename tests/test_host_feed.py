@@ -41,12 +41,15 @@ def dataset(tmp_path_factory):
 
 
 @pytest.mark.skipif(not (has_ref() and os.path.exists(FEED)), reason="oracle/_ref/circminer_feedtest not built")
-@pytest.mark.parametrize("scan,threads,batch", [("0", 4, 1000), ("2", 3, 257), ("0", 1, 262144)])
-def test_host_feed_outputs_are_byte_identical(dataset, tmp_path, scan, threads, batch):
+@pytest.mark.parametrize("scan,threads,batch,devices,per", [("0", 4, 1000, "0", 2), ("2", 3, 257, "0,0,0", 2), ("0", 1, 262144, "0", 1),
+                                                            ("0", 2, 500, "0,0", 1)])
+def test_host_feed_outputs_are_byte_identical(dataset, tmp_path, scan, threads, batch, devices, per):
+    """devices / per: contexts the batches are dealt to (CM_GPU_DEVICES x CM_GPU_CTX_PER_DEVICE: 2, 6, 1, 2 batches in flight)."""
     w = dataset
     ref_out, feed_out = str(tmp_path / "ref"), str(tmp_path / "feed")
     _run(REF, w, ref_out, 1, extra=("-a", scan))
-    _run(FEED, w, feed_out, threads, env={"CM_GPU_BATCH": str(batch)}, extra=("-a", scan))
+    _run(FEED, w, feed_out, threads, env={"CM_GPU_BATCH": str(batch), "CM_GPU_DEVICES": devices, "CM_GPU_CTX_PER_DEVICE": str(per)},
+         extra=("-a", scan))
     ref_files = sorted(os.path.basename(f)[3:] for f in glob.glob(ref_out + "*") if os.path.isfile(f))
     feed_files = sorted(os.path.basename(f)[4:] for f in glob.glob(feed_out + "*") if os.path.isfile(f))
     assert ref_files == feed_files and any(f.endswith("circ_report") for f in ref_files), (ref_files, feed_files)
