@@ -61,6 +61,11 @@ MREAD_DTYPE = np.dtype([
     ("r1_forward", "u1"), ("r2_forward", "u1"), ("gm_compatible", "u1"), ("pad_", "u1", (3,))])
 assert MREAD_DTYPE.itemsize == 76
 
+MATE_DTYPE = np.dtype([("spos", "<u4"), ("epos", "<u4"), ("qspos", "<u4"), ("qepos", "<u4"), ("matched_len", "<u4"),
+                       ("left_ed", "<i4"), ("middle_ed", "<i4"), ("right_ed", "<i4"), ("sclen_left", "<i4"), ("sclen_right", "<i4"),
+                       ("dir", "<i4"), ("type", "<i4"), ("is_concord", "u1"), ("left_ok", "u1"), ("right_ok", "u1"), ("pad_", "u1")])
+assert MATE_DTYPE.itemsize == 52
+
 MREAD_COMPARE_FIELDS = [f for f in MREAD_DTYPE.names if f != "pad_"]
 
 
@@ -87,6 +92,68 @@ def fresh_mreads(n: int, max_ed: int = 4) -> np.ndarray:
 
 class CmGpuError(RuntimeError):
     pass
+
+
+_ANNOT_U4 = ("iv_spos", "iv_epos", "iv_max_end", "iv_min_end", "iv_max_next_exon", "iv_seg_off", "seg_start", "seg_end",
+             "seg_next_exon_beg", "seg_gene_id", "seg_tid_off", "tid", "t2s_off", "gene_start", "gene_end", "chr_shift")
+_ANNOT_OTHER = (("trans_start_ind", np.int32), ("chr_id", np.int32), ("t2s", np.uint8), ("near_border", np.uint64),
+                ("intronic", np.uint64))
+
+
+def annot_struct(a: dict):
+    """cm_annot_flat over the arrays of `a` (+ the list that keeps them alive)."""
+    f = CmAnnotFlat()
+    keep = []
+    for k in ("n_iv", "n_seg", "n_tid", "n_trans", "n_genes", "n_chr", "n_bits"):
+        setattr(f, k, int(a[k]))
+    for nm, dt in [(n, np.uint32) for n in _ANNOT_U4] + list(_ANNOT_OTHER):
+        arr = np.ascontiguousarray(a[nm], dt)
+        if arr.size == 0:
+            arr = np.zeros(1, dt)
+        keep.append(arr)
+        setattr(f, nm, arr.ctypes.data)
+    return f, keep
+
+
+def write_annotation_file(path, a: dict, max_read_len: int = 300, tag: int = 0):
+    """One packed contig's flat annotation as a build-once file (cm_annot_file_write; host only)."""
+    lib = load_library()
+    f, keep = annot_struct(a)
+    r = lib.cm_annot_file_write(os.fsencode(path), C.byref(f), C.c_uint32(max_read_len), C.c_uint64(tag))
+    if r != 0:
+        raise CmGpuError(f"cm_annot_file_write({path}): status {r}")
+
+
+def read_annotation_file(path) -> dict:
+    """The arrays of a file written by write_annotation_file, as numpy copies (cm_annot_file_read; host only)."""
+    lib = load_library()
+    f = CmAnnotFlat()
+    mrl, tag, st = C.c_uint32(), C.c_uint64(), C.c_void_p()
+    r = lib.cm_annot_file_read(os.fsencode(path), C.byref(f), C.byref(mrl), C.byref(tag), C.byref(st))
+    if r != 0:
+        raise CmGpuError(f"cm_annot_file_read({path}): status {r}")
+    try:
+        a = {k: int(getattr(f, k)) for k in ("n_iv", "n_seg", "n_tid", "n_trans", "n_genes", "n_chr", "n_bits")}
+        nw = (a["n_bits"] + 63) // 64
+        counts = dict(iv_spos=a["n_iv"], iv_epos=a["n_iv"], iv_max_end=a["n_iv"], iv_min_end=a["n_iv"], iv_max_next_exon=a["n_iv"],
+                      iv_seg_off=a["n_iv"] + 1, seg_start=a["n_seg"], seg_end=a["n_seg"], seg_next_exon_beg=a["n_seg"],
+                      seg_gene_id=a["n_seg"], seg_tid_off=a["n_seg"] + 1, tid=a["n_tid"], t2s_off=a["n_trans"] + 1,
+                      gene_start=a["n_genes"], gene_end=a["n_genes"], chr_shift=a["n_chr"], trans_start_ind=a["n_trans"],
+                      chr_id=a["n_chr"], near_border=nw, intronic=nw)
+
+        def arr(nm, dt, cnt):
+            buf = (C.c_char * (cnt * np.dtype(dt).itemsize)).from_address(getattr(f, nm)) if cnt else b""
+            return np.frombuffer(buf, dt, cnt).copy()
+        for nm in _ANNOT_U4:
+            a[nm] = arr(nm, np.uint32, counts[nm])
+        for nm, dt in _ANNOT_OTHER:
+            if nm != "t2s":
+                a[nm] = arr(nm, dt, counts[nm])
+        a["t2s"] = arr("t2s", np.uint8, int(a["t2s_off"][-1]) if a["n_trans"] else 0)
+        a["max_read_len"], a["tag"] = mrl.value, tag.value
+        return a
+    finally:
+        lib.cm_annot_file_free(st)
 
 
 _lib = None
@@ -207,29 +274,38 @@ class Mapper:
 
     def load_annotation(self, contig_id, a: dict):
         """`a` holds the flat arrays named as in cm_annot_flat (annotation.flatten / RefHarness.annotation)."""
-        f = CmAnnotFlat()
-        keep = []
-
-        def put(name, dtype):
-            arr = np.ascontiguousarray(a[name], dtype)
-            if arr.size == 0:
-                arr = np.zeros(1, dtype)
-            keep.append(arr)
-            setattr(f, name, arr.ctypes.data)
-
-        f.n_iv = int(a["n_iv"]); f.n_seg = int(a["n_seg"]); f.n_tid = int(a["n_tid"])
-        f.n_trans = int(a["n_trans"]); f.n_genes = int(a["n_genes"]); f.n_chr = int(a["n_chr"])
-        f.n_bits = int(a["n_bits"])
-        for nm in ("iv_spos", "iv_epos", "iv_max_end", "iv_min_end", "iv_max_next_exon", "iv_seg_off", "seg_start",
-                   "seg_end", "seg_next_exon_beg", "seg_gene_id", "seg_tid_off", "tid", "t2s_off", "gene_start",
-                   "gene_end", "chr_shift"):
-            put(nm, np.uint32)
-        put("trans_start_ind", np.int32)
-        put("chr_id", np.int32)
-        put("t2s", np.uint8)
-        put("near_border", np.uint64)
-        put("intronic", np.uint64)
+        f, keep = annot_struct(a)
         self._chk(self.lib.cm_gpu_load_annotation(self.ctx, contig_id, C.byref(f)), "cm_gpu_load_annotation")
+
+    def load_annotation_file(self, contig_id, path, tag=0):
+        """Upload a file written by write_annotation_file (cm_gpu_load_annotation_file)."""
+        self._chk(self.lib.cm_gpu_load_annotation_file(self.ctx, contig_id, os.fsencode(path), C.c_uint64(tag)),
+                  "cm_gpu_load_annotation_file")
+
+    def extend(self, contig_id, mode, prob: dict) -> dict:
+        """TransExtension::extend_both_mates (mode 0) / extend_chain_both_sides (mode 1) per row (cm_gpu_extend_batch);
+        `prob` holds arrays named as the C arguments (lseq, rseq, llen, rlen, l_chain_len, l_rpos, l_qpos, r_*, iv_a, iv_b, dir)."""
+        keep = {k: (None if v is None else np.ascontiguousarray(v)) for k, v in prob.items()}
+        n = len(keep["llen"])
+        F = keep["l_rpos"].shape[1]
+        res = dict(lmm=np.zeros(n, MATE_DTYPE), rmm=np.zeros(n, MATE_DTYPE), ret=np.zeros(n, np.int32))
+        g = lambda k: _vp(keep.get(k))
+        self._chk(self.lib.cm_gpu_extend_batch(self.ctx, contig_id, mode, C.c_uint32(n), g("lseq"), g("rseq"),
+                                               C.c_uint32(keep["lseq"].shape[1]), g("llen"), g("rlen"), C.c_uint32(F), g("l_chain_len"),
+                                               g("l_rpos"), g("l_qpos"), g("r_chain_len"), g("r_rpos"), g("r_qpos"), g("iv_a"), g("iv_b"),
+                                               g("dir"), _vp(res["lmm"]), _vp(res["rmm"]), _vp(res["ret"])), "cm_gpu_extend_batch")
+        return res
+
+    def annot_lookup(self, contig_id, pos, mlen, rlen) -> dict:
+        """GTFParser look-ups per position (cm_gpu_annot_lookup_batch)."""
+        pos = np.ascontiguousarray(pos, np.uint32)
+        n = len(pos)
+        out = dict(ub=np.zeros(n, np.uint32), max_end=np.zeros(n, np.uint32), ol_iv=np.zeros(n, np.int32), loc_iv=np.zeros(n, np.int32),
+                   loc_ind=np.zeros(n, np.int32), shift_idx=np.zeros(n, np.int32), intronic=np.zeros(n, np.uint8))
+        self._chk(self.lib.cm_gpu_annot_lookup_batch(self.ctx, contig_id, C.c_uint32(n), _vp(pos), C.c_uint32(mlen), C.c_uint32(rlen),
+                                                     *[_vp(out[k]) for k in ("ub", "max_end", "ol_iv", "loc_iv", "loc_ind", "shift_idx", "intronic")]),
+                  "cm_gpu_annot_lookup_batch")
+        return out
 
     # ---- stages ---------------------------------------------------------------------------
     def split_match_hash(self, contig_id, seqs, lens=None) -> dict:

@@ -1196,6 +1196,7 @@ extern "C" int cm_gpu_seed_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, con
 #include "cm_host_pipeline.cuh"
 #include "cm_index_io.cuh"
 #include "cm_noalloc.cuh"
+#include "cm_annot_io.cuh"
 
 // the hot-path kernels, loaded on the current device (cudaFuncGetAttributes forces the lazy load)
 static void preload_kernels() {

@@ -591,3 +591,97 @@ extern "C" int cm_gpu_map_rounds_pe(cm_gpu_ctx *ctx, int first_contig, int n_con
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     return CM_OK;
 }
+
+extern "C" int cm_gpu_annot_lookup_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const uint32_t *pos, uint32_t mlen, uint32_t rlen,
+                                         uint32_t *ub, uint32_t *max_end, int32_t *ol_iv, int32_t *loc_iv, int32_t *loc_ind,
+                                         int32_t *shift_idx, uint8_t *intronic) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n && (!pos || !ub || !max_end || !ol_iv || !loc_iv || !loc_ind || !shift_idx || !intronic)) return fail(ctx, CM_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->device);
+    DevView v;
+    int r = make_view(ctx, contig_id, true, v);
+    if (r != CM_OK) return r;
+    if (!n) return CM_OK;
+    cudaStream_t st = ctx->stream;
+    for (int k = 0; k < 8; k++) ENSURE(ctx, ctx->scratch[k], (size_t) n * 4);
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->scratch[0].p, pos, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    k_annot_lookup<<<grid_for(n, 256), 256, 0, st>>>(v, n, (const uint32_t *) ctx->scratch[0].p, mlen, rlen, (uint32_t *) ctx->scratch[1].p,
+                                                    (uint32_t *) ctx->scratch[2].p, (int32_t *) ctx->scratch[3].p, (int32_t *) ctx->scratch[4].p,
+                                                    (int32_t *) ctx->scratch[5].p, (int32_t *) ctx->scratch[6].p, (uint8_t *) ctx->scratch[7].p);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    if ((r = fetch(ctx, ub, ctx->scratch[1].p, n)) != CM_OK || (r = fetch(ctx, max_end, ctx->scratch[2].p, n)) != CM_OK ||
+        (r = fetch(ctx, ol_iv, ctx->scratch[3].p, n)) != CM_OK || (r = fetch(ctx, loc_iv, ctx->scratch[4].p, n)) != CM_OK ||
+        (r = fetch(ctx, loc_ind, ctx->scratch[5].p, n)) != CM_OK || (r = fetch(ctx, shift_idx, ctx->scratch[6].p, n)) != CM_OK ||
+        (r = fetch(ctx, intronic, ctx->scratch[7].p, n)) != CM_OK)
+        return r;
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_extend_batch(cm_gpu_ctx *ctx, int contig_id, int mode, uint32_t n, const char *lseq, const char *rseq, uint32_t stride,
+                                   const uint16_t *llen, const uint16_t *rlen, uint32_t frag_slots, const uint32_t *l_chain_len,
+                                   const uint32_t *l_rpos, const int32_t *l_qpos, const uint32_t *r_chain_len, const uint32_t *r_rpos,
+                                   const int32_t *r_qpos, const int32_t *iv_a, const int32_t *iv_b, const int32_t *dir, cm_mate *lmm,
+                                   cm_mate *rmm, int32_t *ret) {
+    if (!ctx) return CM_ERR_ARG;
+    if (mode != 0 && mode != 1) return fail(ctx, CM_ERR_ARG, "mode must be 0 (extend_both_mates) or 1 (extend_chain_both_sides)");
+    if (!n) return CM_OK;
+    const bool both = mode == 0;
+    if (!lseq || !llen || !l_chain_len || !l_rpos || !l_qpos || !lmm || !ret || !frag_slots || frag_slots > CM_MAX_SEEDS ||
+        (both && (!rseq || !rlen || !r_chain_len || !r_rpos || !r_qpos || !iv_a || !iv_b || !rmm)) || (!both && !dir))
+        return fail(ctx, CM_ERR_ARG, "null or out-of-range argument");
+    const uint32_t F = frag_slots;
+    for (uint32_t i = 0; i < n; i++) {
+        if (llen[i] > stride || (both && rlen[i] > stride) || llen[i] > ctx->p.max_read_len) return fail(ctx, CM_ERR_ARG, "problem %u: read longer than stride", i);
+        if (l_chain_len[i] > F || (both && r_chain_len[i] > F)) return fail(ctx, CM_ERR_ARG, "problem %u: chain longer than frag_slots", i);
+    }
+    cudaSetDevice(ctx->device);
+    DevView v;
+    int r = make_view(ctx, contig_id, true, v);
+    if (r != CM_OK) return r;
+    cudaStream_t st = ctx->stream;
+    // frags as FragDev {rpos, qpos} pairs
+    std::vector<FragDev> hl((size_t) n * F), hr(both ? (size_t) n * F : 0);
+    for (size_t k = 0; k < (size_t) n * F; k++) {
+        hl[k].rpos = l_rpos[k]; hl[k].qpos = l_qpos[k];
+        if (both) { hr[k].rpos = r_rpos[k]; hr[k].qpos = r_qpos[k]; }
+    }
+    const size_t sb = (size_t) n * stride, fb = (size_t) n * F * sizeof(FragDev);
+    DevBuf *S = ctx->scratch;
+    ENSURE(ctx, S[0], 2 * sb + 64);
+    ENSURE(ctx, S[1], (size_t) n * 4);                    // llen | rlen (u16 each)
+    ENSURE(ctx, S[2], 2 * fb);
+    ENSURE(ctx, S[3], (size_t) n * 8);                    // chain lengths l | r
+    ENSURE(ctx, S[4], (size_t) n * 12);                   // iv_a | iv_b | dir
+    ENSURE(ctx, S[5], (size_t) n * 2 * sizeof(cm_mate));
+    ENSURE(ctx, S[6], (size_t) n * 4);
+    uint8_t *d_seq = (uint8_t *) S[0].p;
+    uint16_t *d_len = (uint16_t *) S[1].p;
+    FragDev *d_fr = (FragDev *) S[2].p;
+    uint32_t *d_cl = (uint32_t *) S[3].p;
+    int32_t *d_iv = (int32_t *) S[4].p;
+    cm_mate *d_mm = (cm_mate *) S[5].p;
+    CUDA_TRY(ctx, cudaMemsetAsync(S[4].p, 0, (size_t) n * 12, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_seq, lseq, sb, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_len, llen, (size_t) n * 2, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_fr, hl.data(), fb, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_cl, l_chain_len, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    if (both) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_seq + sb, rseq, sb, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_len + n, rlen, (size_t) n * 2, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_fr + (size_t) n * F, hr.data(), fb, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_cl + n, r_chain_len, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_iv, iv_a, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_iv + n, iv_b, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    } else {
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_iv + 2 * (size_t) n, dir, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    }
+    k_extend<<<grid_for(n, 128), 128, 0, st>>>(v, mode, n, d_seq, d_seq + sb, stride, d_len, d_len + n, (int) F, d_cl, d_fr, d_cl + n,
+                                              d_fr + (size_t) n * F, d_iv, d_iv + n, d_iv + 2 * (size_t) n, d_mm, d_mm + n, (int32_t *) S[6].p);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    if ((r = fetch(ctx, lmm, d_mm, n)) != CM_OK || (both && (r = fetch(ctx, rmm, d_mm + n, n)) != CM_OK) || (r = fetch(ctx, ret, S[6].p, n)) != CM_OK) return r;
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return CM_OK;
+}

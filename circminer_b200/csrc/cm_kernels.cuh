@@ -443,3 +443,65 @@ __global__ void __launch_bounds__(256) k_round_compact(const __grid_constant__ c
         ids_n[j] = ids ? ids[k] : k;
     }
 }
+
+// ------------------------------------------------------------------------------------------
+// Stage-level parity entry for the annotation look-ups the chaining / extension / classification code makes
+// (GTFParser::get_upper_bound src/gene_annotation.h:121, get_location_overlap_ind src/gene_annotation.cpp:555,
+// get_shift :451): one thread per position.
+// ------------------------------------------------------------------------------------------
+__global__ void k_annot_lookup(const __grid_constant__ DevView v, uint32_t n, const uint32_t *__restrict__ pos, uint32_t mlen, uint32_t rlen,
+                               uint32_t *__restrict__ ub, uint32_t *__restrict__ max_end, int32_t *__restrict__ ol_iv,
+                               int32_t *__restrict__ loc_iv, int32_t *__restrict__ loc_ind, int32_t *__restrict__ shift_idx,
+                               uint8_t *__restrict__ intronic) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t p = pos[i];
+    uint32_t me = 0;
+    int ol = -1;
+    ub[i] = cm_upper_bound(v.a, v.p, p, mlen, rlen, me, ol);
+    max_end[i] = me;
+    ol_iv[i] = ol;
+    int ind = -1;
+    loc_iv[i] = cm_location_overlap_ind(v.a, p, ind);
+    loc_ind[i] = ind;
+    shift_idx[i] = cm_get_shift(v.a, p);
+    intronic[i] = cm_bit(v.a.intronic, v.a.n_bits, p) ? 1 : 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// Stage-level parity entry for the extension (TransExtension::extend_both_mates src/extend.cpp:37-125,
+// extend_chain_both_sides :131-213): one thread per problem, chains given by the caller, every DP inline.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cm_mate_export(const MateD &m, cm_mate &o) {
+    o.spos = m.spos; o.epos = m.epos; o.qspos = m.qspos; o.qepos = m.qepos; o.matched_len = m.matched_len;
+    o.left_ed = m.left_ed; o.middle_ed = m.middle_ed; o.right_ed = m.right_ed; o.sclen_left = m.sclen_left; o.sclen_right = m.sclen_right;
+    o.dir = m.dir; o.type = m.type;
+    o.is_concord = m.is_concord; o.left_ok = m.left_ok; o.right_ok = m.right_ok; o.pad_ = 0;
+}
+__global__ void __launch_bounds__(128) k_extend(const __grid_constant__ DevView v, int mode, uint32_t n, const uint8_t *__restrict__ lseq,
+                                                const uint8_t *__restrict__ rseq, uint32_t stride, const uint16_t *__restrict__ llen,
+                                                const uint16_t *__restrict__ rlen, int F, const uint32_t *__restrict__ lcl,
+                                                const FragDev *__restrict__ lfr, const uint32_t *__restrict__ rcl, const FragDev *__restrict__ rfr,
+                                                const int32_t *__restrict__ iv_a, const int32_t *__restrict__ iv_b, const int32_t *__restrict__ dir,
+                                                cm_mate *__restrict__ lmm, cm_mate *__restrict__ rmm, int32_t *__restrict__ ret) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    ExtCtx x;
+    ext_ctx_init(x, &v);
+    ChainView lc, rc;
+    lc.frags = lfr + (size_t) i * F; lc.chain_len = lcl[i]; lc.aux = nullptr; lc.spec = nullptr;
+    MateD a, b;
+    mate_init(a, v.p);
+    mate_init(b, v.p);
+    if (mode == 0) {
+        rc.frags = rfr + (size_t) i * F; rc.chain_len = rcl[i]; rc.aux = nullptr; rc.spec = nullptr;
+        TidSet ts;
+        ts.iv_a = iv_a[i];
+        ts.iv_b = iv_b[i];
+        ret[i] = cm_extend_both_mates(x, lc, rc, ts, lseq + (size_t) i * stride, rseq + (size_t) i * stride, 1, 1, llen[i], rlen[i], a, b) ? 1 : 0;
+        cm_mate_export(b, rmm[i]);
+    } else {
+        ret[i] = cm_extend_chain_both_sides(x, lc, lseq + (size_t) i * stride, llen[i], a, dir[i]);
+    }
+    cm_mate_export(a, lmm[i]);
+}

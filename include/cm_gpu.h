@@ -194,6 +194,16 @@ int cm_gpu_read_bucket(cm_gpu_ctx *ctx, int contig_id, uint32_t hv, uint32_t cap
 /* after GTFParser::load_gtf (src/gene_annotation.cpp:191) */
 int cm_gpu_load_annotation(cm_gpu_ctx *ctx, int contig_id, const cm_annot_flat *annot);
 
+/* The flattened annotation as a build-once artefact: GTFParser::load_gtf (src/gene_annotation.cpp:191-399)
+ * rebuilds its tables and sets the 1.3-Gbit masks bit by bit in every run; a host that has flattened them once writes one
+ * file per packed contig and later runs upload it as it is.  `tag` is the caller's validity stamp (e.g. GTF size ^ mtime):
+ * cm_gpu_load_annotation_file refuses a file with another tag or another max_read_len (near_border_bs depends on -l,
+ * src/gene_annotation.cpp:273-278).  cm_annot_file_* are host-only (no device needed). */
+int cm_annot_file_write(const char *path, const cm_annot_flat *annot, uint32_t max_read_len, uint64_t tag);
+int cm_annot_file_read(const char *path, cm_annot_flat *out, uint32_t *max_read_len, uint64_t *tag, void **storage);
+void cm_annot_file_free(void *storage);
+int cm_gpu_load_annotation_file(cm_gpu_ctx *ctx, int contig_id, const char *path, uint64_t expect_tag);
+
 /* ---- stage-level batch entries (parity tests) -------------------------- */
 /* Reads are ASCII, n strands, fixed row stride `stride` bytes, length len[i].
  * The device derives the reverse complement exactly as
@@ -214,6 +224,38 @@ int cm_gpu_seed_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *se
 int cm_gpu_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride,
                        const uint16_t *len, int32_t *chain_count, int32_t *high_hits, float *score,
                        uint32_t *chain_len, uint32_t *frag_rpos, int32_t *frag_qpos);
+
+/* The annotation look-ups of the hot loops, one position per row (contig-relative, 1-based), for parity with GTFParser:
+ *   ub, max_end, ol_iv   GTFParser::get_upper_bound(pos, mlen, rlen, max_end, ol_exons) (src/gene_annotation.h:121-131 ->
+ *                        get_upper_bound_lookup src/gene_annotation.cpp:464-533); ol_iv = index of ol_exons in
+ *                        FlatIntervalTree::disjoint_intervals, -1 for NULL
+ *   loc_iv, loc_ind      get_location_overlap_ind(pos, false, ind) (src/gene_annotation.cpp:555-568)
+ *   shift_idx            index into con2chr[contig] of get_shift(contig, pos) (:451-457)
+ *   intronic             intronic_bs[contig][pos] (src/common.h:118) */
+int cm_gpu_annot_lookup_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const uint32_t *pos, uint32_t mlen, uint32_t rlen,
+                              uint32_t *ub, uint32_t *max_end, int32_t *ol_iv, int32_t *loc_iv, int32_t *loc_ind,
+                              int32_t *shift_idx, uint8_t *intronic);
+
+/* POD image of the MatchedMate fields the extension writes (src/common.h:260-307) */
+typedef struct cm_mate {
+    uint32_t spos, epos, qspos, qepos, matched_len;
+    int32_t left_ed, middle_ed, right_ed, sclen_left, sclen_right, dir, type;
+    uint8_t is_concord, left_ok, right_ok, pad_;
+} cm_mate;
+
+/* The extension stage, one problem per row (src/extend.h:66-70):
+ *   mode 0: bool TransExtension::extend_both_mates(lch, rch, common_tid, lseq, rseq, 1, 1, lseq_len, rseq_len, lmm, rmm)
+ *           (src/extend.cpp:37-125); common_tid = same_transcript(interval iv_a, interval iv_b) (src/utils.cpp:335-354), empty when
+ *           iv_a < 0; ret = the return value
+ *   mode 1: int extend_chain_both_sides(lch, lseq, lseq_len, lmm, dir) (:131-213); ret = the returned type; the r* arguments,
+ *           iv_a, iv_b and rmm are unused (may be NULL)
+ * Chains are given as chain_len + fragments (rpos, qpos) [n][frag_slots] (fragment length is always kmer); the mates start
+ * from MatchedMate() with the never-initialised fields at 0. */
+int cm_gpu_extend_batch(cm_gpu_ctx *ctx, int contig_id, int mode, uint32_t n, const char *lseq, const char *rseq, uint32_t stride,
+                        const uint16_t *llen, const uint16_t *rlen, uint32_t frag_slots, const uint32_t *l_chain_len,
+                        const uint32_t *l_rpos, const int32_t *l_qpos, const uint32_t *r_chain_len, const uint32_t *r_rpos,
+                        const int32_t *r_qpos, const int32_t *iv_a, const int32_t *iv_b, const int32_t *dir, cm_mate *lmm,
+                        cm_mate *rmm, int32_t *ret);
 
 /* Alignment kernels, one problem per row (src/align.h:165-176):
  *   kind 0: DropAlignment::local_alignment_right_sc  (src/align.cpp:669)

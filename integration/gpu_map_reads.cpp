@@ -14,6 +14,8 @@
 #undef protected
 
 #include <algorithm>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
@@ -108,8 +110,57 @@ void from_pod(const cm_mread *m, MatchedRead *r) {
 #include "host_feed.h"
 namespace {
 
-// GTFParser tables of the current contig as the flat arrays of cm_annot_flat
+// Validity stamp of an annotation cache file: the GTF and the packed reference's layout it was flattened from.
+uint64_t annot_tag() {
+    uint64_t h = 1469598103934665603ull;
+    auto mix = [&](uint64_t v) { h = (h ^ v) * 1099511628211ull; };
+    struct stat st;
+    if (stat(gtfFilename, &st) == 0) { mix((uint64_t) st.st_size); mix((uint64_t) st.st_mtime); }
+    for (auto &per_contig : gtf_parser.con2chr)
+        for (auto &cc : per_contig) {
+            for (char ch : cc.contig) mix((unsigned char) ch);
+            mix(cc.shift);
+        }
+    mix((uint64_t) kmer);
+    return h;
+}
+std::string annot_cache_path(int c) {
+    const char *dir = getenv("CM_GPU_ANNOT_CACHE");   // "0": no cache; a directory: files go there; unset: next to the GTF
+    if (dir && !strcmp(dir, "0")) return "";
+    std::string base = gtfFilename;
+    if (dir && *dir) {
+        const size_t slash = base.find_last_of('/');
+        base = std::string(dir) + "/" + (slash == std::string::npos ? base : base.substr(slash + 1));
+    }
+    return base + ".cmannot." + std::to_string(c + 1) + ".l" + std::to_string(maxReadLength);
+}
+
+// GTFParser tables of the current contig as the flat arrays of cm_annot_flat.  The flattening (two 1.3-Gbit masks read bit by
+// bit out of std::bitset) is done once per (GTF, packed reference, -l): the result is kept as a file beside the GTF
+// (cm_annot_file_write) and later runs upload that file as it is.
 void upload_annotation(int c) {
+    std::vector<int32_t> chr_now;   // this run's chromosome-table indices of the contig's chromosomes (registers the names)
+    for (auto &cc : gtf_parser.con2chr[c]) chr_now.push_back(chr_index(cc.contig));
+    const std::string cache = annot_cache_path(c);
+    const uint64_t tag = annot_tag();
+    if (!cache.empty()) {
+        cm_annot_flat F;
+        uint32_t mrl = 0;
+        uint64_t ftag = 0;
+        void *st = nullptr;
+        if (cm_annot_file_read(cache.c_str(), &F, &mrl, &ftag, &st) == CM_OK) {
+            bool ok = (int) mrl == maxReadLength && ftag == tag && F.n_chr == chr_now.size() && F.n_bits == (uint64_t) _ih_refGenLen + 2;
+            for (size_t i = 0; ok && i < chr_now.size(); i++) ok = F.chr_id[i] == chr_now[i];
+            if (ok) {
+                for (cm_gpu_ctx *root : g_roots)
+                    if (cm_gpu_load_annotation(root, c, &F) != CM_OK) { g_ctx = root; die("cm_gpu_load_annotation"); }
+                cm_annot_file_free(st);
+                if (g_verbose) fprintf(stderr, "circminer_gpu: annotation of contig %d from %s\n", c, cache.c_str());
+                return;
+            }
+            cm_annot_file_free(st);
+        }
+    }
     FlatIntervalTree<UniqSeg> &T = gtf_parser.exons_int_map[c];
     const size_t n_iv = T.disjoint_intervals.size();
     std::vector<uint32_t> iv_spos(n_iv), iv_epos(n_iv), iv_max_end(n_iv), iv_min_end(n_iv), iv_next(n_iv), iv_seg_off(n_iv + 1);
@@ -185,6 +236,13 @@ void upload_annotation(int c) {
     A.near_border = nb.data(); A.intronic = in.data();
     for (cm_gpu_ctx *root : g_roots)
         if (cm_gpu_load_annotation(root, c, &A) != CM_OK) { g_ctx = root; die("cm_gpu_load_annotation"); }
+    if (!cache.empty()) {   // written beside the mapping (to a temporary name first: a reader never sees half a file)
+        const std::string tmp = cache + ".tmp" + std::to_string((long) getpid());
+        const uint32_t mrl = (uint32_t) maxReadLength;
+        const bool ok = cm_annot_file_write(tmp.c_str(), &A, mrl, tag) == CM_OK && rename(tmp.c_str(), cache.c_str()) == 0;
+        if (!ok) remove(tmp.c_str());
+        if (g_verbose) fprintf(stderr, "circminer_gpu: annotation of contig %d %s %s\n", c, ok ? "written to" : "could not be written to", cache.c_str());
+    }
 }
 
 // Devices the mapping round uses: CM_GPU_DEVICES = "all" or a comma list ("0,1,2,3"; a device may be named twice, which gives

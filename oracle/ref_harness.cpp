@@ -264,6 +264,73 @@ int cmref_annot_masks(uint64_t n_bits, uint64_t *near_border, uint64_t *intronic
     return 0;
 }
 
+// the look-ups of cm_gpu_annot_lookup_batch by the reference's own GTFParser (current contigNum)
+int cmref_annot_lookup(uint32_t n, const uint32_t *pos, uint32_t mlen, uint32_t rlen, uint32_t *ub, uint32_t *max_end, int32_t *ol_iv,
+                       int32_t *loc_iv, int32_t *loc_ind, int32_t *shift_idx, uint8_t *intronic) {
+    FlatIntervalTree<UniqSeg> &T = gtf_parser.exons_int_map[contigNum];
+    const IntervalInfo<UniqSeg> *base = T.disjoint_intervals.data();
+    for (uint32_t i = 0; i < n; i++) {
+        const IntervalInfo<UniqSeg> *ol = NULL;
+        uint32_t me = 0;
+        ub[i] = gtf_parser.get_upper_bound(pos[i], mlen, rlen, me, ol);
+        max_end[i] = me;
+        ol_iv[i] = ol ? (int32_t) (ol - base) : -1;
+        int ind = -1;
+        const IntervalInfo<UniqSeg> *lo = gtf_parser.get_location_overlap_ind(pos[i], false, ind);
+        loc_iv[i] = lo ? (int32_t) (lo - base) : -1;
+        loc_ind[i] = ind;
+        ConShift cs = gtf_parser.get_shift(contigNum, pos[i]);
+        shift_idx[i] = -1;
+        for (size_t k = 0; k < gtf_parser.con2chr[contigNum].size(); k++)
+            if (gtf_parser.con2chr[contigNum][k].shift == cs.shift && gtf_parser.con2chr[contigNum][k].contig == cs.contig) shift_idx[i] = (int32_t) k;
+        intronic[i] = intronic_bs[contigNum][pos[i]] ? 1 : 0;
+    }
+    return 0;
+}
+
+// cm_gpu_extend_batch by the reference's own TransExtension (thread 0's, created by FilterRead::init)
+static void mate_export(const MatchedMate &m, cm_mate *o) {
+    o->spos = m.spos; o->epos = m.epos; o->qspos = m.qspos; o->qepos = m.qepos; o->matched_len = m.matched_len;
+    o->left_ed = m.left_ed; o->middle_ed = m.middle_ed; o->right_ed = m.right_ed; o->sclen_left = m.sclen_left; o->sclen_right = m.sclen_right;
+    o->dir = m.dir; o->type = m.type;
+    o->is_concord = m.is_concord; o->left_ok = m.left_ok; o->right_ok = m.right_ok; o->pad_ = 0;
+}
+static void mate_fresh(MatchedMate &m) {   // MatchedMate() leaves these unset; the device starts them at 0
+    m.spos = m.epos = m.qspos = m.qepos = 0;
+    m.matched_len = 0;
+    m.dir = 0;
+    m.is_concord = false;
+}
+int cmref_extend(int mode, uint32_t n, const char *lseq, const char *rseq, uint32_t stride, const uint16_t *llen, const uint16_t *rlen,
+                 uint32_t F, const uint32_t *lcl, const uint32_t *lrp, const int32_t *lqp, const uint32_t *rcl, const uint32_t *rrp,
+                 const int32_t *rqp, const int32_t *iv_a, const int32_t *iv_b, const int32_t *dir, cm_mate *lmm, cm_mate *rmm, int32_t *ret) {
+    std::vector<fragment_t> lf(F), rf(F);
+    std::vector<char> ls(stride + 8), rs(stride + 8);
+    FlatIntervalTree<UniqSeg> &T = gtf_parser.exons_int_map[contigNum];
+    for (uint32_t i = 0; i < n; i++) {
+        chain_t lc, rc;
+        lc.frags = lf.data(); lc.chain_len = lcl[i]; lc.score = 0;
+        for (uint32_t f = 0; f < lcl[i]; f++) { lf[f].rpos = lrp[(size_t) i * F + f]; lf[f].qpos = lqp[(size_t) i * F + f]; lf[f].len = kmer; }
+        memcpy(ls.data(), lseq + (size_t) i * stride, llen[i]); ls[llen[i]] = 0;
+        MatchedMate a, b;
+        mate_fresh(a);
+        mate_fresh(b);
+        if (mode == 0) {
+            rc.frags = rf.data(); rc.chain_len = rcl[i]; rc.score = 0;
+            for (uint32_t f = 0; f < rcl[i]; f++) { rf[f].rpos = rrp[(size_t) i * F + f]; rf[f].qpos = rqp[(size_t) i * F + f]; rf[f].len = kmer; }
+            memcpy(rs.data(), rseq + (size_t) i * stride, rlen[i]); rs[rlen[i]] = 0;
+            std::vector<uint32_t> common_tid;
+            if (iv_a[i] >= 0 && iv_b[i] >= 0) same_transcript(&T.disjoint_intervals[iv_a[i]], &T.disjoint_intervals[iv_b[i]], common_tid);
+            ret[i] = filter_read.extension[0].extend_both_mates(lc, rc, common_tid, ls.data(), rs.data(), 1, 1, llen[i], rlen[i], a, b) ? 1 : 0;
+            mate_export(b, &rmm[i]);
+        } else {
+            ret[i] = filter_read.extension[0].extend_chain_both_sides(lc, ls.data(), llen[i], a, dir[i]);
+        }
+        mate_export(a, &lmm[i]);
+    }
+    return 0;
+}
+
 // ---- stage dumps ---------------------------------------------------------------------
 // GenomeSeeder::split_match_hash on one strand; arrays of max_seg_cnt
 int cmref_seed(const char *seq, int len, int32_t *qpos, uint32_t *frag_count, uint8_t *has_frags,

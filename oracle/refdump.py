@@ -74,6 +74,49 @@ def align_problems(seed: int, n: int, stride: int = 200):
     return out
 
 
+def extend_problems(h, s1, s2, lens):
+    """Problems for the extension stage and the reference's answers: for every pair whose R1 (forward) and R2 (reverse
+    complement) both chain on the current contig, up to two chain pairs (best x best, second x second), left = the chain
+    that starts first; common_tid from the exon intervals under the two chain starts.  Mode 1: the best chain of every R1."""
+    comp = np.zeros(256, np.uint8)
+    for x, y in zip(b"ACGTNacgtn", b"TGCANTGCAN"):
+        comp[x] = y
+    n, L = s1.shape
+    rc2 = np.ascontiguousarray(comp[s2[:, ::-1]])
+    c1, c2 = h.chain(s1, lens), h.chain(rc2, lens)
+    F = c1["frag_rpos"].shape[2]
+    rows = []
+    for k in range(2):
+        ok = np.nonzero((c1["chain_count"] > k) & (c2["chain_count"] > k))[0]
+        rows += [(i, k) for i in ok]
+    idx = np.array([r[0] for r in rows], np.int64)
+    kk = np.array([r[1] for r in rows], np.int64)
+    a_first = c1["frag_rpos"][idx, kk, 0] <= c2["frag_rpos"][idx, kk, 0]
+
+    def pick(x1, x2):
+        return np.where(a_first.reshape((-1,) + (1,) * (x1.ndim - 1)), x1, x2)
+    prob = dict(lseq=pick(s1[idx], rc2[idx]), rseq=pick(rc2[idx], s1[idx]), llen=lens[idx], rlen=lens[idx],
+                l_chain_len=pick(c1["chain_len"][idx, kk], c2["chain_len"][idx, kk]), r_chain_len=pick(c2["chain_len"][idx, kk], c1["chain_len"][idx, kk]),
+                l_rpos=pick(c1["frag_rpos"][idx, kk], c2["frag_rpos"][idx, kk]), r_rpos=pick(c2["frag_rpos"][idx, kk], c1["frag_rpos"][idx, kk]),
+                l_qpos=pick(c1["frag_qpos"][idx, kk], c2["frag_qpos"][idx, kk]), r_qpos=pick(c2["frag_qpos"][idx, kk], c1["frag_qpos"][idx, kk]))
+    iv_l = h.annot_lookup(prob["l_rpos"][:, 0], h.kmer, 100)["loc_iv"]
+    iv_r = h.annot_lookup(prob["r_rpos"][:, 0], h.kmer, 100)["loc_iv"]
+    both = (iv_l >= 0) & (iv_r >= 0)
+    prob["iv_a"] = np.where(both, iv_l, -1).astype(np.int32)
+    prob["iv_b"] = np.where(both, iv_r, -1).astype(np.int32)
+    prob["dir"] = None
+    out = {("p0_" + k): v for k, v in prob.items() if v is not None}
+    out.update({("r0_" + k): v for k, v in h.extend(0, prob).items()})
+    one = np.nonzero(c1["chain_count"] > 0)[0]
+    p1 = dict(lseq=s1[one], rseq=None, llen=lens[one], rlen=None, l_chain_len=c1["chain_len"][one, 0], l_rpos=c1["frag_rpos"][one, 0],
+              l_qpos=c1["frag_qpos"][one, 0], r_chain_len=None, r_rpos=None, r_qpos=None, iv_a=None, iv_b=None,
+              dir=np.where(np.arange(len(one)) % 2 == 0, 1, -1).astype(np.int32))
+    out.update({("p1_" + k): v for k, v in p1.items() if v is not None})
+    r1 = h.extend(1, p1)
+    out["r1_lmm"], out["r1_ret"] = r1["lmm"], r1["ret"]
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", default="T0")
@@ -85,6 +128,8 @@ def main():
     ap.add_argument("--band", type=int, default=3)
     ap.add_argument("--se", action="store_true")
     ap.add_argument("--compact", action="store_true", help="build the reference index with -m (counts only)")
+    ap.add_argument("--lookups", type=int, default=0, help="random positions per contig for the GTFParser look-up dump")
+    ap.add_argument("--extend", action="store_true", help="extension-stage dump: extend_both_mates / extend_chain_both_sides on chain pairs")
     ap.add_argument("--align", type=int, default=0, help="random alignment problems per kind")
     ap.add_argument("--no-stage-dumps", action="store_true", help="only process_read results (large workloads)")
     ap.add_argument("--out", required=True)
@@ -124,6 +169,23 @@ def main():
                 cd = h.chain(s, lens)
                 for k, v in cd.items():
                     out[f"c{c}_chain_{nm}_{k}"] = v
+        if a.lookups:
+            # GTFParser look-ups on random positions and on every position within 3 bases of an interval border
+            ann = h.annotation()
+            rng = np.random.default_rng(1000 + c)
+            ref_len = h.index_pointers()[4]
+            edges = np.concatenate([ann["iv_spos"][:ann["n_iv"]].astype(np.int64), ann["iv_epos"][:ann["n_iv"]].astype(np.int64)])
+            edges = edges[edges < ref_len]
+            near = (edges[:, None] + np.arange(-3, 4)[None, :]).ravel()
+            pos = np.concatenate([rng.integers(1, ref_len - 400, size=a.lookups), near])
+            pos = np.unique(pos[(pos >= 1) & (pos < ref_len - 400)]).astype(np.uint32)
+            out[f"c{c}_lookup_pos"] = pos
+            for tag, (ml, rl) in (("a", (h.kmer, 130)), ("b", (h.kmer, 30))):
+                for k, v in h.annot_lookup(pos, ml, rl).items():
+                    out[f"c{c}_lookup_{tag}_{k}"] = v
+        if a.extend:
+            for k, v in extend_problems(h, s1, s2, lens).items():
+                out[f"c{c}_ext_{k}"] = v
         if a.se:
             out[f"c{c}_se_state"] = h.process_se(s1, lens)
         mr, st = h.process_pe(s1, s2, lens, lens, mr)

@@ -37,6 +37,12 @@ MREAD_DTYPE = np.dtype([
 assert MREAD_DTYPE.itemsize == 76
 
 
+MATE_DTYPE = np.dtype([("spos", "<u4"), ("epos", "<u4"), ("qspos", "<u4"), ("qepos", "<u4"), ("matched_len", "<u4"),
+                       ("left_ed", "<i4"), ("middle_ed", "<i4"), ("right_ed", "<i4"), ("sclen_left", "<i4"), ("sclen_right", "<i4"),
+                       ("dir", "<i4"), ("type", "<i4"), ("is_concord", "u1"), ("left_ok", "u1"), ("right_ok", "u1"), ("pad_", "u1")])
+assert MATE_DTYPE.itemsize == 52
+
+
 def fresh_mreads(n: int, max_ed: int = 4) -> np.ndarray:
     """MatchedRead::MatchedRead(void), /root/reference/src/common.cpp:268-271 (unset fields 0)."""
     m = np.zeros(n, MREAD_DTYPE)
@@ -144,6 +150,30 @@ class RefHarness:
                        ("chr_shift", n_chr), ("chr_id", n_chr)):
             a[k] = a[k][:cnt]
         return a
+
+    def annot_lookup(self, pos, mlen, rlen) -> dict:
+        pos = np.ascontiguousarray(pos, np.uint32)
+        n = len(pos)
+        out = dict(ub=np.zeros(n, np.uint32), max_end=np.zeros(n, np.uint32), ol_iv=np.zeros(n, np.int32), loc_iv=np.zeros(n, np.int32),
+                   loc_ind=np.zeros(n, np.int32), shift_idx=np.zeros(n, np.int32), intronic=np.zeros(n, np.uint8))
+        self.lib.cmref_annot_lookup(C.c_uint32(n), pos.ctypes.data_as(C.c_void_p), C.c_uint32(mlen), C.c_uint32(rlen),
+                                    *[out[k].ctypes.data_as(C.c_void_p) for k in
+                                      ("ub", "max_end", "ol_iv", "loc_iv", "loc_ind", "shift_idx", "intronic")])
+        return out
+
+    def extend(self, mode, prob: dict) -> dict:
+        """TransExtension::extend_both_mates (mode 0) / extend_chain_both_sides (mode 1) on the problems of `prob`
+        (arrays named as the arguments of cm_gpu_extend_batch)."""
+        n = len(prob["llen"])
+        F = prob["l_rpos"].shape[1]
+        res = dict(lmm=np.zeros(n, MATE_DTYPE), rmm=np.zeros(n, MATE_DTYPE), ret=np.zeros(n, np.int32))
+        vp = lambda a: None if a is None else np.ascontiguousarray(a).ctypes.data_as(C.c_void_p)
+        keep = {k: (None if v is None else np.ascontiguousarray(v)) for k, v in prob.items()}
+        g = lambda k: None if keep.get(k) is None else keep[k].ctypes.data_as(C.c_void_p)
+        self.lib.cmref_extend(mode, C.c_uint32(n), g("lseq"), g("rseq"), C.c_uint32(keep["lseq"].shape[1]), g("llen"), g("rlen"),
+                              C.c_uint32(F), g("l_chain_len"), g("l_rpos"), g("l_qpos"), g("r_chain_len"), g("r_rpos"), g("r_qpos"),
+                              g("iv_a"), g("iv_b"), g("dir"), vp(res["lmm"]), vp(res["rmm"]), vp(res["ret"]))
+        return res
 
     def seed(self, seqs: np.ndarray, lens: np.ndarray) -> dict:
         n, S = len(lens), self.S

@@ -42,6 +42,9 @@ const char *cm_gpu_last_error(const cm_gpu_ctx *) { return "mock"; }
 int cm_gpu_load_contig(cm_gpu_ctx *, int, const void *const *, const void *, uint64_t, const uint64_t *, uint32_t) { return CM_OK; }
 int cm_gpu_build_contig_packed(cm_gpu_ctx *, int, const uint64_t *, uint32_t) { return CM_OK; }
 int cm_gpu_load_annotation(cm_gpu_ctx *, int, const cm_annot_flat *) { return CM_OK; }
+int cm_annot_file_write(const char *, const cm_annot_flat *, uint32_t, uint64_t) { return CM_ERR_ARG; }
+int cm_annot_file_read(const char *, cm_annot_flat *, uint32_t *, uint64_t *, void **) { return CM_ERR_ARG; }
+void cm_annot_file_free(void *) {}
 int cm_gpu_host_alloc(size_t bytes, void **out) { *out = malloc(bytes ? bytes : 1); return *out ? CM_OK : CM_ERR_ALLOC; }
 int cm_gpu_host_free(void *p) { free(p); return CM_OK; }
 

@@ -127,3 +127,23 @@ def test_fused_directory_lookup_equals_plain_lookup(t0_packed, kmer, big_th):
         hs.build_contig(c, seq)
         bad = hs.seed_x_check(c, big_th=big_th, n_probe=100000, seed=c + 1)
         assert bad == 0 or (kmer == 14 and bad == 1000000), f"contig {c}: {bad} look-ups differ"
+
+
+def test_annotation_file_round_trip(t0_packed, tmp_path):
+    """cm_annot_file_write / _read (host only): the build-once annotation artefact gives back every array bit for bit;
+    a truncated file is refused."""
+    from circminer_b200 import api
+    for c, a in enumerate(t0_packed["flat"]):
+        path = str(tmp_path / f"annot{c}.bin")
+        api.write_annotation_file(path, a, max_read_len=300, tag=1234 + c)
+        b = api.read_annotation_file(path)
+        assert b["max_read_len"] == 300 and b["tag"] == 1234 + c
+        for k in ("n_iv", "n_seg", "n_tid", "n_trans", "n_genes", "n_chr", "n_bits"):
+            assert int(a[k]) == b[k], k
+        for k in api._ANNOT_U4 + tuple(n for n, _ in api._ANNOT_OTHER):
+            want = np.asarray(a[k])
+            assert want.shape == b[k].shape and (want == b[k]).all(), k
+        raw = open(path, "rb").read()
+        open(path, "wb").write(raw[:len(raw) // 2])
+        with pytest.raises(api.CmGpuError):
+            api.read_annotation_file(path)

@@ -10,6 +10,7 @@ import os
 import subprocess
 import sys
 
+import numpy as np
 import pytest
 
 from conftest import has_ref
@@ -61,3 +62,37 @@ def test_dropin_binary_outputs_are_byte_identical(tmp_path, scan, devices):
         assert filecmp.cmp(a, b, shallow=False), f"{suffix} differs ({os.path.getsize(a)} vs {os.path.getsize(b)} bytes)"
     assert os.path.getsize(ref_out + ".mapping.pam") > 100000
     assert os.path.getsize(ref_out + ".circ_report") > 0
+
+
+@pytest.mark.skipif(not (has_ref() and os.path.exists(GPU)), reason="oracle/_ref/circminer_gpu not built")
+def test_dropin_annotation_cache_file(tmp_path):
+    """The drop-in flattens the annotation once and keeps it as files: the second run uploads the files and
+    writes the same outputs; a changed -l does not reuse them."""
+    from circminer_b200 import api, workload
+    d = str(tmp_path / "t1")
+    w = workload.prepare("T1", d, contig_size=3_500_000, write_reads=True, n_pairs=5000)
+    subprocess.run([sys.executable, "-c",
+                    "import sys; sys.path.insert(0, %r)\n"
+                    "from oracle.refharness import RefHarness, default_params\n"
+                    "RefHarness(default_params()).build_index(%r, contig_size=3500000)" % (ROOT, w["fa"])],
+                   check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=900)
+    cache = str(tmp_path / "cache")
+    os.makedirs(cache)
+    env = {"CM_GPU_ANNOT_CACHE": cache, "CM_GPU_VERBOSE": "1", "CM_GPU_BATCH": "2000"}
+    p1 = _run(GPU, w, str(tmp_path / "a"), env=env)
+    files = sorted(os.listdir(cache))
+    assert len(files) == len(w["contigs"]) and all(".cmannot." in f and f.endswith(".l300") for f in files), files
+    assert "written to" in p1.stderr and "annotation of contig 0 from" not in p1.stderr
+    # the files hold what the Python flattening of the same GTF gives (tests/test_cpu_parity.py checks that one against the reference)
+    for c, f in enumerate(files):
+        got = api.read_annotation_file(os.path.join(cache, f))
+        for k in ("iv_spos", "iv_epos", "iv_seg_off", "seg_start", "seg_end", "seg_tid_off", "tid", "t2s", "gene_start", "gene_end", "chr_shift"):
+            assert (got[k] == np.asarray(w["flat"][c][k])).all(), (c, k)
+        nw = min(len(got["near_border"]), len(w["flat"][c]["near_border"])) - 1
+        assert (got["near_border"][:nw] == w["flat"][c]["near_border"][:nw]).all() and (got["intronic"][:nw] == w["flat"][c]["intronic"][:nw]).all()
+    p2 = _run(GPU, w, str(tmp_path / "b"), env=env)
+    assert "annotation of contig 0 from" in p2.stderr and "written to" not in p2.stderr
+    for suffix in (".mapping.pam", ".candidates.pam", ".circ_report", "_1_remain_R1.fastq", "_2_remain_R2.fastq"):
+        assert filecmp.cmp(str(tmp_path / "a") + suffix, str(tmp_path / "b") + suffix, shallow=False), suffix
+    p3 = _run(GPU, w, str(tmp_path / "c"), env=env, extra=("-l", "200"))
+    assert "annotation of contig 0 from" not in p3.stderr and any(f.endswith(".l200") for f in os.listdir(cache))
