@@ -1030,25 +1030,44 @@ static int launch_prep(cm_gpu_ctx *ctx, uint32_t in_stride) {
 // random gathers directory (dir[hv], dir[hv+1]) -> checksum run (binary search).  Positions are NOT
 // copied: chaining reads them in place through (off, cnt).
 // ------------------------------------------------------------------------------------------
+#ifndef CM_SEED_ILP
+#define CM_SEED_ILP 1   // measured on C3 (28 M seeds): 1.62 ms at 1 and 2, 1.68 at 4, 1.95 at 8 -- the kernel is not short of loads in flight
+#endif
 __global__ void __launch_bounds__(256) k_seed(const __grid_constant__ DevView v, const int2 *__restrict__ seed_key, uint64_t total,
                                               uint32_t *__restrict__ seed_off, uint32_t *__restrict__ seed_cnt,
                                               cm_counters *__restrict__ ctr) {
     __shared__ uint32_t sh[4];   // looked, sectors, hits, warps done
     if (threadIdx.x < 4) sh[threadIdx.x] = 0;
     __syncthreads();             // at the start every warp arrives at once
-    uint64_t gid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    // CM_SEED_ILP seeds per thread, a block apart (coalesced key reads): all their directory entries are requested before the
+    // first one is used, so that a thread keeps several random DRAM reads in flight
+    const uint64_t g0 = (uint64_t) blockIdx.x * (blockDim.x * CM_SEED_ILP) + threadIdx.x;
     uint32_t sectors = 0, hits = 0, looked = 0;
-    if (gid < total) {
-        int2 key = seed_key[gid];
+    int2 key[CM_SEED_ILP];
+    uint32_t w[CM_SEED_ILP][CM_DIRX_WORDS];
+#pragma unroll
+    for (int u = 0; u < CM_SEED_ILP; u++) {
+        const uint64_t gid = g0 + (uint64_t) u * blockDim.x;
+        key[u] = gid < total ? seed_key[gid] : make_int2(-2, 0);
+    }
+    if (v.c.dirx) {
+#pragma unroll
+        for (int u = 0; u < CM_SEED_ILP; u++) cm_dirx_load(v.c, (key[u].x < 0 || key[u].y < 0) ? -1 : key[u].x, w[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < CM_SEED_ILP; u++) {
+        const uint64_t gid = g0 + (uint64_t) u * blockDim.x;
+        if (gid >= total) continue;
         SeedHit h;
         h.off = 0;
         h.cnt = 0;
-        if (key.x != -2) {
-            h = v.c.dirx ? cm_seed_lookup_x(v.c, key.x, key.y, &sectors) : cm_seed_lookup(v.c, key.x, key.y, &sectors);
-            looked = 1;
-            uint32_t kept = h.cnt > (uint32_t) v.p.seed_lim ? 0 : h.cnt;
-            hits = kept;
-            sectors += (6 * kept) / 32;
+        if (key[u].x != -2) {
+            uint32_t sec = 0;
+            h = v.c.dirx ? cm_seed_resolve_x(v.c, w[u], key[u].x, key[u].y, &sec) : cm_seed_lookup(v.c, key[u].x, key[u].y, &sec);
+            looked++;
+            const uint32_t kept = h.cnt > (uint32_t) v.p.seed_lim ? 0 : h.cnt;
+            hits += kept;
+            sectors += sec + (6 * kept) / 32;
         }
         seed_off[gid] = h.off;
         seed_cnt[gid] = h.cnt;
@@ -1096,7 +1115,7 @@ static int launch_seed(cm_gpu_ctx *ctx, const DevView &v) {
     size_t total = (size_t) ctx->n_strands * ctx->batch_F;
     ENSURE(ctx, ctx->seed_off, total * 4);
     ENSURE(ctx, ctx->seed_cnt, total * 4);
-    k_seed<<<grid_for(total, 256), 256, 0, ctx->stream>>>(v, (const int2 *) ctx->seed_key.p, (uint64_t) total,
+    k_seed<<<grid_for(total, 256 * CM_SEED_ILP), 256, 0, ctx->stream>>>(v, (const int2 *) ctx->seed_key.p, (uint64_t) total,
                                                          (uint32_t *) ctx->seed_off.p, (uint32_t *) ctx->seed_cnt.p, ctx->d_counters);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());

@@ -85,26 +85,41 @@ CM_HD SeedHit cm_seed_lookup(const ContigDev &c, int hv, int cv, uint32_t *secto
 // The same look-up through the fused directory (ContigDev::dirx).  Equal range of `target` in the sorted bucket:
 // positions < CM_DIRX_INLINE are answered from the inline checksums, the rest by bisection of the bucket's tail; a large
 // bucket goes through its coarse checksum table first.
-CM_HD SeedHit cm_seed_lookup_x(const ContigDev &c, int hv, int cv, uint32_t *sectors) {
-    SeedHit h;
-    h.off = 0;
-    h.cnt = 0;
-    if (sectors) *sectors = 0;
-    if (hv < 0 || cv < 0) return h;
-    constexpr unsigned NW = sizeof(DirX) / 4;
-    uint32_t w[NW];
+// the directory entry of bucket hv, as words (off, cnt, checksums two per word); all zero for hv < 0
+#define CM_DIRX_WORDS (sizeof(DirX) / 4)
+CM_HD void cm_dirx_load(const ContigDev &c, int hv, uint32_t *w) {
+    constexpr unsigned NW = CM_DIRX_WORDS;
+    if (hv < 0) {
+        for (unsigned k = 0; k < NW; k++) w[k] = 0;
+        return;
+    }
 #if defined(__CUDA_ARCH__)
     const uint4 *dp = reinterpret_cast<const uint4 *>(c.dirx + hv);
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(dp));
     if (NW == 8)
         asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[4 % NW]), "=r"(w[5 % NW]), "=r"(w[6 % NW]), "=r"(w[7 % NW]) : "l"(dp + 1));
 #else
-    {
-        const DirX &e = c.dirx[hv];
-        w[0] = e.off; w[1] = e.cnt;
-        for (int k = 0; k < CM_DIRX_INLINE / 2; k++) w[2 + k] = (uint32_t) e.c[2 * k] | ((uint32_t) e.c[2 * k + 1] << 16);
-    }
+    const DirX &e = c.dirx[hv];
+    w[0] = e.off; w[1] = e.cnt;
+    for (int k = 0; k < CM_DIRX_INLINE / 2; k++) w[2 + k] = (uint32_t) e.c[2 * k] | ((uint32_t) e.c[2 * k + 1] << 16);
 #endif
+}
+
+CM_HD SeedHit cm_seed_resolve_x(const ContigDev &c, const uint32_t *w, int hv, int cv, uint32_t *sectors);
+
+CM_HD SeedHit cm_seed_lookup_x(const ContigDev &c, int hv, int cv, uint32_t *sectors) {
+    uint32_t w[CM_DIRX_WORDS];
+    cm_dirx_load(c, (hv < 0 || cv < 0) ? -1 : hv, w);
+    return cm_seed_resolve_x(c, w, hv, cv, sectors);
+}
+
+// the look-up given the loaded directory entry (split off so that a thread can have several entries in flight)
+CM_HD SeedHit cm_seed_resolve_x(const ContigDev &c, const uint32_t *w, int hv, int cv, uint32_t *sectors) {
+    SeedHit h;
+    h.off = 0;
+    h.cnt = 0;
+    if (sectors) *sectors = 0;
+    if (hv < 0 || cv < 0) return h;
     const uint32_t off = w[0], cnt = w[1];
     if (sectors) *sectors = 1;                 // directory sector
     if (cnt == 0) return h;                    // getCandidates == NULL
