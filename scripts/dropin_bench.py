@@ -61,7 +61,7 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--batch", type=int, default=524288)
     ap.add_argument("--devices", nargs="+", default=["0"], help="CM_GPU_DEVICES settings to time the drop-in under, e.g. 0 0,1 all")
-    ap.add_argument("--skip-reference", action="store_true")
+    ap.add_argument("--stage2", action="store_true", help="also run the reference with -q 0 (mapping only): whole wall minus that = stage 2 (process_circ)")
     a = ap.parse_args()
     from circminer_b200 import synth, workload
     from oracle.cpu_baseline import ensure_ref_index
@@ -84,6 +84,11 @@ def main():
     res["reference"] = run(REF_BIN, d, fq1, fq2, ref_out, ncores)
     res["reference"]["threads"] = ncores
     res["reference"]["reads_per_s_mapping"] = 2.0 * n / res["reference"]["mapping_s"]
+    if a.stage2:
+        q0 = run(REF_BIN, d, fq1, fq2, ref_out + "_q0", ncores, extra=("-q", "0"))
+        res["reference"]["wall_s_mapping_only"] = q0["wall_s"]
+        res["reference"]["stage2_s"] = res["reference"]["wall_s"] - q0["wall_s"]
+        res["reference"]["load_s"] = q0["wall_s"] - q0["mapping_s"]
     same = {}
     res["dropin"] = []
     for dev in a.devices:
