@@ -412,8 +412,13 @@ struct XdropState {
 // One anti-diagonal k = 2q + KP.  EARLY: k may be <= W (boundary cells dpx[k][0], dpx[0][k] still enter the band).
 // Row indices are handled relative to q (h = i - q is a compile-time constant per slot); the cell count of a diagonal
 // is ub - lb + 1 (every i in [lb, ub] has a slot in the band); the best cell is kept as (i, k).
-template <int W, int KP, bool EARLY>
-CM_HD void cm_xdrop_step(XdropState<W> &S, int k, int q, int mat, int mis, int ind, int xd, int &new_ub) {
+#ifndef CM_XDROP_FAST
+#define CM_XDROP_FAST 1
+#endif
+// FULL: every slot of this parity is inside [lb, ub] (the usual state once the band has opened), so the per-slot range
+// tests and the boundary values drop out.
+template <int W, int KP, bool EARLY, bool FULL>
+CM_HD void cm_xdrop_step_impl(XdropState<W> &S, int k, int q, int mat, int mis, int ind, int xd, int &new_ub) {
     const int NEG = -CM_DPTINF;
     constexpr int LO = -(W / 2 + 1);
     const int lq = S.lb - q, uq = S.ub - q, lim = S.pre - xd;   // lim >= -xd > NEG: a cell that survives the X-drop is live
@@ -428,7 +433,7 @@ CM_HD void cm_xdrop_step(XdropState<W> &S, int k, int q, int mat, int mis, int i
         if (((d + KP) & 1) != 0) continue;          // slot belongs to the other parity
         const int h = (KP + d) / 2;                 // exact: KP + d is even
         int v;
-        if (h >= lq && h <= uq) {
+        if (FULL || (h >= lq && h <= uq)) {
             int sc = S.SW[h - 1 - LO] == S.TW[(KP - d) / 2 - 1 - LO] ? mat : mis;
             v = S.X[e] + sc;
             int ab = S.X[e - 1] > S.X[e + 1] ? S.X[e - 1] : S.X[e + 1];
@@ -445,6 +450,23 @@ CM_HD void cm_xdrop_step(XdropState<W> &S, int k, int q, int mat, int mis, int i
     }
     if (dmax >= S.cur) { S.cur = dmax; S.best_i = q + dh; S.best_k = k; }
     new_ub = nub_h > -1000 ? q + nub_h : -1;
+}
+
+template <int W, int KP, bool EARLY>
+CM_HD void cm_xdrop_step(XdropState<W> &S, int k, int q, int mat, int mis, int ind, int xd, int &new_ub) {
+#if CM_XDROP_FAST
+    if (!EARLY) {
+        // rows of the slots of parity KP, relative to q: h = (KP + d) / 2 over d = -W .. W with (d + KP) even
+        constexpr int DMIN = ((W + KP) & 1) ? -W + 1 : -W, DMAX = ((W + KP) & 1) ? W - 1 : W;
+        constexpr int HMIN = (KP + DMIN) / 2, HMAX = (KP + DMAX) / 2;
+        static_assert((KP + DMIN) % 2 == 0 && (KP + DMAX) % 2 == 0, "slot parity");
+        if (S.lb - q <= HMIN && S.ub - q >= HMAX) {
+            cm_xdrop_step_impl<W, KP, false, true>(S, k, q, mat, mis, ind, xd, new_ub);
+            return;
+        }
+    }
+#endif
+    cm_xdrop_step_impl<W, KP, EARLY, false>(S, k, q, mat, mis, ind, xd, new_ub);
 }
 
 // anti-diagonals 2q and 2q + 1; true = the run is over
@@ -484,27 +506,35 @@ CM_HD void cm_xdrop_reg(const uint8_t *s, int n, const uint8_t *t, int m, bool r
     if (W >= 1) { S.X[W + 2] = ind; S.X[W] = ind; }    // dpx[1][0], dpx[0][1]  (anti-diagonal 1)
     constexpr int LO = -(W / 2 + 1), HI = (W + 1) / 2 - 1;
     const uint8_t *s0 = rev ? s + n - 1 : s, *t0 = rev ? t + m - 1 : t;
+    S.pre = 0; S.cur = 0; S.lb = 1; S.ub = 1; S.pre_ub = 0; S.best_i = 0; S.best_k = 0; S.cells = 0;
+    const int K = m + n;
     const int step = rev ? -1 : 1;
 #pragma unroll
     for (int x = 0; x <= W; x++) {                     // window of q = 1
         S.SW[x] = cm_code_at(s0, step, n, 1 + LO + x, 1);
         S.TW[x] = cm_code_at(t0, step, m, 1 + LO + x, 2);
     }
-    S.pre = 0; S.cur = 0; S.lb = 1; S.ub = 1; S.pre_ub = 0; S.best_i = 0; S.best_k = 0; S.cells = 0;
-    const int K = m + n;
-    for (int q = 1; 2 * q <= K; ++q) {
-        // raw bytes of the characters that enter the windows at q + 1: loaded here, first used after the two anti-diagonals
-        const int cn = q + 1 + HI;
-        const bool in_s = cn < n, in_t = cn < m;
-        const uint8_t rs = in_s ? s0[cn * step] : (uint8_t) 0, rt = in_t ? t0[cn * step] : (uint8_t) 0;
-        const bool stop = (2 * q <= W) ? cm_xdrop_pair<W, true>(S, q, K, n, m, mat, mis, ind, xd)
-                                       : cm_xdrop_pair<W, false>(S, q, K, n, m, mat, mis, ind, xd);
-        if (stop) break;
-#pragma unroll
-        for (int x = 0; x < W; x++) { S.SW[x] = S.SW[x + 1]; S.TW[x] = S.TW[x + 1]; }
-        S.SW[W] = in_s ? cm_code(rs, 1) : 1;
-        S.TW[W] = in_t ? cm_code(rt, 2) : 2;
+    // one q = anti-diagonals 2q and 2q + 1.  The raw bytes of the characters that enter the windows at q + 1 are loaded
+    // first and used after the two anti-diagonals.  (A queue of aligned 32-bit words, one load per four characters, was
+    // measured on C3: k_chain_spec 101 -> 114 ms per step -- the kernel is bound by issued instructions, not by these loads.)
+#define CM_XDROP_Q(EARLY)                                                                                             \
+    {                                                                                                                 \
+        const int cn = q + 1 + HI;                                                                                    \
+        const bool in_s = cn < n, in_t = cn < m;                                                                      \
+        const uint8_t rs = in_s ? s0[cn * step] : (uint8_t) 0, rt = in_t ? t0[cn * step] : (uint8_t) 0;               \
+        if (cm_xdrop_pair<W, EARLY>(S, q, K, n, m, mat, mis, ind, xd)) { stop = true; break; }                        \
+        _Pragma("unroll") for (int x = 0; x < W; x++) { S.SW[x] = S.SW[x + 1]; S.TW[x] = S.TW[x + 1]; }               \
+        S.SW[W] = in_s ? cm_code(rs, 1) : 1;                                                                          \
+        S.TW[W] = in_t ? cm_code(rt, 2) : 2;                                                                          \
     }
+    // the anti-diagonals that still see the boundary cells (k <= W) are peeled off: the steady-state loop carries one
+    // variant of the step only
+    int q = 1;
+    bool stop = false;
+    for (; 2 * q <= K && 2 * q <= W; ++q) CM_XDROP_Q(true)
+    if (!stop)
+        for (; 2 * q <= K; ++q) CM_XDROP_Q(false)
+#undef CM_XDROP_Q
     if (st) st->xdrop_cells += S.cells;
     on_s = S.best_i;
     on_t = S.best_k - S.best_i;

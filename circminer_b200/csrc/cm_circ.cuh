@@ -1,0 +1,265 @@
+// Stage 2 on the device, first piece: the per-contig ws-mer index and ProcessCirc::chaining as a batch entry
+// (cm_circ.h has the device functions).  Included by cm_gpu.cu.
+#pragma once
+#include "cm_circ.h"
+
+// key of the ws-mer starting at 1-based position P = tid + 1: its hash, or 4^ws when it holds a non-ACGT base or runs
+// past the end of the contig (sorted to the back and dropped)
+__global__ void k_circ_keys(const uint8_t *genome, uint32_t len, int ws, uint32_t *keys, uint32_t *vals) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= len) return;
+    const uint32_t P = t + 1;
+    int hv = -1;
+    if (P + (uint32_t) ws - 1 <= len) hv = cm_circ_hash(genome + P, ws);
+    keys[t] = hv < 0 ? (1u << (2 * ws)) : (uint32_t) hv;
+    vals[t] = P;
+}
+
+// off[h] = first index of the sorted keys with key >= h, h = 0 .. 4^ws
+__global__ void k_circ_offsets(const uint32_t *keys, uint32_t n, uint32_t n_off, uint32_t *off) {
+    const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
+    if (h >= n_off) return;
+    off[h] = cm_circ_lower(keys, 0, n, h);
+}
+
+static int build_circ_index(cm_gpu_ctx *ctx, int contig_id, int ws) {
+    if (ws < 4 || ws > 12) return fail(ctx, CM_ERR_ARG, "window size %d outside 4..12", ws);
+    ContigHost *ch = get_contig(ctx, contig_id, false);
+    if (!ch || !ch->loaded) return fail(ctx, CM_ERR_STATE, "contig %d not loaded", contig_id);
+    if (ch->circ_ws == ws && ch->circ_pos) return CM_OK;
+    if (ctx->parent) return fail(ctx, CM_ERR_STATE, "the ws-mer index of contig %d is built through the root context (cm_gpu_build_circ_index)", contig_id);
+    if (ch->circ_pos) return fail(ctx, CM_ERR_STATE, "contig %d already has a ws-mer index for window size %d", contig_id, ch->circ_ws);
+    cudaStream_t st = ctx->stream;
+    const uint32_t len = ch->d.ref_len;
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *q : tmp) cudaFree(q); };
+    uint32_t *k0 = nullptr, *k1 = nullptr, *v0 = nullptr, *v1 = nullptr, *off = nullptr;
+    uint8_t *d_tmp = nullptr;
+    int r;
+    if ((r = dev_alloc(ctx, tmp, &k0, (size_t) len)) != CM_OK || (r = dev_alloc(ctx, tmp, &k1, (size_t) len)) != CM_OK ||
+        (r = dev_alloc(ctx, tmp, &v0, (size_t) len)) != CM_OK || (r = dev_alloc(ctx, ch->owned, &v1, (size_t) len)) != CM_OK ||
+        (r = dev_alloc(ctx, ch->owned, &off, ((size_t) 1 << (2 * ws)) + 2)) != CM_OK) { cleanup(); return r; }
+    k_circ_keys<<<grid_for(len, 256), 256, 0, st>>>(ch->d.genome, len, ws, k0, v0);
+    ctx->launches++;
+    size_t tb = 0;
+    // stable sort on the 2 ws + 1 key bits: positions stay ascending inside a hash value
+    cub::DeviceRadixSort::SortPairs(nullptr, tb, k0, k1, v0, v1, (int64_t) len, 0, 2 * ws + 1, st);
+    if ((r = dev_alloc(ctx, tmp, &d_tmp, tb + 16)) != CM_OK) { cleanup(); return r; }
+    cub::DeviceRadixSort::SortPairs(d_tmp, tb, k0, k1, v0, v1, (int64_t) len, 0, 2 * ws + 1, st);
+    const uint32_t n_off = (1u << (2 * ws)) + 1;
+    k_circ_offsets<<<grid_for(n_off, 256), 256, 0, st>>>(k1, len, n_off, off);
+    ctx->launches += 2;
+    cudaError_t e = cudaStreamSynchronize(st);
+    cleanup();
+    if (e != cudaSuccess || (e = cudaGetLastError()) != cudaSuccess) return fail(ctx, CM_ERR_CUDA, "ws-mer index build: %s", cudaGetErrorString(e));
+    ch->circ_pos = v1;
+    ch->circ_off = off;
+    ch->circ_ws = ws;
+    return CM_OK;
+}
+
+extern "C" int cm_gpu_build_circ_index(cm_gpu_ctx *ctx, int contig_id, int window_size) {
+    if (!ctx) return CM_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    return build_circ_index(ctx, contig_id, window_size);
+}
+
+struct CircBatch {
+    uint32_t n;
+    const uint8_t *seqs;
+    uint32_t stride;
+    const uint32_t *qspos, *qepos, *gene_start, *gene_end;
+    int step, R;                    // R = row slots per problem
+    uint32_t *row_pos, *row_cnt;    // [n][R]
+    int32_t *qp;                    // [n][R]
+    int32_t *kmer_cnt;              // [n]
+    uint32_t *cells;                // [n]
+};
+
+// rows of every problem (thread per problem)
+__global__ void k_circ_rows(const __grid_constant__ DevView v, const CircIndex ix, const __grid_constant__ CircBatch b) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= b.n) return;
+    uint32_t cells = 0;
+    const size_t o = (size_t) i * b.R;
+    b.kmer_cnt[i] = cm_circ_rows(ix, v.p, b.seqs + (size_t) i * b.stride, b.qspos[i], b.qepos[i], b.gene_start[i], b.gene_end[i], b.step, b.R,
+                                 b.row_pos + o, b.row_cnt + o, b.qp + o, cells);
+    b.cells[i] = cells;
+}
+
+// chain_seeds_sorted_kbest2 + the cut of ProcessCirc::chaining, thread per problem.  list == nullptr: every problem, with
+// the record slice rec_base[i] .. + rec_cap[i]; a problem whose improvements outgrow its slice is appended to ovf (with the
+// number it needs) and left for a second launch over that list with exactly sized slices.
+__global__ void k_circ_chain(const __grid_constant__ DevView v, const CircIndex ix, const __grid_constant__ CircBatch b, const uint32_t *list,
+                             uint32_t n_list, const uint64_t *cell_base, double *dp_score, uint32_t *dp_prev, const uint64_t *rec_base,
+                             const uint32_t *rec_cap, ChainRec *recs, uint32_t *ovf, uint32_t *ovf_nrec, uint32_t *n_ovf, int F,
+                             int32_t *out_count, float *out_score, uint32_t *out_len, FragDev *out_frags) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_list) return;
+    const uint32_t i = list ? list[k] : k;
+    const int C = v.p.max_chain_len;
+    const size_t o = (size_t) i * b.R;
+    const uint32_t *row_pos = b.row_pos + o, *row_cnt = b.row_cnt + o;
+    uint32_t row_off[CM_CIRC_MAX_ROWS];
+    const int kmer_cnt = b.kmer_cnt[i];
+    const int T = cm_circ_trim(kmer_cnt, row_cnt, row_off);
+    ChainOut out;
+    out.count = out_count + i;
+    out.score = out_score + (size_t) i * C;
+    out.len = out_len + (size_t) i * C;
+    out.frags = out_frags + (size_t) i * C * F;
+    out.F = F;
+    if (T <= 0) { *out.count = 0; return; }
+    const ChainGeomCirc g{ix.pos, b.gene_start[i], ix.ws, b.qp + o};
+    double *ds = dp_score + cell_base[i];
+    uint32_t *dpv = dp_prev + cell_base[i];
+    ChainRec *r = recs + rec_base[k];
+    const uint32_t cap = rec_cap[k];
+    const uint32_t nrec = cm_chain_dp_g(g, v, (int) b.qepos[i], T, row_pos, row_cnt, row_off, ds, dpv, r, cap, nullptr);
+    if (nrec > cap) {
+        const uint32_t s = atomicAdd(n_ovf, 1u);
+        ovf[s] = i;
+        ovf_nrec[s] = nrec;
+        *out.count = -1;
+        return;
+    }
+    cm_chain_backtrack_g(g, v, T, row_pos, row_cnt, row_off, ds, dpv, r, nrec, out, b.gene_start[i]);
+    cm_circ_finish(kmer_cnt, out);
+}
+
+static int circ_scan_u64(const std::vector<uint64_t> &in, std::vector<uint64_t> &out) {
+    out.resize(in.size() + 1);
+    uint64_t s = 0;
+    for (size_t i = 0; i < in.size(); i++) { out[i] = s; s += in[i]; }
+    out[in.size()] = s;
+    return 0;
+}
+
+extern "C" int cm_gpu_circ_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride, const uint32_t *qspos,
+                                       const uint32_t *qepos, const uint32_t *gene_start, const uint32_t *gene_end, int window_size, int step,
+                                       int F, int32_t *chain_count, int32_t *kmer_cnt, float *score, uint32_t *chain_len,
+                                       uint32_t *frag_rpos, int32_t *frag_qpos) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n == 0) return CM_OK;
+    if (!seqs || !qspos || !qepos || !gene_start || !gene_end || !chain_count || !score || !chain_len || !frag_rpos || !frag_qpos)
+        return fail(ctx, CM_ERR_ARG, "null argument");
+    if (step < 1) return fail(ctx, CM_ERR_ARG, "step < 1");
+    if (F < 1 || F > CM_CIRC_MAX_ROWS) return fail(ctx, CM_ERR_ARG, "F = %d outside 1..%d", F, CM_CIRC_MAX_ROWS);
+    for (uint32_t i = 0; i < n; i++) {
+        if (qspos[i] < 1 || qepos[i] > stride) return fail(ctx, CM_ERR_ARG, "problem %u: [qspos, qepos] outside the row", i);
+        if (qepos[i] >= qspos[i] && (int) (qepos[i] - qspos[i] + 1) >= window_size &&
+            (int) ((qepos[i] - qspos[i] + 1 - window_size) / step + 1) > F)
+            return fail(ctx, CM_ERR_ARG, "problem %u: more than F = %d k-mers", i, F);
+    }
+    cudaSetDevice(ctx->device);
+    DevView v;
+    int r = make_view(ctx, contig_id, true, v);
+    if (r != CM_OK) return r;
+    if ((r = build_circ_index(ctx, contig_id, window_size)) != CM_OK) return r;
+    ContigHost *ch = get_contig(ctx, contig_id, false);
+    const CircIndex ix{ch->circ_pos, ch->circ_off, ch->circ_ws};
+    cudaStream_t st = ctx->stream;
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *q : tmp) cudaFree(q); };
+#define CIRC_TRY(x) do { if ((r = (x)) != CM_OK) { cleanup(); return r; } } while (0)
+#define CIRC_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return fail(ctx, CM_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e_)); } } while (0)
+    const int C = ctx->p.max_chain_len, R = F;
+    uint8_t *d_seq = nullptr;
+    uint32_t *d_in = nullptr, *d_row_pos = nullptr, *d_row_cnt = nullptr, *d_cells = nullptr;
+    int32_t *d_qp = nullptr, *d_kc = nullptr;
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_seq, (size_t) n * stride + 64));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_in, (size_t) n * 4));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_row_pos, (size_t) n * R));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_row_cnt, (size_t) n * R));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_qp, (size_t) n * R));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_kc, (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_cells, (size_t) n));
+    CIRC_CUDA(cudaMemcpyAsync(d_seq, seqs, (size_t) n * stride, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_in, qspos, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_in + n, qepos, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_in + 2 * (size_t) n, gene_start, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_in + 3 * (size_t) n, gene_end, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    CircBatch b{n, d_seq, stride, d_in, d_in + n, d_in + 2 * (size_t) n, d_in + 3 * (size_t) n, step, R, d_row_pos, d_row_cnt, d_qp, d_kc, d_cells};
+    k_circ_rows<<<grid_for(n, 128), 128, 0, st>>>(v, ix, b);
+    ctx->launches++;
+    CIRC_CUDA(cudaGetLastError());
+    std::vector<uint32_t> h_cells(n);
+    CIRC_CUDA(cudaMemcpyAsync(h_cells.data(), d_cells, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaStreamSynchronize(st));
+    // arenas: dp cells back to back; records 3 per cell + 8 per problem (as the stage-1 kernel), exact on the second pass
+    std::vector<uint64_t> cells64(h_cells.begin(), h_cells.end()), cell_base, recn(n), rec_base;
+    std::vector<uint32_t> rec_cap(n);
+    for (uint32_t i = 0; i < n; i++) { rec_cap[i] = 3 * h_cells[i] + 8; recn[i] = rec_cap[i]; }
+    circ_scan_u64(cells64, cell_base);
+    circ_scan_u64(recn, rec_base);
+    uint64_t *d_cell_base = nullptr, *d_rec_base = nullptr;
+    uint32_t *d_rec_cap = nullptr, *d_prev = nullptr, *d_ovf = nullptr;
+    double *d_score = nullptr;
+    ChainRec *d_recs = nullptr;
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_cell_base, (size_t) n + 1));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_rec_base, (size_t) n + 1));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_rec_cap, (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_score, (size_t) cell_base[n] + 1));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_prev, (size_t) cell_base[n] + 1));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_recs, (size_t) rec_base[n] + 1));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_ovf, 2 * (size_t) n + 2));
+    CIRC_CUDA(cudaMemcpyAsync(d_cell_base, cell_base.data(), ((size_t) n + 1) * 8, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_rec_base, rec_base.data(), ((size_t) n + 1) * 8, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_rec_cap, rec_cap.data(), (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemsetAsync(d_ovf + 2 * (size_t) n, 0, 8, st));
+    int32_t *d_count = nullptr;
+    float *d_oscore = nullptr;
+    uint32_t *d_olen = nullptr;
+    FragDev *d_frags = nullptr;
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_count, (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_oscore, (size_t) n * C));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_olen, (size_t) n * C));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_frags, (size_t) n * C * F));
+    CIRC_CUDA(cudaMemsetAsync(d_oscore, 0, (size_t) n * C * 4, st));
+    CIRC_CUDA(cudaMemsetAsync(d_olen, 0, (size_t) n * C * 4, st));
+    CIRC_CUDA(cudaMemsetAsync(d_frags, 0, (size_t) n * C * F * sizeof(FragDev), st));
+    uint32_t *d_novf = d_ovf + 2 * (size_t) n;
+    k_circ_chain<<<grid_for(n, 64), 64, 0, st>>>(v, ix, b, nullptr, n, d_cell_base, d_score, d_prev, d_rec_base, d_rec_cap, d_recs, d_ovf, d_ovf + n,
+                                                  d_novf, F, d_count, d_oscore, d_olen, d_frags);
+    ctx->launches++;
+    CIRC_CUDA(cudaGetLastError());
+    uint32_t n_ovf = 0;
+    CIRC_CUDA(cudaMemcpyAsync(&n_ovf, d_novf, 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaStreamSynchronize(st));
+    if (n_ovf) {
+        std::vector<uint32_t> ovf(n_ovf), need(n_ovf);
+        CIRC_CUDA(cudaMemcpy(ovf.data(), d_ovf, (size_t) n_ovf * 4, cudaMemcpyDeviceToHost));
+        CIRC_CUDA(cudaMemcpy(need.data(), d_ovf + n, (size_t) n_ovf * 4, cudaMemcpyDeviceToHost));
+        std::vector<uint64_t> need64(need.begin(), need.end()), base2;
+        circ_scan_u64(need64, base2);
+        uint64_t *d_base2 = nullptr;
+        uint32_t *d_cap2 = nullptr, *d_list = nullptr, *d_ovf2 = nullptr;
+        ChainRec *d_recs2 = nullptr;
+        CIRC_TRY(dev_alloc(ctx, tmp, &d_base2, (size_t) n_ovf + 1));
+        CIRC_TRY(dev_alloc(ctx, tmp, &d_cap2, (size_t) n_ovf));
+        CIRC_TRY(dev_alloc(ctx, tmp, &d_list, (size_t) n_ovf));
+        CIRC_TRY(dev_alloc(ctx, tmp, &d_recs2, (size_t) base2[n_ovf] + 1));
+        CIRC_TRY(dev_alloc(ctx, tmp, &d_ovf2, 2 * (size_t) n_ovf + 2));
+        CIRC_CUDA(cudaMemcpyAsync(d_base2, base2.data(), ((size_t) n_ovf + 1) * 8, cudaMemcpyHostToDevice, st));
+        CIRC_CUDA(cudaMemcpyAsync(d_cap2, need.data(), (size_t) n_ovf * 4, cudaMemcpyHostToDevice, st));
+        CIRC_CUDA(cudaMemcpyAsync(d_list, ovf.data(), (size_t) n_ovf * 4, cudaMemcpyHostToDevice, st));
+        CIRC_CUDA(cudaMemsetAsync(d_ovf2 + 2 * (size_t) n_ovf, 0, 8, st));
+        k_circ_chain<<<grid_for(n_ovf, 64), 64, 0, st>>>(v, ix, b, d_list, n_ovf, d_cell_base, d_score, d_prev, d_base2, d_cap2, d_recs2, d_ovf2,
+                                                      d_ovf2 + n_ovf, d_ovf2 + 2 * (size_t) n_ovf, F, d_count, d_oscore, d_olen, d_frags);
+        ctx->launches++;
+        CIRC_CUDA(cudaGetLastError());
+    }
+    // fragments come back as two planes, like cm_gpu_chain_batch
+    std::vector<FragDev> h_frags((size_t) n * C * F);
+    CIRC_CUDA(cudaMemcpyAsync(chain_count, d_count, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    if (kmer_cnt) CIRC_CUDA(cudaMemcpyAsync(kmer_cnt, d_kc, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(score, d_oscore, (size_t) n * C * 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(chain_len, d_olen, (size_t) n * C * 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(h_frags.data(), d_frags, h_frags.size() * sizeof(FragDev), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaStreamSynchronize(st));
+    for (size_t q = 0; q < h_frags.size(); q++) { frag_rpos[q] = h_frags[q].rpos; frag_qpos[q] = h_frags[q].qpos; }
+    cleanup();
+#undef CIRC_TRY
+#undef CIRC_CUDA
+    return CM_OK;
+}

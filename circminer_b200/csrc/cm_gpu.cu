@@ -36,6 +36,9 @@ struct ContigHost {
     std::vector<void *> owned;        // device allocations of this contig
     std::vector<void *> owned_annot;
     uint32_t n_big = 0;               // buckets with a coarse checksum table
+    // stage 2 (cm_circ.cuh): every ws-mer position of the contig sorted by (hash, position); in `owned`
+    uint32_t *circ_pos = nullptr, *circ_off = nullptr;
+    int circ_ws = 0;
 };
 
 struct cm_gpu_ctx {
@@ -283,6 +286,8 @@ static void free_index(ContigHost &c) {
     c.d = ContigDev();
     c.loaded = false;
     c.n_big = 0;
+    c.circ_pos = c.circ_off = nullptr;
+    c.circ_ws = 0;
 }
 // a contig that shared contexts may be reading cannot be replaced under them
 static int check_reload(cm_gpu_ctx *ctx, ContigHost *ch, int contig_id) {
@@ -1216,6 +1221,7 @@ extern "C" int cm_gpu_seed_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, con
 #include "cm_index_io.cuh"
 #include "cm_noalloc.cuh"
 #include "cm_annot_io.cuh"
+#include "cm_circ.cuh"
 
 // the hot-path kernels, loaded on the current device (cudaFuncGetAttributes forces the lazy load)
 static void preload_kernels() {

@@ -257,6 +257,24 @@ int cm_gpu_extend_batch(cm_gpu_ctx *ctx, int contig_id, int mode, uint32_t n, co
                         const int32_t *r_qpos, const int32_t *iv_a, const int32_t *iv_b, const int32_t *dir, cm_mate *lmm,
                         cm_mate *rmm, int32_t *ret);
 
+/* Stage 2, first piece: the split-read re-seeding and chaining of ProcessCirc::chaining
+ * (src/process_circ.cpp:678-737) -- RegionalHashTable look-ups of every `step`-th window_size-mer of seq[qspos-1 .. qepos-1]
+ * inside one gene (src/hash_table.cpp:58-112: positions relative to the gene start, a k-mer with more than 1000 hits in
+ * the gene has none; more than seedLim hits: none), chain_seeds_sorted_kbest2 (src/chain.cpp:310-539) and the cut at the
+ * first chain that misses more k-mers than its predecessor.  One problem per row: the read as ProcessCirc passes it
+ * (remain_seq, already oriented), the 1-based inclusive range [qspos, qepos] of its unmapped part, and the gene
+ * [gene_start, gene_end] in contig coordinates (GeneInfo::start / end of gtf_parser.get_gene_overlap).
+ * Outputs as cm_gpu_chain_batch: chain_count[n] (bc.best_chain_count after the cut), kmer_cnt[n] (rows without N; may be
+ * NULL), score / chain_len [n][max_chain_len], fragments (rpos in contig coordinates = shift + info, qpos) [n][max_chain_len][F];
+ * F >= (max_read_len - window_size) / step + 1, at most 128; fragment len is always window_size.
+ * cm_gpu_build_circ_index builds the per-contig window_size-mer index the look-ups run on (4 bytes per base, once per
+ * contig, on the root context; cm_gpu_circ_chain_batch builds it on first use when called on a root context). */
+int cm_gpu_build_circ_index(cm_gpu_ctx *ctx, int contig_id, int window_size);
+int cm_gpu_circ_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride, const uint32_t *qspos,
+                            const uint32_t *qepos, const uint32_t *gene_start, const uint32_t *gene_end, int window_size, int step,
+                            int F, int32_t *chain_count, int32_t *kmer_cnt, float *score, uint32_t *chain_len,
+                            uint32_t *frag_rpos, int32_t *frag_qpos);
+
 /* Alignment kernels, one problem per row (src/align.h:165-176):
  *   kind 0: DropAlignment::local_alignment_right_sc  (src/align.cpp:669)
  *   kind 1: DropAlignment::local_alignment_left_sc   (:694)

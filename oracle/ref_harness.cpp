@@ -19,6 +19,8 @@
 #include "match_read.h"
 #include "utils.h"
 #include "fastq_parser.h"
+#include "hash_table.h"
+#include "process_circ.h"
 #undef private
 #undef protected
 
@@ -472,4 +474,65 @@ int cmref_align(int kind, uint32_t n, const char *s, const uint16_t *n_s, const 
     return 0;
 }
 
+
+// Stage 2: ProcessCirc::chaining (process_circ.cpp:678-737) on one RegionalHashTable per gene, built the way
+// get_hash_table does (:814-830: pac2char_otf of the gene, create_table(seq, 0, len)).  One table object is reused:
+// create_table resets it (hash_table.cpp:58-59).
+static ProcessCirc *g_pc = NULL;
+static RegionalHashTable *g_ht = NULL;
+static uint32_t g_ht_s = 0, g_ht_e = 0;
+int cmref_circ_chain(uint32_t n, const char *seqs, uint32_t stride, const uint32_t *qspos, const uint32_t *qepos,
+                     const uint32_t *gene_start, const uint32_t *gene_end, int ws, int step, int F, int32_t *chain_count,
+                     float *score, uint32_t *chain_len, uint32_t *frag_rpos, int32_t *frag_qpos) {
+    if (!g_pc) {
+        for (int m = 1; m <= 2; m++) {   // the constructor sorts the last round's remain files
+            char fn[FILE_NAME_MAX_LEN];
+            sprintf(fn, "%s_1_remain_R%d.fastq", outputFilename, m);
+            FILE *f = fopen(fn, "w");
+            if (f) fclose(f);
+        }
+        finalCleaning = false;
+        g_pc = new ProcessCirc(1, ws);
+    }
+    if (g_pc->window_size != ws) return -1;
+    g_pc->step = step;
+    std::vector<char> row(stride + 1);
+    for (uint32_t i = 0; i < n; i++) {
+        const uint32_t gs = gene_start[i], ge = gene_end[i];
+        const int gene_len = (int) (ge - gs + 1);
+        if (!g_ht || gs != g_ht_s || ge != g_ht_e) {
+            std::vector<char> gene_seq(gene_len + 1);
+            gene_seq[gene_len] = 0;
+            if (!genome_seeder.pac2char_otf(gs, gene_len, gene_seq.data())) return -2;
+            if (!g_ht) g_ht = new RegionalHashTable(ws, gs, ge);
+            g_ht->gene_spos = gs;
+            g_ht->gene_epos = ge;
+            g_ht->create_table(gene_seq.data(), 0, gene_len);
+            g_ht_s = gs;
+            g_ht_e = ge;
+        }
+        memcpy(row.data(), seqs + (size_t) i * stride, stride);
+        row[stride] = 0;
+        chain_list &bc = g_pc->bc1;
+        bc.best_chain_count = 0;
+        g_pc->chaining(qspos[i], qepos[i], g_ht, row.data(), gene_len, gs, bc);
+        chain_count[i] = bc.best_chain_count;
+        const size_t o = (size_t) i * maxChainLen;
+        for (int c = 0; c < maxChainLen; c++) {
+            score[o + c] = 0;
+            chain_len[o + c] = 0;
+            for (int f = 0; f < F; f++) { frag_rpos[(o + c) * F + f] = 0; frag_qpos[(o + c) * F + f] = 0; }
+        }
+        for (int c = 0; c < bc.best_chain_count; c++) {
+            score[o + c] = bc.chains[c].score;
+            chain_len[o + c] = bc.chains[c].chain_len;
+            for (uint32_t f = 0; f < bc.chains[c].chain_len && (int) f < F; f++) {
+                frag_rpos[(o + c) * F + f] = bc.chains[c].frags[f].rpos;
+                frag_qpos[(o + c) * F + f] = bc.chains[c].frags[f].qpos;
+                if (bc.chains[c].frags[f].len != ws) return -3;
+            }
+        }
+    }
+    return 0;
+}
 }  // extern "C"

@@ -175,6 +175,22 @@ class RefHarness:
                               g("iv_a"), g("iv_b"), g("dir"), vp(res["lmm"]), vp(res["rmm"]), vp(res["ret"]))
         return res
 
+    def circ_chain(self, prob: dict, ws: int = 8, step: int = 3) -> dict:
+        """ProcessCirc::chaining (src/process_circ.cpp:678) per row of `prob` (seqs, qspos, qepos, gene_start, gene_end) on the
+        RegionalHashTable of that gene."""
+        a = np.ascontiguousarray(prob["seqs"], np.uint8)
+        n, Cn = a.shape[0], self.params.max_chain_len
+        F = (self.params.max_read_len - ws) // step + 1
+        u = {k: np.ascontiguousarray(prob[k], np.uint32) for k in ("qspos", "qepos", "gene_start", "gene_end")}
+        out = dict(chain_count=np.zeros(n, np.int32), score=np.zeros((n, Cn), np.float32), chain_len=np.zeros((n, Cn), np.uint32),
+                   frag_rpos=np.zeros((n, Cn, F), np.uint32), frag_qpos=np.zeros((n, Cn, F), np.int32))
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        r = self.lib.cmref_circ_chain(C.c_uint32(n), vp(a), C.c_uint32(a.shape[1]), vp(u["qspos"]), vp(u["qepos"]), vp(u["gene_start"]),
+                                      vp(u["gene_end"]), ws, step, F, *[vp(out[k]) for k in ("chain_count", "score", "chain_len", "frag_rpos", "frag_qpos")])
+        if r != 0:
+            raise RuntimeError(f"cmref_circ_chain failed: {r}")
+        return out
+
     def seed(self, seqs: np.ndarray, lens: np.ndarray) -> dict:
         n, S = len(lens), self.S
         out = dict(qpos=np.zeros((n, S), np.int32), frag_count=np.zeros((n, S), np.uint32),

@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "../../circminer_b200/csrc/cm_pipeline.h"
+#include "../../circminer_b200/csrc/cm_circ.h"
 
 #pragma pack(push, 1)
 struct GeneralIndexPacked {
@@ -324,6 +325,53 @@ int hs_chain_batch(HsCtx *c, int contig_id, uint32_t n, const char *seqs, uint32
                 frag_rpos[((size_t) i * C + k) * F + f] = lf ? B.chain_frags[((size_t) s * C + k) * F + f].rpos : 0;
                 frag_qpos[((size_t) i * C + k) * F + f] = lf ? B.chain_frags[((size_t) s * C + k) * F + f].qpos : 0;
             }
+        }
+    }
+    return 0;
+}
+
+// ProcessCirc::chaining per row through the device functions of cm_circ.h; circ_pos / circ_off = the contig's ws-mer index
+// (positions sorted by (hash, position), run offsets), made by the caller
+int hs_circ_chain(HsCtx *c, int contig_id, const uint32_t *circ_pos, const uint32_t *circ_off, uint32_t n, const char *seqs, uint32_t stride,
+                  const uint32_t *qspos, const uint32_t *qepos, const uint32_t *gene_start, const uint32_t *gene_end, int ws, int step, int F,
+                  int32_t *chain_count, int32_t *kmer_cnt, float *score, uint32_t *chain_len, uint32_t *frag_rpos, int32_t *frag_qpos) {
+    DevView v = make_view(c, contig_id);
+    const CircIndex ix{circ_pos, circ_off, ws};
+    const int C = c->p.max_chain_len;
+    std::vector<double> dps;
+    std::vector<uint32_t> dpp;
+    std::vector<ChainRec> recs;
+    std::vector<FragDev> frags((size_t) C * F);
+    for (uint32_t i = 0; i < n; i++) {
+        uint32_t row_pos[CM_CIRC_MAX_ROWS], row_cnt[CM_CIRC_MAX_ROWS], row_off[CM_CIRC_MAX_ROWS], cells;
+        int32_t qp[CM_CIRC_MAX_ROWS];
+        const int kc = cm_circ_rows(ix, c->p, (const uint8_t *) seqs + (size_t) i * stride, qspos[i], qepos[i], gene_start[i], gene_end[i], step, F,
+                                    row_pos, row_cnt, qp, cells);
+        if (kmer_cnt) kmer_cnt[i] = kc;
+        const int T = cm_circ_trim(kc, row_cnt, row_off);
+        std::fill(frags.begin(), frags.end(), FragDev{0, 0});
+        ChainOut out;
+        int32_t cnt = 0;
+        out.count = &cnt;
+        out.score = score + (size_t) i * C;
+        out.len = chain_len + (size_t) i * C;
+        out.frags = frags.data();
+        out.F = F;
+        for (int k = 0; k < C; k++) { out.score[k] = 0.f; out.len[k] = 0; }
+        if (T > 0) {
+            const ChainGeomCirc g{ix.pos, gene_start[i], ws, qp};
+            dps.resize(cells + 1);
+            dpp.resize(cells + 1);
+            uint32_t nrec = cm_chain_dp_g(g, v, (int) qepos[i], T, row_pos, row_cnt, row_off, dps.data(), dpp.data(), (ChainRec *) nullptr, 0u, nullptr);
+            recs.resize(nrec + 1);
+            cm_chain_dp_g(g, v, (int) qepos[i], T, row_pos, row_cnt, row_off, dps.data(), dpp.data(), recs.data(), nrec, nullptr);
+            cm_chain_backtrack_g(g, v, T, row_pos, row_cnt, row_off, dps.data(), dpp.data(), recs.data(), nrec, out, gene_start[i]);
+            cm_circ_finish(kc, out);
+        }
+        chain_count[i] = cnt;
+        for (size_t q = 0; q < frags.size(); q++) {
+            frag_rpos[(size_t) i * C * F + q] = frags[q].rpos;
+            frag_qpos[(size_t) i * C * F + q] = frags[q].qpos;
         }
     }
     return 0;

@@ -107,6 +107,39 @@ class HostSim:
                                 _vp(out["chain_len"]), _vp(out["frag_rpos"]), _vp(out["frag_qpos"]))
         return out
 
+    def circ_chaining(self, contig_id, genome_ascii, seqs, qspos, qepos, gene_start, gene_end, window_size=8, step=3):
+        """ProcessCirc::chaining per row through cm_circ.h; the contig's ws-mer index is made here with numpy
+        (genome_ascii[p - 1] = base at 1-based p)."""
+        ws = window_size
+        g = np.ascontiguousarray(genome_ascii, np.uint8)
+        code = np.full(256, 4, np.int64)
+        for i, ch in enumerate(b"ACGT"):
+            code[ch] = i
+            code[ch + 32] = i
+        v = code[g]
+        nk = len(g) - ws + 1
+        bad = np.concatenate([[0], np.cumsum(v == 4)])
+        ok = (bad[ws:ws + nk] - bad[:nk]) == 0
+        key = np.zeros(nk, np.int64)
+        for j in range(ws):
+            key = key * 4 + (v[j:j + nk] & 3)
+        p0 = np.nonzero(ok)[0]
+        order = np.argsort(key[p0], kind="stable")
+        pos = np.ascontiguousarray(p0[order] + 1, np.uint32)
+        off = np.zeros(4 ** ws + 1, np.uint32)
+        off[1:] = np.cumsum(np.bincount(key[p0], minlength=4 ** ws))
+        a = np.ascontiguousarray(seqs, np.uint8)
+        n, Cn = a.shape[0], self.Cn
+        F = (self.params.max_read_len - ws) // step + 1
+        u = lambda x: np.ascontiguousarray(x, np.uint32)
+        qspos, qepos, gene_start, gene_end = u(qspos), u(qepos), u(gene_start), u(gene_end)
+        out = dict(chain_count=np.zeros(n, np.int32), kmer_cnt=np.zeros(n, np.int32), score=np.zeros((n, Cn), np.float32),
+                   chain_len=np.zeros((n, Cn), np.uint32), frag_rpos=np.zeros((n, Cn, F), np.uint32), frag_qpos=np.zeros((n, Cn, F), np.int32))
+        self.lib.hs_circ_chain(self.ctx, contig_id, _vp(pos), _vp(off), C.c_uint32(n), _vp(a), C.c_uint32(a.shape[1]), _vp(qspos), _vp(qepos),
+                               _vp(gene_start), _vp(gene_end), ws, step, F,
+                               *[_vp(out[k]) for k in ("chain_count", "kmer_cnt", "score", "chain_len", "frag_rpos", "frag_qpos")])
+        return out
+
     def process_read(self, contig_id, seqs1, seqs2, mreads, lens1=None, lens2=None):
         a1, l1 = _rows(seqs1, lens1)
         a2, l2 = _rows(seqs2, lens2)

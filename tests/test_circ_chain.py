@@ -1,0 +1,73 @@
+"""Stage 2, first piece: ProcessCirc::chaining -- RegionalHashTable look-ups inside one gene, chain_seeds_sorted_kbest2
+and the missing-k-mer cut -- against the reference run live (oracle/refdump.py --circ: the reference's own ProcessCirc::chaining on
+its own RegionalHashTable).  CPU: the device functions of csrc/cm_circ.h in the host build; GPU: cm_gpu_circ_chain_batch."""
+import numpy as np
+import pytest
+
+from conftest import has_ref
+from parity import live_dump
+
+KEYS = ("chain_count", "score", "chain_len", "frag_rpos", "frag_qpos")
+
+
+def _compare(got, dump, c):
+    want = {k: dump[f"c{c}_circ_r_{k}"] for k in KEYS}
+    for k in KEYS:
+        g, w = got[k], want[k]
+        bad = np.nonzero((g != w).reshape(len(w), -1).any(axis=1))[0]
+        assert len(bad) == 0, f"contig {c} {k}: {len(bad)} of {len(w)} problems differ, first {bad[:5]}: {g[bad[:2]]} vs {w[bad[:2]]}"
+    return want
+
+
+def _shape_checks(want, prob):
+    cnt = want["chain_count"]
+    assert (cnt > 0).sum() > len(cnt) // 3 and (cnt == 0).sum() > 10      # chains found, and problems without any
+    assert (cnt > 1).sum() > 5                                            # several chains survive the cut
+    assert want["chain_len"].max() >= 10                                  # long chains of overlapping 8-mers
+    short = prob["qepos"].astype(np.int64) - prob["qspos"].astype(np.int64) + 1 < 8
+    assert short.sum() > 3 and (cnt[short] == 0).all()
+
+
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_host_build_equals_process_circ_chaining(tmp_path):
+    from circminer_b200 import workload
+    from circminer_b200.api import default_params
+    from hostsim_api import HostSim
+    w = workload.prepare("T0", str(tmp_path / "t0"), contig_size=250_000)
+    dump = live_dump(str(tmp_path / "circ.npz"), workload="T0", contig_size=250_000, circ=700, no_stage_dumps=True)
+    hs = HostSim(default_params())
+    for c, seq in enumerate(w["contigs"]):
+        hs.build_contig(c, seq)
+        hs.load_annotation(c, w["flat"][c])
+    for c in range(int(dump["n_contigs"])):
+        prob = {k: dump[f"c{c}_circ_p_{k}"] for k in ("seqs", "qspos", "qepos", "gene_start", "gene_end")}
+        got = hs.circ_chaining(c, w["contigs"][c], **prob)
+        want = _compare(got, dump, c)
+        _shape_checks(want, prob)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_gpu_equals_process_circ_chaining(tmp_path):
+    from circminer_b200 import workload
+    from circminer_b200.api import Mapper, default_params
+    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000, n_pairs=2000)
+    dump = live_dump(str(tmp_path / "circ.npz"), workload="T1", contig_size=3_500_000, pairs=2000, circ=3000, no_stage_dumps=True)
+    m = Mapper(default_params())
+    workload.load_into(m, w)
+    for c in range(int(dump["n_contigs"])):
+        prob = {k: dump[f"c{c}_circ_p_{k}"] for k in ("seqs", "qspos", "qepos", "gene_start", "gene_end")}
+        got = m.circ_chaining(c, **prob)
+        want = _compare(got, dump, c)
+        _shape_checks(want, prob)
+        again = m.circ_chaining(c, **prob)       # the index is kept; a second call gives the same
+        for k in KEYS:
+            assert np.array_equal(got[k], again[k])
+    # a shared context reads the root's ws-mer index
+    child = Mapper(parent=m)
+    prob = {k: dump[f"c0_circ_p_{k}"][:200] for k in ("seqs", "qspos", "qepos", "gene_start", "gene_end")}
+    got = child.circ_chaining(0, **prob)
+    for k in KEYS:
+        assert np.array_equal(got[k], dump[f"c0_circ_r_{k}"][:200]), k
+    child.close()
+    m.close()
