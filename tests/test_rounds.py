@@ -111,3 +111,45 @@ def test_rounds_gpu_vs_reference_binary(t1_rounds, scan, chunk, monkeypatch):
     ms, per_round = m.rounds_ms()
     assert per_round[0] == n and len(per_round) >= 1 and ms[5] > 0
     m.close()
+
+
+# ---- C1 at its stated shape: one 2 Mb chromosome, 40 genes, 10 000 pairs 2x100, -k 20 -t 1 -P -z --------------
+@pytest.fixture(scope="module")
+def c1_binary(tmp_path_factory):
+    if not has_ref():
+        pytest.skip("oracle/_ref not built")
+    from circminer_b200 import workload
+    d = str(tmp_path_factory.mktemp("c1r") / "c1")
+    w = workload.prepare("C1", d, write_reads=True)
+    assert len(w["contigs"]) == 1 and len(w["contigs"][0]) == 2_000_000 and w["s1"].shape == (10_000, 100)
+    build_ref_index(w["fa"], 1_100_000_000)
+    out = os.path.join(d, "ref")
+    refbinary.run_reference(w["fa"], w["gtf"], w["fq1"], w["fq2"], out)
+    return w, out
+
+
+def test_c1_hostsim_vs_reference_binary(c1_binary):
+    from hostsim_api import HostSim
+    from circminer_b200.api import default_params, fresh_mreads
+    w, out = c1_binary
+    hs = HostSim(default_params())
+    hs.build_contig(0, w["contigs"][0])
+    hs.load_annotation(0, w["flat"][0])
+    n = len(w["s1"])
+    res = hs.map_rounds(w["s1"], w["s2"], fresh_mreads(n), 0, 1, snapshots=True)
+    check_rounds_against_binary(res, w, out, 1, 0)
+    types = set(np.unique(res["out"]["type"]).tolist())
+    assert {0, 3} <= types, types   # concordant and back-splice pairs
+
+
+@pytest.mark.gpu
+def test_c1_gpu_vs_reference_binary(c1_binary):
+    from circminer_b200 import workload
+    from circminer_b200.api import Mapper, default_params, fresh_mreads
+    w, out = c1_binary
+    m = Mapper(default_params())
+    workload.load_into(m, w)
+    n = len(w["s1"])
+    res = m.map_rounds(w["s1"], w["s2"], fresh_mreads(n), 0, 1, snapshots=True)
+    check_rounds_against_binary(res, w, out, 1, 0)
+    m.close()
