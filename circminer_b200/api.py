@@ -311,6 +311,22 @@ class Mapper:
                   "cm_gpu_circ_chain_batch")
         return out
 
+
+    def circ_exact(self, contig_id, prob: dict, window_size=8) -> dict:
+        """ProcessCirc::find_exact_coord per row (src/process_circ.cpp:739); `prob` holds arrays named as the C arguments
+        (seqs, r1_spos, r1_epos, r2_spos, r2_epos, dir, qspos, rlen, whole_len, chain_len, frag_rpos, frag_qpos)."""
+        a = np.ascontiguousarray(prob["seqs"], np.uint8)
+        n = a.shape[0]
+        u = {k: np.ascontiguousarray(prob[k], np.uint32) for k in ("r1_spos", "r1_epos", "r2_spos", "r2_epos", "qspos", "chain_len", "frag_rpos")}
+        s = {k: np.ascontiguousarray(prob[k], np.int32) for k in ("dir", "rlen", "whole_len", "frag_qpos")}
+        res = dict(pmm=np.zeros(n, MATE_DTYPE), ret=np.zeros(n, np.int32))
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        r = self.lib.cm_gpu_circ_exact_batch(self.ctx, contig_id, C.c_uint32(n), vp(a), C.c_uint32(a.shape[1]), vp(u["r1_spos"]), vp(u["r1_epos"]), vp(u["r2_spos"]), vp(u["r2_epos"]),
+               vp(s["dir"]), vp(u["qspos"]), vp(s["rlen"]), vp(s["whole_len"]), C.c_uint32(u["frag_rpos"].shape[1]), vp(u["chain_len"]),
+               vp(u["frag_rpos"]), vp(s["frag_qpos"]), window_size, vp(res["pmm"]), vp(res["ret"]))
+        self._chk(r, "cm_gpu_circ_exact_batch")
+        return res
+
     def annot_lookup(self, contig_id, pos, mlen, rlen) -> dict:
         """GTFParser look-ups per position (cm_gpu_annot_lookup_batch)."""
         pos = np.ascontiguousarray(pos, np.uint32)

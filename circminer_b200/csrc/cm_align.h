@@ -215,6 +215,86 @@ CM_HDN int cm_local_alignment(const uint8_t *s, int n, const uint8_t *t, int m, 
     return best.ed;
 }
 
+// EditDistAlignment::local_alignment_right_sc (rev = false, align.cpp:602-633) / _left_sc (rev = true, :635-667): the
+// aligner of stage 2's TransExtension (ProcessCirc: extension(0, EDIT_ALIGNMENT)).  s = reference text, t = read text:
+// unit-cost banded (or, for short texts, full) global DP, then the best cell over the last min(maxSc, m) + 1 columns
+// inside the band.  The reference scans columns m down to m - max_sclen and rows upward; candidates of different columns
+// never tie (same score and ed => same soft clip), so scanning the columns as they are produced picks the same one.
+CM_HDN int cm_edit_alignment_sc(const uint8_t *s, int n, const uint8_t *t, int m, bool rev, const cm_params &p, int &sc_len, int &indel,
+                                int &score, AlignStats *st) {
+    const int w = p.band_width, max_sclen = p.max_sc < m ? p.max_sc : m;
+    AlignCand best = cm_cand(p.max_ed + 1, p.max_sc + 1, w + 1);
+    if (st) st->edit_calls++;
+    uint64_t cells = 0;
+    if (w < 0 || n <= 2 * w || m <= w) {            // global_alignment: full table, rolling column over j
+        // only rows <= j + w are read below and a row depends on the rows above it: rows past m + w are not computed
+        const int nn = (w >= 0 && m + w < n) ? m + w : n;
+        if (nn <= CM_FULLDP_MAX) {
+            uint32_t col[CM_FULLDP_MAX + 1];
+            for (int i = 0; i <= nn; i++) col[i] = (uint32_t) i;
+            for (int j = 0; j <= m; j++) {
+                if (j > 0) {
+                    uint32_t diag = col[0];
+                    col[0] = (uint32_t) j;
+                    const uint8_t tc = cm_at(t, m, j - 1, rev);
+                    for (int i = 1; i <= nn; i++) {
+                        const uint32_t up = col[i];
+                        uint32_t v = diag + (cm_base_eq(cm_at(s, n, i - 1, rev), tc) ? 0u : 1u);
+                        const uint32_t a = col[i - 1] + 1, b = up + 1;
+                        v = v < a ? v : a;
+                        v = v < b ? v : b;
+                        diag = up;
+                        col[i] = v;
+                    }
+                    cells += (uint64_t) nn;
+                }
+                if (j >= m - max_sclen) {
+                    const int i0 = j - w > 0 ? j - w : 0, i1 = j + w < nn ? j + w : nn;
+                    for (int i = i0; i <= i1; i++)
+                        if (col[i] <= (uint32_t) p.max_ed) cm_cand_update(best, cm_cand((int) col[i], m - j, j - i));
+                }
+            }
+        }
+    } else {
+        // band: column j holds rows i in [j-w, j+w]; slot d = i - j + w + 1, slots 0 and 2w+2 are the guard lines
+        uint32_t prev[CM_BANDSZ], cur[CM_BANDSZ];
+        const int B = 2 * w + 3;
+        for (int d = 0; d < B; d++) prev[d] = CM_DPTINF;
+        for (int i = 0; i <= w; i++) prev[i + w + 1] = (uint32_t) i;   // column 0
+        for (int j = 0; j <= m; j++) {
+            if (j > 0) {
+                for (int d = 0; d < B; d++) cur[d] = CM_DPTINF;
+                if (j <= w) cur[-j + w + 1] = (uint32_t) j;                // row 0
+                const uint8_t tc = cm_at(t, m, j - 1, rev);
+                const int i0 = j - w < 1 ? 1 : j - w, i1 = j + w > n ? n : j + w;
+                for (int i = i0; i <= i1; i++) {
+                    const int d = i - j + w + 1;
+                    uint32_t v = prev[d] + (cm_base_eq(cm_at(s, n, i - 1, rev), tc) ? 0u : 1u);
+                    const uint32_t a = cur[d - 1] + 1, b = prev[d + 1] + 1;
+                    v = v < a ? v : a;
+                    v = v < b ? v : b;
+                    cur[d] = v;
+                }
+                cells += (uint64_t) (i1 >= i0 ? i1 - i0 + 1 : 0);
+                for (int d = 0; d < B; d++) prev[d] = cur[d];
+            }
+            if (j >= m - max_sclen) {
+                const int i0 = j - w > 0 ? j - w : 0, i1 = j + w < n ? j + w : n;
+                for (int i = i0; i <= i1; i++) {
+                    const uint32_t v = prev[i - j + w + 1];
+                    if (v <= (uint32_t) p.max_ed) cm_cand_update(best, cm_cand((int) v, m - j, j - i));
+                }
+            }
+        }
+    }
+    if (st) st->edit_cells += cells;
+    if (m <= p.max_ed) cm_cand_update(best, cm_cand(m, 0, 0));   // very small text that cannot pass the threshold
+    score = m - best.sclen - 2 * best.ed;
+    sc_len = best.sclen;
+    indel = best.indel;
+    return best.ed;
+}
+
 // One-side band (columns j in [i, i+W] of row i) in registers: slot d = j - i + 1, updated in place (its own old
 // value = dp[i-1][j-1], old slot d+1 = dp[i-1][j], new slot d-1 = dp[i][j-1]); the W+1 characters of t under the band
 // slide by one per row.  Same arithmetic and guards as the run-time-indexed loop in cm_one_side_banded.

@@ -263,3 +263,95 @@ extern "C" int cm_gpu_circ_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t 
 #undef CIRC_CUDA
     return CM_OK;
 }
+
+// ---- ProcessCirc::find_exact_coord, one thread per problem -------------------------------------------------------------
+struct CircExactIn {
+    uint32_t n;
+    const uint8_t *seqs;
+    uint32_t stride;
+    const uint32_t *r1_spos, *r1_epos, *r2_spos, *r2_epos, *qspos;
+    const int32_t *dir, *rlen, *whole_len;
+    int F;
+    const uint32_t *chain_len;
+    const FragDev *frags;
+};
+
+__global__ void __launch_bounds__(128) k_circ_exact(const __grid_constant__ DevView v, const __grid_constant__ CircExactIn in, cm_mate *pmm,
+                                                    int32_t *ret) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= in.n) return;
+    ExtCtx x;
+    ext_ctx_init(x, &v);
+    x.edit_mode = true;
+    ChainView bc;
+    bc.frags = in.frags + (size_t) i * in.F;
+    bc.chain_len = in.chain_len[i];
+    bc.aux = nullptr;
+    bc.spec = nullptr;
+    MateD a, b, pm;
+    mate_init(a, v.p);
+    mate_init(b, v.p);
+    mate_init(pm, v.p);
+    a.spos = in.r1_spos[i]; a.epos = in.r1_epos[i];
+    b.spos = in.r2_spos[i]; b.epos = in.r2_epos[i];
+    ret[i] = cm_circ_exact(x, a, b, pm, in.dir[i], in.qspos[i], in.seqs + (size_t) i * in.stride, in.rlen[i], in.whole_len[i], bc) ? 1 : 0;
+    cm_mate_export(pm, pmm[i]);
+}
+
+extern "C" int cm_gpu_circ_exact_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride, const uint32_t *r1_spos,
+                                       const uint32_t *r1_epos, const uint32_t *r2_spos, const uint32_t *r2_epos, const int32_t *dir,
+                                       const uint32_t *qspos, const int32_t *rlen, const int32_t *whole_len, uint32_t frag_slots,
+                                       const uint32_t *chain_len, const uint32_t *frag_rpos, const int32_t *frag_qpos, int window_size,
+                                       cm_mate *pmm, int32_t *ret) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n == 0) return CM_OK;
+    if (!seqs || !r1_spos || !r1_epos || !r2_spos || !r2_epos || !dir || !qspos || !rlen || !whole_len || !chain_len || !frag_rpos || !frag_qpos ||
+        !pmm || !ret)
+        return fail(ctx, CM_ERR_ARG, "null argument");
+    if (window_size < 4 || window_size > 12 || frag_slots < 1) return fail(ctx, CM_ERR_ARG, "window size outside 4..12 or no fragment slots");
+    for (uint32_t i = 0; i < n; i++) {
+        if (chain_len[i] < 1 || chain_len[i] > frag_slots) return fail(ctx, CM_ERR_ARG, "problem %u: chain of %u fragments (slots: %u)", i, chain_len[i], frag_slots);
+        if (qspos[i] < 1 || rlen[i] < 1 || qspos[i] - 1 + (uint32_t) rlen[i] > stride || whole_len[i] < 0 || (uint32_t) whole_len[i] > stride)
+            return fail(ctx, CM_ERR_ARG, "problem %u: read range outside the row", i);
+    }
+    cudaSetDevice(ctx->device);
+    DevView v;
+    int r = make_view(ctx, contig_id, true, v);
+    if (r != CM_OK) return r;
+    v.p.kmer = window_size;   // fragment length of the chains; the extension code reads nothing else from it
+    cudaStream_t st = ctx->stream;
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *q : tmp) cudaFree(q); };
+#define CIRC_TRY(x) do { if ((r = (x)) != CM_OK) { cleanup(); return r; } } while (0)
+#define CIRC_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return fail(ctx, CM_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e_)); } } while (0)
+    const size_t F = frag_slots;
+    uint8_t *d_seq = nullptr;
+    uint32_t *d_u = nullptr;
+    FragDev *d_fr = nullptr;
+    cm_mate *d_mm = nullptr;
+    int32_t *d_ret = nullptr;
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_seq, (size_t) n * stride + 64));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_u, (size_t) n * 9));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_fr, (size_t) n * F));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_mm, (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_ret, (size_t) n));
+    std::vector<FragDev> h_fr((size_t) n * F);
+    for (size_t q = 0; q < h_fr.size(); q++) { h_fr[q].rpos = frag_rpos[q]; h_fr[q].qpos = frag_qpos[q]; }
+    const void *srcs[9] = {r1_spos, r1_epos, r2_spos, r2_epos, qspos, dir, rlen, whole_len, chain_len};
+    CIRC_CUDA(cudaMemcpyAsync(d_seq, seqs, (size_t) n * stride, cudaMemcpyHostToDevice, st));
+    for (int k = 0; k < 9; k++) CIRC_CUDA(cudaMemcpyAsync(d_u + (size_t) k * n, srcs[k], (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_fr, h_fr.data(), h_fr.size() * sizeof(FragDev), cudaMemcpyHostToDevice, st));
+    CircExactIn in{n, d_seq, stride, d_u, d_u + n, d_u + 2 * (size_t) n, d_u + 3 * (size_t) n, d_u + 4 * (size_t) n,
+                   (const int32_t *) (d_u + 5 * (size_t) n), (const int32_t *) (d_u + 6 * (size_t) n), (const int32_t *) (d_u + 7 * (size_t) n),
+                   (int) F, d_u + 8 * (size_t) n, d_fr};
+    k_circ_exact<<<grid_for(n, 128), 128, 0, st>>>(v, in, d_mm, d_ret);
+    ctx->launches++;
+    CIRC_CUDA(cudaGetLastError());
+    CIRC_CUDA(cudaMemcpyAsync(pmm, d_mm, (size_t) n * sizeof(cm_mate), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(ret, d_ret, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaStreamSynchronize(st));
+    cleanup();
+#undef CIRC_TRY
+#undef CIRC_CUDA
+    return CM_OK;
+}

@@ -8,6 +8,9 @@
 // found by two bisections, and are chained in place -- the same ascending positions RegionalHashTable::add_loc collects.
 #pragma once
 #include "cm_chain.h"
+#include "cm_align.h"
+#include "cm_extend.h"
+#include "cm_filter.h"
 
 #define CM_CIRC_MAXHIT 1000   // MAXHIT, src/hash_table.cpp:6: a ws-mer with more hits in the gene has none
 
@@ -105,4 +108,51 @@ CM_HD void cm_circ_finish(int kmer_cnt, ChainOut &out) {
         out.score[j] = 0.f;
     }
     *out.count = after;
+}
+
+// ---- ProcessCirc::find_exact_coord (process_circ.cpp:739-789) ---------------------------------------------------------
+// same_transcript(segments, 3, common_tid) (src/utils.cpp:447-494): the first of the eight start / end combinations of the
+// three mates whose exon intervals all exist and share a transcript.  The three-interval overload (:356-376) intersects
+// the common transcripts of the first two intervals with the transcripts of the FIRST interval again -- the third is only
+// tested for NULL -- so common_tid is the two-interval set of (seg0, seg1): TidSet{iv0, iv1}.
+CM_HD bool cm_circ_same_transcript3(const AnnotDev &a, MateD &m0, MateD &m1, MateD &m2, TidSet &ts) {
+    cm_overlap_to_spos(a, m0); cm_overlap_to_spos(a, m1); cm_overlap_to_spos(a, m2);
+    cm_overlap_to_epos(a, m0); cm_overlap_to_epos(a, m1); cm_overlap_to_epos(a, m2);
+    for (int c0 = 0; c0 < 2; c0++)
+        for (int c1 = 0; c1 < 2; c1++)
+            for (int c2 = 0; c2 < 2; c2++) {
+                const int i0 = c0 ? m0.exons_epos : m0.exons_spos, i1 = c1 ? m1.exons_epos : m1.exons_spos,
+                          i2 = c2 ? m2.exons_epos : m2.exons_spos;
+                if (i0 < 0 || i1 < 0 || i2 < 0) continue;
+                if (cm_same_transcript(a, i0, i1)) { ts.iv_a = i0; ts.iv_b = i1; return true; }
+            }
+    ts.iv_a = ts.iv_b = -1;
+    return false;
+}
+
+// x.v->p.kmer must be the fragment length of the chain (window_size) and x.edit_mode set; r1 / r2 need spos and epos
+// (contig coordinates) only; pm starts as MatchedMate().  qspos is 1-based as in the reference call.
+CM_HDN bool cm_circ_exact(ExtCtx &x, MateD &r1, MateD &r2, MateD &pm, int dir, uint32_t qspos, const uint8_t *rseq, int rlen, int whole_len,
+                          const ChainView &bc) {
+    const cm_params &p = x.v->p;
+    const AnnotDev &a = x.v->a;
+    // set_mm (process_circ.cpp:1713-1752) = MatchedMate::set (src/common.cpp:154-161)
+    pm.spos = bc.frags[0].rpos;
+    pm.epos = bc.frags[bc.chain_len - 1].rpos + (uint32_t) p.kmer - 1;
+    pm.qspos = qspos;
+    pm.qepos = qspos + (uint32_t) rlen - 1;
+    pm.matched_len = (pm.qepos + 1 >= pm.qspos) ? (pm.qepos - pm.qspos + 1) : 0;
+    pm.dir = dir;
+    --qspos;
+    TidSet ts;
+    if (!cm_circ_same_transcript3(a, r1, r2, pm, ts)) return false;
+    pm.middle_ed = cm_calc_middle_ed(x, bc, p.max_ed, rseq, rlen);
+    if (pm.middle_ed > p.max_ed) return false;
+    pm.is_concord = false;
+    int err = pm.middle_ed;
+    pm.matched_len = (uint32_t) rlen;
+    const bool lok = cm_extend_chain_left(x, ts, bc, rseq + qspos, (int32_t) qspos, 0u /* MINLB */, pm, err);
+    const bool rok = cm_extend_chain_right(x, ts, bc, rseq, qspos == 0 ? rlen : whole_len, CM_MAXUB, pm, err);
+    cm_update_match_mate_info(lok, rok, err, pm, p);
+    return pm.type == CM_CONCRD;
 }

@@ -149,6 +149,7 @@ struct ExtCtx {
     const EndSpec *seed;    // pre-computed DPs of that end's transcript walk (nullable)
     EndSpec *capture;       // pre-alignment kernel only: where the walk's DPs are recorded (nullable)
     const uint8_t *tbase;   // strand row the t_off of seed / capture entries refer to
+    bool edit_mode;         // TransExtension(id, EDIT_ALIGNMENT): stage 2's extension (src/process_circ.cpp:25)
 };
 CM_HD void ext_ctx_init(ExtCtx &x, const DevView *v) {
     x.v = v;
@@ -157,6 +158,7 @@ CM_HD void ext_ctx_init(ExtCtx &x, const DevView *v) {
     x.seed = nullptr;
     x.capture = nullptr;
     x.tbase = nullptr;
+    x.edit_mode = false;
 }
 
 // The genome-text alignment problem of one chain end as extend_left / extend_right pose it in their
@@ -297,6 +299,7 @@ CM_HD void cm_spec_put(ExtCtx &x, const uint8_t *s, int n, const uint8_t *t, int
 }
 // DropAlignment::local_alignment_{right,left}_sc of reference text s against read text t
 CM_HD int cm_x_drop(ExtCtx &x, const uint8_t *s, int n, const uint8_t *t, int m, bool rev, int &sclen, int &indel, int &score) {
+    if (x.edit_mode) return cm_edit_alignment_sc(s, n, t, m, rev, x.v->p, sclen, indel, score, &x.st);   // alignment-> is virtual (src/align.h:170-171)
     const DropHint &h = x.hint;
     const bool hinted = h.valid && h.s == s && h.t == t && h.n == n && h.m == m && h.rev == (int) rev;
     if (!hinted) {
@@ -487,7 +490,8 @@ CM_HDN bool cm_extend_right(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &
     const uint8_t *ref;
     if (!consecutive && (ref = cm_pac2char(*x.v, orig_pos + 1, ref_len)) != nullptr) {
         int score;
-        min_ed = cm_drop_alignment_sc(ref, ref_len, seq, seq_len, false, p, sclen_best, indel, score, &x.st, &x.hint);
+        min_ed = x.edit_mode ? cm_edit_alignment_sc(ref, ref_len, seq, seq_len, false, p, sclen_best, indel, score, &x.st)
+                             : cm_drop_alignment_sc(ref, ref_len, seq, seq_len, false, p, sclen_best, indel, score, &x.st, &x.hint);
         if (min_ed <= ed_th && sclen_best <= p.max_sc) {
             ar_set(curr, orig_pos + (uint32_t) seq_len - (uint32_t) indel, min_ed, sclen_best, indel, seq_len, score);
             if (ar_update_by_score(best, curr, true)) {
@@ -661,7 +665,8 @@ CM_HDN bool cm_extend_left(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &p
     const uint8_t *ref;
     if (!consecutive && (ref = cm_pac2char(*x.v, orig_pos - (uint32_t) ref_len, ref_len)) != nullptr) {
         int score;
-        min_ed = cm_drop_alignment_sc(ref, ref_len, seq, seq_len, true, p, sclen_best, indel, score, &x.st, &x.hint);
+        min_ed = x.edit_mode ? cm_edit_alignment_sc(ref, ref_len, seq, seq_len, true, p, sclen_best, indel, score, &x.st)
+                             : cm_drop_alignment_sc(ref, ref_len, seq, seq_len, true, p, sclen_best, indel, score, &x.st, &x.hint);
         if (min_ed <= ed_th && sclen_best <= p.max_sc) {
             ar_set(curr, orig_pos - (uint32_t) seq_len + (uint32_t) indel, min_ed, sclen_best, indel, seq_len, score);
             if (ar_update_by_score(best, curr, false)) {

@@ -275,6 +275,19 @@ int cm_gpu_circ_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const ch
                             int F, int32_t *chain_count, int32_t *kmer_cnt, float *score, uint32_t *chain_len,
                             uint32_t *frag_rpos, int32_t *frag_qpos);
 
+/* Stage 2, second piece: ProcessCirc::find_exact_coord (src/process_circ.cpp:739-789) per row -- set_mm, the
+ * three-mate same_transcript (src/utils.cpp:447-494), calc_middle_ed and extend_chain_left / _right of stage 2's
+ * TransExtension(0, EDIT_ALIGNMENT), whose soft-clipping aligner is EditDistAlignment (src/align.cpp:602-667), and
+ * update_match_mate_info.  Inputs: the read as ProcessCirc passes it (remain_seq), the two mates of the pair by their contig
+ * coordinates (all the function reads of them), dir, qspos (1-based), rlen = length of the unmapped part, whole_len, and one
+ * chain of cm_gpu_circ_chain_batch (chain_len + fragments [n][frag_slots], fragment length window_size).
+ * Outputs: partial_mm (from MatchedMate() with the never-initialised fields at 0) and the return value. */
+int cm_gpu_circ_exact_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride, const uint32_t *r1_spos,
+                            const uint32_t *r1_epos, const uint32_t *r2_spos, const uint32_t *r2_epos, const int32_t *dir,
+                            const uint32_t *qspos, const int32_t *rlen, const int32_t *whole_len, uint32_t frag_slots,
+                            const uint32_t *chain_len, const uint32_t *frag_rpos, const int32_t *frag_qpos, int window_size,
+                            cm_mate *pmm, int32_t *ret);
+
 /* Alignment kernels, one problem per row (src/align.h:165-176):
  *   kind 0: DropAlignment::local_alignment_right_sc  (src/align.cpp:669)
  *   kind 1: DropAlignment::local_alignment_left_sc   (:694)

@@ -455,8 +455,10 @@ int cmref_align(int kind, uint32_t n, const char *s, const uint16_t *n_s, const 
                 uint32_t stride, const int32_t *aux, int32_t *out_ed, int32_t *out_sclen, int32_t *out_indel,
                 int32_t *out_score) {
     static DropAlignment *al = NULL;
-    if (!al) al = new DropAlignment();
+    static EditDistAlignment *eal = NULL;
+    if (!al) { al = new DropAlignment(); eal = new EditDistAlignment(); }
     al->init();
+    eal->init();
     std::vector<char> sb(stride + 8), tb(stride + 8);
     for (uint32_t i = 0; i < n; i++) {
         int ns = n_s[i], nt = n_t[i];
@@ -468,8 +470,10 @@ int cmref_align(int kind, uint32_t n, const char *s, const uint16_t *n_s, const 
         else if (kind == 2) ed = al->local_alignment_right(sb.data(), ns, tb.data(), nt, indel);
         else if (kind == 3) ed = al->local_alignment_left(sb.data(), ns, tb.data(), nt, indel);
         else if (kind == 4) ed = al->global_one_side_banded_alignment(sb.data(), ns, tb.data(), nt, aux[i]);
+        else if (kind == 5) ed = eal->local_alignment_right_sc(sb.data(), ns, tb.data(), nt, sc, indel);
+        else if (kind == 6) ed = eal->local_alignment_left_sc(sb.data(), ns, tb.data(), nt, sc, indel);
         out_ed[i] = ed; out_sclen[i] = sc; out_indel[i] = indel;
-        out_score[i] = (kind == 4) ? 0 : al->get_score();
+        out_score[i] = (kind == 4) ? 0 : (kind >= 5 ? eal->get_score() : al->get_score());
     }
     return 0;
 }
@@ -481,9 +485,7 @@ int cmref_align(int kind, uint32_t n, const char *s, const uint16_t *n_s, const 
 static ProcessCirc *g_pc = NULL;
 static RegionalHashTable *g_ht = NULL;
 static uint32_t g_ht_s = 0, g_ht_e = 0;
-int cmref_circ_chain(uint32_t n, const char *seqs, uint32_t stride, const uint32_t *qspos, const uint32_t *qepos,
-                     const uint32_t *gene_start, const uint32_t *gene_end, int ws, int step, int F, int32_t *chain_count,
-                     float *score, uint32_t *chain_len, uint32_t *frag_rpos, int32_t *frag_qpos) {
+static int circ_pc(int ws) {
     if (!g_pc) {
         for (int m = 1; m <= 2; m++) {   // the constructor sorts the last round's remain files
             char fn[FILE_NAME_MAX_LEN];
@@ -494,7 +496,37 @@ int cmref_circ_chain(uint32_t n, const char *seqs, uint32_t stride, const uint32
         finalCleaning = false;
         g_pc = new ProcessCirc(1, ws);
     }
-    if (g_pc->window_size != ws) return -1;
+    return g_pc->window_size == ws ? 0 : -1;
+}
+
+// ProcessCirc::find_exact_coord (process_circ.cpp:739-789) per row: the two mates of the pair are given by their contig
+// coordinates (all find_exact_coord reads of them), the chain as fragments of length ws
+int cmref_circ_exact(uint32_t n, const char *seqs, uint32_t stride, const uint32_t *r1_spos, const uint32_t *r1_epos, const uint32_t *r2_spos,
+                     const uint32_t *r2_epos, const int32_t *dir, const uint32_t *qspos, const int32_t *rlen, const int32_t *whole_len,
+                     uint32_t F, const uint32_t *cl, const uint32_t *rp, const int32_t *qp, int ws, cm_mate *pmm, int32_t *ret) {
+    if (circ_pc(ws) != 0) return -1;
+    std::vector<fragment_t> fr(F);
+    std::vector<char> row(stride + 8);
+    for (uint32_t i = 0; i < n; i++) {
+        chain_t bc;
+        bc.frags = fr.data(); bc.chain_len = cl[i]; bc.score = 0;
+        for (uint32_t f = 0; f < cl[i]; f++) { fr[f].rpos = rp[(size_t) i * F + f]; fr[f].qpos = qp[(size_t) i * F + f]; fr[f].len = ws; }
+        memcpy(row.data(), seqs + (size_t) i * stride, stride);
+        row[stride] = 0;
+        MatchedMate a, b, pm;
+        mate_fresh(a); mate_fresh(b); mate_fresh(pm);
+        a.spos = r1_spos[i]; a.epos = r1_epos[i];
+        b.spos = r2_spos[i]; b.epos = r2_epos[i];
+        ret[i] = g_pc->find_exact_coord(a, b, pm, dir[i], qspos[i], row.data(), rlen[i], whole_len[i], bc) ? 1 : 0;
+        mate_export(pm, &pmm[i]);
+    }
+    return 0;
+}
+
+int cmref_circ_chain(uint32_t n, const char *seqs, uint32_t stride, const uint32_t *qspos, const uint32_t *qepos,
+                     const uint32_t *gene_start, const uint32_t *gene_end, int ws, int step, int F, int32_t *chain_count,
+                     float *score, uint32_t *chain_len, uint32_t *frag_rpos, int32_t *frag_qpos) {
+    if (circ_pc(ws) != 0) return -1;
     g_pc->step = step;
     std::vector<char> row(stride + 1);
     for (uint32_t i = 0; i < n; i++) {

@@ -171,6 +171,52 @@ def circ_problems(h, L, n, seed):
     return dict(seqs=seqs, qspos=qs, qepos=qe, gene_start=a_gs, gene_end=a_ge)
 
 
+def circ_exact_problems(h, prob, res, seed, top=10):
+    """find_exact_coord problems from chaining results: every chain ProcessCirc would try (the first min(count, TOPCHAIN)),
+    with the pair's two mates placed in exon intervals of the chain's neighbourhood (common transcripts exist) or anywhere
+    in the gene (mostly none)."""
+    rng = np.random.default_rng(seed)
+    ann = h.annotation()
+    ivs, ive = ann["iv_spos"].astype(np.int64), ann["iv_epos"].astype(np.int64)
+    has_seg = np.diff(ann["iv_seg_off"].astype(np.int64)) > 0
+    L = prob["seqs"].shape[1]
+    rows = []
+    for i in np.nonzero(res["chain_count"] > 0)[0]:
+        for j in range(min(int(res["chain_count"][i]), top)):
+            rows.append((int(i), j))
+    n = len(rows)
+    F = res["frag_rpos"].shape[2]
+    out = dict(seqs=np.zeros((n, L), np.uint8), r1_spos=np.zeros(n, np.uint32), r1_epos=np.zeros(n, np.uint32), r2_spos=np.zeros(n, np.uint32),
+               r2_epos=np.zeros(n, np.uint32), dir=np.zeros(n, np.int32), qspos=np.zeros(n, np.uint32), rlen=np.zeros(n, np.int32),
+               whole_len=np.full(n, L, np.int32), chain_len=np.zeros(n, np.uint32), frag_rpos=np.zeros((n, F), np.uint32),
+               frag_qpos=np.zeros((n, F), np.int32))
+
+    def place(anchor, gs, ge):
+        if rng.random() < 0.75:
+            k = int(np.searchsorted(ivs, anchor, side="right")) - 1 + int(rng.integers(-2, 3))
+            k = min(max(k, 0), len(ivs) - 1)
+            if has_seg[k]:
+                s = int(rng.integers(ivs[k], ive[k] + 1))
+                return s, s + int(rng.integers(20, L))
+        s = int(rng.integers(gs, max(gs + 1, ge - L)))
+        return s, s + int(rng.integers(20, L))
+
+    for r, (i, j) in enumerate(rows):
+        cl = int(res["chain_len"][i, j])
+        out["seqs"][r] = prob["seqs"][i]
+        out["chain_len"][r] = cl
+        out["frag_rpos"][r] = res["frag_rpos"][i, j]
+        out["frag_qpos"][r] = res["frag_qpos"][i, j]
+        out["qspos"][r] = prob["qspos"][i]
+        out["rlen"][r] = int(prob["qepos"][i]) - int(prob["qspos"][i]) + 1
+        out["dir"][r] = 1 if rng.random() < 0.5 else -1
+        gs, ge = int(prob["gene_start"][i]), int(prob["gene_end"][i])
+        anchor = int(res["frag_rpos"][i, j, 0])
+        out["r1_spos"][r], out["r1_epos"][r] = place(anchor, gs, ge)
+        out["r2_spos"][r], out["r2_epos"][r] = place(anchor, gs, ge)
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", default="T0")
@@ -245,8 +291,14 @@ def main():
             prob = circ_problems(h, L, a.circ, 4000 + c)
             for k, v in prob.items():
                 out[f"c{c}_circ_p_{k}"] = v
-            for k, v in h.circ_chain(prob).items():
+            cres = h.circ_chain(prob)
+            for k, v in cres.items():
                 out[f"c{c}_circ_r_{k}"] = v
+            ex = circ_exact_problems(h, prob, cres, 5000 + c)
+            for k, v in ex.items():
+                out[f"c{c}_circx_p_{k}"] = v
+            for k, v in h.circ_exact(ex).items():
+                out[f"c{c}_circx_r_{k}"] = v
         if a.se:
             out[f"c{c}_se_state"] = h.process_se(s1, lens)
         mr, st = h.process_pe(s1, s2, lens, lens, mr)

@@ -377,6 +377,35 @@ int hs_circ_chain(HsCtx *c, int contig_id, const uint32_t *circ_pos, const uint3
     return 0;
 }
 
+// ProcessCirc::find_exact_coord per row through cm_circ_exact (same arguments as cm_gpu_circ_exact_batch)
+int hs_circ_exact(HsCtx *c, int contig_id, uint32_t n, const char *seqs, uint32_t stride, const uint32_t *r1_spos, const uint32_t *r1_epos,
+                  const uint32_t *r2_spos, const uint32_t *r2_epos, const int32_t *dir, const uint32_t *qspos, const int32_t *rlen,
+                  const int32_t *whole_len, uint32_t F, const uint32_t *chain_len, const uint32_t *frag_rpos, const int32_t *frag_qpos, int ws,
+                  cm_mate *pmm, int32_t *ret) {
+    DevView v = make_view(c, contig_id);
+    v.p.kmer = ws;
+    std::vector<FragDev> fr(F);
+    for (uint32_t i = 0; i < n; i++) {
+        ExtCtx x;
+        ext_ctx_init(x, &v);
+        x.edit_mode = true;
+        for (uint32_t f = 0; f < F; f++) fr[f] = FragDev{frag_rpos[(size_t) i * F + f], frag_qpos[(size_t) i * F + f]};
+        ChainView bc;
+        bc.frags = fr.data(); bc.chain_len = chain_len[i]; bc.aux = nullptr; bc.spec = nullptr;
+        MateD a, b, pm;
+        mate_init(a, v.p); mate_init(b, v.p); mate_init(pm, v.p);
+        a.spos = r1_spos[i]; a.epos = r1_epos[i];
+        b.spos = r2_spos[i]; b.epos = r2_epos[i];
+        ret[i] = cm_circ_exact(x, a, b, pm, dir[i], qspos[i], (const uint8_t *) seqs + (size_t) i * stride, rlen[i], whole_len[i], bc) ? 1 : 0;
+        cm_mate &o = pmm[i];
+        o.spos = pm.spos; o.epos = pm.epos; o.qspos = pm.qspos; o.qepos = pm.qepos; o.matched_len = pm.matched_len;
+        o.left_ed = pm.left_ed; o.middle_ed = pm.middle_ed; o.right_ed = pm.right_ed; o.sclen_left = pm.sclen_left; o.sclen_right = pm.sclen_right;
+        o.dir = pm.dir; o.type = pm.type;
+        o.is_concord = pm.is_concord; o.left_ok = pm.left_ok; o.right_ok = pm.right_ok; o.pad_ = 0;
+    }
+    return 0;
+}
+
 int hs_process_batch_pe(HsCtx *c, int contig_id, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
                         const uint16_t *len1, const uint16_t *len2, const cm_mread *in, cm_mread *out, int32_t *state,
                         cm_counters *ctr) {
@@ -467,6 +496,7 @@ int hs_align_batch(HsCtx *c, int kind, uint32_t n, const char *s, const uint16_t
         if (kind == 0 || kind == 1) ed = cm_drop_alignment_sc(si, n_s[i], ti, n_t[i], kind == 1, c->p, sc, indel, score, nullptr);
         else if (kind == 2 || kind == 3) ed = cm_local_alignment(si, n_s[i], ti, n_t[i], kind == 3, c->p, indel, score, nullptr);
         else if (kind == 4) ed = cm_one_side_banded(si, n_s[i], ti, n_t[i], aux[i], nullptr);
+        else if (kind == 5 || kind == 6) ed = cm_edit_alignment_sc(si, n_s[i], ti, n_t[i], kind == 6, c->p, sc, indel, score, nullptr);
         out_ed[i] = ed; out_sclen[i] = sc; out_indel[i] = indel; out_score[i] = score;
     }
     return 0;

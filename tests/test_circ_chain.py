@@ -8,6 +8,23 @@ from conftest import has_ref
 from parity import live_dump
 
 KEYS = ("chain_count", "score", "chain_len", "frag_rpos", "frag_qpos")
+XKEYS = ("seqs", "r1_spos", "r1_epos", "r2_spos", "r2_epos", "dir", "qspos", "rlen", "whole_len", "chain_len", "frag_rpos", "frag_qpos")
+MATE_FIELDS = ("spos", "epos", "qspos", "qepos", "matched_len", "left_ed", "middle_ed", "right_ed", "sclen_left", "sclen_right", "dir", "type",
+               "is_concord", "left_ok", "right_ok")
+
+
+def _compare_exact(engine, dump, c, min_concord):
+    """find_exact_coord on every chain ProcessCirc would try: the return value and every MatchedMate field of partial_mm."""
+    prob = {k: dump[f"c{c}_circx_p_{k}"] for k in XKEYS}
+    got = engine.circ_exact(c, prob)
+    want_ret, want = dump[f"c{c}_circx_r_ret"], dump[f"c{c}_circx_r_pmm"]
+    bad = np.nonzero(got["ret"] != want_ret)[0]
+    assert len(bad) == 0, f"contig {c}: find_exact_coord return differs on {len(bad)} of {len(want_ret)} problems, first {bad[:5]}"
+    for f in MATE_FIELDS:
+        bad = np.nonzero(got["pmm"][f] != want[f])[0]
+        assert len(bad) == 0, f"contig {c} partial_mm.{f}: {len(bad)} of {len(want)} differ, first {bad[:5]}: {got['pmm'][f][bad[:5]]} vs {want[f][bad[:5]]}"
+    assert (want_ret == 1).sum() >= min_concord and (want_ret == 0).sum() > 10, (int((want_ret == 1).sum()), len(want_ret))
+    return want
 
 
 def _compare(got, dump, c):
@@ -44,6 +61,7 @@ def test_host_build_equals_process_circ_chaining(tmp_path):
         got = hs.circ_chaining(c, w["contigs"][c], **prob)
         want = _compare(got, dump, c)
         _shape_checks(want, prob)
+        _compare_exact(hs, dump, c, 5)
 
 
 @pytest.mark.gpu
@@ -60,6 +78,8 @@ def test_gpu_equals_process_circ_chaining(tmp_path):
         got = m.circ_chaining(c, **prob)
         want = _compare(got, dump, c)
         _shape_checks(want, prob)
+        pm = _compare_exact(m, dump, c, 20)
+        assert {0, 9} <= set(np.unique(pm["type"]).tolist())   # CONCRD and CANDID partial mates
         again = m.circ_chaining(c, **prob)       # the index is kept; a second call gives the same
         for k in KEYS:
             assert np.array_equal(got[k], again[k])
