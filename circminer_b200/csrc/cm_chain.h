@@ -164,8 +164,9 @@ CM_HDN uint32_t cm_chain_dp(const DevView &v, int seq_len, int T, const uint32_t
 }
 
 // Back-tracking (chain.cpp:234-300) over the recorded improvements.
-// rpos_add: added to every reported position (the `shift` of chain_seeds_sorted_kbest2; the `repeats` test runs on the
-// shifted values on both sides of the comparison there, so it is unaffected)
+// rpos_add: added to every reported position (the `shift` of chain_seeds_sorted_kbest2).  There the `repeats` set holds the
+// SHIFTED positions of the emitted chains (chain.cpp:509-510) while the look-up key is the unshifted frags[].info (:494-495):
+// kept as it is -- with a non-zero shift the filter only fires when a gene-relative position happens to equal a contig position.
 template <class G>
 CM_HD void cm_chain_backtrack_g(const G &g, const DevView &v, int T, const uint32_t *row_pos_off, const uint32_t *row_cnt,
                                 const uint32_t *row_off, const double *dp_score, const uint32_t *dp_prev, const ChainRec *recs,
@@ -200,7 +201,7 @@ CM_HD void cm_chain_backtrack_g(const G &g, const DevView &v, int T, const uint3
             in_group++;
             if (best_count >= max_best) break;
             uint32_t loc = recs[r].loc;
-            uint32_t spos = g.at(row_pos_off[loc >> 16] + (loc & 0xFFFF)) + rpos_add;
+            uint32_t spos = g.at(row_pos_off[loc >> 16] + (loc & 0xFFFF));
             if (s < best_score) {
                 // `repeats`: rpos of every non-first fragment of the chains emitted so far.  A small Bloom
                 // filter answers most queries; the exact scan runs only on a filter hit.

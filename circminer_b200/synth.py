@@ -309,6 +309,61 @@ def make_reads(cfg: SynthConfig, chroms, genes, genome=None, avoid_n=False):
     return r1, r2, kind
 
 
+
+def split_read_problems(text, gene_start, gene_end, L, n, seed):
+    """Stage-2 (ProcessCirc::chaining) problems on one packed contig: rows shaped like the reads stage 2 re-maps (two pieces of
+    one gene joined out of order, a few substitutions), one piece twice, random rows, rows with N, short and empty ranges; genes
+    of every size, sometimes only a part of one.  text[p - 1] = base at 1-based contig position p (ASCII); genes in contig
+    coordinates.  -> dict(seqs, qspos, qepos, gene_start, gene_end)."""
+    rng = np.random.default_rng(seed)
+    gs, ge = np.asarray(gene_start).astype(np.int64), np.asarray(gene_end).astype(np.int64)
+    ref_len = len(text)
+    ok = np.nonzero((ge - gs + 1 >= 60) & (ge <= ref_len))[0]
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    seqs = np.zeros((n, L), np.uint8)
+    qs, qe, a_gs, a_ge = (np.zeros(n, np.uint32) for _ in range(4))
+    for i in range(n):
+        g = int(ok[rng.integers(len(ok))])
+        s, e = int(gs[g]), int(ge[g])
+        glen = e - s + 1
+        u = rng.random()
+        if u < 0.65:      # two pieces of the gene, second piece upstream of the first
+            l1 = int(rng.integers(20, L - 20))
+            l1 = min(l1, glen - 1)
+            l2 = min(L - l1, glen - 1)
+            p1 = s + int(rng.integers(0, glen - l1 + 1))
+            p2 = s + int(rng.integers(0, glen - l2 + 1))
+            row = np.concatenate([text[p1 - 1:p1 - 1 + l1], text[p2 - 1:p2 - 1 + l2]])
+            row = np.concatenate([row, acgt[rng.integers(0, 4, size=L - len(row))]])
+            mut = rng.random(L) < 0.01
+            row = np.where(mut, acgt[rng.integers(0, 4, size=L)], row)
+        elif u < 0.8:     # one piece, repeated twice (several hits per k-mer)
+            l1 = min(L // 2, glen)
+            p1 = s + int(rng.integers(0, glen - l1 + 1))
+            piece = text[p1 - 1:p1 - 1 + l1]
+            row = np.concatenate([piece, piece, acgt[rng.integers(0, 4, size=L)]])[:L]
+        else:
+            row = acgt[rng.integers(0, 4, size=L)]
+        if rng.random() < 0.15:
+            row = row.copy()
+            row[rng.integers(0, L, size=int(rng.integers(1, 4)))] = ord("N")
+        seqs[i] = row
+        v = rng.random()
+        if v < 0.3:
+            qs[i], qe[i] = 1, L
+        elif v < 0.6:
+            qs[i], qe[i] = 1, int(rng.integers(8, L))
+        elif v < 0.9:
+            qs[i], qe[i] = int(rng.integers(2, L - 8)), L
+        else:            # shorter than a window, or empty
+            qs[i] = int(rng.integers(1, L))
+            qe[i] = min(L, int(qs[i]) + int(rng.integers(-1, 8)))
+        if rng.random() < 0.1:   # a window that is only part of the gene, down to a few bases
+            e = min(e, s + int(rng.integers(3, 400)))
+        a_gs[i], a_ge[i] = s, e
+    return dict(seqs=seqs, qspos=qs, qepos=qe, gene_start=a_gs, gene_end=a_ge)
+
+
 def read_names(n: int, kind=None):
     w = max(7, len(str(n)))
     return [f"r{str(i).zfill(w)}" for i in range(n)]

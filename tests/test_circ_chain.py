@@ -91,3 +91,63 @@ def test_gpu_equals_process_circ_chaining(tmp_path):
         assert np.array_equal(got[k], dump[f"c0_circ_r_{k}"][:200]), k
     child.close()
     m.close()
+
+
+def _repeat_rich(tmp_path, run):
+    """C3's shape at 1/50 (Alu / L1-like families and tandem repeats inside genes): hundreds of equal-score chains per problem,
+    where chain_seeds_sorted_kbest2's `repeats` filter matters -- it looks up the gene-relative position in a set of shifted
+    ones (src/chain.cpp:494-495 vs :509-510), which is kept."""
+    from circminer_b200 import synth, workload
+    from oracle.cpu_baseline import ensure_ref_index
+    w = workload.prepare("C3s", str(tmp_path / "c3s"), n_pairs=1000)
+    p = workload.params_for("C3s")
+    flat = w["flat"][0]
+    prob = synth.split_read_problems(w["contigs"][0], flat["gene_start"], flat["gene_end"], w["s1"].shape[1], 1500, 77)
+    order = np.argsort(prob["gene_start"], kind="stable")
+    prob = {k: v[order] for k, v in prob.items()}
+    ensure_ref_index(w, "C3s", p.kmer)
+    np.savez(str(tmp_path / "prob.npz"), **prob)
+    code = ("import sys, json, numpy as np; sys.path.insert(0, %r)\n"
+            "from circminer_b200 import workload\n"
+            "from oracle.refharness import RefHarness\n"
+            "w = json.load(open(%r)); prob = dict(np.load(%r))\n"
+            "h = RefHarness(workload.params_for('C3s')); h.open(w['fa'], w['gtf'], %r); h.next_contig()\n"
+            "np.savez(%r, **h.circ_chain(prob))\n")
+    import json
+    import subprocess
+    import sys
+    from conftest import ROOT
+    json.dump(dict(fa=w["fa"], gtf=w["gtf"]), open(str(tmp_path / "w.json"), "w"))
+    subprocess.run([sys.executable, "-c", code % (ROOT, str(tmp_path / "w.json"), str(tmp_path / "prob.npz"), str(tmp_path / "ref"),
+                                                  str(tmp_path / "want.npz"))], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    want = np.load(str(tmp_path / "want.npz"))
+    got = run(w, p, prob)
+    for k in KEYS:
+        bad = np.nonzero((got[k] != want[k]).reshape(len(want[k]), -1).any(axis=1))[0]
+        assert len(bad) == 0, f"{k}: {len(bad)} of {len(want[k])} problems differ, first {bad[:5]}"
+    assert (want["chain_count"] == p.max_chain_len).sum() > 20   # problems with a full list of tied chains
+
+
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_host_build_chaining_in_repeat_rich_genes(tmp_path):
+    def run(w, p, prob):
+        from hostsim_api import HostSim
+        hs = HostSim(p)
+        hs.build_contig(0, w["contigs"][0])
+        hs.load_annotation(0, w["flat"][0])
+        return hs.circ_chaining(0, w["contigs"][0], **prob)
+    _repeat_rich(tmp_path, run)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_gpu_chaining_in_repeat_rich_genes(tmp_path):
+    def run(w, p, prob):
+        from circminer_b200.api import Mapper
+        m = Mapper(p)
+        m.build_contig(0, np.ascontiguousarray(w["contigs"][0]))
+        m.load_annotation(0, w["flat"][0])
+        got = m.circ_chaining(0, **prob)
+        m.close()
+        return got
+    _repeat_rich(tmp_path, run)
