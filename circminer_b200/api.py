@@ -296,13 +296,15 @@ class Mapper:
                                                g("dir"), _vp(res["lmm"]), _vp(res["rmm"]), _vp(res["ret"])), "cm_gpu_extend_batch")
         return res
 
-    def circ_chaining(self, contig_id, seqs, qspos, qepos, gene_start, gene_end, window_size=8, step=3) -> dict:
+    def circ_chaining(self, contig_id, seqs, qspos, qepos, gene_start, gene_end, window_size=8, step=3, F=None) -> dict:
         """ProcessCirc::chaining per row (src/process_circ.cpp:678; cm_gpu_circ_chain_batch): rows = remain_seq as ASCII codes."""
         a = np.ascontiguousarray(seqs, np.uint8)
         n, Cn = a.shape[0], self.Cn
-        F = (self.params.max_read_len - window_size) // step + 1
         u = lambda x: np.ascontiguousarray(x, np.uint32)
         qspos, qepos, gene_start, gene_end = u(qspos), u(qepos), u(gene_start), u(gene_end)
+        if F is None:   # fragment slots: what the longest range of the batch can need (the reference sizes by maxReadLength)
+            span = int((qepos.astype(np.int64) - qspos.astype(np.int64) + 1).max()) if n else 0
+            F = max(1, (max(span, window_size) - window_size) // step + 1)
         out = dict(chain_count=np.zeros(n, np.int32), kmer_cnt=np.zeros(n, np.int32), score=np.zeros((n, Cn), np.float32),
                    chain_len=np.zeros((n, Cn), np.uint32), frag_rpos=np.zeros((n, Cn, F), np.uint32), frag_qpos=np.zeros((n, Cn, F), np.int32))
         self._chk(self.lib.cm_gpu_circ_chain_batch(self.ctx, contig_id, C.c_uint32(n), _vp(a), C.c_uint32(a.shape[1]), _vp(qspos), _vp(qepos),

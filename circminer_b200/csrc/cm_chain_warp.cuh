@@ -14,47 +14,48 @@
 //    a second pass writes the records there -- the list is identical to the serial one.
 #pragma once
 
-__device__ __forceinline__ uint32_t cw_upper(const uint32_t *pu, uint32_t lo, uint32_t hi, uint32_t x) {
-    // first index in [lo, hi) with pu[idx] > x (hi when none)
+template <class G>
+__device__ __forceinline__ uint32_t cw_upper(const G &g, uint32_t base, uint32_t lo, uint32_t hi, uint32_t x) {
+    // first index in [lo, hi) with row[idx] > x (hi when none); row[idx] = g.at(base + idx)
     while (lo < hi) {
         uint32_t mid = (lo + hi) >> 1;
-        if (pu[mid] <= x) lo = mid + 1; else hi = mid;
+        if (g.at(base + mid) <= x) lo = mid + 1; else hi = mid;
     }
     return lo;
 }
 
 // One hit (t, i): the u / j loops of chain.cpp:139-212.  WRITE = false counts the improvements,
 // WRITE = true also stores them (up to `room` records) at out[0..].
-template <bool WRITE>
-__device__ __forceinline__ uint32_t cw_eval(const DevView &v, int T, int t, uint32_t i, uint32_t seg_start, uint32_t read_remain,
+template <bool WRITE, class G>
+__device__ __forceinline__ uint32_t cw_eval(const G &g, const DevView &v, int T, int t, uint32_t i, uint32_t seg_start, uint32_t read_remain,
                                             const uint32_t *row_pos_off, const uint32_t *row_cnt, const uint32_t *row_off,
                                             const uint32_t *lbv, const uint32_t *stv, const double *dp_score, double &best,
                                             uint32_t &best_prev, ChainRec *out, uint32_t room, uint64_t &nlinks) {
-    const int kmer = v.p.kmer;
-    const uint32_t *pos = v.c.pos;
+    const int kmer = g.kmer;
     const uint32_t seg_end = seg_start + kmer - 1;
     uint32_t max_lpos_lim = CM_MAXUB, max_exon_end = 0, nimp = 0;
     int ol_iv = -1;
     for (int u = t + 1; u < T; u++) {
         const uint32_t cu = row_cnt[u];
         if (cu == 0 || stv[u] >= cu) continue;
-        const uint32_t *pu = pos + row_pos_off[u];
-        if (seg_start + (uint32_t) v.p.max_intron_len < pu[stv[u]]) continue;
+        const uint32_t pu0 = row_pos_off[u];
+        auto pu = [&](uint32_t idx) { return g.at(pu0 + idx); };
+        if (seg_start + (uint32_t) v.p.max_intron_len < pu(stv[u])) continue;
         uint32_t j = lbv[u];
         if (j >= cu) continue;
         if (max_lpos_lim == CM_MAXUB)
             max_lpos_lim = cm_upper_bound(v.a, v.p, seg_start, (uint32_t) kmer, read_remain, max_exon_end, ol_iv);
-        const int distr = (u - t) * kmer - kmer;
-        while (j < cu && pu[j] <= max_lpos_lim) {
+        const int distr = g.qpos(u) - g.qpos(t) - kmer;
+        while (j < cu && pu(j) <= max_lpos_lim) {
             nlinks++;
             int genome_dist;
-            if (max_exon_end == 0 || (pu[j] + kmer - 1) <= max_exon_end) genome_dist = (int) (pu[j] - seg_end - 1);
+            if (max_exon_end == 0 || (pu(j) + kmer - 1) <= max_exon_end) genome_dist = (int) (pu(j) - seg_end - 1);
             else genome_dist = CM_INF;
             int distt, trans_dist;
             int gd = genome_dist - distr;
             if ((gd < 0 ? -gd : gd) <= v.p.max_ed) {
                 distt = genome_dist;
-            } else if (cm_check_junction(v.a, v.p, seg_start, pu[j], ol_iv, kmer, distr, trans_dist)) {
+            } else if (cm_check_junction(v.a, v.p, seg_start, pu(j), ol_iv, kmer, distr, trans_dist)) {
                 distt = trans_dist;
             } else {
                 j++;
@@ -78,34 +79,34 @@ __device__ __forceinline__ uint32_t cw_eval(const DevView &v, int T, int t, uint
 }
 
 // DP pass of one strand by one warp.  Returns the number of improvement records (all lanes).
-__device__ uint32_t cw_chain_dp(const DevView &v, int seq_len, int T, const uint32_t *row_pos_off, const uint32_t *row_cnt,
+template <class G>
+__device__ uint32_t cw_chain_dp(const G &g, const DevView &v, int seq_len, int T, const uint32_t *row_pos_off, const uint32_t *row_cnt,
                                 const uint32_t *row_off, double *dp_score, uint32_t *dp_prev, ChainRec *recs, uint32_t rec_cap,
                                 uint64_t &nlinks) {
     const unsigned FULL = 0xffffffffu;
     const uint32_t lane = threadIdx.x & 31u;
-    const int kmer = v.p.kmer;
-    const uint32_t *pos = v.c.pos;
+    const int kmer = g.kmer;
     for (int t = 0; t < T; t++)
         for (uint32_t i = lane; i < row_cnt[t]; i += 32) {
             dp_score[row_off[t] + i] = (double) kmer;
             dp_prev[row_off[t] + i] = CM_NOPREV;
         }
     uint32_t nrec = 0;
-    uint32_t lbv[CM_MAX_SEEDS], stv[CM_MAX_SEEDS], carry[CM_MAX_SEEDS];
+    uint32_t lbv[G::MAXROWS], stv[G::MAXROWS], carry[G::MAXROWS];
     for (int t = T - 2; t >= 0; t--) {
         const uint32_t ct = row_cnt[t];
         if (ct == 0) continue;
         __syncwarp();   // rows u > t are final and visible to every lane
-        const uint32_t read_remain = (uint32_t) (seq_len - t * kmer - kmer);
+        const uint32_t read_remain = (uint32_t) (seq_len - g.qpos(t) - kmer);
         for (int u = t + 1; u < T; u++) carry[u] = 0;
         for (uint32_t c0 = 0; c0 < ct; c0 += 32) {
             const uint32_t i = c0 + lane;
             const bool act = i < ct;
-            const uint32_t seg_start = act ? pos[row_pos_off[t] + i] : 0xFFFFFFFFu;
+            const uint32_t seg_start = act ? g.at(row_pos_off[t] + i) : 0xFFFFFFFFu;
             // cursors of every later row, uniformly over the warp: L(i) and the stale L(i-1)
             for (int u = t + 1; u < T; u++) {
                 const uint32_t cu = row_cnt[u];
-                uint32_t lb = cu ? cw_upper(pos + row_pos_off[u], 0, cu, seg_start) : 0;
+                uint32_t lb = cu ? cw_upper(g, row_pos_off[u], 0, cu, seg_start) : 0;
                 uint32_t st = __shfl_up_sync(FULL, lb, 1);
                 if (lane == 0) st = carry[u];
                 carry[u] = __shfl_sync(FULL, lb, 31);
@@ -116,7 +117,7 @@ __device__ uint32_t cw_chain_dp(const DevView &v, int seq_len, int T, const uint
             uint32_t best_prev = CM_NOPREV;
             uint32_t nimp = 0;
             uint64_t nl = 0;
-            if (act) nimp = cw_eval<false>(v, T, t, i, seg_start, read_remain, row_pos_off, row_cnt, row_off, lbv, stv, dp_score, best,
+            if (act) nimp = cw_eval<false>(g, v, T, t, i, seg_start, read_remain, row_pos_off, row_cnt, row_off, lbv, stv, dp_score, best,
                                            best_prev, nullptr, 0, nl);
             nlinks += nl;
             // slice of the record list for this lane
@@ -132,7 +133,7 @@ __device__ uint32_t cw_chain_dp(const DevView &v, int seq_len, int T, const uint
                     double b2 = (double) kmer;
                     uint32_t p2 = CM_NOPREV;
                     uint64_t nl2 = 0;
-                    cw_eval<true>(v, T, t, i, seg_start, read_remain, row_pos_off, row_cnt, row_off, lbv, stv, dp_score, b2, p2,
+                    cw_eval<true>(g, v, T, t, i, seg_start, read_remain, row_pos_off, row_cnt, row_off, lbv, stv, dp_score, b2, p2,
                                   recs + at, rec_cap - at, nl2);
                 }
             }
@@ -157,12 +158,14 @@ __device__ __forceinline__ double cw_max_double(double x) {
 
 // Back-tracking (chain.cpp:234-300) by one warp: the scans over the record list run 32 records at a time,
 // the per-chain work (repeats test, walk along the prev pointers) stays sequential in list order.
-__device__ void cw_chain_backtrack(const DevView &v, int T, const uint32_t *row_pos_off, const uint32_t *row_cnt, const uint32_t *row_off,
-                                   const double *dp_score, const uint32_t *dp_prev, const ChainRec *recs, uint32_t nrec, ChainOut out) {
+// rpos_add: see cm_chain_backtrack_g (the repeats look-up key stays unshifted, the stored positions are shifted)
+template <class G>
+__device__ void cw_chain_backtrack(const G &g, const DevView &v, int T, const uint32_t *row_pos_off, const uint32_t *row_cnt, const uint32_t *row_off,
+                                   const double *dp_score, const uint32_t *dp_prev, const ChainRec *recs, uint32_t nrec, ChainOut out,
+                                   uint32_t rpos_add) {
     const unsigned FULL = 0xffffffffu;
     const uint32_t lane = threadIdx.x & 31u;
-    const int kmer = v.p.kmer;
-    const uint32_t *pos = v.c.pos;
+    const int kmer = g.kmer;
     const uint32_t max_best = (uint32_t) v.p.max_chain_len;
     const double NONE = -1e300;
     uint32_t best_count = 0;
@@ -196,7 +199,7 @@ __device__ void cw_chain_backtrack(const DevView &v, int T, const uint32_t *row_
                 in_group++;
                 if (best_count >= max_best) { done = true; break; }
                 const uint32_t loc = __shfl_sync(FULL, my_loc, src);
-                const uint32_t spos = pos[row_pos_off[loc >> 16] + (loc & 0xFFFF)];
+                const uint32_t spos = g.at(row_pos_off[loc >> 16] + (loc & 0xFFFF));
                 if (s < best_score) {
                     // `repeats`: lane c scans the non-first fragments of emitted chain c (at most 30 chains)
                     bool rep = false;
@@ -210,8 +213,8 @@ __device__ void cw_chain_backtrack(const DevView &v, int T, const uint32_t *row_
                     uint32_t n = 0, cur = loc;
                     while (cur != CM_NOPREV) {
                         uint32_t row = cur >> 16, ind = cur & 0xFFFF;
-                        out.frags[j * out.F + n].rpos = pos[row_pos_off[row] + ind];
-                        out.frags[j * out.F + n].qpos = (int32_t) row * kmer;
+                        out.frags[j * out.F + n].rpos = g.at(row_pos_off[row] + ind) + rpos_add;
+                        out.frags[j * out.F + n].qpos = (int32_t) g.qpos((int) row);
                         n++;
                         cur = dp_prev[row_off[row] + ind];
                     }
@@ -227,8 +230,8 @@ __device__ void cw_chain_backtrack(const DevView &v, int T, const uint32_t *row_
             for (uint32_t i = 0; i < row_cnt[t]; i++) {
                 if (best_count >= max_best) break;
                 uint32_t j = best_count++;
-                out.frags[j * out.F].rpos = pos[row_pos_off[t] + i];
-                out.frags[j * out.F].qpos = t * kmer;
+                out.frags[j * out.F].rpos = g.at(row_pos_off[t] + i) + rpos_add;
+                out.frags[j * out.F].qpos = g.qpos(t);
                 out.score[j] = (float) dp_score[row_off[t] + i];
                 out.len[j] = 1;
             }
@@ -260,7 +263,8 @@ __global__ void __launch_bounds__(128) k_chain_warp(const __grid_constant__ DevV
     const uint32_t cap = cm_rec_cap(cells, rec_mult);
     ChainRec *r = recs + cm_rec_base(base, s, rec_mult);
     uint64_t links = 0;
-    const uint32_t nrec = cw_chain_dp(v, b.strand_len[s], T, row_pos_off, row_cnt, row_off, dp_score + base, dp_prev + base, r, cap, links);
+    const ChainGeomMain g{v.c.pos, v.p.kmer};
+    const uint32_t nrec = cw_chain_dp(g, v, b.strand_len[s], T, row_pos_off, row_cnt, row_off, dp_score + base, dp_prev + base, r, cap, links);
     if (nrec > cap) {
         if (lane == 0) {
             uint32_t k = atomicAdd(n_ovf, 1u);
@@ -274,7 +278,7 @@ __global__ void __launch_bounds__(128) k_chain_warp(const __grid_constant__ DevV
         out.len = b.chain_len + (size_t) s * b.C;
         out.frags = b.chain_frags + (size_t) s * b.C * b.F;
         out.F = b.F;
-        cw_chain_backtrack(v, T, row_pos_off, row_cnt, row_off, dp_score + base, dp_prev + base, r, nrec, out);
+        cw_chain_backtrack(g, v, T, row_pos_off, row_cnt, row_off, dp_score + base, dp_prev + base, r, nrec, out, 0u);
     }
     if (links) {
         cm_counters *c = ctr + (w & (CM_CTR_SLOTS - 1));

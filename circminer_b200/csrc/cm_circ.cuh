@@ -87,14 +87,18 @@ __global__ void k_circ_rows(const __grid_constant__ DevView v, const CircIndex i
     b.cells[i] = cells;
 }
 
-// chain_seeds_sorted_kbest2 + the cut of ProcessCirc::chaining, thread per problem.  list == nullptr: every problem, with
-// the record slice rec_base[i] .. + rec_cap[i]; a problem whose improvements outgrow its slice is appended to ovf (with the
-// number it needs) and left for a second launch over that list with exactly sized slices.
-__global__ void k_circ_chain(const __grid_constant__ DevView v, const CircIndex ix, const __grid_constant__ CircBatch b, const uint32_t *list,
-                             uint32_t n_list, const uint64_t *cell_base, double *dp_score, uint32_t *dp_prev, const uint64_t *rec_base,
-                             const uint32_t *rec_cap, ChainRec *recs, uint32_t *ovf, uint32_t *ovf_nrec, uint32_t *n_ovf, int F,
-                             int32_t *out_count, float *out_score, uint32_t *out_len, FragDev *out_frags) {
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+// chain_seeds_sorted_kbest2 + the cut of ProcessCirc::chaining, one WARP per problem (cm_chain_warp.cuh over the stage-2 row
+// geometry: the hits of a row are spread over the lanes).  A thread per problem is not enough here: a read that falls into a
+// tandem repeat of a gene has rows of up to seedLim hits that all lie within reach of each other (8-mers every 2 bp), about
+// 10^8 link evaluations for one problem -- seconds on one thread, and the whole batch waits for it.
+// list == nullptr: every problem, with the record slice rec_base[k] .. + rec_cap[k]; a problem whose improvements outgrow
+// its slice is appended to ovf (with the number it needs) and left for a second launch over that list with exact slices.
+__global__ void __launch_bounds__(128) k_circ_chain(const __grid_constant__ DevView v, const CircIndex ix, const __grid_constant__ CircBatch b,
+                                                    const uint32_t *list, uint32_t n_list, const uint64_t *cell_base, double *dp_score,
+                                                    uint32_t *dp_prev, const uint64_t *rec_base, const uint32_t *rec_cap, ChainRec *recs,
+                                                    uint32_t *ovf, uint32_t *ovf_nrec, uint32_t *n_ovf, int F, int32_t *out_count,
+                                                    float *out_score, uint32_t *out_len, FragDev *out_frags) {
+    const uint32_t k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     if (k >= n_list) return;
     const uint32_t i = list ? list[k] : k;
     const int C = v.p.max_chain_len;
@@ -109,22 +113,37 @@ __global__ void k_circ_chain(const __grid_constant__ DevView v, const CircIndex 
     out.len = out_len + (size_t) i * C;
     out.frags = out_frags + (size_t) i * C * F;
     out.F = F;
-    if (T <= 0) { *out.count = 0; return; }
+    if (T <= 0) {
+        if (lane == 0) *out.count = 0;
+        return;
+    }
     const ChainGeomCirc g{ix.pos, b.gene_start[i], ix.ws, b.qp + o};
     double *ds = dp_score + cell_base[i];
     uint32_t *dpv = dp_prev + cell_base[i];
     ChainRec *r = recs + rec_base[k];
     const uint32_t cap = rec_cap[k];
-    const uint32_t nrec = cm_chain_dp_g(g, v, (int) b.qepos[i], T, row_pos, row_cnt, row_off, ds, dpv, r, cap, nullptr);
+    uint64_t links = 0;
+    const uint32_t nrec = cw_chain_dp(g, v, (int) b.qepos[i], T, row_pos, row_cnt, row_off, ds, dpv, r, cap, links);
     if (nrec > cap) {
-        const uint32_t s = atomicAdd(n_ovf, 1u);
-        ovf[s] = i;
-        ovf_nrec[s] = nrec;
-        *out.count = -1;
+        if (lane == 0) {
+            const uint32_t s = atomicAdd(n_ovf, 1u);
+            ovf[s] = i;
+            ovf_nrec[s] = nrec;
+            *out.count = -1;
+        }
         return;
     }
-    cm_chain_backtrack_g(g, v, T, row_pos, row_cnt, row_off, ds, dpv, r, nrec, out, b.gene_start[i]);
-    cm_circ_finish(kmer_cnt, out);
+    cw_chain_backtrack(g, v, T, row_pos, row_cnt, row_off, ds, dpv, r, nrec, out, b.gene_start[i]);
+    if (lane == 0) cm_circ_finish(kmer_cnt, out);
+}
+
+// fragments as two planes (the layout of cm_gpu_chain_batch's outputs)
+__global__ void k_circ_split_frags(const FragDev *__restrict__ fr, size_t n, uint32_t *__restrict__ rpos, int32_t *__restrict__ qpos) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const FragDev f = fr[i];
+    rpos[i] = f.rpos;
+    qpos[i] = f.qpos;
 }
 
 static int circ_scan_u64(const std::vector<uint64_t> &in, std::vector<uint64_t> &out) {
@@ -161,6 +180,9 @@ extern "C" int cm_gpu_circ_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t 
     cudaStream_t st = ctx->stream;
     std::vector<void *> tmp;
     auto cleanup = [&]() { for (void *q : tmp) cudaFree(q); };
+    const bool verbose = getenv("CM_GPU_VERBOSE") != nullptr;
+    auto now = []() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double t_ph[6] = {now(), 0, 0, 0, 0, 0};
 #define CIRC_TRY(x) do { if ((r = (x)) != CM_OK) { cleanup(); return r; } } while (0)
 #define CIRC_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return fail(ctx, CM_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e_)); } } while (0)
     const int C = ctx->p.max_chain_len, R = F;
@@ -186,6 +208,7 @@ extern "C" int cm_gpu_circ_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t 
     std::vector<uint32_t> h_cells(n);
     CIRC_CUDA(cudaMemcpyAsync(h_cells.data(), d_cells, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
     CIRC_CUDA(cudaStreamSynchronize(st));
+    t_ph[1] = now();
     // arenas: dp cells back to back; records 3 per cell + 8 per problem (as the stage-1 kernel), exact on the second pass
     std::vector<uint64_t> cells64(h_cells.begin(), h_cells.end()), cell_base, recn(n), rec_base;
     std::vector<uint32_t> rec_cap(n);
@@ -219,13 +242,15 @@ extern "C" int cm_gpu_circ_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t 
     CIRC_CUDA(cudaMemsetAsync(d_olen, 0, (size_t) n * C * 4, st));
     CIRC_CUDA(cudaMemsetAsync(d_frags, 0, (size_t) n * C * F * sizeof(FragDev), st));
     uint32_t *d_novf = d_ovf + 2 * (size_t) n;
-    k_circ_chain<<<grid_for(n, 64), 64, 0, st>>>(v, ix, b, nullptr, n, d_cell_base, d_score, d_prev, d_rec_base, d_rec_cap, d_recs, d_ovf, d_ovf + n,
+    k_circ_chain<<<grid_for((size_t) n * 32, 128), 128, 0, st>>>(v, ix, b, nullptr, n, d_cell_base, d_score, d_prev, d_rec_base, d_rec_cap, d_recs, d_ovf, d_ovf + n,
                                                   d_novf, F, d_count, d_oscore, d_olen, d_frags);
     ctx->launches++;
     CIRC_CUDA(cudaGetLastError());
     uint32_t n_ovf = 0;
+    t_ph[2] = now();
     CIRC_CUDA(cudaMemcpyAsync(&n_ovf, d_novf, 4, cudaMemcpyDeviceToHost, st));
     CIRC_CUDA(cudaStreamSynchronize(st));
+    t_ph[3] = now();
     if (n_ovf) {
         std::vector<uint32_t> ovf(n_ovf), need(n_ovf);
         CIRC_CUDA(cudaMemcpy(ovf.data(), d_ovf, (size_t) n_ovf * 4, cudaMemcpyDeviceToHost));
@@ -244,21 +269,35 @@ extern "C" int cm_gpu_circ_chain_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t 
         CIRC_CUDA(cudaMemcpyAsync(d_cap2, need.data(), (size_t) n_ovf * 4, cudaMemcpyHostToDevice, st));
         CIRC_CUDA(cudaMemcpyAsync(d_list, ovf.data(), (size_t) n_ovf * 4, cudaMemcpyHostToDevice, st));
         CIRC_CUDA(cudaMemsetAsync(d_ovf2 + 2 * (size_t) n_ovf, 0, 8, st));
-        k_circ_chain<<<grid_for(n_ovf, 64), 64, 0, st>>>(v, ix, b, d_list, n_ovf, d_cell_base, d_score, d_prev, d_base2, d_cap2, d_recs2, d_ovf2,
+        k_circ_chain<<<grid_for((size_t) n_ovf * 32, 128), 128, 0, st>>>(v, ix, b, d_list, n_ovf, d_cell_base, d_score, d_prev, d_base2, d_cap2, d_recs2, d_ovf2,
                                                       d_ovf2 + n_ovf, d_ovf2 + 2 * (size_t) n_ovf, F, d_count, d_oscore, d_olen, d_frags);
         ctx->launches++;
         CIRC_CUDA(cudaGetLastError());
     }
+    if (verbose) { cudaStreamSynchronize(st); }
+    t_ph[4] = now();
     // fragments come back as two planes, like cm_gpu_chain_batch
-    std::vector<FragDev> h_frags((size_t) n * C * F);
+    const size_t nf = (size_t) n * C * F;
+    uint32_t *d_rp = nullptr;
+    int32_t *d_qp2 = nullptr;
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_rp, nf));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_qp2, nf));
+    k_circ_split_frags<<<grid_for(nf, 256), 256, 0, st>>>(d_frags, nf, d_rp, d_qp2);
+    ctx->launches++;
+    CIRC_CUDA(cudaGetLastError());
     CIRC_CUDA(cudaMemcpyAsync(chain_count, d_count, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
     if (kmer_cnt) CIRC_CUDA(cudaMemcpyAsync(kmer_cnt, d_kc, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
     CIRC_CUDA(cudaMemcpyAsync(score, d_oscore, (size_t) n * C * 4, cudaMemcpyDeviceToHost, st));
     CIRC_CUDA(cudaMemcpyAsync(chain_len, d_olen, (size_t) n * C * 4, cudaMemcpyDeviceToHost, st));
-    CIRC_CUDA(cudaMemcpyAsync(h_frags.data(), d_frags, h_frags.size() * sizeof(FragDev), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(frag_rpos, d_rp, nf * 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(frag_qpos, d_qp2, nf * 4, cudaMemcpyDeviceToHost, st));
     CIRC_CUDA(cudaStreamSynchronize(st));
-    for (size_t q = 0; q < h_frags.size(); q++) { frag_rpos[q] = h_frags[q].rpos; frag_qpos[q] = h_frags[q].qpos; }
     cleanup();
+    t_ph[5] = now();
+    if (verbose)
+        fprintf(stderr, "cm_gpu: circ chaining of %u problems: rows %.3f s, arenas + uploads %.3f s (%.1f M cells), chain kernel %.3f s, overflow pass (%u) %.3f s, "
+                "results to the host %.3f s\n", n, t_ph[1] - t_ph[0], t_ph[2] - t_ph[1], (double) cell_base[n] / 1e6, t_ph[3] - t_ph[2], n_ovf,
+                t_ph[4] - t_ph[3], t_ph[5] - t_ph[4]);
 #undef CIRC_TRY
 #undef CIRC_CUDA
     return CM_OK;

@@ -8,6 +8,7 @@ from conftest import has_ref
 from parity import live_dump
 
 KEYS = ("chain_count", "score", "chain_len", "frag_rpos", "frag_qpos")
+REF_F = (300 - 8) // 3 + 1   # fragment slots of the reference's chain lists: (maxReadLength - window_size) / step + 1
 XKEYS = ("seqs", "r1_spos", "r1_epos", "r2_spos", "r2_epos", "dir", "qspos", "rlen", "whole_len", "chain_len", "frag_rpos", "frag_qpos")
 MATE_FIELDS = ("spos", "epos", "qspos", "qepos", "matched_len", "left_ed", "middle_ed", "right_ed", "sclen_left", "sclen_right", "dir", "type",
                "is_concord", "left_ok", "right_ok")
@@ -75,18 +76,18 @@ def test_gpu_equals_process_circ_chaining(tmp_path):
     workload.load_into(m, w)
     for c in range(int(dump["n_contigs"])):
         prob = {k: dump[f"c{c}_circ_p_{k}"] for k in ("seqs", "qspos", "qepos", "gene_start", "gene_end")}
-        got = m.circ_chaining(c, **prob)
+        got = m.circ_chaining(c, F=REF_F, **prob)
         want = _compare(got, dump, c)
         _shape_checks(want, prob)
         pm = _compare_exact(m, dump, c, 20)
         assert {0, 9} <= set(np.unique(pm["type"]).tolist())   # CONCRD and CANDID partial mates
-        again = m.circ_chaining(c, **prob)       # the index is kept; a second call gives the same
+        again = m.circ_chaining(c, F=REF_F, **prob)       # the index is kept; a second call gives the same
         for k in KEYS:
             assert np.array_equal(got[k], again[k])
     # a shared context reads the root's ws-mer index
     child = Mapper(parent=m)
     prob = {k: dump[f"c0_circ_p_{k}"][:200] for k in ("seqs", "qspos", "qepos", "gene_start", "gene_end")}
-    got = child.circ_chaining(0, **prob)
+    got = child.circ_chaining(0, F=REF_F, **prob)
     for k in KEYS:
         assert np.array_equal(got[k], dump[f"c0_circ_r_{k}"][:200]), k
     child.close()
@@ -147,7 +148,7 @@ def test_gpu_chaining_in_repeat_rich_genes(tmp_path):
         m = Mapper(p)
         m.build_contig(0, np.ascontiguousarray(w["contigs"][0]))
         m.load_annotation(0, w["flat"][0])
-        got = m.circ_chaining(0, **prob)
+        got = m.circ_chaining(0, F=REF_F, **prob)
         m.close()
         return got
     _repeat_rich(tmp_path, run)
