@@ -65,6 +65,13 @@ MATE_DTYPE = np.dtype([("spos", "<u4"), ("epos", "<u4"), ("qspos", "<u4"), ("qep
                        ("left_ed", "<i4"), ("middle_ed", "<i4"), ("right_ed", "<i4"), ("sclen_left", "<i4"), ("sclen_right", "<i4"),
                        ("dir", "<i4"), ("type", "<i4"), ("is_concord", "u1"), ("left_ok", "u1"), ("right_ok", "u1"), ("pad_", "u1")])
 assert MATE_DTYPE.itemsize == 52
+# cm_circ_mate / cm_circ_res (include/cm_gpu.h): stage 2's MatchedMate with its cached exon look-ups, and CircRes::set_bp
+CIRC_MATE_DTYPE = np.dtype([("m", MATE_DTYPE), ("exons_spos", "<i4"), ("exons_epos", "<i4"), ("exon_ind_spos", "<i4"), ("exon_ind_epos", "<i4"),
+                            ("looked_up_spos", "u1"), ("looked_up_epos", "u1"), ("pad_", "u1", (2,))])
+assert CIRC_MATE_DTYPE.itemsize == 72
+CIRC_RES_DTYPE = np.dtype([("spos", "<u4"), ("epos", "<u4"), ("start_signal", "u1", (2,)), ("end_signal", "u1", (2,)), ("start_bp_ref", "u1", (2,)),
+                           ("end_bp_ref", "u1", (2,)), ("start_signal_n", "u1"), ("end_signal_n", "u1"), ("ref_n", "u1"), ("was_set", "u1")])
+assert CIRC_RES_DTYPE.itemsize == 20
 
 MREAD_COMPARE_FIELDS = [f for f in MREAD_DTYPE.names if f != "pad_"]
 
@@ -328,6 +335,23 @@ class Mapper:
                vp(u["frag_rpos"]), vp(s["frag_qpos"]), window_size, vp(res["pmm"]), vp(res["ret"]))
         self._chk(r, "cm_gpu_circ_exact_batch")
         return res
+
+
+    def circ_check(self, contig_id, rec: dict, window_size=8) -> dict:
+        """ProcessCirc::check_split_map (three mates) per row (src/process_circ.cpp:892; cm_gpu_circ_check_batch).  rec: remain_rows,
+        fullmap_rows, remain_len, fullmap_len, r1_partial, in_r1, in_r2, in_pm -> ret, cr and the mates as the call leaves them."""
+        rr = np.ascontiguousarray(rec["remain_rows"], np.uint8)
+        fr = np.ascontiguousarray(rec["fullmap_rows"], np.uint8)
+        n = rr.shape[0]
+        rl, fl = np.ascontiguousarray(rec["remain_len"], np.int32), np.ascontiguousarray(rec["fullmap_len"], np.int32)
+        rp = np.ascontiguousarray(rec["r1_partial"], np.uint8)
+        out = dict(r1=np.array(rec["in_r1"], CIRC_MATE_DTYPE), r2=np.array(rec["in_r2"], CIRC_MATE_DTYPE), pm=np.array(rec["in_pm"], CIRC_MATE_DTYPE),
+                   ret=np.zeros(n, np.int32), cr=np.zeros(n, CIRC_RES_DTYPE))
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        r = self.lib.cm_gpu_circ_check_batch(self.ctx, contig_id, C.c_uint32(n), vp(rr), vp(fr), C.c_uint32(rr.shape[1] if n else 0), vp(rl), vp(fl), vp(rp), vp(out["r1"]), vp(out["r2"]),
+               vp(out["pm"]), window_size, vp(out["ret"]), vp(out["cr"]))
+        self._chk(r, "cm_gpu_circ_check_batch")
+        return out
 
     def annot_lookup(self, contig_id, pos, mlen, rlen) -> dict:
         """GTFParser look-ups per position (cm_gpu_annot_lookup_batch)."""

@@ -2,6 +2,7 @@
 // (cm_circ.h has the device functions).  Included by cm_gpu.cu.
 #pragma once
 #include "cm_circ.h"
+#include "cm_circ_split.h"
 
 // key of the ws-mer starting at 1-based position P = tid + 1: its hash, or 4^ws when it holds a non-ACGT base or runs
 // past the end of the contig (sorted to the back and dropped)
@@ -388,6 +389,73 @@ extern "C" int cm_gpu_circ_exact_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t 
     CIRC_CUDA(cudaGetLastError());
     CIRC_CUDA(cudaMemcpyAsync(pmm, d_mm, (size_t) n * sizeof(cm_mate), cudaMemcpyDeviceToHost, st));
     CIRC_CUDA(cudaMemcpyAsync(ret, d_ret, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaStreamSynchronize(st));
+    cleanup();
+#undef CIRC_TRY
+#undef CIRC_CUDA
+    return CM_OK;
+}
+
+// ---- ProcessCirc::check_split_map (three mates) and everything under it, one thread per problem ------------------------------
+__global__ void __launch_bounds__(64) k_circ_check(const __grid_constant__ DevView v, uint32_t n, const uint8_t *__restrict__ remain_seq,
+                                                   const uint8_t *__restrict__ fullmap_seq, uint32_t stride, const int32_t *__restrict__ remain_len,
+                                                   const int32_t *__restrict__ fullmap_len, const uint8_t *__restrict__ r1_partial,
+                                                   cm_circ_mate *r1, cm_circ_mate *r2, cm_circ_mate *pm, int32_t *__restrict__ ret, cm_circ_res *cr) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    ret[i] = cm_circ_check_row(v, remain_seq + (size_t) i * stride, remain_len[i], fullmap_seq + (size_t) i * stride, fullmap_len[i],
+                               r1_partial[i] != 0, r1[i], r2[i], pm[i], cr[i]);
+}
+
+extern "C" int cm_gpu_circ_check_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *remain_seq, const char *fullmap_seq, uint32_t stride,
+                                       const int32_t *remain_len, const int32_t *fullmap_len, const uint8_t *r1_partial, cm_circ_mate *mm_r1,
+                                       cm_circ_mate *mm_r2, cm_circ_mate *partial_mm, int window_size, int32_t *ret, cm_circ_res *cr) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n == 0) return CM_OK;
+    if (!remain_seq || !fullmap_seq || !remain_len || !fullmap_len || !r1_partial || !mm_r1 || !mm_r2 || !partial_mm || !ret || !cr)
+        return fail(ctx, CM_ERR_ARG, "null argument");
+    if (window_size < 4 || window_size > 12) return fail(ctx, CM_ERR_ARG, "window size outside 4..12");
+    for (uint32_t i = 0; i < n; i++)
+        if (remain_len[i] < 0 || fullmap_len[i] < 0 || (uint32_t) remain_len[i] > stride || (uint32_t) fullmap_len[i] > stride)
+            return fail(ctx, CM_ERR_ARG, "problem %u: read longer than the row", i);
+    cudaSetDevice(ctx->device);
+    DevView v;
+    int r = make_view(ctx, contig_id, true, v);
+    if (r != CM_OK) return r;
+    v.p.kmer = window_size;
+    cudaStream_t st = ctx->stream;
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *q : tmp) cudaFree(q); };
+#define CIRC_TRY(x) do { if ((r = (x)) != CM_OK) { cleanup(); return r; } } while (0)
+#define CIRC_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return fail(ctx, CM_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e_)); } } while (0)
+    uint8_t *d_rs = nullptr, *d_fs = nullptr, *d_rp = nullptr;
+    int32_t *d_len = nullptr, *d_ret = nullptr;
+    cm_circ_mate *d_m = nullptr;
+    cm_circ_res *d_cr = nullptr;
+    const size_t bytes = (size_t) n * stride;
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_rs, bytes + 64));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_fs, bytes + 64));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_rp, (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_len, 2 * (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_ret, (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_m, 3 * (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_cr, (size_t) n));
+    CIRC_CUDA(cudaMemcpyAsync(d_rs, remain_seq, bytes, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_fs, fullmap_seq, bytes, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_rp, r1_partial, (size_t) n, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_len, remain_len, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_len + n, fullmap_len, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_m, mm_r1, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_m + n, mm_r2, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_m + 2 * (size_t) n, partial_mm, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
+    k_circ_check<<<grid_for(n, 64), 64, 0, st>>>(v, n, d_rs, d_fs, stride, d_len, d_len + n, d_rp, d_m, d_m + n, d_m + 2 * (size_t) n, d_ret, d_cr);
+    ctx->launches++;
+    CIRC_CUDA(cudaGetLastError());
+    CIRC_CUDA(cudaMemcpyAsync(mm_r1, d_m, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(mm_r2, d_m + n, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(partial_mm, d_m + 2 * (size_t) n, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(ret, d_ret, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(cr, d_cr, (size_t) n * sizeof(cm_circ_res), cudaMemcpyDeviceToHost, st));
     CIRC_CUDA(cudaStreamSynchronize(st));
     cleanup();
 #undef CIRC_TRY

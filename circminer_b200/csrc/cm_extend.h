@@ -111,10 +111,12 @@ struct ChainView {
     const EndSpec *spec;   // nullable: [0] left end, [1] right end; valid where aux->has_l / has_r
 };
 
-// common_tid of a MatePair: tids of interval iv_a that also occur in interval iv_b (iv_a < 0: empty)
+// common_tid of a MatePair: tids of interval iv_a that also occur in interval iv_b (iv_a == -1: empty).
+// iv_a <= -2: exactly one transcript, tid = -2 - iv_a (stage 2's split_realignment, src/process_circ.cpp:1254-1256)
 struct TidSet {
     int iv_a, iv_b;
 };
+CM_HD TidSet cm_tid_single(uint32_t tid) { TidSet t; t.iv_a = -2 - (int) tid; t.iv_b = -1; return t; }
 
 struct AlignMemoEntry {   // map<AllCoord, AlignRes> align_res (src/extend.cpp:299)
     uint32_t rspos, rlen, qspos, qlen;
@@ -478,6 +480,8 @@ CM_HDN bool cm_extend_right(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &
             if (cm_iv_has_tid(a, ts.iv_b, t))
                 cm_extend_right_trans(x, t, pos, ref_len, seq, seq_len, ed_th, ub, best, consecutive, memo);
         }
+    } else if (ts.iv_a <= -2) {
+        cm_extend_right_trans(x, (uint32_t) (-2 - ts.iv_a), pos, ref_len, seq, seq_len, ed_th, ub, best, consecutive, memo);
     }
     uint32_t best_rmpos = best.pos;
     int min_ed = best.ed;
@@ -653,6 +657,8 @@ CM_HDN bool cm_extend_left(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &p
             if (cm_iv_has_tid(a, ts.iv_b, t))
                 cm_extend_left_trans(x, t, pos, ref_len, seq, seq_len, ed_th, lb, best, consecutive, memo);
         }
+    } else if (ts.iv_a <= -2) {
+        cm_extend_left_trans(x, (uint32_t) (-2 - ts.iv_a), pos, ref_len, seq, seq_len, ed_th, lb, best, consecutive, memo);
     }
     uint32_t lmpos_best = best.pos;
     int min_ed = best.ed;

@@ -288,6 +288,33 @@ int cm_gpu_circ_exact_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const ch
                             const uint32_t *chain_len, const uint32_t *frag_rpos, const int32_t *frag_qpos, int window_size,
                             cm_mate *pmm, int32_t *ret);
 
+/* MatchedMate as stage 2's classification reads and writes it: the cm_mate fields plus the cached exon look-ups
+ * (looked_up_spos / _epos, exons_spos / _epos as indices into FlatIntervalTree::disjoint_intervals or -1, exon_ind_spos / _epos),
+ * which stay as they are when final_check trims the positions (src/process_circ.cpp:1158-1177). */
+typedef struct cm_circ_mate {
+    cm_mate m;
+    int32_t exons_spos, exons_epos, exon_ind_spos, exon_ind_epos;
+    uint8_t looked_up_spos, looked_up_epos, pad_[2];
+} cm_circ_mate;
+
+/* CircRes::set_bp (src/common.cpp:468-477): breakpoints, the two signals (0 or 2 characters) and the reference bases */
+typedef struct cm_circ_res {
+    uint32_t spos, epos;
+    uint8_t start_signal[2], end_signal[2], start_bp_ref[2], end_bp_ref[2];
+    uint8_t start_signal_n, end_signal_n, ref_n, was_set;
+} cm_circ_res;
+
+/* Stage 2, third piece: ProcessCirc::check_split_map(mm_r1, mm_r2, partial_mm, r1_partial, cr) (src/process_circ.cpp:892-919)
+ * with everything under it -- final_check (:1135-1341), both split_realignment overloads (:1343-1489),
+ * rescue_overlapping_bsj (:1491-1552), the four-mate check_split_map (:922-1133), get_junctions (src/utils.cpp:697-757).
+ * One problem per row: the three mates (in / out: final_check trims the full mate and fills look-up caches), r1_partial,
+ * remain_seq and fullmap_seq (rows of `stride` bytes) with their lengths.  Outputs: the return value (FR 0, RF 1, CR 20,
+ * NCR 21, MCR 22, UD 30; -1 when a fixed-size list of the device code overflowed and the row must be redone by the caller)
+ * and cr (was_set = 0 when the reference would not have called set_bp). */
+int cm_gpu_circ_check_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *remain_seq, const char *fullmap_seq, uint32_t stride,
+                            const int32_t *remain_len, const int32_t *fullmap_len, const uint8_t *r1_partial, cm_circ_mate *mm_r1,
+                            cm_circ_mate *mm_r2, cm_circ_mate *partial_mm, int window_size, int32_t *ret, cm_circ_res *cr);
+
 /* Alignment kernels, one problem per row (src/align.h:165-176):
  *   kind 0: DropAlignment::local_alignment_right_sc  (src/align.cpp:669)
  *   kind 1: DropAlignment::local_alignment_left_sc   (:694)

@@ -567,4 +567,140 @@ int cmref_circ_chain(uint32_t n, const char *seqs, uint32_t stride, const uint32
     }
     return 0;
 }
+
+// ---- stage 2, the single-split path with every check_split_map call recorded -------------------------------------------
+static void circ_mate_export(const MatchedMate &m, cm_circ_mate *o) {
+    FlatIntervalTree<UniqSeg> &T = gtf_parser.exons_int_map[contigNum];
+    const IntervalInfo<UniqSeg> *base = T.disjoint_intervals.data();
+    mate_export(m, &o->m);
+    o->exons_spos = m.exons_spos ? (int32_t) (m.exons_spos - base) : -1;
+    o->exons_epos = m.exons_epos ? (int32_t) (m.exons_epos - base) : -1;
+    o->exon_ind_spos = m.exon_ind_spos;
+    o->exon_ind_epos = m.exon_ind_epos;
+    o->looked_up_spos = m.looked_up_spos;
+    o->looked_up_epos = m.looked_up_epos;
+    o->pad_[0] = o->pad_[1] = 0;
+}
+static void circ_res_export(const CircRes &cr, bool was_set, cm_circ_res *o) {
+    memset(o, 0, sizeof(*o));
+    if (!was_set) return;
+    o->spos = cr.spos; o->epos = cr.epos;
+    o->start_signal_n = (uint8_t) cr.start_signal.size(); o->end_signal_n = (uint8_t) cr.end_signal.size();
+    for (size_t k = 0; k < 2; k++) {
+        if (k < cr.start_signal.size()) o->start_signal[k] = cr.start_signal[k];
+        if (k < cr.end_signal.size()) o->end_signal[k] = cr.end_signal[k];
+        if (k < cr.start_bp_ref.size()) o->start_bp_ref[k] = cr.start_bp_ref[k];
+        if (k < cr.end_bp_ref.size()) o->end_bp_ref[k] = cr.end_bp_ref[k];
+    }
+    o->ref_n = (uint8_t) (cr.start_bp_ref.size() == 2 && cr.end_bp_ref.size() == 2 ? 2 : 0);
+    o->was_set = 1;
+}
+
+// The control flow of ProcessCirc::call_circ_single_split (process_circ.cpp:360-483) over the reference's own member functions
+// (get_gene_overlap, RegionalHashTable, chaining, find_exact_coord, check_split_map), for every pair whose MatchedRead is a
+// CHIBSJ of the current contig (positions of `mr` are chromosome coordinates as process_read leaves them).  Every
+// check_split_map call is recorded: the three mates as they were handed in, r1_partial, the two oriented reads, what it
+// returned, the CircRes it filled and the mates as it left them.  best_type[i] = the type call_circ_single_split ends with
+// (NF = 40 when nothing was found), 0xFF.. when the pair was not a candidate.  Returns the number of records (<= cap).
+int cmref_circ_single(uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride, const uint16_t *len1, const uint16_t *len2,
+                      const cm_mread *mr_in, int ws, uint32_t cap, uint32_t *call_pair, uint8_t *r1_partial_out, char *remain_rows,
+                      char *fullmap_rows, int32_t *remain_len, int32_t *fullmap_len, cm_circ_mate *in_r1, cm_circ_mate *in_r2,
+                      cm_circ_mate *in_pm, int32_t *ret, cm_circ_res *cr_out, cm_circ_mate *out_r1, cm_circ_mate *out_r2,
+                      cm_circ_mate *out_pm, int32_t *best_type) {
+    if (circ_pc(ws) != 0) return -1;
+    ProcessCirc &pc = *g_pc;
+    uint32_t n_rec = 0;
+    std::vector<char> s1(stride + 8), s2(stride + 8), rc1(stride + 8), rc2(stride + 8);
+    for (uint32_t i = 0; i < n; i++) {
+        best_type[i] = -1;
+        MatchedRead mr;
+        mread_to_ref(&mr_in[i], &mr);
+        if (mr.type != CHIBSJ || (int) mr.contig_num != contigNum) continue;
+        const int l1 = len1[i], l2 = len2[i];
+        memcpy(s1.data(), seqs1 + (size_t) i * stride, l1); s1[l1] = 0;
+        memcpy(s2.data(), seqs2 + (size_t) i * stride, l2); s2[l2] = 0;
+        revcomp(s1.data(), l1, rc1.data()); rc1[l1] = 0;
+        revcomp(s2.data(), l2, rc2.data()); rc2[l2] = 0;
+        // call_circ (:334-358)
+        pc.fullmap_seq = NULL; pc.remain_seq = NULL; pc.r1_seq = NULL; pc.r2_seq = NULL;
+        pc.fullmap_seq_len = 0; pc.remain_seq_len = 0; pc.r1_seq_len = 0; pc.r2_seq_len = 0;
+        const bool r1_partial = mr.mlen_r1 < mr.mlen_r2;
+        pc.remain_seq = r1_partial ? (mr.r1_forward ? s1.data() : rc1.data()) : (mr.r2_forward ? s2.data() : rc2.data());
+        pc.fullmap_seq = !r1_partial ? (mr.r1_forward ? s1.data() : rc1.data()) : (mr.r2_forward ? s2.data() : rc2.data());
+        pc.remain_seq_len = r1_partial ? l1 : l2;
+        pc.fullmap_seq_len = !r1_partial ? l1 : l2;
+        gtf_parser.chrloc2conloc(mr.chr_r1, mr.spos_r1, mr.epos_r1);
+        gtf_parser.chrloc2conloc(mr.chr_r2, mr.spos_r2, mr.epos_r2);
+        MatchedMate mm_r1(mr, 1, l1, r1_partial);
+        MatchedMate mm_r2(mr, 2, l2, !r1_partial);
+        // this constructor leaves is_concord / left_ok / right_ok unset (src/common.cpp:192-235); nothing on the path reads them
+        mm_r1.is_concord = mm_r1.left_ok = mm_r1.right_ok = false;
+        mm_r2.is_concord = mm_r2.left_ok = mm_r2.right_ok = false;
+        const MatchedMate &pmate = r1_partial ? mm_r1 : mm_r2;
+        const uint32_t plen = r1_partial ? l1 : l2;
+        const bool right_side = (pmate.qspos - 1) > (plen - pmate.qepos);
+        uint32_t qspos = right_side ? 1 : pmate.qepos + 1;
+        uint32_t qepos = right_side ? pmate.qspos - 1 : plen;
+        const int whole_seq_len = plen;
+        const int remain_len_i = qepos - qspos + 1;
+        best_type[i] = NF;
+        if (qepos < qspos || remain_len_i < ws) continue;
+        const IntervalInfo<GeneInfo> *gene_info = gtf_parser.get_gene_overlap(mm_r1.spos, false);
+        if (gene_info == NULL) continue;
+        int best = NF;
+        bool done = false;
+        for (unsigned int g = 0; g < gene_info->seg_list.size() && !done; ++g) {
+            const GeneInfo &gi = gene_info->seg_list[g];
+            const uint32_t gene_len = gi.end - gi.start + 1;
+            if (!g_ht || gi.start != g_ht_s || gi.end != g_ht_e) {
+                std::vector<char> gene_seq(gene_len + 1);
+                gene_seq[gene_len] = 0;
+                if (!genome_seeder.pac2char_otf(gi.start, gene_len, gene_seq.data())) return -2;
+                if (!g_ht) g_ht = new RegionalHashTable(ws, gi.start, gi.end);
+                g_ht->gene_spos = gi.start; g_ht->gene_epos = gi.end;
+                g_ht->create_table(gene_seq.data(), 0, gene_len);
+                g_ht_s = gi.start; g_ht_e = gi.end;
+            }
+            chain_list &bc = pc.bc1;
+            pc.chaining(qspos, qepos, g_ht, pc.remain_seq, gene_len, gi.start, bc);
+            if (bc.best_chain_count <= 0) continue;
+            const bool forward = r1_partial ? mr.r1_forward : mr.r2_forward;
+            const int dir = forward ? 1 : -1;
+            for (int j = 0; j < (bc.best_chain_count < 10 ? bc.best_chain_count : 10) && !done; ++j) {   // TOPCHAIN
+                MatchedMate partial_mm;
+                mate_fresh(partial_mm);
+                pc.find_exact_coord(mm_r1, mm_r2, partial_mm, dir, qspos, pc.remain_seq, remain_len_i, whole_seq_len, bc.chains[j]);
+                if (partial_mm.type != CONCRD) continue;
+                CircRes cr;
+                if (n_rec < cap) {
+                    call_pair[n_rec] = i;
+                    r1_partial_out[n_rec] = r1_partial;
+                    memset(remain_rows + (size_t) n_rec * stride, 0, stride);
+                    memset(fullmap_rows + (size_t) n_rec * stride, 0, stride);
+                    memcpy(remain_rows + (size_t) n_rec * stride, pc.remain_seq, pc.remain_seq_len);
+                    memcpy(fullmap_rows + (size_t) n_rec * stride, pc.fullmap_seq, pc.fullmap_seq_len);
+                    remain_len[n_rec] = pc.remain_seq_len; fullmap_len[n_rec] = pc.fullmap_seq_len;
+                    circ_mate_export(mm_r1, &in_r1[n_rec]); circ_mate_export(mm_r2, &in_r2[n_rec]); circ_mate_export(partial_mm, &in_pm[n_rec]);
+                }
+                char *keep_remain = pc.remain_seq, *keep_full = pc.fullmap_seq;   // the four-mate path repoints remain_seq (:973, :983)
+                const uint32_t keep_rl = pc.remain_seq_len;
+                const int type = pc.check_split_map(mm_r1, mm_r2, partial_mm, r1_partial, cr);
+                if (n_rec < cap) {
+                    ret[n_rec] = type;
+                    circ_res_export(cr, !cr.start_bp_ref.empty(), &cr_out[n_rec]);
+                    circ_mate_export(mm_r1, &out_r1[n_rec]); circ_mate_export(mm_r2, &out_r2[n_rec]); circ_mate_export(partial_mm, &out_pm[n_rec]);
+                }
+                n_rec++;
+                (void) keep_remain; (void) keep_full; (void) keep_rl;
+                if (type < CR) { best = type; done = true; break; }
+                if (type >= CR && type <= MCR && type < best) {
+                    best = type;
+                    if (type == CR) { done = true; break; }
+                }
+            }
+        }
+        best_type[i] = best;
+    }
+    return (int) (n_rec < cap ? n_rec : cap);
+}
 }  // extern "C"

@@ -186,6 +186,7 @@ def main():
     ap.add_argument("--lookups", type=int, default=0, help="random positions per contig for the GTFParser look-up dump")
     ap.add_argument("--extend", action="store_true", help="extension-stage dump: extend_both_mates / extend_chain_both_sides on chain pairs")
     ap.add_argument("--circ", type=int, default=0, help="stage-2 chaining problems per contig (ProcessCirc::chaining)")
+    ap.add_argument("--circ-single", action="store_true", help="stage 2: record every check_split_map call of the single-split path")
     ap.add_argument("--align", type=int, default=0, help="random alignment problems per kind")
     ap.add_argument("--no-stage-dumps", action="store_true", help="only process_read results (large workloads)")
     ap.add_argument("--out", required=True)
@@ -254,6 +255,12 @@ def main():
                 out[f"c{c}_circx_p_{k}"] = v
             for k, v in h.circ_exact(ex).items():
                 out[f"c{c}_circx_r_{k}"] = v
+        if a.circ_single:
+            # stage 1 on this contig first (fresh MatchedReads: every back-splice pair of this contig is a candidate), then the
+            # single-split path of stage 2 with every check_split_map call recorded
+            mr1, _ = h.process_pe(s1, s2, lens, lens, fresh_mreads(n, a.max_ed))
+            for k, v in h.circ_single(s1, s2, lens, lens, mr1).items():
+                out[f"c{c}_circs_{k}"] = v
         if a.se:
             out[f"c{c}_se_state"] = h.process_se(s1, lens)
         mr, st = h.process_pe(s1, s2, lens, lens, mr)

@@ -208,6 +208,31 @@ class RefHarness:
         assert r == 0, r
         return res
 
+    def circ_single(self, s1, s2, l1, l2, mreads, ws: int = 8, cap: int = 20000) -> dict:
+        """ProcessCirc::call_circ_single_split's path for every CHIBSJ pair of the current contig with every check_split_map call
+        recorded (cmref_circ_single)."""
+        from circminer_b200.api import CIRC_MATE_DTYPE, CIRC_RES_DTYPE
+        a1, a2 = np.ascontiguousarray(s1, np.uint8), np.ascontiguousarray(s2, np.uint8)
+        n, stride = a1.shape
+        l1, l2 = np.ascontiguousarray(l1, np.uint16), np.ascontiguousarray(l2, np.uint16)
+        mr = np.ascontiguousarray(mreads)
+        rec = dict(call_pair=np.zeros(cap, np.uint32), r1_partial=np.zeros(cap, np.uint8), remain_rows=np.zeros((cap, stride), np.uint8),
+                   fullmap_rows=np.zeros((cap, stride), np.uint8), remain_len=np.zeros(cap, np.int32), fullmap_len=np.zeros(cap, np.int32),
+                   in_r1=np.zeros(cap, CIRC_MATE_DTYPE), in_r2=np.zeros(cap, CIRC_MATE_DTYPE), in_pm=np.zeros(cap, CIRC_MATE_DTYPE),
+                   ret=np.zeros(cap, np.int32), cr=np.zeros(cap, CIRC_RES_DTYPE), out_r1=np.zeros(cap, CIRC_MATE_DTYPE),
+                   out_r2=np.zeros(cap, CIRC_MATE_DTYPE), out_pm=np.zeros(cap, CIRC_MATE_DTYPE))
+        best = np.zeros(n, np.int32)
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        order = ("call_pair", "r1_partial", "remain_rows", "fullmap_rows", "remain_len", "fullmap_len", "in_r1", "in_r2", "in_pm", "ret", "cr",
+                 "out_r1", "out_r2", "out_pm")
+        k = self.lib.cmref_circ_single(C.c_uint32(n), vp(a1), vp(a2), C.c_uint32(stride), vp(l1), vp(l2), vp(mr), ws, C.c_uint32(cap),
+                                       *[vp(rec[x]) for x in order], vp(best))
+        if k < 0:
+            raise RuntimeError(f"cmref_circ_single failed: {k}")
+        out = {x: rec[x][:k] for x in order}
+        out["best_type"] = best
+        return out
+
     def seed(self, seqs: np.ndarray, lens: np.ndarray) -> dict:
         n, S = len(lens), self.S
         out = dict(qpos=np.zeros((n, S), np.int32), frag_count=np.zeros((n, S), np.uint32),

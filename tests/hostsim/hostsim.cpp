@@ -10,6 +10,8 @@
 
 #include "../../circminer_b200/csrc/cm_pipeline.h"
 #include "../../circminer_b200/csrc/cm_circ.h"
+#define CM_CIRC_TRACE 1
+#include "../../circminer_b200/csrc/cm_circ_split.h"
 
 #pragma pack(push, 1)
 struct GeneralIndexPacked {
@@ -404,6 +406,23 @@ int hs_circ_exact(HsCtx *c, int contig_id, uint32_t n, const char *seqs, uint32_
         o.is_concord = pm.is_concord; o.left_ok = pm.left_ok; o.right_ok = pm.right_ok; o.pad_ = 0;
     }
     return 0;
+}
+
+// ProcessCirc::check_split_map (three mates) per row through cm_circ_check_row (arguments of cm_gpu_circ_check_batch)
+int hs_circ_check(HsCtx *c, int contig_id, uint32_t n, const char *remain_seq, const char *fullmap_seq, uint32_t stride, const int32_t *remain_len,
+                  const int32_t *fullmap_len, const uint8_t *r1_partial, cm_circ_mate *mm_r1, cm_circ_mate *mm_r2, cm_circ_mate *partial_mm, int ws,
+                  int32_t *ret, cm_circ_res *cr) {
+    DevView v = make_view(c, contig_id);
+    v.p.kmer = ws;
+    for (uint32_t i = 0; i < n; i++)
+        ret[i] = cm_circ_check_row(v, (const uint8_t *) remain_seq + (size_t) i * stride, remain_len[i], (const uint8_t *) fullmap_seq + (size_t) i * stride,
+                                   fullmap_len[i], r1_partial[i] != 0, mm_r1[i], mm_r2[i], partial_mm[i], cr[i]);
+    return 0;
+}
+
+// which paths of the stage-2 classification the rows so far reached (see CM_CIRC_HIT in cm_circ_split.h); resets the counters
+void hs_circ_trace(long *out16) {
+    for (int k = 0; k < 16; k++) { out16[k] = g_circ_trace[k]; g_circ_trace[k] = 0; }
 }
 
 int hs_process_batch_pe(HsCtx *c, int contig_id, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,

@@ -157,6 +157,24 @@ class HostSim:
         assert r == 0
         return res
 
+
+    def circ_check(self, contig_id, rec: dict, window_size=8) -> dict:
+        """ProcessCirc::check_split_map (three mates) per row (src/process_circ.cpp:892; cm_gpu_circ_check_batch).  rec: remain_rows,
+        fullmap_rows, remain_len, fullmap_len, r1_partial, in_r1, in_r2, in_pm -> ret, cr and the mates as the call leaves them."""
+        from circminer_b200.api import CIRC_MATE_DTYPE, CIRC_RES_DTYPE
+        rr = np.ascontiguousarray(rec["remain_rows"], np.uint8)
+        fr = np.ascontiguousarray(rec["fullmap_rows"], np.uint8)
+        n = rr.shape[0]
+        rl, fl = np.ascontiguousarray(rec["remain_len"], np.int32), np.ascontiguousarray(rec["fullmap_len"], np.int32)
+        rp = np.ascontiguousarray(rec["r1_partial"], np.uint8)
+        out = dict(r1=np.array(rec["in_r1"], CIRC_MATE_DTYPE), r2=np.array(rec["in_r2"], CIRC_MATE_DTYPE), pm=np.array(rec["in_pm"], CIRC_MATE_DTYPE),
+                   ret=np.zeros(n, np.int32), cr=np.zeros(n, CIRC_RES_DTYPE))
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        r = self.lib.hs_circ_check(self.ctx, contig_id, C.c_uint32(n), vp(rr), vp(fr), C.c_uint32(rr.shape[1] if n else 0), vp(rl), vp(fl), vp(rp), vp(out["r1"]), vp(out["r2"]),
+               vp(out["pm"]), window_size, vp(out["ret"]), vp(out["cr"]))
+        assert r == 0
+        return out
+
     def process_read(self, contig_id, seqs1, seqs2, mreads, lens1=None, lens2=None):
         a1, l1 = _rows(seqs1, lens1)
         a2, l2 = _rows(seqs2, lens2)

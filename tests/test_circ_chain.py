@@ -152,3 +152,62 @@ def test_gpu_chaining_in_repeat_rich_genes(tmp_path):
         m.close()
         return got
     _repeat_rich(tmp_path, run)
+
+
+# ---- third piece: check_split_map and what is under it ------------------------------------------------------------------------
+def _check_split_map(tmp_path, make_engine, pairs):
+    """Every check_split_map call the reference makes on the single-split path of the back-splice pairs of T1 (oracle/refdump.py
+    --circ-single: its own call_circ_single_split control flow over its own member functions, every call recorded): the return
+    value, the CircRes it fills (breakpoints, signals, reference bases) and the three mates as it leaves them."""
+    from circminer_b200 import workload
+    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000, n_pairs=pairs)
+    dump = live_dump(str(tmp_path / "cs.npz"), workload="T1", contig_size=3_500_000, pairs=pairs, circ_single=True, no_stage_dumps=True)
+    eng = make_engine(w)
+    seen = set()
+    total = 0
+    for c in range(int(dump["n_contigs"])):
+        rec = {k[len(f"c{c}_circs_"):]: dump[k] for k in dump.files if k.startswith(f"c{c}_circs_")}
+        n = len(rec["ret"])
+        total += n
+        if not n:
+            continue
+        got = eng.circ_check(c, rec)
+        bad = np.nonzero(got["ret"] != rec["ret"])[0]
+        assert len(bad) == 0, f"contig {c}: check_split_map differs on {len(bad)} of {n} calls, first {bad[:5]}: {got['ret'][bad[:5]]} vs {rec['ret'][bad[:5]]}"
+        for nm, k in (("r1", "out_r1"), ("r2", "out_r2"), ("pm", "out_pm"), ("cr", "cr")):
+            bad = np.nonzero(got[nm] != rec[k])[0]
+            assert len(bad) == 0, f"contig {c} {nm}: {len(bad)} of {n} differ, first {bad[:3]}: {got[nm][bad[:1]]} vs {rec[k][bad[:1]]}"
+        seen |= set(np.unique(rec["ret"]).tolist())
+    assert total > 100 and {0, 20, 30} <= seen, (total, seen)   # FR, CR and UD calls
+    return eng
+
+
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_host_build_equals_check_split_map(tmp_path):
+    def make(w):
+        from circminer_b200.api import default_params
+        from hostsim_api import HostSim
+        hs = HostSim(default_params())
+        for c, seq in enumerate(w["contigs"]):
+            hs.build_contig(c, seq)
+            hs.load_annotation(c, w["flat"][c])
+        return hs
+    hs = _check_split_map(tmp_path, make, 8000)
+    import ctypes as C
+    tr = (C.c_long * 16)()
+    hs.lib.hs_circ_trace(tr)
+    # both arms of final_check ran; the rescue / four-mate paths are rare on this data (reported, not required)
+    assert tr[0] > 10 and tr[1] > 50, list(tr)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_gpu_equals_check_split_map(tmp_path):
+    def make(w):
+        from circminer_b200 import workload
+        from circminer_b200.api import Mapper, default_params
+        m = Mapper(default_params())
+        workload.load_into(m, w)
+        return m
+    m = _check_split_map(tmp_path, make, 20000)
+    m.close()
