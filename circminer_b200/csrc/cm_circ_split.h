@@ -50,31 +50,31 @@ struct CircSplitCtx {          // the ProcessCirc members these functions read a
     int overflow;              // a fixed-size list was too small: the result is not to be used
 };
 
-struct CircSig {               // a string of 0 or 2 characters
-    uint8_t c[2];
-    uint8_t n;
+struct CircSig {               // a string of 0 or 2 characters, as scalars (no byte array to index)
+    uint32_t c0, c1, n;
 };
 CM_HD CircSig cm_sig2(const uint8_t *seq, int len, int i) {   // string() + seq[i] + seq[i + 1]
     CircSig s;
     s.n = 2;
-    s.c[0] = (i >= 0 && i < len) ? seq[i] : 0;
-    s.c[1] = (i + 1 >= 0 && i + 1 < len) ? seq[i + 1] : 0;
+    s.c0 = (i >= 0 && i < len) ? (uint32_t) seq[i] : 0u;
+    s.c1 = (i + 1 >= 0 && i + 1 < len) ? (uint32_t) seq[i + 1] : 0u;
     return s;
 }
-CM_HD CircSig cm_sig_empty() { CircSig s; s.n = 0; s.c[0] = s.c[1] = 0; return s; }
+CM_HD CircSig cm_sig_empty() { CircSig s; s.n = 0; s.c0 = s.c1 = 0; return s; }
 // get_consensus(s1, s2) (src/utils.cpp:759-769)
 CM_HD CircSig cm_sig_consensus(const CircSig &a, const CircSig &b) {
     CircSig r = cm_sig_empty();
     if (a.n != b.n) return r;
     r.n = a.n;
-    for (int i = 0; i < a.n; i++) r.c[i] = a.c[i] == b.c[i] ? a.c[i] : (uint8_t) 'N';
+    if (a.n >= 1) r.c0 = a.c0 == b.c0 ? a.c0 : (uint32_t) 'N';
+    if (a.n >= 2) r.c1 = a.c1 == b.c1 ? a.c1 : (uint32_t) 'N';
     return r;
 }
 CM_HD void cm_circ_set_bp(const DevView &v, CircResD &cr, uint32_t beg_bp, uint32_t end_bp, const CircSig &ss, const CircSig &es) {
     cr.spos = beg_bp;
     cr.epos = end_bp;
-    cr.ss_n = ss.n; cr.ss[0] = ss.c[0]; cr.ss[1] = ss.c[1];
-    cr.es_n = es.n; cr.es[0] = es.c[0]; cr.es[1] = es.c[1];
+    cr.ss_n = (uint8_t) ss.n; cr.ss[0] = (uint8_t) ss.c0; cr.ss[1] = (uint8_t) ss.c1;
+    cr.es_n = (uint8_t) es.n; cr.es[0] = (uint8_t) es.c0; cr.es[1] = (uint8_t) es.c1;
     // pac2char_otf(beg_bp, 2) / pac2char_otf(end_bp - 1, 2)
     const uint8_t *a = cm_pac2char(v, beg_bp, 2), *b = cm_pac2char(v, end_bp - 1, 2);
     cr.ref_n = (a && b) ? 2 : 0;
