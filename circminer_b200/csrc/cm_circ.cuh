@@ -322,7 +322,6 @@ __global__ void __launch_bounds__(128) k_circ_exact(const __grid_constant__ DevV
     if (i >= in.n) return;
     ExtCtx x;
     ext_ctx_init(x, &v);
-    x.edit_mode = true;
     ChainView bc;
     bc.frags = in.frags + (size_t) i * in.F;
     bc.chain_len = in.chain_len[i];

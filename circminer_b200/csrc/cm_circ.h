@@ -130,7 +130,7 @@ CM_HD bool cm_circ_same_transcript3(const AnnotDev &a, MateD &m0, MateD &m1, Mat
     return false;
 }
 
-// x.v->p.kmer must be the fragment length of the chain (window_size) and x.edit_mode set; r1 / r2 need spos and epos
+// x.v->p.kmer must be the fragment length of the chain (window_size); r1 / r2 need spos and epos
 // (contig coordinates) only; pm starts as MatchedMate().  qspos is 1-based as in the reference call.
 CM_HDN bool cm_circ_exact(ExtCtx &x, MateD &r1, MateD &r2, MateD &pm, int dir, uint32_t qspos, const uint8_t *rseq, int rlen, int whole_len,
                           const ChainView &bc) {
@@ -151,8 +151,8 @@ CM_HDN bool cm_circ_exact(ExtCtx &x, MateD &r1, MateD &r2, MateD &pm, int dir, u
     pm.is_concord = false;
     int err = pm.middle_ed;
     pm.matched_len = (uint32_t) rlen;
-    const bool lok = cm_extend_chain_left(x, ts, bc, rseq + qspos, (int32_t) qspos, 0u /* MINLB */, pm, err);
-    const bool rok = cm_extend_chain_right(x, ts, bc, rseq, qspos == 0 ? rlen : whole_len, CM_MAXUB, pm, err);
+    const bool lok = cm_extend_chain_left<true>(x, ts, bc, rseq + qspos, (int32_t) qspos, 0u /* MINLB */, pm, err);
+    const bool rok = cm_extend_chain_right<true>(x, ts, bc, rseq, qspos == 0 ? rlen : whole_len, CM_MAXUB, pm, err);
     cm_update_match_mate_info(lok, rok, err, pm, p);
     return pm.type == CM_CONCRD;
 }

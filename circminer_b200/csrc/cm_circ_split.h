@@ -117,8 +117,8 @@ CM_HDN int cm_circ_split_realign7(CircSplitCtx &c, uint32_t qcutpos, uint32_t be
     const uint32_t lb = beg_bp, ub = end_bp;
     AlignResD bl = ar_init(lb), br = ar_init(ub);
     const TidSet ts = cm_tid_single(tid);
-    const bool lok = cm_extend_left(x, ts, seq, lm_pos, (int) qcutpos - 1, p.max_ed - last_bp_err, lb, bl);
-    const bool rok = cm_extend_right(x, ts, seq + qcutpos + 1, rm_pos, (int) (seq_len - qcutpos - 1), p.max_ed - first_bp_err, ub, br);
+    const bool lok = cm_extend_left<true>(x, ts, seq, lm_pos, (int) qcutpos - 1, p.max_ed - last_bp_err, lb, bl);
+    const bool rok = cm_extend_right<true>(x, ts, seq + qcutpos + 1, rm_pos, (int) (seq_len - qcutpos - 1), p.max_ed - first_bp_err, ub, br);
     bl.ed += last_bp_err;
     br.ed += first_bp_err;
     if (lok && rok && bl.ed + br.ed <= p.max_ed) return bl.ed + br.ed;
@@ -342,8 +342,8 @@ CM_HDN int cm_circ_split_realign5(CircSplitCtx &c, uint32_t qcutpos, MateD &full
     uint32_t lm_pos = left.epos, rm_pos = right.spos;
     const uint32_t lb = right.spos, ub = left.epos;
     AlignResD bl = ar_init(lb), br = ar_init(ub);
-    const bool lok = cm_extend_left(x, ts, c.fullmap_seq, lm_pos, (int) qcutpos - 1, p.max_ed - last_bp_err, lb, bl);
-    const bool rok = cm_extend_right(x, ts, c.fullmap_seq + qcutpos + 1, rm_pos, (int) (flen - qcutpos - 1), p.max_ed - first_bp_err, ub, br);
+    const bool lok = cm_extend_left<true>(x, ts, c.fullmap_seq, lm_pos, (int) qcutpos - 1, p.max_ed - last_bp_err, lb, bl);
+    const bool rok = cm_extend_right<true>(x, ts, c.fullmap_seq + qcutpos + 1, rm_pos, (int) (flen - qcutpos - 1), p.max_ed - first_bp_err, ub, br);
     bl.ed += last_bp_err;
     br.ed += first_bp_err;
     CM_CIRC_HIT(4);
@@ -563,7 +563,6 @@ CM_HDN int cm_circ_check_row(const DevView &v, const uint8_t *remain_seq, int re
                              bool r1_partial, cm_circ_mate &r1, cm_circ_mate &r2, cm_circ_mate &pm, cm_circ_res &out) {
     ExtCtx x;
     ext_ctx_init(x, &v);
-    x.edit_mode = true;
     CircSplitCtx c;
     c.x = &x;
     c.remain_seq = remain_seq; c.remain_len = remain_len;

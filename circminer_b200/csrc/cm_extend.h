@@ -151,7 +151,6 @@ struct ExtCtx {
     const EndSpec *seed;    // pre-computed DPs of that end's transcript walk (nullable)
     EndSpec *capture;       // pre-alignment kernel only: where the walk's DPs are recorded (nullable)
     const uint8_t *tbase;   // strand row the t_off of seed / capture entries refer to
-    bool edit_mode;         // TransExtension(id, EDIT_ALIGNMENT): stage 2's extension (src/process_circ.cpp:25)
 };
 CM_HD void ext_ctx_init(ExtCtx &x, const DevView *v) {
     x.v = v;
@@ -160,7 +159,6 @@ CM_HD void ext_ctx_init(ExtCtx &x, const DevView *v) {
     x.seed = nullptr;
     x.capture = nullptr;
     x.tbase = nullptr;
-    x.edit_mode = false;
 }
 
 // The genome-text alignment problem of one chain end as extend_left / extend_right pose it in their
@@ -300,8 +298,12 @@ CM_HD void cm_spec_put(ExtCtx &x, const uint8_t *s, int n, const uint8_t *t, int
     e.ed = (int8_t) ed; e.sclen = (int16_t) sclen; e.indel = (int16_t) indel; e.score = score;
 }
 // DropAlignment::local_alignment_{right,left}_sc of reference text s against read text t
+// EDIT: the TransExtension was made with EDIT_ALIGNMENT (stage 2, src/process_circ.cpp:25): alignment-> is virtual
+// (src/align.h:170-171) and the soft-clipping aligner is EditDistAlignment's.  A template parameter of the whole extension tree
+// (default false), so that stage 1's kernels carry none of it.
+template <bool EDIT = false>
 CM_HD int cm_x_drop(ExtCtx &x, const uint8_t *s, int n, const uint8_t *t, int m, bool rev, int &sclen, int &indel, int &score) {
-    if (x.edit_mode) return cm_edit_alignment_sc(s, n, t, m, rev, x.v->p, sclen, indel, score, &x.st);   // alignment-> is virtual (src/align.h:170-171)
+    if (EDIT) return cm_edit_alignment_sc(s, n, t, m, rev, x.v->p, sclen, indel, score, &x.st);
     const DropHint &h = x.hint;
     const bool hinted = h.valid && h.s == s && h.t == t && h.n == n && h.m == m && h.rev == (int) rev;
     if (!hinted) {
@@ -346,13 +348,14 @@ CM_HDN bool cm_extend_right_middle(ExtCtx &x, uint32_t pos, uint32_t exon_len, c
 }
 
 // extend_right_end (src/extend.cpp:463-487)
+template <bool EDIT = false>
 CM_HDN void cm_extend_right_end(ExtCtx &x, uint32_t pos, uint32_t ref_len, const uint8_t *qseq, int qseq_len, int ed_th,
                                 AlignResD &best, AlignResD &curr, AlignResD &exon_res) {
     const cm_params &p = x.v->p;
     const uint8_t *ref = cm_pac2char(*x.v, pos + 1, (int) ref_len);
     if (!ref) return;
     int sclen, indel, score;
-    int edit_dist = cm_x_drop(x, ref, (int) ref_len, qseq, qseq_len, false, sclen, indel, score);
+    int edit_dist = cm_x_drop<EDIT>(x, ref, (int) ref_len, qseq, qseq_len, false, sclen, indel, score);
     uint32_t new_rmpos = pos + (uint32_t) qseq_len - (uint32_t) indel;
     ar_set(exon_res, new_rmpos, edit_dist, sclen, indel, qseq_len, score);
     int actual_mapped_bp = qseq_len - sclen;
@@ -377,6 +380,7 @@ CM_HD void cm_apply_memo_end(const AlignResD &m, int ed_th, AlignResD &best, Ali
 }
 
 // extend_right_trans (src/extend.cpp:491-650): [pos + 1, pos + len]
+template <bool EDIT = false>
 CM_HDN void cm_extend_right_trans(ExtCtx &x, uint32_t tid, uint32_t pos, int ref_len, const uint8_t *qseq, int qseq_len,
                                   int ed_th, uint32_t ub, AlignResD &best, bool &consecutive, AlignMemo &memo) {
     const AnnotDev &a = x.v->a;
@@ -446,7 +450,7 @@ CM_HDN void cm_extend_right_trans(ExtCtx &x, uint32_t tid, uint32_t pos, int ref
     if (mi >= 0) {
         cm_apply_memo_end(memo.e[mi].res, ed_th, best, curr, true, p);
     } else {
-        cm_extend_right_end(x, rspos, (uint32_t) remain_ref_len, qseq + covered, qseq_len - covered, ed_th, best, curr, exon_res);
+        cm_extend_right_end<EDIT>(x, rspos, (uint32_t) remain_ref_len, qseq + covered, qseq_len - covered, ed_th, best, curr, exon_res);
         memo_insert(memo, rspos, (uint32_t) remain_ref_len, (uint32_t) covered, (uint32_t) (qseq_len - covered), exon_res);
     }
 }
@@ -460,6 +464,7 @@ CM_HD bool cm_iv_has_tid(const AnnotDev &a, int iv, uint32_t t) {
 }
 
 // extend_right (src/extend.cpp:285-357): pos exclusive, [pos+1, pos+len]
+template <bool EDIT = false>
 CM_HDN bool cm_extend_right(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &pos, int len, int ed_th, uint32_t ub,
                             AlignResD &best) {
     const AnnotDev &a = x.v->a;
@@ -478,10 +483,10 @@ CM_HDN bool cm_extend_right(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &
         for (uint32_t k = b; k < e; k++) {
             uint32_t t = a.tid[k];
             if (cm_iv_has_tid(a, ts.iv_b, t))
-                cm_extend_right_trans(x, t, pos, ref_len, seq, seq_len, ed_th, ub, best, consecutive, memo);
+                cm_extend_right_trans<EDIT>(x, t, pos, ref_len, seq, seq_len, ed_th, ub, best, consecutive, memo);
         }
-    } else if (ts.iv_a <= -2) {
-        cm_extend_right_trans(x, (uint32_t) (-2 - ts.iv_a), pos, ref_len, seq, seq_len, ed_th, ub, best, consecutive, memo);
+    } else if (EDIT && ts.iv_a <= -2) {     // one transcript: stage 2 only
+        cm_extend_right_trans<EDIT>(x, (uint32_t) (-2 - ts.iv_a), pos, ref_len, seq, seq_len, ed_th, ub, best, consecutive, memo);
     }
     uint32_t best_rmpos = best.pos;
     int min_ed = best.ed;
@@ -494,7 +499,7 @@ CM_HDN bool cm_extend_right(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &
     const uint8_t *ref;
     if (!consecutive && (ref = cm_pac2char(*x.v, orig_pos + 1, ref_len)) != nullptr) {
         int score;
-        min_ed = x.edit_mode ? cm_edit_alignment_sc(ref, ref_len, seq, seq_len, false, p, sclen_best, indel, score, &x.st)
+        min_ed = EDIT ? cm_edit_alignment_sc(ref, ref_len, seq, seq_len, false, p, sclen_best, indel, score, &x.st)
                              : cm_drop_alignment_sc(ref, ref_len, seq, seq_len, false, p, sclen_best, indel, score, &x.st, &x.hint);
         if (min_ed <= ed_th && sclen_best <= p.max_sc) {
             ar_set(curr, orig_pos + (uint32_t) seq_len - (uint32_t) indel, min_ed, sclen_best, indel, seq_len, score);
@@ -538,13 +543,14 @@ CM_HDN bool cm_extend_left_middle(ExtCtx &x, uint32_t pos, uint32_t exon_len, co
 }
 
 // extend_left_end (src/extend.cpp:681-705)
+template <bool EDIT = false>
 CM_HDN void cm_extend_left_end(ExtCtx &x, uint32_t pos, uint32_t ref_len, const uint8_t *qseq, int qseq_len, int ed_th,
                                AlignResD &best, AlignResD &curr, AlignResD &exon_res) {
     const cm_params &p = x.v->p;
     const uint8_t *ref = cm_pac2char(*x.v, pos - ref_len, (int) ref_len);
     if (!ref) return;
     int sclen, indel, score;
-    int edit_dist = cm_x_drop(x, ref, (int) ref_len, qseq, qseq_len, true, sclen, indel, score);
+    int edit_dist = cm_x_drop<EDIT>(x, ref, (int) ref_len, qseq, qseq_len, true, sclen, indel, score);
     uint32_t new_lmpos = pos - (uint32_t) qseq_len + (uint32_t) indel;
     ar_set(exon_res, new_lmpos, edit_dist, sclen, indel, qseq_len, score);
     int actual_mapped_bp = qseq_len - sclen;
@@ -555,6 +561,7 @@ CM_HDN void cm_extend_left_end(ExtCtx &x, uint32_t pos, uint32_t ref_len, const 
 }
 
 // extend_left_trans (src/extend.cpp:708-875): [pos - len, pos - 1]
+template <bool EDIT = false>
 CM_HDN void cm_extend_left_trans(ExtCtx &x, uint32_t tid, uint32_t pos, int ref_len, const uint8_t *qseq, int qseq_len,
                                  int ed_th, uint32_t lb, AlignResD &best, bool &consecutive, AlignMemo &memo) {
     const AnnotDev &a = x.v->a;
@@ -631,12 +638,13 @@ CM_HDN void cm_extend_left_trans(ExtCtx &x, uint32_t tid, uint32_t pos, int ref_
     if (mi >= 0) {
         cm_apply_memo_end(memo.e[mi].res, ed_th, best, curr, false, p);
     } else {
-        cm_extend_left_end(x, lepos, (uint32_t) remain_ref_len, qseq, qseq_len - covered, ed_th, best, curr, exon_res);
+        cm_extend_left_end<EDIT>(x, lepos, (uint32_t) remain_ref_len, qseq, qseq_len - covered, ed_th, best, curr, exon_res);
         memo_insert(memo, lepos, (uint32_t) remain_ref_len, (uint32_t) covered, (uint32_t) (qseq_len - covered), exon_res);
     }
 }
 
 // extend_left (src/extend.cpp:361-432): pos exclusive, [pos-len, pos-1]
+template <bool EDIT = false>
 CM_HDN bool cm_extend_left(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &pos, int len, int ed_th, uint32_t lb,
                            AlignResD &best) {
     const AnnotDev &a = x.v->a;
@@ -655,10 +663,10 @@ CM_HDN bool cm_extend_left(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &p
         for (uint32_t k = b; k < e; k++) {
             uint32_t t = a.tid[k];
             if (cm_iv_has_tid(a, ts.iv_b, t))
-                cm_extend_left_trans(x, t, pos, ref_len, seq, seq_len, ed_th, lb, best, consecutive, memo);
+                cm_extend_left_trans<EDIT>(x, t, pos, ref_len, seq, seq_len, ed_th, lb, best, consecutive, memo);
         }
-    } else if (ts.iv_a <= -2) {
-        cm_extend_left_trans(x, (uint32_t) (-2 - ts.iv_a), pos, ref_len, seq, seq_len, ed_th, lb, best, consecutive, memo);
+    } else if (EDIT && ts.iv_a <= -2) {
+        cm_extend_left_trans<EDIT>(x, (uint32_t) (-2 - ts.iv_a), pos, ref_len, seq, seq_len, ed_th, lb, best, consecutive, memo);
     }
     uint32_t lmpos_best = best.pos;
     int min_ed = best.ed;
@@ -671,7 +679,7 @@ CM_HDN bool cm_extend_left(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &p
     const uint8_t *ref;
     if (!consecutive && (ref = cm_pac2char(*x.v, orig_pos - (uint32_t) ref_len, ref_len)) != nullptr) {
         int score;
-        min_ed = x.edit_mode ? cm_edit_alignment_sc(ref, ref_len, seq, seq_len, true, p, sclen_best, indel, score, &x.st)
+        min_ed = EDIT ? cm_edit_alignment_sc(ref, ref_len, seq, seq_len, true, p, sclen_best, indel, score, &x.st)
                              : cm_drop_alignment_sc(ref, ref_len, seq, seq_len, true, p, sclen_best, indel, score, &x.st, &x.hint);
         if (min_ed <= ed_th && sclen_best <= p.max_sc) {
             ar_set(curr, orig_pos - (uint32_t) seq_len + (uint32_t) indel, min_ed, sclen_best, indel, seq_len, score);
@@ -695,6 +703,7 @@ CM_HDN bool cm_extend_left(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &p
 
 // ---- chain level -------------------------------------------------------------------------
 // extend_chain_right (src/extend.cpp:215-246)
+template <bool EDIT = false>
 CM_HDN bool cm_extend_chain_right(ExtCtx &x, TidSet ts, const ChainView &ch, const uint8_t *seq, int seq_len, uint32_t ub,
                                   MateD &mr, int &err) {
     const cm_params &p = x.v->p;
@@ -706,7 +715,7 @@ CM_HDN bool cm_extend_chain_right(ExtCtx &x, TidSet ts, const ChainView &ch, con
     if (remain_end > 0) {
         cm_set_hint(x, ch, seq, seq_len, true);
         if (x.hint.valid && ch.spec) { x.seed = ch.spec + 1; x.tbase = seq; }
-        right_ok = cm_extend_right(x, ts, seq + seq_len - remain_end, rm_pos, remain_end, p.max_ed - err, ub, best);
+        right_ok = cm_extend_right<EDIT>(x, ts, seq + seq_len - remain_end, rm_pos, remain_end, p.max_ed - err, ub, best);
         x.hint.valid = 0;
         x.seed = nullptr;
     }
@@ -723,6 +732,7 @@ CM_HDN bool cm_extend_chain_right(ExtCtx &x, TidSet ts, const ChainView &ch, con
 }
 
 // extend_chain_left (src/extend.cpp:248-280)
+template <bool EDIT = false>
 CM_HDN bool cm_extend_chain_left(ExtCtx &x, TidSet ts, const ChainView &ch, const uint8_t *seq, int32_t qspos, uint32_t lb,
                                  MateD &mr, int &err) {
     const cm_params &p = x.v->p;
@@ -733,7 +743,7 @@ CM_HDN bool cm_extend_chain_left(ExtCtx &x, TidSet ts, const ChainView &ch, cons
     if (remain_beg > 0) {
         if (qspos == 0) cm_set_hint(x, ch, seq, 0, false);
         if (x.hint.valid && ch.spec) { x.seed = ch.spec; x.tbase = seq; }
-        left_ok = cm_extend_left(x, ts, seq, lm_pos, remain_beg, p.max_ed - err, lb, best);
+        left_ok = cm_extend_left<EDIT>(x, ts, seq, lm_pos, remain_beg, p.max_ed - err, lb, best);
         x.hint.valid = 0;
         x.seed = nullptr;
     }

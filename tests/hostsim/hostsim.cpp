@@ -390,7 +390,6 @@ int hs_circ_exact(HsCtx *c, int contig_id, uint32_t n, const char *seqs, uint32_
     for (uint32_t i = 0; i < n; i++) {
         ExtCtx x;
         ext_ctx_init(x, &v);
-        x.edit_mode = true;
         for (uint32_t f = 0; f < F; f++) fr[f] = FragDev{frag_rpos[(size_t) i * F + f], frag_qpos[(size_t) i * F + f]};
         ChainView bc;
         bc.frags = fr.data(); bc.chain_len = chain_len[i]; bc.aux = nullptr; bc.spec = nullptr;
