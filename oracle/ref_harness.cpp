@@ -703,4 +703,39 @@ int cmref_circ_single(uint32_t n, const char *seqs1, const char *seqs2, uint32_t
     }
     return (int) (n_rec < cap ? n_rec : cap);
 }
+
+static void circ_mate_import(const cm_circ_mate *i, MatchedMate &m) {
+    FlatIntervalTree<UniqSeg> &T = gtf_parser.exons_int_map[contigNum];
+    const IntervalInfo<UniqSeg> *base = T.disjoint_intervals.data();
+    m.spos = i->m.spos; m.epos = i->m.epos; m.qspos = i->m.qspos; m.qepos = i->m.qepos; m.matched_len = i->m.matched_len;
+    m.left_ed = i->m.left_ed; m.middle_ed = i->m.middle_ed; m.right_ed = i->m.right_ed; m.sclen_left = i->m.sclen_left; m.sclen_right = i->m.sclen_right;
+    m.dir = i->m.dir; m.type = i->m.type;
+    m.is_concord = i->m.is_concord; m.left_ok = i->m.left_ok; m.right_ok = i->m.right_ok;
+    m.looked_up_spos = i->looked_up_spos; m.looked_up_epos = i->looked_up_epos;
+    m.exons_spos = i->exons_spos >= 0 ? base + i->exons_spos : NULL;
+    m.exons_epos = i->exons_epos >= 0 ? base + i->exons_epos : NULL;
+    m.exon_ind_spos = i->exon_ind_spos; m.exon_ind_epos = i->exon_ind_epos;
+}
+
+// ProcessCirc::check_split_map(mm_r1, mm_r2, partial_mm, r1_partial, cr) on given inputs (the arguments of cm_gpu_circ_check_batch)
+int cmref_circ_check(uint32_t n, const char *remain_seq, const char *fullmap_seq, uint32_t stride, const int32_t *remain_len,
+                     const int32_t *fullmap_len, const uint8_t *r1_partial, cm_circ_mate *mm_r1, cm_circ_mate *mm_r2, cm_circ_mate *partial_mm,
+                     int ws, int32_t *ret, cm_circ_res *cr_out) {
+    if (circ_pc(ws) != 0) return -1;
+    ProcessCirc &pc = *g_pc;
+    std::vector<char> rs(stride + 8), fs(stride + 8);
+    for (uint32_t i = 0; i < n; i++) {
+        memcpy(rs.data(), remain_seq + (size_t) i * stride, stride); rs[remain_len[i]] = 0;
+        memcpy(fs.data(), fullmap_seq + (size_t) i * stride, stride); fs[fullmap_len[i]] = 0;
+        pc.remain_seq = rs.data(); pc.fullmap_seq = fs.data(); pc.r1_seq = NULL; pc.r2_seq = NULL;
+        pc.remain_seq_len = remain_len[i]; pc.fullmap_seq_len = fullmap_len[i]; pc.r1_seq_len = 0; pc.r2_seq_len = 0;
+        MatchedMate a, b, p;
+        circ_mate_import(&mm_r1[i], a); circ_mate_import(&mm_r2[i], b); circ_mate_import(&partial_mm[i], p);
+        CircRes cr;
+        ret[i] = pc.check_split_map(a, b, p, r1_partial[i] != 0, cr);
+        circ_res_export(cr, !cr.start_bp_ref.empty(), &cr_out[i]);
+        circ_mate_export(a, &mm_r1[i]); circ_mate_export(b, &mm_r2[i]); circ_mate_export(p, &partial_mm[i]);
+    }
+    return 0;
+}
 }  // extern "C"

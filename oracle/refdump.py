@@ -259,8 +259,19 @@ def main():
             # stage 1 on this contig first (fresh MatchedReads: every back-splice pair of this contig is a candidate), then the
             # single-split path of stage 2 with every check_split_map call recorded
             mr1, _ = h.process_pe(s1, s2, lens, lens, fresh_mreads(n, a.max_ed))
-            for k, v in h.circ_single(s1, s2, lens, lens, mr1).items():
+            rec = h.circ_single(s1, s2, lens, lens, mr1)
+            for k, v in rec.items():
                 out[f"c{c}_circs_{k}"] = v
+            if len(rec["ret"]):
+                # the same calls once more on the recorded inputs alone (check_split_map as a function of its arguments), timed
+                import time
+                t0 = time.time()
+                again = h.circ_check(rec)
+                out[f"c{c}_circs_check_seconds"] = time.time() - t0
+                same = (again["ret"] == rec["ret"]).all() and (again["cr"] == rec["cr"]).all() and (again["r1"] == rec["out_r1"]).all() \
+                    and (again["r2"] == rec["out_r2"]).all() and (again["pm"] == rec["out_pm"]).all()
+                if not same:
+                    raise SystemExit("check_split_map on the recorded inputs does not reproduce the recorded call")
         if a.se:
             out[f"c{c}_se_state"] = h.process_se(s1, lens)
         mr, st = h.process_pe(s1, s2, lens, lens, mr)

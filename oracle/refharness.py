@@ -233,6 +233,21 @@ class RefHarness:
         out["best_type"] = best
         return out
 
+    def circ_check(self, rec: dict, ws: int = 8) -> dict:
+        """ProcessCirc::check_split_map on given inputs (same record layout as Mapper.circ_check)."""
+        from circminer_b200.api import CIRC_MATE_DTYPE, CIRC_RES_DTYPE
+        rr, fr = np.ascontiguousarray(rec["remain_rows"], np.uint8), np.ascontiguousarray(rec["fullmap_rows"], np.uint8)
+        n = rr.shape[0]
+        rl, fl = np.ascontiguousarray(rec["remain_len"], np.int32), np.ascontiguousarray(rec["fullmap_len"], np.int32)
+        rp = np.ascontiguousarray(rec["r1_partial"], np.uint8)
+        out = dict(r1=np.array(rec["in_r1"], CIRC_MATE_DTYPE), r2=np.array(rec["in_r2"], CIRC_MATE_DTYPE), pm=np.array(rec["in_pm"], CIRC_MATE_DTYPE),
+                   ret=np.zeros(n, np.int32), cr=np.zeros(n, CIRC_RES_DTYPE))
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        r = self.lib.cmref_circ_check(C.c_uint32(n), vp(rr), vp(fr), C.c_uint32(rr.shape[1]), vp(rl), vp(fl), vp(rp), vp(out["r1"]), vp(out["r2"]),
+                                      vp(out["pm"]), ws, vp(out["ret"]), vp(out["cr"]))
+        assert r == 0, r
+        return out
+
     def seed(self, seqs: np.ndarray, lens: np.ndarray) -> dict:
         n, S = len(lens), self.S
         out = dict(qpos=np.zeros((n, S), np.int32), frag_count=np.zeros((n, S), np.uint32),
