@@ -353,6 +353,36 @@ class Mapper:
         self._chk(r, "cm_gpu_circ_check_batch")
         return out
 
+    def circ_single(self, contig_id, s1, s2, l1, l2, mr_con, gene_cnt, gene_se, window_size=8, step=3, cap=20000) -> dict:
+        """ProcessCirc::call_circ_single_split for a batch (src/process_circ.cpp:360; cm_gpu_circ_single_batch).  mr_con: MatchedReads
+        with contig coordinates; gene_cnt[n], gene_se[n][G][2]: the genes get_gene_overlap(mm_r1.spos) lists for each pair."""
+        a1, a2 = np.ascontiguousarray(s1, np.uint8), np.ascontiguousarray(s2, np.uint8)
+        n, stride = a1.shape
+        l1, l2 = np.ascontiguousarray(l1, np.uint16), np.ascontiguousarray(l2, np.uint16)
+        mr = np.ascontiguousarray(mr_con)
+        gene_cnt = np.asarray(gene_cnt, np.int64)
+        goff = np.zeros(n + 1, np.uint32)
+        goff[1:] = np.cumsum(gene_cnt)
+        sel = np.arange(gene_se.shape[1])[None, :] < gene_cnt[:, None]
+        gs = np.ascontiguousarray(gene_se[:, :, 0][sel], np.uint32)
+        ge = np.ascontiguousarray(gene_se[:, :, 1][sel], np.uint32)
+        if len(gs) == 0:
+            gs, ge = np.zeros(1, np.uint32), np.zeros(1, np.uint32)
+        rec = dict(call_pair=np.zeros(cap, np.uint32), r1_partial=np.zeros(cap, np.uint8), in_r1=np.zeros(cap, CIRC_MATE_DTYPE),
+                   in_r2=np.zeros(cap, CIRC_MATE_DTYPE), in_pm=np.zeros(cap, CIRC_MATE_DTYPE), ret=np.zeros(cap, np.int32),
+                   cr=np.zeros(cap, CIRC_RES_DTYPE), out_r1=np.zeros(cap, CIRC_MATE_DTYPE), out_r2=np.zeros(cap, CIRC_MATE_DTYPE),
+                   out_pm=np.zeros(cap, CIRC_MATE_DTYPE))
+        best, best_cr = np.zeros(n, np.int32), np.zeros(n, CIRC_RES_DTYPE)
+        k = C.c_uint32(0)
+        self._chk(self.lib.cm_gpu_circ_single_batch(self.ctx, contig_id, C.c_uint32(n), _vp(a1), _vp(a2), C.c_uint32(stride), _vp(l1), _vp(l2), _vp(mr),
+                                                    _vp(goff), _vp(gs), _vp(ge), window_size, step, C.c_uint32(cap), C.byref(k),
+                                                    *[_vp(rec[x]) for x in ("call_pair", "r1_partial", "in_r1", "in_r2", "in_pm", "ret", "cr",
+                                                                            "out_r1", "out_r2", "out_pm")], _vp(best), _vp(best_cr)),
+                  "cm_gpu_circ_single_batch")
+        out = {x: v[:min(k.value, cap)] for x, v in rec.items()}
+        out["n_attempts"], out["best_type"], out["best_cr"] = k.value, best, best_cr
+        return out
+
     def annot_lookup(self, contig_id, pos, mlen, rlen) -> dict:
         """GTFParser look-ups per position (cm_gpu_annot_lookup_batch)."""
         pos = np.ascontiguousarray(pos, np.uint32)

@@ -399,16 +399,17 @@ extern "C" int cm_gpu_circ_exact_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t 
 __global__ void __launch_bounds__(64) k_circ_check(const __grid_constant__ DevView v, uint32_t n, const uint8_t *__restrict__ remain_seq,
                                                    const uint8_t *__restrict__ fullmap_seq, uint32_t stride, const int32_t *__restrict__ remain_len,
                                                    const int32_t *__restrict__ fullmap_len, const uint8_t *__restrict__ r1_partial,
-                                                   cm_circ_mate *r1, cm_circ_mate *r2, cm_circ_mate *pm, int32_t *__restrict__ ret, cm_circ_res *cr) {
+                                                   cm_circ_mate *r1, cm_circ_mate *r2, cm_circ_mate *pm, int32_t *__restrict__ ret, cm_circ_res *cr,
+                                                   uint8_t *__restrict__ remain_is_fullmap) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     ret[i] = cm_circ_check_row(v, remain_seq + (size_t) i * stride, remain_len[i], fullmap_seq + (size_t) i * stride, fullmap_len[i],
-                               r1_partial[i] != 0, r1[i], r2[i], pm[i], cr[i]);
+                               r1_partial[i] != 0, r1[i], r2[i], pm[i], cr[i], remain_is_fullmap + i);
 }
 
-extern "C" int cm_gpu_circ_check_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *remain_seq, const char *fullmap_seq, uint32_t stride,
-                                       const int32_t *remain_len, const int32_t *fullmap_len, const uint8_t *r1_partial, cm_circ_mate *mm_r1,
-                                       cm_circ_mate *mm_r2, cm_circ_mate *partial_mm, int window_size, int32_t *ret, cm_circ_res *cr) {
+static int circ_check_impl(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *remain_seq, const char *fullmap_seq, uint32_t stride,
+                           const int32_t *remain_len, const int32_t *fullmap_len, const uint8_t *r1_partial, cm_circ_mate *mm_r1,
+                           cm_circ_mate *mm_r2, cm_circ_mate *partial_mm, int window_size, int32_t *ret, cm_circ_res *cr, uint8_t *remain_is_fullmap) {
     if (!ctx) return CM_ERR_ARG;
     if (n == 0) return CM_OK;
     if (!remain_seq || !fullmap_seq || !remain_len || !fullmap_len || !r1_partial || !mm_r1 || !mm_r2 || !partial_mm || !ret || !cr)
@@ -434,7 +435,7 @@ extern "C" int cm_gpu_circ_check_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t 
     const size_t bytes = (size_t) n * stride;
     CIRC_TRY(dev_alloc(ctx, tmp, &d_rs, bytes + 64));
     CIRC_TRY(dev_alloc(ctx, tmp, &d_fs, bytes + 64));
-    CIRC_TRY(dev_alloc(ctx, tmp, &d_rp, (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_rp, 2 * (size_t) n));
     CIRC_TRY(dev_alloc(ctx, tmp, &d_len, 2 * (size_t) n));
     CIRC_TRY(dev_alloc(ctx, tmp, &d_ret, (size_t) n));
     CIRC_TRY(dev_alloc(ctx, tmp, &d_m, 3 * (size_t) n));
@@ -447,7 +448,7 @@ extern "C" int cm_gpu_circ_check_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t 
     CIRC_CUDA(cudaMemcpyAsync(d_m, mm_r1, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
     CIRC_CUDA(cudaMemcpyAsync(d_m + n, mm_r2, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
     CIRC_CUDA(cudaMemcpyAsync(d_m + 2 * (size_t) n, partial_mm, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
-    k_circ_check<<<grid_for(n, 64), 64, 0, st>>>(v, n, d_rs, d_fs, stride, d_len, d_len + n, d_rp, d_m, d_m + n, d_m + 2 * (size_t) n, d_ret, d_cr);
+    k_circ_check<<<grid_for(n, 64), 64, 0, st>>>(v, n, d_rs, d_fs, stride, d_len, d_len + n, d_rp, d_m, d_m + n, d_m + 2 * (size_t) n, d_ret, d_cr, d_rp + n);
     ctx->launches++;
     CIRC_CUDA(cudaGetLastError());
     CIRC_CUDA(cudaMemcpyAsync(mm_r1, d_m, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
@@ -455,9 +456,143 @@ extern "C" int cm_gpu_circ_check_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t 
     CIRC_CUDA(cudaMemcpyAsync(partial_mm, d_m + 2 * (size_t) n, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
     CIRC_CUDA(cudaMemcpyAsync(ret, d_ret, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
     CIRC_CUDA(cudaMemcpyAsync(cr, d_cr, (size_t) n * sizeof(cm_circ_res), cudaMemcpyDeviceToHost, st));
+    if (remain_is_fullmap) CIRC_CUDA(cudaMemcpyAsync(remain_is_fullmap, d_rp + n, (size_t) n, cudaMemcpyDeviceToHost, st));
     CIRC_CUDA(cudaStreamSynchronize(st));
     cleanup();
 #undef CIRC_TRY
 #undef CIRC_CUDA
+    return CM_OK;
+}
+extern "C" int cm_gpu_circ_check_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *remain_seq, const char *fullmap_seq, uint32_t stride,
+                                       const int32_t *remain_len, const int32_t *fullmap_len, const uint8_t *r1_partial, cm_circ_mate *mm_r1,
+                                       cm_circ_mate *mm_r2, cm_circ_mate *partial_mm, int window_size, int32_t *ret, cm_circ_res *cr) {
+    return circ_check_impl(ctx, contig_id, n, remain_seq, fullmap_seq, stride, remain_len, fullmap_len, r1_partial, mm_r1, mm_r2, partial_mm,
+                           window_size, ret, cr, nullptr);
+}
+
+// ---- find_exact_coord with the pair's mates carried from chain to chain (cm_circ_exact_row) ----------------------------------
+__global__ void __launch_bounds__(128) k_circ_exact_mates(const __grid_constant__ DevView v, const __grid_constant__ CircExactIn in, cm_circ_mate *r1,
+                                                          cm_circ_mate *r2, cm_circ_mate *pm, int32_t *ret) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= in.n) return;
+    ChainView bc;
+    bc.frags = in.frags + (size_t) i * in.F;
+    bc.chain_len = in.chain_len[i];
+    bc.aux = nullptr;
+    bc.spec = nullptr;
+    ret[i] = cm_circ_exact_row(v, r1[i], r2[i], pm[i], in.dir[i], in.qspos[i], in.seqs + (size_t) i * in.stride, in.rlen[i], in.whole_len[i], bc);
+}
+
+extern "C" int cm_gpu_circ_exact_mates_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride, cm_circ_mate *mm_r1,
+                                             cm_circ_mate *mm_r2, const int32_t *dir, const uint32_t *qspos, const int32_t *rlen,
+                                             const int32_t *whole_len, uint32_t frag_slots, const uint32_t *chain_len, const uint32_t *frag_rpos,
+                                             const int32_t *frag_qpos, int window_size, cm_circ_mate *partial_mm, int32_t *ret) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n == 0) return CM_OK;
+    if (!seqs || !mm_r1 || !mm_r2 || !dir || !qspos || !rlen || !whole_len || !chain_len || !frag_rpos || !frag_qpos || !partial_mm || !ret)
+        return fail(ctx, CM_ERR_ARG, "null argument");
+    if (window_size < 4 || window_size > 12 || frag_slots < 1) return fail(ctx, CM_ERR_ARG, "window size outside 4..12 or no fragment slots");
+    for (uint32_t i = 0; i < n; i++) {
+        if (chain_len[i] < 1 || chain_len[i] > frag_slots) return fail(ctx, CM_ERR_ARG, "problem %u: chain of %u fragments (slots: %u)", i, chain_len[i], frag_slots);
+        if (qspos[i] < 1 || rlen[i] < 1 || qspos[i] - 1 + (uint32_t) rlen[i] > stride || whole_len[i] < 0 || (uint32_t) whole_len[i] > stride)
+            return fail(ctx, CM_ERR_ARG, "problem %u: read range outside the row", i);
+    }
+    cudaSetDevice(ctx->device);
+    DevView v;
+    int r = make_view(ctx, contig_id, true, v);
+    if (r != CM_OK) return r;
+    v.p.kmer = window_size;
+    cudaStream_t st = ctx->stream;
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *q : tmp) cudaFree(q); };
+#define CIRC_TRY(x) do { if ((r = (x)) != CM_OK) { cleanup(); return r; } } while (0)
+#define CIRC_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return fail(ctx, CM_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e_)); } } while (0)
+    const size_t F = frag_slots;
+    uint8_t *d_seq = nullptr;
+    uint32_t *d_u = nullptr;
+    FragDev *d_fr = nullptr;
+    cm_circ_mate *d_mm = nullptr;
+    int32_t *d_ret = nullptr;
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_seq, (size_t) n * stride + 64));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_u, (size_t) n * 5));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_fr, (size_t) n * F));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_mm, 3 * (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_ret, (size_t) n));
+    std::vector<FragDev> h_fr((size_t) n * F);
+    for (size_t q = 0; q < h_fr.size(); q++) { h_fr[q].rpos = frag_rpos[q]; h_fr[q].qpos = frag_qpos[q]; }
+    const void *srcs[5] = {qspos, dir, rlen, whole_len, chain_len};
+    CIRC_CUDA(cudaMemcpyAsync(d_seq, seqs, (size_t) n * stride, cudaMemcpyHostToDevice, st));
+    for (int k = 0; k < 5; k++) CIRC_CUDA(cudaMemcpyAsync(d_u + (size_t) k * n, srcs[k], (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_fr, h_fr.data(), h_fr.size() * sizeof(FragDev), cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_mm, mm_r1, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_mm + n, mm_r2, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
+    CircExactIn in{n, d_seq, stride, nullptr, nullptr, nullptr, nullptr, d_u, (const int32_t *) (d_u + n), (const int32_t *) (d_u + 2 * (size_t) n),
+                   (const int32_t *) (d_u + 3 * (size_t) n), (int) F, d_u + 4 * (size_t) n, d_fr};
+    k_circ_exact_mates<<<grid_for(n, 128), 128, 0, st>>>(v, in, d_mm, d_mm + n, d_mm + 2 * (size_t) n, d_ret);
+    ctx->launches++;
+    CIRC_CUDA(cudaGetLastError());
+    CIRC_CUDA(cudaMemcpyAsync(mm_r1, d_mm, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(mm_r2, d_mm + n, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(partial_mm, d_mm + 2 * (size_t) n, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(ret, d_ret, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaStreamSynchronize(st));
+    cleanup();
+#undef CIRC_TRY
+#undef CIRC_CUDA
+    return CM_OK;
+}
+
+// ---- call_circ_single_split for a batch (cm_circ_orch.h over the three device entries) ---------------------------------------
+#include "cm_circ_orch.h"
+static int gpu_eng_chain(void *self, int contig, uint32_t n, const char *seqs, uint32_t stride, const uint32_t *qspos, const uint32_t *qepos,
+                         const uint32_t *gs, const uint32_t *ge, int ws, int step, int F, int32_t *count, float *score, uint32_t *clen, uint32_t *rpos,
+                         int32_t *qpos) {
+    return cm_gpu_circ_chain_batch((cm_gpu_ctx *) self, contig, n, seqs, stride, qspos, qepos, gs, ge, ws, step, F, count, nullptr, score, clen, rpos, qpos);
+}
+static int gpu_eng_exact(void *self, int contig, uint32_t n, const char *seqs, uint32_t stride, cm_circ_mate *r1, cm_circ_mate *r2, const int32_t *dir,
+                         const uint32_t *qspos, const int32_t *rlen, const int32_t *wl, uint32_t F, const uint32_t *clen, const uint32_t *rpos,
+                         const int32_t *qpos, int ws, cm_circ_mate *pm, int32_t *ret) {
+    return cm_gpu_circ_exact_mates_batch((cm_gpu_ctx *) self, contig, n, seqs, stride, r1, r2, dir, qspos, rlen, wl, F, clen, rpos, qpos, ws, pm, ret);
+}
+static int gpu_eng_check(void *self, int contig, uint32_t n, const char *rem, const char *ful, uint32_t stride, const int32_t *rl, const int32_t *fl,
+                         const uint8_t *r1p, cm_circ_mate *r1, cm_circ_mate *r2, cm_circ_mate *pm, int ws, int32_t *ret, cm_circ_res *cr, uint8_t *sw) {
+    return circ_check_impl((cm_gpu_ctx *) self, contig, n, rem, ful, stride, rl, fl, r1p, r1, r2, pm, ws, ret, cr, sw);
+}
+
+extern "C" int cm_gpu_circ_single_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
+                                        const uint16_t *len1, const uint16_t *len2, const cm_mread *mr, const uint32_t *gene_off,
+                                        const uint32_t *gene_start, const uint32_t *gene_end, int window_size, int step, uint32_t attempt_cap,
+                                        uint32_t *n_attempts, uint32_t *att_pair, uint8_t *att_r1_partial, cm_circ_mate *att_in_r1,
+                                        cm_circ_mate *att_in_r2, cm_circ_mate *att_in_pm, int32_t *att_ret, cm_circ_res *att_cr,
+                                        cm_circ_mate *att_out_r1, cm_circ_mate *att_out_r2, cm_circ_mate *att_out_pm, int32_t *best_type,
+                                        cm_circ_res *best_cr) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n_attempts) *n_attempts = 0;
+    if (n == 0) return CM_OK;
+    if (!seqs1 || !seqs2 || !len1 || !len2 || !mr || !gene_off || !gene_start || !gene_end || !n_attempts || !best_type)
+        return fail(ctx, CM_ERR_ARG, "null argument");
+    if (step < 1 || window_size < 4 || window_size > 12) return fail(ctx, CM_ERR_ARG, "window size outside 4..12 or step < 1");
+    for (uint32_t i = 0; i < n; i++)
+        if (len1[i] > stride || len2[i] > stride || gene_off[i + 1] < gene_off[i]) return fail(ctx, CM_ERR_ARG, "pair %u: read longer than the row or gene list out of order", i);
+    const CircEngine E{ctx, contig_id, gpu_eng_chain, gpu_eng_exact, gpu_eng_check};
+    const CircSingleIn in{n, seqs1, seqs2, stride, len1, len2, mr, gene_off, gene_start, gene_end, window_size, step, ctx->p.max_read_len,
+                          ctx->p.max_chain_len};
+    std::vector<CircAttempt> att;
+    const int r = circ_orch_single(E, in, att, best_type, best_cr);
+    if (r == -100) return fail(ctx, CM_ERR_STATE, "a fixed-size list of the stage-2 classification overflowed (CM_CIRC_TID_CAP / CM_CIRC_JUNC_CAP)");
+    if (r != 0) return r;
+    *n_attempts = (uint32_t) att.size();
+    for (size_t k = 0; k < att.size() && k < attempt_cap; k++) {
+        if (att_pair) att_pair[k] = att[k].pair;
+        if (att_r1_partial) att_r1_partial[k] = att[k].r1_partial;
+        if (att_in_r1) att_in_r1[k] = att[k].in_r1;
+        if (att_in_r2) att_in_r2[k] = att[k].in_r2;
+        if (att_in_pm) att_in_pm[k] = att[k].in_pm;
+        if (att_ret) att_ret[k] = att[k].ret;
+        if (att_cr) att_cr[k] = att[k].cr;
+        if (att_out_r1) att_out_r1[k] = att[k].out_r1;
+        if (att_out_r2) att_out_r2[k] = att[k].out_r2;
+        if (att_out_pm) att_out_pm[k] = att[k].out_pm;
+    }
     return CM_OK;
 }

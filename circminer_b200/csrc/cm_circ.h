@@ -115,14 +115,17 @@ CM_HD void cm_circ_finish(int kmer_cnt, ChainOut &out) {
 // three mates whose exon intervals all exist and share a transcript.  The three-interval overload (:356-376) intersects
 // the common transcripts of the first two intervals with the transcripts of the FIRST interval again -- the third is only
 // tested for NULL -- so common_tid is the two-interval set of (seg0, seg1): TidSet{iv0, iv1}.
+// The start look-ups are made on the mates themselves (find_exact_coord calls overlap_to_spos on them and they keep the result);
+// the end look-ups happen on the copies same_transcript works on (segments.push_back) and are not kept.
 CM_HD bool cm_circ_same_transcript3(const AnnotDev &a, MateD &m0, MateD &m1, MateD &m2, TidSet &ts) {
     cm_overlap_to_spos(a, m0); cm_overlap_to_spos(a, m1); cm_overlap_to_spos(a, m2);
-    cm_overlap_to_epos(a, m0); cm_overlap_to_epos(a, m1); cm_overlap_to_epos(a, m2);
+    MateD c0m = m0, c1m = m1, c2m = m2;
+    cm_overlap_to_epos(a, c0m); cm_overlap_to_epos(a, c1m); cm_overlap_to_epos(a, c2m);
     for (int c0 = 0; c0 < 2; c0++)
         for (int c1 = 0; c1 < 2; c1++)
             for (int c2 = 0; c2 < 2; c2++) {
-                const int i0 = c0 ? m0.exons_epos : m0.exons_spos, i1 = c1 ? m1.exons_epos : m1.exons_spos,
-                          i2 = c2 ? m2.exons_epos : m2.exons_spos;
+                const int i0 = c0 ? c0m.exons_epos : c0m.exons_spos, i1 = c1 ? c1m.exons_epos : c1m.exons_spos,
+                          i2 = c2 ? c2m.exons_epos : c2m.exons_spos;
                 if (i0 < 0 || i1 < 0 || i2 < 0) continue;
                 if (cm_same_transcript(a, i0, i1)) { ts.iv_a = i0; ts.iv_b = i1; return true; }
             }

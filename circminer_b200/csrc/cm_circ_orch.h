@@ -1,0 +1,255 @@
+// Stage 2, the single-split path end to end: the control flow of ProcessCirc::call_circ_single_split
+// (src/process_circ.cpp:360-483) for a batch of read pairs, as rounds over the three batch entries
+//   chaining (per pair and overlapping gene)  ->  find_exact_coord (chain by chain)  ->  check_split_map (for the CONCRD ones)
+// Host code only (no CUDA): the same loop drives the device entries in libcm_gpu.so and the host build of the device functions
+// in the CPU tests, through the CircEngine function table.
+//
+// The chains of one read cannot go through the entries all at once: the two mates of the pair keep what the previous
+// check_split_map left on them (a trim by final_check, cached exon look-ups), remain_seq may have been pointed at the other
+// read, and the loop ends at the first FR / RF or CR.  So round (g, j) handles chain j of gene g for every pair that is
+// still going.
+#pragma once
+#include <cstdint>
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+#include "../../include/cm_gpu.h"
+
+#define CM_CIRC_TOPCHAIN 10   // TOPCHAIN, src/process_circ.cpp:19
+#define CM_CIRC_T_CHIBSJ 3    // CHIBSJ, src/common.h:62
+#define CM_CIRC_T_CONCRD 0
+
+struct CircEngine {
+    void *self;
+    int contig;
+    int (*chain)(void *self, int contig, uint32_t n, const char *seqs, uint32_t stride, const uint32_t *qspos, const uint32_t *qepos,
+                 const uint32_t *gene_start, const uint32_t *gene_end, int ws, int step, int F, int32_t *count, float *score, uint32_t *clen,
+                 uint32_t *rpos, int32_t *qpos);
+    int (*exact)(void *self, int contig, uint32_t n, const char *seqs, uint32_t stride, cm_circ_mate *r1, cm_circ_mate *r2, const int32_t *dir,
+                 const uint32_t *qspos, const int32_t *rlen, const int32_t *whole_len, uint32_t F, const uint32_t *clen, const uint32_t *rpos,
+                 const int32_t *qpos, int ws, cm_circ_mate *pm, int32_t *ret);
+    int (*check)(void *self, int contig, uint32_t n, const char *remain, const char *fullmap, uint32_t stride, const int32_t *rlen,
+                 const int32_t *flen, const uint8_t *r1_partial, cm_circ_mate *r1, cm_circ_mate *r2, cm_circ_mate *pm, int ws, int32_t *ret,
+                 cm_circ_res *cr, uint8_t *remain_is_fullmap);
+};
+
+// MatchedMate(const MatchedRead &, r1_2, rlen, partial) (src/common.cpp:192-235); the three flags it leaves unset are 0
+static inline void circ_orch_mate(const cm_mread &mr, int r1_2, int rlen, bool partial, cm_circ_mate &o) {
+    memset(&o, 0, sizeof(o));
+    cm_mate &m = o.m;
+    m.type = mr.type;
+    if (r1_2 == 1) {
+        m.spos = mr.spos_r1; m.epos = mr.epos_r1; m.qspos = mr.qspos_r1; m.qepos = mr.qepos_r1;
+        m.middle_ed = mr.ed_r1; m.matched_len = mr.mlen_r1; m.dir = mr.r1_forward ? 1 : -1;
+    } else {
+        m.spos = mr.spos_r2; m.epos = mr.epos_r2; m.qspos = mr.qspos_r2; m.qepos = mr.qepos_r2;
+        m.middle_ed = mr.ed_r2; m.matched_len = mr.mlen_r2; m.dir = mr.r2_forward ? 1 : -1;
+    }
+    if (partial) {
+        if ((m.qspos - 1) > ((uint32_t) rlen - m.qepos)) { m.sclen_left = 0; m.sclen_right = rlen - (int) m.qepos; }
+        else { m.sclen_left = (int) m.qspos - 1; m.sclen_right = 0; }
+    } else {
+        m.sclen_left = (int) m.qspos - 1;
+        m.sclen_right = rlen - (int) m.qepos;
+    }
+    o.exons_spos = o.exons_epos = -1;
+    o.exon_ind_spos = o.exon_ind_epos = -1;
+}
+
+static inline void circ_orch_revcomp(const char *s, int len, char *rc) {
+    for (int i = 0; i < len; i++) {
+        char c = s[i];
+        char r = 'N';
+        if (c == 'A' || c == 'a') r = 'T';
+        else if (c == 'C' || c == 'c') r = 'G';
+        else if (c == 'G' || c == 'g') r = 'C';
+        else if (c == 'T' || c == 't') r = 'A';
+        rc[len - 1 - i] = r;
+    }
+}
+
+struct CircSingleIn {
+    uint32_t n;
+    const char *seqs1, *seqs2;     // rows of `stride` bytes, as read
+    uint32_t stride;
+    const uint16_t *len1, *len2;
+    const cm_mread *mr;            // stage 1's MatchedRead, positions in CONTIG coordinates (after chrloc2conloc)
+    const uint32_t *gene_off;      // [n + 1]: genes of gtf_parser.get_gene_overlap(mm_r1.spos, false)->seg_list, in that order
+    const uint32_t *gene_start, *gene_end;
+    int ws, step, max_read_len, max_chain_len;   // max_chain_len: rows of the engine's chain lists (cm_params::max_chain_len)
+};
+
+struct CircAttempt {               // one check_split_map call
+    uint32_t pair, gene, chain;
+    uint8_t r1_partial;
+    cm_circ_mate in_r1, in_r2, in_pm, out_r1, out_r2, out_pm;
+    int32_t ret;
+    cm_circ_res cr;
+};
+
+// Runs the batch.  attempts: every check_split_map call in (pair, gene, chain) order -- the order the reference makes them in
+// when it goes through the pairs one after the other.  best_type[i]: what call_circ_single_split ends with for pair i (NF 40
+// when nothing was found, FR / RF, CR / NCR / MCR), -1 when the pair is not a single-split candidate of this contig;
+// best_cr[i] is meaningful for CR / NCR / MCR (the CircRes that is pushed to circ_res).  Returns 0 or the engine's error code.
+static inline int circ_orch_single(const CircEngine &E, const CircSingleIn &in, std::vector<CircAttempt> &attempts, int32_t *best_type,
+                                   cm_circ_res *best_cr) {
+    const uint32_t n = in.n, stride = in.stride;
+    const int ws = in.ws, F = (in.max_read_len - ws) / in.step + 1;
+    attempts.clear();
+    struct Pair {
+        bool going, r1_partial, remain_is_full;
+        uint32_t qspos, qepos;
+        int dir, rlen, whole_len, plen_remain, plen_full, best;
+        cm_circ_mate r1, r2;
+    };
+    std::vector<Pair> P(n);
+    // both orientations of the two reads of every candidate: remain / fullmap rows
+    std::vector<char> remain((size_t) n * stride, 0), fullmap((size_t) n * stride, 0);
+    uint32_t max_genes = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        Pair &p = P[i];
+        p.going = false;
+        best_type[i] = -1;
+        if (best_cr) memset(&best_cr[i], 0, sizeof(cm_circ_res));
+        const cm_mread &mr = in.mr[i];
+        if (mr.type != CM_CIRC_T_CHIBSJ) continue;
+        const int l1 = in.len1[i], l2 = in.len2[i];
+        p.r1_partial = mr.mlen_r1 < mr.mlen_r2;
+        const char *s1 = in.seqs1 + (size_t) i * stride, *s2 = in.seqs2 + (size_t) i * stride;
+        char *rem = &remain[(size_t) i * stride], *ful = &fullmap[(size_t) i * stride];
+        auto put = [&](char *dst, const char *src, int len, bool fwd) { if (fwd) memcpy(dst, src, len); else circ_orch_revcomp(src, len, dst); };
+        if (p.r1_partial) { put(rem, s1, l1, mr.r1_forward); put(ful, s2, l2, mr.r2_forward); p.plen_remain = l1; p.plen_full = l2; }
+        else { put(rem, s2, l2, mr.r2_forward); put(ful, s1, l1, mr.r1_forward); p.plen_remain = l2; p.plen_full = l1; }
+        circ_orch_mate(mr, 1, l1, p.r1_partial, p.r1);
+        circ_orch_mate(mr, 2, l2, !p.r1_partial, p.r2);
+        const cm_mate &pm = p.r1_partial ? p.r1.m : p.r2.m;
+        const uint32_t plen = (uint32_t) p.plen_remain;
+        const bool right_side = (pm.qspos - 1) > (plen - pm.qepos);
+        p.qspos = right_side ? 1 : pm.qepos + 1;
+        p.qepos = right_side ? pm.qspos - 1 : plen;
+        p.whole_len = (int) plen;
+        p.rlen = (int) (p.qepos - p.qspos + 1);
+        p.dir = (p.r1_partial ? mr.r1_forward : mr.r2_forward) ? 1 : -1;
+        p.best = 40;   // NF
+        p.remain_is_full = false;
+        best_type[i] = 40;
+        if (p.qepos < p.qspos || p.rlen < ws) continue;
+        const uint32_t ng = in.gene_off[i + 1] - in.gene_off[i];
+        if (ng == 0) continue;
+        p.going = true;
+        if (ng > max_genes) max_genes = ng;
+    }
+    std::vector<uint32_t> idx, sub, csub;
+    for (uint32_t g = 0; g < max_genes; g++) {
+        idx.clear();
+        for (uint32_t i = 0; i < n; i++)
+            if (P[i].going && g < in.gene_off[i + 1] - in.gene_off[i]) idx.push_back(i);
+        if (idx.empty()) break;
+        const uint32_t m = (uint32_t) idx.size();
+        // chaining of (pair, gene g) on the read remain_seq points at now
+        std::vector<char> cs((size_t) m * stride);
+        std::vector<uint32_t> qs(m), qe(m), gs(m), ge(m);
+        for (uint32_t k = 0; k < m; k++) {
+            const uint32_t i = idx[k];
+            memcpy(&cs[(size_t) k * stride], P[i].remain_is_full ? &fullmap[(size_t) i * stride] : &remain[(size_t) i * stride], stride);
+            qs[k] = P[i].qspos; qe[k] = P[i].qepos;
+            gs[k] = in.gene_start[in.gene_off[i] + g]; ge[k] = in.gene_end[in.gene_off[i] + g];
+        }
+        std::vector<int32_t> count(m);
+        const size_t CH = (size_t) in.max_chain_len;
+        std::vector<float> score(m * CH);
+        std::vector<uint32_t> clen(m * CH), rpos(m * CH * F);
+        std::vector<int32_t> qpos(m * CH * F);
+        int r = E.chain(E.self, E.contig, m, cs.data(), stride, qs.data(), qe.data(), gs.data(), ge.data(), ws, in.step, F, count.data(), score.data(),
+                        clen.data(), rpos.data(), qpos.data());
+        if (r != 0) return r;
+        for (int j = 0; j < CM_CIRC_TOPCHAIN; j++) {
+            sub.clear();
+            for (uint32_t k = 0; k < m; k++)
+                if (P[idx[k]].going && j < (count[k] < CM_CIRC_TOPCHAIN ? count[k] : CM_CIRC_TOPCHAIN)) sub.push_back(k);
+            if (sub.empty()) break;
+            const uint32_t q = (uint32_t) sub.size();
+            std::vector<char> xs((size_t) q * stride), xf((size_t) q * stride);
+            std::vector<cm_circ_mate> r1(q), r2(q), pm(q);
+            std::vector<int32_t> dir(q), rlen(q), wlen(q), ret(q), xq(q * (size_t) F), flen(q), remlen(q);
+            std::vector<uint32_t> xqs(q), xcl(q), xr(q * (size_t) F);
+            std::vector<uint8_t> r1p(q);
+            for (uint32_t t = 0; t < q; t++) {
+                const uint32_t k = sub[t], i = idx[k];
+                // remain_seq as it is now (a check_split_map of an earlier chain may have pointed it at the other read)
+                memcpy(&xs[(size_t) t * stride], P[i].remain_is_full ? &fullmap[(size_t) i * stride] : &remain[(size_t) i * stride], stride);
+                r1[t] = P[i].r1; r2[t] = P[i].r2;
+                dir[t] = P[i].dir; xqs[t] = P[i].qspos; rlen[t] = P[i].rlen; wlen[t] = P[i].whole_len;
+                xcl[t] = clen[k * CH + j];
+                memcpy(&xr[(size_t) t * F], &rpos[(k * CH + j) * F], (size_t) F * 4);
+                memcpy(&xq[(size_t) t * F], &qpos[(k * CH + j) * F], (size_t) F * 4);
+            }
+            r = E.exact(E.self, E.contig, q, xs.data(), stride, r1.data(), r2.data(), dir.data(), xqs.data(), rlen.data(), wlen.data(), (uint32_t) F,
+                        xcl.data(), xr.data(), xq.data(), ws, pm.data(), ret.data());
+            if (r != 0) return r;
+            for (uint32_t t = 0; t < q; t++) { P[idx[sub[t]]].r1 = r1[t]; P[idx[sub[t]]].r2 = r2[t]; }   // the look-ups find_exact_coord cached
+            csub.clear();
+            for (uint32_t t = 0; t < q; t++)
+                if (pm[t].m.type == CM_CIRC_T_CONCRD) csub.push_back(t);
+            if (csub.empty()) continue;
+            const uint32_t c = (uint32_t) csub.size();
+            std::vector<cm_circ_mate> c1(c), c2(c), cp(c);
+            std::vector<int32_t> cret(c);
+            std::vector<cm_circ_res> ccr(c);
+            std::vector<uint8_t> sw(c);
+            std::vector<char> crem((size_t) c * stride), cful((size_t) c * stride);
+            std::vector<int32_t> crl(c), cfl(c);
+            std::vector<uint8_t> cr1p(c);
+            for (uint32_t u = 0; u < c; u++) {
+                const uint32_t t = csub[u], i = idx[sub[t]];
+                c1[u] = P[i].r1; c2[u] = P[i].r2; cp[u] = pm[t];
+                // remain_seq / fullmap_seq as ProcessCirc holds them now; their lengths never change
+                memcpy(&crem[(size_t) u * stride], &xs[(size_t) t * stride], stride);
+                memcpy(&cful[(size_t) u * stride], &fullmap[(size_t) i * stride], stride);
+                crl[u] = P[i].plen_remain; cfl[u] = P[i].plen_full;
+                cr1p[u] = P[i].r1_partial;
+            }
+            std::vector<cm_circ_mate> i1 = c1, i2 = c2, ip = cp;
+            r = E.check(E.self, E.contig, c, crem.data(), cful.data(), stride, crl.data(), cfl.data(), cr1p.data(), c1.data(), c2.data(), cp.data(), ws,
+                        cret.data(), ccr.data(), sw.data());
+            if (r != 0) return r;
+            for (uint32_t u = 0; u < c; u++) {
+                const uint32_t t = csub[u], i = idx[sub[t]];
+                Pair &p = P[i];
+                if (cret[u] < 0) return -100;   // a fixed-size list of the device code overflowed
+                CircAttempt a;
+                a.pair = i; a.gene = g; a.chain = (uint32_t) j; a.r1_partial = p.r1_partial;
+                a.in_r1 = i1[u]; a.in_r2 = i2[u]; a.in_pm = ip[u];
+                a.out_r1 = c1[u]; a.out_r2 = c2[u]; a.out_pm = cp[u];
+                a.ret = cret[u]; a.cr = ccr[u];
+                attempts.push_back(a);
+                p.r1 = c1[u]; p.r2 = c2[u];
+                if (sw[u]) p.remain_is_full = true;
+                const int type = cret[u];
+                if (type < 20) { p.best = type; p.going = false; }                      // FR / RF: return
+                else if (type <= 22 && type < p.best) {                                 // CR / NCR / MCR better than what we have
+                    p.best = type;
+                    if (best_cr) best_cr[i] = ccr[u];
+                    if (type == 20) p.going = false;                                    // CR: push and return
+                }
+            }
+        }
+    }
+    for (uint32_t i = 0; i < n; i++)
+        if (best_type[i] != -1) best_type[i] = P[i].best;
+    // (pair, gene, chain) order
+    std::vector<CircAttempt> sorted;
+    sorted.reserve(attempts.size());
+    std::vector<uint32_t> order(attempts.size());
+    for (size_t k = 0; k < order.size(); k++) order[k] = (uint32_t) k;
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) {
+        const CircAttempt &a = attempts[x], &b = attempts[y];
+        if (a.pair != b.pair) return a.pair < b.pair;
+        if (a.gene != b.gene) return a.gene < b.gene;
+        return a.chain < b.chain;
+    });
+    for (uint32_t k : order) sorted.push_back(attempts[k]);
+    attempts.swap(sorted);
+    return 0;
+}

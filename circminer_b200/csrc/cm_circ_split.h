@@ -559,8 +559,11 @@ CM_HD void cm_circ_mate_out(const MateD &m, cm_circ_mate &o) {
     o.exons_spos = m.exons_spos; o.exons_epos = m.exons_epos; o.exon_ind_spos = m.exon_ind_spos; o.exon_ind_epos = m.exon_ind_epos;
 }
 // v.p.kmer must be window_size; fullmap / remain = the two reads as call_circ_single_split orients them
+// remain_is_fullmap (nullable): the four-mate path may leave ProcessCirc::remain_seq pointing at the other read
+// (process_circ.cpp:973, :983), which the next chain of the same read then sees
 CM_HDN int cm_circ_check_row(const DevView &v, const uint8_t *remain_seq, int remain_len, const uint8_t *fullmap_seq, int fullmap_len,
-                             bool r1_partial, cm_circ_mate &r1, cm_circ_mate &r2, cm_circ_mate &pm, cm_circ_res &out) {
+                             bool r1_partial, cm_circ_mate &r1, cm_circ_mate &r2, cm_circ_mate &pm, cm_circ_res &out,
+                             uint8_t *remain_is_fullmap = nullptr) {
     ExtCtx x;
     ext_ctx_init(x, &v);
     CircSplitCtx c;
@@ -582,10 +585,28 @@ CM_HDN int cm_circ_check_row(const DevView &v, const uint8_t *remain_seq, int re
     cm_circ_mate_out(a, r1);
     cm_circ_mate_out(b, r2);
     cm_circ_mate_out(p, pm);
+    if (remain_is_fullmap) *remain_is_fullmap = (c.remain_seq == fullmap_seq && fullmap_seq != remain_seq) ? 1 : 0;
     out.spos = cr.spos; out.epos = cr.epos;
     for (int k = 0; k < 2; k++) {
         out.start_signal[k] = cr.ss[k]; out.end_signal[k] = cr.es[k]; out.start_bp_ref[k] = cr.sref[k]; out.end_bp_ref[k] = cr.eref[k];
     }
     out.start_signal_n = cr.ss_n; out.end_signal_n = cr.es_n; out.ref_n = cr.ref_n; out.was_set = cr.was_set;
     return c.overflow ? -1 : ret;
+}
+
+// find_exact_coord with the pair's mates as ProcessCirc keeps them from chain to chain (their cached start look-ups survive a
+// trim by final_check); pm comes back with the caches find_exact_coord leaves on it
+CM_HDN int cm_circ_exact_row(const DevView &v, cm_circ_mate &r1, cm_circ_mate &r2, cm_circ_mate &pm_out, int dir, uint32_t qspos, const uint8_t *rseq,
+                             int rlen, int whole_len, const ChainView &bc) {
+    ExtCtx x;
+    ext_ctx_init(x, &v);
+    MateD a, b, pm;
+    cm_circ_mate_in(r1, a);
+    cm_circ_mate_in(r2, b);
+    mate_init(pm, v.p);
+    const int ret = cm_circ_exact(x, a, b, pm, dir, qspos, rseq, rlen, whole_len, bc) ? 1 : 0;
+    cm_circ_mate_out(a, r1);
+    cm_circ_mate_out(b, r2);
+    cm_circ_mate_out(pm, pm_out);
+    return ret;
 }

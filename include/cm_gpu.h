@@ -315,6 +315,30 @@ int cm_gpu_circ_check_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const ch
                             const int32_t *remain_len, const int32_t *fullmap_len, const uint8_t *r1_partial, cm_circ_mate *mm_r1,
                             cm_circ_mate *mm_r2, cm_circ_mate *partial_mm, int window_size, int32_t *ret, cm_circ_res *cr);
 
+/* find_exact_coord as cm_gpu_circ_exact_batch, with the two mates of the pair going in and out as ProcessCirc keeps them from one
+ * chain of a read to the next (their cached look-ups survive a trim by final_check) and partial_mm coming back with the look-ups
+ * find_exact_coord leaves on it -- what check_split_map is then called with. */
+int cm_gpu_circ_exact_mates_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs, uint32_t stride, cm_circ_mate *mm_r1,
+                                  cm_circ_mate *mm_r2, const int32_t *dir, const uint32_t *qspos, const int32_t *rlen, const int32_t *whole_len,
+                                  uint32_t frag_slots, const uint32_t *chain_len, const uint32_t *frag_rpos, const int32_t *frag_qpos,
+                                  int window_size, cm_circ_mate *partial_mm, int32_t *ret);
+
+/* ProcessCirc::call_circ_single_split (src/process_circ.cpp:360-483) for a batch of pairs: for every pair whose MatchedRead is a
+ * CHIBSJ, per gene of gtf_parser.get_gene_overlap(mm_r1.spos, false)->seg_list (given by the caller in that order: gene_off[n + 1],
+ * gene_start / gene_end), chaining, then chain by chain (TOPCHAIN = 10) find_exact_coord and, when it is CONCRD, check_split_map,
+ * until FR / RF or CR.  mr: stage 1's MatchedRead with its positions in CONTIG coordinates (after GTFParser::chrloc2conloc).
+ * Outputs: every check_split_map call in the reference's order (pair, gene, chain) -- the pair, the mates before and after,
+ * the type it returned and its CircRes: what print_split_mapping and the type column of candidates.pam are written from --
+ * n_attempts (the first attempt_cap are stored; the att_* arrays may be NULL), and per pair best_type (what the function ends
+ * with: 40 = nothing, 0 / 1 = FR / RF, 20..22 = the CircRes pushed to circ_res, in best_cr, contig coordinates; -1 = not a
+ * candidate). */
+int cm_gpu_circ_single_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
+                             const uint16_t *len1, const uint16_t *len2, const cm_mread *mr, const uint32_t *gene_off, const uint32_t *gene_start,
+                             const uint32_t *gene_end, int window_size, int step, uint32_t attempt_cap, uint32_t *n_attempts, uint32_t *att_pair,
+                             uint8_t *att_r1_partial, cm_circ_mate *att_in_r1, cm_circ_mate *att_in_r2, cm_circ_mate *att_in_pm, int32_t *att_ret,
+                             cm_circ_res *att_cr, cm_circ_mate *att_out_r1, cm_circ_mate *att_out_r2, cm_circ_mate *att_out_pm, int32_t *best_type,
+                             cm_circ_res *best_cr);
+
 /* Alignment kernels, one problem per row (src/align.h:165-176):
  *   kind 0: DropAlignment::local_alignment_right_sc  (src/align.cpp:669)
  *   kind 1: DropAlignment::local_alignment_left_sc   (:694)

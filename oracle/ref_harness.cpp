@@ -606,13 +606,18 @@ int cmref_circ_single(uint32_t n, const char *seqs1, const char *seqs2, uint32_t
                       const cm_mread *mr_in, int ws, uint32_t cap, uint32_t *call_pair, uint8_t *r1_partial_out, char *remain_rows,
                       char *fullmap_rows, int32_t *remain_len, int32_t *fullmap_len, cm_circ_mate *in_r1, cm_circ_mate *in_r2,
                       cm_circ_mate *in_pm, int32_t *ret, cm_circ_res *cr_out, cm_circ_mate *out_r1, cm_circ_mate *out_r2,
-                      cm_circ_mate *out_pm, int32_t *best_type) {
+                      cm_circ_mate *out_pm, int32_t *best_type, cm_mread *mr_con, uint32_t gene_cap, uint32_t *gene_cnt, uint32_t *gene_se) {
+    // mr_con[i]: the MatchedRead with contig coordinates (type -1 for pairs that are no candidates here); gene_cnt[i] /
+    // gene_se[i][gene_cap][2]: start / end of the genes get_gene_overlap(mm_r1.spos) lists, in its order
     if (circ_pc(ws) != 0) return -1;
     ProcessCirc &pc = *g_pc;
     uint32_t n_rec = 0;
     std::vector<char> s1(stride + 8), s2(stride + 8), rc1(stride + 8), rc2(stride + 8);
     for (uint32_t i = 0; i < n; i++) {
         best_type[i] = -1;
+        gene_cnt[i] = 0;
+        mr_con[i] = mr_in[i];
+        mr_con[i].type = -1;
         MatchedRead mr;
         mread_to_ref(&mr_in[i], &mr);
         if (mr.type != CHIBSJ || (int) mr.contig_num != contigNum) continue;
@@ -631,6 +636,8 @@ int cmref_circ_single(uint32_t n, const char *seqs1, const char *seqs2, uint32_t
         pc.fullmap_seq_len = !r1_partial ? l1 : l2;
         gtf_parser.chrloc2conloc(mr.chr_r1, mr.spos_r1, mr.epos_r1);
         gtf_parser.chrloc2conloc(mr.chr_r2, mr.spos_r2, mr.epos_r2);
+        mr_con[i].type = mr.type;
+        mr_con[i].spos_r1 = mr.spos_r1; mr_con[i].epos_r1 = mr.epos_r1; mr_con[i].spos_r2 = mr.spos_r2; mr_con[i].epos_r2 = mr.epos_r2;
         MatchedMate mm_r1(mr, 1, l1, r1_partial);
         MatchedMate mm_r2(mr, 2, l2, !r1_partial);
         // this constructor leaves is_concord / left_ok / right_ok unset (src/common.cpp:192-235); nothing on the path reads them
@@ -647,6 +654,12 @@ int cmref_circ_single(uint32_t n, const char *seqs1, const char *seqs2, uint32_t
         if (qepos < qspos || remain_len_i < ws) continue;
         const IntervalInfo<GeneInfo> *gene_info = gtf_parser.get_gene_overlap(mm_r1.spos, false);
         if (gene_info == NULL) continue;
+        if (gene_info->seg_list.size() > gene_cap) return -3;
+        gene_cnt[i] = (uint32_t) gene_info->seg_list.size();
+        for (unsigned int g = 0; g < gene_info->seg_list.size(); ++g) {
+            gene_se[((size_t) i * gene_cap + g) * 2] = gene_info->seg_list[g].start;
+            gene_se[((size_t) i * gene_cap + g) * 2 + 1] = gene_info->seg_list[g].end;
+        }
         int best = NF;
         bool done = false;
         for (unsigned int g = 0; g < gene_info->seg_list.size() && !done; ++g) {
@@ -735,6 +748,60 @@ int cmref_circ_check(uint32_t n, const char *remain_seq, const char *fullmap_seq
         ret[i] = pc.check_split_map(a, b, p, r1_partial[i] != 0, cr);
         circ_res_export(cr, !cr.start_bp_ref.empty(), &cr_out[i]);
         circ_mate_export(a, &mm_r1[i]); circ_mate_export(b, &mm_r2[i]); circ_mate_export(p, &partial_mm[i]);
+    }
+    return 0;
+}
+
+// The reference's own ProcessCirc::call_circ_single_split (process_circ.cpp:360-483), unmodified, on the same pairs: what it
+// writes to candidates.pam per check_split_map call (the type at the end of every line) and what it pushes to circ_res.  Pins
+// the control flow restated in cmref_circ_single.  types[i][type_cap], n_types[i]; pushed[i] = 1 with the pushed CircRes's
+// type / spos / epos (chromosome coordinates, as the reference stores them).
+int cmref_circ_single_real(uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride, const uint16_t *len1, const uint16_t *len2,
+                           const cm_mread *mr_in, int ws, uint32_t type_cap, uint32_t *n_types, int32_t *types, uint8_t *pushed, int32_t *push_type,
+                           uint32_t *push_spos, uint32_t *push_epos) {
+    if (circ_pc(ws) != 0) return -1;
+    ProcessCirc &pc = *g_pc;
+    pc.refresh_hash_table_list();   // do_process drops the per-gene tables when the contig changes (gene ids are per contig)
+    for (uint32_t i = 0; i < n; i++) {
+        n_types[i] = 0; pushed[i] = 0; push_type[i] = -1; push_spos[i] = push_epos[i] = 0;
+        MatchedRead mr;
+        mread_to_ref(&mr_in[i], &mr);
+        if (mr.type != CHIBSJ || (int) mr.contig_num != contigNum) continue;
+        const int l1 = len1[i], l2 = len2[i];
+        memcpy(g_rec1->seq, seqs1 + (size_t) i * stride, l1); g_rec1->seq[l1] = 0;
+        memcpy(g_rec2->seq, seqs2 + (size_t) i * stride, l2); g_rec2->seq[l2] = 0;
+        revcomp(g_rec1->seq, l1, g_rec1->rcseq); g_rec1->rcseq[l1] = 0;
+        revcomp(g_rec2->seq, l2, g_rec2->rcseq); g_rec2->rcseq[l2] = 0;
+        g_rec1->seq_len = l1; g_rec2->seq_len = l2;
+        strcpy(g_rec1->rname, "r"); strcpy(g_rec2->rname, "r");
+        *(g_rec1->mr) = mr;
+        *(g_rec2->mr) = mr;
+        char *buf = NULL;
+        size_t blen = 0;
+        FILE *mem = open_memstream(&buf, &blen);
+        FILE *keep = pc.candid_file;
+        pc.candid_file = mem;
+        const size_t before = pc.circ_res.size();
+        pc.call_circ(g_rec1, g_rec2);
+        fflush(mem);
+        pc.candid_file = keep;
+        fclose(mem);
+        // one line per attempt: ... \t<type>\n
+        for (char *ln = buf; ln && *ln;) {
+            char *nl = strchr(ln, '\n');
+            if (!nl) break;
+            char *tab = nl;
+            while (tab > ln && *(tab - 1) != '\t') tab--;
+            if (n_types[i] < type_cap) types[(size_t) i * type_cap + n_types[i]] = atoi(tab);
+            n_types[i]++;
+            ln = nl + 1;
+        }
+        free(buf);
+        if (pc.circ_res.size() > before) {
+            const CircRes &cr = pc.circ_res.back();
+            pushed[i] = 1; push_type[i] = cr.type; push_spos[i] = cr.spos; push_epos[i] = cr.epos;
+            pc.circ_res.pop_back();
+        }
     }
     return 0;
 }

@@ -260,6 +260,9 @@ def main():
             # single-split path of stage 2 with every check_split_map call recorded
             mr1, _ = h.process_pe(s1, s2, lens, lens, fresh_mreads(n, a.max_ed))
             rec = h.circ_single(s1, s2, lens, lens, mr1)
+            out[f"c{c}_circs_mr_chr"] = mr1
+            for k, v in h.circ_single_real(s1, s2, lens, lens, mr1).items():   # the unmodified call_circ on the same pairs
+                out[f"c{c}_circreal_{k}"] = v
             for k, v in rec.items():
                 out[f"c{c}_circs_{k}"] = v
             if len(rec["ret"]):

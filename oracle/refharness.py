@@ -222,15 +222,35 @@ class RefHarness:
                    ret=np.zeros(cap, np.int32), cr=np.zeros(cap, CIRC_RES_DTYPE), out_r1=np.zeros(cap, CIRC_MATE_DTYPE),
                    out_r2=np.zeros(cap, CIRC_MATE_DTYPE), out_pm=np.zeros(cap, CIRC_MATE_DTYPE))
         best = np.zeros(n, np.int32)
+        gene_cap = 16
+        mr_con = np.zeros(n, mr.dtype)
+        gene_cnt = np.zeros(n, np.uint32)
+        gene_se = np.zeros((n, gene_cap, 2), np.uint32)
         vp = lambda x: x.ctypes.data_as(C.c_void_p)
         order = ("call_pair", "r1_partial", "remain_rows", "fullmap_rows", "remain_len", "fullmap_len", "in_r1", "in_r2", "in_pm", "ret", "cr",
                  "out_r1", "out_r2", "out_pm")
         k = self.lib.cmref_circ_single(C.c_uint32(n), vp(a1), vp(a2), C.c_uint32(stride), vp(l1), vp(l2), vp(mr), ws, C.c_uint32(cap),
-                                       *[vp(rec[x]) for x in order], vp(best))
+                                       *[vp(rec[x]) for x in order], vp(best), vp(mr_con), C.c_uint32(gene_cap), vp(gene_cnt), vp(gene_se))
         if k < 0:
             raise RuntimeError(f"cmref_circ_single failed: {k}")
         out = {x: rec[x][:k] for x in order}
         out["best_type"] = best
+        out["mr_con"], out["gene_cnt"], out["gene_se"] = mr_con, gene_cnt, gene_se
+        return out
+
+    def circ_single_real(self, s1, s2, l1, l2, mreads, ws: int = 8, type_cap: int = 64) -> dict:
+        """The unmodified ProcessCirc::call_circ on every CHIBSJ pair of the current contig: the types it writes to candidates.pam
+        and what it pushes to circ_res (cmref_circ_single_real)."""
+        a1, a2 = np.ascontiguousarray(s1, np.uint8), np.ascontiguousarray(s2, np.uint8)
+        n, stride = a1.shape
+        l1, l2 = np.ascontiguousarray(l1, np.uint16), np.ascontiguousarray(l2, np.uint16)
+        mr = np.ascontiguousarray(mreads)
+        out = dict(n_types=np.zeros(n, np.uint32), types=np.zeros((n, type_cap), np.int32), pushed=np.zeros(n, np.uint8),
+                   push_type=np.zeros(n, np.int32), push_spos=np.zeros(n, np.uint32), push_epos=np.zeros(n, np.uint32))
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        r = self.lib.cmref_circ_single_real(C.c_uint32(n), vp(a1), vp(a2), C.c_uint32(stride), vp(l1), vp(l2), vp(mr), ws, C.c_uint32(type_cap),
+                                            *[vp(out[k]) for k in ("n_types", "types", "pushed", "push_type", "push_spos", "push_epos")])
+        assert r == 0, r
         return out
 
     def circ_check(self, rec: dict, ws: int = 8) -> dict:

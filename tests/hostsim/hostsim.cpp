@@ -12,6 +12,7 @@
 #include "../../circminer_b200/csrc/cm_circ.h"
 #define CM_CIRC_TRACE 1
 #include "../../circminer_b200/csrc/cm_circ_split.h"
+#include "../../circminer_b200/csrc/cm_circ_orch.h"
 
 #pragma pack(push, 1)
 struct GeneralIndexPacked {
@@ -417,6 +418,69 @@ int hs_circ_check(HsCtx *c, int contig_id, uint32_t n, const char *remain_seq, c
         ret[i] = cm_circ_check_row(v, (const uint8_t *) remain_seq + (size_t) i * stride, remain_len[i], (const uint8_t *) fullmap_seq + (size_t) i * stride,
                                    fullmap_len[i], r1_partial[i] != 0, mm_r1[i], mm_r2[i], partial_mm[i], cr[i]);
     return 0;
+}
+
+// find_exact_coord with the pair's mates carried from chain to chain (arguments of cm_gpu_circ_exact_mates_batch)
+int hs_circ_exact_mates(HsCtx *c, int contig_id, uint32_t n, const char *seqs, uint32_t stride, cm_circ_mate *r1, cm_circ_mate *r2, const int32_t *dir,
+                        const uint32_t *qspos, const int32_t *rlen, const int32_t *whole_len, uint32_t F, const uint32_t *chain_len,
+                        const uint32_t *frag_rpos, const int32_t *frag_qpos, int ws, cm_circ_mate *pm, int32_t *ret) {
+    DevView v = make_view(c, contig_id);
+    v.p.kmer = ws;
+    std::vector<FragDev> fr(F);
+    for (uint32_t i = 0; i < n; i++) {
+        for (uint32_t f = 0; f < F; f++) fr[f] = FragDev{frag_rpos[(size_t) i * F + f], frag_qpos[(size_t) i * F + f]};
+        ChainView bc;
+        bc.frags = fr.data(); bc.chain_len = chain_len[i]; bc.aux = nullptr; bc.spec = nullptr;
+        ret[i] = cm_circ_exact_row(v, r1[i], r2[i], pm[i], dir[i], qspos[i], (const uint8_t *) seqs + (size_t) i * stride, rlen[i], whole_len[i], bc);
+    }
+    return 0;
+}
+
+// the single-split loop (cm_circ_orch.h) over the host build of the three pieces
+struct HsCircEngine {
+    HsCtx *c;
+    const uint32_t *circ_pos, *circ_off;
+};
+static int hs_eng_chain(void *self, int contig, uint32_t n, const char *seqs, uint32_t stride, const uint32_t *qspos, const uint32_t *qepos,
+                        const uint32_t *gs, const uint32_t *ge, int ws, int step, int F, int32_t *count, float *score, uint32_t *clen, uint32_t *rpos,
+                        int32_t *qpos) {
+    HsCircEngine *e = (HsCircEngine *) self;
+    return hs_circ_chain(e->c, contig, e->circ_pos, e->circ_off, n, seqs, stride, qspos, qepos, gs, ge, ws, step, F, count, nullptr, score, clen, rpos, qpos);
+}
+static int hs_eng_exact(void *self, int contig, uint32_t n, const char *seqs, uint32_t stride, cm_circ_mate *r1, cm_circ_mate *r2, const int32_t *dir,
+                        const uint32_t *qspos, const int32_t *rlen, const int32_t *wl, uint32_t F, const uint32_t *clen, const uint32_t *rpos,
+                        const int32_t *qpos, int ws, cm_circ_mate *pm, int32_t *ret) {
+    return hs_circ_exact_mates(((HsCircEngine *) self)->c, contig, n, seqs, stride, r1, r2, dir, qspos, rlen, wl, F, clen, rpos, qpos, ws, pm, ret);
+}
+static int hs_eng_check(void *self, int contig, uint32_t n, const char *rem, const char *ful, uint32_t stride, const int32_t *rl, const int32_t *fl,
+                        const uint8_t *r1p, cm_circ_mate *r1, cm_circ_mate *r2, cm_circ_mate *pm, int ws, int32_t *ret, cm_circ_res *cr, uint8_t *sw) {
+    HsCtx *c = ((HsCircEngine *) self)->c;
+    DevView v = make_view(c, contig);
+    v.p.kmer = ws;
+    for (uint32_t i = 0; i < n; i++)
+        ret[i] = cm_circ_check_row(v, (const uint8_t *) rem + (size_t) i * stride, rl[i], (const uint8_t *) ful + (size_t) i * stride, fl[i], r1p[i] != 0,
+                                   r1[i], r2[i], pm[i], cr[i], sw + i);
+    return 0;
+}
+// -> number of attempts (<= cap written), or < 0
+int hs_circ_single(HsCtx *c, int contig_id, const uint32_t *circ_pos, const uint32_t *circ_off, uint32_t n, const char *seqs1, const char *seqs2,
+                   uint32_t stride, const uint16_t *len1, const uint16_t *len2, const cm_mread *mr, const uint32_t *gene_off, const uint32_t *gene_start,
+                   const uint32_t *gene_end, int ws, int step, uint32_t cap, uint32_t *att_pair, uint8_t *att_r1_partial, cm_circ_mate *in_r1,
+                   cm_circ_mate *in_r2, cm_circ_mate *in_pm, int32_t *ret, cm_circ_res *cr, cm_circ_mate *out_r1, cm_circ_mate *out_r2,
+                   cm_circ_mate *out_pm, int32_t *best_type, cm_circ_res *best_cr) {
+    HsCircEngine he{c, circ_pos, circ_off};
+    CircEngine E{&he, contig_id, hs_eng_chain, hs_eng_exact, hs_eng_check};
+    CircSingleIn in{n, seqs1, seqs2, stride, len1, len2, mr, gene_off, gene_start, gene_end, ws, step, c->p.max_read_len, c->p.max_chain_len};
+    std::vector<CircAttempt> att;
+    int r = circ_orch_single(E, in, att, best_type, best_cr);
+    if (r != 0) return r < 0 ? r : -r;
+    for (size_t k = 0; k < att.size() && k < cap; k++) {
+        att_pair[k] = att[k].pair; att_r1_partial[k] = att[k].r1_partial;
+        in_r1[k] = att[k].in_r1; in_r2[k] = att[k].in_r2; in_pm[k] = att[k].in_pm;
+        out_r1[k] = att[k].out_r1; out_r2[k] = att[k].out_r2; out_pm[k] = att[k].out_pm;
+        ret[k] = att[k].ret; cr[k] = att[k].cr;
+    }
+    return (int) att.size();
 }
 
 // which paths of the stage-2 classification the rows so far reached (see CM_CIRC_HIT in cm_circ_split.h); resets the counters

@@ -110,7 +110,25 @@ class HostSim:
     def circ_chaining(self, contig_id, genome_ascii, seqs, qspos, qepos, gene_start, gene_end, window_size=8, step=3):
         """ProcessCirc::chaining per row through cm_circ.h; the contig's ws-mer index is made here with numpy
         (genome_ascii[p - 1] = base at 1-based p)."""
+        pos, off = self._circ_index(genome_ascii, window_size)
         ws = window_size
+        a = np.ascontiguousarray(seqs, np.uint8)
+        n, Cn = a.shape[0], self.Cn
+        F = (self.params.max_read_len - ws) // step + 1
+        u = lambda x: np.ascontiguousarray(x, np.uint32)
+        qspos, qepos, gene_start, gene_end = u(qspos), u(qepos), u(gene_start), u(gene_end)
+        out = dict(chain_count=np.zeros(n, np.int32), kmer_cnt=np.zeros(n, np.int32), score=np.zeros((n, Cn), np.float32),
+                   chain_len=np.zeros((n, Cn), np.uint32), frag_rpos=np.zeros((n, Cn, F), np.uint32), frag_qpos=np.zeros((n, Cn, F), np.int32))
+        self.lib.hs_circ_chain(self.ctx, contig_id, _vp(pos), _vp(off), C.c_uint32(n), _vp(a), C.c_uint32(a.shape[1]), _vp(qspos), _vp(qepos),
+                               _vp(gene_start), _vp(gene_end), ws, step, F,
+                               *[_vp(out[k]) for k in ("chain_count", "kmer_cnt", "score", "chain_len", "frag_rpos", "frag_qpos")])
+        return out
+
+    def _circ_index(self, genome_ascii, ws):
+        """The contig's ws-mer index (positions sorted by (hash, position), run offsets), cached per genome array."""
+        key = (id(genome_ascii), ws)
+        if getattr(self, "_circ_ix", None) and self._circ_ix[0] == key:
+            return self._circ_ix[1], self._circ_ix[2]
         g = np.ascontiguousarray(genome_ascii, np.uint8)
         code = np.full(256, 4, np.int64)
         for i, ch in enumerate(b"ACGT"):
@@ -128,16 +146,37 @@ class HostSim:
         pos = np.ascontiguousarray(p0[order] + 1, np.uint32)
         off = np.zeros(4 ** ws + 1, np.uint32)
         off[1:] = np.cumsum(np.bincount(key[p0], minlength=4 ** ws))
-        a = np.ascontiguousarray(seqs, np.uint8)
-        n, Cn = a.shape[0], self.Cn
-        F = (self.params.max_read_len - ws) // step + 1
-        u = lambda x: np.ascontiguousarray(x, np.uint32)
-        qspos, qepos, gene_start, gene_end = u(qspos), u(qepos), u(gene_start), u(gene_end)
-        out = dict(chain_count=np.zeros(n, np.int32), kmer_cnt=np.zeros(n, np.int32), score=np.zeros((n, Cn), np.float32),
-                   chain_len=np.zeros((n, Cn), np.uint32), frag_rpos=np.zeros((n, Cn, F), np.uint32), frag_qpos=np.zeros((n, Cn, F), np.int32))
-        self.lib.hs_circ_chain(self.ctx, contig_id, _vp(pos), _vp(off), C.c_uint32(n), _vp(a), C.c_uint32(a.shape[1]), _vp(qspos), _vp(qepos),
-                               _vp(gene_start), _vp(gene_end), ws, step, F,
-                               *[_vp(out[k]) for k in ("chain_count", "kmer_cnt", "score", "chain_len", "frag_rpos", "frag_qpos")])
+        self._circ_ix = ((id(genome_ascii), ws), pos, off)
+        return pos, off
+
+    def circ_single(self, contig_id, genome_ascii, s1, s2, l1, l2, mr_con, gene_cnt, gene_se, window_size=8, step=3, cap=20000):
+        """call_circ_single_split's loop (csrc/cm_circ_orch.h) over the host build of chaining / find_exact_coord / check_split_map."""
+        from circminer_b200.api import CIRC_MATE_DTYPE, CIRC_RES_DTYPE
+        pos, off = self._circ_index(genome_ascii, window_size)
+        a1, a2 = np.ascontiguousarray(s1, np.uint8), np.ascontiguousarray(s2, np.uint8)
+        n, stride = a1.shape
+        l1, l2 = np.ascontiguousarray(l1, np.uint16), np.ascontiguousarray(l2, np.uint16)
+        mr = np.ascontiguousarray(mr_con)
+        gene_cnt = np.asarray(gene_cnt, np.int64)
+        goff = np.zeros(n + 1, np.uint32)
+        goff[1:] = np.cumsum(gene_cnt)
+        sel = np.arange(gene_se.shape[1])[None, :] < gene_cnt[:, None]
+        gs = np.ascontiguousarray(gene_se[:, :, 0][sel], np.uint32)
+        ge = np.ascontiguousarray(gene_se[:, :, 1][sel], np.uint32)
+        if len(gs) == 0:
+            gs, ge = np.zeros(1, np.uint32), np.zeros(1, np.uint32)
+        rec = dict(call_pair=np.zeros(cap, np.uint32), r1_partial=np.zeros(cap, np.uint8), in_r1=np.zeros(cap, CIRC_MATE_DTYPE),
+                   in_r2=np.zeros(cap, CIRC_MATE_DTYPE), in_pm=np.zeros(cap, CIRC_MATE_DTYPE), ret=np.zeros(cap, np.int32),
+                   cr=np.zeros(cap, CIRC_RES_DTYPE), out_r1=np.zeros(cap, CIRC_MATE_DTYPE), out_r2=np.zeros(cap, CIRC_MATE_DTYPE),
+                   out_pm=np.zeros(cap, CIRC_MATE_DTYPE))
+        best, best_cr = np.zeros(n, np.int32), np.zeros(n, CIRC_RES_DTYPE)
+        k = self.lib.hs_circ_single(self.ctx, contig_id, _vp(pos), _vp(off), C.c_uint32(n), _vp(a1), _vp(a2), C.c_uint32(stride), _vp(l1), _vp(l2),
+                                    _vp(mr), _vp(goff), _vp(gs), _vp(ge), window_size, step, C.c_uint32(cap),
+                                    *[_vp(rec[x]) for x in ("call_pair", "r1_partial", "in_r1", "in_r2", "in_pm", "ret", "cr", "out_r1", "out_r2", "out_pm")],
+                                    _vp(best), _vp(best_cr))
+        assert k >= 0, k
+        out = {x: v[:k] for x, v in rec.items()}
+        out["best_type"], out["best_cr"] = best, best_cr
         return out
 
 

@@ -211,3 +211,72 @@ def test_gpu_equals_check_split_map(tmp_path):
         return m
     m = _check_split_map(tmp_path, make, 20000)
     m.close()
+
+
+# ---- the single-split path end to end -------------------------------------------------------------------------------------------
+def _single_split(tmp_path, make_engine, run, pairs):
+    """call_circ_single_split for a batch (csrc/cm_circ_orch.h over the three pieces) against the reference in two steps:
+    (1) the UNMODIFIED ProcessCirc::call_circ on every back-splice pair of T1 -- the type column it writes to candidates.pam per
+    attempt and the CircRes it pushes to circ_res; (2) its control flow restated over the reference's own member functions with
+    every check_split_map call recorded (oracle/ref_harness.cpp: cmref_circ_single), which must agree with (1) and gives the
+    mates of every attempt.  The batch entry must reproduce both: attempts in order with their mates before and after, types,
+    CircRes, and per pair what the function ends with."""
+    from circminer_b200 import workload
+    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000, n_pairs=pairs)
+    dump = live_dump(str(tmp_path / "cs.npz"), workload="T1", contig_size=3_500_000, pairs=pairs, circ_single=True, no_stage_dumps=True)
+    eng = make_engine(w)
+    n, L = w["s1"].shape
+    lens = np.full(n, L, np.uint16)
+    total = 0
+    for c in range(int(dump["n_contigs"])):
+        rec = {k[len(f"c{c}_circs_"):]: dump[k] for k in dump.files if k.startswith(f"c{c}_circs_")}
+        real = {k[len(f"c{c}_circreal_"):]: dump[k] for k in dump.files if k.startswith(f"c{c}_circreal_")}
+        cnt = np.bincount(rec["call_pair"], minlength=n)
+        off = np.concatenate([[0], np.cumsum(cnt)])
+        # (2) agrees with (1)
+        assert (real["n_types"] == cnt).all()
+        for i in np.nonzero(cnt)[0]:
+            assert (real["types"][i, :cnt[i]] == rec["ret"][off[i]:off[i + 1]]).all(), i
+        got = run(eng, c, w, lens, rec)
+        assert len(got["ret"]) == len(rec["ret"]), (len(got["ret"]), len(rec["ret"]))
+        for k in ("call_pair", "r1_partial", "ret", "cr", "in_r1", "in_r2", "in_pm", "out_r1", "out_r2", "out_pm"):
+            bad = np.nonzero(got[k] != rec[k])[0]
+            assert len(bad) == 0, f"contig {c} {k}: {len(bad)} of {len(rec[k])} attempts differ, first {bad[:5]}"
+        assert (got["best_type"] == rec["best_type"]).all()
+        bt = got["best_type"]
+        pushed = (bt >= 20) & (bt <= 22)
+        assert (pushed == (real["pushed"] == 1)).all() and (real["push_type"][pushed] == bt[pushed]).all()
+        shift = rec["mr_con"]["spos_r1"].astype(np.int64) - rec["mr_chr"]["spos_r1"].astype(np.int64)   # contig -> chromosome coordinates
+        assert (got["best_cr"]["spos"][pushed].astype(np.int64) - shift[pushed] == real["push_spos"][pushed]).all()
+        assert (got["best_cr"]["epos"][pushed].astype(np.int64) - shift[pushed] == real["push_epos"][pushed]).all()
+        total += int(pushed.sum())
+    assert total > 50
+    return eng
+
+
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_host_build_equals_call_circ_single_split(tmp_path):
+    def make(w):
+        from circminer_b200.api import default_params
+        from hostsim_api import HostSim
+        hs = HostSim(default_params())
+        for c, seq in enumerate(w["contigs"]):
+            hs.build_contig(c, seq)
+            hs.load_annotation(c, w["flat"][c])
+        return hs
+    _single_split(tmp_path, make, lambda hs, c, w, lens, rec: hs.circ_single(c, w["contigs"][c], w["s1"], w["s2"], lens, lens, rec["mr_con"],
+                                                                             rec["gene_cnt"], rec["gene_se"]), 8000)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_gpu_equals_call_circ_single_split(tmp_path):
+    def make(w):
+        from circminer_b200 import workload
+        from circminer_b200.api import Mapper, default_params
+        m = Mapper(default_params())
+        workload.load_into(m, w)
+        return m
+    m = _single_split(tmp_path, make, lambda m, c, w, lens, rec: m.circ_single(c, w["s1"], w["s2"], lens, lens, rec["mr_con"], rec["gene_cnt"],
+                                                                               rec["gene_se"]), 20000)
+    m.close()
