@@ -1,0 +1,247 @@
+// Stage 2 of the drop-in binary: ProcessCirc::do_process (src/process_circ.cpp:195-332) with the single-split pairs of every
+// contig going through libcm_gpu.so in one batch (cm_gpu_circ_single_batch) instead of call_circ_single_split one pair at a time.
+//
+// How it is bound: integration/gpu_shim.h renames the one call `process_circ.do_process()` of circ_detect (src/circminer.cpp:349-352)
+// to cm_shim_do_process, a member this file defines; no reference source is edited.  Everything around the per-pair work is
+// the reference's own code called in do_process's order: index / GTF set-up, the sorted remain FASTQ through FASTQParser,
+// load_genome per contig, call_circ for the double-split pairs (and whatever else is not a CHIBSJ), report_events.  For a CHIBSJ
+// pair the batch returns every check_split_map attempt with its three mates and type -- the line print_split_mapping +
+// fprintf(candid_file, "%d\n", type) write -- and the CircRes call_circ_single_split pushes; they are written / pushed here
+// when the pair's turn comes, so candidates.pam and circ_report are byte-identical.
+// CM_GPU_STAGE2=0 runs the reference's do_process instead.
+#define private public
+#define protected public
+#define do_process cm_shim_do_process
+#include "common.h"
+#include "fastq_parser.h"
+#include "gene_annotation.h"
+#include "genome.h"
+#include "match_read.h"
+#include "process_circ.h"
+#include "utils.h"
+#undef do_process
+#undef private
+#undef protected
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../include/cm_gpu.h"
+
+extern "C" {
+#include "mrsfast/Common.h"
+#include "mrsfast/HashTable.h"
+}
+
+cm_gpu_ctx *cm_shim_stage2_contig(int c);       // gpu_map_reads.cpp: index + annotation of contig c on the device, the root context
+void cm_ref_do_process(ProcessCirc *p);         // ref_do_process.cpp: the reference's own do_process
+
+namespace {
+
+struct Pair {                 // one pair of the sorted remain files
+    std::string rname, seq1, seq2, rc1, rc2;
+    MatchedRead mr;
+};
+
+void die2(cm_gpu_ctx *ctx, const char *what) {
+    fprintf(stderr, "circminer_gpu: %s failed: %s\n", what, cm_gpu_last_error(ctx));
+    exit(1);
+}
+
+// the pairs of one contig: CHIBSJ ones through the batch, then everything in file order
+void process_contig(ProcessCirc &pc, std::vector<Pair> &P) {
+    const size_t n_all = P.size();
+    std::vector<size_t> who;                        // CHIBSJ pairs
+    for (size_t i = 0; i < n_all; i++)
+        if (P[i].mr.type == CHIBSJ) who.push_back(i);
+    const uint32_t n = (uint32_t) who.size();
+    std::vector<uint32_t> att_pair, att_first(n + 1, 0);
+    std::vector<cm_circ_mate> a_r1, a_r2, a_pm, a_in1;
+    std::vector<int32_t> a_ret, best(n, -1);
+    std::vector<cm_circ_res> best_cr(n);
+    if (n) {
+        cm_gpu_ctx *ctx = cm_shim_stage2_contig(contigNum);
+        uint32_t stride = 0;
+        for (size_t k : who) stride = std::max<uint32_t>(stride, (uint32_t) std::max(P[k].seq1.size(), P[k].seq2.size()));
+        stride = (stride + 15) & ~15u;
+        std::vector<char> s1((size_t) n * stride, 0), s2((size_t) n * stride, 0);
+        std::vector<uint16_t> l1(n), l2(n);
+        std::vector<cm_mread> mr(n);
+        std::vector<uint32_t> goff(n + 1, 0), gs, ge;
+        for (uint32_t k = 0; k < n; k++) {
+            const Pair &p = P[who[k]];
+            memcpy(&s1[(size_t) k * stride], p.seq1.data(), p.seq1.size());
+            memcpy(&s2[(size_t) k * stride], p.seq2.data(), p.seq2.size());
+            l1[k] = (uint16_t) p.seq1.size(); l2[k] = (uint16_t) p.seq2.size();
+            MatchedRead m = p.mr;
+            gtf_parser.chrloc2conloc(m.chr_r1, m.spos_r1, m.epos_r1);      // call_circ_single_split :372-373
+            gtf_parser.chrloc2conloc(m.chr_r2, m.spos_r2, m.epos_r2);
+            cm_mread &o = mr[k];
+            memset(&o, 0, sizeof(o));
+            o.spos_r1 = m.spos_r1; o.epos_r1 = m.epos_r1; o.spos_r2 = m.spos_r2; o.epos_r2 = m.epos_r2;
+            o.qspos_r1 = m.qspos_r1; o.qepos_r1 = m.qepos_r1; o.qspos_r2 = m.qspos_r2; o.qepos_r2 = m.qepos_r2;
+            o.mlen_r1 = m.mlen_r1; o.mlen_r2 = m.mlen_r2; o.ed_r1 = m.ed_r1; o.ed_r2 = m.ed_r2;
+            o.type = m.type; o.tlen = m.tlen; o.contig_num = m.contig_num;
+            o.r1_forward = m.r1_forward; o.r2_forward = m.r2_forward;
+            const IntervalInfo<GeneInfo> *gi = gtf_parser.get_gene_overlap(m.spos_r1, false);   // :404
+            if (gi)
+                for (const GeneInfo &g : gi->seg_list) { gs.push_back(g.start); ge.push_back(g.end); }
+            goff[k + 1] = (uint32_t) gs.size();
+        }
+        if (gs.empty()) { gs.push_back(0); ge.push_back(0); }
+        uint32_t n_att = 0;
+        uint32_t cap = 4 * n + 1024;
+        for (int pass = 0; pass < 2; pass++) {      // a second pass only when more attempts came back than the first guess holds
+            att_pair.assign(cap, 0); a_r1.resize(cap); a_r2.resize(cap); a_pm.resize(cap); a_in1.resize(cap); a_ret.assign(cap, 0);
+            if (cm_gpu_circ_single_batch(ctx, contigNum, n, s1.data(), s2.data(), stride, l1.data(), l2.data(), mr.data(), goff.data(), gs.data(),
+                                         ge.data(), pc.window_size, pc.step, cap, &n_att, att_pair.data(), nullptr, a_in1.data(), nullptr, nullptr,
+                                         a_ret.data(), nullptr, a_r1.data(), a_r2.data(), a_pm.data(), best.data(), best_cr.data()) != CM_OK)
+                die2(ctx, "cm_gpu_circ_single_batch");
+            if (n_att <= cap) break;
+            cap = n_att;
+        }
+        // attempts are in (pair, gene, chain) order: first attempt of every pair
+        uint32_t a = 0;
+        for (uint32_t k = 0; k < n; k++) {
+            att_first[k] = a;
+            while (a < n_att && att_pair[a] == k) a++;
+        }
+        att_first[n] = a;
+        if (getenv("CM_GPU_VERBOSE"))
+            fprintf(stderr, "circminer_gpu: stage 2, contig %d: %u single-split pairs of %zu in one batch, %u check_split_map attempts\n", contigNum, n,
+                    n_all, n_att);
+    }
+    // file order
+    Record r1, r2;
+    r1.init();
+    r2.init();
+    uint32_t k = 0;
+    for (size_t i = 0; i < n_all; i++) {
+        Pair &p = P[i];
+        if (p.mr.type == CHIBSJ) {
+            for (uint32_t t = att_first[k]; t < att_first[k + 1]; t++) {
+                // print_split_mapping (:1685-1696) + the type; con_shift = get_shift(contigNum, mm_r1.spos) as it was before the call
+                ConShift cs = gtf_parser.get_shift(contigNum, a_in1[t].m.spos);
+                const cm_mate &pm = a_pm[t].m, &m1 = a_r1[t].m, &m2 = a_r2[t].m;
+                fprintf(pc.candid_file, "%s\t%s\t%u\t%u\t%d\t%d\t%d\t%u\t%u\t%d\t%d\t%d\t%u\t%u\t%d\t%d\t%d\t", p.rname.c_str(), cs.contig.c_str(),
+                        pm.spos - cs.shift, pm.epos - cs.shift, pm.qspos, pm.matched_len, pm.dir, m1.spos - cs.shift, m1.epos - cs.shift, m1.qspos,
+                        m1.matched_len, m1.dir, m2.spos - cs.shift, m2.epos - cs.shift, m2.qspos, m2.matched_len, m2.dir);
+                fprintf(pc.candid_file, "%d\n", a_ret[t]);
+            }
+            if (best[k] >= CR && best[k] <= MCR) {
+                // the attempt that set best_cr: the last one whose type equals the final best (types only improve)
+                uint32_t t_best = att_first[k];
+                for (uint32_t t = att_first[k]; t < att_first[k + 1]; t++)
+                    if (a_ret[t] == best[k]) { t_best = t; break; }
+                ConShift cs = gtf_parser.get_shift(contigNum, a_in1[t_best].m.spos);
+                const cm_circ_res &c = best_cr[k];
+                CircRes cr;
+                cr.chr = cs.contig;
+                cr.rname = p.rname;
+                cr.spos = c.spos - cs.shift;
+                cr.epos = c.epos - cs.shift;
+                cr.type = best[k];
+                cr.start_signal = std::string((const char *) c.start_signal, c.start_signal_n);
+                cr.end_signal = std::string((const char *) c.end_signal, c.end_signal_n);
+                cr.start_bp_ref = std::string((const char *) c.start_bp_ref, c.ref_n);
+                cr.end_bp_ref = std::string((const char *) c.end_bp_ref, c.ref_n);
+                pc.circ_res.push_back(cr);
+            }
+            k++;
+        } else {
+            strcpy(r1.rname, p.rname.c_str()); strcpy(r2.rname, p.rname.c_str());
+            strcpy(r1.seq, p.seq1.c_str()); strcpy(r1.rcseq, p.rc1.c_str());
+            strcpy(r2.seq, p.seq2.c_str()); strcpy(r2.rcseq, p.rc2.c_str());
+            r1.seq_len = (uint32_t) p.seq1.size(); r2.seq_len = (uint32_t) p.seq2.size();
+            *r1.mr = p.mr;
+            *r2.mr = p.mr;
+            pc.call_circ(&r1, &r2);
+        }
+    }
+    r1.finalize();
+    r2.finalize();
+}
+
+}  // namespace
+
+void ProcessCirc::cm_shim_do_process(void) {
+    const char *sw = getenv("CM_GPU_STAGE2");
+    if ((sw && !strcmp(sw, "0")) || !pairedEnd) {
+        cm_ref_do_process(this);
+        return;
+    }
+    // ---- set-up, as do_process :200-262 -----------------------------------------------------------------------------------
+    double cputime_start = get_cpu_time(), realtime_start = get_real_time();
+    std::vector<ContigLen> orig_contig_len;
+    genome_packer.load_index_info(orig_contig_len);
+    char index_file[FILE_NAME_MAX_LEN];
+    strcpy(index_file, genome_packer.get_index_fname().c_str());
+    initCommon();
+    THREAD_COUNT = threadCount;
+    for (int i = 0; i < 255; i++) THREAD_ID[i] = i;
+    if (!checkHashTable(index_file)) return;
+    if (!initLoadingCompressedGenomeMeta(index_file)) return;
+    kmer = WINDOW_SIZE + checkSumLength;
+    genome_seeder.init(LOADCONTIGSTRINMEM);
+    if (stage == 1) {
+        Logger::instance().info("Loading GTF file...\n");
+        gtf_parser.init(gtfFilename, orig_contig_len);
+        if (!gtf_parser.load_gtf()) {
+            fprintf(stdout, "Error in reading GTF file.\n");
+            exit(1);
+        }
+        const double c = get_cpu_time(), r = get_real_time();
+        Logger::instance().info("Completed! (CPU time: %.2lfs; Real time: %.2lfs)\n", c - cputime_start, r - realtime_start);
+        cputime_start = c;
+        realtime_start = r;
+    }
+    const double fq_cputime_start = cputime_start, fq_realtime_start = realtime_start;
+    // ---- the sorted remain files, contig by contig --------------------------------------------------------------------------
+    FASTQParser fq_parser1, fq_parser2;
+    fq_parser1.init();
+    fq_parser1.reset(fq_file1);
+    fq_parser2.init();
+    fq_parser2.reset(fq_file2);
+    open_candid_file();
+    std::vector<Pair> group;
+    int group_contig = -1;
+    auto flush = [&]() {
+        if (group.empty()) return;
+        while (pre_contig != group_contig) {      // :315-318
+            load_genome();
+            refresh_hash_table_list();
+        }
+        process_contig(*this, group);
+        group.clear();
+    };
+    while (true) {
+        Record *c1 = fq_parser1.get_next_read(0);
+        if (c1 == NULL) break;
+        Record *c2 = fq_parser2.get_next_read(0);
+        if ((int) c1->mr->contig_num != group_contig) {
+            flush();
+            group_contig = c1->mr->contig_num;
+        }
+        group.emplace_back();
+        Pair &p = group.back();
+        p.rname = c1->rname;
+        p.seq1.assign(c1->seq, c1->seq_len);
+        p.rc1.assign(c1->rcseq, c1->seq_len);
+        if (c2) {
+            p.seq2.assign(c2->seq, c2->seq_len);
+            p.rc2.assign(c2->rcseq, c2->seq_len);
+        }
+        p.mr = *c1->mr;
+    }
+    flush();
+    refresh_hash_table_list();
+    report_events();
+    Logger::instance().info.set_prefix("[INFO] ");
+    Logger::instance().info("CircRNA detection Completed! (CPU time: %.2lfs; Real time: %.2lfs)\n", get_cpu_time() - fq_cputime_start,
+                            get_real_time() - fq_realtime_start);
+    finalizeLoadingCompressedGenome();
+    genome_seeder.finalize();
+}

@@ -26,6 +26,7 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <set>
 #include <vector>
 
 #include "../include/cm_gpu.h"
@@ -44,6 +45,7 @@ extern pthread_mutex_t buffer_lock;
 namespace {
 
 cm_gpu_ctx *g_ctx = nullptr;            // first root context (serial / SAM path, error text)
+std::set<int> g_resident;               // contigs built on the devices so far
 std::vector<cm_gpu_ctx *> g_roots;      // one per device in use: owns that GPU's resident contigs and annotation
 std::vector<cm_gpu_ctx *> g_workers;    // contexts batches are dealt to: every root plus its shared contexts
 cm_params g_params;
@@ -324,6 +326,7 @@ void ensure_round(int c) {
     const double t_idx = now_s();
     upload_annotation(c);
     g_loaded_contig = c;
+    g_resident.insert(c);
     if (g_workers.empty()) {
         // CM_GPU_CTX_PER_DEVICE (default 2): contexts per device; the extra ones share their root's index and let one batch's
         // copies run beside another batch's kernels
@@ -668,6 +671,13 @@ void *gpu_map_reads(void *args) {
 void *idle(void *) { return NULL; }
 
 }   // namespace
+
+// stage 2 (gpu_circ_detect.cpp): contig c with its annotation on the first device; the contigs of the mapping rounds are still
+// resident there and are not rebuilt (shared contexts hold them)
+cm_gpu_ctx *cm_shim_stage2_contig(int c) {
+    if (!g_resident.count(c)) ensure_round(c);
+    return g_roots[0];
+}
 
 int cm_shim_pthread_create(pthread_t *t, const pthread_attr_t *a, void *(*)(void *), void *arg) {
     FilterArgs *fa = (FilterArgs *) arg;

@@ -261,7 +261,11 @@ def main():
             mr1, _ = h.process_pe(s1, s2, lens, lens, fresh_mreads(n, a.max_ed))
             rec = h.circ_single(s1, s2, lens, lens, mr1)
             out[f"c{c}_circs_mr_chr"] = mr1
-            for k, v in h.circ_single_real(s1, s2, lens, lens, mr1).items():   # the unmodified call_circ on the same pairs
+            import time
+            t0 = time.time()
+            real = h.circ_single_real(s1, s2, lens, lens, mr1)   # the unmodified call_circ on the same pairs
+            out[f"c{c}_circreal_seconds"] = time.time() - t0
+            for k, v in real.items():
                 out[f"c{c}_circreal_{k}"] = v
             for k, v in rec.items():
                 out[f"c{c}_circs_{k}"] = v

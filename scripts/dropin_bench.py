@@ -35,7 +35,10 @@ def run(binary, d, fq1, fq2, out, threads, env=None, extra=()):
         raise SystemExit(f"{binary} failed:\n{txt[-2000:]}")
     rounds = [float(x) for x in re.findall(r"Completed round \S+ \(CPU time: [\d.]+s; Real time: ([\d.]+)s\)", txt)]
     phases = [ln for ln in txt.splitlines() if ln.startswith(("circminer_gpu:", "cm_gpu:"))]
-    return {"wall_s": wall, "round_s": rounds, "mapping_s": sum(rounds), "phases": phases}
+    circ = re.search(r"CircRNA detection Completed! \(CPU time: [\d.]+s; Real time: ([\d.]+)s\)", txt)   # do_process (src/process_circ.cpp:325)
+    sort = re.findall(r"Sorting remaining read mappings.*?\n.*?Completed! \(CPU time: [\d.]+s; Real time: ([\d.]+)s\)", txt, re.S)
+    return {"wall_s": wall, "round_s": rounds, "mapping_s": sum(rounds), "phases": phases,
+            "stage2_do_process_s": float(circ.group(1)) if circ else None, "stage2_sort_s": float(sort[0]) if sort else None}
 
 
 def digest(path, sort_lines=False):

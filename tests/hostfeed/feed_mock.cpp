@@ -45,6 +45,11 @@ int cm_gpu_load_annotation(cm_gpu_ctx *, int, const cm_annot_flat *) { return CM
 int cm_annot_file_write(const char *, const cm_annot_flat *, uint32_t, uint64_t) { return CM_ERR_ARG; }
 int cm_annot_file_read(const char *, cm_annot_flat *, uint32_t *, uint64_t *, void **) { return CM_ERR_ARG; }
 void cm_annot_file_free(void *) {}
+// stage 2 has no stand-in here: the host-feed tests run the binary with CM_GPU_STAGE2=0 (the reference's own do_process)
+int cm_gpu_circ_single_batch(cm_gpu_ctx *, int, uint32_t, const char *, const char *, uint32_t, const uint16_t *, const uint16_t *, const cm_mread *,
+                             const uint32_t *, const uint32_t *, const uint32_t *, int, int, uint32_t, uint32_t *, uint32_t *, uint8_t *, cm_circ_mate *,
+                             cm_circ_mate *, cm_circ_mate *, int32_t *, cm_circ_res *, cm_circ_mate *, cm_circ_mate *, cm_circ_mate *, int32_t *,
+                             cm_circ_res *) { return CM_ERR_STATE; }
 int cm_gpu_host_alloc(size_t bytes, void **out) { *out = malloc(bytes ? bytes : 1); return *out ? CM_OK : CM_ERR_ALLOC; }
 int cm_gpu_host_free(void *p) { free(p); return CM_OK; }
 

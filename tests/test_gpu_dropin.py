@@ -52,7 +52,12 @@ def test_dropin_binary_outputs_are_byte_identical(tmp_path, scan, devices):
     assert len({ln.split()[0] for ln in info if ln.strip()}) >= 2, "expected at least two packed contigs"
     ref_out, gpu_out = str(tmp_path / "ref"), str(tmp_path / "gpu")
     _run(REF, w, ref_out, extra=("-a", scan))
-    _run(GPU, w, gpu_out, env={"CM_GPU_BATCH": "4096" if devices == "0" else "1500", "CM_GPU_DEVICES": devices}, extra=("-a", scan))
+    pg = _run(GPU, w, gpu_out, env={"CM_GPU_BATCH": "4096" if devices == "0" else "1500", "CM_GPU_DEVICES": devices, "CM_GPU_VERBOSE": "1"},
+              extra=("-a", scan))
+    # stage 2's single-split pairs went through the device (integration/gpu_circ_detect.cpp), not through the reference's loop
+    import re
+    st2 = [(int(a), int(b)) for a, b in re.findall(r"stage 2, contig \d+: (\d+) single-split pairs of \d+ in one batch, (\d+) check_split_map", pg.stderr)]
+    assert st2 and sum(a for a, _ in st2) > 50 and sum(b for _, b in st2) > 20, pg.stderr[-1500:]
     ref_files = sorted(os.path.basename(f)[3:] for f in glob.glob(ref_out + "*") if os.path.isfile(f))
     gpu_files = sorted(os.path.basename(f)[3:] for f in glob.glob(gpu_out + "*") if os.path.isfile(f))
     assert ref_files == gpu_files and any(f.endswith("circ_report") for f in ref_files), (ref_files, gpu_files)

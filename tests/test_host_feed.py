@@ -48,7 +48,7 @@ def test_host_feed_outputs_are_byte_identical(dataset, tmp_path, scan, threads, 
     w = dataset
     ref_out, feed_out = str(tmp_path / "ref"), str(tmp_path / "feed")
     _run(REF, w, ref_out, 1, extra=("-a", scan))
-    _run(FEED, w, feed_out, threads, env={"CM_GPU_BATCH": str(batch), "CM_GPU_DEVICES": devices, "CM_GPU_CTX_PER_DEVICE": str(per)},
+    _run(FEED, w, feed_out, threads, env={"CM_GPU_BATCH": str(batch), "CM_GPU_DEVICES": devices, "CM_GPU_CTX_PER_DEVICE": str(per), "CM_GPU_STAGE2": "0"},
          extra=("-a", scan))
     ref_files = sorted(os.path.basename(f)[3:] for f in glob.glob(ref_out + "*") if os.path.isfile(f))
     feed_files = sorted(os.path.basename(f)[4:] for f in glob.glob(feed_out + "*") if os.path.isfile(f))
