@@ -576,7 +576,7 @@ extern "C" int cm_gpu_circ_single_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t
         if (len1[i] > stride || len2[i] > stride || gene_off[i + 1] < gene_off[i]) return fail(ctx, CM_ERR_ARG, "pair %u: read longer than the row or gene list out of order", i);
     const CircEngine E{ctx, contig_id, gpu_eng_chain, gpu_eng_exact, gpu_eng_check};
     const CircSingleIn in{n, seqs1, seqs2, stride, len1, len2, mr, gene_off, gene_start, gene_end, window_size, step, ctx->p.max_read_len,
-                          ctx->p.max_chain_len};
+                          ctx->p.max_chain_len, 4};
     std::vector<CircAttempt> att;
     const int r = circ_orch_single(E, in, att, best_type, best_cr);
     if (r == -100) return fail(ctx, CM_ERR_STATE, "a fixed-size list of the stage-2 classification overflowed (CM_CIRC_TID_CAP / CM_CIRC_JUNC_CAP)");
@@ -593,6 +593,164 @@ extern "C" int cm_gpu_circ_single_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t
         if (att_out_r1) att_out_r1[k] = att[k].out_r1;
         if (att_out_r2) att_out_r2[k] = att[k].out_r2;
         if (att_out_pm) att_out_pm[k] = att[k].out_pm;
+    }
+    return CM_OK;
+}
+
+// ---- call_circ_double_split for a batch (circ_orch_double) -------------------------------------------------------------------
+struct CircDoubleIn {
+    uint32_t n;
+    const uint8_t *r1seq, *r2seq;
+    uint32_t stride;
+    const uint32_t *qs1, *qe1, *qs2, *qe2, *clen1, *clen2;
+    int F;
+    const FragDev *fr1, *fr2;
+};
+__global__ void __launch_bounds__(128) k_circ_double(const __grid_constant__ DevView v, const __grid_constant__ CircDoubleIn in, cm_circ_mate *r1,
+                                                     cm_circ_mate *r2, cm_circ_mate *p1, cm_circ_mate *p2, int32_t *code) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= in.n) return;
+    ChainView c1, c2;
+    c1.frags = in.fr1 + (size_t) i * in.F; c1.chain_len = in.clen1[i]; c1.aux = nullptr; c1.spec = nullptr;
+    c2.frags = in.fr2 + (size_t) i * in.F; c2.chain_len = in.clen2[i]; c2.aux = nullptr; c2.spec = nullptr;
+    code[i] = cm_circ_double_row(v, r1[i], r2[i], in.qs1[i], in.qe1[i], in.qs2[i], in.qe2[i], in.r1seq + (size_t) i * in.stride,
+                                 in.r2seq + (size_t) i * in.stride, c1, c2, p1[i], p2[i]);
+}
+__global__ void __launch_bounds__(64) k_circ_check4(const __grid_constant__ DevView v, uint32_t n, const uint8_t *__restrict__ r1seq,
+                                                    const uint8_t *__restrict__ r2seq, uint32_t stride, const int32_t *__restrict__ l1,
+                                                    const int32_t *__restrict__ l2, const cm_circ_mate *__restrict__ m, int32_t *__restrict__ ret,
+                                                    cm_circ_res *cr) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    ret[i] = cm_circ_check4_row(v, r1seq + (size_t) i * stride, l1[i], r2seq + (size_t) i * stride, l2[i], nullptr, 0, m[i], m[n + i], m[2 * (size_t) n + i],
+                                m[3 * (size_t) n + i], cr[i]);
+}
+
+#define CIRC_TRY(x) do { if ((r = (x)) != CM_OK) { cleanup(); return r; } } while (0)
+#define CIRC_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return fail(ctx, CM_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e_)); } } while (0)
+static int gpu_eng_dbl(void *self, int contig, uint32_t n, const char *r1seq, const char *r2seq, uint32_t stride, cm_circ_mate *r1, cm_circ_mate *r2,
+                       const uint32_t *qs1, const uint32_t *qe1, const uint32_t *qs2, const uint32_t *qe2, uint32_t F, const uint32_t *clen1,
+                       const uint32_t *rpos1, const int32_t *qpos1, const uint32_t *clen2, const uint32_t *rpos2, const int32_t *qpos2, int ws,
+                       cm_circ_mate *p1, cm_circ_mate *p2, int32_t *code) {
+    cm_gpu_ctx *ctx = (cm_gpu_ctx *) self;
+    cudaSetDevice(ctx->device);
+    DevView v;
+    int r = make_view(ctx, contig, true, v);
+    if (r != CM_OK) return r;
+    v.p.kmer = ws;
+    cudaStream_t st = ctx->stream;
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *q : tmp) cudaFree(q); };
+    uint8_t *d_s1 = nullptr, *d_s2 = nullptr;
+    uint32_t *d_u = nullptr;
+    FragDev *d_f = nullptr;
+    cm_circ_mate *d_m = nullptr;
+    int32_t *d_code = nullptr;
+    const size_t bytes = (size_t) n * stride;
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_s1, bytes + 64));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_s2, bytes + 64));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_u, 6 * (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_f, 2 * (size_t) n * F));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_m, 4 * (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_code, (size_t) n));
+    std::vector<FragDev> hf(2 * (size_t) n * F);
+    for (size_t q = 0; q < (size_t) n * F; q++) {
+        hf[q].rpos = rpos1[q]; hf[q].qpos = qpos1[q];
+        hf[(size_t) n * F + q].rpos = rpos2[q]; hf[(size_t) n * F + q].qpos = qpos2[q];
+    }
+    const void *srcs[6] = {qs1, qe1, qs2, qe2, clen1, clen2};
+    CIRC_CUDA(cudaMemcpyAsync(d_s1, r1seq, bytes, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_s2, r2seq, bytes, cudaMemcpyHostToDevice, st));
+    for (int k = 0; k < 6; k++) CIRC_CUDA(cudaMemcpyAsync(d_u + (size_t) k * n, srcs[k], (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_f, hf.data(), hf.size() * sizeof(FragDev), cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_m, r1, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_m + n, r2, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
+    CircDoubleIn in{n, d_s1, d_s2, stride, d_u, d_u + n, d_u + 2 * (size_t) n, d_u + 3 * (size_t) n, d_u + 4 * (size_t) n, d_u + 5 * (size_t) n, (int) F,
+                    d_f, d_f + (size_t) n * F};
+    k_circ_double<<<grid_for(n, 128), 128, 0, st>>>(v, in, d_m, d_m + n, d_m + 2 * (size_t) n, d_m + 3 * (size_t) n, d_code);
+    ctx->launches++;
+    CIRC_CUDA(cudaGetLastError());
+    CIRC_CUDA(cudaMemcpyAsync(r1, d_m, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(r2, d_m + n, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(p1, d_m + 2 * (size_t) n, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(p2, d_m + 3 * (size_t) n, (size_t) n * sizeof(cm_circ_mate), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(code, d_code, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaStreamSynchronize(st));
+    cleanup();
+    return CM_OK;
+}
+static int gpu_eng_check4(void *self, int contig, uint32_t n, const char *r1seq, const char *r2seq, uint32_t stride, const int32_t *l1, const int32_t *l2,
+                          const cm_circ_mate *r1, const cm_circ_mate *r2, const cm_circ_mate *p1, const cm_circ_mate *p2, int ws, int32_t *ret,
+                          cm_circ_res *cr) {
+    cm_gpu_ctx *ctx = (cm_gpu_ctx *) self;
+    cudaSetDevice(ctx->device);
+    DevView v;
+    int r = make_view(ctx, contig, true, v);
+    if (r != CM_OK) return r;
+    v.p.kmer = ws;
+    cudaStream_t st = ctx->stream;
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *q : tmp) cudaFree(q); };
+    uint8_t *d_s1 = nullptr, *d_s2 = nullptr;
+    int32_t *d_l = nullptr, *d_ret = nullptr;
+    cm_circ_mate *d_m = nullptr;
+    cm_circ_res *d_cr = nullptr;
+    const size_t bytes = (size_t) n * stride;
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_s1, bytes + 64));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_s2, bytes + 64));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_l, 2 * (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_ret, (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_m, 4 * (size_t) n));
+    CIRC_TRY(dev_alloc(ctx, tmp, &d_cr, (size_t) n));
+    CIRC_CUDA(cudaMemcpyAsync(d_s1, r1seq, bytes, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_s2, r2seq, bytes, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_l, l1, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    CIRC_CUDA(cudaMemcpyAsync(d_l + n, l2, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    const cm_circ_mate *src[4] = {r1, r2, p1, p2};
+    for (int k = 0; k < 4; k++) CIRC_CUDA(cudaMemcpyAsync(d_m + (size_t) k * n, src[k], (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
+    k_circ_check4<<<grid_for(n, 64), 64, 0, st>>>(v, n, d_s1, d_s2, stride, d_l, d_l + n, d_m, d_ret, d_cr);
+    ctx->launches++;
+    CIRC_CUDA(cudaGetLastError());
+    CIRC_CUDA(cudaMemcpyAsync(ret, d_ret, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaMemcpyAsync(cr, d_cr, (size_t) n * sizeof(cm_circ_res), cudaMemcpyDeviceToHost, st));
+    CIRC_CUDA(cudaStreamSynchronize(st));
+    cleanup();
+    return CM_OK;
+}
+#undef CIRC_TRY
+#undef CIRC_CUDA
+
+extern "C" int cm_gpu_circ_double_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
+                                        const uint16_t *len1, const uint16_t *len2, const cm_mread *mr, const uint32_t *gene_off,
+                                        const uint32_t *gene_start, const uint32_t *gene_end, int window_size, int step, uint32_t event_cap,
+                                        uint32_t *n_events, uint32_t *ev_pair, uint8_t *ev_kind, cm_circ_mate *ev_r1, cm_circ_mate *ev_r2,
+                                        cm_circ_mate *ev_p1, cm_circ_mate *ev_p2, int32_t *ev_ret, cm_circ_res *ev_cr, int32_t *push_type,
+                                        cm_circ_res *push_cr) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n_events) *n_events = 0;
+    if (n == 0) return CM_OK;
+    if (!seqs1 || !seqs2 || !len1 || !len2 || !mr || !gene_off || !gene_start || !gene_end || !n_events || !push_type)
+        return fail(ctx, CM_ERR_ARG, "null argument");
+    if (step < 1 || window_size < 4 || window_size > 12) return fail(ctx, CM_ERR_ARG, "window size outside 4..12 or step < 1");
+    for (uint32_t i = 0; i < n; i++)
+        if (len1[i] > stride || len2[i] > stride || gene_off[i + 1] < gene_off[i]) return fail(ctx, CM_ERR_ARG, "pair %u: read longer than the row or gene list out of order", i);
+    const CircEngine E{ctx, contig_id, gpu_eng_chain, gpu_eng_exact, gpu_eng_check, gpu_eng_dbl, gpu_eng_check4};
+    const CircSingleIn in{n, seqs1, seqs2, stride, len1, len2, mr, gene_off, gene_start, gene_end, window_size, step, ctx->p.max_read_len,
+                          ctx->p.max_chain_len, 4};
+    std::vector<CircEvent> ev;
+    const int r = circ_orch_double(E, in, ev, push_type, push_cr);
+    if (r == -100) return fail(ctx, CM_ERR_STATE, "a fixed-size list of the stage-2 classification overflowed (CM_CIRC_TID_CAP / CM_CIRC_JUNC_CAP)");
+    if (r != 0) return r;
+    *n_events = (uint32_t) ev.size();
+    for (size_t k = 0; k < ev.size() && k < event_cap; k++) {
+        if (ev_pair) ev_pair[k] = ev[k].pair;
+        if (ev_kind) ev_kind[k] = ev[k].kind;
+        if (ev_r1) ev_r1[k] = ev[k].r1;
+        if (ev_r2) ev_r2[k] = ev[k].r2;
+        if (ev_p1) ev_p1[k] = ev[k].p1;
+        if (ev_p2) ev_p2[k] = ev[k].p2;
+        if (ev_ret) ev_ret[k] = ev[k].ret;
+        if (ev_cr) ev_cr[k] = ev[k].cr;
     }
     return CM_OK;
 }

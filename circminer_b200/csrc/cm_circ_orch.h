@@ -32,6 +32,15 @@ struct CircEngine {
     int (*check)(void *self, int contig, uint32_t n, const char *remain, const char *fullmap, uint32_t stride, const int32_t *rlen,
                  const int32_t *flen, const uint8_t *r1_partial, cm_circ_mate *r1, cm_circ_mate *r2, cm_circ_mate *pm, int ws, int32_t *ret,
                  cm_circ_res *cr, uint8_t *remain_is_fullmap);
+    // the double-split path (may be null for callers of circ_orch_single only): one (chain of R1's part, chain of R2's part) per row,
+    // and the four-mate check_split_map
+    int (*dbl)(void *self, int contig, uint32_t n, const char *r1seq, const char *r2seq, uint32_t stride, cm_circ_mate *r1, cm_circ_mate *r2,
+               const uint32_t *qs1, const uint32_t *qe1, const uint32_t *qs2, const uint32_t *qe2, uint32_t F, const uint32_t *clen1,
+               const uint32_t *rpos1, const int32_t *qpos1, const uint32_t *clen2, const uint32_t *rpos2, const int32_t *qpos2, int ws,
+               cm_circ_mate *p1, cm_circ_mate *p2, int32_t *code);
+    int (*check4)(void *self, int contig, uint32_t n, const char *r1seq, const char *r2seq, uint32_t stride, const int32_t *l1, const int32_t *l2,
+                  const cm_circ_mate *r1, const cm_circ_mate *r2, const cm_circ_mate *p1, const cm_circ_mate *p2, int ws, int32_t *ret,
+                  cm_circ_res *cr);
 };
 
 // MatchedMate(const MatchedRead &, r1_2, rlen, partial) (src/common.cpp:192-235); the three flags it leaves unset are 0
@@ -78,6 +87,8 @@ struct CircSingleIn {
     const uint32_t *gene_off;      // [n + 1]: genes of gtf_parser.get_gene_overlap(mm_r1.spos, false)->seg_list, in that order
     const uint32_t *gene_start, *gene_end;
     int ws, step, max_read_len, max_chain_len;   // max_chain_len: rows of the engine's chain lists (cm_params::max_chain_len)
+    int also_type;                 // a second MatchedRead type to take besides CHIBSJ (call_circ_double_split calls
+                                   // call_circ_single_split on CHI2BSJ pairs); -1: none
 };
 
 struct CircAttempt {               // one check_split_map call
@@ -113,7 +124,7 @@ static inline int circ_orch_single(const CircEngine &E, const CircSingleIn &in, 
         best_type[i] = -1;
         if (best_cr) memset(&best_cr[i], 0, sizeof(cm_circ_res));
         const cm_mread &mr = in.mr[i];
-        if (mr.type != CM_CIRC_T_CHIBSJ) continue;
+        if (mr.type != CM_CIRC_T_CHIBSJ && mr.type != in.also_type) continue;
         const int l1 = in.len1[i], l2 = in.len2[i];
         p.r1_partial = mr.mlen_r1 < mr.mlen_r2;
         const char *s1 = in.seqs1 + (size_t) i * stride, *s2 = in.seqs2 + (size_t) i * stride;
@@ -251,5 +262,182 @@ static inline int circ_orch_single(const CircEngine &E, const CircSingleIn &in, 
     });
     for (uint32_t k : order) sorted.push_back(attempts[k]);
     attempts.swap(sorted);
+    return 0;
+}
+
+// ---- call_circ_double_split (src/process_circ.cpp:485-645) for a batch ---------------------------------------------------------
+// Unlike the single-split loop, the attempts of one pair do not feed each other (the four-mate check_split_map works on copies),
+// so every (gene, chain of R1's part, chain of R2's part) is evaluated in one batch and the function's rules -- where it calls
+// call_circ_single_split on the same pair, where it stops -- are applied afterwards in its order.
+struct CircEvent {
+    uint32_t pair;
+    uint8_t kind;                  // 0: call_circ_single_split(record1, record2) is called here; 1: a four-mate check_split_map call
+    cm_circ_mate r1, r2, p1, p2;   // kind 1: mm_r1, mm_r2, r1_partial_mm, r2_partial_mm as print_split_mapping prints them
+    int32_t ret;
+    cm_circ_res cr;
+};
+
+// events: per pair in order.  push_type[i]: CR / NCR / MCR when the function pushes its own best_cr (push_cr[i], push_spos_of_r1[i] =
+// mm_r1.spos for get_shift), else -1.  Pairs that are not CHI2BSJ get no events.
+static inline int circ_orch_double(const CircEngine &E, const CircSingleIn &in, std::vector<CircEvent> &events, int32_t *push_type,
+                                   cm_circ_res *push_cr) {
+    const uint32_t n = in.n, stride = in.stride;
+    const int ws = in.ws, F = (in.max_read_len - ws) / in.step + 1;
+    const size_t CH = (size_t) in.max_chain_len;
+    events.clear();
+    struct Pair {
+        bool cand, early_single;
+        uint32_t qs1, qe1, qs2, qe2, first_prob, ng;
+        int rl1, rl2, l1, l2;
+        cm_circ_mate r1, r2;
+    };
+    std::vector<Pair> P(n);
+    std::vector<char> o1((size_t) n * stride, 0), o2((size_t) n * stride, 0);   // the two reads as mapped (r?_remain_seq)
+    // chaining problems: (pair, gene, mate)
+    std::vector<uint32_t> pr_pair, pr_gene, pr_mate;
+    for (uint32_t i = 0; i < n; i++) {
+        Pair &p = P[i];
+        p.cand = false;
+        push_type[i] = -1;
+        if (push_cr) memset(&push_cr[i], 0, sizeof(cm_circ_res));
+        const cm_mread &mr = in.mr[i];
+        if (mr.type != 4) continue;   // CHI2BSJ
+        p.l1 = in.len1[i]; p.l2 = in.len2[i];
+        const char *s1 = in.seqs1 + (size_t) i * stride, *s2 = in.seqs2 + (size_t) i * stride;
+        if (mr.r1_forward) memcpy(&o1[(size_t) i * stride], s1, p.l1); else circ_orch_revcomp(s1, p.l1, &o1[(size_t) i * stride]);
+        if (mr.r2_forward) memcpy(&o2[(size_t) i * stride], s2, p.l2); else circ_orch_revcomp(s2, p.l2, &o2[(size_t) i * stride]);
+        const bool rs1 = (mr.qspos_r1 - 1) > ((uint32_t) p.l1 - mr.qepos_r1), rs2 = (mr.qspos_r2 - 1) > ((uint32_t) p.l2 - mr.qepos_r2);
+        p.qs1 = rs1 ? 1 : mr.qepos_r1 + 1; p.qe1 = rs1 ? mr.qspos_r1 - 1 : (uint32_t) p.l1;
+        p.qs2 = rs2 ? 1 : mr.qepos_r2 + 1; p.qe2 = rs2 ? mr.qspos_r2 - 1 : (uint32_t) p.l2;
+        p.rl1 = (int) (p.qe1 - p.qs1 + 1); p.rl2 = (int) (p.qe2 - p.qs2 + 1);
+        if (p.rl1 < ws && p.rl2 < ws) continue;                    // fully mapped: return
+        p.early_single = p.rl1 < ws || p.rl2 < ws;                 // single split first -- and the function goes on
+        p.cand = true;
+        circ_orch_mate(mr, 1, p.l1, true, p.r1);
+        circ_orch_mate(mr, 2, p.l2, true, p.r2);
+        p.ng = in.gene_off[i + 1] - in.gene_off[i];
+        p.first_prob = (uint32_t) pr_pair.size();
+        for (uint32_t g = 0; g < p.ng; g++)
+            for (uint32_t mt = 0; mt < 2; mt++) { pr_pair.push_back(i); pr_gene.push_back(g); pr_mate.push_back(mt); }
+    }
+    const uint32_t np = (uint32_t) pr_pair.size();
+    std::vector<int32_t> count(np, 0);
+    std::vector<uint32_t> clen(np * CH), rpos(np * CH * (size_t) F);
+    std::vector<int32_t> qpos(np * CH * (size_t) F);
+    if (np) {
+        std::vector<char> cs((size_t) np * stride);
+        std::vector<uint32_t> qs(np), qe(np), gs(np), ge(np);
+        std::vector<float> score(np * CH);
+        for (uint32_t k = 0; k < np; k++) {
+            const uint32_t i = pr_pair[k];
+            const Pair &p = P[i];
+            memcpy(&cs[(size_t) k * stride], pr_mate[k] ? &o2[(size_t) i * stride] : &o1[(size_t) i * stride], stride);
+            qs[k] = pr_mate[k] ? p.qs2 : p.qs1; qe[k] = pr_mate[k] ? p.qe2 : p.qe1;
+            gs[k] = in.gene_start[in.gene_off[i] + pr_gene[k]]; ge[k] = in.gene_end[in.gene_off[i] + pr_gene[k]];
+            if (qe[k] < qs[k]) { qs[k] = 1; qe[k] = 0; }            // nothing left of this mate: chaining gives no chain
+        }
+        int r = E.chain(E.self, E.contig, np, cs.data(), stride, qs.data(), qe.data(), gs.data(), ge.data(), ws, in.step, F, count.data(), score.data(),
+                        clen.data(), rpos.data(), qpos.data());
+        if (r != 0) return r;
+    }
+    // all chain pairs of the genes where both parts have chains
+    struct Combo { uint32_t pair, gene, j, k, prob1; };
+    std::vector<Combo> combos;
+    for (uint32_t i = 0; i < n; i++) {
+        const Pair &p = P[i];
+        if (!p.cand) continue;
+        for (uint32_t g = 0; g < p.ng; g++) {
+            const uint32_t a = p.first_prob + 2 * g;
+            const int c1 = count[a] < CM_CIRC_TOPCHAIN ? count[a] : CM_CIRC_TOPCHAIN, c2 = count[a + 1] < CM_CIRC_TOPCHAIN ? count[a + 1] : CM_CIRC_TOPCHAIN;
+            if (count[a] <= 0 || count[a + 1] <= 0) continue;
+            for (int j = 0; j < c1; j++)
+                for (int k = 0; k < c2; k++) combos.push_back(Combo{i, g, (uint32_t) j, (uint32_t) k, a});
+        }
+    }
+    const uint32_t nc = (uint32_t) combos.size();
+    std::vector<cm_circ_mate> d1(nc), d2(nc), dp1(nc), dp2(nc);
+    std::vector<int32_t> code(nc, 0), cret(nc, 0);
+    std::vector<cm_circ_res> ccr(nc);
+    std::vector<uint8_t> checked(nc, 0);
+    if (nc) {
+        std::vector<char> a1((size_t) nc * stride), a2((size_t) nc * stride);
+        std::vector<uint32_t> qs1(nc), qe1(nc), qs2(nc), qe2(nc), cl1(nc), cl2(nc), rp1((size_t) nc * F), rp2((size_t) nc * F);
+        std::vector<int32_t> qp1((size_t) nc * F), qp2((size_t) nc * F);
+        for (uint32_t t = 0; t < nc; t++) {
+            const Combo &c = combos[t];
+            const Pair &p = P[c.pair];
+            memcpy(&a1[(size_t) t * stride], &o1[(size_t) c.pair * stride], stride);
+            memcpy(&a2[(size_t) t * stride], &o2[(size_t) c.pair * stride], stride);
+            d1[t] = p.r1; d2[t] = p.r2;
+            qs1[t] = p.qs1; qe1[t] = p.qe1; qs2[t] = p.qs2; qe2[t] = p.qe2;
+            const size_t x1 = (size_t) c.prob1 * CH + c.j, x2 = ((size_t) c.prob1 + 1) * CH + c.k;
+            cl1[t] = clen[x1]; cl2[t] = clen[x2];
+            memcpy(&rp1[(size_t) t * F], &rpos[x1 * F], (size_t) F * 4); memcpy(&qp1[(size_t) t * F], &qpos[x1 * F], (size_t) F * 4);
+            memcpy(&rp2[(size_t) t * F], &rpos[x2 * F], (size_t) F * 4); memcpy(&qp2[(size_t) t * F], &qpos[x2 * F], (size_t) F * 4);
+        }
+        int r = E.dbl(E.self, E.contig, nc, a1.data(), a2.data(), stride, d1.data(), d2.data(), qs1.data(), qe1.data(), qs2.data(), qe2.data(), (uint32_t) F,
+                      cl1.data(), rp1.data(), qp1.data(), cl2.data(), rp2.data(), qp2.data(), ws, dp1.data(), dp2.data(), code.data());
+        if (r != 0) return r;
+        std::vector<uint32_t> sel;
+        for (uint32_t t = 0; t < nc; t++)
+            if (code[t] == 2 && dp1[t].m.type == CM_CIRC_T_CONCRD && dp2[t].m.type == CM_CIRC_T_CONCRD) sel.push_back(t);
+        const uint32_t m = (uint32_t) sel.size();
+        if (m) {
+            std::vector<char> b1((size_t) m * stride), b2((size_t) m * stride);
+            std::vector<int32_t> l1(m), l2(m), rr(m);
+            std::vector<cm_circ_mate> m1(m), m2(m), q1(m), q2(m);
+            std::vector<cm_circ_res> cr(m);
+            for (uint32_t u = 0; u < m; u++) {
+                const uint32_t t = sel[u];
+                memcpy(&b1[(size_t) u * stride], &a1[(size_t) t * stride], stride);
+                memcpy(&b2[(size_t) u * stride], &a2[(size_t) t * stride], stride);
+                l1[u] = P[combos[t].pair].l1; l2[u] = P[combos[t].pair].l2;
+                m1[u] = d1[t]; m2[u] = d2[t]; q1[u] = dp1[t]; q2[u] = dp2[t];
+            }
+            r = E.check4(E.self, E.contig, m, b1.data(), b2.data(), stride, l1.data(), l2.data(), m1.data(), m2.data(), q1.data(), q2.data(), ws, rr.data(),
+                         cr.data());
+            if (r != 0) return r;
+            for (uint32_t u = 0; u < m; u++) {
+                if (rr[u] < 0) return -100;
+                checked[sel[u]] = 1; cret[sel[u]] = rr[u]; ccr[sel[u]] = cr[u];
+            }
+        }
+    }
+    // the function's own order and rules, pair by pair
+    uint32_t t = 0;   // combos are in (pair, gene, j, k) order
+    for (uint32_t i = 0; i < n; i++) {
+        const Pair &p = P[i];
+        if (!p.cand) continue;
+        auto single_here = [&]() { CircEvent e; memset(&e, 0, sizeof(e)); e.pair = i; e.kind = 0; events.push_back(e); };
+        if (p.early_single) single_here();
+        int best = 40;
+        bool returned = false;
+        if (p.ng == 0) {                                            // gene not found: return
+            while (t < nc && combos[t].pair == i) t++;
+            continue;
+        }
+        for (uint32_t g = 0; g < p.ng && !returned; g++) {
+            const uint32_t a = p.first_prob + 2 * g;
+            if (count[a] <= 0 && count[a + 1] <= 0) continue;
+            if (count[a] <= 0 || count[a + 1] <= 0) { single_here(); continue; }
+            for (; t < nc && combos[t].pair == i && combos[t].gene == g; t++) {
+                if (returned || !checked[t]) continue;
+                CircEvent e;
+                e.pair = i; e.kind = 1; e.r1 = d1[t]; e.r2 = d2[t]; e.p1 = dp1[t]; e.p2 = dp2[t]; e.ret = cret[t]; e.cr = ccr[t];
+                events.push_back(e);
+                const int type = cret[t];
+                if (type < 20) { best = type; returned = true; }
+                else if (type <= 22 && type < best) {
+                    best = type;
+                    if (push_cr) push_cr[i] = ccr[t];
+                    if (type == 20) { push_type[i] = 20; returned = true; }
+                }
+            }
+        }
+        while (t < nc && combos[t].pair == i) t++;
+        if (returned) continue;
+        if (best >= 20 && best <= 22) push_type[i] = best;
+        else single_here();
+    }
     return 0;
 }

@@ -610,3 +610,108 @@ CM_HDN int cm_circ_exact_row(const DevView &v, cm_circ_mate &r1, cm_circ_mate &r
     cm_circ_mate_out(pm, pm_out);
     return ret;
 }
+
+// ---- call_circ_double_split (process_circ.cpp:485-645): one (chain j of R1's unmapped part, chain k of R2's) -----------------
+// same_transcript(segments, 4, common_tid) (src/utils.cpp:496-604): the sixteen start / end combinations in the reference's
+// order (the fourth mate's end only in the second half); common_tid = transcripts of (seg0 & seg1) that are also in (seg2 & seg3).
+// -> TidSet{i0, i1} with the two further intervals in x.ts_c / x.ts_d.
+CM_HD bool cm_circ_same_transcript4(ExtCtx &x, MateD &m0, MateD &m1, MateD &m2, MateD &m3, TidSet &ts) {
+    const AnnotDev &a = x.v->a;
+    cm_overlap_to_spos(a, m0); cm_overlap_to_spos(a, m1); cm_overlap_to_spos(a, m2); cm_overlap_to_spos(a, m3);
+    MateD c0 = m0, c1 = m1, c2 = m2, c3 = m3;     // the end look-ups are made on same_transcript's copies
+    cm_overlap_to_epos(a, c0); cm_overlap_to_epos(a, c1); cm_overlap_to_epos(a, c2); cm_overlap_to_epos(a, c3);
+    for (int e3 = 0; e3 < 2; e3++)
+        for (int e0 = 0; e0 < 2; e0++)
+            for (int e1 = 0; e1 < 2; e1++)
+                for (int e2 = 0; e2 < 2; e2++) {
+                    const int i0 = e0 ? c0.exons_epos : c0.exons_spos, i1 = e1 ? c1.exons_epos : c1.exons_spos,
+                              i2 = e2 ? c2.exons_epos : c2.exons_spos, i3 = e3 ? c3.exons_epos : c3.exons_spos;
+                    if (i0 < 0 || i1 < 0 || i2 < 0 || i3 < 0) continue;
+                    const uint32_t b = a.seg_tid_off[a.iv_seg_off[i0]], e = a.seg_tid_off[a.iv_seg_off[i0 + 1]];
+                    for (uint32_t k = b; k < e; k++) {
+                        const uint32_t t = a.tid[k];
+                        if (cm_iv_has_tid(a, i1, t) && cm_iv_has_tid(a, i2, t) && cm_iv_has_tid(a, i3, t)) {
+                            ts.iv_a = i0; ts.iv_b = i1; x.ts_c = i2; x.ts_d = i3;
+                            return true;
+                        }
+                    }
+                }
+    ts.iv_a = ts.iv_b = -1;
+    x.ts_c = x.ts_d = -1;
+    return false;
+}
+
+CM_HD void cm_circ_set_mm(const ChainView &ch, uint32_t qspos, int rlen, int dir, int ws, MateD &mm) {   // set_mm, :1713-1752
+    mm.spos = ch.frags[0].rpos;
+    mm.epos = ch.frags[ch.chain_len - 1].rpos + (uint32_t) ws - 1;
+    mm.qspos = qspos;
+    mm.qepos = qspos + (uint32_t) rlen - 1;
+    mm.matched_len = (mm.qepos + 1 >= mm.qspos) ? (mm.qepos - mm.qspos + 1) : 0;
+    mm.dir = dir;
+}
+
+// returns 0: no common transcript (continue), 1: extend_both_mates failed (continue), 2: extended (the caller goes on when both
+// partial mates are CONCRD).  r1 / r2 keep the start look-ups made on them.
+CM_HDN int cm_circ_double_row(const DevView &v, cm_circ_mate &r1io, cm_circ_mate &r2io, uint32_t r1_qspos, uint32_t r1_qepos, uint32_t r2_qspos,
+                              uint32_t r2_qepos, const uint8_t *r1_seq, const uint8_t *r2_seq, const ChainView &c1, const ChainView &c2,
+                              cm_circ_mate &p1_out, cm_circ_mate &p2_out) {
+    ExtCtx x;
+    ext_ctx_init(x, &v);
+    const int ws = v.p.kmer;
+    MateD r1, r2, p1, p2;
+    cm_circ_mate_in(r1io, r1);
+    cm_circ_mate_in(r2io, r2);
+    mate_init(p1, v.p);
+    mate_init(p2, v.p);
+    cm_circ_set_mm(c1, r1_qspos, (int) (r1_qepos - r1_qspos + 1), r1.dir, ws, p1);
+    cm_circ_set_mm(c2, r2_qspos, (int) (r2_qepos - r2_qspos + 1), r2.dir, ws, p2);
+    TidSet ts;
+    const bool same = cm_circ_same_transcript4(x, r1, r2, p1, p2, ts);
+    cm_circ_mate_out(r1, r1io);
+    cm_circ_mate_out(r2, r2io);
+    int ret = 0;
+    if (same) {
+        bool ok;
+        if (c1.frags[0].rpos <= c2.frags[0].rpos)
+            ok = cm_extend_both_mates<true>(x, c1, c2, ts, r1_seq, r2_seq, (int) r1_qspos, (int) r2_qspos, (int) r1_qepos, (int) r2_qepos, p1, p2);
+        else
+            ok = cm_extend_both_mates<true>(x, c2, c1, ts, r2_seq, r1_seq, (int) r2_qspos, (int) r1_qspos, (int) r2_qepos, (int) r1_qepos, p2, p1);
+        ret = ok ? 2 : 1;
+    }
+    cm_circ_mate_out(p1, p1_out);
+    cm_circ_mate_out(p2, p2_out);
+    return ret;
+}
+
+// check_split_map(mm_r1, mm_r2, r1_partial_mm, r2_partial_mm, cr) as call_circ_double_split calls it (:602): r1_seq / r2_seq are the
+// two oriented reads; fullmap_seq is whatever an earlier call_circ_single_split of the same pair left (NULL / 0 when none)
+CM_HDN int cm_circ_check4_row(const DevView &v, const uint8_t *r1_seq, int r1_len, const uint8_t *r2_seq, int r2_len, const uint8_t *fullmap_seq,
+                              int fullmap_len, const cm_circ_mate &r1, const cm_circ_mate &r2, const cm_circ_mate &p1, const cm_circ_mate &p2,
+                              cm_circ_res &out) {
+    ExtCtx x;
+    ext_ctx_init(x, &v);
+    CircSplitCtx c;
+    c.x = &x;
+    c.remain_seq = nullptr; c.remain_len = 0;
+    c.fullmap_seq = fullmap_seq; c.fullmap_len = fullmap_len;
+    c.r1_seq = r1_seq; c.r1_len = r1_len;
+    c.r2_seq = r2_seq; c.r2_len = r2_len;
+    c.depth = 0;
+    c.overflow = 0;
+    MateD a, b, q1, q2;
+    cm_circ_mate_in(r1, a); cm_circ_mate_in(r2, b); cm_circ_mate_in(p1, q1); cm_circ_mate_in(p2, q2);
+    CircResD cr;
+    cr.spos = cr.epos = 0;
+    cr.ss_n = cr.es_n = cr.ref_n = cr.was_set = 0;
+    cr.ss[0] = cr.ss[1] = cr.es[0] = cr.es[1] = cr.sref[0] = cr.sref[1] = cr.eref[0] = cr.eref[1] = 0;
+    CircNested nest;
+    nest.set = false;
+    int ret = cm_circ_check_split_map4(c, a, b, q1, q2, cr, nest);
+    if (nest.set) ret = cm_circ_final_check(c, nest.full, nest.left, nest.right, cr);   // the tail call of its two single-BSJ arms
+    out.spos = cr.spos; out.epos = cr.epos;
+    for (int k = 0; k < 2; k++) {
+        out.start_signal[k] = cr.ss[k]; out.end_signal[k] = cr.es[k]; out.start_bp_ref[k] = cr.sref[k]; out.end_bp_ref[k] = cr.eref[k];
+    }
+    out.start_signal_n = cr.ss_n; out.end_signal_n = cr.es_n; out.ref_n = cr.ref_n; out.was_set = cr.was_set;
+    return c.overflow ? -1 : ret;
+}

@@ -151,6 +151,8 @@ struct ExtCtx {
     const EndSpec *seed;    // pre-computed DPs of that end's transcript walk (nullable)
     EndSpec *capture;       // pre-alignment kernel only: where the walk's DPs are recorded (nullable)
     const uint8_t *tbase;   // strand row the t_off of seed / capture entries refer to
+    int ts_c, ts_d;         // stage 2 (EDIT instantiations only): two more intervals a transcript of the TidSet must occur in
+                            // (the four-interval same_transcript, src/utils.cpp:378-398); -1 = none
 };
 CM_HD void ext_ctx_init(ExtCtx &x, const DevView *v) {
     x.v = v;
@@ -159,6 +161,7 @@ CM_HD void ext_ctx_init(ExtCtx &x, const DevView *v) {
     x.seed = nullptr;
     x.capture = nullptr;
     x.tbase = nullptr;
+    x.ts_c = x.ts_d = -1;
 }
 
 // The genome-text alignment problem of one chain end as extend_left / extend_right pose it in their
@@ -482,7 +485,7 @@ CM_HDN bool cm_extend_right(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &
         uint32_t b = a.seg_tid_off[a.iv_seg_off[ts.iv_a]], e = a.seg_tid_off[a.iv_seg_off[ts.iv_a + 1]];
         for (uint32_t k = b; k < e; k++) {
             uint32_t t = a.tid[k];
-            if (cm_iv_has_tid(a, ts.iv_b, t))
+            if (cm_iv_has_tid(a, ts.iv_b, t) && (!EDIT || x.ts_c < 0 || (cm_iv_has_tid(a, x.ts_c, t) && cm_iv_has_tid(a, x.ts_d, t))))
                 cm_extend_right_trans<EDIT>(x, t, pos, ref_len, seq, seq_len, ed_th, ub, best, consecutive, memo);
         }
     } else if (EDIT && ts.iv_a <= -2) {     // one transcript: stage 2 only
@@ -662,7 +665,7 @@ CM_HDN bool cm_extend_left(ExtCtx &x, TidSet ts, const uint8_t *seq, uint32_t &p
         uint32_t b = a.seg_tid_off[a.iv_seg_off[ts.iv_a]], e = a.seg_tid_off[a.iv_seg_off[ts.iv_a + 1]];
         for (uint32_t k = b; k < e; k++) {
             uint32_t t = a.tid[k];
-            if (cm_iv_has_tid(a, ts.iv_b, t))
+            if (cm_iv_has_tid(a, ts.iv_b, t) && (!EDIT || x.ts_c < 0 || (cm_iv_has_tid(a, x.ts_c, t) && cm_iv_has_tid(a, x.ts_d, t))))
                 cm_extend_left_trans<EDIT>(x, t, pos, ref_len, seq, seq_len, ed_th, lb, best, consecutive, memo);
         }
     } else if (EDIT && ts.iv_a <= -2) {
@@ -760,6 +763,7 @@ CM_HDN bool cm_extend_chain_left(ExtCtx &x, TidSet ts, const ChainView &ch, cons
 }
 
 // extend_both_mates (src/extend.cpp:37-125)
+template <bool EDIT = false>
 CM_HDN bool cm_extend_both_mates(ExtCtx &x, const ChainView &lch, const ChainView &rch, TidSet ts, const uint8_t *lseq,
                                  const uint8_t *rseq, int lqspos, int rqspos, int lseq_len, int rseq_len, MateD &lmm,
                                  MateD &rmm) {
@@ -782,16 +786,16 @@ CM_HDN bool cm_extend_both_mates(ExtCtx &x, const ChainView &lch, const ChainVie
         lmm.matched_len = (uint32_t) (lseq_len - lqspos + 1);
         lmm.qspos = (uint32_t) lqspos;
         lmm.qepos = (uint32_t) lseq_len;
-        llok = cm_extend_chain_left(x, ts, lch, lseq, lqspos - 1, CM_MINLB, lmm, lerr);
+        llok = cm_extend_chain_left<EDIT>(x, ts, lch, lseq, lqspos - 1, CM_MINLB, lmm, lerr);
     }
     if (r_extend) {
         rmm.matched_len = (uint32_t) (rseq_len - rqspos + 1);
         rmm.qspos = (uint32_t) rqspos;
         rmm.qepos = (uint32_t) rseq_len;
-        rlok = cm_extend_chain_left(x, ts, rch, rseq, rqspos - 1, l_extend ? lmm.spos : CM_MINLB, rmm, rerr);
+        rlok = cm_extend_chain_left<EDIT>(x, ts, rch, rseq, rqspos - 1, l_extend ? lmm.spos : CM_MINLB, rmm, rerr);
     }
-    if (r_extend) rrok = cm_extend_chain_right(x, ts, rch, rseq, rseq_len, CM_MAXUB, rmm, rerr);
-    if (l_extend) lrok = cm_extend_chain_right(x, ts, lch, lseq, lseq_len, r_extend ? rmm.epos : CM_MAXUB, lmm, lerr);
+    if (r_extend) rrok = cm_extend_chain_right<EDIT>(x, ts, rch, rseq, rseq_len, CM_MAXUB, rmm, rerr);
+    if (l_extend) lrok = cm_extend_chain_right<EDIT>(x, ts, lch, lseq, lseq_len, r_extend ? rmm.epos : CM_MAXUB, lmm, lerr);
     if (l_extend) cm_update_match_mate_info(llok, lrok, lerr, lmm, p);
     if (r_extend) cm_update_match_mate_info(rlok, rrok, rerr, rmm, p);
     return true;

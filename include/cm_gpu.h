@@ -339,6 +339,19 @@ int cm_gpu_circ_single_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const c
                              cm_circ_res *att_cr, cm_circ_mate *att_out_r1, cm_circ_mate *att_out_r2, cm_circ_mate *att_out_pm, int32_t *best_type,
                              cm_circ_res *best_cr);
 
+/* ProcessCirc::call_circ_double_split (src/process_circ.cpp:485-645) for a batch of CHI2BSJ pairs (inputs as cm_gpu_circ_single_batch).
+ * Per pair, in the function's order, the events that produce output: kind 0 = "call_circ_single_split(record1, record2) is called
+ * here" (before the gene loop when one unmapped part is shorter than window_size, for a gene where only one part chains, at the
+ * end when nothing was pushed; what that call writes is cm_gpu_circ_single_batch's answer for the pair -- it accepts CHI2BSJ
+ * pairs too -- and is the same every time), kind 1 = a four-mate check_split_map call with mm_r1, mm_r2, r1_partial_mm,
+ * r2_partial_mm (what print_split_mapping prints), its type and CircRes.  push_type[i] = 20..22 when the function pushes its own
+ * best_cr (push_cr[i], contig coordinates; con_shift from mm_r1.spos = mr.spos_r1), else -1. */
+int cm_gpu_circ_double_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
+                             const uint16_t *len1, const uint16_t *len2, const cm_mread *mr, const uint32_t *gene_off, const uint32_t *gene_start,
+                             const uint32_t *gene_end, int window_size, int step, uint32_t event_cap, uint32_t *n_events, uint32_t *ev_pair,
+                             uint8_t *ev_kind, cm_circ_mate *ev_r1, cm_circ_mate *ev_r2, cm_circ_mate *ev_p1, cm_circ_mate *ev_p2, int32_t *ev_ret,
+                             cm_circ_res *ev_cr, int32_t *push_type, cm_circ_res *push_cr);
+
 /* Alignment kernels, one problem per row (src/align.h:165-176):
  *   kind 0: DropAlignment::local_alignment_right_sc  (src/align.cpp:669)
  *   kind 1: DropAlignment::local_alignment_left_sc   (:694)

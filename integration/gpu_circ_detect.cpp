@@ -4,7 +4,8 @@
 // How it is bound: integration/gpu_shim.h renames the one call `process_circ.do_process()` of circ_detect (src/circminer.cpp:349-352)
 // to cm_shim_do_process, a member this file defines; no reference source is edited.  Everything around the per-pair work is
 // the reference's own code called in do_process's order: index / GTF set-up, the sorted remain FASTQ through FASTQParser,
-// load_genome per contig, call_circ for the double-split pairs (and whatever else is not a CHIBSJ), report_events.  For a CHIBSJ
+// load_genome per contig, report_events; the double-split pairs go through cm_gpu_circ_double_batch the same way (CM_GPU_STAGE2_DOUBLE=0: through the
+// reference's call_circ).  For a CHIBSJ
 // pair the batch returns every check_split_map attempt with its three mates and type -- the line print_split_mapping +
 // fprintf(candid_file, "%d\n", type) write -- and the CircRes call_circ_single_split pushes; they are written / pushed here
 // when the pair's turn comes, so candidates.pam and circ_report are byte-identical.
@@ -46,38 +47,32 @@ struct Pair {                 // one pair of the sorted remain files
     MatchedRead mr;
 };
 
+double g_t_batch = 0, g_t_ref_pairs = 0, g_t_write = 0, g_t_load = 0;
 void die2(cm_gpu_ctx *ctx, const char *what) {
     fprintf(stderr, "circminer_gpu: %s failed: %s\n", what, cm_gpu_last_error(ctx));
     exit(1);
 }
 
-// the pairs of one contig: CHIBSJ ones through the batch, then everything in file order
-void process_contig(ProcessCirc &pc, std::vector<Pair> &P) {
-    const size_t n_all = P.size();
-    std::vector<size_t> who;                        // CHIBSJ pairs
-    for (size_t i = 0; i < n_all; i++)
-        if (P[i].mr.type == CHIBSJ) who.push_back(i);
-    const uint32_t n = (uint32_t) who.size();
-    std::vector<uint32_t> att_pair, att_first(n + 1, 0);
-    std::vector<cm_circ_mate> a_r1, a_r2, a_pm, a_in1;
-    std::vector<int32_t> a_ret, best(n, -1);
-    std::vector<cm_circ_res> best_cr(n);
-    if (n) {
-        cm_gpu_ctx *ctx = cm_shim_stage2_contig(contigNum);
-        uint32_t stride = 0;
+// inputs of the batch entries for a set of pairs: reads as read, MatchedRead in contig coordinates, genes under mr.spos_r1
+struct Inputs {
+    uint32_t n = 0, stride = 16;
+    std::vector<char> s1, s2;
+    std::vector<uint16_t> l1, l2;
+    std::vector<cm_mread> mr;
+    std::vector<uint32_t> goff, gs, ge;
+    void build(const std::vector<Pair> &P, const std::vector<size_t> &who) {
+        n = (uint32_t) who.size();
         for (size_t k : who) stride = std::max<uint32_t>(stride, (uint32_t) std::max(P[k].seq1.size(), P[k].seq2.size()));
         stride = (stride + 15) & ~15u;
-        std::vector<char> s1((size_t) n * stride, 0), s2((size_t) n * stride, 0);
-        std::vector<uint16_t> l1(n), l2(n);
-        std::vector<cm_mread> mr(n);
-        std::vector<uint32_t> goff(n + 1, 0), gs, ge;
+        s1.assign((size_t) n * stride, 0); s2.assign((size_t) n * stride, 0);
+        l1.resize(n); l2.resize(n); mr.resize(n); goff.assign(n + 1, 0);
         for (uint32_t k = 0; k < n; k++) {
             const Pair &p = P[who[k]];
             memcpy(&s1[(size_t) k * stride], p.seq1.data(), p.seq1.size());
             memcpy(&s2[(size_t) k * stride], p.seq2.data(), p.seq2.size());
             l1[k] = (uint16_t) p.seq1.size(); l2[k] = (uint16_t) p.seq2.size();
             MatchedRead m = p.mr;
-            gtf_parser.chrloc2conloc(m.chr_r1, m.spos_r1, m.epos_r1);      // call_circ_single_split :372-373
+            gtf_parser.chrloc2conloc(m.chr_r1, m.spos_r1, m.epos_r1);      // call_circ_single_split :372-373, call_circ_double_split :518-519
             gtf_parser.chrloc2conloc(m.chr_r2, m.spos_r2, m.epos_r2);
             cm_mread &o = mr[k];
             memset(&o, 0, sizeof(o));
@@ -86,71 +81,154 @@ void process_contig(ProcessCirc &pc, std::vector<Pair> &P) {
             o.mlen_r1 = m.mlen_r1; o.mlen_r2 = m.mlen_r2; o.ed_r1 = m.ed_r1; o.ed_r2 = m.ed_r2;
             o.type = m.type; o.tlen = m.tlen; o.contig_num = m.contig_num;
             o.r1_forward = m.r1_forward; o.r2_forward = m.r2_forward;
-            const IntervalInfo<GeneInfo> *gi = gtf_parser.get_gene_overlap(m.spos_r1, false);   // :404
+            const IntervalInfo<GeneInfo> *gi = gtf_parser.get_gene_overlap(m.spos_r1, false);   // :404, :521
             if (gi)
                 for (const GeneInfo &g : gi->seg_list) { gs.push_back(g.start); ge.push_back(g.end); }
             goff[k + 1] = (uint32_t) gs.size();
         }
         if (gs.empty()) { gs.push_back(0); ge.push_back(0); }
-        uint32_t n_att = 0;
+    }
+};
+
+// call_circ_single_split's answer for every pair of a set
+struct SingleRes {
+    std::vector<uint32_t> first;                    // attempts of pair k: [first[k], first[k + 1])
+    std::vector<cm_circ_mate> in1, r1, r2, pm;
+    std::vector<int32_t> ret, best;
+    std::vector<cm_circ_res> best_cr;
+    uint32_t n_att = 0;
+    void run(ProcessCirc &pc, cm_gpu_ctx *ctx, Inputs &in) {
+        const uint32_t n = in.n;
+        best.assign(n, -1); best_cr.resize(n); first.assign(n + 1, 0);
+        if (!n) return;
+        std::vector<uint32_t> att_pair;
         uint32_t cap = 4 * n + 1024;
         for (int pass = 0; pass < 2; pass++) {      // a second pass only when more attempts came back than the first guess holds
-            att_pair.assign(cap, 0); a_r1.resize(cap); a_r2.resize(cap); a_pm.resize(cap); a_in1.resize(cap); a_ret.assign(cap, 0);
-            if (cm_gpu_circ_single_batch(ctx, contigNum, n, s1.data(), s2.data(), stride, l1.data(), l2.data(), mr.data(), goff.data(), gs.data(),
-                                         ge.data(), pc.window_size, pc.step, cap, &n_att, att_pair.data(), nullptr, a_in1.data(), nullptr, nullptr,
-                                         a_ret.data(), nullptr, a_r1.data(), a_r2.data(), a_pm.data(), best.data(), best_cr.data()) != CM_OK)
+            att_pair.assign(cap, 0); r1.resize(cap); r2.resize(cap); pm.resize(cap); in1.resize(cap); ret.assign(cap, 0);
+            if (cm_gpu_circ_single_batch(ctx, contigNum, n, in.s1.data(), in.s2.data(), in.stride, in.l1.data(), in.l2.data(), in.mr.data(),
+                                         in.goff.data(), in.gs.data(), in.ge.data(), pc.window_size, pc.step, cap, &n_att, att_pair.data(), nullptr,
+                                         in1.data(), nullptr, nullptr, ret.data(), nullptr, r1.data(), r2.data(), pm.data(), best.data(),
+                                         best_cr.data()) != CM_OK)
                 die2(ctx, "cm_gpu_circ_single_batch");
             if (n_att <= cap) break;
             cap = n_att;
         }
-        // attempts are in (pair, gene, chain) order: first attempt of every pair
-        uint32_t a = 0;
+        uint32_t a = 0;                             // attempts are in (pair, gene, chain) order
         for (uint32_t k = 0; k < n; k++) {
-            att_first[k] = a;
+            first[k] = a;
             while (a < n_att && att_pair[a] == k) a++;
         }
-        att_first[n] = a;
-        if (getenv("CM_GPU_VERBOSE"))
-            fprintf(stderr, "circminer_gpu: stage 2, contig %d: %u single-split pairs of %zu in one batch, %u check_split_map attempts\n", contigNum, n,
-                    n_all, n_att);
+        first[n] = a;
     }
+    // what one call_circ_single_split(record1, record2) writes and pushes for pair k
+    void emit(ProcessCirc &pc, const Pair &p, uint32_t k) const {
+        for (uint32_t t = first[k]; t < first[k + 1]; t++) {
+            // print_split_mapping (:1685-1696) + the type; con_shift = get_shift(contigNum, mm_r1.spos) as it was before the call
+            ConShift cs = gtf_parser.get_shift(contigNum, in1[t].m.spos);
+            const cm_mate &q = pm[t].m, &m1 = r1[t].m, &m2 = r2[t].m;
+            fprintf(pc.candid_file, "%s\t%s\t%u\t%u\t%d\t%d\t%d\t%u\t%u\t%d\t%d\t%d\t%u\t%u\t%d\t%d\t%d\t", p.rname.c_str(), cs.contig.c_str(),
+                    q.spos - cs.shift, q.epos - cs.shift, q.qspos, q.matched_len, q.dir, m1.spos - cs.shift, m1.epos - cs.shift, m1.qspos,
+                    m1.matched_len, m1.dir, m2.spos - cs.shift, m2.epos - cs.shift, m2.qspos, m2.matched_len, m2.dir);
+            fprintf(pc.candid_file, "%d\n", ret[t]);
+        }
+        if (best[k] >= CR && best[k] <= MCR) {
+            uint32_t t_best = first[k];             // the attempt that set best_cr: the first one of the final type (types only improve)
+            for (uint32_t t = first[k]; t < first[k + 1]; t++)
+                if (ret[t] == best[k]) { t_best = t; break; }
+            push(pc, p, best[k], best_cr[k], in1[t_best].m.spos);
+        }
+    }
+    static void push(ProcessCirc &pc, const Pair &p, int type, const cm_circ_res &c, uint32_t r1_spos) {
+        ConShift cs = gtf_parser.get_shift(contigNum, r1_spos);
+        CircRes cr;
+        cr.chr = cs.contig;
+        cr.rname = p.rname;
+        cr.spos = c.spos - cs.shift;
+        cr.epos = c.epos - cs.shift;
+        cr.type = type;
+        cr.start_signal = std::string((const char *) c.start_signal, c.start_signal_n);
+        cr.end_signal = std::string((const char *) c.end_signal, c.end_signal_n);
+        cr.start_bp_ref = std::string((const char *) c.start_bp_ref, c.ref_n);
+        cr.end_bp_ref = std::string((const char *) c.end_bp_ref, c.ref_n);
+        pc.circ_res.push_back(cr);
+    }
+};
+
+// the pairs of one contig: the CHIBSJ and CHI2BSJ ones through the batch entries, then everything in file order
+void process_contig(ProcessCirc &pc, std::vector<Pair> &P) {
+    const size_t n_all = P.size();
+    const char *sw2 = getenv("CM_GPU_STAGE2_DOUBLE");
+    const bool gpu_double = !(sw2 && !strcmp(sw2, "0"));       // CM_GPU_STAGE2_DOUBLE=0: double-split pairs through the reference's call_circ
+    std::vector<size_t> who1, who2;
+    for (size_t i = 0; i < n_all; i++) {
+        if (P[i].mr.type == CHIBSJ) who1.push_back(i);
+        else if (P[i].mr.type == CHI2BSJ && gpu_double) who2.push_back(i);
+    }
+    const double t_b0 = get_real_time();
+    Inputs in1, in2;
+    SingleRes S1, S2;
+    std::vector<uint32_t> ev_first(who2.size() + 1, 0), ev_pair;
+    std::vector<uint8_t> ev_kind;
+    std::vector<cm_circ_mate> e_r1, e_r2, e_p1, e_p2;
+    std::vector<int32_t> e_ret, push_type(who2.size(), -1);
+    std::vector<cm_circ_res> push_cr(who2.size());
+    uint32_t n_ev = 0;
+    if (!who1.empty() || !who2.empty()) {
+        cm_gpu_ctx *ctx = cm_shim_stage2_contig(contigNum);
+        in1.build(P, who1);
+        S1.run(pc, ctx, in1);
+        in2.build(P, who2);
+        S2.run(pc, ctx, in2);                                   // what call_circ_single_split gives on the double-split pairs
+        if (in2.n) {
+            uint32_t cap = 8 * in2.n + 1024;
+            for (int pass = 0; pass < 2; pass++) {
+                ev_pair.assign(cap, 0); ev_kind.assign(cap, 0); e_r1.resize(cap); e_r2.resize(cap); e_p1.resize(cap); e_p2.resize(cap); e_ret.assign(cap, 0);
+                if (cm_gpu_circ_double_batch(ctx, contigNum, in2.n, in2.s1.data(), in2.s2.data(), in2.stride, in2.l1.data(), in2.l2.data(), in2.mr.data(),
+                                             in2.goff.data(), in2.gs.data(), in2.ge.data(), pc.window_size, pc.step, cap, &n_ev, ev_pair.data(),
+                                             ev_kind.data(), e_r1.data(), e_r2.data(), e_p1.data(), e_p2.data(), e_ret.data(), nullptr, push_type.data(),
+                                             push_cr.data()) != CM_OK)
+                    die2(ctx, "cm_gpu_circ_double_batch");
+                if (n_ev <= cap) break;
+                cap = n_ev;
+            }
+            uint32_t a = 0;
+            for (uint32_t k = 0; k < in2.n; k++) {
+                ev_first[k] = a;
+                while (a < n_ev && ev_pair[a] == k) a++;
+            }
+            ev_first[in2.n] = a;
+        }
+        if (getenv("CM_GPU_VERBOSE"))
+            fprintf(stderr, "circminer_gpu: stage 2, contig %d: %u single-split pairs of %zu in one batch, %u check_split_map attempts; %u double-split "
+                    "pairs, %u events\n", contigNum, in1.n, n_all, S1.n_att, in2.n, n_ev);
+    }
+    g_t_batch += get_real_time() - t_b0;
     // file order
     Record r1, r2;
     r1.init();
     r2.init();
-    uint32_t k = 0;
+    uint32_t k1 = 0, k2 = 0;
     for (size_t i = 0; i < n_all; i++) {
         Pair &p = P[i];
+        const double t_p0 = get_real_time();
         if (p.mr.type == CHIBSJ) {
-            for (uint32_t t = att_first[k]; t < att_first[k + 1]; t++) {
-                // print_split_mapping (:1685-1696) + the type; con_shift = get_shift(contigNum, mm_r1.spos) as it was before the call
-                ConShift cs = gtf_parser.get_shift(contigNum, a_in1[t].m.spos);
-                const cm_mate &pm = a_pm[t].m, &m1 = a_r1[t].m, &m2 = a_r2[t].m;
-                fprintf(pc.candid_file, "%s\t%s\t%u\t%u\t%d\t%d\t%d\t%u\t%u\t%d\t%d\t%d\t%u\t%u\t%d\t%d\t%d\t", p.rname.c_str(), cs.contig.c_str(),
-                        pm.spos - cs.shift, pm.epos - cs.shift, pm.qspos, pm.matched_len, pm.dir, m1.spos - cs.shift, m1.epos - cs.shift, m1.qspos,
-                        m1.matched_len, m1.dir, m2.spos - cs.shift, m2.epos - cs.shift, m2.qspos, m2.matched_len, m2.dir);
-                fprintf(pc.candid_file, "%d\n", a_ret[t]);
+            S1.emit(pc, p, k1++);
+            g_t_write += get_real_time() - t_p0;
+        } else if (p.mr.type == CHI2BSJ && gpu_double) {
+            const uint32_t k = k2++;
+            for (uint32_t t = ev_first[k]; t < ev_first[k + 1]; t++) {
+                if (ev_kind[t] == 0) { S2.emit(pc, p, k); continue; }
+                // print_split_mapping, four mates (:1698-1711) + the type
+                ConShift cs = gtf_parser.get_shift(contigNum, in2.mr[k].spos_r1);
+                const cm_mate &a = e_p1[t].m, &b = e_p2[t].m, &m1 = e_r1[t].m, &m2 = e_r2[t].m;
+                fprintf(pc.candid_file, "%s\t%s\t%u\t%u\t%d\t%d\t%d\t%u\t%u\t%d\t%d\t%d\t%u\t%u\t%d\t%d\t%d\t%u\t%u\t%d\t%d\t%d\t", p.rname.c_str(),
+                        cs.contig.c_str(), a.spos - cs.shift, a.epos - cs.shift, a.qspos, a.matched_len, a.dir, b.spos - cs.shift, b.epos - cs.shift,
+                        b.qspos, b.matched_len, b.dir, m1.spos - cs.shift, m1.epos - cs.shift, m1.qspos, m1.matched_len, m1.dir, m2.spos - cs.shift,
+                        m2.epos - cs.shift, m2.qspos, m2.matched_len, m2.dir);
+                fprintf(pc.candid_file, "%d\n", e_ret[t]);
             }
-            if (best[k] >= CR && best[k] <= MCR) {
-                // the attempt that set best_cr: the last one whose type equals the final best (types only improve)
-                uint32_t t_best = att_first[k];
-                for (uint32_t t = att_first[k]; t < att_first[k + 1]; t++)
-                    if (a_ret[t] == best[k]) { t_best = t; break; }
-                ConShift cs = gtf_parser.get_shift(contigNum, a_in1[t_best].m.spos);
-                const cm_circ_res &c = best_cr[k];
-                CircRes cr;
-                cr.chr = cs.contig;
-                cr.rname = p.rname;
-                cr.spos = c.spos - cs.shift;
-                cr.epos = c.epos - cs.shift;
-                cr.type = best[k];
-                cr.start_signal = std::string((const char *) c.start_signal, c.start_signal_n);
-                cr.end_signal = std::string((const char *) c.end_signal, c.end_signal_n);
-                cr.start_bp_ref = std::string((const char *) c.start_bp_ref, c.ref_n);
-                cr.end_bp_ref = std::string((const char *) c.end_bp_ref, c.ref_n);
-                pc.circ_res.push_back(cr);
-            }
-            k++;
+            if (push_type[k] >= CR && push_type[k] <= MCR) SingleRes::push(pc, p, push_type[k], push_cr[k], in2.mr[k].spos_r1);
+            g_t_write += get_real_time() - t_p0;
         } else {
             strcpy(r1.rname, p.rname.c_str()); strcpy(r2.rname, p.rname.c_str());
             strcpy(r1.seq, p.seq1.c_str()); strcpy(r1.rcseq, p.rc1.c_str());
@@ -159,6 +237,7 @@ void process_contig(ProcessCirc &pc, std::vector<Pair> &P) {
             *r1.mr = p.mr;
             *r2.mr = p.mr;
             pc.call_circ(&r1, &r2);
+            g_t_ref_pairs += get_real_time() - t_p0;
         }
     }
     r1.finalize();
@@ -210,10 +289,12 @@ void ProcessCirc::cm_shim_do_process(void) {
     int group_contig = -1;
     auto flush = [&]() {
         if (group.empty()) return;
+        const double t_l0 = get_real_time();
         while (pre_contig != group_contig) {      // :315-318
             load_genome();
             refresh_hash_table_list();
         }
+        g_t_load += get_real_time() - t_l0;
         process_contig(*this, group);
         group.clear();
     };
@@ -238,7 +319,12 @@ void ProcessCirc::cm_shim_do_process(void) {
     }
     flush();
     refresh_hash_table_list();
+    const double t_r0 = get_real_time();
     report_events();
+    if (getenv("CM_GPU_VERBOSE"))
+        fprintf(stderr, "circminer_gpu: stage 2: load_genome %.2f s, single-split batches (device + index) %.2f s, their lines / CircRes %.2f s, "
+                "other pairs through the reference's call_circ %.2f s, report_events %.2f s\n", g_t_load, g_t_batch, g_t_write, g_t_ref_pairs,
+                get_real_time() - t_r0);
     Logger::instance().info.set_prefix("[INFO] ");
     Logger::instance().info("CircRNA detection Completed! (CPU time: %.2lfs; Real time: %.2lfs)\n", get_cpu_time() - fq_cputime_start,
                             get_real_time() - fq_realtime_start);

@@ -620,6 +620,23 @@ int cmref_circ_single(uint32_t n, const char *seqs1, const char *seqs2, uint32_t
         mr_con[i].type = -1;
         MatchedRead mr;
         mread_to_ref(&mr_in[i], &mr);
+        if (mr.type == CHI2BSJ && (int) mr.contig_num == contigNum) {
+            // inputs of the double-split path for the batch entry: contig coordinates and the genes under mr.spos_r1 (:521-524)
+            gtf_parser.chrloc2conloc(mr.chr_r1, mr.spos_r1, mr.epos_r1);
+            gtf_parser.chrloc2conloc(mr.chr_r2, mr.spos_r2, mr.epos_r2);
+            mr_con[i].type = mr.type;
+            mr_con[i].spos_r1 = mr.spos_r1; mr_con[i].epos_r1 = mr.epos_r1; mr_con[i].spos_r2 = mr.spos_r2; mr_con[i].epos_r2 = mr.epos_r2;
+            const IntervalInfo<GeneInfo> *gi = gtf_parser.get_gene_overlap(mr.spos_r1, false);
+            if (gi) {
+                if (gi->seg_list.size() > gene_cap) return -3;
+                gene_cnt[i] = (uint32_t) gi->seg_list.size();
+                for (unsigned int g = 0; g < gi->seg_list.size(); ++g) {
+                    gene_se[((size_t) i * gene_cap + g) * 2] = gi->seg_list[g].start;
+                    gene_se[((size_t) i * gene_cap + g) * 2 + 1] = gi->seg_list[g].end;
+                }
+            }
+            continue;
+        }
         if (mr.type != CHIBSJ || (int) mr.contig_num != contigNum) continue;
         const int l1 = len1[i], l2 = len2[i];
         memcpy(s1.data(), seqs1 + (size_t) i * stride, l1); s1[l1] = 0;
@@ -803,6 +820,68 @@ int cmref_circ_single_real(uint32_t n, const char *seqs1, const char *seqs2, uin
             pc.circ_res.pop_back();
         }
     }
+    return 0;
+}
+
+// The unmodified ProcessCirc::call_circ on every pair of type want_type (CHIBSJ 3 / CHI2BSJ 4) of the current contig: the text it
+// writes to candidates.pam (text[text_off[i] .. text_off[i + 1])) and everything it pushes to circ_res (up to push_cap per pair:
+// type, spos, epos in chromosome coordinates, the two signals and reference bases as 8 bytes).
+int cmref_circ_call_real(uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride, const uint16_t *len1, const uint16_t *len2,
+                         const cm_mread *mr_in, int ws, int want_type, uint64_t text_cap, uint64_t *text_off, char *text, uint32_t push_cap,
+                         uint32_t *n_push, int32_t *push_type, uint32_t *push_spos, uint32_t *push_epos, uint8_t *push_sig) {
+    if (circ_pc(ws) != 0) return -1;
+    ProcessCirc &pc = *g_pc;
+    pc.refresh_hash_table_list();
+    uint64_t at = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        text_off[i] = at;
+        n_push[i] = 0;
+        MatchedRead mr;
+        mread_to_ref(&mr_in[i], &mr);
+        if ((int) mr.type != want_type || (int) mr.contig_num != contigNum) continue;
+        const int l1 = len1[i], l2 = len2[i];
+        memcpy(g_rec1->seq, seqs1 + (size_t) i * stride, l1); g_rec1->seq[l1] = 0;
+        memcpy(g_rec2->seq, seqs2 + (size_t) i * stride, l2); g_rec2->seq[l2] = 0;
+        revcomp(g_rec1->seq, l1, g_rec1->rcseq); g_rec1->rcseq[l1] = 0;
+        revcomp(g_rec2->seq, l2, g_rec2->rcseq); g_rec2->rcseq[l2] = 0;
+        g_rec1->seq_len = l1; g_rec2->seq_len = l2;
+        strcpy(g_rec1->rname, "r"); strcpy(g_rec2->rname, "r");
+        *(g_rec1->mr) = mr;
+        *(g_rec2->mr) = mr;
+        char *buf = NULL;
+        size_t blen = 0;
+        FILE *mem = open_memstream(&buf, &blen);
+        FILE *keep = pc.candid_file;
+        pc.candid_file = mem;
+        const size_t before = pc.circ_res.size();
+        pc.call_circ(g_rec1, g_rec2);
+        fflush(mem);
+        pc.candid_file = keep;
+        fclose(mem);
+        if (at + blen > text_cap) { free(buf); return -4; }
+        memcpy(text + at, buf, blen);
+        at += blen;
+        free(buf);
+        for (size_t q = before; q < pc.circ_res.size(); q++) {
+            const CircRes &cr = pc.circ_res[q];
+            const uint32_t u = n_push[i];
+            if (u < push_cap) {
+                const size_t o = (size_t) i * push_cap + u;
+                push_type[o] = cr.type; push_spos[o] = cr.spos; push_epos[o] = cr.epos;
+                uint8_t *sg = push_sig + o * 8;
+                memset(sg, 0, 8);
+                for (size_t c = 0; c < 2; c++) {
+                    if (c < cr.start_signal.size()) sg[c] = cr.start_signal[c];
+                    if (c < cr.end_signal.size()) sg[2 + c] = cr.end_signal[c];
+                    if (c < cr.start_bp_ref.size()) sg[4 + c] = cr.start_bp_ref[c];
+                    if (c < cr.end_bp_ref.size()) sg[6 + c] = cr.end_bp_ref[c];
+                }
+            }
+            n_push[i]++;
+        }
+        pc.circ_res.resize(before);
+    }
+    text_off[n] = at;
     return 0;
 }
 }  // extern "C"

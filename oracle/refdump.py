@@ -267,6 +267,11 @@ def main():
             out[f"c{c}_circreal_seconds"] = time.time() - t0
             for k, v in real.items():
                 out[f"c{c}_circreal_{k}"] = v
+            t0 = time.time()
+            real2 = h.circ_call_real(s1, s2, lens, lens, mr1, 4)   # the unmodified call_circ on the double-split (CHI2BSJ) pairs
+            out[f"c{c}_circreal2_seconds"] = time.time() - t0
+            for k, v in real2.items():
+                out[f"c{c}_circreal2_{k}"] = v
             for k, v in rec.items():
                 out[f"c{c}_circs_{k}"] = v
             if len(rec["ret"]):

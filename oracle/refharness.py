@@ -253,6 +253,26 @@ class RefHarness:
         assert r == 0, r
         return out
 
+    def circ_call_real(self, s1, s2, l1, l2, mreads, want_type: int, ws: int = 8, push_cap: int = 4) -> dict:
+        """The unmodified ProcessCirc::call_circ on every pair of type want_type of the current contig: its candidates.pam text per pair
+        and everything it pushes to circ_res (cmref_circ_call_real)."""
+        a1, a2 = np.ascontiguousarray(s1, np.uint8), np.ascontiguousarray(s2, np.uint8)
+        n, stride = a1.shape
+        l1, l2 = np.ascontiguousarray(l1, np.uint16), np.ascontiguousarray(l2, np.uint16)
+        mr = np.ascontiguousarray(mreads)
+        cap = 64 << 20
+        text = np.zeros(cap, np.uint8)
+        out = dict(text_off=np.zeros(n + 1, np.uint64), n_push=np.zeros(n, np.uint32), push_type=np.zeros((n, push_cap), np.int32),
+                   push_spos=np.zeros((n, push_cap), np.uint32), push_epos=np.zeros((n, push_cap), np.uint32),
+                   push_sig=np.zeros((n, push_cap, 8), np.uint8))
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        r = self.lib.cmref_circ_call_real(C.c_uint32(n), vp(a1), vp(a2), C.c_uint32(stride), vp(l1), vp(l2), vp(mr), ws, want_type, C.c_uint64(cap),
+                                          vp(out["text_off"]), vp(text), C.c_uint32(push_cap),
+                                          *[vp(out[k]) for k in ("n_push", "push_type", "push_spos", "push_epos", "push_sig")])
+        assert r == 0, r
+        out["text"] = text[:int(out["text_off"][-1])].copy()
+        return out
+
     def circ_check(self, rec: dict, ws: int = 8) -> dict:
         """ProcessCirc::check_split_map on given inputs (same record layout as Mapper.circ_check)."""
         from circminer_b200.api import CIRC_MATE_DTYPE, CIRC_RES_DTYPE

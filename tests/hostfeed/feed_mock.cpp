@@ -50,6 +50,9 @@ int cm_gpu_circ_single_batch(cm_gpu_ctx *, int, uint32_t, const char *, const ch
                              const uint32_t *, const uint32_t *, const uint32_t *, int, int, uint32_t, uint32_t *, uint32_t *, uint8_t *, cm_circ_mate *,
                              cm_circ_mate *, cm_circ_mate *, int32_t *, cm_circ_res *, cm_circ_mate *, cm_circ_mate *, cm_circ_mate *, int32_t *,
                              cm_circ_res *) { return CM_ERR_STATE; }
+int cm_gpu_circ_double_batch(cm_gpu_ctx *, int, uint32_t, const char *, const char *, uint32_t, const uint16_t *, const uint16_t *, const cm_mread *,
+                             const uint32_t *, const uint32_t *, const uint32_t *, int, int, uint32_t, uint32_t *, uint32_t *, uint8_t *, cm_circ_mate *,
+                             cm_circ_mate *, cm_circ_mate *, cm_circ_mate *, int32_t *, cm_circ_res *, int32_t *, cm_circ_res *) { return CM_ERR_STATE; }
 int cm_gpu_host_alloc(size_t bytes, void **out) { *out = malloc(bytes ? bytes : 1); return *out ? CM_OK : CM_ERR_ALLOC; }
 int cm_gpu_host_free(void *p) { free(p); return CM_OK; }
 

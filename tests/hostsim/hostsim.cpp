@@ -462,6 +462,56 @@ static int hs_eng_check(void *self, int contig, uint32_t n, const char *rem, con
                                    r1[i], r2[i], pm[i], cr[i], sw + i);
     return 0;
 }
+static int hs_eng_dbl(void *self, int contig, uint32_t n, const char *r1seq, const char *r2seq, uint32_t stride, cm_circ_mate *r1, cm_circ_mate *r2,
+                      const uint32_t *qs1, const uint32_t *qe1, const uint32_t *qs2, const uint32_t *qe2, uint32_t F, const uint32_t *clen1,
+                      const uint32_t *rpos1, const int32_t *qpos1, const uint32_t *clen2, const uint32_t *rpos2, const int32_t *qpos2, int ws,
+                      cm_circ_mate *p1, cm_circ_mate *p2, int32_t *code) {
+    HsCtx *c = ((HsCircEngine *) self)->c;
+    DevView v = make_view(c, contig);
+    v.p.kmer = ws;
+    std::vector<FragDev> f1(F), f2(F);
+    for (uint32_t i = 0; i < n; i++) {
+        for (uint32_t f = 0; f < F; f++) {
+            f1[f] = FragDev{rpos1[(size_t) i * F + f], qpos1[(size_t) i * F + f]};
+            f2[f] = FragDev{rpos2[(size_t) i * F + f], qpos2[(size_t) i * F + f]};
+        }
+        ChainView c1, c2;
+        c1.frags = f1.data(); c1.chain_len = clen1[i]; c1.aux = nullptr; c1.spec = nullptr;
+        c2.frags = f2.data(); c2.chain_len = clen2[i]; c2.aux = nullptr; c2.spec = nullptr;
+        code[i] = cm_circ_double_row(v, r1[i], r2[i], qs1[i], qe1[i], qs2[i], qe2[i], (const uint8_t *) r1seq + (size_t) i * stride,
+                                     (const uint8_t *) r2seq + (size_t) i * stride, c1, c2, p1[i], p2[i]);
+    }
+    return 0;
+}
+static int hs_eng_check4(void *self, int contig, uint32_t n, const char *r1seq, const char *r2seq, uint32_t stride, const int32_t *l1, const int32_t *l2,
+                         const cm_circ_mate *r1, const cm_circ_mate *r2, const cm_circ_mate *p1, const cm_circ_mate *p2, int ws, int32_t *ret,
+                         cm_circ_res *cr) {
+    HsCtx *c = ((HsCircEngine *) self)->c;
+    DevView v = make_view(c, contig);
+    v.p.kmer = ws;
+    for (uint32_t i = 0; i < n; i++)
+        ret[i] = cm_circ_check4_row(v, (const uint8_t *) r1seq + (size_t) i * stride, l1[i], (const uint8_t *) r2seq + (size_t) i * stride, l2[i], nullptr, 0,
+                                    r1[i], r2[i], p1[i], p2[i], cr[i]);
+    return 0;
+}
+// call_circ_double_split for a batch: -> number of events (<= cap written), or < 0
+int hs_circ_double(HsCtx *c, int contig_id, const uint32_t *circ_pos, const uint32_t *circ_off, uint32_t n, const char *seqs1, const char *seqs2,
+                   uint32_t stride, const uint16_t *len1, const uint16_t *len2, const cm_mread *mr, const uint32_t *gene_off, const uint32_t *gene_start,
+                   const uint32_t *gene_end, int ws, int step, uint32_t cap, uint32_t *ev_pair, uint8_t *ev_kind, cm_circ_mate *ev_r1, cm_circ_mate *ev_r2,
+                   cm_circ_mate *ev_p1, cm_circ_mate *ev_p2, int32_t *ev_ret, cm_circ_res *ev_cr, int32_t *push_type, cm_circ_res *push_cr) {
+    HsCircEngine he{c, circ_pos, circ_off};
+    CircEngine E{&he, contig_id, hs_eng_chain, hs_eng_exact, hs_eng_check, hs_eng_dbl, hs_eng_check4};
+    CircSingleIn in{n, seqs1, seqs2, stride, len1, len2, mr, gene_off, gene_start, gene_end, ws, step, c->p.max_read_len, c->p.max_chain_len, 4};
+    std::vector<CircEvent> ev;
+    int r = circ_orch_double(E, in, ev, push_type, push_cr);
+    if (r != 0) return r < 0 ? r : -r;
+    for (size_t k = 0; k < ev.size() && k < cap; k++) {
+        ev_pair[k] = ev[k].pair; ev_kind[k] = ev[k].kind; ev_r1[k] = ev[k].r1; ev_r2[k] = ev[k].r2; ev_p1[k] = ev[k].p1; ev_p2[k] = ev[k].p2;
+        ev_ret[k] = ev[k].ret; ev_cr[k] = ev[k].cr;
+    }
+    return (int) ev.size();
+}
+
 // -> number of attempts (<= cap written), or < 0
 int hs_circ_single(HsCtx *c, int contig_id, const uint32_t *circ_pos, const uint32_t *circ_off, uint32_t n, const char *seqs1, const char *seqs2,
                    uint32_t stride, const uint16_t *len1, const uint16_t *len2, const cm_mread *mr, const uint32_t *gene_off, const uint32_t *gene_start,
@@ -470,7 +520,7 @@ int hs_circ_single(HsCtx *c, int contig_id, const uint32_t *circ_pos, const uint
                    cm_circ_mate *out_pm, int32_t *best_type, cm_circ_res *best_cr) {
     HsCircEngine he{c, circ_pos, circ_off};
     CircEngine E{&he, contig_id, hs_eng_chain, hs_eng_exact, hs_eng_check};
-    CircSingleIn in{n, seqs1, seqs2, stride, len1, len2, mr, gene_off, gene_start, gene_end, ws, step, c->p.max_read_len, c->p.max_chain_len};
+    CircSingleIn in{n, seqs1, seqs2, stride, len1, len2, mr, gene_off, gene_start, gene_end, ws, step, c->p.max_read_len, c->p.max_chain_len, 4};
     std::vector<CircAttempt> att;
     int r = circ_orch_single(E, in, att, best_type, best_cr);
     if (r != 0) return r < 0 ? r : -r;

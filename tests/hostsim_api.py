@@ -214,6 +214,33 @@ class HostSim:
         assert r == 0
         return out
 
+    def circ_double(self, contig_id, genome_ascii, s1, s2, l1, l2, mr_con, gene_cnt, gene_se, window_size=8, step=3, cap=50000):
+        """call_circ_double_split for a batch (csrc/cm_circ_orch.h: circ_orch_double) over the host build of the device functions."""
+        from circminer_b200.api import CIRC_MATE_DTYPE, CIRC_RES_DTYPE
+        pos, off = self._circ_index(genome_ascii, window_size)
+        a1, a2 = np.ascontiguousarray(s1, np.uint8), np.ascontiguousarray(s2, np.uint8)
+        n, stride = a1.shape
+        l1, l2 = np.ascontiguousarray(l1, np.uint16), np.ascontiguousarray(l2, np.uint16)
+        mr = np.ascontiguousarray(mr_con)
+        gene_cnt = np.asarray(gene_cnt, np.int64)
+        goff = np.zeros(n + 1, np.uint32)
+        goff[1:] = np.cumsum(gene_cnt)
+        sel = np.arange(gene_se.shape[1])[None, :] < gene_cnt[:, None]
+        gs = np.ascontiguousarray(gene_se[:, :, 0][sel], np.uint32)
+        ge = np.ascontiguousarray(gene_se[:, :, 1][sel], np.uint32)
+        if len(gs) == 0:
+            gs, ge = np.zeros(1, np.uint32), np.zeros(1, np.uint32)
+        ev = dict(pair=np.zeros(cap, np.uint32), kind=np.zeros(cap, np.uint8), r1=np.zeros(cap, CIRC_MATE_DTYPE), r2=np.zeros(cap, CIRC_MATE_DTYPE),
+                  p1=np.zeros(cap, CIRC_MATE_DTYPE), p2=np.zeros(cap, CIRC_MATE_DTYPE), ret=np.zeros(cap, np.int32), cr=np.zeros(cap, CIRC_RES_DTYPE))
+        push_type, push_cr = np.zeros(n, np.int32), np.zeros(n, CIRC_RES_DTYPE)
+        k = self.lib.hs_circ_double(self.ctx, contig_id, _vp(pos), _vp(off), C.c_uint32(n), _vp(a1), _vp(a2), C.c_uint32(stride), _vp(l1), _vp(l2),
+                                    _vp(mr), _vp(goff), _vp(gs), _vp(ge), window_size, step, C.c_uint32(cap),
+                                    *[_vp(ev[x]) for x in ("pair", "kind", "r1", "r2", "p1", "p2", "ret", "cr")], _vp(push_type), _vp(push_cr))
+        assert 0 <= k <= cap, k
+        out = {x: v[:k] for x, v in ev.items()}
+        out["push_type"], out["push_cr"] = push_type, push_cr
+        return out
+
     def process_read(self, contig_id, seqs1, seqs2, mreads, lens1=None, lens2=None):
         a1, l1 = _rows(seqs1, lens1)
         a2, l2 = _rows(seqs2, lens2)

@@ -237,6 +237,8 @@ def _single_split(tmp_path, make_engine, run, pairs):
         assert (real["n_types"] == cnt).all()
         for i in np.nonzero(cnt)[0]:
             assert (real["types"][i, :cnt[i]] == rec["ret"][off[i]:off[i + 1]]).all(), i
+        rec["mr_con"] = rec["mr_con"].copy()
+        rec["mr_con"]["type"][rec["mr_con"]["type"] == 4] = -1   # the entry takes CHI2BSJ pairs as well; this test is about the CHIBSJ ones
         got = run(eng, c, w, lens, rec)
         assert len(got["ret"]) == len(rec["ret"]), (len(got["ret"]), len(rec["ret"]))
         for k in ("call_pair", "r1_partial", "ret", "cr", "in_r1", "in_r2", "in_pm", "out_r1", "out_r2", "out_pm"):
@@ -279,4 +281,85 @@ def test_gpu_equals_call_circ_single_split(tmp_path):
         return m
     m = _single_split(tmp_path, make, lambda m, c, w, lens, rec: m.circ_single(c, w["s1"], w["s2"], lens, lens, rec["mr_con"], rec["gene_cnt"],
                                                                                rec["gene_se"]), 20000)
+    m.close()
+
+
+# ---- the double-split path ------------------------------------------------------------------------------------------------------
+def _mate5(m, sh):
+    return "%u\t%u\t%d\t%d\t%d\t" % (int(m["spos"]) - sh, int(m["epos"]) - sh, int(m["qspos"]), int(m["matched_len"]), int(m["dir"]))
+
+
+def _double_split(tmp_path, make_engine, single, double, pairs):
+    """call_circ_double_split for a batch against the UNMODIFIED ProcessCirc::call_circ on every CHI2BSJ pair of T1: the text it writes
+    to candidates.pam (print_split_mapping lines of its own four-mate attempts and of the call_circ_single_split calls it makes on
+    the same pair, in order, byte for byte) and everything it pushes to circ_res."""
+    from circminer_b200 import workload
+    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000, n_pairs=pairs)
+    dump = live_dump(str(tmp_path / "cs.npz"), workload="T1", contig_size=3_500_000, pairs=pairs, circ_single=True, no_stage_dumps=True)
+    eng = make_engine(w)
+    n, L = w["s1"].shape
+    lens = np.full(n, L, np.uint16)
+    names = [str(x) for x in dump["chr_names"]]
+    n_pairs = n_kind1 = n_single_calls = 0
+    for c in range(int(dump["n_contigs"])):
+        rec = {k[len(f"c{c}_circs_"):]: dump[k] for k in dump.files if k.startswith(f"c{c}_circs_")}
+        real = {k[len(f"c{c}_circreal2_"):]: dump[k] for k in dump.files if k.startswith(f"c{c}_circreal2_")}
+        idx = np.nonzero(rec["mr_con"]["type"] == 4)[0]
+        args = (w["s1"][idx], w["s2"][idx], lens[idx], lens[idx], rec["mr_con"][idx], rec["gene_cnt"][idx], rec["gene_se"][idx])
+        ev = double(eng, c, w, *args)
+        sg = single(eng, c, w, *args)
+        shift = (rec["mr_con"]["spos_r1"].astype(np.int64) - rec["mr_chr"]["spos_r1"].astype(np.int64))[idx]
+        s_off = np.concatenate([[0], np.cumsum(np.bincount(sg["call_pair"], minlength=len(idx)))])
+        e_off = np.concatenate([[0], np.cumsum(np.bincount(ev["pair"], minlength=len(idx)))])
+        for k, i in enumerate(idx):
+            sh = int(shift[k])
+            s_text = "".join("r\t%s\t" % names[c] + _mate5(sg["out_pm"][a]["m"], sh) + _mate5(sg["out_r1"][a]["m"], sh) + _mate5(sg["out_r2"][a]["m"], sh)
+                             + "%d\n" % sg["ret"][a] for a in range(s_off[k], s_off[k + 1]))
+            bt = int(sg["best_type"][k])
+            s_push = [(bt, int(sg["best_cr"]["spos"][k]) - sh, int(sg["best_cr"]["epos"][k]) - sh)] if 20 <= bt <= 22 else []
+            text, pushes = "", []
+            for a in range(e_off[k], e_off[k + 1]):
+                if ev["kind"][a] == 0:
+                    text += s_text
+                    pushes += s_push
+                    n_single_calls += 1
+                else:
+                    text += ("r\t%s\t" % names[c] + _mate5(ev["p1"][a]["m"], sh) + _mate5(ev["p2"][a]["m"], sh) + _mate5(ev["r1"][a]["m"], sh)
+                             + _mate5(ev["r2"][a]["m"], sh) + "%d\n" % ev["ret"][a])
+                    n_kind1 += 1
+            if ev["push_type"][k] >= 20:
+                pushes.append((int(ev["push_type"][k]), int(ev["push_cr"]["spos"][k]) - sh, int(ev["push_cr"]["epos"][k]) - sh))
+            want = bytes(real["text"][int(real["text_off"][i]):int(real["text_off"][i + 1])]).decode()
+            assert text == want, f"contig {c} pair {i}: candidates.pam text differs\n got {text!r}\nwant {want!r}"
+            wp = [(int(real["push_type"][i][q]), int(real["push_spos"][i][q]), int(real["push_epos"][i][q])) for q in range(real["n_push"][i])]
+            assert pushes == wp, f"contig {c} pair {i}: circ_res pushes differ: {pushes} vs {wp}"
+            n_pairs += 1
+    assert n_pairs > 50 and n_kind1 > 20 and n_single_calls > 20, (n_pairs, n_kind1, n_single_calls)
+    return eng
+
+
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_host_build_equals_call_circ_double_split(tmp_path):
+    def make(w):
+        from circminer_b200.api import default_params
+        from hostsim_api import HostSim
+        hs = HostSim(default_params())
+        for c, seq in enumerate(w["contigs"]):
+            hs.build_contig(c, seq)
+            hs.load_annotation(c, w["flat"][c])
+        return hs
+    _double_split(tmp_path, make, lambda hs, c, w, *a: hs.circ_single(c, w["contigs"][c], *a), lambda hs, c, w, *a: hs.circ_double(c, w["contigs"][c], *a),
+                  20000)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_gpu_equals_call_circ_double_split(tmp_path):
+    def make(w):
+        from circminer_b200 import workload
+        from circminer_b200.api import Mapper, default_params
+        m = Mapper(default_params())
+        workload.load_into(m, w)
+        return m
+    m = _double_split(tmp_path, make, lambda m, c, w, *a: m.circ_single(c, *a), lambda m, c, w, *a: m.circ_double(c, *a), 20000)
     m.close()

@@ -56,8 +56,9 @@ def test_dropin_binary_outputs_are_byte_identical(tmp_path, scan, devices):
               extra=("-a", scan))
     # stage 2's single-split pairs went through the device (integration/gpu_circ_detect.cpp), not through the reference's loop
     import re
-    st2 = [(int(a), int(b)) for a, b in re.findall(r"stage 2, contig \d+: (\d+) single-split pairs of \d+ in one batch, (\d+) check_split_map", pg.stderr)]
-    assert st2 and sum(a for a, _ in st2) > 50 and sum(b for _, b in st2) > 20, pg.stderr[-1500:]
+    st2 = [tuple(int(x) for x in m) for m in re.findall(r"stage 2, contig \d+: (\d+) single-split pairs of \d+ in one batch, (\d+) check_split_map "
+                                                        r"attempts; (\d+) double-split pairs, (\d+) events", pg.stderr)]
+    assert st2 and sum(a for a, _, _, _ in st2) > 50 and sum(b for _, b, _, _ in st2) > 20 and sum(c for _, _, c, _ in st2) > 5, pg.stderr[-1500:]
     ref_files = sorted(os.path.basename(f)[3:] for f in glob.glob(ref_out + "*") if os.path.isfile(f))
     gpu_files = sorted(os.path.basename(f)[3:] for f in glob.glob(gpu_out + "*") if os.path.isfile(f))
     assert ref_files == gpu_files and any(f.endswith("circ_report") for f in ref_files), (ref_files, gpu_files)
