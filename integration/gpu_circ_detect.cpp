@@ -48,6 +48,7 @@ struct Pair {                 // one pair of the sorted remain files
 };
 
 double g_t_batch = 0, g_t_ref_pairs = 0, g_t_write = 0, g_t_load = 0;
+bool g_text_ready = false;    // genome_seeder holds the current contig as characters
 void die2(cm_gpu_ctx *ctx, const char *what) {
     fprintf(stderr, "circminer_gpu: %s failed: %s\n", what, cm_gpu_last_error(ctx));
     exit(1);
@@ -236,6 +237,10 @@ void process_contig(ProcessCirc &pc, std::vector<Pair> &P) {
             r1.seq_len = (uint32_t) p.seq1.size(); r2.seq_len = (uint32_t) p.seq2.size();
             *r1.mr = p.mr;
             *r2.mr = p.mr;
+            if (!g_text_ready && (p.mr.type == CHIBSJ || p.mr.type == CHI2BSJ)) {   // call_circ does nothing for other types
+                genome_seeder.pac2char_whole_contig();
+                g_text_ready = true;
+            }
             pc.call_circ(&r1, &r2);
             g_t_ref_pairs += get_real_time() - t_p0;
         }
@@ -291,7 +296,13 @@ void ProcessCirc::cm_shim_do_process(void) {
         if (group.empty()) return;
         const double t_l0 = get_real_time();
         while (pre_contig != group_contig) {      // :315-318
-            load_genome();
+            // load_genome (:1659-1683) without its last step: the contig's text as characters (pac2char_whole_contig, about a
+            // second per Gbp) is only needed by the reference's own per-pair code, and is made when a pair goes there
+            double tmp;
+            loadCompressedRefGenome(&tmp);
+            pre_contig = atoi(getRefGenomeName()) - 1;
+            contigNum = pre_contig;
+            g_text_ready = false;
             refresh_hash_table_list();
         }
         g_t_load += get_real_time() - t_l0;

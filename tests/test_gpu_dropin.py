@@ -102,3 +102,30 @@ def test_dropin_annotation_cache_file(tmp_path):
         assert filecmp.cmp(str(tmp_path / "a") + suffix, str(tmp_path / "b") + suffix, shallow=False), suffix
     p3 = _run(GPU, w, str(tmp_path / "c"), env=env, extra=("-l", "200"))
     assert "annotation of contig 0 from" not in p3.stderr and any(f.endswith(".l200") for f in os.listdir(cache))
+
+
+@pytest.mark.skipif(not (has_ref() and os.path.exists(GPU)), reason="oracle/_ref/circminer_gpu not built")
+def test_dropin_stage2_switches(tmp_path):
+    """Stage 2 of the drop-in three ways -- both per-read paths on the device (default), the double-split pairs through the
+    reference's call_circ (CM_GPU_STAGE2_DOUBLE=0: the contig text is unpacked lazily for them), the reference's whole do_process
+    (CM_GPU_STAGE2=0) -- and the reference binary: candidates.pam and circ_report are the same bytes every time."""
+    from circminer_b200 import workload
+    d = str(tmp_path / "t1")
+    w = workload.prepare("T1", d, contig_size=3_500_000, write_reads=True)
+    subprocess.run([sys.executable, "-c",
+                    "import sys; sys.path.insert(0, %r)\n"
+                    "from oracle.refharness import RefHarness, default_params\n"
+                    "RefHarness(default_params()).build_index(%r, contig_size=3500000)" % (ROOT, w["fa"])],
+                   check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=900)
+    outs = {"ref": str(tmp_path / "ref")}
+    _run(REF, w, outs["ref"])
+    for tag, env in (("dev", {}), ("dbl0", {"CM_GPU_STAGE2_DOUBLE": "0"}), ("st0", {"CM_GPU_STAGE2": "0"})):
+        outs[tag] = str(tmp_path / tag)
+        p = _run(GPU, w, outs[tag], env=dict(env, CM_GPU_VERBOSE="1"))
+        assert ("stage 2, contig" in p.stderr) == (tag != "st0")
+        if tag == "dbl0":
+            assert "0 double-split pairs" in p.stderr
+    for tag in ("dev", "dbl0", "st0"):
+        for suffix in (".candidates.pam", ".circ_report"):
+            assert filecmp.cmp(outs["ref"] + suffix, outs[tag] + suffix, shallow=False), (tag, suffix)
+    assert os.path.getsize(outs["ref"] + ".candidates.pam") > 10000
