@@ -353,6 +353,21 @@ class Mapper:
         self._chk(r, "cm_gpu_circ_check_batch")
         return out
 
+    def circ_check4(self, contig_id, rec: dict, window_size=8) -> dict:
+        """ProcessCirc::check_split_map (four mates) per row (src/process_circ.cpp:922; cm_gpu_circ_check4_batch).  rec: r1_rows, r2_rows,
+        l1, l2, fullmap_sel, r1_1, r2_1, r1_2, r2_2 -> ret, cr."""
+        a, b = np.ascontiguousarray(rec["r1_rows"], np.uint8), np.ascontiguousarray(rec["r2_rows"], np.uint8)
+        n = a.shape[0]
+        l1, l2 = np.ascontiguousarray(rec["l1"], np.int32), np.ascontiguousarray(rec["l2"], np.int32)
+        fs = np.ascontiguousarray(rec["fullmap_sel"], np.uint8)
+        m = [np.ascontiguousarray(np.array(rec[k], CIRC_MATE_DTYPE)) for k in ("r1_1", "r2_1", "r1_2", "r2_2")]
+        out = dict(ret=np.zeros(n, np.int32), cr=np.zeros(n, CIRC_RES_DTYPE))
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        r = self.lib.cm_gpu_circ_check4_batch(self.ctx, contig_id, C.c_uint32(n), vp(a), vp(b), C.c_uint32(a.shape[1] if n else 0), vp(l1), vp(l2), vp(fs),
+                                              *[vp(x) for x in m], window_size, vp(out["ret"]), vp(out["cr"]))
+        self._chk(r, "cm_gpu_circ_check4_batch")
+        return out
+
     def circ_single(self, contig_id, s1, s2, l1, l2, mr_con, gene_cnt, gene_se, window_size=8, step=3, cap=20000) -> dict:
         """ProcessCirc::call_circ_single_split for a batch (src/process_circ.cpp:360; cm_gpu_circ_single_batch).  mr_con: MatchedReads
         with contig coordinates; gene_cnt[n], gene_se[n][G][2]: the genes get_gene_overlap(mm_r1.spos) lists for each pair."""

@@ -618,12 +618,14 @@ __global__ void __launch_bounds__(128) k_circ_double(const __grid_constant__ Dev
 }
 __global__ void __launch_bounds__(64) k_circ_check4(const __grid_constant__ DevView v, uint32_t n, const uint8_t *__restrict__ r1seq,
                                                     const uint8_t *__restrict__ r2seq, uint32_t stride, const int32_t *__restrict__ l1,
-                                                    const int32_t *__restrict__ l2, const cm_circ_mate *__restrict__ m, int32_t *__restrict__ ret,
-                                                    cm_circ_res *cr) {
+                                                    const int32_t *__restrict__ l2, const uint8_t *__restrict__ fullmap_sel,
+                                                    const cm_circ_mate *__restrict__ m, int32_t *__restrict__ ret, cm_circ_res *cr) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    ret[i] = cm_circ_check4_row(v, r1seq + (size_t) i * stride, l1[i], r2seq + (size_t) i * stride, l2[i], nullptr, 0, m[i], m[n + i], m[2 * (size_t) n + i],
-                                m[3 * (size_t) n + i], cr[i]);
+    const uint8_t *a = r1seq + (size_t) i * stride, *b = r2seq + (size_t) i * stride;
+    const int sel = fullmap_sel ? fullmap_sel[i] : 0;   // what ProcessCirc::fullmap_seq holds: nothing, R1 or R2
+    ret[i] = cm_circ_check4_row(v, a, l1[i], b, l2[i], sel == 1 ? a : sel == 2 ? b : nullptr, sel == 1 ? l1[i] : sel == 2 ? l2[i] : 0, m[i], m[n + i],
+                                m[2 * (size_t) n + i], m[3 * (size_t) n + i], cr[i]);
 }
 
 #define CIRC_TRY(x) do { if ((r = (x)) != CM_OK) { cleanup(); return r; } } while (0)
@@ -679,10 +681,9 @@ static int gpu_eng_dbl(void *self, int contig, uint32_t n, const char *r1seq, co
     cleanup();
     return CM_OK;
 }
-static int gpu_eng_check4(void *self, int contig, uint32_t n, const char *r1seq, const char *r2seq, uint32_t stride, const int32_t *l1, const int32_t *l2,
-                          const cm_circ_mate *r1, const cm_circ_mate *r2, const cm_circ_mate *p1, const cm_circ_mate *p2, int ws, int32_t *ret,
-                          cm_circ_res *cr) {
-    cm_gpu_ctx *ctx = (cm_gpu_ctx *) self;
+static int circ_check4_impl(cm_gpu_ctx *ctx, int contig, uint32_t n, const char *r1seq, const char *r2seq, uint32_t stride, const int32_t *l1,
+                            const int32_t *l2, const uint8_t *fullmap_sel, const cm_circ_mate *r1, const cm_circ_mate *r2, const cm_circ_mate *p1,
+                            const cm_circ_mate *p2, int ws, int32_t *ret, cm_circ_res *cr) {
     cudaSetDevice(ctx->device);
     DevView v;
     int r = make_view(ctx, contig, true, v);
@@ -702,13 +703,18 @@ static int gpu_eng_check4(void *self, int contig, uint32_t n, const char *r1seq,
     CIRC_TRY(dev_alloc(ctx, tmp, &d_ret, (size_t) n));
     CIRC_TRY(dev_alloc(ctx, tmp, &d_m, 4 * (size_t) n));
     CIRC_TRY(dev_alloc(ctx, tmp, &d_cr, (size_t) n));
+    uint8_t *d_sel = nullptr;
+    if (fullmap_sel) {
+        CIRC_TRY(dev_alloc(ctx, tmp, &d_sel, (size_t) n));
+        CIRC_CUDA(cudaMemcpyAsync(d_sel, fullmap_sel, (size_t) n, cudaMemcpyHostToDevice, st));
+    }
     CIRC_CUDA(cudaMemcpyAsync(d_s1, r1seq, bytes, cudaMemcpyHostToDevice, st));
     CIRC_CUDA(cudaMemcpyAsync(d_s2, r2seq, bytes, cudaMemcpyHostToDevice, st));
     CIRC_CUDA(cudaMemcpyAsync(d_l, l1, (size_t) n * 4, cudaMemcpyHostToDevice, st));
     CIRC_CUDA(cudaMemcpyAsync(d_l + n, l2, (size_t) n * 4, cudaMemcpyHostToDevice, st));
     const cm_circ_mate *src[4] = {r1, r2, p1, p2};
     for (int k = 0; k < 4; k++) CIRC_CUDA(cudaMemcpyAsync(d_m + (size_t) k * n, src[k], (size_t) n * sizeof(cm_circ_mate), cudaMemcpyHostToDevice, st));
-    k_circ_check4<<<grid_for(n, 64), 64, 0, st>>>(v, n, d_s1, d_s2, stride, d_l, d_l + n, d_m, d_ret, d_cr);
+    k_circ_check4<<<grid_for(n, 64), 64, 0, st>>>(v, n, d_s1, d_s2, stride, d_l, d_l + n, d_sel, d_m, d_ret, d_cr);
     ctx->launches++;
     CIRC_CUDA(cudaGetLastError());
     CIRC_CUDA(cudaMemcpyAsync(ret, d_ret, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
@@ -717,8 +723,27 @@ static int gpu_eng_check4(void *self, int contig, uint32_t n, const char *r1seq,
     cleanup();
     return CM_OK;
 }
+static int gpu_eng_check4(void *self, int contig, uint32_t n, const char *r1seq, const char *r2seq, uint32_t stride, const int32_t *l1, const int32_t *l2,
+                          const cm_circ_mate *r1, const cm_circ_mate *r2, const cm_circ_mate *p1, const cm_circ_mate *p2, int ws, int32_t *ret,
+                          cm_circ_res *cr) {
+    return circ_check4_impl((cm_gpu_ctx *) self, contig, n, r1seq, r2seq, stride, l1, l2, nullptr, r1, r2, p1, p2, ws, ret, cr);
+}
 #undef CIRC_TRY
 #undef CIRC_CUDA
+
+extern "C" int cm_gpu_circ_check4_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *r1_seq, const char *r2_seq, uint32_t stride,
+                                        const int32_t *r1_len, const int32_t *r2_len, const uint8_t *fullmap_sel, const cm_circ_mate *mm_r1_1,
+                                        const cm_circ_mate *mm_r2_1, const cm_circ_mate *mm_r1_2, const cm_circ_mate *mm_r2_2, int window_size,
+                                        int32_t *ret, cm_circ_res *cr) {
+    if (!ctx) return CM_ERR_ARG;
+    if (n == 0) return CM_OK;
+    if (!r1_seq || !r2_seq || !r1_len || !r2_len || !mm_r1_1 || !mm_r2_1 || !mm_r1_2 || !mm_r2_2 || !ret || !cr) return fail(ctx, CM_ERR_ARG, "null argument");
+    if (window_size < 4 || window_size > 12) return fail(ctx, CM_ERR_ARG, "window size outside 4..12");
+    for (uint32_t i = 0; i < n; i++)
+        if (r1_len[i] < 0 || r2_len[i] < 0 || (uint32_t) r1_len[i] > stride || (uint32_t) r2_len[i] > stride || (fullmap_sel && fullmap_sel[i] > 2))
+            return fail(ctx, CM_ERR_ARG, "row %u: read longer than the row, or fullmap_sel outside 0..2", i);
+    return circ_check4_impl(ctx, contig_id, n, r1_seq, r2_seq, stride, r1_len, r2_len, fullmap_sel, mm_r1_1, mm_r2_1, mm_r1_2, mm_r2_2, window_size, ret, cr);
+}
 
 extern "C" int cm_gpu_circ_double_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
                                         const uint16_t *len1, const uint16_t *len2, const cm_mread *mr, const uint32_t *gene_off,

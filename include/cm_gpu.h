@@ -315,6 +315,16 @@ int cm_gpu_circ_check_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const ch
                             const int32_t *remain_len, const int32_t *fullmap_len, const uint8_t *r1_partial, cm_circ_mate *mm_r1,
                             cm_circ_mate *mm_r2, cm_circ_mate *partial_mm, int window_size, int32_t *ret, cm_circ_res *cr);
 
+/* The four-mate ProcessCirc::check_split_map(mm_r1_1, mm_r2_1, mm_r1_2, mm_r2_2, cr) (src/process_circ.cpp:922-1133) on its own, one
+ * problem per row: the two oriented reads (ProcessCirc::r1_seq / r2_seq) and the four mates (read only).  Its two single-BSJ arms
+ * end in final_check, which reads ProcessCirc::fullmap_seq -- in the reference whatever an earlier call left there; here
+ * fullmap_sel[i] says what it holds (0 nothing, 1 = R1, 2 = R2; NULL = 0 for every row, as call_circ_double_split's own calls).
+ * ret / cr as cm_gpu_circ_check_batch. */
+int cm_gpu_circ_check4_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *r1_seq, const char *r2_seq, uint32_t stride,
+                             const int32_t *r1_len, const int32_t *r2_len, const uint8_t *fullmap_sel, const cm_circ_mate *mm_r1_1,
+                             const cm_circ_mate *mm_r2_1, const cm_circ_mate *mm_r1_2, const cm_circ_mate *mm_r2_2, int window_size,
+                             int32_t *ret, cm_circ_res *cr);
+
 /* find_exact_coord as cm_gpu_circ_exact_batch, with the two mates of the pair going in and out as ProcessCirc keeps them from one
  * chain of a read to the next (their cached look-ups survive a trim by final_check) and partial_mm coming back with the look-ups
  * find_exact_coord leaves on it -- what check_split_map is then called with. */

@@ -769,6 +769,31 @@ int cmref_circ_check(uint32_t n, const char *remain_seq, const char *fullmap_seq
     return 0;
 }
 
+// ProcessCirc::check_split_map(mm_r1_1, mm_r2_1, mm_r1_2, mm_r2_2, cr) (process_circ.cpp:922-1133) on given inputs: the two oriented
+// reads and the four mates; fullmap_sel picks what ProcessCirc::fullmap_seq holds when the call is made (0 none, 1 = R1, 2 = R2) --
+// in the reference it is whatever an earlier call left, here it is an argument so that the call is a function of its inputs.
+int cmref_circ_check4(uint32_t n, const char *r1seq, const char *r2seq, uint32_t stride, const int32_t *l1, const int32_t *l2,
+                      const uint8_t *fullmap_sel, const cm_circ_mate *r1_1, const cm_circ_mate *r2_1, const cm_circ_mate *r1_2,
+                      const cm_circ_mate *r2_2, int ws, int32_t *ret, cm_circ_res *cr_out) {
+    if (circ_pc(ws) != 0) return -1;
+    ProcessCirc &pc = *g_pc;
+    std::vector<char> s1(stride + 8), s2(stride + 8);
+    for (uint32_t i = 0; i < n; i++) {
+        memcpy(s1.data(), r1seq + (size_t) i * stride, stride); s1[l1[i]] = 0;
+        memcpy(s2.data(), r2seq + (size_t) i * stride, stride); s2[l2[i]] = 0;
+        pc.r1_seq = s1.data(); pc.r2_seq = s2.data(); pc.r1_seq_len = l1[i]; pc.r2_seq_len = l2[i];
+        pc.remain_seq = NULL; pc.remain_seq_len = 0;
+        pc.fullmap_seq = fullmap_sel[i] == 1 ? s1.data() : fullmap_sel[i] == 2 ? s2.data() : NULL;
+        pc.fullmap_seq_len = fullmap_sel[i] == 1 ? l1[i] : fullmap_sel[i] == 2 ? l2[i] : 0;
+        MatchedMate a, b, c, d;
+        circ_mate_import(&r1_1[i], a); circ_mate_import(&r2_1[i], b); circ_mate_import(&r1_2[i], c); circ_mate_import(&r2_2[i], d);
+        CircRes cr;
+        ret[i] = pc.check_split_map(a, b, c, d, cr);
+        circ_res_export(cr, !cr.start_bp_ref.empty(), &cr_out[i]);
+    }
+    return 0;
+}
+
 // The reference's own ProcessCirc::call_circ_single_split (process_circ.cpp:360-483), unmodified, on the same pairs: what it
 // writes to candidates.pam per check_split_map call (the type at the end of every line) and what it pushes to circ_res.  Pins
 // the control flow restated in cmref_circ_single.  types[i][type_cap], n_types[i]; pushed[i] = 1 with the pushed CircRes's

@@ -172,6 +172,44 @@ def circ_exact_problems(h, prob, res, seed, top=10):
     return out
 
 
+def circ_check4_problems(rec, seed):
+    """Four-mate check_split_map rows made from recorded three-mate calls: the fully mapped read (when it has no indel, intron or
+    soft clip inside) cut in two adjacent pieces at a random base, with the split read's two mates -- R1 regular and R2 back-spliced,
+    or the mirror image -- which is what the two single-BSJ arms of the four-mate function (process_circ.cpp:968-985) take; they merge
+    the pieces back and end in final_check / rescue_overlapping_bsj.  fullmap_sel names the cut read."""
+    from circminer_b200.api import CIRC_MATE_DTYPE
+    rng = np.random.default_rng(seed)
+    r1p = np.asarray(rec["r1_partial"]).astype(bool)
+    full = np.where(r1p, rec["in_r2"], rec["in_r1"]).astype(CIRC_MATE_DTYPE)
+    part = np.where(r1p, rec["in_r1"], rec["in_r2"]).astype(CIRC_MATE_DTYPE)
+    pm = np.array(rec["in_pm"], CIRC_MATE_DTYPE)
+    fm = full["m"]
+    glen = fm["epos"].astype(np.int64) - fm["spos"] + 1
+    qlen = fm["qepos"].astype(np.int64) - fm["qspos"] + 1
+    idx = np.nonzero((glen == qlen) & (glen == fm["matched_len"]) & (glen >= 20))[0]
+    h = np.array([rng.integers(8, glen[i] - 8) for i in idx], np.uint32)
+    lo, hi = full[idx].copy(), full[idx].copy()
+    lo["m"]["epos"] = lo["m"]["spos"] + h - 1
+    lo["m"]["qepos"] = lo["m"]["qspos"] + h - 1
+    lo["m"]["matched_len"] = h
+    lo["m"]["right_ed"] = 0
+    lo["m"]["sclen_right"] = 0
+    hi["m"]["spos"] = hi["m"]["spos"] + h
+    hi["m"]["qspos"] = hi["m"]["qspos"] + h
+    hi["m"]["matched_len"] = hi["m"]["matched_len"] - h
+    hi["m"]["left_ed"] = 0
+    hi["m"]["middle_ed"] = 0
+    hi["m"]["sclen_left"] = 0
+    p = r1p[idx]
+    return dict(src=idx.astype(np.int32),
+                r1_rows=np.where(p[:, None], rec["remain_rows"][idx], rec["fullmap_rows"][idx]),
+                r2_rows=np.where(p[:, None], rec["fullmap_rows"][idx], rec["remain_rows"][idx]),
+                l1=np.where(p, rec["remain_len"][idx], rec["fullmap_len"][idx]).astype(np.int32),
+                l2=np.where(p, rec["fullmap_len"][idx], rec["remain_len"][idx]).astype(np.int32),
+                fullmap_sel=np.where(p, 2, 1).astype(np.uint8),
+                r1_1=np.where(p, part[idx], lo), r1_2=np.where(p, pm[idx], hi), r2_1=np.where(p, lo, part[idx]), r2_2=np.where(p, hi, pm[idx]))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", default="T0")
@@ -284,6 +322,14 @@ def main():
                     and (again["r2"] == rec["out_r2"]).all() and (again["pm"] == rec["out_pm"]).all()
                 if not same:
                     raise SystemExit("check_split_map on the recorded inputs does not reproduce the recorded call")
+                # the four-mate function on rows made from these calls (its single-BSJ arms, which the reads themselves rarely reach)
+                p4 = circ_check4_problems(rec, 6000 + c)
+                if len(p4["src"]):
+                    r4 = h.circ_check4(p4)
+                    for k, v in p4.items():
+                        out[f"c{c}_circ4_{k}"] = v
+                    out[f"c{c}_circ4_ret"] = r4["ret"]
+                    out[f"c{c}_circ4_cr"] = r4["cr"]
         if a.se:
             out[f"c{c}_se_state"] = h.process_se(s1, lens)
         mr, st = h.process_pe(s1, s2, lens, lens, mr)

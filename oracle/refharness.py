@@ -288,6 +288,22 @@ class RefHarness:
         assert r == 0, r
         return out
 
+    def circ_check4(self, rec: dict, ws: int = 8) -> dict:
+        """ProcessCirc::check_split_map on four mates (process_circ.cpp:922) on given inputs: r1_rows, r2_rows, l1, l2, fullmap_sel,
+        r1_1, r2_1, r1_2, r2_2 -> ret, cr."""
+        from circminer_b200.api import CIRC_MATE_DTYPE, CIRC_RES_DTYPE
+        a, b = np.ascontiguousarray(rec["r1_rows"], np.uint8), np.ascontiguousarray(rec["r2_rows"], np.uint8)
+        n = a.shape[0]
+        l1, l2 = np.ascontiguousarray(rec["l1"], np.int32), np.ascontiguousarray(rec["l2"], np.int32)
+        fs = np.ascontiguousarray(rec["fullmap_sel"], np.uint8)
+        m = [np.ascontiguousarray(np.array(rec[k], CIRC_MATE_DTYPE)) for k in ("r1_1", "r2_1", "r1_2", "r2_2")]
+        out = dict(ret=np.zeros(n, np.int32), cr=np.zeros(n, CIRC_RES_DTYPE))
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        r = self.lib.cmref_circ_check4(C.c_uint32(n), vp(a), vp(b), C.c_uint32(a.shape[1]), vp(l1), vp(l2), vp(fs), *[vp(x) for x in m], ws,
+                                       vp(out["ret"]), vp(out["cr"]))
+        assert r == 0, r
+        return out
+
     def seed(self, seqs: np.ndarray, lens: np.ndarray) -> dict:
         n, S = len(lens), self.S
         out = dict(qpos=np.zeros((n, S), np.int32), frag_count=np.zeros((n, S), np.uint32),

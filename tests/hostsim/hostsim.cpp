@@ -494,6 +494,20 @@ static int hs_eng_check4(void *self, int contig, uint32_t n, const char *r1seq, 
                                     r1[i], r2[i], p1[i], p2[i], cr[i]);
     return 0;
 }
+// check_split_map on four mates as a function of its arguments; fullmap_sel: 0 none, 1 = R1, 2 = R2 (see cmref_circ_check4)
+int hs_circ_check4(HsCtx *c, int contig_id, uint32_t n, const char *r1seq, const char *r2seq, uint32_t stride, const int32_t *l1, const int32_t *l2,
+                   const uint8_t *fullmap_sel, const cm_circ_mate *r1_1, const cm_circ_mate *r2_1, const cm_circ_mate *r1_2, const cm_circ_mate *r2_2,
+                   int ws, int32_t *ret, cm_circ_res *cr) {
+    DevView v = make_view(c, contig_id);
+    v.p.kmer = ws;
+    for (uint32_t i = 0; i < n; i++) {
+        const uint8_t *a = (const uint8_t *) r1seq + (size_t) i * stride, *b = (const uint8_t *) r2seq + (size_t) i * stride;
+        const uint8_t *f = fullmap_sel[i] == 1 ? a : fullmap_sel[i] == 2 ? b : nullptr;
+        const int fl = fullmap_sel[i] == 1 ? l1[i] : fullmap_sel[i] == 2 ? l2[i] : 0;
+        ret[i] = cm_circ_check4_row(v, a, l1[i], b, l2[i], f, fl, r1_1[i], r2_1[i], r1_2[i], r2_2[i], cr[i]);
+    }
+    return 0;
+}
 // call_circ_double_split for a batch: -> number of events (<= cap written), or < 0
 int hs_circ_double(HsCtx *c, int contig_id, const uint32_t *circ_pos, const uint32_t *circ_off, uint32_t n, const char *seqs1, const char *seqs2,
                    uint32_t stride, const uint16_t *len1, const uint16_t *len2, const cm_mread *mr, const uint32_t *gene_off, const uint32_t *gene_start,

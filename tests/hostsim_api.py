@@ -214,6 +214,22 @@ class HostSim:
         assert r == 0
         return out
 
+    def circ_check4(self, contig_id, rec: dict, window_size=8) -> dict:
+        """ProcessCirc::check_split_map (four mates) per row (src/process_circ.cpp:922; cm_circ_check4_row, the function k_circ_check4 runs).
+        rec as RefHarness.circ_check4."""
+        from circminer_b200.api import CIRC_MATE_DTYPE, CIRC_RES_DTYPE
+        a, b = np.ascontiguousarray(rec["r1_rows"], np.uint8), np.ascontiguousarray(rec["r2_rows"], np.uint8)
+        n = a.shape[0]
+        l1, l2 = np.ascontiguousarray(rec["l1"], np.int32), np.ascontiguousarray(rec["l2"], np.int32)
+        fs = np.ascontiguousarray(rec["fullmap_sel"], np.uint8)
+        m = [np.ascontiguousarray(np.array(rec[k], CIRC_MATE_DTYPE)) for k in ("r1_1", "r2_1", "r1_2", "r2_2")]
+        out = dict(ret=np.zeros(n, np.int32), cr=np.zeros(n, CIRC_RES_DTYPE))
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        r = self.lib.hs_circ_check4(self.ctx, contig_id, C.c_uint32(n), vp(a), vp(b), C.c_uint32(a.shape[1] if n else 0), vp(l1), vp(l2), vp(fs),
+                                    *[vp(x) for x in m], window_size, vp(out["ret"]), vp(out["cr"]))
+        assert r == 0
+        return out
+
     def circ_double(self, contig_id, genome_ascii, s1, s2, l1, l2, mr_con, gene_cnt, gene_se, window_size=8, step=3, cap=50000):
         """call_circ_double_split for a batch (csrc/cm_circ_orch.h: circ_orch_double) over the host build of the device functions."""
         from circminer_b200.api import CIRC_MATE_DTYPE, CIRC_RES_DTYPE

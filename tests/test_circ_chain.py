@@ -164,7 +164,7 @@ def _check_split_map(tmp_path, make_engine, pairs):
     dump = live_dump(str(tmp_path / "cs.npz"), workload="T1", contig_size=3_500_000, pairs=pairs, circ_single=True, no_stage_dumps=True)
     eng = make_engine(w)
     seen = set()
-    total = 0
+    total = total4 = 0
     for c in range(int(dump["n_contigs"])):
         rec = {k[len(f"c{c}_circs_"):]: dump[k] for k in dump.files if k.startswith(f"c{c}_circs_")}
         n = len(rec["ret"])
@@ -178,7 +178,16 @@ def _check_split_map(tmp_path, make_engine, pairs):
             bad = np.nonzero(got[nm] != rec[k])[0]
             assert len(bad) == 0, f"contig {c} {nm}: {len(bad)} of {n} differ, first {bad[:3]}: {got[nm][bad[:1]]} vs {rec[k][bad[:1]]}"
         seen |= set(np.unique(rec["ret"]).tolist())
+        # the four-mate function on rows made from these calls (oracle/refdump.py: circ_check4_problems): one read cut in two regular
+        # pieces, the other back-spliced -- its two single-BSJ arms, which merge the pieces and end in final_check
+        r4 = {k[len(f"c{c}_circ4_"):]: dump[k] for k in dump.files if k.startswith(f"c{c}_circ4_")}
+        if r4:
+            got4 = eng.circ_check4(c, r4)
+            bad = np.nonzero((got4["ret"] != r4["ret"]) | (got4["cr"] != r4["cr"]))[0]
+            assert len(bad) == 0, f"contig {c}: four-mate check_split_map differs on {len(bad)} of {len(r4['ret'])} rows, first {bad[:5]}"
+            total4 += len(r4["ret"])
     assert total > 100 and {0, 20, 30} <= seen, (total, seen)   # FR, CR and UD calls
+    assert total4 > 50, total4
     return eng
 
 
@@ -196,8 +205,8 @@ def test_host_build_equals_check_split_map(tmp_path):
     import ctypes as C
     tr = (C.c_long * 16)()
     hs.lib.hs_circ_trace(tr)
-    # both arms of final_check ran; the rescue / four-mate paths are rare on this data (reported, not required)
-    assert tr[0] > 10 and tr[1] > 50, list(tr)
+    # both arms of final_check ran, and through the made-up four-mate rows its two single-BSJ arms (8, 9) and rescue_overlapping_bsj (3, 4)
+    assert tr[0] > 10 and tr[1] > 50 and tr[8] > 5 and tr[9] > 5 and tr[4] > 5, list(tr)
 
 
 @pytest.mark.gpu
