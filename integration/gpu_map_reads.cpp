@@ -679,6 +679,22 @@ cm_gpu_ctx *cm_shim_stage2_contig(int c) {
     return g_roots[0];
 }
 
+// mapping()'s loadHashTable(&tmpTime) (src/circminer.cpp:232), renamed by gpu_shim.h.  The drop-in builds its index on the device
+// from the 3-bit packed contig (ensure_round), so of an index-file record it needs the contig alone: the reference's own
+// loadCompressedRefGenome (src/mrsfast/HashTable.c, what stage 2's load_genome calls, src/process_circ.cpp:1668) reads the same
+// record, leaves the same globals (_ih_refGenName / Off / Len, _ih_crefGen) and the file at the next record, and seeks over the
+// k-mer table instead of reading 8 bytes per base into memory (or, with a compact index, re-deriving it with all threads).
+// CM_GPU_INDEX=upload, which converts the reference's own table, and CM_GPU_REF_TABLE=1 keep the full load.
+extern "C" int cm_shim_loadHashTable(double *load_time) {
+#ifdef CM_SHIM_KEEP_REF_TABLE
+    return loadHashTable(load_time);
+#else
+    const char *how = getenv("CM_GPU_INDEX"), *keep = getenv("CM_GPU_REF_TABLE");
+    if ((how && !strcmp(how, "upload")) || (keep && atoi(keep))) return loadHashTable(load_time);
+    return loadCompressedRefGenome(load_time);
+#endif
+}
+
 int cm_shim_pthread_create(pthread_t *t, const pthread_attr_t *a, void *(*)(void *), void *arg) {
     FilterArgs *fa = (FilterArgs *) arg;
     if (!pairedEnd) {

@@ -5,6 +5,7 @@
 // box without a GPU.  The stand-in answers cm_gpu_process_batch_pe with the reference's own FilterRead::process_read
 // (src/filter.cpp:124), one pair at a time, on the scratch of mapping thread 0; nothing here touches libcm_gpu.so.
 // Built by oracle/Makefile into oracle/_ref/circminer_feedtest; used by tests/test_host_feed.py.
+#define CM_SHIM_KEEP_REF_TABLE 1   // the stand-in below maps with the reference's own table
 #include "../../integration/gpu_map_reads.cpp"
 
 namespace {

@@ -58,3 +58,50 @@ def test_host_feed_outputs_are_byte_identical(dataset, tmp_path, scan, threads, 
         a, b = ref_out + suffix, feed_out + suffix
         assert filecmp.cmp(a, b, shallow=False), f"{suffix} differs ({os.path.getsize(a)} vs {os.path.getsize(b)} bytes)"
     assert os.path.getsize(ref_out + ".mapping.pam") > 10000
+
+
+_LOAD_CHECK = r"""
+import ctypes as C, sys, zlib
+sys.path.insert(0, %(root)r)
+from oracle.refharness import RefHarness, default_params
+h = RefHarness(default_params(), threads=2)
+h.build_index(%(fa)r, contig_size=3500000, compact=%(compact)r)
+h.open(%(fa)r, %(gtf)r, %(tmp)r)
+L = h.lib
+libc = C.CDLL(None)
+libc.ftell.argtypes = [C.c_void_p]; libc.ftell.restype = C.c_long
+g = lambda name, t: t.in_dll(L, name)
+index_file = (%(fa)r + ".packed.fa.index").encode()   # already open: initLoadingHashTableMeta rewinds it
+def state(flag):
+    n = g("_ih_crefGenLen", C.c_int).value
+    buf = C.string_at(g("_ih_crefGen", C.c_void_p).value, n * 8)
+    return (flag, C.string_at(g("_ih_refGenName", C.c_void_p).value), g("_ih_refGenOff", C.c_int).value, g("_ih_refGenLen", C.c_int).value,
+            zlib.crc32(buf), libc.ftell(g("_ih_fp", C.c_void_p).value))
+def walk(fn):
+    assert L.initLoadingHashTableMeta(index_file) == 1
+    out, t = [], C.c_double()
+    while True:
+        flag = fn(C.byref(t))
+        out.append(state(flag))
+        if not flag or len(out) > 50:
+            return out
+a = walk(L.loadHashTable)
+b = walk(L.loadCompressedRefGenome)
+print(len(a), a == b, g("loadFullHashTable", C.c_int).value)
+assert len(a) >= 2 and a == b, (a, b)
+"""
+
+
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("compact", [False, True])
+def test_genome_only_load_leaves_the_state_of_the_full_load(tmp_path, compact):
+    """The drop-in renames mapping()'s loadHashTable to the reference's own loadCompressedRefGenome (integration/gpu_shim.h,
+    cm_shim_loadHashTable): record by record of a full and of a compact index, both leave the same return value, contig name, offset,
+    length, packed contig and file position -- everything the drop-in reads after the call."""
+    from circminer_b200 import workload
+    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000, n_pairs=10, write_reads=True)
+    code = _LOAD_CHECK % dict(root=ROOT, fa=w["fa"], gtf=w["gtf"], tmp=str(tmp_path / "ref"), compact=compact)
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=900)
+    assert p.returncode == 0, (p.stdout + p.stderr)[-3000:]
+    n, same, full = p.stdout.split()[-3:]
+    assert int(n) >= 2 and same == "True" and int(full) == (0 if compact else 1), p.stdout[-500:]
