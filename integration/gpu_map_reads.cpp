@@ -695,6 +695,19 @@ extern "C" int cm_shim_loadHashTable(double *load_time) {
 #endif
 }
 
+// mapping()'s genome_seeder.pac2char_whole_contig() (src/circminer.cpp:244), renamed by gpu_shim.h (the member itself is in
+// gpu_shim_members.cpp): the contig as characters is what the reference's extension reads; the drop-in's rounds read the packed
+// contig on the device, so the unpacking is skipped unless the reference's table is kept as well.
+bool cm_shim_unpack_contig() {
+#ifdef CM_SHIM_KEEP_REF_TABLE
+    return genome_seeder.pac2char_whole_contig();
+#else
+    const char *how = getenv("CM_GPU_INDEX"), *keep = getenv("CM_GPU_REF_TABLE");
+    if ((how && !strcmp(how, "upload")) || (keep && atoi(keep))) return genome_seeder.pac2char_whole_contig();
+    return true;
+#endif
+}
+
 int cm_shim_pthread_create(pthread_t *t, const pthread_attr_t *a, void *(*)(void *), void *arg) {
     FilterArgs *fa = (FilterArgs *) arg;
     if (!pairedEnd) {

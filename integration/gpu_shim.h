@@ -8,7 +8,9 @@
  * (src/circminer.cpp:232) is renamed to cm_shim_loadHashTable (gpu_map_reads.cpp), which calls the reference's own
  * loadCompressedRefGenome -- the same index-file record with the k-mer table skipped, since the index is built on the device
  * (CM_GPU_REF_TABLE=1 keeps the reference's load).  The macro also renames the declaration in mrsfast/HashTable.h, which this
- * translation unit includes inside extern "C".  Everything else -- FASTQ parsing, PAM / remain-FASTQ writers, the round loop
+ * translation unit includes inside extern "C".  mapping()'s genome_seeder.pac2char_whole_contig() (:244, the contig as characters,
+ * which only the reference's own extension reads) is renamed to a member that gpu_shim_members.cpp defines and that skips the
+ * unpacking under the same switch.  Everything else -- FASTQ parsing, PAM / remain-FASTQ writers, the round loop
  * and the report of stage 2 -- is the reference's own code, unmodified. */
 #pragma once
 #include <pthread.h>
@@ -16,3 +18,4 @@ int cm_shim_pthread_create(pthread_t *t, const pthread_attr_t *a, void *(*fn)(vo
 #define pthread_create cm_shim_pthread_create
 #define do_process cm_shim_do_process
 #define loadHashTable cm_shim_loadHashTable
+#define pac2char_whole_contig cm_shim_pac2char_whole_contig

@@ -28,16 +28,22 @@ def run(binary, d, fq1, fq2, out, threads, env=None, extra=()):
     e = dict(os.environ, LC_ALL="C")
     e.update(env or {})
     t0 = time.time()
-    p = subprocess.run(cmd, capture_output=True, text=True, env=e)
+    p = subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=e)
+    timeline, lines = [], []
+    for ln in p.stdout:                       # every log line with the time it appeared at: where the wall time goes
+        lines.append(ln)
+        if len(timeline) < 400 and ln.strip():
+            timeline.append([round(time.time() - t0, 2), ln.rstrip()[:150]])
+    p.wait()
     wall = time.time() - t0
-    txt = p.stdout + p.stderr
+    txt = "".join(lines)
     if p.returncode != 0:
         raise SystemExit(f"{binary} failed:\n{txt[-2000:]}")
     rounds = [float(x) for x in re.findall(r"Completed round \S+ \(CPU time: [\d.]+s; Real time: ([\d.]+)s\)", txt)]
     phases = [ln for ln in txt.splitlines() if ln.startswith(("circminer_gpu:", "cm_gpu:"))]
     circ = re.search(r"CircRNA detection Completed! \(CPU time: [\d.]+s; Real time: ([\d.]+)s\)", txt)   # do_process (src/process_circ.cpp:325)
     sort = re.findall(r"Sorting remaining read mappings.*?\n.*?Completed! \(CPU time: [\d.]+s; Real time: ([\d.]+)s\)", txt, re.S)
-    return {"wall_s": wall, "round_s": rounds, "mapping_s": sum(rounds), "phases": phases,
+    return {"wall_s": wall, "round_s": rounds, "mapping_s": sum(rounds), "phases": phases, "timeline": timeline,
             "stage2_do_process_s": float(circ.group(1)) if circ else None, "stage2_sort_s": float(sort[0]) if sort else None}
 
 
