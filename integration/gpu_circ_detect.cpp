@@ -175,11 +175,17 @@ void process_contig(ProcessCirc &pc, std::vector<Pair> &P) {
     std::vector<cm_circ_res> push_cr(who2.size());
     uint32_t n_ev = 0;
     if (!who1.empty() || !who2.empty()) {
+        double tp[6];
+        tp[0] = get_real_time();
         cm_gpu_ctx *ctx = cm_shim_stage2_contig(contigNum);
+        tp[1] = get_real_time();
         in1.build(P, who1);
-        S1.run(pc, ctx, in1);
         in2.build(P, who2);
+        tp[2] = get_real_time();
+        S1.run(pc, ctx, in1);
+        tp[3] = get_real_time();
         S2.run(pc, ctx, in2);                                   // what call_circ_single_split gives on the double-split pairs
+        tp[4] = get_real_time();
         if (in2.n) {
             uint32_t cap = 8 * in2.n + 1024;
             for (int pass = 0; pass < 2; pass++) {
@@ -199,9 +205,12 @@ void process_contig(ProcessCirc &pc, std::vector<Pair> &P) {
             }
             ev_first[in2.n] = a;
         }
+        tp[5] = get_real_time();
         if (getenv("CM_GPU_VERBOSE"))
             fprintf(stderr, "circminer_gpu: stage 2, contig %d: %u single-split pairs of %zu in one batch, %u check_split_map attempts; %u double-split "
-                    "pairs, %u events\n", contigNum, in1.n, n_all, S1.n_att, in2.n, n_ev);
+                    "pairs, %u events; contig on the device %.3f s, gene lists %.3f s, single-split batch %.3f s, the same on the double-split pairs "
+                    "%.3f s, double-split batch %.3f s\n", contigNum, in1.n, n_all, S1.n_att, in2.n, n_ev, tp[1] - tp[0], tp[2] - tp[1], tp[3] - tp[2],
+                    tp[4] - tp[3], tp[5] - tp[4]);
     }
     g_t_batch += get_real_time() - t_b0;
     // file order
