@@ -228,7 +228,7 @@ static inline int circ_orch_single(const CircEngine &E, const CircSingleIn &in, 
             for (uint32_t u = 0; u < c; u++) {
                 const uint32_t t = csub[u], i = idx[sub[t]];
                 Pair &p = P[i];
-                if (cret[u] < 0) return -100;   // a fixed-size list of the device code overflowed
+                if (cret[u] < 0) { p.best = -2; p.going = false; continue; }   // a fixed-size list of the device code overflowed: the pair is the caller's
                 CircAttempt a;
                 a.pair = i; a.gene = g; a.chain = (uint32_t) j; a.r1_partial = p.r1_partial;
                 a.in_r1 = i1[u]; a.in_r2 = i2[u]; a.in_pm = ip[u];
@@ -397,10 +397,7 @@ static inline int circ_orch_double(const CircEngine &E, const CircSingleIn &in, 
             r = E.check4(E.self, E.contig, m, b1.data(), b2.data(), stride, l1.data(), l2.data(), m1.data(), m2.data(), q1.data(), q2.data(), ws, rr.data(),
                          cr.data());
             if (r != 0) return r;
-            for (uint32_t u = 0; u < m; u++) {
-                if (rr[u] < 0) return -100;
-                checked[sel[u]] = 1; cret[sel[u]] = rr[u]; ccr[sel[u]] = cr[u];
-            }
+            for (uint32_t u = 0; u < m; u++) { checked[sel[u]] = 1; cret[sel[u]] = rr[u]; ccr[sel[u]] = cr[u]; }   // rr < 0: a list overflowed
         }
     }
     // the function's own order and rules, pair by pair
@@ -422,6 +419,7 @@ static inline int circ_orch_double(const CircEngine &E, const CircSingleIn &in, 
             if (count[a] <= 0 || count[a + 1] <= 0) { single_here(); continue; }
             for (; t < nc && combos[t].pair == i && combos[t].gene == g; t++) {
                 if (returned || !checked[t]) continue;
+                if (cret[t] < 0) { push_type[i] = -2; returned = true; continue; }   // reached a row whose lists overflowed: the pair is the caller's
                 CircEvent e;
                 e.pair = i; e.kind = 1; e.r1 = d1[t]; e.r2 = d2[t]; e.p1 = dp1[t]; e.p2 = dp2[t]; e.ret = cret[t]; e.cr = ccr[t];
                 events.push_back(e);

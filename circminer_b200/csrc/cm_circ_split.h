@@ -23,8 +23,15 @@
 #define CM_NF 40
 #define CM_BPRES 5    // src/common.h:42
 #define CM_INDELTH 3  // src/common.h:45
+// Fixed sizes of per-thread lists.  A row that needs more comes back as -1, the pair as type -2 from the batch entries, and the caller
+// redoes that pair with the reference's code (integration/gpu_circ_detect.cpp does).  The host build of the tests overrides them to
+// make that path run.
+#ifndef CM_CIRC_TID_CAP
 #define CM_CIRC_TID_CAP 192    // (transcript, offset) pairs collected per side of a breakpoint
+#endif
+#ifndef CM_CIRC_JUNC_CAP
 #define CM_CIRC_JUNC_CAP 64
+#endif
 #define CM_CIRC_MAX_DEPTH 6
 
 // branch counters of the host build (tests report which paths their inputs reached); nothing on the device

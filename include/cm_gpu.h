@@ -341,7 +341,9 @@ int cm_gpu_circ_exact_mates_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, co
  * the type it returned and its CircRes: what print_split_mapping and the type column of candidates.pam are written from --
  * n_attempts (the first attempt_cap are stored; the att_* arrays may be NULL), and per pair best_type (what the function ends
  * with: 40 = nothing, 0 / 1 = FR / RF, 20..22 = the CircRes pushed to circ_res, in best_cr, contig coordinates; -1 = not a
- * candidate). */
+ * candidate; -2 = a check_split_map of this pair needed more than a fixed-size list of the device code holds (CM_CIRC_TID_CAP
+ * transcripts at one breakpoint, CM_CIRC_JUNC_CAP junctions): its attempts are not to be used and the caller redoes the pair with
+ * ProcessCirc::call_circ_single_split itself). */
 int cm_gpu_circ_single_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
                              const uint16_t *len1, const uint16_t *len2, const cm_mread *mr, const uint32_t *gene_off, const uint32_t *gene_start,
                              const uint32_t *gene_end, int window_size, int step, uint32_t attempt_cap, uint32_t *n_attempts, uint32_t *att_pair,
@@ -355,7 +357,8 @@ int cm_gpu_circ_single_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const c
  * end when nothing was pushed; what that call writes is cm_gpu_circ_single_batch's answer for the pair -- it accepts CHI2BSJ
  * pairs too -- and is the same every time), kind 1 = a four-mate check_split_map call with mm_r1, mm_r2, r1_partial_mm,
  * r2_partial_mm (what print_split_mapping prints), its type and CircRes.  push_type[i] = 20..22 when the function pushes its own
- * best_cr (push_cr[i], contig coordinates; con_shift from mm_r1.spos = mr.spos_r1), else -1. */
+ * best_cr (push_cr[i], contig coordinates; con_shift from mm_r1.spos = mr.spos_r1), -2 when a four-mate check_split_map the
+ * function reaches overflowed a fixed-size list (as best_type -2 above: the pair's events are not to be used), else -1. */
 int cm_gpu_circ_double_batch(cm_gpu_ctx *ctx, int contig_id, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
                              const uint16_t *len1, const uint16_t *len2, const cm_mread *mr, const uint32_t *gene_off, const uint32_t *gene_start,
                              const uint32_t *gene_end, int window_size, int step, uint32_t event_cap, uint32_t *n_events, uint32_t *ev_pair,

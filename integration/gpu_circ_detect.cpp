@@ -48,6 +48,7 @@ struct Pair {                 // one pair of the sorted remain files
 };
 
 double g_t_batch = 0, g_t_ref_pairs = 0, g_t_write = 0, g_t_load = 0;
+long g_n_redone = 0;          // pairs redone by the reference's call_circ because a device list overflowed
 bool g_text_ready = false;    // genome_seeder holds the current contig as characters
 void die2(cm_gpu_ctx *ctx, const char *what) {
     fprintf(stderr, "circminer_gpu: %s failed: %s\n", what, cm_gpu_last_error(ctx));
@@ -221,11 +222,24 @@ void process_contig(ProcessCirc &pc, std::vector<Pair> &P) {
     for (size_t i = 0; i < n_all; i++) {
         Pair &p = P[i];
         const double t_p0 = get_real_time();
+        // a pair whose classification overflowed a fixed-size list of the device code (type -2) goes through the reference's own
+        // call_circ below, like the pairs that were never sent to the device
+        bool on_device = false;
+        uint32_t k = 0;
         if (p.mr.type == CHIBSJ) {
-            S1.emit(pc, p, k1++);
-            g_t_write += get_real_time() - t_p0;
+            k = k1++;
+            on_device = S1.best[k] != -2;
         } else if (p.mr.type == CHI2BSJ && gpu_double) {
-            const uint32_t k = k2++;
+            k = k2++;
+            bool single_used = false;
+            for (uint32_t t = ev_first[k]; t < ev_first[k + 1]; t++) single_used |= ev_kind[t] == 0;
+            on_device = push_type[k] != -2 && !(single_used && S2.best[k] == -2);
+        }
+        if (!on_device && (p.mr.type == CHIBSJ || (p.mr.type == CHI2BSJ && gpu_double))) g_n_redone++;
+        if (on_device && p.mr.type == CHIBSJ) {
+            S1.emit(pc, p, k);
+            g_t_write += get_real_time() - t_p0;
+        } else if (on_device) {
             for (uint32_t t = ev_first[k]; t < ev_first[k + 1]; t++) {
                 if (ev_kind[t] == 0) { S2.emit(pc, p, k); continue; }
                 // print_split_mapping, four mates (:1698-1711) + the type
@@ -343,8 +357,8 @@ void ProcessCirc::cm_shim_do_process(void) {
     report_events();
     if (getenv("CM_GPU_VERBOSE"))
         fprintf(stderr, "circminer_gpu: stage 2: load_genome %.2f s, single-split batches (device + index) %.2f s, their lines / CircRes %.2f s, "
-                "other pairs through the reference's call_circ %.2f s, report_events %.2f s\n", g_t_load, g_t_batch, g_t_write, g_t_ref_pairs,
-                get_real_time() - t_r0);
+                "other pairs through the reference's call_circ %.2f s (%ld of them redone after a device list overflowed), report_events %.2f s\n",
+                g_t_load, g_t_batch, g_t_write, g_t_ref_pairs, g_n_redone, get_real_time() - t_r0);
     Logger::instance().info.set_prefix("[INFO] ");
     Logger::instance().info("CircRNA detection Completed! (CPU time: %.2lfs; Real time: %.2lfs)\n", get_cpu_time() - fq_cputime_start,
                             get_real_time() - fq_realtime_start);

@@ -15,14 +15,16 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SO = os.path.join(HERE, "hostsim", "libhostsim.so")
 
 
-def build():
-    subprocess.check_call(["make", "-s", "-C", os.path.join(HERE, "hostsim")])
+def build(target="libhostsim.so"):
+    subprocess.check_call(["make", "-s", "-C", os.path.join(HERE, "hostsim"), target])
 
 
 class HostSim:
-    def __init__(self, params: CmParams | None = None):
-        build()
-        self.lib = C.CDLL(SO)
+    def __init__(self, params: CmParams | None = None, variant: str = ""):
+        """variant "smallcap": the build with tiny fixed-size lists in the stage-2 classification (tests/hostsim/Makefile)."""
+        so = f"libhostsim_{variant}.so" if variant else "libhostsim.so"
+        build(so)
+        self.lib = C.CDLL(os.path.join(HERE, "hostsim", so))
         self.lib.hs_create.restype = C.c_void_p
         self.params = params or default_params()
         self.ctx = C.c_void_p(self.lib.hs_create(C.byref(self.params)))

@@ -372,3 +372,53 @@ def test_gpu_equals_call_circ_double_split(tmp_path):
         return m
     m = _double_split(tmp_path, make, lambda m, c, w, *a: m.circ_single(c, *a), lambda m, c, w, *a: m.circ_double(c, *a), 20000)
     m.close()
+
+
+@pytest.mark.skipif(not has_ref(), reason="oracle/_ref not built")
+def test_list_overflow_hands_the_pair_back(tmp_path):
+    """A check_split_map that needs more than a fixed-size list of the device code holds (CM_CIRC_TID_CAP transcripts at a breakpoint,
+    CM_CIRC_JUNC_CAP junctions) must not fail the batch: the pair comes back as type -2 (the drop-in redoes it with the reference's
+    call_circ) and every other pair is what the normal build gives.  Host build with the caps at 2 / 1 against the normal one, on the
+    single- and double-split pairs of T1."""
+    from circminer_b200 import workload
+    from circminer_b200.api import default_params
+    from hostsim_api import HostSim
+    pairs = 8000
+    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000, n_pairs=pairs)
+    dump = live_dump(str(tmp_path / "cs.npz"), workload="T1", contig_size=3_500_000, pairs=pairs, circ_single=True, no_stage_dumps=True)
+    sims = []
+    for variant in ("", "smallcap"):
+        hs = HostSim(default_params(), variant=variant)
+        for c, seq in enumerate(w["contigs"]):
+            hs.build_contig(c, seq)
+            hs.load_annotation(c, w["flat"][c])
+        sims.append(hs)
+    n, L = w["s1"].shape
+    lens = np.full(n, L, np.uint16)
+    handed_back = handed_back2 = kept = 0
+    for c in range(int(dump["n_contigs"])):
+        rec = {k[len(f"c{c}_circs_"):]: dump[k] for k in dump.files if k.startswith(f"c{c}_circs_")}
+        args = (w["s1"], w["s2"], lens, lens, rec["mr_con"], rec["gene_cnt"], rec["gene_se"])
+        a, b = (hs.circ_single(c, w["contigs"][c], *args) for hs in sims)
+        over = b["best_type"] == -2
+        handed_back += int(over.sum())
+        assert (a["best_type"] != -2).all()
+        assert (a["best_type"][~over] == b["best_type"][~over]).all() and (a["best_cr"][~over] == b["best_cr"][~over]).all()
+        # attempts of the pairs that were not handed back are the same, in the same order
+        ka, kb = ~over[a["call_pair"]], ~over[b["call_pair"]]
+        assert ka.sum() == kb.sum()
+        for f in ("call_pair", "ret", "cr", "in_r1", "in_r2", "in_pm", "out_r1", "out_r2", "out_pm"):
+            assert (a[f][ka] == b[f][kb]).all(), f
+        kept += int((~over & (a["best_type"] >= 0)).sum())
+        idx = np.nonzero(rec["mr_con"]["type"] == 4)[0]
+        args2 = tuple(x[idx] for x in args)
+        ea, eb = (hs.circ_double(c, w["contigs"][c], *args2) for hs in sims)
+        over2 = eb["push_type"] == -2
+        handed_back2 += int(over2.sum())
+        assert (ea["push_type"] != -2).all()
+        assert (ea["push_type"][~over2] == eb["push_type"][~over2]).all() and (ea["push_cr"][~over2] == eb["push_cr"][~over2]).all()
+        ka, kb = ~over2[ea["pair"]], ~over2[eb["pair"]]
+        assert ka.sum() == kb.sum()
+        for f in ("pair", "kind", "ret", "cr", "r1", "r2", "p1", "p2"):
+            assert (ea[f][ka] == eb[f][kb]).all(), f
+    assert handed_back > 5 and handed_back2 > 0 and kept > 100, (handed_back, handed_back2, kept)
