@@ -4,9 +4,13 @@
 // tokens -> cm_mread, PAM / remain-FASTQ text, write order -- can be checked byte for byte against the reference on a
 // box without a GPU.  The stand-in answers cm_gpu_process_batch_pe with the reference's own FilterRead::process_read
 // (src/filter.cpp:124), one pair at a time, on the scratch of mapping thread 0; nothing here touches libcm_gpu.so.
+// With CM_MOCK_HOSTSIM=<tests/hostsim/libhostsim*.so> it also answers the two stage-2 batch entries, through the g++ build of the
+// device headers and the same host orchestration the library uses (cm_circ_orch.h), so integration/gpu_circ_detect.cpp runs too.
 // Built by oracle/Makefile into oracle/_ref/circminer_feedtest; used by tests/test_host_feed.py.
 #define CM_SHIM_KEEP_REF_TABLE 1   // the stand-in below maps with the reference's own table
 #include "../../integration/gpu_map_reads.cpp"
+#include <dlfcn.h>
+#include <map>
 
 namespace {
 FilterArgs *mock_scratch() { return g_fa; }
@@ -20,6 +24,97 @@ char mock_comp(char c) {
     default: return 0;   // FASTQParser::comp is zero elsewhere (src/fastq_parser.cpp:127-139)
     }
 }
+
+// the host build of the device headers, loaded at run time (it is its own translation unit: no name meets the reference's)
+struct HostSimLib {
+    void *(*create)(const cm_params *) = nullptr;
+    int (*set_text)(void *, int, const uint8_t *, uint32_t) = nullptr;
+    int (*load_annotation)(void *, int, const cm_annot_flat *) = nullptr;
+    int (*circ_single)(void *, int, const uint32_t *, const uint32_t *, uint32_t, const char *, const char *, uint32_t, const uint16_t *, const uint16_t *,
+                       const cm_mread *, const uint32_t *, const uint32_t *, const uint32_t *, int, int, uint32_t, uint32_t *, uint8_t *, cm_circ_mate *,
+                       cm_circ_mate *, cm_circ_mate *, int32_t *, cm_circ_res *, cm_circ_mate *, cm_circ_mate *, cm_circ_mate *, int32_t *,
+                       cm_circ_res *) = nullptr;
+    int (*circ_double)(void *, int, const uint32_t *, const uint32_t *, uint32_t, const char *, const char *, uint32_t, const uint16_t *, const uint16_t *,
+                       const cm_mread *, const uint32_t *, const uint32_t *, const uint32_t *, int, int, uint32_t, uint32_t *, uint8_t *, cm_circ_mate *,
+                       cm_circ_mate *, cm_circ_mate *, cm_circ_mate *, int32_t *, cm_circ_res *, int32_t *, cm_circ_res *) = nullptr;
+    void *ctx = nullptr;
+    int state = 0;   // 0 not tried, 1 loaded, -1 not asked for
+} g_hs;
+bool mock_hs_load() {
+    if (g_hs.state) return g_hs.state > 0;
+    const char *so = getenv("CM_MOCK_HOSTSIM");
+    g_hs.state = -1;
+    if (!so || !*so) return false;
+    void *h = dlopen(so, RTLD_NOW | RTLD_LOCAL);
+    if (!h) { fprintf(stderr, "feed_mock: %s\n", dlerror()); exit(1); }
+    *(void **) &g_hs.create = dlsym(h, "hs_create");
+    *(void **) &g_hs.set_text = dlsym(h, "hs_set_text");
+    *(void **) &g_hs.load_annotation = dlsym(h, "hs_load_annotation");
+    *(void **) &g_hs.circ_single = dlsym(h, "hs_circ_single");
+    *(void **) &g_hs.circ_double = dlsym(h, "hs_circ_double");
+    if (!g_hs.create || !g_hs.set_text || !g_hs.load_annotation || !g_hs.circ_single || !g_hs.circ_double) { fprintf(stderr, "feed_mock: symbols missing in %s\n", so); exit(1); }
+    g_hs.state = 1;
+    return true;
+}
+void *mock_hs_ctx() {
+    if (!g_hs.ctx) g_hs.ctx = g_hs.create(&g_params);
+    return g_hs.ctx;
+}
+// an output array of the C-ABI that the caller may leave NULL: the host build writes all of them
+template <class T> struct MockBuf {
+    std::vector<T> own;
+    T *p;
+    MockBuf(T *given, size_t n) : p(given) { if (!given) { own.resize(n ? n : 1); p = own.data(); } }
+};
+struct MockContig {
+    std::vector<char> text;
+    std::vector<uint32_t> pos, off;     // ws-mer index of the contig: positions (1-based) sorted by (hash, position), run offsets
+    int ws = 0;
+    cm_annot_flat flat;
+    std::vector<std::vector<uint8_t>> store;
+    template <class T> const T *copy(const T *src, size_t n) {
+        store.emplace_back((const uint8_t *) src, (const uint8_t *) src + (n ? n : 1) * sizeof(T));
+        return (const T *) store.back().data();
+    }
+    void keep(const cm_annot_flat *A) {
+        store.clear();
+        flat = *A;
+        flat.iv_spos = copy(A->iv_spos, A->n_iv); flat.iv_epos = copy(A->iv_epos, A->n_iv); flat.iv_max_end = copy(A->iv_max_end, A->n_iv);
+        flat.iv_min_end = copy(A->iv_min_end, A->n_iv); flat.iv_max_next_exon = copy(A->iv_max_next_exon, A->n_iv);
+        flat.iv_seg_off = copy(A->iv_seg_off, (size_t) A->n_iv + 1);
+        flat.seg_start = copy(A->seg_start, A->n_seg); flat.seg_end = copy(A->seg_end, A->n_seg);
+        flat.seg_next_exon_beg = copy(A->seg_next_exon_beg, A->n_seg); flat.seg_gene_id = copy(A->seg_gene_id, A->n_seg);
+        flat.seg_tid_off = copy(A->seg_tid_off, (size_t) A->n_seg + 1);
+        flat.tid = copy(A->tid, A->n_tid);
+        flat.trans_start_ind = copy(A->trans_start_ind, A->n_trans); flat.t2s_off = copy(A->t2s_off, (size_t) A->n_trans + 1);
+        flat.t2s = copy(A->t2s, A->n_trans ? A->t2s_off[A->n_trans] : 0);
+        flat.gene_start = copy(A->gene_start, A->n_genes); flat.gene_end = copy(A->gene_end, A->n_genes);
+        flat.chr_shift = copy(A->chr_shift, A->n_chr); flat.chr_id = copy(A->chr_id, A->n_chr);
+        flat.near_border = copy(A->near_border, (size_t) ((A->n_bits + 63) / 64)); flat.intronic = copy(A->intronic, (size_t) ((A->n_bits + 63) / 64));
+    }
+    void circ_index(int w) {
+        if (ws == w && !off.empty()) return;
+        ws = w;
+        const size_t nb = (size_t) 1 << (2 * w), L = text.size();
+        off.assign(nb + 1, 0);
+        std::vector<uint32_t> key(L, 0xffffffffu);
+        auto code = [](char ch) { switch (ch) { case 'A': case 'a': return 0; case 'C': case 'c': return 1; case 'G': case 'g': return 2; case 'T': case 't': return 3; default: return 4; } };
+        uint32_t h = 0;
+        int good = 0;
+        for (size_t i = 0; i < L; i++) {
+            const int v = code(text[i]);
+            if (v == 4) { good = 0; h = 0; continue; }
+            h = ((h << 2) | (uint32_t) v) & (uint32_t) (nb - 1);
+            if (++good >= w) { key[i + 1 - w] = h; off[h + 1]++; }
+        }
+        for (size_t b = 0; b < nb; b++) off[b + 1] += off[b];
+        pos.assign(off[nb] ? off[nb] : 1, 0);
+        std::vector<uint32_t> at(off.begin(), off.end() - 1);
+        for (size_t i = 0; i < L; i++)
+            if (key[i] != 0xffffffffu) pos[at[key[i]]++] = (uint32_t) i + 1;
+    }
+};
+std::map<int, MockContig> g_mock_contigs;
 }   // namespace
 
 extern "C" {
@@ -41,19 +136,69 @@ int cm_gpu_create(int, const cm_params *, cm_gpu_ctx **out) { *out = (cm_gpu_ctx
 int cm_gpu_create_shared(cm_gpu_ctx *parent, cm_gpu_ctx **out) { *out = parent; return CM_OK; }
 const char *cm_gpu_last_error(const cm_gpu_ctx *) { return "mock"; }
 int cm_gpu_load_contig(cm_gpu_ctx *, int, const void *const *, const void *, uint64_t, const uint64_t *, uint32_t) { return CM_OK; }
-int cm_gpu_build_contig_packed(cm_gpu_ctx *, int, const uint64_t *, uint32_t) { return CM_OK; }
-int cm_gpu_load_annotation(cm_gpu_ctx *, int, const cm_annot_flat *) { return CM_OK; }
+// ---- stage 2 over the host build of the device headers (tests/hostsim), when CM_MOCK_HOSTSIM names its library -------------------
+// With it the stand-in also answers cm_gpu_circ_single_batch / cm_gpu_circ_double_batch, so the drop-in's do_process
+// (integration/gpu_circ_detect.cpp) runs on the CPU and its candidates.pam / circ_report can be compared with the reference's.
+// Without it those two entries fail and the tests run the binary with CM_GPU_STAGE2=0.
+int cm_gpu_build_contig_packed(cm_gpu_ctx *, int c, const uint64_t *, uint32_t len) {
+    if (!mock_hs_load()) return CM_OK;
+    std::vector<char> text((size_t) len + 2);
+    if (!genome_seeder.pac2char_otf(1, (int) len, text.data())) return CM_ERR_STATE;   // the contig the reference has just loaded
+    MockContig &m = g_mock_contigs[c];
+    m.text.assign(text.begin(), text.begin() + len);
+    m.pos.clear(); m.off.clear(); m.ws = 0;
+    return g_hs.set_text(mock_hs_ctx(), c, (const uint8_t *) m.text.data(), len) == 0 ? CM_OK : CM_ERR_STATE;
+}
+int cm_gpu_load_annotation(cm_gpu_ctx *, int c, const cm_annot_flat *A) {
+    if (!mock_hs_load()) return CM_OK;
+    MockContig &m = g_mock_contigs[c];
+    m.keep(A);                                       // the host build keeps pointers; the shim's arrays die after this call
+    return g_hs.load_annotation(mock_hs_ctx(), c, &m.flat) == 0 ? CM_OK : CM_ERR_STATE;
+}
 int cm_annot_file_write(const char *, const cm_annot_flat *, uint32_t, uint64_t) { return CM_ERR_ARG; }
 int cm_annot_file_read(const char *, cm_annot_flat *, uint32_t *, uint64_t *, void **) { return CM_ERR_ARG; }
 void cm_annot_file_free(void *) {}
-// stage 2 has no stand-in here: the host-feed tests run the binary with CM_GPU_STAGE2=0 (the reference's own do_process)
-int cm_gpu_circ_single_batch(cm_gpu_ctx *, int, uint32_t, const char *, const char *, uint32_t, const uint16_t *, const uint16_t *, const cm_mread *,
-                             const uint32_t *, const uint32_t *, const uint32_t *, int, int, uint32_t, uint32_t *, uint32_t *, uint8_t *, cm_circ_mate *,
-                             cm_circ_mate *, cm_circ_mate *, int32_t *, cm_circ_res *, cm_circ_mate *, cm_circ_mate *, cm_circ_mate *, int32_t *,
-                             cm_circ_res *) { return CM_ERR_STATE; }
-int cm_gpu_circ_double_batch(cm_gpu_ctx *, int, uint32_t, const char *, const char *, uint32_t, const uint16_t *, const uint16_t *, const cm_mread *,
-                             const uint32_t *, const uint32_t *, const uint32_t *, int, int, uint32_t, uint32_t *, uint32_t *, uint8_t *, cm_circ_mate *,
-                             cm_circ_mate *, cm_circ_mate *, cm_circ_mate *, int32_t *, cm_circ_res *, int32_t *, cm_circ_res *) { return CM_ERR_STATE; }
+int cm_gpu_circ_single_batch(cm_gpu_ctx *, int c, uint32_t n, const char *s1, const char *s2, uint32_t stride, const uint16_t *l1, const uint16_t *l2,
+                             const cm_mread *mr, const uint32_t *goff, const uint32_t *gs, const uint32_t *ge, int ws, int step, uint32_t cap,
+                             uint32_t *n_att, uint32_t *att_pair, uint8_t *att_r1p, cm_circ_mate *in_r1, cm_circ_mate *in_r2, cm_circ_mate *in_pm,
+                             int32_t *ret, cm_circ_res *cr, cm_circ_mate *out_r1, cm_circ_mate *out_r2, cm_circ_mate *out_pm, int32_t *best_type,
+                             cm_circ_res *best_cr) {
+    if (!mock_hs_load()) return CM_ERR_STATE;
+    if (n_att) *n_att = 0;
+    if (n == 0) return CM_OK;
+    MockContig &m = g_mock_contigs[c];
+    m.circ_index(ws);
+    MockBuf<uint32_t> b_pair(att_pair, cap);
+    MockBuf<uint8_t> b_r1p(att_r1p, cap);
+    MockBuf<cm_circ_mate> b_i1(in_r1, cap), b_i2(in_r2, cap), b_ip(in_pm, cap), b_o1(out_r1, cap), b_o2(out_r2, cap), b_op(out_pm, cap);
+    MockBuf<int32_t> b_ret(ret, cap);
+    MockBuf<cm_circ_res> b_cr(cr, cap);
+    const int r = g_hs.circ_single(mock_hs_ctx(), c, m.pos.data(), m.off.data(), n, s1, s2, stride, l1, l2, mr, goff, gs, ge, ws, step, cap, b_pair.p, b_r1p.p,
+                                   b_i1.p, b_i2.p, b_ip.p, b_ret.p, b_cr.p, b_o1.p, b_o2.p, b_op.p, best_type, best_cr);
+    if (r < 0) return CM_ERR_STATE;
+    *n_att = (uint32_t) r;
+    return CM_OK;
+}
+int cm_gpu_circ_double_batch(cm_gpu_ctx *, int c, uint32_t n, const char *s1, const char *s2, uint32_t stride, const uint16_t *l1, const uint16_t *l2,
+                             const cm_mread *mr, const uint32_t *goff, const uint32_t *gs, const uint32_t *ge, int ws, int step, uint32_t cap,
+                             uint32_t *n_ev, uint32_t *ev_pair, uint8_t *ev_kind, cm_circ_mate *ev_r1, cm_circ_mate *ev_r2, cm_circ_mate *ev_p1,
+                             cm_circ_mate *ev_p2, int32_t *ev_ret, cm_circ_res *ev_cr, int32_t *push_type, cm_circ_res *push_cr) {
+    if (!mock_hs_load()) return CM_ERR_STATE;
+    if (n_ev) *n_ev = 0;
+    if (n == 0) return CM_OK;
+    MockContig &m = g_mock_contigs[c];
+    m.circ_index(ws);
+    MockBuf<uint32_t> b_pair(ev_pair, cap);
+    MockBuf<uint8_t> b_kind(ev_kind, cap);
+    MockBuf<cm_circ_mate> b_r1(ev_r1, cap), b_r2(ev_r2, cap), b_p1(ev_p1, cap), b_p2(ev_p2, cap);
+    MockBuf<int32_t> b_ret(ev_ret, cap);
+    MockBuf<cm_circ_res> b_cr(ev_cr, cap);
+    const int r = g_hs.circ_double(mock_hs_ctx(), c, m.pos.data(), m.off.data(), n, s1, s2, stride, l1, l2, mr, goff, gs, ge, ws, step, cap, b_pair.p, b_kind.p,
+                                   b_r1.p, b_r2.p, b_p1.p, b_p2.p, b_ret.p, b_cr.p, push_type, push_cr);
+    if (r < 0) return CM_ERR_STATE;
+    *n_ev = (uint32_t) r;
+    return CM_OK;
+}
 int cm_gpu_host_alloc(size_t bytes, void **out) { *out = malloc(bytes ? bytes : 1); return *out ? CM_OK : CM_ERR_ALLOC; }
 int cm_gpu_host_free(void *p) { free(p); return CM_OK; }
 

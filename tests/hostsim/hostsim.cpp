@@ -107,6 +107,19 @@ int hs_set_index(HsCtx *c, int contig_id, const uint32_t *dir, const uint16_t *c
     return 0;
 }
 
+// contig text alone, no k-mer index: enough for stage 2 (tests/hostfeed/feed_mock.cpp)
+int hs_set_text(HsCtx *c, int contig_id, const uint8_t *genome_ascii, uint32_t ref_len) {
+    if ((size_t) contig_id >= c->contigs.size()) c->contigs.resize(contig_id + 1, nullptr);
+    delete c->contigs[contig_id];
+    HsContig *h = new HsContig;
+    c->contigs[contig_id] = h;
+    h->genome.assign((size_t) ref_len + 64, 'N');
+    memcpy(h->genome.data() + 1, genome_ascii, ref_len);
+    h->d.dir = nullptr; h->d.cks = nullptr; h->d.pos = nullptr; h->d.genome = h->genome.data();
+    h->d.n_entries = 0; h->d.ref_len = ref_len;
+    return 0;
+}
+
 // Host build of the fused directory + coarse tables of the large buckets (what build_dirx does on the device), then
 // cm_seed_lookup_x against the plain cm_seed_lookup on every stored (bucket, checksum) of a sample of entries, their
 // neighbours checksum +- 1, and random keys.  Returns the number of look-ups that differ (0 = the two are the same map).

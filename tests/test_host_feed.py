@@ -2,7 +2,8 @@
 PAM / remain-FASTQ text in input order) checked on the CPU: oracle/_ref/circminer_feedtest is the drop-in's shim with a
 stand-in for the C-ABI that answers each batch with the reference's own process_read (tests/hostfeed/feed_mock.cpp), so
 every byte that differs from the reference binary is a host-feed bug.  Two packed contigs = two rounds, the second one
-parsing the 23-token headers the first one wrote.  The GPU counterpart is tests/test_gpu_dropin.py."""
+parsing the 23-token headers the first one wrote.  Stage 2 of the drop-in (integration/gpu_circ_detect.cpp) runs here as well,
+with the batch entries answered by the host build of the device code.  The GPU counterpart is tests/test_gpu_dropin.py."""
 import filecmp
 import glob
 import os
@@ -105,3 +106,32 @@ def test_genome_only_load_leaves_the_state_of_the_full_load(tmp_path, compact):
     assert p.returncode == 0, (p.stdout + p.stderr)[-3000:]
     n, same, full = p.stdout.split()[-3:]
     assert int(n) >= 2 and same == "True" and int(full) == (0 if compact else 1), p.stdout[-500:]
+
+
+@pytest.mark.skipif(not (has_ref() and os.path.exists(FEED)), reason="oracle/_ref/circminer_feedtest not built")
+@pytest.mark.parametrize("variant", ["", "smallcap"])
+def test_stage2_of_the_dropin_on_the_cpu(dataset, tmp_path, variant):
+    """The drop-in's do_process (integration/gpu_circ_detect.cpp: batches per contig, lines and CircRes in file order, pairs handed back
+    to the reference's call_circ) with the batch entries answered by the host build of the device code (CM_MOCK_HOSTSIM): candidates.pam
+    and circ_report byte for byte against the reference binary.  "smallcap": the host build with tiny fixed-size lists, so that some
+    pairs come back as type -2 and are redone by the reference's own code in their place -- the files must not change."""
+    import re
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from hostsim_api import build
+    so = f"libhostsim_{variant}.so" if variant else "libhostsim.so"
+    build(so)
+    w = dataset
+    ref_out, feed_out = str(tmp_path / "ref"), str(tmp_path / "feed")
+    _run(REF, w, ref_out, 1)
+    cmd = [FEED, "-r", w["fa"], "-g", w["gtf"], "-1", w["fq1"], "-2", w["fq2"], "-k", "20", "-t", "2", "-P", "-z", "-o", feed_out]
+    env = dict(os.environ, LC_ALL="C", CM_GPU_BATCH="2000", CM_GPU_VERBOSE="1", CM_MOCK_HOSTSIM=os.path.join(ROOT, "tests", "hostsim", so))
+    p = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=1500)
+    assert p.returncode == 0, (p.stdout + p.stderr)[-2000:]
+    for suffix in (".candidates.pam", ".circ_report", ".mapping.pam"):
+        assert filecmp.cmp(ref_out + suffix, feed_out + suffix, shallow=False), f"{suffix} differs"
+    assert os.path.getsize(ref_out + ".candidates.pam") > 1000
+    log = p.stdout + p.stderr
+    batches = re.findall(r"stage 2, contig \d+: (\d+) single-split pairs of \d+ in one batch, \d+ check_split_map attempts; (\d+) double-split", log)
+    assert batches and sum(int(a) for a, _ in batches) > 50 and sum(int(b) for _, b in batches) > 5, log[-1500:]
+    redone = int(re.search(r"\((\d+) of them redone after a device list overflowed\)", log).group(1))
+    assert (redone > 0) == (variant == "smallcap"), (variant, redone)
