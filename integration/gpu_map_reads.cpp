@@ -140,6 +140,31 @@ std::string annot_cache_path(int c) {
 // GTFParser tables of the current contig as the flat arrays of cm_annot_flat.  The flattening (two 1.3-Gbit masks read bit by
 // bit out of std::bitset) is done once per (GTF, packed reference, -l): the result is kept as a file beside the GTF
 // (cm_annot_file_write) and later runs upload that file as it is.
+// The words of a std::bitset.  The standard gives no word access; libstdc++ keeps the bits as an array of unsigned long with bit k
+// in word k / 64, and that is checked on the object itself (size, and 64 words spread over the range against operator[]) before
+// the words are copied -- false means "read it bit by bit".  Bits from n_bits on are cleared, as the bit-by-bit copy leaves them.
+bool g_annot_by_words = false;   // for the CM_GPU_VERBOSE line
+template <size_t N>
+bool bitset_words(const std::bitset<N> &b, uint64_t *dst, size_t nw, uint64_t n_bits) {
+    if (sizeof(unsigned long) != 8 || sizeof(b) != ((N + 63) / 64) * 8 || nw == 0 || nw * 64 > ((N + 63) / 64) * 64 || n_bits > N) return false;
+    const unsigned char *raw = reinterpret_cast<const unsigned char *>(&b);
+    for (int s = 0; s < 64; s++) {
+        const size_t i = (nw - 1) * (size_t) s / 63;
+        uint64_t a = 0, w;
+        for (uint64_t k = (uint64_t) i << 6; k < ((uint64_t) i << 6) + 64 && k < N; k++)
+            if (b[k]) a |= 1ull << (k & 63);
+        memcpy(&w, raw + i * 8, 8);
+        if (a != w) return false;
+    }
+    memcpy(dst, raw, nw * 8);
+    if (n_bits < nw * 64) {
+        const size_t last = (size_t) (n_bits >> 6);
+        if (n_bits & 63) dst[last] &= (1ull << (n_bits & 63)) - 1; else dst[last] = 0;
+        for (size_t i = last + 1; i < nw; i++) dst[i] = 0;
+    }
+    return true;
+}
+
 void upload_annotation(int c) {
     std::vector<int32_t> chr_now;   // this run's chromosome-table indices of the contig's chromosomes (registers the names)
     for (auto &cc : gtf_parser.con2chr[c]) chr_now.push_back(chr_index(cc.contig));
@@ -199,10 +224,13 @@ void upload_annotation(int c) {
     for (auto &cc : gtf_parser.con2chr[c]) { chr_shift.push_back(cc.shift); chr_id.push_back(chr_index(cc.contig)); }
     const uint64_t n_bits = (uint64_t) _ih_refGenLen + 2;
     std::vector<uint64_t> nb((n_bits + 63) / 64, 0), in((n_bits + 63) / 64, 0);
-    {   // std::bitset has no word access: the bits are read one by one, whole words per thread
+    const bool has_nb = (size_t) c < near_border_bs.size(), has_in = (size_t) c < intronic_bs.size();
+    const bool by_words = (!has_nb || bitset_words(near_border_bs[c], nb.data(), nb.size(), n_bits)) &&
+                          (!has_in || bitset_words(intronic_bs[c], in.data(), in.size(), n_bits));
+    g_annot_by_words = by_words;
+    if (!by_words) {   // the bits read one by one, whole words per thread (0.3 s per Gbp and bitset on 16 threads)
         const int T = std::max(1, threadCount);
         const size_t nw = nb.size();
-        const bool has_nb = (size_t) c < near_border_bs.size(), has_in = (size_t) c < intronic_bs.size();
         feed::parallel_for(T, [&](int t) {
             for (size_t w = nw * t / T; w < nw * (t + 1) / T; w++) {
                 uint64_t a = 0, b = 0;
@@ -340,8 +368,9 @@ void ensure_round(int c) {
             }
     }
     if (g_verbose)
-        fprintf(stderr, "circminer_gpu: contig %d on %zu device(s), %zu contexts: context %.3f s, table scan %.3f s, index on device %.3f s, annotation %.3f s\n",
-                c, g_roots.size(), g_workers.size(), t_ctx - t_in, t_scan - t_ctx, t_idx - t_scan, now_s() - t_idx);
+        fprintf(stderr, "circminer_gpu: contig %d on %zu device(s), %zu contexts: context %.3f s, table scan %.3f s, index on device %.3f s, annotation %.3f s (bit vectors %s)\n",
+                c, g_roots.size(), g_workers.size(), t_ctx - t_in, t_scan - t_ctx, t_idx - t_scan, now_s() - t_idx,
+                g_annot_by_words ? "copied by words" : "read bit by bit or from the cache file");
 }
 
 // a Record that outlives FASTQParser's per-thread buffer

@@ -150,6 +150,16 @@ int cm_gpu_build_contig_packed(cm_gpu_ctx *, int c, const uint64_t *, uint32_t l
     return g_hs.set_text(mock_hs_ctx(), c, (const uint8_t *) m.text.data(), len) == 0 ? CM_OK : CM_ERR_STATE;
 }
 int cm_gpu_load_annotation(cm_gpu_ctx *, int c, const cm_annot_flat *A) {
+    // the two bit vectors as the shim hands them over (copied by words from the std::bitsets) against the bitsets read bit by bit
+    for (uint64_t k = 0; k < A->n_bits; k++) {
+        const bool nb = (size_t) c < near_border_bs.size() && near_border_bs[c][k], in = (size_t) c < intronic_bs.size() && intronic_bs[c][k];
+        if (((A->near_border[k >> 6] >> (k & 63)) & 1) != (uint64_t) nb || ((A->intronic[k >> 6] >> (k & 63)) & 1) != (uint64_t) in) {
+            fprintf(stderr, "feed_mock: annotation bit %llu of contig %d differs from the reference's bitset\n", (unsigned long long) k, c);
+            exit(1);
+        }
+    }
+    for (uint64_t k = A->n_bits; k < ((A->n_bits + 63) / 64) * 64; k++)
+        if (((A->near_border[k >> 6] >> (k & 63)) & 1) || ((A->intronic[k >> 6] >> (k & 63)) & 1)) { fprintf(stderr, "feed_mock: annotation bits past n_bits set\n"); exit(1); }
     if (!mock_hs_load()) return CM_OK;
     MockContig &m = g_mock_contigs[c];
     m.keep(A);                                       // the host build keeps pointers; the shim's arrays die after this call

@@ -14,6 +14,26 @@ MATE_FIELDS = ("spos", "epos", "qspos", "qepos", "matched_len", "left_ed", "midd
                "is_concord", "left_ok", "right_ok")
 
 
+_T1_DUMPS = {}
+
+
+def _t1_single_split_dump(pairs):
+    """T1 and the reference's record of its stage 2 (oracle/refdump.py --circ-single), made once per test session and pair count:
+    several tests read the same dump."""
+    if pairs not in _T1_DUMPS:
+        import atexit
+        import os
+        import shutil
+        import tempfile
+        from circminer_b200 import workload
+        d = tempfile.mkdtemp(prefix="cm_t1_circs_")
+        atexit.register(shutil.rmtree, d, ignore_errors=True)
+        w = workload.prepare("T1", os.path.join(d, "t1"), contig_size=3_500_000, n_pairs=pairs)
+        dump = live_dump(os.path.join(d, "cs.npz"), workload="T1", contig_size=3_500_000, pairs=pairs, circ_single=True, no_stage_dumps=True)
+        _T1_DUMPS[pairs] = (w, dump)
+    return _T1_DUMPS[pairs]
+
+
 def _compare_exact(engine, dump, c, min_concord):
     """find_exact_coord on every chain ProcessCirc would try: the return value and every MatchedMate field of partial_mm."""
     prob = {k: dump[f"c{c}_circx_p_{k}"] for k in XKEYS}
@@ -160,8 +180,7 @@ def _check_split_map(tmp_path, make_engine, pairs):
     --circ-single: its own call_circ_single_split control flow over its own member functions, every call recorded): the return
     value, the CircRes it fills (breakpoints, signals, reference bases) and the three mates as it leaves them."""
     from circminer_b200 import workload
-    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000, n_pairs=pairs)
-    dump = live_dump(str(tmp_path / "cs.npz"), workload="T1", contig_size=3_500_000, pairs=pairs, circ_single=True, no_stage_dumps=True)
+    w, dump = _t1_single_split_dump(pairs)
     eng = make_engine(w)
     seen = set()
     total = total4 = 0
@@ -231,8 +250,7 @@ def _single_split(tmp_path, make_engine, run, pairs):
     mates of every attempt.  The batch entry must reproduce both: attempts in order with their mates before and after, types,
     CircRes, and per pair what the function ends with."""
     from circminer_b200 import workload
-    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000, n_pairs=pairs)
-    dump = live_dump(str(tmp_path / "cs.npz"), workload="T1", contig_size=3_500_000, pairs=pairs, circ_single=True, no_stage_dumps=True)
+    w, dump = _t1_single_split_dump(pairs)
     eng = make_engine(w)
     n, L = w["s1"].shape
     lens = np.full(n, L, np.uint16)
@@ -303,8 +321,7 @@ def _double_split(tmp_path, make_engine, single, double, pairs):
     to candidates.pam (print_split_mapping lines of its own four-mate attempts and of the call_circ_single_split calls it makes on
     the same pair, in order, byte for byte) and everything it pushes to circ_res."""
     from circminer_b200 import workload
-    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000, n_pairs=pairs)
-    dump = live_dump(str(tmp_path / "cs.npz"), workload="T1", contig_size=3_500_000, pairs=pairs, circ_single=True, no_stage_dumps=True)
+    w, dump = _t1_single_split_dump(pairs)
     eng = make_engine(w)
     n, L = w["s1"].shape
     lens = np.full(n, L, np.uint16)
@@ -384,8 +401,7 @@ def test_list_overflow_hands_the_pair_back(tmp_path):
     from circminer_b200.api import default_params
     from hostsim_api import HostSim
     pairs = 8000
-    w = workload.prepare("T1", str(tmp_path / "t1"), contig_size=3_500_000, n_pairs=pairs)
-    dump = live_dump(str(tmp_path / "cs.npz"), workload="T1", contig_size=3_500_000, pairs=pairs, circ_single=True, no_stage_dumps=True)
+    w, dump = _t1_single_split_dump(pairs)
     sims = []
     for variant in ("", "smallcap"):
         hs = HostSim(default_params(), variant=variant)
