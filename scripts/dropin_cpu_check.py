@@ -1,7 +1,8 @@
 """The drop-in binary's two stages on a box without a GPU, at C3s scale (C3 at 1/50, repeat-rich): oracle/_ref/circminer_feedtest =
 the drop-in's shim and do_process over a stand-in for libcm_gpu.so (mapping answered by the reference's process_read, stage 2 by the
 host build of the device code, tests/hostfeed/feed_mock.cpp) against the reference binary: candidates.pam and circ_report byte for
-byte, mapping.pam as a multiset of lines.  Test infrastructure: executes oracle/_ref.  python scripts/dropin_cpu_check.py [pairs]"""
+byte, mapping.pam as a multiset of lines.  CM_CHECK_HOSTSIM=libhostsim_smallcap.so: the host build with tiny list caps (pairs handed
+back to the reference's call_circ).  Test infrastructure: executes oracle/_ref.  python scripts/dropin_cpu_check.py [pairs]"""
 import os, subprocess, sys, time, filecmp, re
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, 'tests'))
 from circminer_b200 import workload
@@ -20,7 +21,7 @@ def run(binary,out,env=None,threads=8):
     if pr.returncode: print((pr.stdout+pr.stderr)[-1500:])
     return pr.stdout+pr.stderr
 run(ROOT+"/oracle/_ref/circminer", d+"/ref")
-log=run(ROOT+"/oracle/_ref/circminer_feedtest", d+"/feed", env={"CM_GPU_BATCH":"20000","CM_GPU_VERBOSE":"1","CM_MOCK_HOSTSIM":ROOT+"/tests/hostsim/libhostsim.so"})
+log=run(ROOT+"/oracle/_ref/circminer_feedtest", d+"/feed", env={"CM_GPU_BATCH":"20000","CM_GPU_VERBOSE":"1","CM_MOCK_HOSTSIM":ROOT+"/tests/hostsim/"+os.environ.get("CM_CHECK_HOSTSIM","libhostsim.so")})
 for ln in log.splitlines():
     if 'stage 2' in ln: print(ln[:300])
 for suf in (".candidates.pam",".circ_report"):
