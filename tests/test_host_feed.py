@@ -109,22 +109,25 @@ def test_genome_only_load_leaves_the_state_of_the_full_load(tmp_path, compact):
 
 
 @pytest.mark.skipif(not (has_ref() and os.path.exists(FEED)), reason="oracle/_ref/circminer_feedtest not built")
-@pytest.mark.parametrize("variant", ["", "smallcap"])
+@pytest.mark.parametrize("variant", ["", "smallcap", "double0"])
 def test_stage2_of_the_dropin_on_the_cpu(dataset, tmp_path, variant):
     """The drop-in's do_process (integration/gpu_circ_detect.cpp: batches per contig, lines and CircRes in file order, pairs handed back
     to the reference's call_circ) with the batch entries answered by the host build of the device code (CM_MOCK_HOSTSIM): candidates.pam
     and circ_report byte for byte against the reference binary.  "smallcap": the host build with tiny fixed-size lists, so that some
-    pairs come back as type -2 and are redone by the reference's own code in their place -- the files must not change."""
+    pairs come back as type -2 and are redone by the reference's own code in their place -- the files must not change.  "double0":
+    CM_GPU_STAGE2_DOUBLE=0."""
     import re
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from hostsim_api import build
-    so = f"libhostsim_{variant}.so" if variant else "libhostsim.so"
+    so = "libhostsim_smallcap.so" if variant == "smallcap" else "libhostsim.so"
     build(so)
     w = dataset
     ref_out, feed_out = str(tmp_path / "ref"), str(tmp_path / "feed")
     _run(REF, w, ref_out, 1)
     cmd = [FEED, "-r", w["fa"], "-g", w["gtf"], "-1", w["fq1"], "-2", w["fq2"], "-k", "20", "-t", "2", "-P", "-z", "-o", feed_out]
     env = dict(os.environ, LC_ALL="C", CM_GPU_BATCH="2000", CM_GPU_VERBOSE="1", CM_MOCK_HOSTSIM=os.path.join(ROOT, "tests", "hostsim", so))
+    if variant == "double0":
+        env["CM_GPU_STAGE2_DOUBLE"] = "0"           # double-split pairs through the reference's call_circ, between the batched ones
     p = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=1500)
     assert p.returncode == 0, (p.stdout + p.stderr)[-2000:]
     for suffix in (".candidates.pam", ".circ_report", ".mapping.pam"):
@@ -132,7 +135,7 @@ def test_stage2_of_the_dropin_on_the_cpu(dataset, tmp_path, variant):
     assert os.path.getsize(ref_out + ".candidates.pam") > 1000
     log = p.stdout + p.stderr
     batches = re.findall(r"stage 2, contig \d+: (\d+) single-split pairs of \d+ in one batch, \d+ check_split_map attempts; (\d+) double-split", log)
-    assert batches and sum(int(a) for a, _ in batches) > 50 and sum(int(b) for _, b in batches) > 5, log[-1500:]
+    assert batches and sum(int(a) for a, _ in batches) > 50 and (sum(int(b) for _, b in batches) > 5) == (variant != "double0"), log[-1500:]
     # the annotation's two bit vectors went over as words of the std::bitsets (the stand-in compares every bit with operator[])
     assert "bit vectors copied by words" in log and "read bit by bit" not in log, log[-1500:]
     redone = int(re.search(r"\((\d+) of them redone after a device list overflowed\)", log).group(1))
