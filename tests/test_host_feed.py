@@ -109,13 +109,14 @@ def test_genome_only_load_leaves_the_state_of_the_full_load(tmp_path, compact):
 
 
 @pytest.mark.skipif(not (has_ref() and os.path.exists(FEED)), reason="oracle/_ref/circminer_feedtest not built")
-@pytest.mark.parametrize("variant", ["", "smallcap", "double0", "scan2"])
+@pytest.mark.parametrize("variant", ["", "smallcap", "double0", "scan2", "ragged"])
 def test_stage2_of_the_dropin_on_the_cpu(dataset, tmp_path, variant):
     """The drop-in's do_process (integration/gpu_circ_detect.cpp: batches per contig, lines and CircRes in file order, pairs handed back
     to the reference's call_circ) with the batch entries answered by the host build of the device code (CM_MOCK_HOSTSIM): candidates.pam
     and circ_report byte for byte against the reference binary.  "smallcap": the host build with tiny fixed-size lists, so that some
     pairs come back as type -2 and are redone by the reference's own code in their place -- the files must not change.  "double0":
-    CM_GPU_STAGE2_DOUBLE=0.  "scan2": scan level 2 (-a 2), which leaves stage 2 more candidates."""
+    CM_GPU_STAGE2_DOUBLE=0.  "scan2": scan level 2 (-a 2), which leaves stage 2 more candidates.  "ragged": reads of different
+    lengths."""
     import re
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from hostsim_api import build
@@ -124,6 +125,21 @@ def test_stage2_of_the_dropin_on_the_cpu(dataset, tmp_path, variant):
     w = dataset
     ref_out, feed_out = str(tmp_path / "ref"), str(tmp_path / "feed")
     extra = ("-a", "2") if variant == "scan2" else ()
+    if variant == "ragged":                          # 70 % of the reads cut to a random length of 60 .. 150, each mate on its own
+        import random
+        rnd = random.Random(5)
+        w = dict(w)
+        for key in ("fq1", "fq2"):
+            dst = str(tmp_path / (key + ".fastq"))
+            with open(dataset[key]) as f, open(dst, "w") as g:
+                while True:
+                    h = f.readline()
+                    if not h:
+                        break
+                    seq, plus, qual = f.readline().rstrip("\n"), f.readline(), f.readline().rstrip("\n")
+                    n = rnd.randint(60, len(seq)) if rnd.random() < 0.7 else len(seq)
+                    g.write(h + seq[:n] + "\n" + plus + qual[:n] + "\n")
+            w[key] = dst
     _run(REF, w, ref_out, 1, extra=extra)
     cmd = [FEED, "-r", w["fa"], "-g", w["gtf"], "-1", w["fq1"], "-2", w["fq2"], "-k", "20", "-t", "2", "-P", "-z", "-o", feed_out, *extra]
     env = dict(os.environ, LC_ALL="C", CM_GPU_BATCH="2000", CM_GPU_VERBOSE="1", CM_MOCK_HOSTSIM=os.path.join(ROOT, "tests", "hostsim", so))
