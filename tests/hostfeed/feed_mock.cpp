@@ -5,7 +5,9 @@
 // box without a GPU.  The stand-in answers cm_gpu_process_batch_pe with the reference's own FilterRead::process_read
 // (src/filter.cpp:124), one pair at a time, on the scratch of mapping thread 0; nothing here touches libcm_gpu.so.
 // With CM_MOCK_HOSTSIM=<tests/hostsim/libhostsim*.so> it also answers the two stage-2 batch entries, through the g++ build of the
-// device headers and the same host orchestration the library uses (cm_circ_orch.h), so integration/gpu_circ_detect.cpp runs too.
+// device headers and the same host orchestration the library uses (cm_circ_orch.h), so integration/gpu_circ_detect.cpp runs too;
+// with CM_MOCK_STAGE1=hostsim as well, the mapping batches go through that build instead of the reference's process_read: the whole
+// product logic (shim + device code) inside the reference's driver, on the CPU.
 // Built by oracle/Makefile into oracle/_ref/circminer_feedtest; used by tests/test_host_feed.py.
 #define CM_SHIM_KEEP_REF_TABLE 1   // the stand-in below maps with the reference's own table
 #include "../../integration/gpu_map_reads.cpp"
@@ -37,8 +39,12 @@ struct HostSimLib {
     int (*circ_double)(void *, int, const uint32_t *, const uint32_t *, uint32_t, const char *, const char *, uint32_t, const uint16_t *, const uint16_t *,
                        const cm_mread *, const uint32_t *, const uint32_t *, const uint32_t *, int, int, uint32_t, uint32_t *, uint8_t *, cm_circ_mate *,
                        cm_circ_mate *, cm_circ_mate *, cm_circ_mate *, int32_t *, cm_circ_res *, int32_t *, cm_circ_res *) = nullptr;
+    int (*load_contig)(void *, int, const void *const *, const void *, const uint8_t *, uint32_t) = nullptr;
+    int (*process_batch_pe)(void *, int, uint32_t, const char *, const char *, uint32_t, const uint16_t *, const uint16_t *, const cm_mread *, cm_mread *,
+                            int32_t *, cm_counters *) = nullptr;
     void *ctx = nullptr;
     int state = 0;   // 0 not tried, 1 loaded, -1 not asked for
+    bool stage1 = false;   // CM_MOCK_STAGE1=hostsim: the mapping batches go through the host build as well
 } g_hs;
 bool mock_hs_load() {
     if (g_hs.state) return g_hs.state > 0;
@@ -52,6 +58,11 @@ bool mock_hs_load() {
     *(void **) &g_hs.load_annotation = dlsym(h, "hs_load_annotation");
     *(void **) &g_hs.circ_single = dlsym(h, "hs_circ_single");
     *(void **) &g_hs.circ_double = dlsym(h, "hs_circ_double");
+    *(void **) &g_hs.load_contig = dlsym(h, "hs_load_contig");
+    *(void **) &g_hs.process_batch_pe = dlsym(h, "hs_process_batch_pe");
+    const char *s1 = getenv("CM_MOCK_STAGE1");
+    g_hs.stage1 = s1 && !strcmp(s1, "hostsim") && g_hs.load_contig && g_hs.process_batch_pe;
+    fprintf(stderr, "feed_mock: stage 2 through %s%s\n", so, g_hs.stage1 ? ", the mapping batches too" : "");
     if (!g_hs.create || !g_hs.set_text || !g_hs.load_annotation || !g_hs.circ_single || !g_hs.circ_double) { fprintf(stderr, "feed_mock: symbols missing in %s\n", so); exit(1); }
     g_hs.state = 1;
     return true;
@@ -68,6 +79,7 @@ template <class T> struct MockBuf {
 };
 struct MockContig {
     std::vector<char> text;
+    const void *loaded_for = nullptr;
     std::vector<uint32_t> pos, off;     // ws-mer index of the contig: positions (1-based) sorted by (hash, position), run offsets
     int ws = 0;
     cm_annot_flat flat;
@@ -140,16 +152,23 @@ int cm_gpu_load_contig(cm_gpu_ctx *, int, const void *const *, const void *, uin
 // With it the stand-in also answers cm_gpu_circ_single_batch / cm_gpu_circ_double_batch, so the drop-in's do_process
 // (integration/gpu_circ_detect.cpp) runs on the CPU and its candidates.pam / circ_report can be compared with the reference's.
 // Without it those two entries fail and the tests run the binary with CM_GPU_STAGE2=0.
+std::mutex g_mock_mu;   // the shim builds the contig on all its devices at once; here they are one host-build context
 int cm_gpu_build_contig_packed(cm_gpu_ctx *, int c, const uint64_t *, uint32_t len) {
+    std::lock_guard<std::mutex> lk(g_mock_mu);
     if (!mock_hs_load()) return CM_OK;
+    if (g_mock_contigs.count(c) && g_mock_contigs[c].text.size() == len && g_mock_contigs[c].loaded_for == _ih_crefGen) return CM_OK;   // another device's copy
     std::vector<char> text((size_t) len + 2);
     if (!genome_seeder.pac2char_otf(1, (int) len, text.data())) return CM_ERR_STATE;   // the contig the reference has just loaded
     MockContig &m = g_mock_contigs[c];
     m.text.assign(text.begin(), text.begin() + len);
+    m.loaded_for = _ih_crefGen;
     m.pos.clear(); m.off.clear(); m.ws = 0;
+    if (g_hs.stage1)   // with the k-mer table the reference has just loaded (what cm_gpu_load_contig takes)
+        return g_hs.load_contig(mock_hs_ctx(), c, (const void *const *) _ih_hashTable, _ih_hashTableMem, (const uint8_t *) m.text.data(), len) == 0 ? CM_OK : CM_ERR_STATE;
     return g_hs.set_text(mock_hs_ctx(), c, (const uint8_t *) m.text.data(), len) == 0 ? CM_OK : CM_ERR_STATE;
 }
 int cm_gpu_load_annotation(cm_gpu_ctx *, int c, const cm_annot_flat *A) {
+    std::lock_guard<std::mutex> lk(g_mock_mu);
     // the two bit vectors as the shim hands them over (copied by words from the std::bitsets) against the bitsets read bit by bit
     for (uint64_t k = 0; k < A->n_bits; k++) {
         const bool nb = (size_t) c < near_border_bs.size() && near_border_bs[c][k], in = (size_t) c < intronic_bs.size() && intronic_bs[c][k];
@@ -173,6 +192,7 @@ int cm_gpu_circ_single_batch(cm_gpu_ctx *, int c, uint32_t n, const char *s1, co
                              uint32_t *n_att, uint32_t *att_pair, uint8_t *att_r1p, cm_circ_mate *in_r1, cm_circ_mate *in_r2, cm_circ_mate *in_pm,
                              int32_t *ret, cm_circ_res *cr, cm_circ_mate *out_r1, cm_circ_mate *out_r2, cm_circ_mate *out_pm, int32_t *best_type,
                              cm_circ_res *best_cr) {
+    std::lock_guard<std::mutex> lk(g_mock_mu);
     if (!mock_hs_load()) return CM_ERR_STATE;
     if (n_att) *n_att = 0;
     if (n == 0) return CM_OK;
@@ -193,6 +213,7 @@ int cm_gpu_circ_double_batch(cm_gpu_ctx *, int c, uint32_t n, const char *s1, co
                              const cm_mread *mr, const uint32_t *goff, const uint32_t *gs, const uint32_t *ge, int ws, int step, uint32_t cap,
                              uint32_t *n_ev, uint32_t *ev_pair, uint8_t *ev_kind, cm_circ_mate *ev_r1, cm_circ_mate *ev_r2, cm_circ_mate *ev_p1,
                              cm_circ_mate *ev_p2, int32_t *ev_ret, cm_circ_res *ev_cr, int32_t *push_type, cm_circ_res *push_cr) {
+    std::lock_guard<std::mutex> lk(g_mock_mu);
     if (!mock_hs_load()) return CM_ERR_STATE;
     if (n_ev) *n_ev = 0;
     if (n == 0) return CM_OK;
@@ -212,8 +233,10 @@ int cm_gpu_circ_double_batch(cm_gpu_ctx *, int c, uint32_t n, const char *s1, co
 int cm_gpu_host_alloc(size_t bytes, void **out) { *out = malloc(bytes ? bytes : 1); return *out ? CM_OK : CM_ERR_ALLOC; }
 int cm_gpu_host_free(void *p) { free(p); return CM_OK; }
 
-int cm_gpu_process_batch_pe(cm_gpu_ctx *, int, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
+int cm_gpu_process_batch_pe(cm_gpu_ctx *, int contig, uint32_t n, const char *seqs1, const char *seqs2, uint32_t stride,
                             const uint16_t *len1, const uint16_t *len2, const cm_mread *in, cm_mread *out, int32_t *state) {
+    if (mock_hs_load() && g_hs.stage1)   // the device code's host build instead of the reference's process_read
+        return g_hs.process_batch_pe(mock_hs_ctx(), contig, n, seqs1, seqs2, stride, len1, len2, in, out, state, nullptr) == 0 ? CM_OK : CM_ERR_STATE;
     static std::mutex mu;   // the shim runs one host thread per context; the reference's scratch here is thread 0's
     std::lock_guard<std::mutex> lk(mu);
     static Record *r1 = nullptr, *r2 = nullptr;

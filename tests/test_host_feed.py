@@ -26,6 +26,7 @@ def _run(binary, w, out, threads, env=None, extra=()):
     e.update(env or {})
     p = subprocess.run(cmd, capture_output=True, text=True, env=e, timeout=1500)
     assert p.returncode == 0, (p.stdout + p.stderr)[-2000:]
+    return p.stdout + p.stderr
 
 
 @pytest.fixture(scope="module")
@@ -157,3 +158,27 @@ def test_stage2_of_the_dropin_on_the_cpu(dataset, tmp_path, variant):
     assert "bit vectors copied by words" in log and "read bit by bit" not in log, log[-1500:]
     redone = int(re.search(r"\((\d+) of them redone after a device list overflowed\)", log).group(1))
     assert (redone > 0) == (variant == "smallcap"), (variant, redone)
+
+
+@pytest.mark.skipif(not (has_ref() and os.path.exists(FEED)), reason="oracle/_ref/circminer_feedtest not built")
+@pytest.mark.parametrize("scan", ["0", "2"])
+def test_whole_dropin_over_the_host_build(dataset, tmp_path, scan):
+    """Both stages of the drop-in binary with the device code's host build behind the C-ABI stand-in (CM_MOCK_STAGE1=hostsim: the mapping
+    batches too, not the reference's process_read): the product's logic -- shim, host feed, device functions, stage-2 orchestration --
+    inside the reference's own driver on a box without a GPU.  Every output file byte for byte against the reference binary."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from hostsim_api import build
+    build("libhostsim.so")
+    w = dataset
+    ref_out, feed_out = str(tmp_path / "ref"), str(tmp_path / "feed")
+    _run(REF, w, ref_out, 1, extra=("-a", scan))
+    log = _run(FEED, w, feed_out, 3, env={"CM_GPU_BATCH": "1500", "CM_GPU_DEVICES": "0,0", "CM_MOCK_STAGE1": "hostsim",
+                                          "CM_MOCK_HOSTSIM": os.path.join(ROOT, "tests", "hostsim", "libhostsim.so")}, extra=("-a", scan))
+    assert "the mapping batches too" in log, log[-800:]
+    ref_files = sorted(os.path.basename(f)[3:] for f in glob.glob(ref_out + "*") if os.path.isfile(f))
+    feed_files = sorted(os.path.basename(f)[4:] for f in glob.glob(feed_out + "*") if os.path.isfile(f))
+    assert ref_files == feed_files and any(f.endswith("circ_report") for f in ref_files), (ref_files, feed_files)
+    for suffix in ref_files:
+        a, b = ref_out + suffix, feed_out + suffix
+        assert filecmp.cmp(a, b, shallow=False), f"{suffix} differs ({os.path.getsize(a)} vs {os.path.getsize(b)} bytes)"
+    assert os.path.getsize(ref_out + ".mapping.pam") > 10000 and os.path.getsize(ref_out + ".candidates.pam") > 1000
