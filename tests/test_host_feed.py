@@ -3,7 +3,8 @@ PAM / remain-FASTQ text in input order) checked on the CPU: oracle/_ref/circmine
 stand-in for the C-ABI that answers each batch with the reference's own process_read (tests/hostfeed/feed_mock.cpp), so
 every byte that differs from the reference binary is a host-feed bug.  Two packed contigs = two rounds, the second one
 parsing the 23-token headers the first one wrote.  Stage 2 of the drop-in (integration/gpu_circ_detect.cpp) runs here as well,
-with the batch entries answered by the host build of the device code.  The GPU counterpart is tests/test_gpu_dropin.py."""
+with the batch entries answered by the host build of the device code, and in one test the mapping batches go through that build too.
+The GPU counterpart is tests/test_gpu_dropin.py."""
 import filecmp
 import glob
 import os
