@@ -21,7 +21,8 @@ def run(binary,out,env=None,threads=8):
     if pr.returncode: print((pr.stdout+pr.stderr)[-1500:])
     return pr.stdout+pr.stderr
 run(ROOT+"/oracle/_ref/circminer", d+"/ref")
-log=run(ROOT+"/oracle/_ref/circminer_feedtest", d+"/feed", env={"CM_GPU_BATCH":"20000","CM_GPU_VERBOSE":"1","CM_MOCK_HOSTSIM":ROOT+"/tests/hostsim/"+os.environ.get("CM_CHECK_HOSTSIM","libhostsim.so")})
+stage1 = {"CM_MOCK_STAGE1": "hostsim"} if os.environ.get("CM_CHECK_STAGE1") else {}   # the mapping batches through the host build too
+log=run(ROOT+"/oracle/_ref/circminer_feedtest", d+"/feed", env={**stage1, "CM_GPU_BATCH":"20000","CM_GPU_VERBOSE":"1","CM_MOCK_HOSTSIM":ROOT+"/tests/hostsim/"+os.environ.get("CM_CHECK_HOSTSIM","libhostsim.so")})
 for ln in log.splitlines():
     if 'stage 2' in ln: print(ln[:300])
 for suf in (".candidates.pam",".circ_report"):
