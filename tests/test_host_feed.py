@@ -162,15 +162,41 @@ def test_stage2_of_the_dropin_on_the_cpu(dataset, tmp_path, variant):
 
 
 @pytest.mark.skipif(not (has_ref() and os.path.exists(FEED)), reason="oracle/_ref/circminer_feedtest not built")
-@pytest.mark.parametrize("scan", ["0", "2"])
-def test_whole_dropin_over_the_host_build(dataset, tmp_path, scan):
+@pytest.mark.parametrize("case", ["scan0", "scan2", "dirty"])
+def test_whole_dropin_over_the_host_build(dataset, tmp_path, case):
     """Both stages of the drop-in binary with the device code's host build behind the C-ABI stand-in (CM_MOCK_STAGE1=hostsim: the mapping
     batches too, not the reference's process_read): the product's logic -- shim, host feed, device functions, stage-2 orchestration --
-    inside the reference's own driver on a box without a GPU.  Every output file byte for byte against the reference binary."""
+    inside the reference's own driver on a box without a GPU.  Every output file byte for byte against the reference binary; "dirty":
+    reads with runs of N, lower-case stretches and lengths of 22 .. 45 bases among the others."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from hostsim_api import build
     build("libhostsim.so")
     w = dataset
+    scan = "2" if case == "scan2" else "0"
+    if case == "dirty":                              # runs of N, lower-case stretches, reads of 22 .. 45 bases
+        import random
+        rnd = random.Random(11)
+        w = dict(w)
+        for key in ("fq1", "fq2"):
+            dst = str(tmp_path / (key + ".fastq"))
+            with open(dataset[key]) as f, open(dst, "w") as g:
+                while True:
+                    h = f.readline()
+                    if not h:
+                        break
+                    seq, plus, qual = f.readline().rstrip("\n"), f.readline(), f.readline().rstrip("\n")
+                    r = rnd.random()
+                    if r < 0.06:
+                        a, n = rnd.randint(0, len(seq) - 6), rnd.randint(1, 5)
+                        seq = seq[:a] + "N" * n + seq[a + n:]
+                    elif r < 0.12:
+                        a = rnd.randint(0, len(seq) - 30)
+                        seq = seq[:a] + seq[a:a + 30].lower() + seq[a + 30:]
+                    elif r < 0.18:
+                        n = rnd.randint(22, 45)
+                        seq, qual = seq[:n], qual[:n]
+                    g.write(h + seq + "\n" + plus + qual + "\n")
+            w[key] = dst
     ref_out, feed_out = str(tmp_path / "ref"), str(tmp_path / "feed")
     _run(REF, w, ref_out, 1, extra=("-a", scan))
     log = _run(FEED, w, feed_out, 3, env={"CM_GPU_BATCH": "1500", "CM_GPU_DEVICES": "0,0", "CM_MOCK_STAGE1": "hostsim",
