@@ -209,3 +209,35 @@ def test_whole_dropin_over_the_host_build(dataset, tmp_path, case):
         a, b = ref_out + suffix, feed_out + suffix
         assert filecmp.cmp(a, b, shallow=False), f"{suffix} differs ({os.path.getsize(a)} vs {os.path.getsize(b)} bytes)"
     assert os.path.getsize(ref_out + ".mapping.pam") > 10000 and os.path.getsize(ref_out + ".candidates.pam") > 1000
+
+
+@pytest.mark.skipif(not (has_ref() and os.path.exists(FEED)), reason="oracle/_ref/circminer_feedtest not built")
+def test_whole_dropin_over_the_host_build_k14_compact(tmp_path):
+    """C5's shape in small (T2: 2x250, k = 14 on a compact index, two packed contigs) through both stages of the drop-in over the host
+    build: other seed geometry, longer reads and stage-2 windows than the k = 20 cases.  Every output file byte for byte."""
+    from circminer_b200 import workload
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from hostsim_api import build
+    build("libhostsim.so")
+    w = workload.prepare("T2", str(tmp_path / "t2"), contig_size=1_600_000, write_reads=True)
+    subprocess.run([sys.executable, "-c",
+                    "import sys; sys.path.insert(0, %r)\n"
+                    "from oracle.refharness import RefHarness, default_params\n"
+                    "RefHarness(default_params(kmer=14)).build_index(%r, contig_size=1600000, compact=True)" % (ROOT, w["fa"])],
+                   check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=900)
+    ref_out, feed_out = str(tmp_path / "ref"), str(tmp_path / "feed")
+
+    def run(binary, out, threads, env=None):
+        cmd = [binary, "-r", w["fa"], "-g", w["gtf"], "-1", w["fq1"], "-2", w["fq2"], "-k", "14", "-t", str(threads), "-P", "-z", "-o", out]
+        p = subprocess.run(cmd, capture_output=True, text=True, env=dict(os.environ, LC_ALL="C", **(env or {})), timeout=1500)
+        assert p.returncode == 0, (p.stdout + p.stderr)[-2000:]
+        return p.stdout + p.stderr
+    run(REF, ref_out, 1)
+    log = run(FEED, feed_out, 3, {"CM_GPU_BATCH": "1000", "CM_MOCK_STAGE1": "hostsim", "CM_MOCK_HOSTSIM": os.path.join(ROOT, "tests", "hostsim", "libhostsim.so")})
+    assert "the mapping batches too" in log and "Genome index type: Compact" in log, log[-800:]
+    ref_files = sorted(os.path.basename(f)[3:] for f in glob.glob(ref_out + "*") if os.path.isfile(f))
+    feed_files = sorted(os.path.basename(f)[4:] for f in glob.glob(feed_out + "*") if os.path.isfile(f))
+    assert ref_files == feed_files and any(f.endswith("circ_report") for f in ref_files), (ref_files, feed_files)
+    for suffix in ref_files:
+        assert filecmp.cmp(ref_out + suffix, feed_out + suffix, shallow=False), f"{suffix} differs"
+    assert os.path.getsize(ref_out + ".candidates.pam") > 1000
