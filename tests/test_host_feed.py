@@ -162,12 +162,13 @@ def test_stage2_of_the_dropin_on_the_cpu(dataset, tmp_path, variant):
 
 
 @pytest.mark.skipif(not (has_ref() and os.path.exists(FEED)), reason="oracle/_ref/circminer_feedtest not built")
-@pytest.mark.parametrize("case", ["scan0", "scan2", "dirty"])
+@pytest.mark.parametrize("case", ["scan0", "scan2", "dirty", "params"])
 def test_whole_dropin_over_the_host_build(dataset, tmp_path, case):
     """Both stages of the drop-in binary with the device code's host build behind the C-ABI stand-in (CM_MOCK_STAGE1=hostsim: the mapping
     batches too, not the reference's process_read): the product's logic -- shim, host feed, device functions, stage-2 orchestration --
     inside the reference's own driver on a box without a GPU.  Every output file byte for byte against the reference binary; "dirty":
-    reads with runs of N, lower-case stretches and lengths of 22 .. 45 bases among the others."""
+    reads with runs of N, lower-case stretches and lengths of 22 .. 45 bases among the others; "params": maximum edit distance 6, soft
+    clip 10, band 5, seed limit 50, template length 800, intron 500 000, chain length 12, read length 200."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from hostsim_api import build
     build("libhostsim.so")
@@ -198,9 +199,12 @@ def test_whole_dropin_over_the_host_build(dataset, tmp_path, case):
                     g.write(h + seq + "\n" + plus + qual + "\n")
             w[key] = dst
     ref_out, feed_out = str(tmp_path / "ref"), str(tmp_path / "feed")
-    _run(REF, w, ref_out, 1, extra=("-a", scan))
+    extra = ("-a", scan)
+    if case == "params":                             # every mapping parameter off its default (cm_params as the shim fills it)
+        extra += ("-e", "6", "-c", "10", "-w", "5", "-S", "50", "-T", "800", "-I", "500000", "-C", "12", "-l", "200")
+    _run(REF, w, ref_out, 1, extra=extra)
     log = _run(FEED, w, feed_out, 3, env={"CM_GPU_BATCH": "1500", "CM_GPU_DEVICES": "0,0", "CM_MOCK_STAGE1": "hostsim",
-                                          "CM_MOCK_HOSTSIM": os.path.join(ROOT, "tests", "hostsim", "libhostsim.so")}, extra=("-a", scan))
+                                          "CM_MOCK_HOSTSIM": os.path.join(ROOT, "tests", "hostsim", "libhostsim.so")}, extra=extra)
     assert "the mapping batches too" in log, log[-800:]
     ref_files = sorted(os.path.basename(f)[3:] for f in glob.glob(ref_out + "*") if os.path.isfile(f))
     feed_files = sorted(os.path.basename(f)[4:] for f in glob.glob(feed_out + "*") if os.path.isfile(f))
