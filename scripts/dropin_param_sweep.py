@@ -5,13 +5,14 @@ python scripts/dropin_param_sweep.py -w 7 -e 8 -c 12"""
 import os, subprocess, sys, filecmp, glob
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
 from circminer_b200 import workload
-D = os.environ.get('CM_CHECK_DIR', '/tmp/cm_param_sweep')
+K = os.environ.get('CM_CHECK_K', '20')               # k-mer size: its own data directory, the index is built at that k
+D = os.environ.get('CM_CHECK_DIR', '/tmp/cm_param_sweep') + ('' if K == '20' else '_k' + K)
 w = workload.prepare("T1", os.path.join(D, 't1'), contig_size=3_500_000, n_pairs=6000, write_reads=True)
 if not os.path.exists(w['fa'] + '.packed.fa.index'):
-    subprocess.run([sys.executable, '-c', 'import sys; sys.path.insert(0, %r)\nfrom oracle.refharness import RefHarness, default_params\nRefHarness(default_params()).build_index(%r, contig_size=3500000)' % (ROOT, w['fa'])], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    subprocess.run([sys.executable, '-c', 'import sys; sys.path.insert(0, %r)\nfrom oracle.refharness import RefHarness, default_params\nRefHarness(default_params(kmer=%s)).build_index(%r, contig_size=3500000)' % (ROOT, K, w['fa'])], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
 extra=sys.argv[1:]
 def run(binary,out,threads,env=None):
-    cmd=[binary,"-r",w["fa"],"-g",w["gtf"],"-1",w["fq1"],"-2",w["fq2"],"-k","20","-t",str(threads),"-P","-z","-o",out,*extra]
+    cmd=[binary,"-r",w["fa"],"-g",w["gtf"],"-1",w["fq1"],"-2",w["fq2"],"-k",K,"-t",str(threads),"-P","-z","-o",out,*extra]
     e=dict(os.environ,LC_ALL="C"); e.update(env or {})
     p=subprocess.run(cmd,capture_output=True,text=True,env=e)
     return p.returncode, p.stdout+p.stderr
